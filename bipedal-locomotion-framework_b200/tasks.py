@@ -1,0 +1,147 @@
+"""Task descriptions for the batched QPInverseKinematics problem.
+
+One ``TaskSpec`` per reference task object; the fields are the reference's
+parameter-handler keys:
+
+* ``SE3Task``  -- ``frame_name, kp_linear, kp_angular, mask``      (src/IK/src/SE3Task.cpp:114-214)
+* ``CoMTask``  -- ``kp_linear, mask``                               (src/IK/src/CoMTask.cpp:107-162)
+* ``SO3Task``  -- ``frame_name, kp_angular``                        (src/IK/src/SO3Task.cpp:67-151)
+* ``R3Task``   -- ``frame_name, kp_linear, mask``                   (src/IK/src/R3Task.cpp:60-176)
+* ``JointTrackingTask`` -- ``kp``                                   (src/IK/src/JointTrackingTask.cpp:90-112)
+* ``JointLimitsTask``   -- ``klim, sampling_time, use_model_limits, upper_limits, lower_limits``
+                                                                    (src/IK/src/JointLimitsTask.cpp:136-198)
+* ``JointVelocityLimitsTask`` -- ``upper_limits, lower_limits``     (src/IK/src/JointVelocityLimitsTask.cpp:111-124)
+
+``priority`` 0 = hard constraint, 1 = weighted cost with ``weight``
+(QPInverseKinematics::addTask, src/IK/src/QPInverseKinematics.cpp:167-249).
+"""
+from __future__ import annotations
+
+import dataclasses
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from .models import KinematicModel
+
+# numeric ids shared with include/blfik.h
+TASK_SE3 = 0
+TASK_COM = 1
+TASK_SO3 = 2
+TASK_JOINT_TRACKING = 3
+TASK_JOINT_LIMITS = 4
+TASK_JOINT_VELOCITY_LIMITS = 5
+TASK_R3 = 6
+
+TYPE_NAMES = {TASK_SE3: "SE3Task", TASK_COM: "CoMTask", TASK_SO3: "SO3Task", TASK_JOINT_TRACKING: "JointTrackingTask",
+              TASK_JOINT_LIMITS: "JointLimitsTask", TASK_JOINT_VELOCITY_LIMITS: "JointVelocityLimitsTask", TASK_R3: "R3Task"}
+
+
+def _vec3(v) -> np.ndarray:
+    a = np.atleast_1d(np.asarray(v, dtype=np.float64))
+    if a.size == 1:
+        a = np.repeat(a, 3)
+    if a.size != 3:
+        raise ValueError("gain must be a scalar or a 3-vector")
+    return a.copy()
+
+
+@dataclasses.dataclass
+class TaskSpec:
+    name: str
+    type: int
+    priority: int = 0
+    frame: int = -1
+    mask: Sequence[bool] = (True, True, True)
+    controller_enabled: bool = True
+    kp_linear: np.ndarray = dataclasses.field(default_factory=lambda: np.zeros(3))
+    kp_angular: np.ndarray = dataclasses.field(default_factory=lambda: np.zeros(3))
+    kp_joint: Optional[np.ndarray] = None
+    weight: Optional[np.ndarray] = None
+    klim: Optional[np.ndarray] = None
+    upper: Optional[np.ndarray] = None
+    lower: Optional[np.ndarray] = None
+    sampling_time: float = 0.0
+
+    def rows(self, n: int) -> int:
+        nm = int(sum(bool(m) for m in self.mask))
+        return {TASK_SE3: nm + 3, TASK_COM: nm, TASK_R3: nm, TASK_SO3: 3, TASK_JOINT_TRACKING: n,
+                TASK_JOINT_LIMITS: 2 * n, TASK_JOINT_VELOCITY_LIMITS: 2 * n}[self.type]
+
+    def setpoint_len(self, n: int) -> int:
+        return {TASK_SE3: 13, TASK_COM: 6, TASK_SO3: 7, TASK_R3: 6, TASK_JOINT_TRACKING: 2 * n,
+                TASK_JOINT_LIMITS: 0, TASK_JOINT_VELOCITY_LIMITS: 0}[self.type]
+
+    @property
+    def is_inequality(self) -> bool:
+        return self.type in (TASK_JOINT_LIMITS, TASK_JOINT_VELOCITY_LIMITS)
+
+
+def se3_task(model: KinematicModel, name: str, frame_name: str, kp_linear, kp_angular, priority=0,
+             weight=None, mask=(True, True, True)) -> TaskSpec:
+    t = TaskSpec(name, TASK_SE3, priority, model.frame_index(frame_name), tuple(mask), True, _vec3(kp_linear), _vec3(kp_angular))
+    t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
+    return t
+
+
+def com_task(model: KinematicModel, name: str, kp_linear, priority=0, weight=None, mask=(True, True, True)) -> TaskSpec:
+    t = TaskSpec(name, TASK_COM, priority, -1, tuple(mask), True, _vec3(kp_linear))
+    t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
+    return t
+
+
+def so3_task(model: KinematicModel, name: str, frame_name: str, kp_angular, priority=1, weight=None) -> TaskSpec:
+    t = TaskSpec(name, TASK_SO3, priority, model.frame_index(frame_name), (True, True, True), True, np.zeros(3), _vec3(kp_angular))
+    t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
+    return t
+
+
+def r3_task(model: KinematicModel, name: str, frame_name: str, kp_linear, priority=0, weight=None, mask=(True, True, True)) -> TaskSpec:
+    t = TaskSpec(name, TASK_R3, priority, model.frame_index(frame_name), tuple(mask), True, _vec3(kp_linear))
+    t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
+    return t
+
+
+def joint_tracking_task(model: KinematicModel, name: str, kp, priority=1, weight=None) -> TaskSpec:
+    kp = np.asarray(kp, dtype=np.float64)
+    if kp.size != model.n:
+        raise ValueError("kp size must equal the number of DoFs")  # JointTrackingTask.cpp:100-110
+    t = TaskSpec(name, TASK_JOINT_TRACKING, priority, kp_joint=kp.copy())
+    t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
+    return t
+
+
+def joint_limits_task(model: KinematicModel, name: str, klim, sampling_time: float, use_model_limits=True,
+                      upper_limits=None, lower_limits=None) -> TaskSpec:
+    klim = np.asarray(klim, dtype=np.float64)
+    if klim.size != model.n or np.any(klim < 0) or np.any(klim > 1):
+        raise ValueError("klim must have n entries in [0, 1]")  # JointLimitsTask.cpp:150-166
+    if sampling_time <= 0:
+        raise ValueError("sampling_time must be positive")  # JointLimitsTask.cpp:168-176
+    up = model.q_upper if use_model_limits else np.asarray(upper_limits, dtype=np.float64)
+    lo = model.q_lower if use_model_limits else np.asarray(lower_limits, dtype=np.float64)
+    return TaskSpec(name, TASK_JOINT_LIMITS, 0, klim=klim.copy(), upper=up.copy(), lower=lo.copy(), sampling_time=float(sampling_time))
+
+
+def joint_velocity_limits_task(model: KinematicModel, name: str, upper_limits, lower_limits) -> TaskSpec:
+    up = np.asarray(upper_limits, dtype=np.float64)
+    lo = np.asarray(lower_limits, dtype=np.float64)
+    if up.size != model.n or lo.size != model.n:
+        raise ValueError("limits must have n entries")
+    return TaskSpec(name, TASK_JOINT_VELOCITY_LIMITS, 0, upper=up.copy(), lower=lo.copy())
+
+
+def validate_tasks(model: KinematicModel, tasks: List[TaskSpec]) -> None:
+    """addTask rules of QPInverseKinematics.cpp:167-249."""
+    names = set()
+    for t in tasks:
+        if t.name in names:
+            raise ValueError(f"task '{t.name}' already exists")
+        names.add(t.name)
+        if t.priority not in (0, 1):
+            raise ValueError("priority must be 0 or 1")
+        if t.is_inequality and t.priority != 0:
+            raise ValueError("inequality tasks can only be hard constraints")
+        if t.priority == 1:
+            if t.weight is None or np.asarray(t.weight).size != t.rows(model.n):
+                raise ValueError(f"task '{t.name}': a priority-1 task needs a weight of size {t.rows(model.n)}")
