@@ -1,0 +1,315 @@
+"""ctypes binding of the C ABI in ``include/blfik.h`` (``libblfik_cuda.so``).
+
+This is the only way Python reaches the GPU path: there is no CPU fallback and the
+library is loaded eagerly by ``load()``; a missing ``.so`` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from .models import KinematicModel
+from .tasks import TaskSpec
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libblfik_cuda.so")
+_lib = None
+
+MEM_HOST, MEM_DEVICE = 0, 1
+TICK_INTEGRATE, TICK_WARM_START = 1, 2
+DEBUG_H, DEBUG_G, DEBUG_CEQ, DEBUG_BEQ, DEBUG_LO, DEBUG_HI = range(6)
+
+c_double_p = C.POINTER(C.c_double)
+c_int_p = C.POINTER(C.c_int32)
+
+# every symbol include/blfik.h declares
+EXPORTS = [
+    "blfik_model_create", "blfik_model_destroy", "blfik_problem_create", "blfik_problem_destroy",
+    "blfik_default_settings", "blfik_set_solver_settings", "blfik_set_state", "blfik_get_state",
+    "blfik_set_setpoint", "blfik_setpoint_len", "blfik_set_weight", "blfik_set_gains",
+    "blfik_set_controller_mode", "blfik_tick", "blfik_get_output", "blfik_get_status",
+    "blfik_count_unsolved", "blfik_kinematics", "blfik_integrate", "blfik_debug_enable", "blfik_debug_get",
+    "blfik_num_dofs", "blfik_num_equality_rows", "blfik_num_instances", "blfik_sync", "blfik_get_stream",
+    "blfik_set_stream", "blfik_launch_count", "blfik_last_error",
+]
+
+
+class ModelDesc(C.Structure):
+    _fields_ = [("n_dofs", C.c_int32), ("n_frames", C.c_int32), ("parent", c_int_p), ("dof", c_int_p),
+                ("X_rot", c_double_p), ("X_pos", c_double_p), ("axis", c_double_p), ("mass", c_double_p),
+                ("com", c_double_p), ("frame_link", c_int_p), ("frame_rot", c_double_p), ("frame_pos", c_double_p)]
+
+
+class TaskDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("priority", C.c_int32), ("frame", C.c_int32), ("mask", C.c_int32 * 3),
+                ("controller_enabled", C.c_int32), ("kp_linear", C.c_double * 3), ("kp_angular", C.c_double * 3),
+                ("kp_joint", c_double_p), ("weight", c_double_p), ("klim", c_double_p),
+                ("upper_limits", c_double_p), ("lower_limits", c_double_p), ("sampling_time", C.c_double)]
+
+
+class SolverSettings(C.Structure):
+    _fields_ = [("rho", C.c_double), ("sigma", C.c_double), ("alpha", C.c_double), ("eps", C.c_double),
+                ("admm_iters", C.c_int32), ("max_rounds", C.c_int32), ("polish_iters", C.c_int32),
+                ("eq_iters", C.c_int32)]
+
+
+class BlfikError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"blfik error {code}: {msg}")
+        self.code = code
+
+
+def build(force: bool = False) -> str:
+    """Compile the CUDA library in-tree (nvcc, sm_100a)."""
+    srcdir = os.path.join(_HERE, "csrc")
+    srcs = [os.path.join(srcdir, f) for f in os.listdir(srcdir)] + [os.path.join(_HERE, "..", "include", "blfik.h")]
+    if force or not os.path.exists(LIB_PATH) or any(os.path.getmtime(s) > os.path.getmtime(LIB_PATH) for s in srcs):
+        subprocess.check_call(["make", "-C", srcdir, "-s", "NVFLAGS=-O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC"])
+    return LIB_PATH
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                    "(there is no CPU fallback)")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.blfik_last_error.restype = C.c_char_p
+        _lib.blfik_get_stream.restype = C.c_void_p
+        _lib.blfik_get_stream.argtypes = [C.c_void_p]
+        _lib.blfik_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.blfik_launch_count.restype = C.c_int64
+        _lib.blfik_launch_count.argtypes = [C.c_void_p]
+        _lib.blfik_num_instances.restype = C.c_int64
+        for name in ("blfik_num_instances", "blfik_num_dofs", "blfik_num_equality_rows", "blfik_problem_destroy",
+                     "blfik_model_destroy", "blfik_sync"):
+            getattr(_lib, name).argtypes = [C.c_void_p]
+        _lib.blfik_problem_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_void_p]
+        _lib.blfik_tick.argtypes = [C.c_void_p, C.c_int32, C.c_double, C.c_uint32]
+        _lib.blfik_integrate.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_int32]
+        _lib.blfik_set_state.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
+        _lib.blfik_get_state.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
+        _lib.blfik_set_setpoint.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+        _lib.blfik_get_output.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
+        _lib.blfik_get_status.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
+        _lib.blfik_debug_get.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+        _lib.blfik_debug_enable.argtypes = [C.c_void_p, C.c_int32]
+        _lib.blfik_kinematics.argtypes = [C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 5 + [C.c_int32]
+        _lib.blfik_set_weight.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+        _lib.blfik_set_gains.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib.blfik_set_controller_mode.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+        _lib.blfik_count_unsolved.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.blfik_set_solver_settings.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.blfik_setpoint_len.argtypes = [C.c_void_p, C.c_int32]
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise BlfikError(rc, load().blfik_last_error().decode())
+
+
+def _f64(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _ptr(a):
+    """numpy array / torch tensor / int device pointer / None -> (void*, is_device)."""
+    if a is None:
+        return None, False
+    if isinstance(a, int):
+        return C.c_void_p(a), True
+    if isinstance(a, np.ndarray):
+        assert a.dtype in (np.float64, np.int32) and a.flags.c_contiguous
+        return C.c_void_p(a.ctypes.data), False
+    # torch tensor (plumbing only: device memory + pinned host memory)
+    assert a.is_contiguous()
+    return C.c_void_p(a.data_ptr()), bool(a.is_cuda)
+
+
+class Model:
+    """Device-independent kinematic model handle (``blfik_model``)."""
+
+    def __init__(self, km: KinematicModel):
+        L = load()
+        self.km = km
+        k = dict(parent=np.ascontiguousarray(km.parent, dtype=np.int32), dof=np.ascontiguousarray(km.dof, dtype=np.int32),
+                 Xr=_f64(km.Xr), Xp=_f64(km.Xp), axis=_f64(km.axis), mass=_f64(km.mass), com=_f64(km.com),
+                 fl=np.ascontiguousarray(km.frame_link, dtype=np.int32), Fr=_f64(km.Fr), Fp=_f64(km.Fp))
+        d = ModelDesc(km.n, len(km.frame_names), k["parent"].ctypes.data_as(c_int_p), k["dof"].ctypes.data_as(c_int_p),
+                      k["Xr"].ctypes.data_as(c_double_p), k["Xp"].ctypes.data_as(c_double_p), k["axis"].ctypes.data_as(c_double_p),
+                      k["mass"].ctypes.data_as(c_double_p), k["com"].ctypes.data_as(c_double_p), k["fl"].ctypes.data_as(c_int_p),
+                      k["Fr"].ctypes.data_as(c_double_p), k["Fp"].ctypes.data_as(c_double_p))
+        self.handle = C.c_void_p()
+        _check(L.blfik_model_create(C.byref(d), C.byref(self.handle)))
+
+    def __del__(self):
+        if getattr(self, "handle", None) and _lib is not None:
+            _lib.blfik_model_destroy(self.handle)
+            self.handle = None
+
+
+def task_descs(tasks: Sequence[TaskSpec]):
+    keep: List[np.ndarray] = []
+    arr = (TaskDesc * max(1, len(tasks)))()
+
+    def dp(a):
+        if a is None:
+            return None
+        b = _f64(a)
+        keep.append(b)
+        return b.ctypes.data_as(c_double_p)
+
+    for i, t in enumerate(tasks):
+        d = arr[i]
+        d.type, d.priority, d.frame = int(t.type), int(t.priority), int(t.frame)
+        for c in range(3):
+            d.mask[c] = int(bool(t.mask[c]))
+            d.kp_linear[c] = float(t.kp_linear[c])
+            d.kp_angular[c] = float(t.kp_angular[c])
+        d.controller_enabled = int(bool(t.controller_enabled))
+        d.kp_joint, d.weight, d.klim = dp(t.kp_joint), dp(t.weight), dp(t.klim)
+        d.upper_limits, d.lower_limits = dp(t.upper), dp(t.lower)
+        d.sampling_time = float(t.sampling_time)
+    return arr, keep
+
+
+class Problem:
+    """A batch of N robots sharing one model and one task list on one GPU (``blfik_problem``)."""
+
+    def __init__(self, model: Model, tasks: Sequence[TaskSpec], n_instances: int, device: int = 0):
+        L = load()
+        self.L = L
+        self.model = model
+        self.tasks = list(tasks)
+        self.N = int(n_instances)
+        self.n = model.km.n
+        self.nv = self.n + 6
+        arr, keep = task_descs(self.tasks)
+        self.handle = C.c_void_p()
+        _check(L.blfik_problem_create(model.handle, arr, len(self.tasks), self.N, int(device), C.byref(self.handle)))
+        self.me = L.blfik_num_equality_rows(self.handle)
+        self.device = device
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.L.blfik_problem_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- settings
+    def set_solver(self, **kw) -> SolverSettings:
+        s = SolverSettings()
+        self.L.blfik_default_settings(C.byref(s))
+        for k, v in kw.items():
+            if not hasattr(s, k):
+                raise AttributeError(k)
+            setattr(s, k, v)
+        _check(self.L.blfik_set_solver_settings(self.handle, C.byref(s)))
+        return s
+
+    # ---- inputs
+    def set_state(self, base_pos, base_quat, s):
+        (p, dev), (q, _), (sj, _) = _ptr(base_pos), _ptr(base_quat), _ptr(s)
+        _check(self.L.blfik_set_state(self.handle, p, q, sj, MEM_DEVICE if dev else MEM_HOST))
+
+    def get_state(self):
+        p, q, s = np.empty((self.N, 3)), np.empty((self.N, 4)), np.empty((self.N, self.n))
+        _check(self.L.blfik_get_state(self.handle, p.ctypes.data, q.ctypes.data, s.ctypes.data, MEM_HOST))
+        return p, q, s
+
+    def set_setpoint(self, task: int, data):
+        ptr, dev = _ptr(data)
+        _check(self.L.blfik_set_setpoint(self.handle, int(task), ptr, MEM_DEVICE if dev else MEM_HOST))
+
+    def set_inputs(self, inp):
+        """``inp``: workloads.Inputs (host numpy)."""
+        self.set_state(_f64(inp.base_pos), _f64(inp.base_quat), _f64(inp.s))
+        for t, sp in enumerate(inp.setpoints):
+            if sp is not None:
+                self.set_setpoint(t, _f64(sp))
+
+    def set_weight(self, task: int, weight):
+        w = _f64(weight)
+        _check(self.L.blfik_set_weight(self.handle, int(task), w.ctypes.data))
+
+    def set_gains(self, task: int, kp_linear=None, kp_angular=None, kp_joint=None):
+        a = [None if v is None else _f64(v) for v in (kp_linear, kp_angular, kp_joint)]
+        _check(self.L.blfik_set_gains(self.handle, int(task), *[None if v is None else v.ctypes.data for v in a]))
+
+    def set_controller_mode(self, task: int, enabled: bool):
+        _check(self.L.blfik_set_controller_mode(self.handle, int(task), int(enabled)))
+
+    # ---- tick
+    def tick(self, nticks: int = 1, dt: float = 0.0, integrate: bool = False, warm_start: bool = False):
+        flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0)
+        _check(self.L.blfik_tick(self.handle, int(nticks), float(dt), flags))
+
+    def get_output(self, out=None):
+        if out is None:
+            out = np.empty((self.N, self.nv))
+        ptr, dev = _ptr(out)
+        _check(self.L.blfik_get_output(self.handle, ptr, MEM_DEVICE if dev else MEM_HOST))
+        return out
+
+    def get_status(self):
+        st, it = np.empty(self.N, dtype=np.int32), np.empty(self.N, dtype=np.int32)
+        _check(self.L.blfik_get_status(self.handle, st.ctypes.data, it.ctypes.data, MEM_HOST))
+        return st, it
+
+    def count_unsolved(self) -> int:
+        c = C.c_int64(0)
+        _check(self.L.blfik_count_unsolved(self.handle, C.byref(c)))
+        return int(c.value)
+
+    # ---- stand-alone stages
+    def kinematics(self, frames: Sequence[int], jac: bool = True, com: bool = True):
+        fr = np.ascontiguousarray(frames, dtype=np.int32)
+        nf = len(fr)
+        fp, fR = np.empty((self.N, nf, 3)), np.empty((self.N, nf, 3, 3))
+        fJ = np.empty((self.N, nf, 6, self.nv)) if jac else None
+        c = np.empty((self.N, 3)) if com else None
+        cJ = np.empty((self.N, 3, self.nv)) if (com and jac) else None
+        _check(self.L.blfik_kinematics(self.handle, fr.ctypes.data if nf else None, nf, fp.ctypes.data if nf else None,
+                                       fR.ctypes.data if nf else None, None if fJ is None or not nf else fJ.ctypes.data,
+                                       None if c is None else c.ctypes.data, None if cJ is None else cJ.ctypes.data, MEM_HOST))
+        return dict(frame_pos=fp, frame_rot=fR, frame_jac=fJ, com=c, com_jac=cJ)
+
+    def integrate(self, nu=None, dt: float = 0.01, nsteps: int = 1):
+        ptr, dev = _ptr(None if nu is None else (nu if not isinstance(nu, np.ndarray) else _f64(nu)))
+        _check(self.L.blfik_integrate(self.handle, ptr, MEM_DEVICE if dev else MEM_HOST, float(dt), int(nsteps)))
+
+    # ---- introspection
+    def debug_enable(self, on: bool = True):
+        _check(self.L.blfik_debug_enable(self.handle, int(on)))
+
+    def debug_get(self, what: int) -> np.ndarray:
+        shape = {DEBUG_H: (self.N, self.nv, self.nv), DEBUG_G: (self.N, self.nv), DEBUG_CEQ: (self.N, self.me, self.nv),
+                 DEBUG_BEQ: (self.N, self.me), DEBUG_LO: (self.N, self.n), DEBUG_HI: (self.N, self.n)}[what]
+        out = np.empty(shape)
+        _check(self.L.blfik_debug_get(self.handle, int(what), out.ctypes.data, MEM_HOST))
+        return out
+
+    def sync(self):
+        _check(self.L.blfik_sync(self.handle))
+
+    @property
+    def stream(self) -> int:
+        return int(self.L.blfik_get_stream(self.handle) or 0)
+
+    def set_stream(self, cuda_stream: int):
+        _check(self.L.blfik_set_stream(self.handle, C.c_void_p(cuda_stream)))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.L.blfik_launch_count(self.handle))

@@ -1,0 +1,777 @@
+// blfik_capi.cu -- kernels + the C ABI of include/blfik.h (libblfik_cuda.so).
+// No torch types, no CPU fallback: every compute entry point needs a CUDA device.
+#include "../../include/blfik.h"
+#include "blfik_device.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace blfik;
+
+// =================================================================== kernels
+// The tick: K1 -> K2 -> K3 -> (K4), one warp per robot, `nticks` times per launch.
+__global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
+{
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const WM w = carve(smem + (size_t)wib * P.L.total, P.L);
+    const int n = P.m.n, nv = P.L.nv;
+    for (long long robot = (long long)blockIdx.x * wpb + wib; robot < P.N; robot += (long long)gridDim.x * wpb) {
+        double* bp = P.base_pos + 3 * robot;
+        double* bq = P.base_quat + 4 * robot;
+        double* s = P.s + (size_t)n * robot;
+        bool warm = (P.flags & BLFIK_TICK_WARM_START) != 0;
+        if (warm) {
+            for (int i = lane; i < nv; i += 32) {
+                w.x[i] = P.wx[(size_t)nv * robot + i];
+                w.z[i] = i >= 6 ? P.wz[(size_t)n * robot + i - 6] : 0.0;
+                w.y[i] = i >= 6 ? P.wy[(size_t)n * robot + i - 6] : 0.0;
+            }
+        }
+        QpResult res = {2, 0};
+        int iters = 0;
+        for (int tick = 0; tick < P.nticks; tick++) {
+            k1_fk(P.m, w, bp, bq, s, lane);
+            k2_assemble(P, w, robot, s, lane);
+            if (P.dbg.H && tick == 0) {
+                const int me = P.L.me, LD = P.L.LD;
+                for (int i = lane; i < nv; i += 32) {
+                    for (int j = 0; j < nv; j++) P.dbg.H[((size_t)robot * nv + i) * nv + j] = w.Hs[i * LD + j];
+                    P.dbg.g[(size_t)robot * nv + i] = w.g[i];
+                    for (int r = 0; r < me; r++) P.dbg.Ceq[((size_t)robot * me + r) * nv + i] = w.Cs[r * LD + i];
+                    if (i >= 6) {
+                        P.dbg.lo[(size_t)robot * n + i - 6] = w.lo[i];
+                        P.dbg.hi[(size_t)robot * n + i - 6] = w.hi[i];
+                    }
+                }
+                for (int r = lane; r < me; r += 32) P.dbg.beq[(size_t)robot * me + r] = w.b[r];
+            }
+            res = k3_solve(P, w, warm, lane);
+            iters += res.iters;
+            warm = (P.flags & BLFIK_TICK_WARM_START) != 0;
+            for (int i = lane; i < nv; i += 32) P.nu[(size_t)nv * robot + i] = w.x[i];
+            __syncwarp();
+            if (P.flags & BLFIK_TICK_INTEGRATE) k4_integrate(n, bp, bq, s, w.x, P.dt, lane);
+        }
+        for (int i = lane; i < nv; i += 32) {
+            P.wx[(size_t)nv * robot + i] = w.x[i];
+            if (i >= 6) {
+                P.wz[(size_t)n * robot + i - 6] = w.z[i];
+                P.wy[(size_t)n * robot + i - 6] = w.y[i];
+            }
+        }
+        if (lane == 0) {
+            P.status[robot] = res.status;
+            P.iters[robot] = iters;
+        }
+        __syncwarp();
+    }
+}
+
+// K1 stand-alone: frame poses, frame Jacobians, CoM and CoM Jacobian of the current state.
+__global__ void __launch_bounds__(256) blfik_kinematics_kernel(const KinParams P)
+{
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const WM w = carve(smem + (size_t)wib * P.L.total, P.L);
+    const int n = P.m.n, nv = n + 6, LD = P.L.LD;
+    for (long long robot = (long long)blockIdx.x * wpb + wib; robot < P.N; robot += (long long)gridDim.x * wpb) {
+        k1_fk(P.m, w, P.base_pos + 3 * robot, P.base_quat + 4 * robot, P.s + (size_t)n * robot, lane);
+        for (int f = 0; f < P.nframes; f++) {
+            double R[9], pf[3];
+            const int fr = P.frames[f];
+            k1_frame_pose(P.m, w, fr, R, pf);
+            const size_t o = (size_t)robot * P.nframes + f;
+            if (P.frame_pos && lane < 3) P.frame_pos[o * 3 + lane] = pf[lane];
+            if (P.frame_rot && lane < 9) P.frame_rot[o * 9 + lane] = R[lane];
+            if (P.frame_jac) {
+                k1_frame_jac(P.m, w, P.m.frame_link[fr], pf, w.Jt, LD, lane);
+                __syncwarp();
+                for (int r = 0; r < 6; r++)
+                    for (int c = lane; c < nv; c += 32) P.frame_jac[(o * 6 + r) * nv + c] = w.Jt[r * LD + c];
+                __syncwarp();
+            }
+        }
+        if (P.com || P.com_jac) {
+            double com[3];
+            k1_com(P.m, w, com, P.com_jac ? w.Jt : nullptr, LD, lane);
+            __syncwarp();
+            if (P.com && lane < 3) P.com[3 * robot + lane] = com[lane];
+            if (P.com_jac)
+                for (int r = 0; r < 3; r++)
+                    for (int c = lane; c < nv; c += 32) P.com_jac[((size_t)robot * 3 + r) * nv + c] = w.Jt[r * LD + c];
+        }
+        __syncwarp();
+    }
+}
+
+// K4 stand-alone: nsteps ForwardEuler steps with a held control input.
+__global__ void __launch_bounds__(256) blfik_integrate_kernel(int n, long long N, double* base_pos, double* base_quat,
+                                                              double* s, const double* nu, double dt, int nsteps)
+{
+    const int lane = threadIdx.x & 31;
+    const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long robot = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; robot < N; robot += warps)
+        for (int k = 0; k < nsteps; k++)
+            k4_integrate(n, base_pos + 3 * robot, base_quat + 4 * robot, s + (size_t)n * robot,
+                         nu + (size_t)(n + 6) * robot, dt, lane);
+}
+
+__global__ void blfik_count_unsolved_kernel(const int* status, long long N, unsigned long long* out)
+{
+    unsigned long long c = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long long)gridDim.x * blockDim.x)
+        c += status[i] != 0;
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(kFull, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+// =================================================================== host side
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess) return fail(BLFIK_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct blfik_model {
+    int n = 0, nf = 0, maxdepth = 0;
+    std::vector<int> parent, dof, depth, link_of_dof, frame_link;
+    std::vector<unsigned long long> anc;
+    std::vector<double> Xr, Xp, axis, mass, com, msub, Fr, Fp;
+    double total_mass = 0;
+};
+
+struct HostTask {
+    blfik_task_desc d;
+    std::vector<double> kp_joint, weight, klim, upper, lower;
+    int rows = 0, sp_len = 0, row_offset = 0;
+    bool setpoint_set = false;
+    double* d_setpoint = nullptr;
+    double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
+};
+
+struct blfik_problem {
+    const blfik_model* model = nullptr;
+    int device = 0;
+    long long N = 0;
+    int n = 0, nv = 0, me = 0;
+    std::vector<HostTask> tasks;
+    Settings st;
+    Layout L;
+    DevModel dm;
+    std::vector<void*> allocs;
+    DevTask* d_tasks = nullptr;
+    bool tasks_dirty = true;
+    double *base_pos = nullptr, *base_quat = nullptr, *s = nullptr, *nu = nullptr, *wx = nullptr, *wz = nullptr, *wy = nullptr;
+    int *status = nullptr, *iters = nullptr;
+    unsigned long long* d_count = nullptr;
+    bool state_set = false, ticked = false;
+    DebugOut dbg = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool debug = false;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int warps_per_block = 4, grid = 148;
+    size_t smem_bytes = 0;
+    int num_sms = 148;
+    long long launches = 0;
+};
+
+static int rows_of(const blfik_task_desc& d, int n)
+{
+    const int nm = (d.mask[0] != 0) + (d.mask[1] != 0) + (d.mask[2] != 0);
+    switch (d.type) {
+    case BLFIK_TASK_SE3: return nm + 3;
+    case BLFIK_TASK_COM: return nm;
+    case BLFIK_TASK_R3: return nm;
+    case BLFIK_TASK_SO3: return 3;
+    case BLFIK_TASK_JOINT_TRACKING: return n;
+    case BLFIK_TASK_JOINT_LIMITS: return 2 * n;
+    case BLFIK_TASK_JOINT_VELOCITY_LIMITS: return 2 * n;
+    default: return -1;
+    }
+}
+static int sp_len_of(int type, int n)
+{
+    switch (type) {
+    case BLFIK_TASK_SE3: return 13;
+    case BLFIK_TASK_COM: return 6;
+    case BLFIK_TASK_R3: return 6;
+    case BLFIK_TASK_SO3: return 7;
+    case BLFIK_TASK_JOINT_TRACKING: return 2 * n;
+    default: return 0;
+    }
+}
+static bool is_dense(int type) { return type == BLFIK_TASK_SE3 || type == BLFIK_TASK_COM || type == BLFIK_TASK_SO3 || type == BLFIK_TASK_R3; }
+static bool is_inequality(int type) { return type == BLFIK_TASK_JOINT_LIMITS || type == BLFIK_TASK_JOINT_VELOCITY_LIMITS; }
+
+extern "C" const char* blfik_last_error(void) { return g_err.c_str(); }
+
+extern "C" void blfik_default_settings(blfik_solver_settings* s)
+{
+    if (!s) return;
+    s->rho = 1.0, s->sigma = 1e-3, s->alpha = 1.6, s->eps = 1e-7;
+    s->admm_iters = 10, s->max_rounds = 20, s->polish_iters = 4, s->eq_iters = 5;
+}
+
+// ------------------------------------------------------------------- model
+extern "C" int blfik_model_create(const blfik_model_desc* d, blfik_model** out)
+{
+    if (!d || !out) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] null argument");
+    const int n = d->n_dofs, nl = n + 1, nf = d->n_frames;
+    if (n < 1 || n > 58) return fail(BLFIK_ERR_UNSUPPORTED, "[blfik_model_create] n_dofs must be in [1, 58], got %d", n);
+    if (nf < 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] negative n_frames");
+    if (!d->parent || !d->dof || !d->X_rot || !d->X_pos || !d->axis || !d->mass || !d->com || (nf && (!d->frame_link || !d->frame_rot || !d->frame_pos)))
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] null array in the model description");
+    blfik_model* m = new (std::nothrow) blfik_model;
+    if (!m) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] out of host memory");
+    m->n = n, m->nf = nf;
+    m->parent.assign(d->parent, d->parent + nl), m->dof.assign(d->dof, d->dof + nl);
+    m->Xr.assign(d->X_rot, d->X_rot + 9 * nl), m->Xp.assign(d->X_pos, d->X_pos + 3 * nl);
+    m->axis.assign(d->axis, d->axis + 3 * nl), m->mass.assign(d->mass, d->mass + nl), m->com.assign(d->com, d->com + 3 * nl);
+    m->frame_link.assign(d->frame_link, d->frame_link + nf);
+    m->Fr.assign(d->frame_rot, d->frame_rot + 9 * nf), m->Fp.assign(d->frame_pos, d->frame_pos + 3 * nf);
+    m->depth.assign(nl, 0), m->anc.assign(nl, 0ull), m->link_of_dof.assign(n, -1), m->msub.assign(n, 0.0);
+    std::vector<char> seen(n, 0);
+    if (m->parent[0] != -1) { delete m; return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] parent[0] must be -1"); }
+    for (int k = 1; k < nl; k++) {
+        const int p = m->parent[k], j = m->dof[k];
+        if (p < 0 || p >= k) { delete m; return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] links must be topologically ordered (parent[%d]=%d)", k, p); }
+        if (j < 0 || j >= n || seen[j]) { delete m; return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] dof[] must be a permutation of 0..n-1"); }
+        seen[j] = 1;
+        m->link_of_dof[j] = k;
+        m->depth[k] = m->depth[p] + 1;
+        if (m->depth[k] > m->maxdepth) m->maxdepth = m->depth[k];
+        m->anc[k] = m->anc[p] | (1ull << j);
+    }
+    for (int k = 0; k < nl; k++) {
+        m->total_mass += m->mass[k];
+        for (int j = 0; j < n; j++)
+            if ((m->anc[k] >> j) & 1ull) m->msub[j] += m->mass[k];
+    }
+    if (!(m->total_mass > 0)) { delete m; return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] total mass must be positive"); }
+    for (int f = 0; f < nf; f++)
+        if (m->frame_link[f] < 0 || m->frame_link[f] >= nl) { delete m; return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_model_create] frame %d is attached to link %d", f, m->frame_link[f]); }
+    *out = m;
+    return BLFIK_OK;
+}
+
+extern "C" void blfik_model_destroy(blfik_model* m) { delete m; }
+
+// ------------------------------------------------------------------- problem
+template <typename T>
+static int dev_upload(blfik_problem* p, const std::vector<T>& v, T** out)
+{
+    *out = nullptr;
+    if (v.empty()) return BLFIK_OK;
+    void* ptr = nullptr;
+    CU(cudaMalloc(&ptr, v.size() * sizeof(T)));
+    p->allocs.push_back(ptr);
+    CU(cudaMemcpy(ptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    *out = static_cast<T*>(ptr);
+    return BLFIK_OK;
+}
+template <typename T>
+static int dev_alloc(blfik_problem* p, size_t count, T** out, bool zero = true)
+{
+    void* ptr = nullptr;
+    CU(cudaMalloc(&ptr, (count ? count : 1) * sizeof(T)));
+    p->allocs.push_back(ptr);
+    if (zero) CU(cudaMemset(ptr, 0, (count ? count : 1) * sizeof(T)));
+    *out = static_cast<T*>(ptr);
+    return BLFIK_OK;
+}
+
+static Layout make_layout(int n, int me)
+{
+    Layout L;
+    const int nv = n + 6, nl = n + 1;
+    L.nv = nv, L.me = me;
+    L.LD = (nv & 1) ? nv : nv + 1;
+    L.LDE = (me & 1) ? me : me + 1;
+    int o = 0;
+    auto take = [&](int cnt) { int r = o; o += (cnt + 1) & ~1; return r; };
+    L.linkR = take(9 * nl), L.linkP = take(3 * nl), L.axisW = take(3 * nl), L.mcw = take(3 * nl);
+    L.Hs = take(nv * L.LD), L.A = take(nv * L.LD), L.B = take(nv * L.LD);
+    L.Cs = take(me * L.LD), L.Ym = take(nv * L.LDE), L.Wm = take(nv * L.LDE), L.Ss = take(me * L.LDE), L.Jt = take(6 * L.LD);
+    const int vmax = nv > me ? nv : me;
+    L.g = take(nv), L.b = take(me), L.lo = take(nv), L.hi = take(nv), L.x = take(nv), L.z = take(nv), L.y = take(nv);
+    L.r = take(nv), L.xb = take(nv), L.wb = take(me), L.lam = take(vmax), L.gp = take(nv), L.bp = take(vmax), L.bd = take(nv), L.t = take(nv);
+    L.act = take((nv + 1) / 2 + 1);
+    L.total = o;
+    return L;
+}
+
+static int refresh_tasks(blfik_problem* p)
+{
+    if (!p->tasks_dirty) return BLFIK_OK;
+    std::vector<DevTask> dt(p->tasks.size());
+    for (size_t t = 0; t < p->tasks.size(); t++) {
+        HostTask& h = p->tasks[t];
+        DevTask& d = dt[t];
+        d.type = h.d.type, d.priority = h.d.priority, d.frame = h.d.frame, d.rows = h.rows, d.enabled = h.d.controller_enabled;
+        d.sp_len = h.sp_len, d.row_offset = h.row_offset;
+        for (int c = 0; c < 3; c++) d.mask[c] = h.d.mask[c] != 0, d.kp_lin[c] = h.d.kp_linear[c], d.kp_ang[c] = h.d.kp_angular[c];
+        auto up = [&](const std::vector<double>& v, double* dst) -> int {
+            if (!v.empty()) CU(cudaMemcpyAsync(dst, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+            return BLFIK_OK;
+        };
+        int rc;
+        if ((rc = up(h.kp_joint, h.d_kp_joint)) || (rc = up(h.weight, h.d_weight)) || (rc = up(h.klim, h.d_klim)) || (rc = up(h.upper, h.d_upper)) || (rc = up(h.lower, h.d_lower))) return rc;
+        d.kp_joint = h.d_kp_joint, d.weight = h.d_weight, d.klim = h.d_klim, d.upper = h.d_upper, d.lower = h.d_lower;
+        d.inv_dt = h.d.sampling_time > 0 ? 1.0 / h.d.sampling_time : 0.0;
+        d.setpoint = h.d_setpoint;
+    }
+    if (!dt.empty()) CU(cudaMemcpyAsync(p->d_tasks, dt.data(), dt.size() * sizeof(DevTask), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaStreamSynchronize(p->stream));  // dt is a stack-lifetime host buffer
+    p->tasks_dirty = false;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_desc* tasks, int32_t ntasks, int64_t N,
+                                    int32_t device, blfik_problem** out)
+{
+    if (!model || !out || (ntasks > 0 && !tasks)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] null argument");
+    if (N < 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] n_instances must be positive");
+    if (ntasks < 1 || ntasks > 64) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] ntasks must be in [1, 64]");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(BLFIK_ERR_CUDA, "[blfik_problem_create] no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] device %d out of range (%d devices)", device, ndev);
+    CU(cudaSetDevice(device));
+
+    blfik_problem* p = new (std::nothrow) blfik_problem;
+    if (!p) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] out of host memory");
+    p->model = model, p->device = device, p->N = N, p->n = model->n, p->nv = model->n + 6;
+    const int n = p->n;
+    blfik_solver_settings ds;
+    blfik_default_settings(&ds);
+    p->st = {ds.rho, ds.sigma, ds.alpha, ds.eps, ds.admm_iters, ds.max_rounds, ds.polish_iters, ds.eq_iters};
+
+    auto bail = [&](int rc) { blfik_problem_destroy(p); return rc; };
+    // ---- addTask rules, QPInverseKinematics.cpp:167-249
+    int me = 0;
+    for (int t = 0; t < ntasks; t++) {
+        HostTask h;
+        h.d = tasks[t];
+        h.rows = rows_of(h.d, n);
+        if (h.rows < 0) return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: unknown type %d", t, h.d.type));
+        if (h.d.priority != 0 && h.d.priority != 1)
+            return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: priority must be 0 or 1 (got %d)", t, h.d.priority));
+        if (is_inequality(h.d.type) && h.d.priority != 0)
+            return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: inequality tasks can only be hard constraints (priority 0)", t));
+        if (h.d.priority == 1 && !h.d.weight)
+            return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: a priority-1 task needs a weight", t));
+        if ((h.d.type == BLFIK_TASK_SE3 || h.d.type == BLFIK_TASK_SO3 || h.d.type == BLFIK_TASK_R3) && (h.d.frame < 0 || h.d.frame >= model->nf))
+            return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: frame index %d out of range", t, h.d.frame));
+        if (h.rows == 0) return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: the mask selects no row", t));
+        h.sp_len = sp_len_of(h.d.type, n);
+        if (h.d.type == BLFIK_TASK_JOINT_TRACKING) {
+            if (!h.d.kp_joint) return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: JointTrackingTask needs kp", t));
+            h.kp_joint.assign(h.d.kp_joint, h.d.kp_joint + n);
+        }
+        if (h.d.type == BLFIK_TASK_JOINT_LIMITS) {
+            if (!h.d.klim || !h.d.upper_limits || !h.d.lower_limits || !(h.d.sampling_time > 0))
+                return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: JointLimitsTask needs klim, limits and a positive sampling_time", t));
+            h.klim.assign(h.d.klim, h.d.klim + n);
+            for (int j = 0; j < n; j++)
+                if (!(h.klim[j] >= 0 && h.klim[j] <= 1))
+                    return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: klim must be in [0, 1]", t));
+        }
+        if (is_inequality(h.d.type)) {
+            if (!h.d.upper_limits || !h.d.lower_limits) return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: limits missing", t));
+            h.upper.assign(h.d.upper_limits, h.d.upper_limits + n), h.lower.assign(h.d.lower_limits, h.d.lower_limits + n);
+        }
+        if (h.d.priority == 1) h.weight.assign(h.d.weight, h.d.weight + h.rows);
+        if (h.d.priority == 0 && is_dense(h.d.type)) {
+            h.row_offset = me;
+            me += h.rows;
+        }
+        h.d.kp_joint = h.d.weight = h.d.klim = h.d.upper_limits = h.d.lower_limits = nullptr;  // owned copies only
+        h.setpoint_set = h.sp_len == 0;
+        p->tasks.push_back(std::move(h));
+    }
+    if (me > 64) return bail(fail(BLFIK_ERR_UNSUPPORTED, "[blfik_problem_create] more than 64 dense equality rows (%d)", me));
+    p->me = me;
+    p->L = make_layout(n, me);
+
+    // ---- launch geometry: as many warps (robots) per SM as shared memory allows
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail(fail(BLFIK_ERR_CUDA, "cudaGetDeviceProperties failed"));
+    p->num_sms = prop.multiProcessorCount;
+    const size_t per_warp = (size_t)p->L.total * sizeof(double);
+    const size_t smem_max = prop.sharedMemPerBlockOptin;
+    if (per_warp > smem_max) return bail(fail(BLFIK_ERR_UNSUPPORTED, "[blfik_problem_create] one robot needs %zu B of shared memory, the device offers %zu", per_warp, smem_max));
+    const size_t sm_total = prop.sharedMemPerMultiprocessor;
+    int warps_per_sm = (int)((sm_total - 2048) / (per_warp + 256));
+    if (warps_per_sm < 1) warps_per_sm = 1;
+    int wpb = warps_per_sm >= 8 ? 4 : (warps_per_sm >= 4 ? 2 : 1);
+    while ((size_t)wpb * per_warp > smem_max && wpb > 1) wpb >>= 1;
+    int blocks_per_sm = warps_per_sm / wpb;
+    if (blocks_per_sm < 1) blocks_per_sm = 1;
+    p->warps_per_block = wpb;
+    p->smem_bytes = (size_t)wpb * per_warp;
+    long long want = (N + wpb - 1) / wpb;
+    long long cap = (long long)p->num_sms * blocks_per_sm;
+    p->grid = (int)(want < cap ? want : cap);
+    if (cudaFuncSetAttribute(blfik_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes) != cudaSuccess ||
+        cudaFuncSetAttribute(blfik_kinematics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes) != cudaSuccess)
+        return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cannot reserve %zu B of shared memory: %s", p->smem_bytes, cudaGetErrorString(cudaGetLastError())));
+
+    if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(fail(BLFIK_ERR_CUDA, "cudaStreamCreate failed"));
+    p->own_stream = true;
+
+    // ---- device copies
+    int rc;
+    DevModel& dm = p->dm;
+    dm.n = n, dm.nl = n + 1, dm.nf = model->nf, dm.maxdepth = model->maxdepth, dm.inv_total_mass = 1.0 / model->total_mass;
+    int *d_parent, *d_dof, *d_depth, *d_lod, *d_fl;
+    unsigned long long* d_anc;
+    double *d_Xr, *d_Xp, *d_axis, *d_mass, *d_com, *d_msub, *d_Fr, *d_Fp;
+    if ((rc = dev_upload(p, model->parent, &d_parent)) || (rc = dev_upload(p, model->dof, &d_dof)) || (rc = dev_upload(p, model->depth, &d_depth)) ||
+        (rc = dev_upload(p, model->link_of_dof, &d_lod)) || (rc = dev_upload(p, model->frame_link, &d_fl)) || (rc = dev_upload(p, model->anc, &d_anc)) ||
+        (rc = dev_upload(p, model->Xr, &d_Xr)) || (rc = dev_upload(p, model->Xp, &d_Xp)) || (rc = dev_upload(p, model->axis, &d_axis)) ||
+        (rc = dev_upload(p, model->mass, &d_mass)) || (rc = dev_upload(p, model->com, &d_com)) || (rc = dev_upload(p, model->msub, &d_msub)) ||
+        (rc = dev_upload(p, model->Fr, &d_Fr)) || (rc = dev_upload(p, model->Fp, &d_Fp)))
+        return bail(rc);
+    dm.parent = d_parent, dm.dof = d_dof, dm.depth = d_depth, dm.link_of_dof = d_lod, dm.frame_link = d_fl, dm.anc = d_anc;
+    dm.Xr = d_Xr, dm.Xp = d_Xp, dm.axis = d_axis, dm.mass = d_mass, dm.com = d_com, dm.msub = d_msub, dm.Fr = d_Fr, dm.Fp = d_Fp;
+
+    const size_t Ns = (size_t)N;
+    if ((rc = dev_alloc(p, Ns * 3, &p->base_pos)) || (rc = dev_alloc(p, Ns * 4, &p->base_quat)) || (rc = dev_alloc(p, Ns * n, &p->s)) ||
+        (rc = dev_alloc(p, Ns * p->nv, &p->nu)) || (rc = dev_alloc(p, Ns * p->nv, &p->wx)) || (rc = dev_alloc(p, Ns * n, &p->wz)) ||
+        (rc = dev_alloc(p, Ns * n, &p->wy)) || (rc = dev_alloc(p, Ns, &p->status)) || (rc = dev_alloc(p, Ns, &p->iters)) ||
+        (rc = dev_alloc(p, 1, &p->d_count)) || (rc = dev_alloc(p, p->tasks.size(), &p->d_tasks)))
+        return bail(rc);
+    for (HostTask& h : p->tasks) {
+        if (h.sp_len && (rc = dev_alloc(p, Ns * h.sp_len, &h.d_setpoint))) return bail(rc);
+        if ((rc = dev_upload(p, h.kp_joint, &h.d_kp_joint)) || (rc = dev_upload(p, h.weight, &h.d_weight)) || (rc = dev_upload(p, h.klim, &h.d_klim)) ||
+            (rc = dev_upload(p, h.upper, &h.d_upper)) || (rc = dev_upload(p, h.lower, &h.d_lower)))
+            return bail(rc);
+    }
+    p->tasks_dirty = true;
+    *out = p;
+    return BLFIK_OK;
+}
+
+extern "C" void blfik_problem_destroy(blfik_problem* p)
+{
+    if (!p) return;
+    cudaSetDevice(p->device);
+    if (p->stream) cudaStreamSynchronize(p->stream);
+    for (void* a : p->allocs) cudaFree(a);
+    if (p->own_stream && p->stream) cudaStreamDestroy(p->stream);
+    delete p;
+}
+
+extern "C" int blfik_set_solver_settings(blfik_problem* p, const blfik_solver_settings* s)
+{
+    if (!p || !s) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_solver_settings] null argument");
+    if (!(s->rho > 0) || !(s->sigma > 0) || !(s->alpha > 0 && s->alpha < 2) || !(s->eps > 0) || s->admm_iters < 1 || s->max_rounds < 1 || s->polish_iters < 1 || s->eq_iters < 1)
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_solver_settings] rho, sigma, eps must be positive, alpha in (0, 2), iteration counts >= 1");
+    p->st = {s->rho, s->sigma, s->alpha, s->eps, s->admm_iters, s->max_rounds, s->polish_iters, s->eq_iters};
+    return BLFIK_OK;
+}
+
+static cudaMemcpyKind kind_in(int mem) { return mem == BLFIK_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice; }
+static cudaMemcpyKind kind_out(int mem) { return mem == BLFIK_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost; }
+
+#define CHECK_P(p, fn)                                                                         \
+    do {                                                                                       \
+        if (!(p)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[" fn "] null problem handle");     \
+        CU(cudaSetDevice((p)->device));                                                        \
+    } while (0)
+
+extern "C" int blfik_set_state(blfik_problem* p, const double* bp, const double* bq, const double* s, int32_t mem)
+{
+    CHECK_P(p, "blfik_set_state");
+    if (!bp || !bq || !s) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_state] null buffer");
+    const size_t N = (size_t)p->N;
+    CU(cudaMemcpyAsync(p->base_pos, bp, N * 3 * sizeof(double), kind_in(mem), p->stream));
+    CU(cudaMemcpyAsync(p->base_quat, bq, N * 4 * sizeof(double), kind_in(mem), p->stream));
+    CU(cudaMemcpyAsync(p->s, s, N * p->n * sizeof(double), kind_in(mem), p->stream));
+    p->state_set = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_get_state(blfik_problem* p, double* bp, double* bq, double* s, int32_t mem)
+{
+    CHECK_P(p, "blfik_get_state");
+    if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_get_state] the state has never been set");
+    const size_t N = (size_t)p->N;
+    if (bp) CU(cudaMemcpyAsync(bp, p->base_pos, N * 3 * sizeof(double), kind_out(mem), p->stream));
+    if (bq) CU(cudaMemcpyAsync(bq, p->base_quat, N * 4 * sizeof(double), kind_out(mem), p->stream));
+    if (s) CU(cudaMemcpyAsync(s, p->s, N * p->n * sizeof(double), kind_out(mem), p->stream));
+    if (mem == BLFIK_MEM_HOST) CU(cudaStreamSynchronize(p->stream));
+    return BLFIK_OK;
+}
+
+#define CHECK_TASK(p, t, fn)                                                                                     \
+    do {                                                                                                         \
+        if ((t) < 0 || (t) >= (int)(p)->tasks.size())                                                            \
+            return fail(BLFIK_ERR_INVALID_ARGUMENT, "[" fn "] task index %d out of range (%d tasks)", (int)(t), (int)(p)->tasks.size()); \
+    } while (0)
+
+extern "C" int32_t blfik_setpoint_len(const blfik_problem* p, int32_t t)
+{
+    if (!p || t < 0 || t >= (int)p->tasks.size()) return -1;
+    return p->tasks[t].sp_len;
+}
+
+extern "C" int blfik_set_setpoint(blfik_problem* p, int32_t t, const double* data, int32_t mem)
+{
+    CHECK_P(p, "blfik_set_setpoint");
+    CHECK_TASK(p, t, "blfik_set_setpoint");
+    HostTask& h = p->tasks[t];
+    if (h.sp_len == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint] task %d takes no set-point", t);
+    if (!data) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint] null buffer");
+    CU(cudaMemcpyAsync(h.d_setpoint, data, (size_t)p->N * h.sp_len * sizeof(double), kind_in(mem), p->stream));
+    h.setpoint_set = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_set_weight(blfik_problem* p, int32_t t, const double* weight)
+{
+    CHECK_P(p, "blfik_set_weight");
+    CHECK_TASK(p, t, "blfik_set_weight");
+    HostTask& h = p->tasks[t];
+    // QPInverseKinematics.cpp:251-305: only priority-1 tasks carry a weight
+    if (h.d.priority != 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_weight] task %d is a hard constraint; only priority-1 tasks have a weight", t);
+    if (!weight) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_weight] null weight");
+    h.weight.assign(weight, weight + h.rows);
+    p->tasks_dirty = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_set_gains(blfik_problem* p, int32_t t, const double* kl, const double* ka, const double* kj)
+{
+    CHECK_P(p, "blfik_set_gains");
+    CHECK_TASK(p, t, "blfik_set_gains");
+    HostTask& h = p->tasks[t];
+    if (kl) memcpy(h.d.kp_linear, kl, 3 * sizeof(double));
+    if (ka) memcpy(h.d.kp_angular, ka, 3 * sizeof(double));
+    if (kj) {
+        if (h.d.type != BLFIK_TASK_JOINT_TRACKING) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_gains] task %d has no joint gains", t);
+        h.kp_joint.assign(kj, kj + p->n);
+    }
+    p->tasks_dirty = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_set_controller_mode(blfik_problem* p, int32_t t, int32_t enabled)
+{
+    CHECK_P(p, "blfik_set_controller_mode");
+    CHECK_TASK(p, t, "blfik_set_controller_mode");
+    p->tasks[t].d.controller_enabled = enabled != 0;
+    p->tasks_dirty = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_debug_enable(blfik_problem* p, int32_t enabled)
+{
+    CHECK_P(p, "blfik_debug_enable");
+    if (enabled && !p->dbg.H) {
+        const size_t N = (size_t)p->N, nv = p->nv, me = p->me, n = p->n;
+        int rc;
+        if ((rc = dev_alloc(p, N * nv * nv, &p->dbg.H)) || (rc = dev_alloc(p, N * nv, &p->dbg.g)) || (rc = dev_alloc(p, N * me * nv, &p->dbg.Ceq)) ||
+            (rc = dev_alloc(p, N * me, &p->dbg.beq)) || (rc = dev_alloc(p, N * n, &p->dbg.lo)) || (rc = dev_alloc(p, N * n, &p->dbg.hi)))
+            return rc;
+    }
+    p->debug = enabled != 0;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_debug_get(blfik_problem* p, int32_t what, double* out, int32_t mem)
+{
+    CHECK_P(p, "blfik_debug_get");
+    if (!p->dbg.H || !p->ticked) return fail(BLFIK_ERR_NOT_READY, "[blfik_debug_get] call blfik_debug_enable(1) and blfik_tick first");
+    if (!out) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_debug_get] null buffer");
+    const size_t N = (size_t)p->N, nv = p->nv, me = p->me, n = p->n;
+    const double* src = nullptr;
+    size_t cnt = 0;
+    switch (what) {
+    case BLFIK_DEBUG_H: src = p->dbg.H, cnt = N * nv * nv; break;
+    case BLFIK_DEBUG_G: src = p->dbg.g, cnt = N * nv; break;
+    case BLFIK_DEBUG_CEQ: src = p->dbg.Ceq, cnt = N * me * nv; break;
+    case BLFIK_DEBUG_BEQ: src = p->dbg.beq, cnt = N * me; break;
+    case BLFIK_DEBUG_LO: src = p->dbg.lo, cnt = N * n; break;
+    case BLFIK_DEBUG_HI: src = p->dbg.hi, cnt = N * n; break;
+    default: return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_debug_get] unknown selector %d", what);
+    }
+    if (cnt) CU(cudaMemcpyAsync(out, src, cnt * sizeof(double), kind_out(mem), p->stream));
+    if (mem == BLFIK_MEM_HOST) CU(cudaStreamSynchronize(p->stream));
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_tick(blfik_problem* p, int32_t nticks, double dt, uint32_t flags)
+{
+    CHECK_P(p, "blfik_tick");
+    // the reference's advance() fails when a set-point was never set (SE3Task.cpp:245-249) and
+    // kinDyn must hold a state
+    if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_tick] the robot state has never been set");
+    for (size_t t = 0; t < p->tasks.size(); t++)
+        if (!p->tasks[t].setpoint_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_tick] the set point of task %d has not been set at least once", (int)t);
+    if (nticks < 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_tick] nticks must be >= 1");
+    if ((flags & BLFIK_TICK_INTEGRATE) && !(dt > 0)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_tick] dt must be positive when integrating");
+    int rc = refresh_tasks(p);
+    if (rc) return rc;
+    TickParams P;
+    P.m = p->dm, P.tasks = p->d_tasks, P.ntasks = (int)p->tasks.size(), P.N = p->N;
+    P.base_pos = p->base_pos, P.base_quat = p->base_quat, P.s = p->s, P.nu = p->nu, P.wx = p->wx, P.wz = p->wz, P.wy = p->wy;
+    P.status = p->status, P.iters = p->iters, P.st = p->st, P.nticks = nticks, P.dt = dt, P.flags = flags;
+    P.dbg = p->debug ? p->dbg : DebugOut{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    P.L = p->L;
+    blfik_tick_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(P);
+    CU(cudaGetLastError());
+    p->launches++;
+    p->ticked = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_get_output(blfik_problem* p, double* nu, int32_t mem)
+{
+    CHECK_P(p, "blfik_get_output");
+    if (!p->ticked) return fail(BLFIK_ERR_NOT_READY, "[blfik_get_output] no tick has run yet");
+    if (!nu) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_get_output] null buffer");
+    CU(cudaMemcpyAsync(nu, p->nu, (size_t)p->N * p->nv * sizeof(double), kind_out(mem), p->stream));
+    if (mem == BLFIK_MEM_HOST) CU(cudaStreamSynchronize(p->stream));
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_get_status(blfik_problem* p, int32_t* status, int32_t* iters, int32_t mem)
+{
+    CHECK_P(p, "blfik_get_status");
+    if (!p->ticked) return fail(BLFIK_ERR_NOT_READY, "[blfik_get_status] no tick has run yet");
+    if (status) CU(cudaMemcpyAsync(status, p->status, (size_t)p->N * sizeof(int), kind_out(mem), p->stream));
+    if (iters) CU(cudaMemcpyAsync(iters, p->iters, (size_t)p->N * sizeof(int), kind_out(mem), p->stream));
+    if (mem == BLFIK_MEM_HOST) CU(cudaStreamSynchronize(p->stream));
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_count_unsolved(blfik_problem* p, int64_t* count)
+{
+    CHECK_P(p, "blfik_count_unsolved");
+    if (!p->ticked) return fail(BLFIK_ERR_NOT_READY, "[blfik_count_unsolved] no tick has run yet");
+    if (!count) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_count_unsolved] null output");
+    CU(cudaMemsetAsync(p->d_count, 0, sizeof(unsigned long long), p->stream));
+    blfik_count_unsolved_kernel<<<p->num_sms, 256, 0, p->stream>>>(p->status, p->N, p->d_count);
+    CU(cudaGetLastError());
+    p->launches++;
+    unsigned long long h = 0;
+    CU(cudaMemcpyAsync(&h, p->d_count, sizeof h, cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    *count = (int64_t)h;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_kinematics(blfik_problem* p, const int32_t* frames, int32_t nframes, double* frame_pos, double* frame_rot,
+                                double* frame_jac, double* com, double* com_jac, int32_t mem)
+{
+    CHECK_P(p, "blfik_kinematics");
+    if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_kinematics] the robot state has never been set");
+    if (nframes < 0 || (nframes > 0 && !frames)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_kinematics] bad frame list");
+    for (int f = 0; f < nframes; f++)
+        if (frames[f] < 0 || frames[f] >= p->model->nf) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_kinematics] frame index %d out of range", frames[f]);
+    const size_t N = (size_t)p->N, nv = p->nv, nf = (size_t)nframes;
+    // scratch on the device: outputs are produced there, then copied to wherever the caller wants them
+    struct Buf { double* user; double* dev; size_t cnt; } bufs[5] = {
+        {frame_pos, nullptr, N * nf * 3}, {frame_rot, nullptr, N * nf * 9}, {frame_jac, nullptr, N * nf * 6 * nv}, {com, nullptr, N * 3}, {com_jac, nullptr, N * 3 * nv}};
+    std::vector<void*> tmp;
+    auto cleanup = [&]() { for (void* t : tmp) cudaFree(t); };
+    int* d_frames = nullptr;
+    if (nframes) {
+        if (cudaMalloc((void**)&d_frames, nf * sizeof(int)) != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_kinematics] cudaMalloc failed");
+        tmp.push_back(d_frames);
+        cudaMemcpyAsync(d_frames, frames, nf * sizeof(int), cudaMemcpyHostToDevice, p->stream);
+    }
+    for (Buf& b : bufs) {
+        if (!b.user || !b.cnt) { b.user = nullptr; continue; }
+        if (mem == BLFIK_MEM_DEVICE) b.dev = b.user;
+        else {
+            if (cudaMalloc((void**)&b.dev, b.cnt * sizeof(double)) != cudaSuccess) { cleanup(); return fail(BLFIK_ERR_CUDA, "[blfik_kinematics] cudaMalloc failed"); }
+            tmp.push_back(b.dev);
+        }
+    }
+    KinParams K;
+    K.m = p->dm, K.N = p->N, K.base_pos = p->base_pos, K.base_quat = p->base_quat, K.s = p->s, K.frames = d_frames, K.nframes = nframes;
+    K.frame_pos = bufs[0].user ? bufs[0].dev : nullptr, K.frame_rot = bufs[1].user ? bufs[1].dev : nullptr;
+    K.frame_jac = bufs[2].user ? bufs[2].dev : nullptr, K.com = bufs[3].user ? bufs[3].dev : nullptr, K.com_jac = bufs[4].user ? bufs[4].dev : nullptr;
+    K.L = p->L;
+    blfik_kinematics_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(K);
+    cudaError_t e = cudaGetLastError();
+    p->launches++;
+    if (e == cudaSuccess && mem == BLFIK_MEM_HOST)
+        for (Buf& b : bufs)
+            if (b.user && e == cudaSuccess) e = cudaMemcpyAsync(b.user, b.dev, b.cnt * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+    cleanup();
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_kinematics] %s", cudaGetErrorString(e));
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_integrate(blfik_problem* p, const double* nu, int32_t mem, double dt, int32_t nsteps)
+{
+    CHECK_P(p, "blfik_integrate");
+    if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_integrate] the state has never been set");
+    // FixedStepIntegrator.h:73-85: the step must be positive; :94-140 with tf - t0 < dT underflows in the
+    // reference -- rejected here instead of reproduced
+    if (!(dt > 0)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate] the integration step must be positive");
+    if (nsteps < 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate] nsteps must be >= 1 (final time before initial time + dT)");
+    const double* src = p->nu;
+    if (nu) {
+        if (mem == BLFIK_MEM_DEVICE) src = nu;
+        else {
+            CU(cudaMemcpyAsync(p->nu, nu, (size_t)p->N * p->nv * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+            p->ticked = true;  // nu now holds a caller-provided control input
+        }
+    } else if (!p->ticked) {
+        return fail(BLFIK_ERR_NOT_READY, "[blfik_integrate] no control input: pass nu or run a tick first");
+    }
+    const long long blocks = (p->N * 32 + 255) / 256;
+    const long long cap = (long long)p->num_sms * 8;
+    blfik_integrate_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, p->stream>>>(p->n, p->N, p->base_pos, p->base_quat, p->s, src, dt, nsteps);
+    CU(cudaGetLastError());
+    p->launches++;
+    return BLFIK_OK;
+}
+
+extern "C" int32_t blfik_num_dofs(const blfik_problem* p) { return p ? p->n : -1; }
+extern "C" int32_t blfik_num_equality_rows(const blfik_problem* p) { return p ? p->me : -1; }
+extern "C" int64_t blfik_num_instances(const blfik_problem* p) { return p ? p->N : -1; }
+extern "C" int64_t blfik_launch_count(const blfik_problem* p) { return p ? p->launches : -1; }
+
+extern "C" int blfik_sync(blfik_problem* p)
+{
+    CHECK_P(p, "blfik_sync");
+    CU(cudaStreamSynchronize(p->stream));
+    return BLFIK_OK;
+}
+
+extern "C" void* blfik_get_stream(blfik_problem* p) { return p ? (void*)p->stream : nullptr; }
+
+extern "C" int blfik_set_stream(blfik_problem* p, void* s)
+{
+    CHECK_P(p, "blfik_set_stream");
+    CU(cudaStreamSynchronize(p->stream));
+    if (p->own_stream && p->stream) cudaStreamDestroy(p->stream);
+    p->stream = (cudaStream_t)s;
+    p->own_stream = false;
+    return BLFIK_OK;
+}

@@ -1,0 +1,887 @@
+// blfik_device.cuh -- device side of the batched IK tick (sm_100a, FP64).
+//
+// Execution model: ONE WARP PER ROBOT.  Lane i owns velocity variable i (row i of every
+// nv x nv matrix); all per-robot matrices live in that warp's slice of shared memory, the
+// kinematic tree (batch-shared constants) is read through L1.  Control flow is warp-uniform
+// by construction (loop bounds depend only on the model/problem, never on the robot), so a
+// warp never diverges except on the rare "polish rejected" retry path.
+//
+// Stages:  K1 fk_jac -> K2 task_assemble -> K3 qp (ADMM + polish) -> K4 se3_euler
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace blfik {
+
+constexpr double kInf = 1e30;       // OsqpEigen::INFTY
+constexpr double kInfHalf = 0.5e30;
+constexpr unsigned kFull = 0xffffffffu;
+
+enum TaskType : int { T_SE3 = 0, T_COM = 1, T_SO3 = 2, T_JOINT_TRACKING = 3, T_JOINT_LIMITS = 4, T_JOINT_VEL_LIMITS = 5, T_R3 = 6 };
+
+struct DevModel {
+    int n, nl, nf, maxdepth;
+    const int* parent;       // [nl]
+    const int* dof;          // [nl]
+    const int* depth;        // [nl]
+    const int* link_of_dof;  // [n]
+    const unsigned long long* anc;  // [nl] bit j set <=> DoF j is on the path base -> link
+    const double* Xr;        // [nl][9]
+    const double* Xp;        // [nl][3]
+    const double* axis;      // [nl][3]
+    const double* mass;      // [nl]
+    const double* com;       // [nl][3]
+    const double* msub;      // [n] mass of the subtree distal to DoF j
+    double inv_total_mass;
+    const int* frame_link;   // [nf]
+    const double* Fr;        // [nf][9]
+    const double* Fp;        // [nf][3]
+};
+
+struct DevTask {
+    int type, priority, frame, rows, enabled, sp_len, row_offset;
+    int mask[3];
+    double kp_lin[3], kp_ang[3];
+    const double* kp_joint;
+    const double* weight;
+    const double* klim;
+    const double* upper;
+    const double* lower;
+    double inv_dt;
+    const double* setpoint;  // device [N][sp_len]
+};
+
+struct Settings {
+    double rho, sigma, alpha, eps;
+    int admm_iters, max_rounds, polish_iters, eq_iters;
+};
+
+// shared-memory layout of one warp, in doubles (computed on the host)
+struct Layout {
+    int nv, me, LD, LDE;
+    int linkR, linkP, axisW, mcw;          // kinematics
+    int Hs, A, B, Cs, Ym, Wm, Ss, Jt;      // matrices
+    int g, b, lo, hi, x, z, y, r, xb, wb, lam, gp, bp, bd, t;  // vectors
+    int act;                               // int[nv] stored in a double slot array
+    int total;                             // doubles per warp
+};
+
+struct DebugOut {
+    double *H, *g, *Ceq, *beq, *lo, *hi;   // any may be null
+};
+
+struct TickParams {
+    DevModel m;
+    const DevTask* tasks;
+    int ntasks;
+    long long N;
+    double *base_pos, *base_quat, *s;      // state (in/out)
+    double* nu;                            // [N][nv] out
+    double *wx, *wz, *wy;                  // warm start [N][nv], [N][n], [N][n]
+    int *status, *iters;
+    Settings st;
+    int nticks;
+    double dt;
+    unsigned flags;
+    DebugOut dbg;
+    Layout L;
+};
+
+struct KinParams {
+    DevModel m;
+    long long N;
+    const double *base_pos, *base_quat, *s;
+    const int* frames;
+    int nframes;
+    double *frame_pos, *frame_rot, *frame_jac, *com, *com_jac;
+    Layout L;
+};
+
+struct WM {  // one warp's shared memory, as pointers
+    double *linkR, *linkP, *axisW, *mcw;
+    double *Hs, *A, *B, *Cs, *Ym, *Wm, *Ss, *Jt;
+    double *g, *b, *lo, *hi, *x, *z, *y, *r, *xb, *wb, *lam, *gp, *bp, *bd, *t;
+    int* act;
+};
+
+__device__ __forceinline__ WM carve(double* base, const Layout& L)
+{
+    WM w;
+    w.linkR = base + L.linkR, w.linkP = base + L.linkP, w.axisW = base + L.axisW, w.mcw = base + L.mcw;
+    w.Hs = base + L.Hs, w.A = base + L.A, w.B = base + L.B, w.Cs = base + L.Cs;
+    w.Ym = base + L.Ym, w.Wm = base + L.Wm, w.Ss = base + L.Ss, w.Jt = base + L.Jt;
+    w.g = base + L.g, w.b = base + L.b, w.lo = base + L.lo, w.hi = base + L.hi;
+    w.x = base + L.x, w.z = base + L.z, w.y = base + L.y, w.r = base + L.r;
+    w.xb = base + L.xb, w.wb = base + L.wb, w.lam = base + L.lam;
+    w.gp = base + L.gp, w.bp = base + L.bp, w.bd = base + L.bd, w.t = base + L.t;
+    w.act = reinterpret_cast<int*>(base + L.act);
+    return w;
+}
+
+// ------------------------------------------------------------------ small math
+__device__ __forceinline__ void mat3_mul(const double* A, const double* B, double* C)
+{
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+}
+__device__ __forceinline__ void mat3_vec(const double* A, const double* v, double* o)
+{
+#pragma unroll
+    for (int i = 0; i < 3; i++) o[i] = A[3 * i] * v[0] + A[3 * i + 1] * v[1] + A[3 * i + 2] * v[2];
+}
+__device__ __forceinline__ void cross3(const double* a, const double* b, double* o)
+{
+    o[0] = a[1] * b[2] - a[2] * b[1];
+    o[1] = a[2] * b[0] - a[0] * b[2];
+    o[2] = a[0] * b[1] - a[1] * b[0];
+}
+__device__ __forceinline__ double warp_max(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(kFull, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    return v;
+}
+
+__device__ __forceinline__ void quat_to_rot(const double* q, double* R)
+{
+    const double x = q[0], y = q[1], z = q[2], w = q[3];
+    R[0] = 1 - 2 * (y * y + z * z), R[1] = 2 * (x * y - z * w), R[2] = 2 * (x * z + y * w);
+    R[3] = 2 * (x * y + z * w), R[4] = 1 - 2 * (x * x + z * z), R[5] = 2 * (y * z - x * w);
+    R[6] = 2 * (x * z - y * w), R[7] = 2 * (y * z + x * w), R[8] = 1 - 2 * (x * x + y * y);
+}
+
+// rotation matrix -> unit quaternion (x,y,z,w); Conversions::toManifRot semantics
+// (ManifConversions.h:44-50: Eigen Quaternion(Matrix3) then normalize()).
+__device__ __forceinline__ void rot_to_quat(const double* R, double* q)
+{
+    double t = R[0] + R[4] + R[8];
+    if (t > 0) {
+        t = sqrt(t + 1.0);
+        q[3] = 0.5 * t;
+        t = 0.5 / t;
+        q[0] = (R[7] - R[5]) * t, q[1] = (R[2] - R[6]) * t, q[2] = (R[3] - R[1]) * t;
+    } else if (R[0] >= R[4] && R[0] >= R[8]) {
+        t = sqrt(R[0] - R[4] - R[8] + 1.0);
+        q[0] = 0.5 * t;
+        t = 0.5 / t;
+        q[3] = (R[7] - R[5]) * t, q[1] = (R[3] + R[1]) * t, q[2] = (R[6] + R[2]) * t;
+    } else if (R[4] > R[0] && R[4] >= R[8]) {
+        t = sqrt(R[4] - R[8] - R[0] + 1.0);
+        q[1] = 0.5 * t;
+        t = 0.5 / t;
+        q[3] = (R[2] - R[6]) * t, q[2] = (R[7] + R[5]) * t, q[0] = (R[1] + R[3]) * t;
+    } else {
+        t = sqrt(R[8] - R[0] - R[4] + 1.0);
+        q[2] = 0.5 * t;
+        t = 0.5 / t;
+        q[3] = (R[3] - R[1]) * t, q[0] = (R[2] + R[6]) * t, q[1] = (R[5] + R[7]) * t;
+    }
+    const double inv = rsqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    q[0] *= inv, q[1] *= inv, q[2] *= inv, q[3] *= inv;
+}
+
+__device__ __forceinline__ void quat_mul(const double* a, const double* b, double* o)
+{
+    o[0] = a[3] * b[0] + a[0] * b[3] + a[1] * b[2] - a[2] * b[1];
+    o[1] = a[3] * b[1] - a[0] * b[2] + a[1] * b[3] + a[2] * b[0];
+    o[2] = a[3] * b[2] + a[0] * b[1] - a[1] * b[0] + a[2] * b[3];
+    o[3] = a[3] * b[3] - a[0] * b[0] - a[1] * b[1] - a[2] * b[2];
+}
+
+// manif SO3::log on a unit quaternion
+__device__ __forceinline__ void so3_log(const double* q, double* phi)
+{
+    const double n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2];
+    const double w = q[3];
+    double scale;
+    if (n2 > 1e-20) {
+        const double n = sqrt(n2);
+        const double two_angle = 2.0 * (w < 0 ? atan2(-n, -w) : atan2(n, w));
+        scale = two_angle / n;
+    } else {
+        scale = 2.0 / w;
+    }
+    phi[0] = scale * q[0], phi[1] = scale * q[1], phi[2] = scale * q[2];
+}
+
+// manif SO3Tangent::exp
+__device__ __forceinline__ void so3_exp(const double* phi, double* q)
+{
+    const double th2 = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
+    double k;
+    if (th2 > 1e-16) {
+        const double th = sqrt(th2);
+        double sn, cs;
+        sincos(0.5 * th, &sn, &cs);
+        k = sn / th;
+        q[3] = cs;
+    } else {
+        k = 0.5 - th2 / 48.0;
+        q[3] = 1.0 - th2 / 8.0;
+    }
+    q[0] = k * phi[0], q[1] = k * phi[1], q[2] = k * phi[2];
+}
+
+// LieGroupControllers P-law on SO(3), left trivialisation: w* = w_ff + Kp o Log(R_d R^-1)
+__device__ __forceinline__ void so3_control(const double* Rcur, const double* qd, const double* wff,
+                                            const double* kp, bool enabled, double* out)
+{
+    double qc[4], qe[4], e[3];
+    rot_to_quat(Rcur, qc);
+    qc[0] = -qc[0], qc[1] = -qc[1], qc[2] = -qc[2];
+    quat_mul(qd, qc, qe);
+    so3_log(qe, e);
+#pragma unroll
+    for (int c = 0; c < 3; c++) out[c] = enabled ? wff[c] + kp[c] * e[c] : wff[c];
+}
+
+// ------------------------------------------------------------------ K1: FK + Jacobians
+// Level-synchronous tree walk, one link per lane.  Leaves in shared memory, for every link,
+// the world rotation/origin, the world joint axis and mass * world CoM.
+__device__ __forceinline__ void k1_fk(const DevModel& m, const WM& w, const double* bp, const double* bq,
+                                      const double* s, int lane)
+{
+    for (int k = lane; k < m.nl; k += 32) {
+        double R[9];
+        if (k == 0) {
+            double q[4] = {bq[0], bq[1], bq[2], bq[3]};
+            quat_to_rot(q, R);
+            w.linkP[0] = bp[0], w.linkP[1] = bp[1], w.linkP[2] = bp[2];
+        } else {
+            // local transform Xr * Rot(axis, s)
+            const double* a = m.axis + 3 * k;
+            double sn, cs;
+            sincos(s[m.dof[k]], &sn, &cs);
+            const double v = 1 - cs;
+            double Rj[9];
+            Rj[0] = cs + a[0] * a[0] * v, Rj[1] = a[0] * a[1] * v - a[2] * sn, Rj[2] = a[0] * a[2] * v + a[1] * sn;
+            Rj[3] = a[1] * a[0] * v + a[2] * sn, Rj[4] = cs + a[1] * a[1] * v, Rj[5] = a[1] * a[2] * v - a[0] * sn;
+            Rj[6] = a[2] * a[0] * v - a[1] * sn, Rj[7] = a[2] * a[1] * v + a[0] * sn, Rj[8] = cs + a[2] * a[2] * v;
+            double X[9];
+#pragma unroll
+            for (int c = 0; c < 9; c++) X[c] = m.Xr[9 * k + c];
+            mat3_mul(X, Rj, R);
+        }
+#pragma unroll
+        for (int c = 0; c < 9; c++) w.linkR[9 * k + c] = R[c];
+    }
+    __syncwarp();
+    for (int d = 1; d <= m.maxdepth; d++) {
+        for (int k = lane; k < m.nl; k += 32) {
+            if (m.depth[k] == d) {
+                const int par = m.parent[k];
+                double Rp[9], Rl[9], R[9], xp[3], off[3];
+#pragma unroll
+                for (int c = 0; c < 9; c++) Rp[c] = w.linkR[9 * par + c], Rl[c] = w.linkR[9 * k + c];
+                mat3_mul(Rp, Rl, R);
+                xp[0] = m.Xp[3 * k], xp[1] = m.Xp[3 * k + 1], xp[2] = m.Xp[3 * k + 2];
+                mat3_vec(Rp, xp, off);
+#pragma unroll
+                for (int c = 0; c < 9; c++) w.linkR[9 * k + c] = R[c];
+#pragma unroll
+                for (int c = 0; c < 3; c++) w.linkP[3 * k + c] = w.linkP[3 * par + c] + off[c];
+            }
+        }
+        __syncwarp();
+    }
+    for (int k = lane; k < m.nl; k += 32) {
+        double R[9], a[3], c[3], aw[3], cw[3];
+#pragma unroll
+        for (int i = 0; i < 9; i++) R[i] = w.linkR[9 * k + i];
+#pragma unroll
+        for (int i = 0; i < 3; i++) a[i] = m.axis[3 * k + i], c[i] = m.com[3 * k + i];
+        mat3_vec(R, a, aw);
+        mat3_vec(R, c, cw);
+        const double mk = m.mass[k];
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            w.axisW[3 * k + i] = aw[i];
+            w.mcw[3 * k + i] = mk * (w.linkP[3 * k + i] + cw[i]);
+        }
+    }
+    __syncwarp();
+}
+
+// world pose of a frame (every lane computes the same values)
+__device__ __forceinline__ void k1_frame_pose(const DevModel& m, const WM& w, int frame, double* R, double* p)
+{
+    const int L = m.frame_link[frame];
+    double Rl[9], Fr[9], fp[3], off[3];
+#pragma unroll
+    for (int c = 0; c < 9; c++) Rl[c] = w.linkR[9 * L + c], Fr[c] = m.Fr[9 * frame + c];
+#pragma unroll
+    for (int c = 0; c < 3; c++) fp[c] = m.Fp[3 * frame + c];
+    mat3_mul(Rl, Fr, R);
+    mat3_vec(Rl, fp, off);
+#pragma unroll
+    for (int c = 0; c < 3; c++) p[c] = w.linkP[3 * L + c] + off[c];
+}
+
+// MIXED-representation 6 x nv Jacobian of a point pf rigidly attached to link L; column c by lane c.
+// dst has row stride ld; rows 0-2 linear, 3-5 angular.
+__device__ __forceinline__ void k1_frame_jac(const DevModel& m, const WM& w, int L, const double* pf, double* dst,
+                                             int ld, int lane)
+{
+    const int nv = m.n + 6;
+    const unsigned long long anc = m.anc[L];
+    for (int c = lane; c < nv; c += 32) {
+        double lin[3] = {0, 0, 0}, ang[3] = {0, 0, 0};
+        if (c < 3) {
+            lin[c] = 1.0;
+        } else if (c < 6) {
+            const double r[3] = {pf[0] - w.linkP[0], pf[1] - w.linkP[1], pf[2] - w.linkP[2]};
+            ang[c - 3] = 1.0;
+            cross3(ang, r, lin);
+        } else if ((anc >> (c - 6)) & 1ull) {
+            const int k = m.link_of_dof[c - 6];
+            const double d[3] = {pf[0] - w.linkP[3 * k], pf[1] - w.linkP[3 * k + 1], pf[2] - w.linkP[3 * k + 2]};
+            ang[0] = w.axisW[3 * k], ang[1] = w.axisW[3 * k + 1], ang[2] = w.axisW[3 * k + 2];
+            cross3(ang, d, lin);
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++) dst[i * ld + c] = lin[i], dst[(3 + i) * ld + c] = ang[i];
+    }
+}
+
+// CoM position (all lanes) and 3 x nv CoM Jacobian through subtree sums:
+// column j = (1/M) a_j x (sum_{k in sub(j)} m_k c_k - M_sub(j) o_j)
+__device__ __forceinline__ void k1_com(const DevModel& m, const WM& w, double* com, double* dst, int ld, int lane)
+{
+    const int nv = m.n + 6;
+    double acc[3] = {0, 0, 0};
+    for (int k = lane; k < m.nl; k += 32) {
+        acc[0] += w.mcw[3 * k], acc[1] += w.mcw[3 * k + 1], acc[2] += w.mcw[3 * k + 2];
+    }
+#pragma unroll
+    for (int i = 0; i < 3; i++) com[i] = warp_sum(acc[i]) * m.inv_total_mass;
+    if (!dst) return;
+    for (int c = lane; c < nv; c += 32) {
+        double lin[3] = {0, 0, 0};
+        if (c < 3) {
+            lin[c] = 1.0;
+        } else if (c < 6) {
+            const double r[3] = {com[0] - w.linkP[0], com[1] - w.linkP[1], com[2] - w.linkP[2]};
+            double e[3] = {0, 0, 0};
+            e[c - 3] = 1.0;
+            cross3(e, r, lin);
+        } else {
+            const int j = c - 6;
+            const int kj = m.link_of_dof[j];
+            double mc[3] = {0, 0, 0};
+            for (int k = 1; k < m.nl; k++) {
+                if ((m.anc[k] >> j) & 1ull) {
+                    mc[0] += w.mcw[3 * k], mc[1] += w.mcw[3 * k + 1], mc[2] += w.mcw[3 * k + 2];
+                }
+            }
+            const double ms = m.msub[j];
+            const double d[3] = {(mc[0] - ms * w.linkP[3 * kj]) * m.inv_total_mass,
+                                 (mc[1] - ms * w.linkP[3 * kj + 1]) * m.inv_total_mass,
+                                 (mc[2] - ms * w.linkP[3 * kj + 2]) * m.inv_total_mass};
+            const double a[3] = {w.axisW[3 * kj], w.axisW[3 * kj + 1], w.axisW[3 * kj + 2]};
+            cross3(a, d, lin);
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++) dst[i * ld + c] = lin[i];
+    }
+}
+
+// ------------------------------------------------------------------ K2: task assembly
+// Builds, in shared memory, what QPInverseKinematics::advance builds (QPInverseKinematics.cpp:442-491):
+// H, g from the priority-1 tasks; the dense equality rows (Cs, b) from the priority-0 SE3/CoM/SO3/R3 tasks;
+// and, because every inequality row of the reference is +-e_j' (JointLimitsTask.cpp:110-113,
+// JointVelocityLimitsTask.cpp), the intersection of those rows as a per-joint box [lo, hi].
+// A priority-0 JointTrackingTask (rows e_j' x = b_j) becomes lo = hi = b_j.
+__device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, long long robot, const double* s, int lane)
+{
+    const DevModel& m = P.m;
+    const Layout& L = P.L;
+    const int nv = L.nv, LD = L.LD, n = m.n;
+    for (int i = lane; i < nv; i += 32) {
+        for (int j = 0; j < nv; j++) w.Hs[i * LD + j] = 0.0;
+        w.g[i] = 0.0, w.lo[i] = -kInf, w.hi[i] = kInf;
+    }
+    __syncwarp();
+    for (int t = 0; t < P.ntasks; t++) {
+        const DevTask& tk = P.tasks[t];
+        const double* sp = tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr;
+        if (tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM) {
+            double bt[6];
+            int src[6];
+            int rows = 0;
+            if (tk.type == T_COM) {
+                double com[3];
+                k1_com(m, w, com, w.Jt, LD, lane);
+                for (int c = 0; c < 3; c++)
+                    if (tk.mask[c]) {  // CoMTask.cpp:194-203: b = v_ff + kp (p_d - p_com)
+                        bt[rows] = sp[3 + c] + tk.kp_lin[c] * (sp[c] - com[c]);
+                        src[rows++] = c;
+                    }
+            } else {
+                double R[9], pf[3];
+                k1_frame_pose(m, w, tk.frame, R, pf);
+                k1_frame_jac(m, w, m.frame_link[tk.frame], pf, w.Jt, LD, lane);
+                if (tk.type == T_SE3 || tk.type == T_R3) {
+                    const int voff = tk.type == T_SE3 ? 7 : 3;
+                    for (int c = 0; c < 3; c++)
+                        if (tk.mask[c]) {  // SE3Task.cpp:276-316
+                            bt[rows] = tk.enabled ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pf[c]) : sp[voff + c];
+                            src[rows++] = c;
+                        }
+                }
+                if (tk.type == T_SE3 || tk.type == T_SO3) {
+                    const double* qd = tk.type == T_SE3 ? sp + 3 : sp;
+                    const double* wff = tk.type == T_SE3 ? sp + 10 : sp + 4;
+                    double qdl[4] = {qd[0], qd[1], qd[2], qd[3]}, wl[3] = {wff[0], wff[1], wff[2]}, out[3];
+                    so3_control(R, qdl, wl, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), out);
+                    for (int c = 0; c < 3; c++) bt[rows] = out[c], src[rows++] = 3 + c;
+                }
+            }
+            __syncwarp();
+            if (tk.priority == 0) {
+                for (int r = 0; r < rows; r++) {
+                    for (int c = lane; c < nv; c += 32) w.Cs[(tk.row_offset + r) * LD + c] = w.Jt[src[r] * LD + c];
+                    if (lane == 0) w.b[tk.row_offset + r] = bt[r];
+                }
+            } else {
+                for (int i = lane; i < nv; i += 32) {
+                    double gi = 0.0;
+                    for (int r = 0; r < rows; r++) {
+                        const double wa = tk.weight[r] * w.Jt[src[r] * LD + i];
+                        gi += wa * bt[r];
+                        for (int j = 0; j < nv; j++) w.Hs[i * LD + j] += wa * w.Jt[src[r] * LD + j];
+                    }
+                    w.g[i] -= gi;
+                }
+            }
+            __syncwarp();
+        } else {
+            for (int j = lane; j < n; j += 32) {
+                const int i = 6 + j;
+                if (tk.type == T_JOINT_TRACKING) {  // JointTrackingTask.cpp:151
+                    const double bj = sp[n + j] + tk.kp_joint[j] * (sp[j] - s[j]);
+                    if (tk.priority == 1) {
+                        w.Hs[i * LD + i] += tk.weight[j];
+                        w.g[i] -= tk.weight[j] * bj;
+                    } else {
+                        w.lo[i] = fmax(w.lo[i], bj), w.hi[i] = fmin(w.hi[i], bj);
+                    }
+                } else if (tk.type == T_JOINT_LIMITS) {  // JointLimitsTask.cpp:227-231
+                    w.hi[i] = fmin(w.hi[i], tk.klim[j] * (tk.upper[j] - s[j]) * tk.inv_dt);
+                    w.lo[i] = fmax(w.lo[i], tk.klim[j] * (tk.lower[j] - s[j]) * tk.inv_dt);
+                } else {  // JointVelocityLimitsTask.cpp:140-141
+                    w.hi[i] = fmin(w.hi[i], tk.upper[j]);
+                    w.lo[i] = fmax(w.lo[i], tk.lower[j]);
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+// ------------------------------------------------------------------ K3: QP
+// In-place lower Cholesky of the n x n matrix M (row stride ld), rows by lane.  Every lane also
+// recomputes the pivot redundantly so that one __syncwarp per column suffices.  Pivots below
+// `floor_` are clamped (rank-deficient equality rows behave like OSQP's delta-regularised ones).
+// Returns false if a pivot is not finite.
+__device__ __forceinline__ bool chol_inplace(double* M, int n, int ld, double floor_, int lane)
+{
+    bool ok = true;
+    for (int k = 0; k < n; k++) {
+        double piv = M[k * ld + k];
+        for (int j = 0; j < k; j++) piv -= M[k * ld + j] * M[k * ld + j];
+        if (!(piv > floor_)) {
+            if (!(piv == piv)) ok = false;
+            piv = floor_;
+        }
+        const double d = sqrt(piv), inv = 1.0 / d;
+        double vals[2];
+        int cnt = 0;
+        for (int i = lane; i < n; i += 32, cnt++) {
+            double v = 0.0;
+            if (i > k) {
+                v = M[i * ld + k];
+                for (int j = 0; j < k; j++) v -= M[i * ld + j] * M[k * ld + j];
+                v *= inv;
+            }
+            vals[cnt & 1] = v;
+        }
+        __syncwarp();
+        cnt = 0;
+        for (int i = lane; i < n; i += 32, cnt++) {
+            if (i > k) M[i * ld + k] = vals[cnt & 1];
+            else if (i == k) M[k * ld + k] = d;
+            else M[i * ld + k] = 0.0;  // upper triangle explicitly zero
+        }
+        __syncwarp();
+    }
+    return ok;
+}
+
+// One factorisation ("setup") of the equality-projected proximal operator
+//     x~ = argmin 1/2 x'Px - r'x  s.t.  C x = b,      P = H + sigma I + diag(rho)
+// as x~ = N r + xb with N = P^-1 - W W',  W = P^-1 C' Ls^-T,  S = C P^-1 C' = Ls Ls',  xb = W Ls^-1 b.
+// polish = true factors the active-set-reduced problem instead: rows/columns of the active
+// joints are decoupled (H -> identity there, C columns zeroed) and there is no rho.
+// Leaves N in w.A, W in w.Wm, Ls in w.Ss, Ls^-1 b in w.wb, xb in w.xb.
+__device__ __forceinline__ bool qp_setup(const Layout& L, const WM& w, double sigma, const double* rho_vec,
+                                         bool polish, const double* bvec, int lane)
+{
+    const int nv = L.nv, me = L.me, LD = L.LD, LDE = L.LDE;
+    bool ok = true;
+    // S1: P
+    for (int i = lane; i < nv; i += 32) {
+        const bool ai = polish && w.act[i];
+        for (int j = 0; j < nv; j++) {
+            double v = w.Hs[i * LD + j];
+            if (polish && (ai || w.act[j])) v = (i == j) ? 1.0 : 0.0;
+            if (i == j) v += sigma + (polish ? 0.0 : rho_vec[i]);
+            w.A[i * LD + j] = v;
+        }
+    }
+    __syncwarp();
+    // S2: P = L L'
+    ok = chol_inplace(w.A, nv, LD, 1e-300, lane) && ok;
+    // S3: B = L^-1 (lower), column c by lane c, uniform loops
+    for (int c = lane; c < nv; c += 32) {
+        for (int i = 0; i < nv; i++) {
+            double v = (i == c) ? 1.0 : 0.0;
+            for (int j = 0; j < i; j++) v -= w.A[i * LD + j] * w.B[j * LD + c];
+            w.B[i * LD + c] = (i >= c) ? v / w.A[i * LD + i] : 0.0;
+        }
+    }
+    __syncwarp();
+    if (me > 0) {
+        // S4: Y = L^-1 C'   (nv x me)
+        for (int i = lane; i < nv; i += 32) {
+            for (int r = 0; r < me; r++) {
+                double v = 0.0;
+                for (int j = 0; j <= i; j++) {
+                    const double cj = (polish && w.act[j]) ? 0.0 : w.Cs[r * LD + j];
+                    v += w.B[i * LD + j] * cj;
+                }
+                w.Ym[i * LDE + r] = v;
+            }
+        }
+        __syncwarp();
+        // S5: S = Y'Y (me x me)
+        double smax = 0.0;
+        for (int p = lane; p < me * me; p += 32) {
+            const int r = p / me, c = p - r * me;
+            double v = 0.0;
+            for (int i = 0; i < nv; i++) v += w.Ym[i * LDE + r] * w.Ym[i * LDE + c];
+            w.Ss[r * LDE + c] = v;
+            if (r == c) smax = fmax(smax, v);
+        }
+        smax = warp_max(smax);
+        __syncwarp();
+        // S6: S = Ls Ls'
+        ok = chol_inplace(w.Ss, me, LDE, 1e-14 * smax + 1e-300, lane) && ok;
+        // S7: V = Y Ls^-T, row i by lane i (in place)
+        for (int i = lane; i < nv; i += 32) {
+            for (int r = 0; r < me; r++) {
+                double v = w.Ym[i * LDE + r];
+                for (int c = 0; c < r; c++) v -= w.Ss[r * LDE + c] * w.Ym[i * LDE + c];
+                w.Ym[i * LDE + r] = v / w.Ss[r * LDE + r];
+            }
+        }
+        __syncwarp();
+        // S8: W = L^-T V  (nv x me), row j by lane j
+        for (int j = lane; j < nv; j += 32) {
+            for (int r = 0; r < me; r++) {
+                double v = 0.0;
+                for (int i = j; i < nv; i++) v += w.B[i * LD + j] * w.Ym[i * LDE + r];
+                w.Wm[j * LDE + r] = v;
+            }
+        }
+        __syncwarp();
+    }
+    // S9: N = L^-T L^-1 - W W'  (into w.A, row a by lane a)
+    for (int a = lane; a < nv; a += 32) {
+        for (int c = 0; c < nv; c++) {
+            double v = 0.0;
+            const int i0 = a > c ? a : c;
+            for (int i = i0; i < nv; i++) v += w.B[i * LD + a] * w.B[i * LD + c];
+            for (int r = 0; r < me; r++) v -= w.Wm[a * LDE + r] * w.Wm[c * LDE + r];
+            w.A[a * LD + c] = v;
+        }
+    }
+    // wb = Ls^-1 b (forward substitution, one entry finalised per step)
+    for (int r = lane; r < me; r += 32) w.wb[r] = bvec[r];
+    __syncwarp();
+    for (int c = 0; c < me; c++) {
+        if (lane == (c & 31)) w.wb[c] = w.wb[c] / w.Ss[c * LDE + c];
+        __syncwarp();
+        const double wc = w.wb[c];
+        for (int r = lane; r < me; r += 32)
+            if (r > c) w.wb[r] -= w.Ss[r * LDE + c] * wc;
+        __syncwarp();
+    }
+    for (int i = lane; i < nv; i += 32) {
+        double v = 0.0;
+        for (int r = 0; r < me; r++) v += w.Wm[i * LDE + r] * w.wb[r];
+        w.xb[i] = v;
+    }
+    __syncwarp();
+    return ok;
+}
+
+// y = N r + xb for this lane's rows (r, xb, N in shared memory)
+__device__ __forceinline__ double apply_N(const Layout& L, const WM& w, int i)
+{
+    double v = w.xb[i];
+    for (int j = 0; j < L.nv; j++) v += w.A[i * L.LD + j] * w.r[j];
+    return v;
+}
+
+struct QpResult {
+    int status, iters;
+};
+
+// The QP of one tick:  min 1/2 x'Hx + g'x  s.t.  Cs x = b,  lo <= x_J <= hi.
+// ADMM (OSQP's iteration, with the equality rows projected exactly inside the x-update) predicts the
+// active set; the polish solves the active-set-reduced equality QP and is accepted only with a KKT
+// certificate (primal box feasibility + dual signs + stationarity), which makes the returned point the
+// exact optimum; otherwise ADMM continues.  Without box rows the problem is a pure equality QP and a few
+// proximal steps solve it.
+__device__ __forceinline__ QpResult k3_solve(const TickParams& P, const WM& w, bool warm, int lane)
+{
+    const Layout& L = P.L;
+    const Settings& st = P.st;
+    const int nv = L.nv, me = L.me, LD = L.LD, LDE = L.LDE;
+    QpResult res = {1, 0};
+
+    // per-variable step: 0 (unbounded), rho (box), 1e3 rho (lo == hi, OSQP's equality-row scaling)
+    bool any_box = false, infeasible = false;
+    double gmax = 0.0;
+    for (int i = lane; i < nv; i += 32) {
+        const double lo = w.lo[i], hi = w.hi[i];
+        double rv = 0.0;
+        if (lo > -kInfHalf || hi < kInfHalf) rv = (lo == hi) ? 1e3 * st.rho : st.rho;
+        if (lo > hi) infeasible = true;
+        w.t[i] = rv;  // rho_vec lives in w.t during ADMM
+        any_box |= rv > 0.0;
+        gmax = fmax(gmax, fabs(w.g[i]));
+        if (!warm) {
+            w.x[i] = 0.0, w.z[i] = 0.0, w.y[i] = 0.0;
+        }
+        if (rv > 0.0) w.z[i] = fmin(fmax(w.z[i], lo), hi);
+        else w.z[i] = 0.0, w.y[i] = 0.0;
+    }
+    any_box = __any_sync(kFull, any_box);
+    infeasible = __any_sync(kFull, infeasible);
+    gmax = warp_max(gmax);
+    __syncwarp();
+    if (infeasible) {
+        res.status = 2;
+        return res;
+    }
+
+    if (!any_box) {
+        // pure equality QP: proximal-point iterations x <- argmin 1/2x'Hx+g'x+sigma/2|x-x_k|^2 s.t. Cx=b
+        if (!qp_setup(L, w, st.sigma, w.t, false, w.b, lane)) {
+            res.status = 2;
+            return res;
+        }
+        double dx = 0.0;
+        for (int it = 0; it < st.eq_iters; it++) {
+            for (int i = lane; i < nv; i += 32) w.r[i] = st.sigma * w.x[i] - w.g[i];
+            __syncwarp();
+            dx = 0.0;
+            double xn[2];
+            int cnt = 0;
+            for (int i = lane; i < nv; i += 32, cnt++) {
+                xn[cnt & 1] = apply_N(L, w, i);
+                dx = fmax(dx, fabs(xn[cnt & 1] - w.x[i]));
+            }
+            __syncwarp();
+            cnt = 0;
+            for (int i = lane; i < nv; i += 32, cnt++) w.x[i] = xn[cnt & 1];
+            __syncwarp();
+            res.iters++;
+        }
+        dx = warp_max(dx);
+        res.status = (dx == dx) ? ((st.sigma * dx <= st.eps * (1.0 + gmax)) ? 0 : 1) : 2;
+        return res;
+    }
+
+    for (int round = 0; round < st.max_rounds; round++) {
+        // ---- ADMM phase
+        for (int i = lane; i < nv; i += 32) {
+            const double lo = w.lo[i], hi = w.hi[i];
+            w.t[i] = (lo > -kInfHalf || hi < kInfHalf) ? ((lo == hi) ? 1e3 * st.rho : st.rho) : 0.0;
+        }
+        __syncwarp();
+        if (!qp_setup(L, w, st.sigma, w.t, false, w.b, lane)) {
+            res.status = 2;
+            return res;
+        }
+        double rp = 0.0, rd = 0.0;
+        for (int it = 0; it < st.admm_iters; it++) {
+            for (int i = lane; i < nv; i += 32) {
+                const double rv = w.t[i];
+                w.r[i] = st.sigma * w.x[i] - w.g[i] + (rv > 0.0 ? rv * w.z[i] - w.y[i] : 0.0);
+            }
+            __syncwarp();
+            rp = 0.0, rd = 0.0;
+            double xt[2];
+            int cnt = 0;
+            for (int i = lane; i < nv; i += 32, cnt++) xt[cnt & 1] = apply_N(L, w, i);
+            __syncwarp();
+            cnt = 0;
+            for (int i = lane; i < nv; i += 32, cnt++) {
+                const double xti = xt[cnt & 1], rv = w.t[i];
+                const double xo = w.x[i];
+                const double xn = st.alpha * xti + (1.0 - st.alpha) * xo;
+                rd = fmax(rd, st.sigma * fabs(xn - xo));
+                w.x[i] = xn;
+                if (rv > 0.0) {
+                    const double zo = w.z[i], yo = w.y[i];
+                    const double zr = st.alpha * xti + (1.0 - st.alpha) * zo;
+                    const double zn = fmin(fmax(zr + yo / rv, w.lo[i]), w.hi[i]);
+                    w.y[i] = yo + rv * (zr - zn);
+                    w.z[i] = zn;
+                    rd = fmax(rd, rv * fabs(zn - zo));
+                    rp = fmax(rp, fabs(xn - zn));
+                }
+            }
+            __syncwarp();
+            res.iters++;
+        }
+        rp = warp_max(rp), rd = warp_max(rd);
+        if (!(rp == rp) || !(rd == rd)) {
+            res.status = 2;
+            return res;
+        }
+        const bool admm_converged = rp <= st.eps && rd <= st.eps * (1.0 + gmax);
+
+        // ---- polish: active set by OSQP's rule (polish.c), then the reduced equality QP
+        for (int i = lane; i < nv; i += 32) {
+            const double rv = w.t[i];
+            int a = 0;
+            double bd = 0.0;
+            if (rv > 0.0) {
+                const double lo = w.lo[i], hi = w.hi[i], z = w.z[i], y = w.y[i];
+                if (lo == hi) a = 3, bd = lo;
+                else if (z - lo < -y) a = 1, bd = lo;
+                else if (hi - z < y) a = 2, bd = hi;
+            }
+            w.act[i] = a;
+            w.bd[i] = bd;
+        }
+        __syncwarp();
+        for (int i = lane; i < nv; i += 32) {
+            double v;
+            if (w.act[i]) {
+                v = -w.bd[i];
+            } else {
+                v = w.g[i];
+                for (int j = 6; j < nv; j++)
+                    if (w.act[j]) v += w.Hs[i * LD + j] * w.bd[j];
+            }
+            w.gp[i] = v;
+            w.lam[i] = w.act[i] ? w.bd[i] : w.x[i];  // polish iterate xp lives in w.lam[0..nv)
+        }
+        for (int r = lane; r < me; r += 32) {
+            double v = w.b[r];
+            for (int j = 6; j < nv; j++)
+                if (w.act[j]) v -= w.Cs[r * LD + j] * w.bd[j];
+            w.bp[r] = v;
+        }
+        __syncwarp();
+        bool pol_ok = qp_setup(L, w, st.sigma, w.t, true, w.bp, lane);
+        double* xp = w.lam;
+        for (int it = 0; it < st.polish_iters; it++) {
+            for (int i = lane; i < nv; i += 32) w.r[i] = st.sigma * xp[i] - w.gp[i];
+            __syncwarp();
+            double xn[2];
+            int cnt = 0;
+            for (int i = lane; i < nv; i += 32, cnt++) xn[cnt & 1] = apply_N(L, w, i);
+            __syncwarp();
+            cnt = 0;
+            for (int i = lane; i < nv; i += 32, cnt++) xp[i] = xn[cnt & 1];
+            __syncwarp();
+        }
+        // multipliers of the equality rows: lambda = Ls^-T (W' r - wb), r = sigma xp - g'
+        for (int i = lane; i < nv; i += 32) w.r[i] = st.sigma * xp[i] - w.gp[i];
+        __syncwarp();
+        double* lam = w.bp;  // reuse (b' is consumed)
+        for (int r = lane; r < me; r += 32) {
+            double v = -w.wb[r];
+            for (int i = 0; i < nv; i++) v += w.Wm[i * LDE + r] * w.r[i];
+            lam[r] = v;
+        }
+        __syncwarp();
+        for (int c = me - 1; c >= 0; c--) {
+            if (lane == (c & 31)) lam[c] = lam[c] / w.Ss[c * LDE + c];
+            __syncwarp();
+            const double lc = lam[c];
+            for (int r = lane; r < c; r += 32) lam[r] -= w.Ss[c * LDE + r] * lc;
+            __syncwarp();
+        }
+        // certificate: y_full = -(H xp + g + C' lambda)
+        bool cert = pol_ok;
+        for (int i = lane; i < nv; i += 32) {
+            double v = w.g[i];
+            for (int j = 0; j < nv; j++) v += w.Hs[i * LD + j] * xp[j];
+            for (int r = 0; r < me; r++) v += w.Cs[r * LD + i] * lam[r];
+            const double yf = -v;
+            const int a = w.act[i];
+            const double xi = xp[i];
+            const double tolx = 1e-9 * (1.0 + fabs(xi));
+            const double toly = 1e-8 * (1.0 + gmax);
+            if (!(xi == xi) || !(yf == yf)) cert = false;
+            if (w.t[i] > 0.0 && (xi > w.hi[i] + tolx || xi < w.lo[i] - tolx)) cert = false;
+            if (a == 0 && fabs(yf) > toly) cert = false;
+            if (a == 1 && yf > toly) cert = false;
+            if (a == 2 && yf < -toly) cert = false;
+            w.r[i] = yf;  // keep for the warm start
+        }
+        cert = __all_sync(kFull, cert);
+        __syncwarp();
+        if (cert) {
+            for (int i = lane; i < nv; i += 32) {
+                const double xi = xp[i];
+                w.x[i] = xi;
+                if (w.t[i] > 0.0) {
+                    w.z[i] = fmin(fmax(xi, w.lo[i]), w.hi[i]);
+                    w.y[i] = w.act[i] ? w.r[i] : 0.0;
+                }
+            }
+            __syncwarp();
+            res.status = 0;
+            return res;
+        }
+        if (admm_converged) {
+            res.status = 0;
+            return res;
+        }
+    }
+    res.status = 1;
+    return res;
+}
+
+// ------------------------------------------------------------------ K4: ForwardEuler on R3 x SO(3) x R^n
+// p += v dt;  R <- exp(w dt) R (manif tangent + group = left-plus, ForwardEuler.h:82);  s += sdot dt
+__device__ __forceinline__ void k4_integrate(int n, double* bp, double* bq, double* s, const double* nu, double dt,
+                                             int lane)
+{
+    if (lane < 3) bp[lane] += nu[lane] * dt;
+    double phi[3] = {nu[3] * dt, nu[4] * dt, nu[5] * dt}, dq[4], q[4] = {bq[0], bq[1], bq[2], bq[3]}, qn[4];
+    so3_exp(phi, dq);
+    quat_mul(dq, q, qn);
+    const double inv = 1.0 / sqrt(qn[0] * qn[0] + qn[1] * qn[1] + qn[2] * qn[2] + qn[3] * qn[3]);
+    __syncwarp();
+    if (lane < 4) bq[lane] = qn[lane] * inv;
+    for (int j = lane; j < n; j += 32) s[j] += nu[6 + j] * dt;
+    __syncwarp();
+}
+
+}  // namespace blfik

@@ -1,0 +1,228 @@
+/*
+ * blfik.h -- C ABI of libblfik_cuda.so: the batched IntegrationBasedIK control tick
+ * of bipedal-locomotion-framework on NVIDIA B200 (sm_100a), FP64.
+ *
+ * One call of blfik_tick() runs, for N independent robots at once, what the
+ * reference runs for one robot per control period (citations relative to the
+ * reference tree):
+ *
+ *   kinDyn->setRobotState(...)            caller, e.g. src/IK/tests/QPInverseKinematicsTest.cpp:466-472
+ *   task->update() for every task         src/IK/src/QPInverseKinematics.cpp:429-439
+ *   H, g, constraint stack                src/IK/src/QPInverseKinematics.cpp:442-491
+ *   OsqpEigen solve                       src/IK/src/QPInverseKinematics.cpp:494-528
+ *   unpack [base twist; joint velocity]   src/IK/src/QPInverseKinematics.cpp:531-541
+ *   ForwardEuler::oneStepIntegration      src/ContinuousDynamicalSystem/include/BipedalLocomotion/
+ *                                         ContinuousDynamicalSystem/ForwardEuler.h:96-124
+ *
+ * The boundary is plain C: opaque handles, plain pointers and sizes.  All batch
+ * arrays are robot-major ("array of robots"): element (i, c) of an array with C
+ * components per robot lives at data[i*C + c].  Quaternions are stored (x, y, z, w)
+ * as Eigen/manif do; twists are [linear; angular] in the MIXED representation
+ * (base linear and angular velocity expressed in the inertial frame), as
+ * QPInverseKinematics.cpp:531-541 and SE3Task.cpp:92-102 require.
+ *
+ * Error convention (the reference returns bool and logs, e.g.
+ * QPInverseKinematics.cpp:416-426): every function returns BLFIK_OK (0) or a
+ * negative blfik_error; blfik_last_error() gives the message.  There is no CPU
+ * fallback: without a CUDA device every compute entry point fails.
+ *
+ * Threading: a blfik_problem is single-writer; work is enqueued on the problem's
+ * CUDA stream and is asynchronous until blfik_sync() or a host-memory getter.
+ */
+#ifndef BLFIK_H
+#define BLFIK_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BLFIK_VERSION 1
+#define BLFIK_INFTY 1e30 /* OsqpEigen::INFTY, QPInverseKinematics.cpp:481-482 */
+
+typedef enum {
+    BLFIK_OK = 0,
+    BLFIK_ERR_INVALID_ARGUMENT = -1,
+    BLFIK_ERR_CUDA = -2,
+    BLFIK_ERR_UNSUPPORTED = -3,
+    BLFIK_ERR_NOT_READY = -4,  /* e.g. a set-point was never set (SE3Task.cpp:245-249) */
+    BLFIK_ERR_SOLVER = -5      /* at least one instance did not reach status 0 (QPInverseKinematics.cpp:518-523) */
+} blfik_error;
+
+/* task kinds; the names are the reference's factory strings (BLF_REGISTER_IK_TASK) */
+typedef enum {
+    BLFIK_TASK_SE3 = 0,                   /* src/IK/src/SE3Task.cpp                 */
+    BLFIK_TASK_COM = 1,                   /* src/IK/src/CoMTask.cpp                 */
+    BLFIK_TASK_SO3 = 2,                   /* src/IK/src/SO3Task.cpp                 */
+    BLFIK_TASK_JOINT_TRACKING = 3,        /* src/IK/src/JointTrackingTask.cpp       */
+    BLFIK_TASK_JOINT_LIMITS = 4,          /* src/IK/src/JointLimitsTask.cpp         */
+    BLFIK_TASK_JOINT_VELOCITY_LIMITS = 5, /* src/IK/src/JointVelocityLimitsTask.cpp */
+    BLFIK_TASK_R3 = 6                     /* src/IK/src/R3Task.cpp                  */
+} blfik_task_type;
+
+/* where a caller-provided batch buffer lives */
+typedef enum { BLFIK_MEM_HOST = 0, BLFIK_MEM_DEVICE = 1 } blfik_mem;
+
+/* per-instance solver status after a tick */
+typedef enum {
+    BLFIK_STATUS_SOLVED = 0,     /* KKT point certified (polish) or ADMM residuals below eps */
+    BLFIK_STATUS_MAX_ITER = 1,   /* OSQP "solved inaccurate": iteration budget exhausted      */
+    BLFIK_STATUS_FAILED = 2      /* infeasible bounds, factorisation breakdown or NaN         */
+} blfik_status;
+
+/* flags of blfik_tick */
+#define BLFIK_TICK_INTEGRATE 1u   /* apply ForwardEuler after each solve (closed loop)           */
+#define BLFIK_TICK_WARM_START 2u  /* start ADMM from the previous tick's (x, z, y) (reference does,
+                                     QPInverseKinematics.cpp:494-509)                             */
+
+/* Kinematic tree in the layout iDynTree's reduced models boil down to (stands in for
+ * std::shared_ptr<iDynTree::KinDynComputations>, IKLinearTask.h:40).  Link 0 is the
+ * floating base; parent[k] < k; link k>=1 is the child of the revolute joint with DoF
+ * index dof[k]:  W_H_k = W_H_parent * (X_rot[k], X_pos[k]) * Rot(axis[k], s[dof[k]]). */
+typedef struct {
+    int32_t n_dofs;
+    int32_t n_frames;
+    const int32_t* parent;     /* [n_dofs+1]                                            */
+    const int32_t* dof;        /* [n_dofs+1], dof[0] = -1                               */
+    const double* X_rot;       /* [n_dofs+1][9] row-major                               */
+    const double* X_pos;       /* [n_dofs+1][3]                                         */
+    const double* axis;        /* [n_dofs+1][3] unit, in the joint (= child link) frame */
+    const double* mass;        /* [n_dofs+1]                                            */
+    const double* com;         /* [n_dofs+1][3] in the link frame                       */
+    const int32_t* frame_link; /* [n_frames]                                            */
+    const double* frame_rot;   /* [n_frames][9] link <- frame                           */
+    const double* frame_pos;   /* [n_frames][3]                                         */
+} blfik_model_desc;
+
+/* One task; fields mirror the reference's parameter-handler keys. */
+typedef struct {
+    int32_t type;               /* blfik_task_type                                      */
+    int32_t priority;           /* 0 hard constraint, 1 weighted cost (addTask, QPInverseKinematics.cpp:167-249) */
+    int32_t frame;              /* frame index ("frame_name"), SE3/SO3/R3               */
+    int32_t mask[3];            /* "mask" of the linear part, SE3/CoM/R3                */
+    int32_t controller_enabled; /* setTaskControllerMode, SE3Task.cpp:251-258           */
+    double kp_linear[3];        /* "kp_linear" (scalar gains are replicated)            */
+    double kp_angular[3];       /* "kp_angular"                                         */
+    const double* kp_joint;     /* "kp" [n]                 JointTrackingTask           */
+    const double* weight;       /* "weight" [rows]          priority-1 tasks            */
+    const double* klim;         /* "klim" [n]               JointLimitsTask             */
+    const double* upper_limits; /* [n] JointLimitsTask (positions) / JointVelocityLimitsTask (velocities) */
+    const double* lower_limits; /* [n]                                                  */
+    double sampling_time;       /* "sampling_time" [s]      JointLimitsTask             */
+} blfik_task_desc;
+
+/* ADMM + polish parameters.  rho/sigma/alpha have OSQP's meaning (osqp v0.6.3); the
+ * equality rows are projected exactly inside the x-update (the rho_eq -> inf limit
+ * of OSQP's per-row rho), the box rows (joint limits) are the ADMM-split part.       */
+typedef struct {
+    double rho;            /* step on the box rows                    (default 1.0)    */
+    double sigma;          /* proximal regularisation                 (default 1e-3)   */
+    double alpha;          /* over-relaxation                         (default 1.6)    */
+    double eps;            /* inf-norm residual tolerance of ADMM     (default 1e-7)   */
+    int32_t admm_iters;    /* ADMM iterations before each polish try  (default 10)     */
+    int32_t max_rounds;    /* ADMM+polish rounds before giving up     (default 20)     */
+    int32_t polish_iters;  /* proximal refinement steps in the polish (default 4)      */
+    int32_t eq_iters;      /* proximal steps when there are no box rows (default 5)    */
+} blfik_solver_settings;
+
+typedef struct blfik_model blfik_model;
+typedef struct blfik_problem blfik_problem;
+
+/* ---- life cycle ------------------------------------------------------------------ */
+/* replaces kinDyn->loadRobotModel(...) + setFrameVelocityRepresentation(MIXED)        */
+int blfik_model_create(const blfik_model_desc* desc, blfik_model** out);
+void blfik_model_destroy(blfik_model* model);
+
+/* replaces QPInverseKinematics::addTask x ntasks + finalize()
+ * (QPInverseKinematics.cpp:167-249, 323-395) for a batch of N robots on one device.    */
+int blfik_problem_create(const blfik_model* model, const blfik_task_desc* tasks, int32_t ntasks,
+                         int64_t n_instances, int32_t device, blfik_problem** out);
+void blfik_problem_destroy(blfik_problem* problem);
+
+void blfik_default_settings(blfik_solver_settings* s);
+int blfik_set_solver_settings(blfik_problem* problem, const blfik_solver_settings* s);
+
+/* ---- per-tick inputs -------------------------------------------------------------- */
+/* replaces kinDyn->setRobotState(world_H_base, s, ...) / dynamics->setState(...)
+ * (FloatingBaseSystemVelocityKinematics.cpp:69-73): base_pos [N][3], base_quat [N][4], s [N][n] */
+int blfik_set_state(blfik_problem* problem, const double* base_pos, const double* base_quat,
+                    const double* s, int32_t mem);
+/* replaces integrator->getSolution() (Integrator.h:117-122)                            */
+int blfik_get_state(blfik_problem* problem, double* base_pos, double* base_quat, double* s,
+                    int32_t mem);
+
+/* replaces task->setSetPoint(...) (SE3Task.cpp:323-336, CoMTask.cpp:237-247, SO3Task.cpp:194-206,
+ * JointTrackingTask.cpp:162-185, R3Task.cpp:245-256).  data is [N][len] with len:
+ *   SE3: 13 = p_d(3) q_d(4) v_ff(3) w_ff(3)     CoM / R3: 6 = p_d(3) v_ff(3)
+ *   SO3:  7 = q_d(4) w_ff(3)                    JointTracking: 2n = s_d(n) sdot_d(n)          */
+int blfik_set_setpoint(blfik_problem* problem, int32_t task, const double* data, int32_t mem);
+int32_t blfik_setpoint_len(const blfik_problem* problem, int32_t task);
+
+/* replaces QPInverseKinematics::setTaskWeight (QPInverseKinematics.cpp:251-305); host pointer,
+ * shared by the whole batch, takes effect on the next tick                             */
+int blfik_set_weight(blfik_problem* problem, int32_t task, const double* weight);
+/* replaces the kp_* keys / setTaskControllerMode after construction                     */
+int blfik_set_gains(blfik_problem* problem, int32_t task, const double* kp_linear,
+                    const double* kp_angular, const double* kp_joint);
+int blfik_set_controller_mode(blfik_problem* problem, int32_t task, int32_t enabled);
+
+/* ---- the tick ---------------------------------------------------------------------- */
+/* replaces QPInverseKinematics::advance() (+ ForwardEuler::integrate(0, dt) when
+ * BLFIK_TICK_INTEGRATE) repeated nticks times with the set-points held.  Asynchronous.   */
+int blfik_tick(blfik_problem* problem, int32_t nticks, double dt, uint32_t flags);
+
+/* replaces QPInverseKinematics::getOutput() (QPInverseKinematics.cpp:553-556): nu [N][6+n] =
+ * [base linear; base angular; joint velocity] per robot                                 */
+int blfik_get_output(blfik_problem* problem, double* nu, int32_t mem);
+/* per-instance blfik_status and ADMM iteration count (either may be NULL); host getters
+ * synchronise.  blfik_count_unsolved is isOutputValid() for the batch.                  */
+int blfik_get_status(blfik_problem* problem, int32_t* status, int32_t* iters, int32_t mem);
+int blfik_count_unsolved(blfik_problem* problem, int64_t* count);
+
+/* ---- stand-alone stages (K1, K4) ---------------------------------------------------- */
+/* replaces kinDyn->getWorldTransform / getFrameFreeFloatingJacobian / getCenterOfMassPosition /
+ * getCenterOfMassJacobian (call sites SE3Task.cpp:263-296, CoMTask.cpp:194-214) for the
+ * current state.  Any output may be NULL.  frames: nframes indices.
+ *   frame_pos [N][nframes][3], frame_rot [N][nframes][9], frame_jac [N][nframes][6][nv],
+ *   com [N][3], com_jac [N][3][nv]                                                      */
+int blfik_kinematics(blfik_problem* problem, const int32_t* frames, int32_t nframes,
+                     double* frame_pos, double* frame_rot, double* frame_jac, double* com,
+                     double* com_jac, int32_t mem);
+/* replaces dynamics->setControlInput({twist, sdot}) + integrator->integrate(0, dt)
+ * (FloatingBaseSystemVelocityKinematics.cpp:80-84, FixedStepIntegrator.h:94-140);
+ * nu == NULL integrates the last tick's output.  nsteps full Euler steps of dt.          */
+int blfik_integrate(blfik_problem* problem, const double* nu, int32_t mem, double dt,
+                    int32_t nsteps);
+
+/* ---- introspection for parity tests -------------------------------------------------- */
+typedef enum {
+    BLFIK_DEBUG_H = 0,   /* [N][nv][nv]  Hessian  (QPInverseKinematics.cpp:442-454)      */
+    BLFIK_DEBUG_G = 1,   /* [N][nv]      gradient                                        */
+    BLFIK_DEBUG_CEQ = 2, /* [N][me][nv]  dense equality rows in addTask order            */
+    BLFIK_DEBUG_BEQ = 3, /* [N][me]                                                      */
+    BLFIK_DEBUG_LO = 4,  /* [N][n]  joint-velocity box = intersection of the +-identity
+                            inequality rows (JointLimitsTask.cpp:227-231,
+                            JointVelocityLimitsTask.cpp:140-141)                          */
+    BLFIK_DEBUG_HI = 5   /* [N][n]                                                       */
+} blfik_debug_what;
+/* enable before a tick (allocates the dump buffers), then read after it                  */
+int blfik_debug_enable(blfik_problem* problem, int32_t enabled);
+int blfik_debug_get(blfik_problem* problem, int32_t what, double* out, int32_t mem);
+
+/* ---- plumbing ------------------------------------------------------------------------ */
+int32_t blfik_num_dofs(const blfik_problem* problem);
+int32_t blfik_num_equality_rows(const blfik_problem* problem);
+int64_t blfik_num_instances(const blfik_problem* problem);
+int blfik_sync(blfik_problem* problem);
+/* the problem's cudaStream_t (as void*); set_stream makes later work use the caller's stream */
+void* blfik_get_stream(blfik_problem* problem);
+int blfik_set_stream(blfik_problem* problem, void* cuda_stream);
+/* number of kernel launches issued so far by this problem                                */
+int64_t blfik_launch_count(const blfik_problem* problem);
+const char* blfik_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BLFIK_H */
