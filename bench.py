@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""bench.py -- IK ticks/s of the batched IntegrationBasedIK tick (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one control tick (FK + Jacobians -> task assembly -> QP -> ForwardEuler) over one
+batch of synthetic robots: the headline workload C3 of BASELINE.json (ergoCub-23, CoM + 2xSE3 feet
++ JointLimits + JointVelocityLimits hard constraints, SO3 chest + JointTracking costs), 65,536
+instances PER GPU (weak scaling: the batch is sharded by instance index, no collective on the data
+path).  Every step restores the same initial state on the device and solves cold (no warm start),
+so all K steps do identical work.
+
+`value`  : device-resident inputs, CUDA-event time of the K steps, max over ranks.
+`e2e`    : the same step through the public host-buffer API: pinned host -> device copies of the
+           state and set-points, the tick, and the device -> host read of nu + status, all timed.
+`--impl reference`: the reference's CPU implementation cannot be built here (no Eigen / iDynTree /
+           OSQP / manif in the image), so this arm times the CPU oracle -- the C restatement of the
+           reference path -- on all host cores, on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+PER_GPU_INSTANCES = 65536
+CONFIG_ID = 3
+
+
+# ------------------------------------------------------------------ helpers
+def algorithmic_flops_per_tick(n: int, me: int, admm_iters_total: np.ndarray, admm_iters_per_round: int,
+                               polish_iters: int) -> float:
+    """FP64 flops of the algorithm as designed (triangular structure exploited, 1 FMA = 2 flops),
+    summed over the batch.  DESIGN.md "Roofline" derives every term."""
+    nv = n + 6
+    kin = 4000.0 + 60.0 * n                       # FK, frame Jacobians, CoM subtree pass, controllers
+    asm = 2.0 * 3 * nv * nv + 6.0 * n             # SO3 cost rows (3 x nv x nv MAC) + diagonal tasks
+    setup = nv ** 3 + 3.0 * me * nv * nv + 2.0 * me * me * nv + me ** 3 / 3.0
+    it = 2.0 * nv * nv + 12.0 * nv                # N r + x_b and the lane-local updates
+    cert = 2.0 * nv * nv + 4.0 * me * nv + me * me
+    rounds = np.maximum(1, np.ceil(admm_iters_total / max(1, admm_iters_per_round)))
+    per = kin + asm + rounds * (2.0 * setup + polish_iters * it + cert) + admm_iters_total * it
+    return float(per.sum())
+
+
+def algorithmic_bytes_per_tick(n: int, sp_doubles: int) -> float:
+    """HBM bytes one instance-tick must move: state in, set-points in, nu + state + status out."""
+    nv = n + 6
+    return 8.0 * ((7 + n) + sp_doubles + nv + (7 + n)) + 8.0
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi SM clocks / throttle reasons while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.1)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = sorted(float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit())
+        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
+        reasons = set()
+        for s in self.samples:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.samples)}
+
+
+def cpu_oracle_rate(workload, inputs, sample: int, threads: int, repeats: int = 1):
+    """ticks/s of the CPU oracle (parity settings: eps 1e-7 + polish, cold start) on `sample` instances."""
+    from oracle.oracle import Oracle
+    orc = Oracle(workload.model, workload.tasks)
+    sub = inputs.slice(0, sample)
+    best = 0.0
+    for _ in range(repeats):
+        p, q, s = sub.base_pos.copy(), sub.base_quat.copy(), sub.s.copy()
+        t0 = time.perf_counter()
+        _, status, _ = orc.tick_batch(p, q, s, sub.setpoints, dt_integrate=workload.dt, nticks=1, nthreads=threads)
+        dt = time.perf_counter() - t0
+        best = max(best, sample / dt)
+    return best, int((status != 0).sum())
+
+
+# ------------------------------------------------------------------ reference arm
+def run_reference(args, rank: int, world: int) -> None:
+    if rank != 0:
+        return
+    import blf_b200  # noqa: F401
+    from blf_b200 import workloads as W
+    w = W.config(CONFIG_ID)
+    cores = os.cpu_count() or 1
+    sample = 512 * cores
+    inputs = W.synth_inputs(w, sample, CONFIG_ID)
+    for _ in range(max(0, min(args.warmup, 1))):
+        cpu_oracle_rate(w, inputs, min(sample, 64 * cores), cores)
+    steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    rates = [cpu_oracle_rate(w, inputs, sample, cores)[0] for _ in range(steps)]
+    wall = time.perf_counter() - t0
+    value = sample * steps / sum(sample / r for r in rates)
+    line = {
+        "impl": "reference", "metric": "IK ticks/s", "value": value, "unit": "ticks/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * wall / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"C3 ergoCub-23 IK tick (m=107 reference rows), bounded sample of {sample} instances per step",
+                   "instances_per_step": sample, "dt": w.dt},
+        "cpu_baseline": {"value": value, "unit": "ticks/s", "cores": cores, "kind": "port",
+                         "sample": f"{sample} instances x {steps} steps, CPU oracle (C restatement of the reference path; "
+                                   "the reference binary cannot be built here), OSQP-equivalent ADMM eps 1e-7 + polish, cold start"},
+        "e2e": {"value": value, "unit": "ticks/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ our arm
+def run_ours(args, rank: int, local_rank: int, world: int) -> None:
+    import torch
+    import torch.distributed as dist
+    import blf_b200  # noqa: F401
+    from blf_b200 import capi, workloads as W
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    w = W.config(CONFIG_ID)
+    n, nv = w.model.n, w.model.n + 6
+    n_local = args.instances
+    n_global = n_local * world
+    lo, hi = W.shard_range(n_global, rank, world)
+    # global synthetic batch, sliced by instance range: data of instance i are independent of `world`
+    inputs = W.synth_inputs(w, n_global, CONFIG_ID).slice(lo, hi)
+
+    model = capi.Model(w.model)
+    prob = capi.Problem(model, w.tasks, n_local, device=local_rank)
+    stream = torch.cuda.ExternalStream(prob.stream, device=local_rank)
+
+    dev = torch.device("cuda", local_rank)
+    d_state = [torch.from_numpy(a).to(dev) for a in (inputs.base_pos, inputs.base_quat, inputs.s)]
+    h_state = [torch.from_numpy(a).pin_memory() for a in (inputs.base_pos, inputs.base_quat, inputs.s)]
+    h_sp = [None if sp is None else torch.from_numpy(sp).pin_memory() for sp in inputs.setpoints]
+    h_nu = torch.empty((n_local, nv), dtype=torch.float64).pin_memory()
+    h_status = torch.empty(n_local, dtype=torch.int32).pin_memory()
+    sp_doubles = sum(0 if sp is None else sp.shape[1] for sp in inputs.setpoints)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    prob.set_inputs(inputs)
+    prob.sync()
+
+    def device_step():
+        prob.set_state(*d_state)                       # device -> device restore of the initial state
+        prob.tick(1, w.dt, integrate=True, warm_start=False)
+
+    def e2e_step():
+        prob.set_state(*h_state)                       # pinned host -> device
+        for t, sp in enumerate(h_sp):
+            if sp is not None:
+                prob.set_setpoint(t, sp)
+        prob.tick(1, w.dt, integrate=True, warm_start=False)
+        prob.L.blfik_get_output(prob.handle, h_nu.data_ptr(), capi.MEM_HOST)   # device -> host (+ sync)
+        prob.L.blfik_get_status(prob.handle, h_status.data_ptr(), None, capi.MEM_HOST)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step_fn, steps):
+        total = 0.0
+        for _ in range(steps):
+            flush.fill_(1)                            # evict L2 (126 MB) between steps, untimed
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            step_fn()
+            e1.record(stream)
+            e1.synchronize()
+            total += e0.elapsed_time(e1)
+        return total
+
+    for _ in range(max(3, args.warmup)):
+        device_step()
+    prob.sync()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    launches0 = prob.launch_count
+    barrier()
+    ms_dev = timed(device_step, args.steps)
+    barrier()
+    launches = prob.launch_count - launches0
+    status, iters = prob.get_status()
+    unsolved = int((status != 0).sum())
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    ms_e2e = timed(e2e_step, args.steps)
+    barrier()
+    clocks = sampler.stop() if sampler else None
+
+    t = torch.tensor([ms_dev, ms_e2e, float(unsolved)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms_dev, ms_e2e, unsolved = float(tmax[0]), float(tmax[1]), int(tsum[2])
+    ticks_total = n_global * args.steps
+
+    if rank == 0:
+        fp64_peak = capi.measure_fp64_peak(local_rank, 300.0)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        flops_launch = algorithmic_flops_per_tick(n, prob.me, iters.astype(np.float64), prob_settings["admm_iters"],
+                                                  prob_settings["polish_iters"])
+        kernel_ms = ms_dev / args.steps
+        achieved_tf = flops_launch / (kernel_ms * 1e-3) * 1e-12
+        bytes_launch = algorithmic_bytes_per_tick(n, sp_doubles) * n_local
+        cores = os.cpu_count() or 1
+        cpu_sample = 1024 * cores
+        cpu_rate, cpu_bad = cpu_oracle_rate(w, inputs, min(cpu_sample, n_local), cores)
+        line = {
+            "metric": "IK ticks/s", "value": ticks_total / (ms_dev * 1e-3), "unit": "ticks/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C3: ergoCub-23 IK tick, CoM + 2xSE3 feet + JointLimits + JointVelocityLimits (priority 0, "
+                                   "m=107 reference rows) + SO3 chest + JointTracking (priority 1), then ForwardEuler",
+                       "instances_per_gpu": n_local, "instances_total": n_global, "dt": w.dt,
+                       "parallelism": f"instance-sharded x{world}, no collective", "warm_start": False,
+                       "solver": prob_settings, "l2": "256 MiB write between steps (untimed) flushes the 126 MB L2",
+                       "unsolved_instances": unsolved},
+            "e2e": {"value": ticks_total / (ms_e2e * 1e-3), "unit": "ticks/s",
+                    "h2d_bytes_per_step": int(8 * n_local * (7 + n + sp_doubles)),
+                    "d2h_bytes_per_step": int(n_local * (8 * nv + 4))},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                         "frac": achieved_tf / fp64_peak if fp64_peak else None, "traffic": None,
+                         "peak_source": "measured live by blfik_measure_fp64_peak (dependency-free DFMA loop); "
+                                        "MEASURED_PEAKS.json has no FP64 figure",
+                         "kernel": "blfik_tick_kernel", "flops_per_launch": flops_launch,
+                         "hbm": {"achieved": bytes_launch / (kernel_ms * 1e-3) * 1e-9, "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": bytes_launch / (kernel_ms * 1e-3) * 1e-9 / hbm_peak, "peak_source": hbm_src,
+                                 "bytes_per_launch": bytes_launch}},
+            "cpu_baseline": {"value": cpu_rate, "unit": "ticks/s", "cores": cores, "kind": "port",
+                             "sample": f"{min(cpu_sample, n_local)} instances x 1 tick of the same workload, CPU oracle "
+                                       f"(eps 1e-7 + polish, cold start), {cpu_bad} unsolved"},
+            "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    prob.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+prob_settings = {"rho": 1.0, "sigma": 1e-3, "alpha": 1.6, "eps": 1e-7, "admm_iters": 10, "max_rounds": 20,
+                 "polish_iters": 4, "eq_iters": 5}
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--instances", type=int, default=PER_GPU_INSTANCES, help="instances per GPU")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world == 1 and args.gpus > 1:
+        # convenience: relaunch under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__),
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--instances", str(args.instances)]
+        raise SystemExit(subprocess.call(cmd))
+    run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

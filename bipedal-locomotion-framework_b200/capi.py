@@ -34,7 +34,7 @@ EXPORTS = [
     "blfik_set_controller_mode", "blfik_tick", "blfik_get_output", "blfik_get_status",
     "blfik_count_unsolved", "blfik_kinematics", "blfik_integrate", "blfik_debug_enable", "blfik_debug_get",
     "blfik_num_dofs", "blfik_num_equality_rows", "blfik_num_instances", "blfik_sync", "blfik_get_stream",
-    "blfik_set_stream", "blfik_launch_count", "blfik_last_error",
+    "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak",
 ]
 
 
@@ -107,6 +107,15 @@ def load():
         _lib.blfik_set_solver_settings.argtypes = [C.c_void_p, C.c_void_p]
         _lib.blfik_setpoint_len.argtypes = [C.c_void_p, C.c_int32]
     return _lib
+
+
+def measure_fp64_peak(device: int = 0, millis: float = 200.0) -> float:
+    """Sustained DFMA throughput of ``device`` in TFLOP/s (roofline denominator)."""
+    out = C.c_double(0.0)
+    lib = load()
+    lib.blfik_measure_fp64_peak.argtypes = [C.c_int32, C.c_double, C.c_void_p]
+    _check(lib.blfik_measure_fp64_peak(int(device), float(millis), C.byref(out)))
+    return float(out.value)
 
 
 def _check(rc: int) -> None:

@@ -130,6 +130,21 @@ __global__ void blfik_count_unsolved_kernel(const int* status, long long N, unsi
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
 }
 
+// FP64 roofline probe: 8 independent FMA chains per thread, no memory traffic.
+__global__ void __launch_bounds__(512) blfik_dfma_probe_kernel(double* sink, int iters, double a, double b)
+{
+    double c0 = threadIdx.x, c1 = c0 + 1, c2 = c0 + 2, c3 = c0 + 3, c4 = c0 + 4, c5 = c0 + 5, c6 = c0 + 6, c7 = c0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            c0 = fma(c0, a, b), c1 = fma(c1, a, b), c2 = fma(c2, a, b), c3 = fma(c3, a, b);
+            c4 = fma(c4, a, b), c5 = fma(c5, a, b), c6 = fma(c6, a, b), c7 = fma(c7, a, b);
+        }
+    }
+    const double r = ((c0 + c1) + (c2 + c3)) + ((c4 + c5) + (c6 + c7));
+    if (r == 123.456) sink[0] = r;
+}
+
 // =================================================================== host side
 static thread_local std::string g_err;
 
@@ -749,6 +764,40 @@ extern "C" int blfik_integrate(blfik_problem* p, const double* nu, int32_t mem, 
     blfik_integrate_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, p->stream>>>(p->n, p->N, p->base_pos, p->base_quat, p->s, src, dt, nsteps);
     CU(cudaGetLastError());
     p->launches++;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_measure_fp64_peak(int32_t device, double millis, double* tflops)
+{
+    if (!tflops) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_measure_fp64_peak] null output");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    double* sink = nullptr;
+    CU(cudaMalloc((void**)&sink, sizeof(double)));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    const int blocks = prop.multiProcessorCount * 4, threads = 512;
+    int iters = 2000;
+    double best = 0.0, spent = 0.0;
+    blfik_dfma_probe_kernel<<<blocks, threads>>>(sink, 200, 0.999999, 1e-9);  // warm-up
+    CU(cudaDeviceSynchronize());
+    while (spent < millis) {
+        CU(cudaEventRecord(e0));
+        blfik_dfma_probe_kernel<<<blocks, threads>>>(sink, iters, 0.999999, 1e-9);
+        CU(cudaEventRecord(e1));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        spent += ms;
+        const double flops = 2.0 * 64.0 * (double)iters * blocks * threads;
+        const double tf = flops / (ms * 1e-3) * 1e-12;
+        if (tf > best) best = tf;
+        if (ms < 5.0) iters *= 2;
+    }
+    cudaEventDestroy(e0), cudaEventDestroy(e1), cudaFree(sink);
+    *tflops = best;
     return BLFIK_OK;
 }
 

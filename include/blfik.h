@@ -222,6 +222,12 @@ int blfik_set_stream(blfik_problem* problem, void* cuda_stream);
 int64_t blfik_launch_count(const blfik_problem* problem);
 const char* blfik_last_error(void);
 
+/* Measurement utility (no counterpart in the reference): sustained FP64 FMA throughput of
+ * `device` in TFLOP/s from a dependency-free DFMA loop over all SMs, timed with CUDA events
+ * for about `millis` ms.  It is the denominator of the roofline fraction bench.py reports,
+ * because MEASURED_PEAKS.json carries no FP64 figure.                                     */
+int blfik_measure_fp64_peak(int32_t device, double millis, double* tflops);
+
 #ifdef __cplusplus
 }
 #endif
