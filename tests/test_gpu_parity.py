@@ -1,0 +1,405 @@
+"""Parity of the CUDA path (through the C ABI, ctypes) against the CPU oracle and the committed fixtures.
+
+Tolerances are BASELINE.json's (north_star): kinematics / Jacobians 1e-12 relative, nu within 1e-5 (inf-norm)
+of the QP optimum, integrated state within 1e-9 per tick."""
+import os
+
+import numpy as np
+import pytest
+
+import blf_b200  # noqa: F401
+from blf_b200 import capi, models as M, tasks as T, workloads as W
+from oracle.oracle import Oracle
+import scenarios as S
+
+pytestmark = pytest.mark.gpu
+
+TOL_KIN = 1e-12
+TOL_NU = 1e-5
+TOL_STATE = 1e-9
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def make(w_model, tasks, N):
+    model = capi.Model(w_model)
+    return model, capi.Problem(model, tasks, N)
+
+
+def oracle_box(o, C, l, u, me, n):
+    """per-joint box implied by the reference's +-identity inequality rows (rows after the me dense ones)."""
+    lo, hi = np.full(n, -1e30), np.full(n, 1e30)
+    r = me
+    for t in o.tasks:
+        if t.priority != 0 or not t.is_inequality:
+            continue
+        hi = np.minimum(hi, u[r:r + n])
+        lo = np.maximum(lo, -u[r + n:r + 2 * n])
+        r += 2 * n
+    return lo, hi
+
+
+@pytest.mark.parametrize("mk", [M.ergocub23, M.icub32, M.icub26, lambda: M.random_tree(20, 2), lambda: M.random_tree(35, 3)])
+def test_k1_kinematics_vs_oracle(mk):
+    m = mk()
+    N = 67                                     # ragged: not a multiple of the warps per block
+    rng = np.random.default_rng(11)
+    p = rng.uniform(-1, 1, (N, 3)); q = W.so3_exp(rng.uniform(-1.5, 1.5, (N, 3))); s = m.q_nominal + rng.uniform(-0.6, 0.6, (N, m.n))
+    tasks = [T.joint_tracking_task(m, "j", np.ones(m.n), priority=1, weight=np.ones(m.n))]
+    model, prob = make(m, tasks, N)
+    prob.set_state(p, q, s)
+    frames = list(range(0, len(m.frame_names), 2))
+    k = prob.kinematics(frames)
+    o = Oracle(m)
+    for i in range(N):
+        R, P = o.fk(p[i], q[i], s[i])
+        for fi, f in enumerate(frames):
+            Rf, pf = o.frame_pose(R, P, f)
+            J = o.frame_jacobian(R, P, f)
+            assert np.abs(k["frame_pos"][i, fi] - pf).max() <= TOL_KIN * (1 + np.abs(pf).max())
+            assert np.abs(k["frame_rot"][i, fi] - Rf).max() <= TOL_KIN
+            assert np.abs(k["frame_jac"][i, fi] - J).max() <= TOL_KIN * (1 + np.abs(J).max())
+        c, Jc = o.com(R, P)
+        assert np.abs(k["com"][i] - c).max() <= TOL_KIN * (1 + np.abs(c).max())
+        assert np.abs(k["com_jac"][i] - Jc).max() <= TOL_KIN * (1 + np.abs(Jc).max())
+    prob.close()
+
+
+@pytest.mark.parametrize("cid", [1, 3, 4])
+def test_k2_assembly_vs_oracle(cid):
+    w = W.config(cid)
+    N = 40
+    inp = W.synth_inputs(w, N, cid)
+    model, prob = make(w.model, w.tasks, N)
+    prob.set_inputs(inp)
+    prob.debug_enable(True)
+    prob.tick(1, w.dt)
+    H, g = prob.debug_get(capi.DEBUG_H), prob.debug_get(capi.DEBUG_G)
+    Ce, be = prob.debug_get(capi.DEBUG_CEQ), prob.debug_get(capi.DEBUG_BEQ)
+    lo, hi = prob.debug_get(capi.DEBUG_LO), prob.debug_get(capi.DEBUG_HI)
+    o = Oracle(w.model, w.tasks)
+    me, n = prob.me, w.model.n
+    assert me == 15
+    for i in range(N):
+        Ho, go, Co, l, u = o.assemble(inp.base_pos[i], inp.base_quat[i], inp.s[i], [None if sp is None else sp[i] for sp in inp.setpoints])
+        assert np.abs(H[i] - Ho).max() <= 1e-12 * (1 + np.abs(Ho).max())
+        assert np.abs(g[i] - go).max() <= 1e-12 * (1 + np.abs(go).max())
+        assert np.abs(Ce[i] - Co[:me]).max() <= TOL_KIN * (1 + np.abs(Co).max())
+        assert np.abs(be[i] - u[:me]).max() <= 1e-12 * (1 + np.abs(u[:me]).max())
+        lo_o, hi_o = oracle_box(o, Co, l, u, me, n)
+        assert np.allclose(lo[i], lo_o, rtol=1e-13, atol=1e-12) and np.allclose(hi[i], hi_o, rtol=1e-13, atol=1e-12)
+    prob.close()
+
+
+@pytest.mark.parametrize("cid,N", [(1, 256), (2, 4096), (3, 2048), (4, 1024)])
+def test_k3_solution_vs_oracle(cid, N):
+    """nu against the oracle's optimum (OSQP-equivalent ADMM eps 1e-7 + polish, KKT <= 1e-9)."""
+    w = W.config(cid)
+    inp = W.synth_inputs(w, N, cid)
+    model, prob = make(w.model, w.tasks, N)
+    prob.set_inputs(inp)
+    prob.tick(1, w.dt)
+    nu = prob.get_output()
+    st, it = prob.get_status()
+    sub = slice(0, min(N, 512))
+    o = Oracle(w.model, w.tasks)
+    nur, str_, _ = o.tick_batch(inp.base_pos[sub].copy(), inp.base_quat[sub].copy(), inp.s[sub].copy(),
+                                [None if sp is None else sp[sub] for sp in inp.setpoints], nthreads=8)
+    assert (st != 0).sum() <= max(1, N // 1000), f"unsolved: {np.bincount(st)}"
+    assert prob.count_unsolved() == int((st != 0).sum())
+    ok = (st[sub] == 0) & (str_ == 0)
+    assert ok.mean() > 0.99
+    assert np.abs(nu[sub][ok] - nur[ok]).max() <= TOL_NU
+    prob.close()
+
+
+@pytest.mark.parametrize("cid", [1, 3, 4])
+def test_golden_fixtures(cid):
+    g = np.load(os.path.join(GOLD, f"golden_c{cid}.npz"))
+    w = W.config(cid)
+    N = g["s"].shape[0]
+    model, prob = make(w.model, w.tasks, N)
+    prob.set_state(g["base_pos"], g["base_quat"], g["s"])
+    for t in range(len(w.tasks)):
+        if f"sp{t}" in g.files:
+            prob.set_setpoint(t, g[f"sp{t}"])
+    k = prob.kinematics([int(f) for f in g["frames"]])
+    assert np.abs(k["frame_jac"] - g["frame_jac"]).max() <= TOL_KIN * 10
+    assert np.abs(k["frame_pos"] - g["frame_pos"]).max() <= TOL_KIN * 10
+    assert np.abs(k["com_jac"] - g["com_jac"]).max() <= TOL_KIN * 10
+    prob.tick(1, w.dt, integrate=True)
+    nu = prob.get_output()
+    st, _ = prob.get_status()
+    assert np.array_equal(st, g["status"])
+    assert np.abs(nu - g["nu"]).max() <= TOL_NU
+    p, q, s = prob.get_state()
+    # the integrated state differs from the fixture only through nu * dt
+    assert np.abs(s - g["next_s"]).max() <= TOL_STATE and np.abs(p - g["next_pos"]).max() <= TOL_STATE
+    assert np.minimum(np.abs(q - g["next_quat"]).max(1), np.abs(q + g["next_quat"]).max(1)).max() <= TOL_STATE
+    prob.close()
+
+
+def test_k4_integrator_vs_oracle_and_closed_form():
+    m = M.ergocub23()
+    N = 50
+    rng = np.random.default_rng(5)
+    p = rng.uniform(-1, 1, (N, 3)); q = W.so3_exp(rng.uniform(-2, 2, (N, 3))); s = rng.uniform(-1, 1, (N, m.n))
+    nu = rng.normal(size=(N, m.nv))
+    model, prob = make(m, [T.joint_tracking_task(m, "j", np.ones(m.n), priority=1, weight=np.ones(m.n))], N)
+    prob.set_state(p, q, s)
+    prob.integrate(nu, dt=0.01, nsteps=1)
+    p1, q1, s1 = prob.get_state()
+    o = Oracle(m)
+    for i in range(N):
+        pr, qr, sr = o.integrate(p[i], q[i], s[i], nu[i], 0.01)
+        assert np.abs(p1[i] - pr).max() <= 1e-15 and np.abs(s1[i] - sr).max() <= 1e-15
+        assert np.abs(q1[i] - qr).max() <= 1e-14
+    # 5000 steps of 100 us (the reference integrator test), closed form with left-plus
+    prob.set_state(p, q, s)
+    prob.integrate(nu, dt=1e-4, nsteps=5000)
+    p2, q2, s2 = prob.get_state()
+    from helpers import rodrigues
+    for i in range(0, N, 7):
+        Rexp = rodrigues(nu[i, 3:6] * 0.5) @ W.quat_to_rot(q[i][None])[0]
+        assert np.abs(W.quat_to_rot(q2[i][None])[0] - Rexp).max() < 1e-9
+        assert np.abs(p2[i] - (p[i] + 0.5 * nu[i, :3])).max() < 1e-10 and np.abs(s2[i] - (s[i] + 0.5 * nu[i, 6:])).max() < 1e-10
+    with pytest.raises(capi.BlfikError):
+        prob.integrate(nu, dt=0.0)
+    with pytest.raises(capi.BlfikError):
+        prob.integrate(nu, dt=0.01, nsteps=0)
+    prob.close()
+
+
+@pytest.mark.parametrize("n,strict", [(20, False), (35, False), (20, True), (35, True)])
+def test_closed_loop_scenarios_lockstep(n, strict):
+    """The reference's 'QP-IK' / 'With strict limits' loops (30 ticks, dT 10 ms) on the GPU, the oracle re-solving every
+    tick from the GPU's state: nu within 1e-5, integrated state within 1e-9 per tick; final errors within the reference's
+    own acceptance tolerances."""
+    sc = S.qp_ik_scenario(n, strict_limits=strict)
+    N = 8
+    rng = np.random.default_rng(3)
+    p0 = np.tile(sc.p0, (N, 1)); q0 = np.tile(sc.q0, (N, 1)); s0 = sc.s0[None] + rng.normal(0, 0.02, (N, n))
+    s0[0] = sc.s0
+    s0[:, sc.strict] = sc.s0[sc.strict]
+    model, prob = make(sc.model, sc.tasks, N)
+    prob.set_state(p0, q0, s0)
+    sps = S.tile_setpoints(sc, N)
+    for t, sp in enumerate(sps):
+        if sp is not None:
+            prob.set_setpoint(t, sp)
+    o = Oracle(sc.model, sc.tasks)
+    p, q, s = p0.copy(), q0.copy(), s0.copy()
+    for tick in range(S.TICKS):
+        pr, qr, sr = p.copy(), q.copy(), s.copy()
+        nur, str_, _ = o.tick_batch(pr, qr, sr, sps, dt_integrate=S.DT)
+        prob.tick(1, S.DT, integrate=True, warm_start=True)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        p, q, s = prob.get_state()
+        assert np.all(st == 0) and np.all(str_ == 0)
+        assert np.abs(nu - nur).max() <= TOL_NU
+        assert np.abs(s - (sr + (nu - nur)[:, 6:] * S.DT)).max() <= TOL_STATE
+        assert np.abs(p - pr).max() <= TOL_NU * S.DT + TOL_STATE
+        for j in sc.strict:
+            assert np.abs(nu[:, 6 + j]).max() < 1e-2
+    from helpers import rot_log
+    R, P = o.fk(p[0], q[0], s[0])
+    com, _ = o.com(R, P)
+    Rf, pf = o.frame_pose(R, P, sc.ee)
+    if strict:
+        assert np.abs(s[:, sc.strict] - s0[:, sc.strict]).max() < 1e-2
+    else:
+        assert np.linalg.norm(com - sc.com_des) <= 2e-1 * np.linalg.norm(sc.com_des)
+        assert np.abs(sc.R_des.T @ (pf - sc.p_ee_des)).max() < 2e-1 and np.abs(rot_log(sc.R_des.T @ Rf)).max() < 2e-1
+    prob.close()
+
+
+def test_multi_tick_launch_equals_single_ticks_and_warm_start():
+    w = W.config(3)
+    N = 96
+    inp = W.synth_inputs(w, N, 3)
+    model, pa = make(w.model, w.tasks, N)
+    model2, pb = make(w.model, w.tasks, N)
+    for pr in (pa, pb):
+        pr.set_inputs(inp)
+    pa.tick(12, w.dt, integrate=True, warm_start=True)
+    for _ in range(12):
+        pb.tick(1, w.dt, integrate=True, warm_start=True)
+    sa, sb = pa.get_state(), pb.get_state()
+    for a, b in zip(sa, sb):
+        assert np.array_equal(a, b)
+    assert np.array_equal(pa.get_output(), pb.get_output())
+    # warm and cold starts reach the same optimum
+    pc = capi.Problem(model, w.tasks, N)
+    pc.set_state(*sa)
+    for t, sp in enumerate(inp.setpoints):
+        if sp is not None:
+            pc.set_setpoint(t, sp)
+    pc.tick(1, w.dt)
+    pa.tick(1, w.dt, warm_start=True)
+    ok = (pa.get_status()[0] == 0) & (pc.get_status()[0] == 0)
+    assert ok.all()
+    assert np.abs(pa.get_output() - pc.get_output()).max() <= 1e-7
+    for pr in (pa, pb, pc):
+        pr.close()
+
+
+def test_set_weight_gains_and_controller_mode_take_effect():
+    """setTaskWeight (QPInverseKinematics.cpp:251-305), gains and setTaskControllerMode (SE3Task.cpp:251-258)."""
+    w = W.config(4)
+    N = 32
+    inp = W.synth_inputs(w, N, 4)
+    model, prob = make(w.model, w.tasks, N)
+    prob.set_inputs(inp)
+    prob.tick(1, w.dt)
+    nu0 = prob.get_output()
+    tasks = [T.TaskSpec(**vars(t)) for t in w.tasks]
+    tasks[3].weight = np.full(6, 2.5)
+    prob.set_weight(3, tasks[3].weight)
+    tasks[6].kp_joint = np.full(w.model.n, 1.5)
+    prob.set_gains(6, kp_joint=tasks[6].kp_joint)
+    tasks[1].kp_linear = np.array([1.0, 2.0, 3.0]); tasks[1].kp_angular = np.array([0.5, 0.6, 0.7])
+    prob.set_gains(1, kp_linear=tasks[1].kp_linear, kp_angular=tasks[1].kp_angular)
+    tasks[2].controller_enabled = False
+    prob.set_controller_mode(2, False)
+    prob.tick(1, w.dt)
+    nu1 = prob.get_output()
+    o = Oracle(w.model, tasks)
+    nur, st, _ = o.tick_batch(inp.base_pos.copy(), inp.base_quat.copy(), inp.s.copy(), inp.setpoints)
+    assert np.all(st == 0)
+    assert np.abs(nu1 - nur).max() <= TOL_NU
+    assert np.abs(nu1 - nu0).max() > 1e-3
+    with pytest.raises(capi.BlfikError):
+        prob.set_weight(0, np.ones(3))         # priority-0 task has no weight
+    with pytest.raises(capi.BlfikError):
+        prob.set_weight(99, np.ones(3))
+    prob.close()
+
+
+def test_error_paths_mirror_the_reference():
+    """advance() fails until a state and every set-point were set (QPInverseKinematics.cpp:416-426, SE3Task.cpp:245-249)."""
+    w = W.config(3)
+    model, prob = make(w.model, w.tasks, 4)
+    with pytest.raises(capi.BlfikError) as e:
+        prob.tick(1, w.dt)
+    assert e.value.code == -4
+    inp = W.synth_inputs(w, 4, 3)
+    prob.set_state(inp.base_pos, inp.base_quat, inp.s)
+    with pytest.raises(capi.BlfikError) as e:
+        prob.tick(1, w.dt)
+    assert e.value.code == -4 and "set point" in str(e.value)
+    with pytest.raises(capi.BlfikError):
+        prob.get_output()
+    with pytest.raises(capi.BlfikError):
+        prob.set_setpoint(3, np.zeros((4, 1)))   # JointLimitsTask takes no set-point
+    prob.set_inputs(inp)
+    with pytest.raises(capi.BlfikError):
+        prob.tick(0, w.dt)
+    with pytest.raises(capi.BlfikError):
+        prob.tick(1, 0.0, integrate=True)
+    prob.tick(1, w.dt)
+    assert prob.count_unsolved() == 0
+    prob.close()
+    # construction-time rules (addTask, QPInverseKinematics.cpp:167-249)
+    m = capi.Model(w.model)
+    bad = T.joint_limits_task(w.model, "l", np.full(23, 0.5), 0.01)
+    bad.priority = 1
+    bad.weight = np.ones(46)
+    with pytest.raises(capi.BlfikError) as e:
+        capi.Problem(m, [bad], 4)
+    assert "inequality" in str(e.value)
+    with pytest.raises(capi.BlfikError):
+        capi.Problem(m, [T.joint_tracking_task(w.model, "j", np.ones(23), priority=1)], 4)   # no weight
+
+
+def test_edge_cases_masks_equality_joint_task_infeasible_box():
+    m = M.ergocub23()
+    n = m.n
+    rng = np.random.default_rng(9)
+    # (a) masks + R3 + priority-0 JointTracking on top of a velocity box: the joints are pinned (lo = hi)
+    tasks = [T.se3_task(m, "lf", "l_sole", 5.0, 5.0, mask=(True, False, True)),
+             T.r3_task(m, "hand", "l_hand_palm", 3.0, priority=1, weight=[2.0, 2.0], mask=(True, True, False)),
+             T.com_task(m, "com", 2.0, priority=1, weight=[4.0, 4.0], mask=(True, True, False)),
+             T.joint_tracking_task(m, "reg", np.full(n, 1.0), priority=1, weight=np.ones(n)),
+             T.joint_velocity_limits_task(m, "jv", np.full(n, 0.4), np.full(n, -0.4))]
+    w = W.Workload("edge", m, tasks, 0.01, "")
+    for N in (1, 33):
+        inp = W.synth_inputs(w, N, 7)
+        model, prob = make(m, tasks, N)
+        prob.set_inputs(inp)
+        prob.tick(1, 0.01)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        o = Oracle(m, tasks)
+        nur, str_, _ = o.tick_batch(inp.base_pos.copy(), inp.base_quat.copy(), inp.s.copy(), inp.setpoints)
+        ok = (st == 0) & (str_ == 0)
+        assert ok.mean() >= 0.9
+        assert np.abs(nu[ok] - nur[ok]).max() <= TOL_NU
+        assert np.abs(nu[ok][:, 6:]).max() <= 0.4 + 1e-9
+        prob.close()
+    # (b) hard joint tracking: x_J = b exactly
+    tasks_b = [T.joint_tracking_task(m, "pin", np.full(n, 2.0), priority=0),
+               T.se3_task(m, "lf", "l_sole", 5.0, 5.0, priority=1, weight=np.ones(6))]
+    wb = W.Workload("pin", m, tasks_b, 0.01, "")
+    inp = W.synth_inputs(wb, 16, 8)
+    model, prob = make(m, tasks_b, 16)
+    prob.set_inputs(inp)
+    prob.tick(1, 0.01)
+    nu = prob.get_output()
+    st, _ = prob.get_status()
+    assert np.all(st == 0)
+    b = inp.setpoints[0][:, n:] + 2.0 * (inp.setpoints[0][:, :n] - inp.s)
+    assert np.abs(nu[:, 6:] - b).max() <= 1e-9
+    o = Oracle(m, tasks_b)
+    nur, str_, _ = o.tick_batch(inp.base_pos.copy(), inp.base_quat.copy(), inp.s.copy(), inp.setpoints)
+    assert np.abs(nu - nur)[str_ == 0].max() <= TOL_NU
+    prob.close()
+    # (c) contradictory limits -> every instance reports FAILED, nothing hangs
+    tasks_c = [T.joint_velocity_limits_task(m, "jv", np.full(n, -1.0), np.full(n, 1.0)),
+               T.joint_tracking_task(m, "reg", np.ones(n), priority=1, weight=np.ones(n))]
+    wc = W.Workload("bad", m, tasks_c, 0.01, "")
+    inp = W.synth_inputs(wc, 8, 9)
+    model, prob = make(m, tasks_c, 8)
+    prob.set_inputs(inp)
+    prob.tick(1, 0.01)
+    st, _ = prob.get_status()
+    assert np.all(st == 2) and prob.count_unsolved() == 8
+    prob.close()
+
+
+def test_full_size_properties_and_shard_invariance():
+    """BASELINE.json's headline size (65,536 ergoCub instances, C3) through size-independent properties:
+    every solved instance satisfies the hard constraints (J_foot nu = b_foot, J_com nu = b_com, joint box) and the
+    results of a shard do not depend on the batch it was computed in (bitwise)."""
+    w = W.config(3)
+    N = 65536
+    inp = W.synth_inputs(w, N, 3)
+    model, prob = make(w.model, w.tasks, N)
+    prob.set_inputs(inp)
+    prob.tick(1, w.dt)
+    nu = prob.get_output()
+    st, it = prob.get_status()
+    solved = st == 0
+    assert solved.mean() > 0.999, np.bincount(st)
+    n = w.model.n
+    hi = np.minimum(0.5 * (w.model.q_upper - inp.s) / w.dt, 2.0)
+    lo = np.maximum(0.5 * (w.model.q_lower - inp.s) / w.dt, -2.0)
+    assert np.all(nu[solved][:, 6:] <= hi[solved] + 1e-8) and np.all(nu[solved][:, 6:] >= lo[solved] - 1e-8)
+    frames = [w.tasks[1].frame, w.tasks[2].frame]
+    k = prob.kinematics(frames)
+    for fi, ti in enumerate((1, 2)):
+        sp = inp.setpoints[ti]
+        t = w.tasks[ti]
+        v = np.einsum("nrc,nc->nr", k["frame_jac"][:, fi], nu)
+        b_lin = sp[:, 7:10] + t.kp_linear * (sp[:, :3] - k["frame_pos"][:, fi])
+        assert np.abs(v[:, :3] - b_lin)[solved].max() <= 1e-9
+    vc = np.einsum("nrc,nc->nr", k["com_jac"], nu)
+    bc = inp.setpoints[0][:, 3:] + w.tasks[0].kp_linear * (inp.setpoints[0][:, :3] - k["com"])
+    assert np.abs(vc - bc)[solved].max() <= 1e-9
+    prob.close()
+    a, b = W.shard_range(N, 3, 8)
+    part = inp.slice(a, b)
+    model2, p2 = make(w.model, w.tasks, b - a)
+    p2.set_inputs(part)
+    p2.tick(1, w.dt)
+    assert np.array_equal(p2.get_output(), nu[a:b])
+    p2.close()

@@ -1,0 +1,228 @@
+"""Oracle pins for K2 (tasks, assembly) and K3 (QP): the identities the reference's own unit tests check
+(src/IK/tests/*TaskTest.cpp) re-expressed against independent numpy computations, KKT residuals, a scipy
+cross-check and the reference's closed-loop convergence scenarios."""
+import numpy as np
+import pytest
+
+import blf_b200  # noqa: F401
+from blf_b200 import models as M, tasks as T, workloads as W
+from oracle.oracle import Oracle
+from helpers import random_state, rot_log, solve_qp_active_set
+import scenarios as S
+
+
+@pytest.fixture(scope="module")
+def ergo():
+    return M.ergocub23()
+
+
+def _so3_ctrl(Rcur, qd, wff, kp):
+    Rd = W.quat_to_rot(np.asarray(qd)[None])[0]
+    return wff + kp * rot_log(Rd @ Rcur.T)        # left-trivialised error Log(R_d R^T)
+
+
+def test_se3_task_A_is_jacobian_b_is_control_law(ergo):
+    """SE3TaskTest.cpp:79-139: A == frame Jacobian, b == [R3 control; SO3 control]."""
+    m = ergo
+    rng = np.random.default_rng(0)
+    t = T.se3_task(m, "t", "l_sole", [1.0, 2.0, 3.0], [4.0, 5.0, 6.0], priority=0)
+    o = Oracle(m, [t])
+    p, q, s = random_state(m, rng)
+    R, P = o.fk(p, q, s)
+    sp = np.concatenate([rng.normal(size=3), W.so3_exp(rng.normal(size=(1, 3)))[0], rng.normal(size=6)])
+    A, b = o.task_update(0, R, P, s, sp)
+    J = o.frame_jacobian(R, P, t.frame)
+    Rf, pf = o.frame_pose(R, P, t.frame)
+    assert np.array_equal(A, J)
+    assert np.allclose(b[:3], sp[7:10] + t.kp_linear * (sp[:3] - pf), atol=1e-13)
+    assert np.allclose(b[3:], _so3_ctrl(Rf, sp[3:7], sp[10:13], t.kp_angular), atol=1e-12)
+
+
+def test_se3_task_mask_and_disabled_controller(ergo):
+    """SE3TaskTest.cpp:142-231 (mask: selected linear rows, then the 3 angular rows) and SE3Task.cpp:251-258."""
+    m = ergo
+    rng = np.random.default_rng(1)
+    t = T.se3_task(m, "t", "r_sole", 2.0, 3.0, mask=(True, False, True))
+    o = Oracle(m, [t])
+    p, q, s = random_state(m, rng)
+    R, P = o.fk(p, q, s)
+    sp = np.concatenate([rng.normal(size=3), W.so3_exp(rng.normal(size=(1, 3)))[0], rng.normal(size=6)])
+    A, b = o.task_update(0, R, P, s, sp)
+    J = o.frame_jacobian(R, P, t.frame)
+    assert A.shape == (5, m.nv)
+    assert np.array_equal(A, J[[0, 2, 3, 4, 5]])
+    t.controller_enabled = False
+    o.set_tasks([t])
+    _, b2 = o.task_update(0, R, P, s, sp)
+    assert np.allclose(b2, np.concatenate([sp[[7, 9]], sp[10:13]]))   # feed-forward only
+
+
+def test_com_so3_r3_tasks(ergo):
+    """CoMTaskTest.cpp:82-130, SO3TaskTest.cpp:83-131 (A = J.bottomRows<3>()), R3TaskTest."""
+    m = ergo
+    rng = np.random.default_rng(2)
+    tasks = [T.com_task(m, "c", [1.0, 2.0, 3.0]), T.so3_task(m, "o", "chest", 5.0, priority=1, weight=[1, 1, 1]),
+             T.r3_task(m, "r", "l_hand_palm", 4.0, mask=(False, True, True))]
+    o = Oracle(m, tasks)
+    p, q, s = random_state(m, rng)
+    R, P = o.fk(p, q, s)
+    c, Jc = o.com(R, P)
+    spc = rng.normal(size=6)
+    A, b = o.task_update(0, R, P, s, spc)
+    assert np.array_equal(A, Jc) and np.allclose(b, spc[3:] + tasks[0].kp_linear * (spc[:3] - c))
+    spo = np.concatenate([W.so3_exp(rng.normal(size=(1, 3)))[0], rng.normal(size=3)])
+    A, b = o.task_update(1, R, P, s, spo)
+    Rf, pf = o.frame_pose(R, P, tasks[1].frame)
+    assert np.array_equal(A, o.frame_jacobian(R, P, tasks[1].frame)[3:])
+    assert np.allclose(b, _so3_ctrl(Rf, spo[:4], spo[4:], tasks[1].kp_angular), atol=1e-12)
+    spr = rng.normal(size=6)
+    A, b = o.task_update(2, R, P, s, spr)
+    Rf, pf = o.frame_pose(R, P, tasks[2].frame)
+    assert np.array_equal(A, o.frame_jacobian(R, P, tasks[2].frame)[[1, 2]])
+    assert np.allclose(b, (spr[3:] + 4.0 * (spr[:3] - pf))[[1, 2]])
+
+
+def test_joint_tasks(ergo):
+    """JointTrackingTaskTest.cpp:84-114 (A = [0 I], b = -Kp s for a zero set-point), JointLimitsTaskTest.cpp:98-138
+    (A = [I; -I] on the joint columns, b = klim (limit - s)/dt on both halves), JointVelocityLimitsTaskTest.cpp:88-130."""
+    m = ergo
+    n = m.n
+    rng = np.random.default_rng(3)
+    kp, klim = rng.uniform(1, 5, n), rng.uniform(0, 1, n)
+    up, lo = m.q_upper, m.q_lower
+    tasks = [T.joint_tracking_task(m, "jt", kp, priority=1, weight=np.ones(n)),
+             T.joint_limits_task(m, "jl", klim, 0.01), T.joint_velocity_limits_task(m, "jv", np.full(n, 2.0), np.full(n, -3.0))]
+    o = Oracle(m, tasks)
+    p, q, s = random_state(m, rng)
+    R, P = o.fk(p, q, s)
+    A, b = o.task_update(0, R, P, s, np.zeros(2 * n))
+    assert np.array_equal(A, np.hstack([np.zeros((n, 6)), np.eye(n)])) and np.allclose(b, -kp * s)
+    A, b = o.task_update(1, R, P, s, None)
+    assert np.array_equal(A, np.vstack([np.hstack([np.zeros((n, 6)), np.eye(n)]), np.hstack([np.zeros((n, 6)), -np.eye(n)])]))
+    assert np.allclose(b[:n], klim * (up - s) / 0.01) and np.allclose(b[n:], klim * (s - lo) / 0.01)
+    A, b = o.task_update(2, R, P, s, None)
+    assert np.allclose(b[:n], 2.0) and np.allclose(b[n:], 3.0)
+
+
+@pytest.mark.parametrize("cid", [1, 3, 4])
+def test_assembly_follows_advance(cid):
+    """QPInverseKinematics.cpp:442-491: H = sum A'WA, g = -sum A'Wb, C/l/u stacked in task order, -1e30 lower bounds."""
+    w = W.config(cid)
+    inp = W.synth_inputs(w, 4, cid)
+    o = Oracle(w.model, w.tasks)
+    n, nv = w.model.n, w.model.nv
+    for i in range(4):
+        sps = [None if sp is None else sp[i] for sp in inp.setpoints]
+        H, g, C, l, u = o.assemble(inp.base_pos[i], inp.base_quat[i], inp.s[i], sps)
+        R, P = o.fk(inp.base_pos[i], inp.base_quat[i], inp.s[i])
+        H2, g2, rows = np.zeros((nv, nv)), np.zeros(nv), []
+        for ti, t in enumerate(w.tasks):
+            A, b = o.task_update(ti, R, P, inp.s[i], sps[ti])
+            if t.priority == 1:
+                H2 += A.T @ np.diag(t.weight) @ A
+                g2 -= A.T @ (t.weight * b)
+            else:
+                rows.append((A, b, t.is_inequality))
+        assert np.allclose(H, H2, atol=1e-12) and np.allclose(g, g2, atol=1e-12)
+        assert np.array_equal(C, np.vstack([r[0] for r in rows]))
+        assert np.array_equal(u, np.concatenate([r[1] for r in rows]))
+        assert np.array_equal(l, np.concatenate([np.full(len(r[1]), -1e30) if r[2] else r[1] for r in rows]))
+        assert C.shape[0] == {1: 15, 3: 107, 4: 15}[cid]
+
+
+@pytest.mark.parametrize("cid", [1, 3, 4])
+def test_qp_kkt_and_scipy_crosscheck(cid):
+    """The oracle's optimum satisfies the KKT conditions to <= 1e-9 and agrees with scipy's SLSQP."""
+    w = W.config(cid)
+    inp = W.synth_inputs(w, 6, cid)
+    o = Oracle(w.model, w.tasks)
+    for i in range(6):
+        sps = [None if sp is None else sp[i] for sp in inp.setpoints]
+        H, g, C, l, u = o.assemble(inp.base_pos[i], inp.base_quat[i], inp.s[i], sps)
+        x, y, z, info = o.qp_solve(H, g, C, l, u)
+        assert info.status == 0
+        assert o.qp_kkt(H, g, C, l, u, x, y) <= 1e-9
+        if i < 3:
+            xs = solve_qp_active_set(H, g, C, l, u)
+            assert np.abs(xs - x).max() < 2e-6
+
+
+def test_qp_warm_start_and_default_settings():
+    """OSQP defaults (what the reference actually runs, QPInverseKinematics.cpp:339) land within 1e-2 of the optimum;
+    warm-starting from the solution converges at the first termination check."""
+    w = W.config(3)
+    inp = W.synth_inputs(w, 4, 3)
+    o = Oracle(w.model, w.tasks)
+    for i in range(4):
+        sps = [None if sp is None else sp[i] for sp in inp.setpoints]
+        H, g, C, l, u = o.assemble(inp.base_pos[i], inp.base_quat[i], inp.s[i], sps)
+        x, y, z, info = o.qp_solve(H, g, C, l, u)
+        xd, yd, zd, infod = o.qp_solve(H, g, C, l, u, o.settings(parity=False))
+        assert infod.status == 0 and np.abs(xd - x).max() < 2e-2
+        x2, _, _, info2 = o.qp_solve(H, g, C, l, u, o.settings(), x0=x, y0=y, z0=z)
+        assert info2.iters <= 25 and np.abs(x2 - x).max() < 1e-8
+
+
+@pytest.mark.parametrize("n", [20, 35])
+@pytest.mark.parametrize("strict", [False, True])
+def test_closed_loop_convergence_scenarios(n, strict):
+    """'QP-IK' (QPInverseKinematicsTest.cpp:357-500, tolerance 2e-1) and 'With strict limits' (:502-640:
+    |sdot_0|, |sdot_3| < 1e-2 on every tick, positions within 1e-2 of the initial ones)."""
+    sc = S.qp_ik_scenario(n, strict_limits=strict)
+    o = Oracle(sc.model, sc.tasks)
+    p, q, s = sc.p0[None].copy(), sc.q0[None].copy(), sc.s0[None].copy()
+    warm = o.new_warm(1)
+    for _ in range(S.TICKS):
+        nu, status, _ = o.tick_batch(p, q, s, S.tile_setpoints(sc, 1), warm=warm, dt_integrate=S.DT)
+        assert status[0] == 0
+        for j in sc.strict:
+            assert abs(nu[0, 6 + j]) < 1e-2
+    for j in sc.strict:
+        assert abs(s[0, j] - sc.s0[j]) < 1e-2
+    R, P = o.fk(p[0], q[0], s[0])
+    com, _ = o.com(R, P)
+    Rf, pf = o.frame_pose(R, P, sc.ee)
+    if not strict:   # the strict case of the reference only checks the limits
+        assert np.linalg.norm(com - sc.com_des) <= 2e-1 * min(np.linalg.norm(com), np.linalg.norm(sc.com_des))
+        assert np.abs(sc.R_des.T @ (pf - sc.p_ee_des)).max() < 2e-1 and np.abs(rot_log(sc.R_des.T @ Rf)).max() < 2e-1
+
+
+def test_unconstrained_scenario():
+    """'...Unconstrained' (QPInverseKinematicsTest.cpp:932-1063): every task at priority 1."""
+    sc = S.qp_ik_scenario(20, unconstrained=True)
+    o = Oracle(sc.model, sc.tasks)
+    assert o.m == 0
+    p, q, s = sc.p0[None].copy(), sc.q0[None].copy(), sc.s0[None].copy()
+    for _ in range(S.TICKS):
+        nu, status, _ = o.tick_batch(p, q, s, S.tile_setpoints(sc, 1), dt_integrate=S.DT)
+        assert status[0] == 0
+    R, P = o.fk(p[0], q[0], s[0])
+    com, _ = o.com(R, P)
+    assert np.linalg.norm(com - sc.com_des) < 2e-1
+
+
+def test_icub_python_test_vector():
+    """The one concrete humanoid input of the reference (bindings/python/IK/tests/test_QP_inverse_kinematics.py:293-425):
+    identity base, its 32 joint values, CoM/SE3(r_sole)/JointTracking tasks with its gains; its assertions are
+    advance() == True and 'second solution differs from the first'."""
+    m = M.icub32()
+    s = np.array([0.4147046680648114, 0.020109925966605414, -0.008920202688283316, -0.9417931898020863, -0.5243497613177115,
+                  -0.021969353979888327, 0.41490863370740766, 0.019729971064546152, -0.00875663754461344, -0.942238731363784,
+                  -0.5245880299799013, -0.021615580177534933, 0.10368807143683698, -1.7513061346176159e-06, -3.762644846952276e-05,
+                  -0.1599473872698949, 0.4341604471687158, 0.18350557928473807, 0.5390720970077302, 6.0766272665334824e-05,
+                  -0.0010549820549572227, -6.457409077219657e-05, 0.0002255313408076292, 2.3204341497780863e-05, 5.920527253092593e-07,
+                  -0.1591984430641039, 0.4340643739146118, 0.18311274358002663, 0.5398797698508592, 5.367856260643534e-05,
+                  -0.0010455524092736824, 6.414366731688693e-05])
+    tasks = [T.com_task(m, "Com_task", 10.0), T.se3_task(m, "se3_task", "r_sole", 10.0, 10.0),
+             T.joint_tracking_task(m, "joint_tracking_task", [5.0] * 32, priority=1, weight=[1.0] * 32)]
+    o = Oracle(m, tasks)
+    p, q = np.zeros((1, 3)), np.array([[0.0, 0, 0, 1]])
+    rng = np.random.default_rng(0)
+    outs = []
+    for com_z, y in ((0.53, 0.1), (0.5, 0.2)):
+        sps = [np.array([[0, 0, com_z, 0, 0, 0]]), np.array([[-0.02, y, 0.0, 0, 0, 0, 1] + [0.0] * 6]),
+               np.concatenate([s + rng.uniform(-5e-3, 5e-3, 32), np.zeros(32)])[None]]
+        nu, status, _ = o.tick_batch(p.copy(), q.copy(), s[None].copy(), sps)
+        assert status[0] == 0
+        outs.append(nu[0])
+    assert np.abs(outs[0] - outs[1]).max() > 1e-3
