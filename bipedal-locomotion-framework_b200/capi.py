@@ -34,7 +34,7 @@ EXPORTS = [
     "blfik_set_controller_mode", "blfik_tick", "blfik_get_output", "blfik_get_status",
     "blfik_count_unsolved", "blfik_kinematics", "blfik_integrate", "blfik_debug_enable", "blfik_debug_get",
     "blfik_num_dofs", "blfik_num_equality_rows", "blfik_num_instances", "blfik_sync", "blfik_get_stream",
-    "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak",
+    "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak", "blfik_kinematics_noalloc",
 ]
 
 
@@ -100,6 +100,7 @@ def load():
         _lib.blfik_debug_get.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
         _lib.blfik_debug_enable.argtypes = [C.c_void_p, C.c_int32]
         _lib.blfik_kinematics.argtypes = [C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 5 + [C.c_int32]
+        _lib.blfik_kinematics_noalloc.argtypes = _lib.blfik_kinematics.argtypes
         _lib.blfik_set_weight.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
         _lib.blfik_set_gains.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.blfik_set_controller_mode.argtypes = [C.c_void_p, C.c_int32, C.c_int32]

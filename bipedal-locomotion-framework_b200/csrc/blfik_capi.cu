@@ -741,6 +741,87 @@ extern "C" int blfik_kinematics(blfik_problem* p, const int32_t* frames, int32_t
     return BLFIK_OK;
 }
 
+// ------------------------------------------------------------------- allocation-free kinematics
+// Staging memory for blfik_kinematics_noalloc.  It is part of the library image: every GPU that loads
+// the library carries these 4 MiB until the process exits.  In HOST code the name below is only a
+// stand-in for the symbol, not a device address; the address a kernel can use comes from
+// cudaGetSymbolAddress, looked up once per device in noalloc_scratch().
+static __device__ __align__(256) unsigned char g_noalloc_scratch[BLFIK_NOALLOC_SCRATCH_BYTES];
+
+static constexpr int kMaxDevices = 64;
+static unsigned char* g_noalloc_ptr[kMaxDevices];  // device address per device ordinal, 0 = not looked up yet
+
+// Device address of the staging array on `device`, which must be the current device.
+static int noalloc_scratch(int device, unsigned char** out)
+{
+    if (device < 0 || device >= kMaxDevices)
+        return fail(BLFIK_ERR_UNSUPPORTED, "[blfik_kinematics_noalloc] device ordinal %d is beyond the %d this entry point tracks", device, kMaxDevices);
+    if (!g_noalloc_ptr[device]) {
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+            return fail(BLFIK_ERR_CUDA, "[blfik_kinematics_noalloc] cannot resolve the staging array on device %d: %s", device, cudaGetErrorString(e));
+        g_noalloc_ptr[device] = static_cast<unsigned char*>(ptr);
+    }
+    *out = g_noalloc_ptr[device];
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_kinematics_noalloc(blfik_problem* p, const int32_t* frames, int32_t nframes, double* frame_pos, double* frame_rot,
+                                        double* frame_jac, double* com, double* com_jac, int32_t mem)
+{
+    CHECK_P(p, "blfik_kinematics_noalloc");  // makes p->device current, which the symbol look-up needs
+    if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_kinematics_noalloc] the robot state has never been set");
+    if (nframes < 0 || (nframes > 0 && !frames)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_kinematics_noalloc] bad frame list");
+    for (int f = 0; f < nframes; f++)
+        if (frames[f] < 0 || frames[f] >= p->model->nf) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_kinematics_noalloc] frame index %d out of range", frames[f]);
+    const size_t N = (size_t)p->N, nv = p->nv, nf = (size_t)nframes;
+    struct Buf { double* user; double* dev; size_t bytes; } bufs[5] = {
+        {frame_pos, nullptr, N * nf * 3 * sizeof(double)}, {frame_rot, nullptr, N * nf * 9 * sizeof(double)},
+        {frame_jac, nullptr, N * nf * 6 * nv * sizeof(double)}, {com, nullptr, N * 3 * sizeof(double)}, {com_jac, nullptr, N * 3 * nv * sizeof(double)}};
+    auto round256 = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    // what has to live in the staging array: the frame list always, results only when they go to the host
+    size_t need = round256(nf * sizeof(int));
+    for (Buf& b : bufs) {
+        if (!b.user || !b.bytes) { b.user = nullptr; continue; }
+        if (mem != BLFIK_MEM_DEVICE) need += round256(b.bytes);
+    }
+    if (need > (size_t)BLFIK_NOALLOC_SCRATCH_BYTES)
+        return fail(BLFIK_ERR_UNSUPPORTED,
+                    "[blfik_kinematics_noalloc] this request needs %zu bytes of staging, the built-in array holds %zu "
+                    "(BLFIK_NOALLOC_SCRATCH_BYTES); ask for fewer outputs or robots, or use blfik_kinematics",
+                    need, (size_t)BLFIK_NOALLOC_SCRATCH_BYTES);
+    unsigned char* base = nullptr;
+    int rc = noalloc_scratch(p->device, &base);
+    if (rc) return rc;
+    size_t off = 0;
+    int* d_frames = reinterpret_cast<int*>(base);
+    off += round256(nf * sizeof(int));
+    if (nframes) CU(cudaMemcpyAsync(d_frames, frames, nf * sizeof(int), cudaMemcpyHostToDevice, p->stream));
+    for (Buf& b : bufs) {
+        if (!b.user) continue;
+        if (mem == BLFIK_MEM_DEVICE) b.dev = b.user;
+        else {
+            b.dev = reinterpret_cast<double*>(base + off);
+            off += round256(b.bytes);
+        }
+    }
+    KinParams K;
+    K.m = p->dm, K.N = p->N, K.base_pos = p->base_pos, K.base_quat = p->base_quat, K.s = p->s, K.frames = d_frames, K.nframes = nframes;
+    K.frame_pos = bufs[0].user ? bufs[0].dev : nullptr, K.frame_rot = bufs[1].user ? bufs[1].dev : nullptr;
+    K.frame_jac = bufs[2].user ? bufs[2].dev : nullptr, K.com = bufs[3].user ? bufs[3].dev : nullptr, K.com_jac = bufs[4].user ? bufs[4].dev : nullptr;
+    K.L = p->L;
+    blfik_kinematics_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(K);
+    CU(cudaGetLastError());
+    p->launches++;
+    if (mem != BLFIK_MEM_DEVICE)
+        for (Buf& b : bufs)
+            if (b.user) CU(cudaMemcpyAsync(b.user, b.dev, b.bytes, cudaMemcpyDeviceToHost, p->stream));
+    // the staging array is free for the next caller only once everything has left it
+    CU(cudaStreamSynchronize(p->stream));
+    return BLFIK_OK;
+}
+
 extern "C" int blfik_integrate(blfik_problem* p, const double* nu, int32_t mem, double dt, int32_t nsteps)
 {
     CHECK_P(p, "blfik_integrate");

@@ -189,6 +189,27 @@ int blfik_count_unsolved(blfik_problem* problem, int64_t* count);
 int blfik_kinematics(blfik_problem* problem, const int32_t* frames, int32_t nframes,
                      double* frame_pos, double* frame_rot, double* frame_jac, double* com,
                      double* com_jac, int32_t mem);
+/* No counterpart in the reference.  Same outputs as blfik_kinematics, for callers that must not
+ * allocate device memory while they run: a hard-real-time control thread (cudaMalloc/cudaFree take
+ * driver locks and synchronise the whole device, so one call can blow a 1 ms period), or a process
+ * whose device memory is entirely owned by another allocator.  blfik_kinematics stages host-bound
+ * results and the frame list in buffers it allocates and frees per call; this variant stages them in
+ * a fixed BLFIK_NOALLOC_SCRATCH_BYTES array that lives inside the library image on every GPU that
+ * loads it, and calls no cudaMalloc / cudaFree / allocating routine.
+ *  - Limit: the frame list plus every requested output, each rounded up to 256 B, must fit in
+ *    BLFIK_NOALLOC_SCRATCH_BYTES (ergoCub, two frames with Jacobians + CoM + CoM Jacobian: about
+ *    1,100 robots).  Larger requests fail with BLFIK_ERR_UNSUPPORTED and a message that states the
+ *    bytes needed and the maximum; nothing is launched.
+ *  - The first call on each device looks up the device address of the array (with that device
+ *    current).  Make that first call during set-up, before any CUDA stream capture begins.
+ *  - All calls on one device share the one array, and it keeps whatever the previous call left in
+ *    it.  Every byte a call reads back it has written itself in that call, so nothing needs
+ *    clearing; but two calls that overlap on the GPU (two problems, two streams, two threads) race
+ *    on it.  Serialise them.  The call returns after its results have reached the caller's buffers. */
+#define BLFIK_NOALLOC_SCRATCH_BYTES (4u << 20)
+int blfik_kinematics_noalloc(blfik_problem* problem, const int32_t* frames, int32_t nframes,
+                             double* frame_pos, double* frame_rot, double* frame_jac, double* com,
+                             double* com_jac, int32_t mem);
 /* replaces dynamics->setControlInput({twist, sdot}) + integrator->integrate(0, dt)
  * (FloatingBaseSystemVelocityKinematics.cpp:80-84, FixedStepIntegrator.h:94-140);
  * nu == NULL integrates the last tick's output.  nsteps full Euler steps of dt.          */
