@@ -38,19 +38,25 @@ CONFIG_ID = 3
 
 
 # ------------------------------------------------------------------ helpers
-def algorithmic_flops_per_tick(n: int, me: int, admm_iters_total: np.ndarray, admm_iters_per_round: int,
-                               polish_iters: int) -> float:
-    """FP64 flops of the algorithm as designed (triangular structure exploited, 1 FMA = 2 flops),
-    summed over the batch.  DESIGN.md "Roofline" derives every term."""
+def algorithmic_flops_per_tick(n: int, me: int, K: int, iters_total: np.ndarray, fast_path: bool, admm_iters_per_round: int = 10,
+                               polish_iters: int = 4) -> float:
+    """FP64 flops of the algorithm as designed (symmetry / triangular structure exploited, 1 FMA = 2 flops),
+    summed over the batch.  DESIGN.md section 4 derives every term.  `iters_total` is the per-instance count of
+    N mat-vecs the kernel reports (ADMM + polish iterations)."""
     nv = n + 6
     kin = 4000.0 + 60.0 * n                       # FK, frame Jacobians, CoM subtree pass, controllers
-    asm = 2.0 * 3 * nv * nv + 6.0 * n             # SO3 cost rows (3 x nv x nv MAC) + diagonal tasks
-    setup = nv ** 3 + 3.0 * me * nv * nv + 2.0 * me * me * nv + me ** 3 / 3.0
     it = 2.0 * nv * nv + 12.0 * nv                # N r + x_b and the lane-local updates
-    cert = 2.0 * nv * nv + 4.0 * me * nv + me * me
-    rounds = np.maximum(1, np.ceil(admm_iters_total / max(1, admm_iters_per_round)))
-    per = kin + asm + rounds * (2.0 * setup + polish_iters * it + cert) + admm_iters_total * it
-    return float(per.sum())
+    if fast_path:
+        # G = E + B D^-1 B' (K^2 nv), Cholesky (K^3/3), U (K^2 nv), N = D^-1 - U U' (nv^2 K), x_b
+        setup = 2.0 * K * K * nv + K ** 3 / 3.0 + nv * nv * K + 2.0 * K * nv + K * K
+        per = kin + 6.0 * n + setup + iters_total * it
+    else:
+        asm = 2.0 * (K - me) * nv * nv + 6.0 * n  # dense cost rows into H
+        setup = nv ** 3 + 3.0 * me * nv * nv + 2.0 * me * me * nv + me ** 3 / 3.0
+        cert = 2.0 * nv * nv + 4.0 * me * nv + me * me
+        rounds = np.maximum(1, np.ceil(iters_total / max(1, admm_iters_per_round)))
+        per = kin + asm + rounds * (2.0 * setup + polish_iters * it + cert) + iters_total * it
+    return float(np.sum(per))
 
 
 def algorithmic_bytes_per_tick(n: int, sp_doubles: int) -> float:
@@ -248,7 +254,9 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         except Exception:
             pass
         hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-        flops_launch = algorithmic_flops_per_tick(n, prob.me, iters.astype(np.float64), prob_settings["admm_iters"],
+        K = sum(t.rows(n) for t in w.tasks if t.type in (0, 1, 2, 6))
+        fast = prob.kernel_path == 2
+        flops_launch = algorithmic_flops_per_tick(n, prob.me, K, iters.astype(np.float64), fast, prob_settings["admm_iters"],
                                                   prob_settings["polish_iters"])
         kernel_ms = ms_dev / args.steps
         achieved_tf = flops_launch / (kernel_ms * 1e-3) * 1e-12
@@ -274,7 +282,8 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
                          "frac": achieved_tf / fp64_peak if fp64_peak else None, "traffic": None,
                          "peak_source": "measured live by blfik_measure_fp64_peak (dependency-free DFMA loop); "
                                         "MEASURED_PEAKS.json has no FP64 figure",
-                         "kernel": "blfik_tick_kernel", "flops_per_launch": flops_launch,
+                         "kernel": "blfik_tick_fast_kernel<29,20>" if fast else "blfik_tick_kernel", "flops_per_launch": flops_launch,
+                         "mean_matvecs_per_tick": float(iters.mean()),
                          "hbm": {"achieved": bytes_launch / (kernel_ms * 1e-3) * 1e-9, "peak": hbm_peak, "unit": "GB/s",
                                  "frac": bytes_launch / (kernel_ms * 1e-3) * 1e-9 / hbm_peak, "peak_source": hbm_src,
                                  "bytes_per_launch": bytes_launch}},
@@ -289,7 +298,7 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         dist.destroy_process_group()
 
 
-prob_settings = {"rho": 1.0, "sigma": 1e-3, "alpha": 1.6, "eps": 1e-7, "admm_iters": 10, "max_rounds": 20,
+prob_settings = {"rho": 1.0, "sigma": 1e-2, "alpha": 1.6, "eps": 1e-7, "admm_iters": 10, "max_rounds": 8,
                  "polish_iters": 4, "eq_iters": 5}
 
 

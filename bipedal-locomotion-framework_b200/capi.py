@@ -35,6 +35,7 @@ EXPORTS = [
     "blfik_count_unsolved", "blfik_kinematics", "blfik_integrate", "blfik_debug_enable", "blfik_debug_get",
     "blfik_num_dofs", "blfik_num_equality_rows", "blfik_num_instances", "blfik_sync", "blfik_get_stream",
     "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak", "blfik_kinematics_noalloc",
+    "blfik_set_kernel_path", "blfik_get_kernel_path",
 ]
 
 
@@ -107,6 +108,8 @@ def load():
         _lib.blfik_count_unsolved.argtypes = [C.c_void_p, C.c_void_p]
         _lib.blfik_set_solver_settings.argtypes = [C.c_void_p, C.c_void_p]
         _lib.blfik_setpoint_len.argtypes = [C.c_void_p, C.c_int32]
+        _lib.blfik_set_kernel_path.argtypes = [C.c_void_p, C.c_int32]
+        _lib.blfik_get_kernel_path.argtypes = [C.c_void_p]
     return _lib
 
 
@@ -319,6 +322,15 @@ class Problem:
 
     def set_stream(self, cuda_stream: int):
         _check(self.L.blfik_set_stream(self.handle, C.c_void_p(cuda_stream)))
+
+    def set_kernel_path(self, path: int):
+        """0 = automatic, 1 = force the generic shared-memory kernel."""
+        _check(self.L.blfik_set_kernel_path(self.handle, int(path)))
+
+    @property
+    def kernel_path(self) -> int:
+        """2 = register-resident kernel, 1 = generic kernel."""
+        return int(self.L.blfik_get_kernel_path(self.handle))
 
     @property
     def launch_count(self) -> int:

@@ -2,6 +2,7 @@
 // No torch types, no CPU fallback: every compute entry point needs a CUDA device.
 #include "../../include/blfik.h"
 #include "blfik_device.cuh"
+#include "blfik_fast.cuh"
 
 #include <cstdarg>
 #include <cstdio>
@@ -176,7 +177,7 @@ struct blfik_model {
 struct HostTask {
     blfik_task_desc d;
     std::vector<double> kp_joint, weight, klim, upper, lower;
-    int rows = 0, sp_len = 0, row_offset = 0;
+    int rows = 0, sp_len = 0, row_offset = 0, brow = 0;
     bool setpoint_set = false;
     double* d_setpoint = nullptr;
     double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
@@ -206,7 +207,47 @@ struct blfik_problem {
     size_t smem_bytes = 0;
     int num_sms = 148;
     long long launches = 0;
+    // register-resident kernel (blfik_fast.cuh), used when nv <= 32 and K <= 32
+    int K = 0;                       // dense task rows (cost + equality)
+    int path = 0;                    // 0 auto, 1 force the generic shared-memory kernel
+    void (*fast_kernel)(const FastParams) = nullptr;
+    FastLayout F;
+    size_t fast_smem = 0;
+    int fast_grid = 0, fast_wpb = 4;
+    int max_as_iters = 6, max_polish_iters = 40, max_total_iters = 400;
 };
+
+template <int NV, int KP>
+static FastLayout make_fast_layout(int nl)
+{
+    constexpr int LDB = FastDims<NV, KP>::LDB, LDG = FastDims<NV, KP>::LDG;
+    FastLayout F;
+    int o = 0;
+    auto take = [&](int cnt) { int r = o; o += (cnt + 1) & ~1; return r; };
+    F.linkR = take(9 * nl), F.linkP = take(3 * nl), F.axisW = take(3 * nl), F.mcw = take(3 * nl);
+    F.LGt = take(KP * LDG + KP);    // + KP: the rotating elimination reads up to KP slots past a column
+    F.Bm = take(KP * LDB);
+    // link arrays, LGt and Bm are dead once U is known: the N rows (NV x LDB) live on top of them
+    if (o < NV * LDB) o = (NV * LDB + 1) & ~1;
+    // G (by columns), then U rows; dead after N is formed: the active-set matrix (|A| x (|A||1)) lives there
+    const int n = nl - 1;
+    int r2 = (NV > KP ? NV : KP) * LDG;
+    if (r2 < n * (n | 1)) r2 = n * (n | 1);
+    F.Us = take(r2);
+    F.cvec = take(KP), F.evec = take(KP), F.dinv = take(LDB), F.rvec = take(LDB), F.wv = take(LDG);
+    F.dA = take(32), F.muA = take(32), F.idxA = take(16);
+    F.Ns = F.linkR, F.MA = F.Us;
+    F.ma_cap = n < 32 ? n : 32;
+    F.total = o;
+    return F;
+}
+
+template <int NV, int KP>
+static void pick_fast(blfik_problem* p)
+{
+    p->fast_kernel = blfik_tick_fast_kernel<NV, KP>;
+    p->F = make_fast_layout<NV, KP>(p->n + 1);
+}
 
 static int rows_of(const blfik_task_desc& d, int n)
 {
@@ -241,8 +282,8 @@ extern "C" const char* blfik_last_error(void) { return g_err.c_str(); }
 extern "C" void blfik_default_settings(blfik_solver_settings* s)
 {
     if (!s) return;
-    s->rho = 1.0, s->sigma = 1e-3, s->alpha = 1.6, s->eps = 1e-7;
-    s->admm_iters = 10, s->max_rounds = 20, s->polish_iters = 4, s->eq_iters = 5;
+    s->rho = 1.0, s->sigma = 1e-2, s->alpha = 1.6, s->eps = 1e-7;
+    s->admm_iters = 10, s->max_rounds = 8, s->polish_iters = 4, s->eq_iters = 5;
 }
 
 // ------------------------------------------------------------------- model
@@ -341,7 +382,7 @@ static int refresh_tasks(blfik_problem* p)
         HostTask& h = p->tasks[t];
         DevTask& d = dt[t];
         d.type = h.d.type, d.priority = h.d.priority, d.frame = h.d.frame, d.rows = h.rows, d.enabled = h.d.controller_enabled;
-        d.sp_len = h.sp_len, d.row_offset = h.row_offset;
+        d.sp_len = h.sp_len, d.row_offset = h.row_offset, d.brow = h.brow;
         for (int c = 0; c < 3; c++) d.mask[c] = h.d.mask[c] != 0, d.kp_lin[c] = h.d.kp_linear[c], d.kp_ang[c] = h.d.kp_angular[c];
         auto up = [&](const std::vector<double>& v, double* dst) -> int {
             if (!v.empty()) CU(cudaMemcpyAsync(dst, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, p->stream));
@@ -419,6 +460,10 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
             h.row_offset = me;
             me += h.rows;
         }
+        if (is_dense(h.d.type)) {
+            h.brow = p->K;
+            p->K += h.rows;
+        }
         h.d.kp_joint = h.d.weight = h.d.klim = h.d.upper_limits = h.d.lower_limits = nullptr;  // owned copies only
         h.setpoint_set = h.sp_len == 0;
         p->tasks.push_back(std::move(h));
@@ -449,6 +494,37 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
     if (cudaFuncSetAttribute(blfik_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes) != cudaSuccess ||
         cudaFuncSetAttribute(blfik_kinematics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes) != cudaSuccess)
         return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cannot reserve %zu B of shared memory: %s", p->smem_bytes, cudaGetErrorString(cudaGetLastError())));
+
+    // ---- register-resident kernel: pick the smallest instantiation that holds (nv, K)
+    {
+        const int nv = p->nv, K = p->K;
+        if (nv <= 32 && K <= 32) {
+            if (nv == 29) {
+                if (K <= 16) pick_fast<29, 16>(p);
+                else if (K <= 20) pick_fast<29, 20>(p);
+                else pick_fast<29, 32>(p);
+            } else {
+                if (K <= 16) pick_fast<32, 16>(p);
+                else if (K <= 20) pick_fast<32, 20>(p);
+                else pick_fast<32, 32>(p);
+            }
+            const size_t fper = (size_t)p->F.total * sizeof(double);
+            int fw = (int)((sm_total - 3072) / (fper + 64));
+            if (fw > 12) fw = 12;            // register file: 3 blocks x 4 warps at <= 168 registers per thread
+            int fb = fw / p->fast_wpb;
+            if (fb < 1) {
+                p->fast_kernel = nullptr;    // does not fit: generic kernel
+            } else {
+                p->fast_smem = (size_t)p->fast_wpb * fper;
+                const long long fwant = (N + p->fast_wpb - 1) / p->fast_wpb;
+                const long long fcap = (long long)p->num_sms * fb;
+                p->fast_grid = (int)(fwant < fcap ? fwant : fcap);
+                if (cudaFuncSetAttribute((const void*)p->fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->fast_smem) != cudaSuccess)
+                    return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cannot reserve %zu B of shared memory for the register-resident kernel: %s",
+                                     p->fast_smem, cudaGetErrorString(cudaGetLastError())));
+            }
+        }
+    }
 
     if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(fail(BLFIK_ERR_CUDA, "cudaStreamCreate failed"));
     p->own_stream = true;
@@ -653,11 +729,32 @@ extern "C" int blfik_tick(blfik_problem* p, int32_t nticks, double dt, uint32_t 
     P.status = p->status, P.iters = p->iters, P.st = p->st, P.nticks = nticks, P.dt = dt, P.flags = flags;
     P.dbg = p->debug ? p->dbg : DebugOut{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     P.L = p->L;
-    blfik_tick_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(P);
+    if (p->fast_kernel && p->path == 0) {
+        FastParams FP;
+        FP.T = P, FP.F = p->F, FP.nv = p->nv, FP.K = p->K;
+        FP.max_as_iters = p->max_as_iters, FP.max_polish_iters = p->max_polish_iters, FP.max_total_iters = p->max_total_iters;
+        p->fast_kernel<<<p->fast_grid, p->fast_wpb * 32, p->fast_smem, p->stream>>>(FP);
+    } else {
+        blfik_tick_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(P);
+    }
     CU(cudaGetLastError());
     p->launches++;
     p->ticked = true;
     return BLFIK_OK;
+}
+
+extern "C" int blfik_set_kernel_path(blfik_problem* p, int32_t path)
+{
+    CHECK_P(p, "blfik_set_kernel_path");
+    if (path != 0 && path != 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_kernel_path] path must be 0 (auto) or 1 (generic kernel)");
+    p->path = path;
+    return BLFIK_OK;
+}
+
+extern "C" int32_t blfik_get_kernel_path(const blfik_problem* p)
+{
+    if (!p) return -1;
+    return (p->fast_kernel && p->path == 0) ? 2 : 1;
 }
 
 extern "C" int blfik_get_output(blfik_problem* p, double* nu, int32_t mem)

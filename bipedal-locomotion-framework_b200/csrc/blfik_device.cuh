@@ -40,6 +40,7 @@ struct DevModel {
 
 struct DevTask {
     int type, priority, frame, rows, enabled, sp_len, row_offset;
+    int brow;  // first row in the dense task-row matrix of the register-resident kernel
     int mask[3];
     double kp_lin[3], kp_ang[3];
     const double* kp_joint;

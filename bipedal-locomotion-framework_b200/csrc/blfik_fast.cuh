@@ -1,0 +1,688 @@
+// blfik_fast.cuh -- register-resident tick kernel for problems with nv <= 32 velocity variables and
+// K <= 32 dense task rows (every humanoid configuration of BASELINE.json on ergoCub / iCub-26).
+//
+// Same algorithm family as blfik_device.cuh (K1 -> K2 -> K3 -> K4, one warp per robot, equality-projected ADMM
+// + certified polish), re-derived so that the factorisation is small and every hot operand is a register:
+//
+//  * The Hessian of every problem on this path is "diagonal + a few dense rows": JointTrackingTask gives the
+//    diagonal, SE3/SO3/CoM/R3 tasks give rows B_r (cost rows with weight w_r, or equality rows).  The x-update
+//        x~ = argmin 1/2 x'Dx + sum_cost w_r/2 (B_r x - b_r)^2 - rhs'x   s.t.  B_eq x = b_eq,
+//        D = diag(sigma + rho_i + joint weights)
+//    is the KKT system [[D, B'], [B, -E]] (E_r = 1/w_r on cost rows, 0 on equality rows).  Eliminating x needs
+//    only the K x K matrix G = E + B D^-1 B' = L_G L_G':
+//        x~ = N rhs + x_b,   N = D^-1 - U U',   U = D^-1 B' L_G^-T,   x_b = U L_G^-1 b.
+//    H is never formed.  ergoCub C3: K = 18 (15 equality + 3 chest rows) instead of an nv = 29 Cholesky, an nv x nv
+//    triangular inverse and three nv x me products.
+//  * Lane i keeps row i of N (and its x, z, y, lo, hi, rho) in registers; the only shared-memory operand of the
+//    mat-vec is the broadcast right-hand side, read two doubles per LDS.128.
+//  * The polish reuses the SAME factorisation: pinning the active joints is a rank-|A| correction of N
+//    (x = x1 - N[:,A] (N[A,A])^-1 (x1[A] - bound)), and the multipliers of the pinned joints come out of that
+//    correction, so the KKT certificate needs no second setup.  A rejected certificate updates the active set
+//    (primal-dual active-set step); if that does not settle, ADMM continues.
+#pragma once
+#include "blfik_device.cuh"
+
+namespace blfik {
+
+__host__ __device__ constexpr int ld2odd(int n)
+{
+    int h = (n + 1) / 2;
+    if ((h & 1) == 0) h++;
+    return 2 * h;  // smallest 2*odd >= n: conflict-free for lane-strided 64/128-bit accesses, rows 16 B aligned
+}
+
+// per-warp shared memory (offsets in doubles; the host fills this in)
+struct FastLayout {
+    int linkR, linkP, axisW, mcw;
+    int LGt;    // KP x LDG : L_G stored by columns (column k contiguous), diagonal slot holds 1 / l_kk
+    int Bm;     // KP x LDB : dense task rows
+    int Us;     // NV x LDG : U rows
+    int cvec;   // KP : right-hand sides b_r
+    int evec;   // KP : E_r
+    int dinv;   // LDB: 1 / D_i
+    int rvec;   // LDB: broadcast vector of the mat-vec
+    int wv;     // LDG: w = L_G^-1 b
+    int dA, muA;  // 32 each
+    int idxA;   // 32 ints (16 doubles)
+    int Ns;     // alias: N rows for dynamic column access (over Bm/Us)
+    int MA;     // alias: |A| x (|A| | 1) scratch for the active-set matrix (over the dead U region)
+    int ma_cap; // largest |A| the alias can hold
+    int total;
+};
+
+struct FastParams {
+    TickParams T;
+    FastLayout F;
+    int nv, K;          // actual sizes (<= NV, <= KP)
+    int max_as_iters;   // active-set refinement steps per round
+    int max_polish_iters;
+    int max_total_iters;  // per-tick budget of mat-vecs (ADMM + polish); exceeding it ends the solve with status 1
+};
+
+template <int NV, int KP>
+struct FastDims {
+    static constexpr int LDB = ld2odd(NV);
+    static constexpr int LDG = ld2odd(KP);
+};
+
+// frame Jacobian written straight into selected rows of the task-row matrix: source row s (0-2 linear,
+// 3-5 angular) goes to row map[s] of dst, or nowhere if map[s] < 0.
+__device__ __forceinline__ void fast_frame_jac(const DevModel& m, const double* linkP, const double* axisW, int L, const double* pf,
+                                               double* dst, int ld, const int* map, int lane)
+{
+    const int nv = m.n + 6;
+    const unsigned long long anc = m.anc[L];
+    if (lane < nv) {
+        const int c = lane;
+        double lin[3] = {0, 0, 0}, ang[3] = {0, 0, 0};
+        if (c < 3) {
+            lin[c] = 1.0;
+        } else if (c < 6) {
+            const double r[3] = {pf[0] - linkP[0], pf[1] - linkP[1], pf[2] - linkP[2]};
+            ang[c - 3] = 1.0;
+            cross3(ang, r, lin);
+        } else if ((anc >> (c - 6)) & 1ull) {
+            const int k = m.link_of_dof[c - 6];
+            const double d[3] = {pf[0] - linkP[3 * k], pf[1] - linkP[3 * k + 1], pf[2] - linkP[3 * k + 2]};
+            ang[0] = axisW[3 * k], ang[1] = axisW[3 * k + 1], ang[2] = axisW[3 * k + 2];
+            cross3(ang, d, lin);
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            if (map[i] >= 0) dst[map[i] * ld + c] = lin[i];
+            if (map[3 + i] >= 0) dst[map[3 + i] * ld + c] = ang[i];
+        }
+    }
+}
+
+__device__ __forceinline__ void fast_com_jac(const DevModel& m, const double* linkP, const double* axisW, const double* mcw,
+                                             const double* com, double* dst, int ld, const int* map, int lane)
+{
+    const int nv = m.n + 6;
+    if (lane < nv) {
+        const int c = lane;
+        double lin[3] = {0, 0, 0};
+        if (c < 3) {
+            lin[c] = 1.0;
+        } else if (c < 6) {
+            const double r[3] = {com[0] - linkP[0], com[1] - linkP[1], com[2] - linkP[2]};
+            double e[3] = {0, 0, 0};
+            e[c - 3] = 1.0;
+            cross3(e, r, lin);
+        } else {
+            const int j = c - 6;
+            const int kj = m.link_of_dof[j];
+            double mc[3] = {0, 0, 0};
+            for (int k = 1; k < m.nl; k++) {
+                if ((m.anc[k] >> j) & 1ull) {
+                    mc[0] += mcw[3 * k], mc[1] += mcw[3 * k + 1], mc[2] += mcw[3 * k + 2];
+                }
+            }
+            const double ms = m.msub[j];
+            const double d[3] = {(mc[0] - ms * linkP[3 * kj]) * m.inv_total_mass, (mc[1] - ms * linkP[3 * kj + 1]) * m.inv_total_mass,
+                                 (mc[2] - ms * linkP[3 * kj + 2]) * m.inv_total_mass};
+            const double a[3] = {axisW[3 * kj], axisW[3 * kj + 1], axisW[3 * kj + 2]};
+            cross3(a, d, lin);
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+            if (map[i] >= 0) dst[map[i] * ld + c] = lin[i];
+    }
+}
+
+// y_i = xb_i + sum_j nrow[j] * v[j], v broadcast from shared memory two doubles per load
+template <int NV>
+__device__ __forceinline__ double fast_matvec(const double (&nrow)[NV], const double* v, double xb)
+{
+    double a0 = xb, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    const double2* v2 = reinterpret_cast<const double2*>(v);
+#pragma unroll
+    for (int jj = 0; jj < NV / 2; jj++) {
+        const double2 t = v2[jj];
+        if (jj & 1) {
+            a2 = fma(nrow[2 * jj], t.x, a2);
+            a3 = fma(nrow[2 * jj + 1], t.y, a3);
+        } else {
+            a0 = fma(nrow[2 * jj], t.x, a0);
+            a1 = fma(nrow[2 * jj + 1], t.y, a1);
+        }
+    }
+    if (NV & 1) a0 = fma(nrow[NV - 1], v[NV - 1], a0);
+    return (a0 + a1) + (a2 + a3);
+}
+
+// In-place inverse of the a x a SPD matrix M (row stride ld) in shared memory by Gauss-Jordan sweeps,
+// row t by lane t.  a <= 32.  Returns false if a pivot is not positive.
+__device__ __forceinline__ bool fast_small_inverse(double* M, int a, int ld, int lane)
+{
+    bool ok = true;
+    for (int k = 0; k < a; k++) {
+        const double p = M[k * ld + k];
+        if (!(p > 0.0)) ok = false;
+        const double ip = 1.0 / p;
+        __syncwarp();
+        if (lane == k) {
+            for (int j = 0; j < a; j++) M[k * ld + j] = (j == k) ? ip : M[k * ld + j] * ip;
+        }
+        __syncwarp();
+        if (lane < a && lane != k) {
+            const double f = M[lane * ld + k];
+            for (int j = 0; j < a; j++) M[lane * ld + j] = (j == k) ? -f * ip : M[lane * ld + j] - f * M[k * ld + j];
+        }
+        __syncwarp();
+    }
+    return ok;
+}
+
+
+// out[j-1] = in[j] - f * col[k + j] for j = 1 .. KP-1 (col = column k of L_G^T storage, 16 B aligned; PAR = k & 1).
+// The arrays "rotate" by one slot per elimination step, so the pivot is always element 0 and the step loop
+// can stay rolled with statically indexed registers (two steps per trip ping-pong between two arrays).
+template <int KP, int PAR>
+__device__ __forceinline__ void rot_update(const double (&in)[KP], double (&out)[KP], double f, const double* colk)
+{
+    if (PAR == 0) {
+        out[0] = fma(-f, colk[1], in[1]);
+#pragma unroll
+        for (int j = 2; j + 1 < KP; j += 2) {
+            const double2 c2 = *reinterpret_cast<const double2*>(colk + j);
+            out[j - 1] = fma(-f, c2.x, in[j]);
+            out[j] = fma(-f, c2.y, in[j + 1]);
+        }
+    } else {
+#pragma unroll
+        for (int j = 1; j + 1 < KP; j += 2) {
+            const double2 c2 = *reinterpret_cast<const double2*>(colk + j);
+            out[j - 1] = fma(-f, c2.x, in[j]);
+            out[j] = fma(-f, c2.y, in[j + 1]);
+        }
+        out[KP - 2] = fma(-f, colk[KP - 1], in[KP - 1]);
+    }
+    out[KP - 1] = 0.0;
+}
+
+// One factorisation per tick.  In: task rows Bm (KP x LDB), 1/D (dinv), right-hand sides cvec, E (evec).
+// Out: row `lane` of N in registers (nrow) and in shared memory (Ns), x_b.  Gs/Us share one region.
+template <int NV, int KP>
+__device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double* LGt, double* Ns, const double* dinv,
+                                           const double* cvec, const double* evec, double* wv, double dinv_i, bool mine,
+                                           int nv, int lane, double (&nrow)[NV], double& xb)
+{
+    constexpr int LDB = FastDims<NV, KP>::LDB;
+    constexpr int LDG = FastDims<NV, KP>::LDG;
+    double* Gs = Us;   // G by columns, consumed before U is written
+    bool ok = true;
+    // ---- G = E + B D^-1 B', row r by lane r (lanes >= KP shadow row 0)
+    {
+        double brow[LDB];
+        const int myr = lane < KP ? lane : 0;
+        const double2* myrow = reinterpret_cast<const double2*>(Bm + myr * LDB);
+        const double2* dv = reinterpret_cast<const double2*>(dinv);
+#pragma unroll
+        for (int jj = 0; jj < LDB / 2; jj++) {
+            const double2 b2 = myrow[jj], d2 = dv[jj];
+            brow[2 * jj] = b2.x * d2.x, brow[2 * jj + 1] = b2.y * d2.y;
+        }
+        const double er = evec[myr];
+#pragma unroll 1
+        for (int c = 0; c < KP; c++) {
+            const double2* oth = reinterpret_cast<const double2*>(Bm + c * LDB);
+            double a0 = (c == lane) ? er : 0.0, a1 = 0.0;
+#pragma unroll
+            for (int jj = 0; jj < LDB / 2; jj++) {
+                const double2 o2 = oth[jj];
+                a0 = fma(brow[2 * jj], o2.x, a0);
+                a1 = fma(brow[2 * jj + 1], o2.y, a1);
+            }
+            if (lane < KP) Gs[c * LDG + lane] = a0 + a1;
+        }
+    }
+    __syncwarp();
+    // ---- Cholesky G = L L' (rotating rows, rolled); column k of L goes to LGt[k][*], diagonal slot = 1 / l_kk
+    {
+        double gA[KP], gB[KP];
+        const int myr = lane < KP ? lane : 0;
+#pragma unroll
+        for (int j = 0; j < KP; j++) gA[j] = Gs[j * LDG + myr];
+        const double floor_ = 1e-14 * warp_max(lane < KP ? Gs[myr * LDG + myr] : 0.0) + 1e-300;
+        __syncwarp();
+#pragma unroll 1
+        for (int k = 0; k < KP; k += 2) {
+            {
+                double piv = __shfl_sync(kFull, gA[0], k);
+                if (!(piv > floor_)) {
+                    if (!(piv == piv)) ok = false;
+                    piv = floor_;
+                }
+                const double rinv = rsqrt(piv);
+                const double lrk = gA[0] * rinv;
+                if (lane < KP) LGt[k * LDG + lane] = (lane == k) ? rinv : ((lane > k) ? lrk : 0.0);
+                __syncwarp();
+                rot_update<KP, 0>(gA, gB, lrk, LGt + k * LDG + k);
+            }
+            {
+                const int k1 = k + 1;
+                double piv = __shfl_sync(kFull, gB[0], k1);
+                if (!(piv > floor_)) {
+                    if (!(piv == piv)) ok = false;
+                    piv = floor_;
+                }
+                const double rinv = rsqrt(piv);
+                const double lrk = gB[0] * rinv;
+                if (lane < KP) LGt[k1 * LDG + lane] = (lane == k1) ? rinv : ((lane > k1) ? lrk : 0.0);
+                __syncwarp();
+                rot_update<KP, 1>(gB, gA, lrk, LGt + k1 * LDG + k1);
+            }
+        }
+    }
+    // ---- U = D^-1 B' L^-T, row i by lane i (forward substitution, rotating); a spare lane solves L w = b
+    {
+        const bool spare = nv < 32;
+        const bool wlane = spare && lane == nv;
+        const int passes = spare ? 1 : 2;   // nv == 32: a second pass in which lane 0 solves for w
+#pragma unroll 1
+        for (int pass = 0; pass < passes; pass++) {
+            const bool wl = pass == 1 ? (lane == 0) : wlane;
+            double tA[KP], tB[KP];
+#pragma unroll
+            for (int j = 0; j < KP; j++) tA[j] = (pass == 0 && mine) ? Bm[j * LDB + lane] * dinv_i : (wl ? cvec[j] : 0.0);
+#pragma unroll 1
+            for (int c = 0; c < KP; c += 2) {
+                {
+                    const double uc = tA[0] * LGt[c * LDG + c];
+                    if (pass == 0 && lane < NV) Us[lane * LDG + c] = mine ? uc : 0.0;
+                    if (wl) wv[c] = uc;
+                    rot_update<KP, 0>(tA, tB, uc, LGt + c * LDG + c);
+                }
+                {
+                    const int c1 = c + 1;
+                    const double uc = tB[0] * LGt[c1 * LDG + c1];
+                    if (pass == 0 && lane < NV) Us[lane * LDG + c1] = mine ? uc : 0.0;
+                    if (wl) wv[c1] = uc;
+                    rot_update<KP, 1>(tB, tA, uc, LGt + c1 * LDG + c1);
+                }
+            }
+        }
+    }
+    __syncwarp();
+    // ---- N = D^-1 - U U' (row i by lane i, into Ns), x_b = U w
+    {
+        double u[KP];
+        const double2* myu = reinterpret_cast<const double2*>(Us + (lane < NV ? lane : 0) * LDG);
+#pragma unroll
+        for (int rr = 0; rr < KP / 2; rr++) {
+            const double2 t2 = myu[rr];
+            u[2 * rr] = t2.x, u[2 * rr + 1] = t2.y;
+        }
+#pragma unroll 1
+        for (int jx = 0; jx < NV; jx++) {
+            const double2* uj = reinterpret_cast<const double2*>(Us + jx * LDG);
+            double a0 = (jx == lane) ? dinv_i : 0.0, a1 = 0.0;
+#pragma unroll
+            for (int rr = 0; rr < KP / 2; rr++) {
+                const double2 t2 = uj[rr];
+                a0 = fma(-u[2 * rr], t2.x, a0);
+                a1 = fma(-u[2 * rr + 1], t2.y, a1);
+            }
+            if (lane < NV) Ns[lane * LDB + jx] = mine ? a0 + a1 : 0.0;
+        }
+        const double2* w2 = reinterpret_cast<const double2*>(wv);
+        double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+        for (int rr = 0; rr < KP / 2; rr++) {
+            const double2 t2 = w2[rr];
+            a0 = fma(u[2 * rr], t2.x, a0);
+            a1 = fma(u[2 * rr + 1], t2.y, a1);
+        }
+        xb = mine ? a0 + a1 : 0.0;
+    }
+    __syncwarp();
+    {
+        const double2* myn = reinterpret_cast<const double2*>(Ns + (lane < NV ? lane : 0) * LDB);
+#pragma unroll
+        for (int jj = 0; jj < NV / 2; jj++) {
+            const double2 t2 = myn[jj];
+            nrow[2 * jj] = t2.x, nrow[2 * jj + 1] = t2.y;
+        }
+        if (NV & 1) nrow[NV - 1] = Ns[(lane < NV ? lane : 0) * LDB + NV - 1];
+    }
+    return ok;
+}
+
+template <int NV, int KP>
+__global__ void __launch_bounds__(128, 3) blfik_tick_fast_kernel(const FastParams FP)
+{
+    constexpr int LDB = FastDims<NV, KP>::LDB;
+    constexpr int LDG = FastDims<NV, KP>::LDG;
+    extern __shared__ double smem[];
+    const TickParams& P = FP.T;
+    const FastLayout& F = FP.F;
+    const DevModel& m = P.m;
+    const Settings& st = P.st;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    double* base = smem + (size_t)wib * F.total;
+    double* linkR = base + F.linkR;
+    double* linkP = base + F.linkP;
+    double* axisW = base + F.axisW;
+    double* mcw = base + F.mcw;
+    double* LGt = base + F.LGt;
+    double* Bm = base + F.Bm;
+    double* Us = base + F.Us;
+    double* cvec = base + F.cvec;
+    double* evec = base + F.evec;
+    double* dinv = base + F.dinv;
+    double* rvec = base + F.rvec;
+    double* wv = base + F.wv;
+    double* dA = base + F.dA;
+    double* muA = base + F.muA;
+    int* idxA = reinterpret_cast<int*>(base + F.idxA);
+    double* Ns = base + F.Ns;
+    double* MA = base + F.MA;
+    const int n = m.n, nv = FP.nv, K = FP.K;
+    const bool mine = lane < nv;         // this lane owns velocity variable `lane`
+    const bool joint = mine && lane >= 6;
+    WM wk;                               // view for the K1 helpers of blfik_device.cuh
+    wk.linkR = linkR, wk.linkP = linkP, wk.axisW = axisW, wk.mcw = mcw;
+
+    for (long long robot = (long long)blockIdx.x * wpb + wib; robot < P.N; robot += (long long)gridDim.x * wpb) {
+        double* bp = P.base_pos + 3 * robot;
+        double* bq = P.base_quat + 4 * robot;
+        double* s = P.s + (size_t)n * robot;
+        const bool warm_flag = (P.flags & BLFIK_TICK_WARM_START) != 0;
+        double x = 0.0, z = 0.0, y = 0.0;
+        if (warm_flag && mine) {
+            x = P.wx[(size_t)nv * robot + lane];
+            if (joint) z = P.wz[(size_t)n * robot + lane - 6], y = P.wy[(size_t)n * robot + lane - 6];
+        }
+        int status = 2, iters_total = 0;
+        for (int tick = 0; tick < P.nticks; tick++) {
+            // ================================================================ K1
+            k1_fk(m, wk, bp, bq, s, lane);
+            // ================================================================ K2
+            // zero the row matrix (padding rows / columns must read as zero)
+            for (int e = lane; e < KP * LDB / 2; e += 32) reinterpret_cast<double2*>(Bm)[e] = make_double2(0.0, 0.0);
+            if (lane < KP) cvec[lane] = 0.0, evec[lane] = 1.0;
+            __syncwarp();
+            double dh = 0.0, gd = 0.0, lo = -kInf, hi = kInf;   // diagonal weight, sum w b, joint box
+            const double sj = joint ? s[lane - 6] : 0.0;
+            for (int t = 0; t < P.ntasks; t++) {
+                const DevTask& tk = P.tasks[t];
+                const double* sp = tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr;
+                if (tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM) {
+                    int map[6] = {-1, -1, -1, -1, -1, -1};
+                    double bt[6];
+                    int rows = 0;
+                    if (tk.type == T_COM) {
+                        double com[3], acc[3] = {0, 0, 0};
+                        for (int k = lane; k < m.nl; k += 32) acc[0] += mcw[3 * k], acc[1] += mcw[3 * k + 1], acc[2] += mcw[3 * k + 2];
+#pragma unroll
+                        for (int c = 0; c < 3; c++) com[c] = warp_sum(acc[c]) * m.inv_total_mass;
+#pragma unroll
+                        for (int c = 0; c < 3; c++)
+                            if (tk.mask[c]) {
+                                bt[rows] = sp[3 + c] + tk.kp_lin[c] * (sp[c] - com[c]);
+                                map[c] = tk.brow + rows++;
+                            }
+                        fast_com_jac(m, linkP, axisW, mcw, com, Bm, LDB, map, lane);
+                    } else {
+                        double R[9], pf[3];
+                        k1_frame_pose(m, wk, tk.frame, R, pf);
+                        if (tk.type == T_SE3 || tk.type == T_R3) {
+                            const int voff = tk.type == T_SE3 ? 7 : 3;
+#pragma unroll
+                            for (int c = 0; c < 3; c++)
+                                if (tk.mask[c]) {
+                                    bt[rows] = tk.enabled ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pf[c]) : sp[voff + c];
+                                    map[c] = tk.brow + rows++;
+                                }
+                        }
+                        if (tk.type == T_SE3 || tk.type == T_SO3) {
+                            const double* qd = tk.type == T_SE3 ? sp + 3 : sp;
+                            const double* wff = tk.type == T_SE3 ? sp + 10 : sp + 4;
+                            double qdl[4] = {qd[0], qd[1], qd[2], qd[3]}, wl[3] = {wff[0], wff[1], wff[2]}, out[3];
+                            so3_control(R, qdl, wl, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), out);
+#pragma unroll
+                            for (int c = 0; c < 3; c++) {
+                                bt[rows] = out[c];
+                                map[3 + c] = tk.brow + rows++;
+                            }
+                        }
+                        fast_frame_jac(m, linkP, axisW, m.frame_link[tk.frame], pf, Bm, LDB, map, lane);
+                    }
+                    if (lane < rows) {
+                        double bv = bt[0];
+#pragma unroll
+                        for (int r = 1; r < 6; r++) bv = (lane == r) ? bt[r] : bv;
+                        cvec[tk.brow + lane] = bv;
+                        evec[tk.brow + lane] = tk.priority == 0 ? 0.0 : 1.0 / tk.weight[lane];
+                    }
+                } else if (joint) {
+                    const int j = lane - 6;
+                    if (tk.type == T_JOINT_TRACKING) {
+                        const double bj = sp[n + j] + tk.kp_joint[j] * (sp[j] - sj);
+                        if (tk.priority == 1) {
+                            dh += tk.weight[j];
+                            gd += tk.weight[j] * bj;
+                        } else {
+                            lo = fmax(lo, bj), hi = fmin(hi, bj);
+                        }
+                    } else if (tk.type == T_JOINT_LIMITS) {
+                        hi = fmin(hi, tk.klim[j] * (tk.upper[j] - sj) * tk.inv_dt);
+                        lo = fmax(lo, tk.klim[j] * (tk.lower[j] - sj) * tk.inv_dt);
+                    } else {
+                        hi = fmin(hi, tk.upper[j]);
+                        lo = fmax(lo, tk.lower[j]);
+                    }
+                }
+            }
+            // per-variable ADMM step: 0 (no bound), rho (box), 1e3 rho (pinned: lo == hi)
+            const bool bounded = joint && (lo > -kInfHalf || hi < kInfHalf);
+            const bool pinned = bounded && lo == hi;
+            const double rho_i = bounded ? (pinned ? 1e3 * st.rho : st.rho) : 0.0;
+            const double D_i = mine ? st.sigma + rho_i + dh : 1.0;
+            const double Q_i = mine ? st.sigma + rho_i : 0.0;
+            const double dinv_i = 1.0 / D_i;
+            const double inv_rho = bounded ? 1.0 / rho_i : 0.0;
+            dinv[lane] = mine ? dinv_i : 0.0;
+            if (LDB > 32 && lane < LDB - 32) dinv[32 + lane] = 0.0, rvec[32 + lane] = 0.0;
+            const bool any_box = __any_sync(kFull, bounded);
+            const bool infeasible = __any_sync(kFull, bounded && lo > hi);
+            const double gmax = warp_max(fabs(gd));
+            __syncwarp();
+
+            if (P.dbg.H && tick == 0) {   // parity introspection only: materialise H, g, C_eq, b_eq, box
+                const int me = P.L.me;
+                if (mine) {
+                    for (int jx = 0; jx < nv; jx++) {
+                        double h = (jx == lane) ? dh : 0.0;
+                        for (int r = 0; r < K; r++)
+                            if (evec[r] > 0.0) h += Bm[r * LDB + lane] * Bm[r * LDB + jx] / evec[r];
+                        P.dbg.H[((size_t)robot * nv + lane) * nv + jx] = h;
+                    }
+                    double g = -gd;
+                    int er = 0;
+                    for (int r = 0; r < K; r++) {
+                        if (evec[r] > 0.0) g -= Bm[r * LDB + lane] * cvec[r] / evec[r];
+                        else {
+                            P.dbg.Ceq[((size_t)robot * me + er) * nv + lane] = Bm[r * LDB + lane];
+                            if (lane == 0) P.dbg.beq[(size_t)robot * me + er] = cvec[r];
+                            er++;
+                        }
+                    }
+                    P.dbg.g[(size_t)robot * nv + lane] = g;
+                    if (joint) P.dbg.lo[(size_t)robot * n + lane - 6] = lo, P.dbg.hi[(size_t)robot * n + lane - 6] = hi;
+                }
+                __syncwarp();
+            }
+
+            status = 1;
+            int iters = 0;
+            double nrow[NV];
+            double xb = 0.0;
+            if (infeasible) {
+                status = 2;
+            } else {
+                // ============================================================ K3 setup
+                const bool fac_ok = fast_setup<NV, KP>(Bm, Us, LGt, Ns, dinv, cvec, evec, wv, dinv_i, mine, nv, lane, nrow, xb);
+                if (!fac_ok) status = 2;
+            }
+
+            if (status != 2) {
+                // ============================================================ K3 iterations
+                if (!warm_flag) x = 0.0, z = 0.0, y = 0.0;
+                if (bounded) z = fmin(fmax(z, lo), hi);
+                else z = 0.0, y = 0.0;
+                const double tolx_rel = 1e-9;
+                const double toly = 1e-8 * (1.0 + gmax);
+                const double tol_fix = 1e-10 * (1.0 + gmax);
+                double xp = x;
+                double mu_mine = 0.0;
+                int act = 0;   // 0 free, 1 lower, 2 upper, 3 pinned
+                bool done = false;
+                for (int round = 0; round < st.max_rounds && !done && iters < FP.max_total_iters; round++) {
+                    // ---- ADMM (skipped when there is no box row: the problem is a pure equality QP)
+                    double rp = 0.0, rd = 0.0;
+                    if (any_box) {
+                        for (int it = 0; it < st.admm_iters; it++) {
+                            rvec[lane] = mine ? st.sigma * x + gd + (bounded ? rho_i * z - y : 0.0) : 0.0;
+                            __syncwarp();
+                            const double xt = fast_matvec<NV>(nrow, rvec, xb);
+                            __syncwarp();
+                            const double xn = st.alpha * xt + (1.0 - st.alpha) * x;
+                            rd = st.sigma * fabs(xn - x);
+                            rp = 0.0;
+                            x = xn;
+                            if (bounded) {
+                                const double zr = st.alpha * xt + (1.0 - st.alpha) * z;
+                                const double zn = fmin(fmax(zr + y * inv_rho, lo), hi);
+                                y += rho_i * (zr - zn);
+                                rd = fmax(rd, rho_i * fabs(zn - z));
+                                z = zn;
+                                rp = fabs(xn - zn);
+                            }
+                            iters++;
+                        }
+                        rp = warp_max(mine ? rp : 0.0), rd = warp_max(mine ? rd : 0.0);
+                        if (!(rp == rp) || !(rd == rd)) {
+                            status = 2;
+                            break;
+                        }
+                    }
+                    const bool admm_converged = any_box && rp <= st.eps && rd <= st.eps * (1.0 + gmax);
+                    // ---- polish: OSQP's active-set rule, then primal-dual active-set refinement on the same N
+                    act = 0;
+                    if (bounded) {
+                        if (pinned) act = 3;
+                        else if (z - lo < -y) act = 1;
+                        else if (hi - z < y) act = 2;
+                    }
+                    xp = x;
+                    for (int as_it = 0; as_it < FP.max_as_iters && !done && iters < FP.max_total_iters; as_it++) {
+                        const unsigned amask = __ballot_sync(kFull, act != 0);
+                        const int a = __popc(amask);
+                        const int rank = __popc(amask & ((1u << lane) - 1u));
+                        const double bd = (act == 1) ? lo : hi;   // pinned: lo == hi
+                        const int mld = a | 1;
+                        bool small_ok = true;
+                        if (a > FP.F.ma_cap) break;               // cannot hold the active-set matrix: leave it to ADMM
+                        if (a > 0) {
+                            if (act) idxA[rank] = lane;
+                            __syncwarp();
+                            if (lane < a) {
+                                const int ri = idxA[lane];
+                                for (int uu = 0; uu < a; uu++) MA[lane * mld + uu] = Ns[ri * LDB + idxA[uu]];
+                            }
+                            __syncwarp();
+                            small_ok = fast_small_inverse(MA, a, mld, lane);
+                            small_ok = __all_sync(kFull, small_ok);
+                        }
+                        if (!small_ok) break;
+                        if (act) xp = bd;
+                        double dx = 0.0;
+                        bool conv = false;
+                        for (int it = 0; it < FP.max_polish_iters; it++) {
+                            rvec[lane] = mine ? Q_i * xp + gd : 0.0;
+                            __syncwarp();
+                            double x1 = fast_matvec<NV>(nrow, rvec, xb);
+                            __syncwarp();
+                            if (a > 0) {
+                                if (act) dA[rank] = x1 - bd;
+                                __syncwarp();
+                                if (lane < a) {
+                                    double mu = 0.0;
+                                    for (int uu = 0; uu < a; uu++) mu = fma(MA[lane * mld + uu], dA[uu], mu);
+                                    muA[lane] = mu;
+                                }
+                                __syncwarp();
+                                if (mine)
+                                    for (int uu = 0; uu < a; uu++) x1 = fma(-Ns[lane * LDB + idxA[uu]], muA[uu], x1);
+                                if (act) x1 = bd, mu_mine = muA[rank];
+                            }
+                            dx = mine ? Q_i * fabs(x1 - xp) : 0.0;
+                            xp = mine ? x1 : 0.0;
+                            iters++;
+                            if ((it & 1) == 1 || it + 1 == FP.max_polish_iters) {
+                                const double dxm = warp_max(dx);
+                                if (!(dxm == dxm)) break;
+                                if (dxm <= tol_fix) {
+                                    conv = true;
+                                    break;
+                                }
+                            }
+                        }
+                        // KKT certificate: box feasibility of the free joints, multiplier signs of the pinned ones
+                        bool viol_lo = false, viol_up = false, bad = false;
+                        if (bounded && act == 0) {
+                            const double tolx = tolx_rel * (1.0 + fabs(xp));
+                            viol_up = xp > hi + tolx, viol_lo = xp < lo - tolx;
+                        }
+                        if (act == 1 && mu_mine > toly) bad = true;
+                        if (act == 2 && mu_mine < -toly) bad = true;
+                        if (!(xp == xp)) bad = true, conv = false;
+                        const bool any_change = __any_sync(kFull, viol_lo || viol_up || bad);
+                        if (conv && !any_change) {
+                            done = true;
+                            status = 0;
+                            x = xp;
+                            if (bounded) {
+                                z = fmin(fmax(xp, lo), hi);
+                                y = act ? mu_mine : 0.0;
+                            }
+                        } else if (!conv && !any_change) {
+                            break;   // right active set, fixed point not reached in the budget: continue with ADMM
+                        } else {
+                            if (bad) act = 0;
+                            if (viol_lo) act = 1;
+                            if (viol_up) act = 2;
+                        }
+                    }
+                    if (!done && admm_converged) {
+                        done = true;
+                        status = 0;
+                    }
+                    if (!any_box && !done) break;   // nothing ADMM could add
+                }
+                if (!done && status != 2) status = 1;
+            }
+            iters_total += iters;
+            if (mine) P.nu[(size_t)nv * robot + lane] = x;
+            if (P.flags & BLFIK_TICK_INTEGRATE) {
+                rvec[lane] = mine ? x : 0.0;
+                __syncwarp();
+                k4_integrate(n, bp, bq, s, rvec, P.dt, lane);
+            }
+            __syncwarp();
+        }
+        if (mine) {
+            P.wx[(size_t)nv * robot + lane] = x;
+            if (joint) P.wz[(size_t)n * robot + lane - 6] = z, P.wy[(size_t)n * robot + lane - 6] = y;
+        }
+        if (lane == 0) {
+            P.status[robot] = status;
+            P.iters[robot] = iters_total;
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace blfik

@@ -117,11 +117,11 @@ typedef struct {
  * of OSQP's per-row rho), the box rows (joint limits) are the ADMM-split part.       */
 typedef struct {
     double rho;            /* step on the box rows                    (default 1.0)    */
-    double sigma;          /* proximal regularisation                 (default 1e-3)   */
+    double sigma;          /* proximal regularisation                 (default 1e-2)   */
     double alpha;          /* over-relaxation                         (default 1.6)    */
     double eps;            /* inf-norm residual tolerance of ADMM     (default 1e-7)   */
     int32_t admm_iters;    /* ADMM iterations before each polish try  (default 10)     */
-    int32_t max_rounds;    /* ADMM+polish rounds before giving up     (default 20)     */
+    int32_t max_rounds;    /* ADMM+polish rounds before giving up     (default 8)      */
     int32_t polish_iters;  /* proximal refinement steps in the polish (default 4)      */
     int32_t eq_iters;      /* proximal steps when there are no box rows (default 5)    */
 } blfik_solver_settings;
@@ -239,6 +239,13 @@ int blfik_sync(blfik_problem* problem);
 /* the problem's cudaStream_t (as void*); set_stream makes later work use the caller's stream */
 void* blfik_get_stream(blfik_problem* problem);
 int blfik_set_stream(blfik_problem* problem, void* cuda_stream);
+/* Two kernels implement the tick: a register-resident one for nv <= 32 velocity variables and <= 32
+ * dense task rows (all ergoCub / iCub-26 configurations), and a generic shared-memory one for everything
+ * else.  path 0 = choose automatically (default), 1 = force the generic kernel (parity tests run both).
+ * blfik_get_kernel_path returns 2 when the next tick runs the register-resident kernel, else 1.
+ * No reference counterpart (the reference has a single OSQP code path).                     */
+int blfik_set_kernel_path(blfik_problem* problem, int32_t path);
+int32_t blfik_get_kernel_path(const blfik_problem* problem);
 /* number of kernel launches issued so far by this problem                                */
 int64_t blfik_launch_count(const blfik_problem* problem);
 const char* blfik_last_error(void);

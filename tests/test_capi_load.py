@@ -27,7 +27,7 @@ def test_default_settings_and_model_validation():
     lib = capi.load()
     s = capi.SolverSettings()
     lib.blfik_default_settings(C.byref(s))
-    assert (s.rho, s.sigma, s.alpha, s.eps) == (1.0, 1e-3, 1.6, 1e-7) and s.admm_iters == 10
+    assert (s.rho, s.sigma, s.alpha, s.eps) == (1.0, 1e-2, 1.6, 1e-7) and s.admm_iters == 10
     km = M.ergocub23()
     model = capi.Model(km)          # host-only: works without a GPU
     assert model.handle
