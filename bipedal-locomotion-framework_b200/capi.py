@@ -35,7 +35,7 @@ EXPORTS = [
     "blfik_count_unsolved", "blfik_kinematics", "blfik_integrate", "blfik_debug_enable", "blfik_debug_get",
     "blfik_num_dofs", "blfik_num_equality_rows", "blfik_num_instances", "blfik_sync", "blfik_get_stream",
     "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak", "blfik_kinematics_noalloc",
-    "blfik_set_kernel_path", "blfik_get_kernel_path",
+    "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state",
 ]
 
 

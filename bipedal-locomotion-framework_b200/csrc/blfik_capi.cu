@@ -979,6 +979,47 @@ extern "C" int blfik_measure_fp64_peak(int32_t device, double millis, double* tf
     return BLFIK_OK;
 }
 
+extern "C" int blfik_integrate_state(int32_t n, int64_t N, double* bp, double* bq, double* s, const double* nu, double dt, int32_t nsteps,
+                                     int32_t mem, int32_t device)
+{
+    if (n < 1 || N < 1 || !bp || !bq || !s || !nu) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate_state] bad sizes or null buffer");
+    if (!(dt > 0)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate_state] the integration step must be positive");
+    if (nsteps < 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate_state] nsteps must be >= 1");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(BLFIK_ERR_CUDA, "[blfik_integrate_state] no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate_state] device %d out of range", device);
+    CU(cudaSetDevice(device));
+    const size_t Ns = (size_t)N, nv = (size_t)n + 6;
+    double *dp = bp, *dq = bq, *ds = s;
+    const double* dnu = nu;
+    double* stage = nullptr;
+    if (mem != BLFIK_MEM_DEVICE) {
+        const size_t total = Ns * (3 + 4 + (size_t)n + nv);
+        CU(cudaMalloc((void**)&stage, total * sizeof(double)));
+        dp = stage, dq = dp + Ns * 3, ds = dq + Ns * 4;
+        double* dn = ds + Ns * n;
+        dnu = dn;
+        cudaMemcpy(dp, bp, Ns * 3 * sizeof(double), cudaMemcpyHostToDevice);
+        cudaMemcpy(dq, bq, Ns * 4 * sizeof(double), cudaMemcpyHostToDevice);
+        cudaMemcpy(ds, s, Ns * n * sizeof(double), cudaMemcpyHostToDevice);
+        cudaMemcpy(dn, nu, Ns * nv * sizeof(double), cudaMemcpyHostToDevice);
+    }
+    const long long blocks = ((long long)N * 32 + 255) / 256;
+    blfik_integrate_kernel<<<(int)(blocks < 148 * 8 ? blocks : 148 * 8), 256>>>(n, N, dp, dq, ds, dnu, dt, nsteps);
+    e = cudaGetLastError();
+    if (e == cudaSuccess && mem != BLFIK_MEM_DEVICE) {
+        cudaMemcpy(bp, dp, Ns * 3 * sizeof(double), cudaMemcpyDeviceToHost);
+        cudaMemcpy(bq, dq, Ns * 4 * sizeof(double), cudaMemcpyDeviceToHost);
+        e = cudaMemcpy(s, ds, Ns * n * sizeof(double), cudaMemcpyDeviceToHost);
+    } else if (e == cudaSuccess) {
+        e = cudaDeviceSynchronize();
+    }
+    if (stage) cudaFree(stage);
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_integrate_state] %s", cudaGetErrorString(e));
+    return BLFIK_OK;
+}
+
 extern "C" int32_t blfik_num_dofs(const blfik_problem* p) { return p ? p->n : -1; }
 extern "C" int32_t blfik_num_equality_rows(const blfik_problem* p) { return p ? p->me : -1; }
 extern "C" int64_t blfik_num_instances(const blfik_problem* p) { return p ? p->N : -1; }

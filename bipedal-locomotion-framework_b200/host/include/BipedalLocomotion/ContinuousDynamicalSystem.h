@@ -1,0 +1,227 @@
+/**
+ * ContinuousDynamicalSystem.h -- FloatingBaseSystemVelocityKinematics and ForwardEuler with a batch dimension.
+ *   reference: src/ContinuousDynamicalSystem/include/BipedalLocomotion/ContinuousDynamicalSystem/
+ *              FloatingBaseSystemVelocityKinematics.h:34-128 (.cpp:14-84), ForwardEuler.h:49-124,
+ *              FixedStepIntegrator.h:38-140, Integrator.h:41-129
+ * State = (p in R3, R in SO(3), s in R^n); Input = (mixed twist in R6, sdot in R^n);
+ * one Euler step: p += v dt, R <- exp(w dt) R (manif tangent + group = left-plus), s += sdot dt.
+ * The step itself runs on the GPU (blfik_integrate_state); there is no CPU integrator here.
+ */
+#ifndef BLF_B200_CONTINUOUS_DYNAMICAL_SYSTEM_H
+#define BLF_B200_CONTINUOUS_DYNAMICAL_SYSTEM_H
+
+#include <BipedalLocomotion/Core.h>
+#include <blfik.h>
+
+#include <tuple>
+
+namespace BipedalLocomotion
+{
+namespace ContinuousDynamicalSystem
+{
+
+class FloatingBaseSystemVelocityKinematics
+{
+public:
+    using State = std::tuple<Vector3d, SO3d, VectorXd>;
+    using StateDerivative = std::tuple<Vector3d, SO3Tangentd, VectorXd>;
+    using Input = std::tuple<std::array<double, 6>, VectorXd>;
+
+    /** no mandatory parameter; `rho` is accepted and ignored with an info message (.cpp:14-31) */
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> handler)
+    {
+        auto ptr = handler.lock();
+        double rho;
+        if (ptr && ptr->getParameter("rho", rho))
+            log()->info("[FloatingBaseSystemVelocityKinematics::initialize] The rho parameter is not used by this system.");
+        return true;
+    }
+    /** number of robots integrated at once (default 1) */
+    void setBatchSize(std::size_t N) { m_N = N; }
+    std::size_t getBatchSize() const { return m_N; }
+
+    bool setState(const State& state, std::ptrdiff_t instance = -1)
+    {
+        const VectorXd& s = std::get<2>(state);
+        if (m_n == 0) m_n = s.size();
+        if (s.size() != m_n) {
+            log()->error("[FloatingBaseSystemVelocityKinematics::setState] Wrong size of the joint vector.");
+            return false;
+        }
+        resize();
+        const auto q = std::get<1>(state).quat().coeffs();
+        for (std::size_t i = 0; i < m_N; i++) {
+            if (instance >= 0 && static_cast<std::size_t>(instance) != i) continue;
+            for (int c = 0; c < 3; c++) m_p[3 * i + c] = std::get<0>(state)[c];
+            for (int c = 0; c < 4; c++) m_q[4 * i + c] = q[c];
+            for (std::size_t j = 0; j < m_n; j++) m_s[m_n * i + j] = s[j];
+        }
+        return true;
+    }
+    bool setStateBatch(std::size_t n, const double* p, const double* q, const double* s)
+    {
+        m_n = n;
+        resize();
+        m_p.assign(p, p + 3 * m_N), m_q.assign(q, q + 4 * m_N), m_s.assign(s, s + n * m_N);
+        return true;
+    }
+    State getState(std::size_t instance = 0) const
+    {
+        State st;
+        if (m_p.empty()) return st;
+        for (int c = 0; c < 3; c++) std::get<0>(st)[c] = m_p[3 * instance + c];
+        std::get<1>(st) = SO3d(Quaterniond{m_q[4 * instance], m_q[4 * instance + 1], m_q[4 * instance + 2], m_q[4 * instance + 3]});
+        std::get<2>(st).assign(m_s.begin() + m_n * instance, m_s.begin() + m_n * (instance + 1));
+        return st;
+    }
+    bool setControlInput(const Input& input, std::ptrdiff_t instance = -1)
+    {
+        const VectorXd& ds = std::get<1>(input);
+        if (m_n == 0) m_n = ds.size();
+        resize();
+        if (ds.size() != m_n) {  // .cpp:52-56
+            log()->error("[FloatingBaseSystemVelocityKinematics::dynamics] Wrong size of the vectors.");
+            return false;
+        }
+        const std::size_t nv = m_n + 6;
+        for (std::size_t i = 0; i < m_N; i++) {
+            if (instance >= 0 && static_cast<std::size_t>(instance) != i) continue;
+            for (int c = 0; c < 6; c++) m_nu[nv * i + c] = std::get<0>(input)[c];
+            for (std::size_t j = 0; j < m_n; j++) m_nu[nv * i + 6 + j] = ds[j];
+        }
+        m_inputSet = true;
+        return true;
+    }
+    /** [N][6+n] robot-major (the layout QPInverseKinematics::getBatchOutput returns) */
+    bool setControlInputBatch(const double* nu)
+    {
+        if (m_n == 0) return false;
+        resize();
+        m_nu.assign(nu, nu + (m_n + 6) * m_N);
+        m_inputSet = true;
+        return true;
+    }
+    /** dp = twist.head3, omega = twist.tail3, ds = sdot (.cpp:33-67) */
+    bool dynamics(const std::chrono::nanoseconds&, StateDerivative& d, std::size_t instance = 0) const
+    {
+        if (!m_inputSet) return false;
+        const std::size_t nv = m_n + 6;
+        for (int c = 0; c < 3; c++) std::get<0>(d)[c] = m_nu[nv * instance + c], std::get<1>(d).w[c] = m_nu[nv * instance + 3 + c];
+        std::get<2>(d).assign(m_nu.begin() + nv * instance + 6, m_nu.begin() + nv * (instance + 1));
+        return true;
+    }
+    std::size_t dofs() const { return m_n; }
+    std::vector<double>&basePositions() { return m_p; }
+    std::vector<double>&baseQuaternions() { return m_q; }
+    std::vector<double>&jointPositions() { return m_s; }
+    const std::vector<double>& controlInput() const { return m_nu; }
+    bool hasInput() const { return m_inputSet; }
+
+private:
+    void resize()
+    {
+        if (m_p.size() != 3 * m_N) {
+            m_p.assign(3 * m_N, 0.0), m_q.assign(4 * m_N, 0.0), m_s.assign(m_n * m_N, 0.0);
+            for (std::size_t i = 0; i < m_N; i++) m_q[4 * i + 3] = 1.0;
+        }
+        if (m_nu.size() != (m_n + 6) * m_N) m_nu.assign((m_n + 6) * m_N, 0.0);
+    }
+    std::size_t m_N{1}, m_n{0};
+    std::vector<double> m_p, m_q, m_s, m_nu;
+    bool m_inputSet{false};
+};
+
+/** deprecated alias kept by the reference (FloatingBaseSystemVelocityKinematics.h:126-128) */
+using FloatingBaseSystemKinematics = FloatingBaseSystemVelocityKinematics;
+
+template <class _DynamicalSystem> class ForwardEuler
+{
+public:
+    using DynamicalSystem = _DynamicalSystem;
+    using State = typename _DynamicalSystem::State;
+
+    /** only once (Integrator.h:94-99) */
+    bool setDynamicalSystem(std::shared_ptr<DynamicalSystem> dynamicalSystem)
+    {
+        constexpr auto errorPrefix = "[Integrator::setDynamicalSystem]";
+        if (m_dynamicalSystem != nullptr) {
+            log()->error("{} The dynamical system has been already set.", errorPrefix);
+            return false;
+        }
+        if (dynamicalSystem == nullptr) {
+            log()->error("{} The dynamical system passed to the function is corrupted.", errorPrefix);
+            return false;
+        }
+        m_dynamicalSystem = dynamicalSystem;
+        return true;
+    }
+    std::weak_ptr<DynamicalSystem> dynamicalSystem() const { return m_dynamicalSystem; }
+    /** FixedStepIntegrator.h:73-85 */
+    bool setIntegrationStep(const std::chrono::nanoseconds& dT)
+    {
+        if (dT <= std::chrono::nanoseconds::zero()) {
+            log()->error("[FixedStepIntegrator::setIntegrationStep] The integration must be a strictly positive number.");
+            return false;
+        }
+        m_dT = dT;
+        return true;
+    }
+    std::chrono::nanoseconds getIntegrationStep() const { return m_dT; }
+    void setDevice(int device) { m_device = device; }
+
+    /** FixedStepIntegrator.h:94-140: (iterations - 1) steps of dT, then one step that lands on finalTime.
+     *  The reference's size_t underflow for finalTime - initialTime < dT is rejected instead of reproduced. */
+    bool integrate(const std::chrono::nanoseconds& initialTime, const std::chrono::nanoseconds& finalTime)
+    {
+        constexpr auto errorPrefix = "[FixedStepIntegrator::integrate]";
+        if (m_dynamicalSystem == nullptr) {
+            log()->error("{} Please set the dynamical system before call this function.", errorPrefix);
+            return false;
+        }
+        if (initialTime > finalTime) {
+            log()->error("{} The final time has to be greater than the initial one.", errorPrefix);
+            return false;
+        }
+        if (m_dT <= std::chrono::nanoseconds::zero()) {
+            log()->error("{} Please set the integration step.", errorPrefix);
+            return false;
+        }
+        const std::size_t iterations = static_cast<std::size_t>((finalTime - initialTime) / m_dT);
+        if (iterations < 1) {
+            log()->error("{} The integration interval is shorter than the integration step.", errorPrefix);
+            return false;
+        }
+        auto& sys = *m_dynamicalSystem;
+        if (!sys.hasInput()) {
+            log()->error("[ForwardEuler::oneStepIntegration] Unable to compute the system dynamics.");
+            return false;
+        }
+        const double dT = std::chrono::duration<double>(m_dT).count();
+        const auto lastStep = finalTime - (initialTime + m_dT * static_cast<long long>(iterations - 1));
+        if (iterations > 1 && !step(sys, dT, static_cast<int>(iterations - 1))) return false;
+        return step(sys, std::chrono::duration<double>(lastStep).count(), 1);
+    }
+    /** Integrator.h:117-122 */
+    State getSolution(std::size_t instance = 0) const { return m_dynamicalSystem ? m_dynamicalSystem->getState(instance) : State(); }
+
+private:
+    bool step(DynamicalSystem& sys, double dt, int nsteps)
+    {
+        const int rc = blfik_integrate_state(static_cast<int32_t>(sys.dofs()), static_cast<int64_t>(sys.getBatchSize()), sys.basePositions().data(),
+                                             sys.baseQuaternions().data(), sys.jointPositions().data(), sys.controlInput().data(), dt, nsteps,
+                                             BLFIK_MEM_HOST, m_device);
+        if (rc != BLFIK_OK) {
+            log()->error("[ForwardEuler::oneStepIntegration] {}", blfik_last_error());
+            return false;
+        }
+        return true;
+    }
+    std::shared_ptr<DynamicalSystem> m_dynamicalSystem;
+    std::chrono::nanoseconds m_dT{0};
+    int m_device{0};
+};
+
+}  // namespace ContinuousDynamicalSystem
+}  // namespace BipedalLocomotion
+
+#endif

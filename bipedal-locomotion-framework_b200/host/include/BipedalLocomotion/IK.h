@@ -1,0 +1,344 @@
+/**
+ * IK.h -- the IK:: classes of the reference with a batch dimension: IKLinearTask, SE3Task, CoMTask, SO3Task, R3Task,
+ * JointTrackingTask, JointLimitsTask, JointVelocityLimitsTask, IntegrationBasedIK{,State,Problem}, QPInverseKinematics.
+ * Same class / method / parameter-key names and the same bool + log()->error convention as
+ * the headers under src/IK/include/BipedalLocomotion/IK; N = 1 reproduces the reference semantics, N > 1 runs N robots per tick.
+ * The numerical work happens in libblfik_cuda.so (include/blfik.h); tasks only describe themselves
+ * (blfik_task_desc) and hold their batch of set-points.
+ */
+#ifndef BLF_B200_IK_H
+#define BLF_B200_IK_H
+
+#include <BipedalLocomotion/KinDynBatch.h>
+
+namespace BipedalLocomotion
+{
+namespace IK
+{
+
+/** IKLinearTask.h:31-43 */
+class IKLinearTask : public System::LinearTask
+{
+public:
+    virtual bool setKinDyn(std::shared_ptr<KinDynBatch> kinDyn)
+    {
+        if (!kinDyn || !kinDyn->isValid()) {
+            log()->error("[{}::setKinDyn] Invalid kinDyn object.", className());
+            return false;
+        }
+        m_kinDyn = kinDyn;
+        return true;
+    }
+    bool setVariablesHandler(const System::VariablesHandler& variablesHandler) override
+    {
+        if (!m_isInitialized) {
+            log()->error("[{}::setVariablesHandler] The task is not initialized. Please call initialize method.", className());
+            return false;
+        }
+        if (!variablesHandler.getVariable(m_robotVelocityVariable.name, m_robotVelocityVariable)) {
+            log()->error("[{}::setVariablesHandler] Unable to get the variable named {}.", className(), m_robotVelocityVariable.name);
+            return false;
+        }
+        if (m_robotVelocityVariable.size != static_cast<std::ptrdiff_t>(m_kinDyn->getNrOfDegreesOfFreedom() + 6)) {
+            log()->error("[{}::setVariablesHandler] The size of the robot velocity variable is different from the one expected. "
+                         "Expected size: {}. Given size: {}.",
+                         className(), m_kinDyn->getNrOfDegreesOfFreedom() + 6, m_robotVelocityVariable.size);
+            return false;
+        }
+        m_nVars = variablesHandler.getNumberOfVariables();
+        m_A.resize(size(), m_nVars);   // zero outside the robot-velocity column block (SE3Task.cpp:61-64)
+        m_b.assign(size(), 0.0);
+        return true;
+    }
+    bool isValid() const override { return m_isValid; }
+    std::shared_ptr<KinDynBatch> kinDyn() const { return m_kinDyn; }
+
+    // ---- hooks of the batched back-end (no counterpart in the reference)
+    virtual const char* className() const = 0;
+    /** describe this task to the C ABI; `keep` owns the arrays the descriptor points to */
+    virtual bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const = 0;
+    /** doubles per robot of the set-point record (0: the task takes none) */
+    virtual std::size_t setPointLength() const { return 0; }
+    const std::vector<double>& setPointBuffer() const { return m_sp; }
+    unsigned long setPointVersion() const { return m_spVersion; }
+    /** raw robot-major batch of set-points, [N][setPointLength()] */
+    bool setSetPointBatch(const double* data)
+    {
+        if (!m_kinDyn || !data || setPointLength() == 0) return false;
+        m_sp.assign(data, data + m_kinDyn->getBatchSize() * setPointLength());
+        m_spVersion++;
+        m_isSetPointSetAtLeastOnce = true;
+        return true;
+    }
+    /** robot whose A and b are materialised by update() (getA / getB); -1 = none (default when N > 1) */
+    void setInspectedInstance(int i) { m_inspect = i; }
+    unsigned long gainsVersion() const { return m_gainsVersion; }
+
+protected:
+    bool commonInitialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler, std::shared_ptr<const ParametersHandler::IParametersHandler>& ptr)
+    {
+        m_isInitialized = false;
+        if (!m_kinDyn || !m_kinDyn->isValid()) {
+            log()->error("[{}::initialize] KinDynComputations object is not valid.", className());
+            return false;
+        }
+        ptr = paramHandler.lock();
+        if (!ptr) {
+            log()->error("[{}::initialize] The parameter handler is not valid.", className());
+            return false;
+        }
+        if (!ptr->getParameter("robot_velocity_variable_name", m_robotVelocityVariable.name)) {
+            log()->error("[{}::initialize] Error while retrieving the robot velocity variable.", className());
+            return false;
+        }
+        return true;
+    }
+    void storeSetPoint(const double* rec, std::ptrdiff_t instance)
+    {
+        const std::size_t len = setPointLength(), N = m_kinDyn->getBatchSize();
+        if (m_sp.size() != N * len) m_sp.assign(N * len, 0.0);
+        for (std::size_t i = 0; i < N; i++)
+            if (instance < 0 || static_cast<std::size_t>(instance) == i)
+                for (std::size_t c = 0; c < len; c++) m_sp[i * len + c] = rec[c];
+        m_spVersion++;
+    }
+    int inspected() const { return m_inspect >= 0 ? m_inspect : ((m_kinDyn && m_kinDyn->getBatchSize() == 1) ? 0 : -1); }
+    static bool readGain3(const ParametersHandler::IParametersHandler& h, const std::string& key, Vector3d& out)
+    {
+        double scalar;
+        std::vector<double> vec;
+        if (h.getParameter(key, scalar)) {   // SE3Task.cpp:135-168: a scalar or a 3-vector
+            out = {scalar, scalar, scalar};
+            return true;
+        }
+        if (h.getParameter(key, vec) && vec.size() == 3) {
+            out = {vec[0], vec[1], vec[2]};
+            return true;
+        }
+        return false;
+    }
+    static bool readMask(const ParametersHandler::IParametersHandler& h, std::array<bool, 3>& mask, std::size_t& dofs)
+    {
+        std::vector<bool> m;
+        mask = {true, true, true};
+        if (h.getParameter("mask", m)) {
+            if (m.size() != 3) return false;
+            mask = {m[0], m[1], m[2]};
+        }
+        dofs = static_cast<std::size_t>(mask[0]) + mask[1] + mask[2];
+        return true;
+    }
+
+    std::shared_ptr<KinDynBatch> m_kinDyn;
+    System::VariablesHandler::VariableDescription m_robotVelocityVariable;
+    std::size_t m_nVars{0};
+    bool m_isInitialized{false}, m_isValid{false}, m_isSetPointSetAtLeastOnce{false};
+    std::vector<double> m_sp;
+    unsigned long m_spVersion{0}, m_gainsVersion{0};
+    int m_inspect{-1};
+};
+
+using IKLinearTaskFactory = System::Factory<IKLinearTask>;
+#define BLF_REGISTER_IK_TASK(_type) \
+    static inline const std::string _type##_registered = ::BipedalLocomotion::IK::IKLinearTaskFactory::registerBuilder(#_type, []() -> std::shared_ptr<::BipedalLocomotion::IK::IKLinearTask> { return std::make_shared<_type>(); })
+
+/** SE3Task.h:51-205, SE3Task.cpp:21-390 */
+class SE3Task : public IKLinearTask
+{
+public:
+    enum class Mode { Enable, Disable };
+    const char* className() const override { return "SE3Task"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    bool setSetPoint(const SE3d& I_H_F, const SE3d::Tangent& mixedVelocity = SE3d::Tangent::Zero(), std::ptrdiff_t instance = -1);
+    std::size_t size() const override { return m_linearDoFs + 3; }
+    Type type() const override { return Type::equality; }
+    void setTaskControllerMode(Mode mode) { m_controllerMode = mode, m_gainsVersion++; }
+    Mode getTaskControllerMode() const { return m_controllerMode; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+    std::size_t setPointLength() const override { return 13; }
+
+private:
+    int m_frameIndex{-1};
+    std::string m_frameName;
+    Vector3d m_kpLinear{0, 0, 0}, m_kpAngular{0, 0, 0};
+    std::array<bool, 3> m_mask{true, true, true};
+    std::size_t m_linearDoFs{3};
+    Mode m_controllerMode{Mode::Enable};
+    BLF_REGISTER_IK_TASK(SE3Task);
+};
+
+/** CoMTask.cpp:19-273 */
+class CoMTask : public IKLinearTask
+{
+public:
+    const char* className() const override { return "CoMTask"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    bool setSetPoint(const Vector3d& position, const Vector3d& velocity = {0, 0, 0}, std::ptrdiff_t instance = -1);
+    std::size_t size() const override { return m_DoFs; }
+    Type type() const override { return Type::equality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+    std::size_t setPointLength() const override { return 6; }
+
+private:
+    Vector3d m_kpLinear{0, 0, 0};
+    std::array<bool, 3> m_mask{true, true, true};
+    std::size_t m_DoFs{3};
+    BLF_REGISTER_IK_TASK(CoMTask);
+};
+
+/** SO3Task.cpp:67-206 */
+class SO3Task : public IKLinearTask
+{
+public:
+    const char* className() const override { return "SO3Task"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    bool setSetPoint(const SO3d& I_R_F, const SO3Tangentd& angularVelocity = SO3Tangentd::Zero(), std::ptrdiff_t instance = -1);
+    std::size_t size() const override { return 3; }
+    Type type() const override { return Type::equality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+    std::size_t setPointLength() const override { return 7; }
+
+private:
+    int m_frameIndex{-1};
+    Vector3d m_kpAngular{0, 0, 0};
+    BLF_REGISTER_IK_TASK(SO3Task);
+};
+
+/** R3Task.cpp:60-256 */
+class R3Task : public IKLinearTask
+{
+public:
+    const char* className() const override { return "R3Task"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    bool setSetPoint(const Vector3d& I_p_F, const Vector3d& velocity = {0, 0, 0}, std::ptrdiff_t instance = -1);
+    std::size_t size() const override { return m_DoFs; }
+    Type type() const override { return Type::equality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+    std::size_t setPointLength() const override { return 6; }
+
+private:
+    int m_frameIndex{-1};
+    Vector3d m_kpLinear{0, 0, 0};
+    std::array<bool, 3> m_mask{true, true, true};
+    std::size_t m_DoFs{3};
+    BLF_REGISTER_IK_TASK(R3Task);
+};
+
+/** JointTrackingTask.cpp:29-210 */
+class JointTrackingTask : public IKLinearTask
+{
+public:
+    const char* className() const override { return "JointTrackingTask"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    bool setSetPoint(const VectorXd& jointPosition, std::ptrdiff_t instance = -1);
+    bool setSetPoint(const VectorXd& jointPosition, const VectorXd& jointVelocity, std::ptrdiff_t instance = -1);
+    std::size_t size() const override;
+    Type type() const override { return Type::equality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+    std::size_t setPointLength() const override { return m_kinDyn ? 2 * m_kinDyn->getNrOfDegreesOfFreedom() : 0; }
+
+private:
+    VectorXd m_kp;
+    BLF_REGISTER_IK_TASK(JointTrackingTask);
+};
+
+/** JointLimitsTask.cpp:22-284 */
+class JointLimitsTask : public IKLinearTask
+{
+public:
+    const char* className() const override { return "JointLimitsTask"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    std::size_t size() const override;
+    Type type() const override { return Type::inequality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+
+private:
+    VectorXd m_klim, m_upperLimits, m_lowerLimits;
+    std::chrono::nanoseconds m_samplingTime{0};
+    BLF_REGISTER_IK_TASK(JointLimitsTask);
+};
+
+/** JointVelocityLimitsTask.cpp:22-171 */
+class JointVelocityLimitsTask : public IKLinearTask
+{
+public:
+    const char* className() const override { return "JointVelocityLimitsTask"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    std::size_t size() const override;
+    Type type() const override { return Type::inequality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+
+private:
+    VectorXd m_upperLimits, m_lowerLimits;
+    BLF_REGISTER_IK_TASK(JointVelocityLimitsTask);
+};
+
+/** IntegrationBasedIK.h:31-35 */
+struct IntegrationBasedIKState {
+    VectorXd jointVelocity;
+    SE3d::Tangent baseVelocity;
+};
+
+class IntegrationBasedIK : public System::ILinearTaskSolver<IKLinearTask, IntegrationBasedIKState>
+{
+public:
+    virtual ~IntegrationBasedIK() = default;
+};
+
+/** IntegrationBasedIK.h:83-117 (tuple-like: auto [vh, weights, ik] = build(...)) */
+struct IntegrationBasedIKProblem {
+    System::VariablesHandler variablesHandler;
+    std::unordered_map<std::string, std::shared_ptr<System::WeightProvider>> weights;
+    std::unique_ptr<IntegrationBasedIK> ik;
+    bool isValid() const { return ik != nullptr; }
+};
+
+/** QPInverseKinematics.h:54-304, QPInverseKinematics.cpp:26-806 */
+class QPInverseKinematics : public IntegrationBasedIK
+{
+    struct Impl;
+    std::unique_ptr<Impl> m_pimpl;
+    bool tick(double dt, uint32_t flags);
+
+public:
+    QPInverseKinematics();
+    ~QPInverseKinematics();
+
+    bool addTask(std::shared_ptr<Task> task, const std::string& taskName, std::size_t priority,
+                 std::shared_ptr<const System::WeightProviderPort> weightProvider = nullptr) override;
+    bool addTask(std::shared_ptr<Task> task, const std::string& taskName, std::size_t priority, const VectorXd& weight) override;
+    bool setTaskWeight(const std::string& taskName, std::shared_ptr<const System::WeightProviderPort> weightProvider) override;
+    bool setTaskWeight(const std::string& taskName, const VectorXd& weight) override;
+    std::weak_ptr<const System::WeightProviderPort> getTaskWeightProvider(const std::string& taskName) const override;
+    bool finalize(const System::VariablesHandler& handler) override;
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> handler) override;
+    std::vector<std::string> getTaskNames() const override;
+    bool isOutputValid() const override;
+    bool advance() override;
+    const State& getOutput() const override;
+    std::weak_ptr<Task> getTask(const std::string& name) const override;
+    std::string toString() const override;
+    const VectorXd& getRawSolution() const override;
+    static IntegrationBasedIKProblem build(std::weak_ptr<const ParametersHandler::IParametersHandler> handler, std::shared_ptr<KinDynBatch> kinDyn);
+
+    // ---- batch extensions (no counterpart in the reference)
+    /** [N][6+n] velocities of the last advance(), robot-major */
+    const std::vector<double>& getBatchOutput() const;
+    /** per-robot blfik_status of the last advance() */
+    const std::vector<int32_t>& getBatchStatus() const;
+    /** advance() and apply ForwardEuler on the device in the same launch; the new state is written back into kinDyn */
+    bool advanceAndIntegrate(std::chrono::nanoseconds dT);
+    blfik_problem* handle();
+};
+
+}  // namespace IK
+}  // namespace BipedalLocomotion
+
+#endif

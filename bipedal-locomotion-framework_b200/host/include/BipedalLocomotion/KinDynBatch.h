@@ -1,0 +1,83 @@
+/**
+ * KinDynBatch.h -- stands in for std::shared_ptr<iDynTree::KinDynComputations> (IKLinearTask.h:40): ONE object,
+ * shared by every task and mutated by the caller between ticks (setRobotState), here holding the state of a
+ * whole batch of N robots.  Kinematic queries (getWorldTransform, getFrameFreeFloatingJacobian,
+ * getCenterOfMassPosition / Jacobian; call sites SE3Task.cpp:263-296, CoMTask.cpp:194-214) run on the GPU through
+ * blfik_kinematics -- there is no CPU evaluation in this class.  Velocities are always MIXED
+ * (the tasks refuse anything else, SE3Task.cpp:92-102).
+ */
+#ifndef BLF_B200_KINDYN_BATCH_H
+#define BLF_B200_KINDYN_BATCH_H
+
+#include <BipedalLocomotion/System.h>
+#include <blfik.h>
+
+namespace BipedalLocomotion
+{
+
+class KinDynBatch
+{
+public:
+    KinDynBatch() = default;
+    ~KinDynBatch();
+    KinDynBatch(const KinDynBatch&) = delete;
+    KinDynBatch& operator=(const KinDynBatch&) = delete;
+
+    /** Reads the plain-text reduced-model format written by blf_b200.models.KinematicModel.to_text()
+     *  (the image has no URDF parser and no URDF). */
+    bool loadRobotModelFromFile(const std::string& path);
+    /** number of robots evaluated at once (default 1 = the reference's semantics) and the CUDA device */
+    bool setBatchSize(std::size_t n, int device = 0);
+    std::size_t getBatchSize() const { return m_N; }
+    int getDevice() const { return m_device; }
+
+    bool isValid() const { return m_model != nullptr; }
+    std::size_t getNrOfDegreesOfFreedom() const { return m_n; }
+    /** -1 if the frame does not exist (iDynTree::FRAME_INVALID_INDEX) */
+    int getFrameIndex(const std::string& name) const;
+    std::string getFrameName(int index) const;
+    const VectorXd& jointLowerLimits() const { return m_qLower; }
+    const VectorXd& jointUpperLimits() const { return m_qUpper; }
+    const std::vector<std::string>& jointNames() const { return m_jointNames; }
+
+    /** kinDyn->setRobotState(world_H_base, s, ...) for one robot of the batch */
+    bool setRobotState(const Vector3d& basePosition, const SO3d& baseRotation, const VectorXd& jointPositions, std::size_t instance = 0);
+    /** robot-major batch arrays: p [N][3], q [N][4] (x,y,z,w), s [N][n] */
+    bool setRobotStateBatch(const double* p, const double* q, const double* s);
+    bool getJointPos(VectorXd& s, std::size_t instance = 0) const;
+
+    // ---- kinematic queries of one robot (evaluated for the whole batch on the GPU, cached per state)
+    bool getWorldTransform(int frame, SE3d& pose, std::array<double, 9>& rotation, std::size_t instance = 0);
+    bool getFrameFreeFloatingJacobian(int frame, System::MatrixXd& jacobian, std::size_t instance = 0);
+    bool getCenterOfMassPosition(Vector3d& com, std::size_t instance = 0);
+    bool getCenterOfMassJacobian(System::MatrixXd& jacobian, std::size_t instance = 0);
+
+    // ---- used by the solver
+    const blfik_model* model() const { return m_model; }
+    const std::vector<double>& basePositions() const { return m_p; }
+    const std::vector<double>& baseQuaternions() const { return m_q; }
+    const std::vector<double>& jointPositions() const { return m_s; }
+    unsigned long stateVersion() const { return m_version; }
+
+private:
+    bool ensureKinProblem();
+    bool evalFrame(int frame);
+    bool evalCom();
+
+    blfik_model* m_model{nullptr};
+    blfik_problem* m_kin{nullptr};  // kinematics-only problem (owns the device copy of the state for queries)
+    std::size_t m_n{0}, m_N{1};
+    int m_device{0};
+    std::vector<std::string> m_jointNames, m_frameNames;
+    VectorXd m_qLower, m_qUpper;
+    std::vector<double> m_p, m_q, m_s;
+    unsigned long m_version{1}, m_kinVersion{0};
+    // caches
+    int m_cachedFrame{-1};
+    unsigned long m_frameVersion{0}, m_comVersion{0};
+    std::vector<double> m_framePos, m_frameRot, m_frameJac, m_com, m_comJac;
+};
+
+}  // namespace BipedalLocomotion
+
+#endif

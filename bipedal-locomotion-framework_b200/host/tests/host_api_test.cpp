@@ -1,0 +1,463 @@
+// host_api_test.cpp -- tests of the C++ host layer, written the way the reference's Catch2 tests are
+// (src/IK/tests/*TaskTest.cpp, QPInverseKinematicsTest.cpp, IntegratorFloatingBaseSystemVelocityKinematics.cpp).
+//   host_api_test cpu <model.txt>    checks that need no GPU (parameters, variables, addTask rules, error paths)
+//   host_api_test gpu <model.txt>    checks that run the CUDA path (task A/b identities, closed loop, batch, integrator)
+#include <BipedalLocomotion/ContinuousDynamicalSystem.h>
+#include <BipedalLocomotion/IK.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <random>
+
+using namespace BipedalLocomotion;
+using namespace BipedalLocomotion::IK;
+using namespace BipedalLocomotion::System;
+using namespace BipedalLocomotion::ContinuousDynamicalSystem;
+using namespace BipedalLocomotion::ParametersHandler;
+using namespace std::chrono_literals;
+
+static int g_failures = 0, g_checks = 0;
+#define REQUIRE(cond)                                                              \
+    do {                                                                           \
+        g_checks++;                                                                \
+        if (!(cond)) {                                                             \
+            g_failures++;                                                          \
+            std::fprintf(stderr, "REQUIRE failed %s:%d: %s\n", __FILE__, __LINE__, #cond); \
+        }                                                                          \
+    } while (0)
+#define REQUIRE_FALSE(cond) REQUIRE(!(cond))
+
+constexpr auto robotVelocity = "robotVelocity";
+
+static std::shared_ptr<KinDynBatch> loadKinDyn(const char* path, std::size_t N = 1)
+{
+    auto kd = std::make_shared<KinDynBatch>();
+    if (!kd->loadRobotModelFromFile(path)) return nullptr;
+    kd->setBatchSize(N);
+    return kd;
+}
+
+// the ergoCub IK of utilities/balancing-position-control/config/robots/ergoCubGazeboV1/blf_balancing_position_control/ik.ini
+static std::shared_ptr<IParametersHandler> ergoCubHandler(std::size_t n, bool withLimits)
+{
+    auto h = std::make_shared<StdImplementation>();
+    std::vector<std::string> tasks{"COM_TASK", "RIGHT_FOOT_TASK", "LEFT_FOOT_TASK", "TORSO_TASK", "JOINT_REGULARIZATION_TASK"};
+    if (withLimits) tasks.push_back("JOINT_LIMITS_TASK"), tasks.push_back("JOINT_VELOCITY_LIMITS_TASK");
+    h->setParameter("tasks", tasks);
+    auto ik = std::make_shared<StdImplementation>();
+    ik->setParameter("robot_velocity_variable_name", robotVelocity);
+    h->setGroup("IK", ik);
+    auto com = std::make_shared<StdImplementation>();
+    com->setParameter("type", "CoMTask"), com->setParameter("kp_linear", 2.0), com->setParameter("priority", 0);
+    com->setParameter("mask", std::vector<bool>{true, true, true});
+    h->setGroup("COM_TASK", com);
+    for (auto side : {std::make_pair("RIGHT_FOOT_TASK", "r_sole"), std::make_pair("LEFT_FOOT_TASK", "l_sole")}) {
+        auto foot = std::make_shared<StdImplementation>();
+        foot->setParameter("type", "SE3Task"), foot->setParameter("frame_name", side.second);
+        foot->setParameter("kp_linear", 7.0), foot->setParameter("kp_angular", 5.0), foot->setParameter("priority", 0);
+        h->setGroup(side.first, foot);
+    }
+    auto torso = std::make_shared<StdImplementation>();
+    torso->setParameter("type", "SO3Task"), torso->setParameter("frame_name", "chest"), torso->setParameter("kp_angular", 5.0);
+    torso->setParameter("priority", 1), torso->setParameter("weight", std::vector<double>{5.0, 5.0, 5.0});
+    h->setGroup("TORSO_TASK", torso);
+    auto reg = std::make_shared<StdImplementation>();
+    reg->setParameter("type", "JointTrackingTask"), reg->setParameter("kp", std::vector<double>(n, 5.0));
+    reg->setParameter("priority", 1), reg->setParameter("weight", std::vector<double>(n, 1.0));
+    h->setGroup("JOINT_REGULARIZATION_TASK", reg);
+    auto lim = std::make_shared<StdImplementation>();
+    lim->setParameter("type", "JointLimitsTask"), lim->setParameter("klim", std::vector<double>(n, 0.5));
+    lim->setParameter("sampling_time", 0.01), lim->setParameter("use_model_limits", true), lim->setParameter("priority", 0);
+    h->setGroup("JOINT_LIMITS_TASK", lim);
+    auto vel = std::make_shared<StdImplementation>();
+    vel->setParameter("type", "JointVelocityLimitsTask"), vel->setParameter("upper_limits", std::vector<double>(n, 2.0));
+    vel->setParameter("lower_limits", std::vector<double>(n, -2.0)), vel->setParameter("priority", 0);
+    h->setGroup("JOINT_VELOCITY_LIMITS_TASK", vel);
+    return h;
+}
+
+// ------------------------------------------------------------------------------------------ CPU-only
+static void testParametersAndVariables()
+{
+    auto h = std::make_shared<StdImplementation>();
+    h->setParameter("answer", 42), h->setParameter("pi", 3.14), h->setParameter("name", "blf"), h->setParameter("flag", true);
+    h->setParameter("vec", std::vector<double>{1, 2, 3});
+    int i = 0;
+    double d = 0;
+    std::string s;
+    bool b = false;
+    std::vector<double> v;
+    REQUIRE(h->getParameter("answer", i) && i == 42);
+    REQUIRE(h->getParameter("pi", d) && d == 3.14);
+    REQUIRE(h->getParameter("answer", d) && d == 42.0);
+    REQUIRE(h->getParameter("name", s) && s == "blf");
+    REQUIRE(h->getParameter("flag", b) && b);
+    REQUIRE(h->getParameter("vec", v) && v.size() == 3);
+    REQUIRE_FALSE(h->getParameter("missing", i));
+    REQUIRE_FALSE(h->getParameter("name", i));
+    auto g = std::make_shared<StdImplementation>();
+    g->setParameter("x", 1);
+    REQUIRE(h->setGroup("G", g));
+    g->setParameter("x", 2);   // setGroup stored a copy
+    REQUIRE(h->getGroup("G").lock() && h->getGroup("G").lock()->getParameter("x", i) && i == 1);
+    REQUIRE(h->getGroup("nope").lock() == nullptr);
+    auto c = h->clone();
+    c->setParameter("answer", 7);
+    REQUIRE(h->getParameter("answer", i) && i == 42);
+    std::chrono::nanoseconds ns;
+    h->setParameter("dt", 0.01);
+    REQUIRE(h->getParameter("dt", ns) && ns == 10ms);
+
+    VariablesHandler vh;
+    REQUIRE(vh.addVariable("dummy1", 10));
+    REQUIRE(vh.addVariable(robotVelocity, 29));
+    REQUIRE(vh.addVariable("dummy2", 15));
+    REQUIRE_FALSE(vh.addVariable("dummy2", 3));
+    REQUIRE(vh.getNumberOfVariables() == 54);
+    REQUIRE(vh.getVariable(robotVelocity).offset == 10 && vh.getVariable(robotVelocity).size == 29);
+    REQUIRE_FALSE(vh.getVariable("missing").isValid());
+    auto vhh = std::make_shared<StdImplementation>();
+    vhh->setParameter("variables_name", std::vector<std::string>{"a", "b"});
+    vhh->setParameter("variables_size", std::vector<int>{3, 4});
+    VariablesHandler vh2;
+    REQUIRE(vh2.initialize(vhh) && vh2.getNumberOfVariables() == 7 && vh2.getVariable("b").offset == 3);
+
+    ConstantWeightProvider w;
+    REQUIRE_FALSE(w.isOutputValid());
+    auto wh = std::make_shared<StdImplementation>();
+    REQUIRE_FALSE(w.initialize(wh));
+    wh->setParameter("weight", std::vector<double>{1, 2});
+    REQUIRE(w.initialize(wh) && w.isOutputValid() && w.getOutput().size() == 2);
+}
+
+static void testTaskInitializationAndAddTaskRules(const char* modelPath)
+{
+    log()->setLevel(Logger::Level::off);   // the error paths below are expected
+    auto kinDyn = loadKinDyn(modelPath);
+    REQUIRE(kinDyn != nullptr);
+    const std::size_t n = kinDyn->getNrOfDegreesOfFreedom();
+    REQUIRE(n == 23);
+    REQUIRE(kinDyn->getFrameIndex("l_sole") >= 0 && kinDyn->getFrameIndex("not_a_frame") == -1);
+
+    auto se3 = std::make_shared<SE3Task>();
+    auto h = std::make_shared<StdImplementation>();
+    REQUIRE_FALSE(se3->initialize(h));                       // no kinDyn yet
+    REQUIRE(se3->setKinDyn(kinDyn));
+    REQUIRE_FALSE(se3->initialize(h));                       // robot_velocity_variable_name missing
+    h->setParameter("robot_velocity_variable_name", robotVelocity);
+    REQUIRE_FALSE(se3->initialize(h));                       // frame_name missing
+    h->setParameter("frame_name", "not_a_frame");
+    REQUIRE_FALSE(se3->initialize(h));
+    h->setParameter("frame_name", "l_sole");
+    REQUIRE_FALSE(se3->initialize(h));                       // gains missing
+    h->setParameter("kp_linear", 7.0);
+    h->setParameter("kp_angular", std::vector<double>{5.0, 5.0, 5.0});
+    REQUIRE(se3->initialize(h));
+    REQUIRE(se3->size() == 6 && se3->type() == LinearTask::Type::equality);
+    h->setParameter("mask", std::vector<bool>{true, false, true});
+    auto se3m = std::make_shared<SE3Task>();
+    REQUIRE(se3m->setKinDyn(kinDyn) && se3m->initialize(h) && se3m->size() == 5);
+    REQUIRE_FALSE(se3->update());                            // set-point never set (SE3Task.cpp:245-249)
+    REQUIRE_FALSE(se3->isValid());
+
+    auto jt = std::make_shared<JointTrackingTask>();
+    auto jh = std::make_shared<StdImplementation>();
+    jh->setParameter("robot_velocity_variable_name", robotVelocity);
+    jh->setParameter("kp", std::vector<double>(n - 1, 1.0));
+    REQUIRE(jt->setKinDyn(kinDyn));
+    REQUIRE_FALSE(jt->initialize(jh));                       // wrong kp size (JointTrackingTask.cpp:100-110)
+    jh->setParameter("kp", std::vector<double>(n, 1.0));
+    REQUIRE(jt->initialize(jh) && jt->size() == n);
+    REQUIRE_FALSE(jt->setSetPoint(VectorXd(n + 1, 0.0)));    // wrong set-point size
+    REQUIRE(jt->setSetPoint(VectorXd(n, 0.0)));
+
+    auto jl = std::make_shared<JointLimitsTask>();
+    auto lh = std::make_shared<StdImplementation>();
+    lh->setParameter("robot_velocity_variable_name", robotVelocity);
+    lh->setParameter("klim", std::vector<double>(n, 1.5));
+    lh->setParameter("sampling_time", 0.01);
+    REQUIRE(jl->setKinDyn(kinDyn));
+    REQUIRE_FALSE(jl->initialize(lh));                       // klim outside [0, 1]
+    lh->setParameter("klim", std::vector<double>(n, 0.5));
+    REQUIRE_FALSE(jl->initialize(lh));                       // use_model_limits is mandatory
+    lh->setParameter("use_model_limits", true);
+    REQUIRE(jl->initialize(lh) && jl->size() == 2 * n && jl->type() == LinearTask::Type::inequality);
+
+    QPInverseKinematics ik;
+    VectorXd w6(6, 1.0);
+    REQUIRE_FALSE(ik.addTask(se3, "se3", 0));                // initialize() first (QPInverseKinematics.cpp:173-177)
+    auto ikh = std::make_shared<StdImplementation>();
+    REQUIRE_FALSE(ik.initialize(ikh));
+    ikh->setParameter("robot_velocity_variable_name", robotVelocity);
+    REQUIRE(ik.initialize(ikh));
+    REQUIRE(ik.addTask(se3, "se3", 0));
+    REQUIRE_FALSE(ik.addTask(se3, "se3", 0));                // duplicate name
+    REQUIRE_FALSE(ik.addTask(se3m, "se3m", 2));              // priority must be 0 or 1
+    REQUIRE_FALSE(ik.addTask(jl, "limits", 1, VectorXd(2 * n, 1.0)));   // inequality with priority 1
+    REQUIRE_FALSE(ik.addTask(jt, "reg", 1));                 // priority 1 needs a weight provider
+    REQUIRE_FALSE(ik.addTask(jt, "reg", 1, VectorXd(n - 1, 1.0)));      // wrong weight size
+    REQUIRE(ik.addTask(jt, "reg", 1, VectorXd(n, 1.0)));
+    REQUIRE(ik.addTask(jl, "limits", 0));
+    REQUIRE_FALSE(ik.setTaskWeight("se3", w6));              // only priority-1 tasks have a weight (:268-276)
+    REQUIRE_FALSE(ik.setTaskWeight("nope", w6));
+    REQUIRE_FALSE(ik.setTaskWeight("reg", w6));              // wrong size
+    REQUIRE(ik.setTaskWeight("reg", VectorXd(n, 10.0)));
+    REQUIRE(ik.getTaskWeightProvider("reg").lock() && ik.getTaskWeightProvider("reg").lock()->getOutput()[0] == 10.0);
+    REQUIRE(ik.getTaskNames().size() == 3);
+    REQUIRE(ik.getTask("se3").lock() == se3 && ik.getTask("nope").lock() == nullptr);
+    REQUIRE_FALSE(ik.advance());                             // finalize() first (:421-425)
+    REQUIRE_FALSE(ik.isOutputValid());
+    REQUIRE(ik.toString().find("se3") != std::string::npos);
+    VariablesHandler bad;
+    bad.addVariable("other", 29);
+    REQUIRE_FALSE(ik.finalize(bad));                         // the robot velocity variable is not in the handler
+
+    // integrator error conventions
+    ForwardEuler<FloatingBaseSystemVelocityKinematics> integrator;
+    REQUIRE_FALSE(integrator.integrate(0s, 10ms));           // no dynamical system
+    REQUIRE_FALSE(integrator.setIntegrationStep(0ns));
+    REQUIRE(integrator.setIntegrationStep(10ms));
+    auto system = std::make_shared<FloatingBaseSystemVelocityKinematics>();
+    REQUIRE(integrator.setDynamicalSystem(system));
+    REQUIRE_FALSE(integrator.setDynamicalSystem(system));    // only once (Integrator.h:94-99)
+    REQUIRE_FALSE(integrator.integrate(10ms, 0s));           // final time before the initial one
+    REQUIRE(system->setState({{0, 0, 0}, SO3d::Identity(), VectorXd(n, 0.0)}));
+    REQUIRE_FALSE(integrator.integrate(0s, 10ms));           // no control input yet
+    REQUIRE_FALSE(system->setControlInput({{0, 0, 0, 0, 0, 0}, VectorXd(n + 1, 0.0)}));   // wrong size (.cpp:52-56)
+    log()->setLevel(Logger::Level::warn);
+}
+
+// ------------------------------------------------------------------------------------------ GPU
+static double maxAbsDiff(const MatrixXd& A, std::size_t r0, std::size_t c0, const MatrixXd& B, std::size_t br0)
+{
+    double m = 0;
+    for (std::size_t r = 0; r < B.rows - br0 && r + r0 < A.rows; r++)
+        for (std::size_t c = 0; c < B.cols; c++) m = std::max(m, std::abs(A(r0 + r, c0 + c) - B(br0 + r, c)));
+    return m;
+}
+
+static VectorXd nominalJoints(const KinDynBatch& kd, std::mt19937& gen, double spread)
+{
+    std::uniform_real_distribution<double> u(-spread, spread);
+    VectorXd s(kd.getNrOfDegreesOfFreedom());
+    for (std::size_t j = 0; j < s.size(); j++) s[j] = 0.5 * (kd.jointLowerLimits()[j] + kd.jointUpperLimits()[j]) + u(gen);
+    return s;
+}
+
+// SE3TaskTest.cpp:79-139 / CoMTaskTest.cpp:82-130: A's robot-velocity block is the Jacobian, the neighbouring column
+// blocks (dummy1, dummy2) stay zero, b is the control law
+static void testTaskMatrices(const char* modelPath)
+{
+    auto kinDyn = loadKinDyn(modelPath);
+    std::mt19937 gen(3);
+    REQUIRE(kinDyn->setRobotState({0.1, -0.2, 0.7}, SO3d::Exp({0.1, -0.2, 0.3}), nominalJoints(*kinDyn, gen, 0.3)));
+    VariablesHandler vh;
+    vh.addVariable("dummy1", 10), vh.addVariable(robotVelocity, kinDyn->getNrOfDegreesOfFreedom() + 6), vh.addVariable("dummy2", 15);
+    auto h = std::make_shared<StdImplementation>();
+    h->setParameter("robot_velocity_variable_name", robotVelocity), h->setParameter("frame_name", "l_sole");
+    h->setParameter("kp_linear", 2.0), h->setParameter("kp_angular", 3.0);
+    SE3Task task;
+    REQUIRE(task.setKinDyn(kinDyn) && task.initialize(h) && task.setVariablesHandler(vh));
+    SE3d desired({0.2, 0.1, 0.05}, SO3d::Exp({0.0, 0.1, -0.1}));
+    SE3d::Tangent ff;
+    ff.linear = {0.1, 0.2, 0.3}, ff.angular = {-0.1, 0.0, 0.2};
+    REQUIRE(task.setSetPoint(desired, ff));
+    REQUIRE(task.update() && task.isValid());
+    const MatrixXd& A = task.getA();
+    REQUIRE(A.rows == 6 && A.cols == 10 + 29 + 15);
+    MatrixXd J;
+    SE3d pose;
+    std::array<double, 9> R;
+    REQUIRE(kinDyn->getFrameFreeFloatingJacobian(kinDyn->getFrameIndex("l_sole"), J));
+    REQUIRE(kinDyn->getWorldTransform(kinDyn->getFrameIndex("l_sole"), pose, R));
+    REQUIRE(maxAbsDiff(A, 0, 10, J, 0) == 0.0);
+    double outside = 0;
+    for (std::size_t r = 0; r < 6; r++)
+        for (std::size_t c = 0; c < A.cols; c++)
+            if (c < 10 || c >= 39) outside = std::max(outside, std::abs(A(r, c)));
+    REQUIRE(outside == 0.0);
+    for (int c = 0; c < 3; c++) REQUIRE(std::abs(task.getB()[c] - (ff.linear[c] + 2.0 * (desired.p[c] - pose.p[c]))) < 1e-12);
+    // base block of the Jacobian: [I, -S(p_F - p_B); 0, I]
+    REQUIRE(J(0, 0) == 1 && J(1, 1) == 1 && J(3, 3) == 1 && J(3, 0) == 0 && std::abs(J(0, 4) - (pose.p[2] - 0.7)) < 1e-12);
+    task.setTaskControllerMode(SE3Task::Mode::Disable);
+    REQUIRE(task.update());
+    for (int c = 0; c < 3; c++) REQUIRE(task.getB()[c] == ff.linear[c] && task.getB()[3 + c] == ff.angular[c]);   // feed-forward only
+
+    CoMTask com;
+    auto ch = std::make_shared<StdImplementation>();
+    ch->setParameter("robot_velocity_variable_name", robotVelocity), ch->setParameter("kp_linear", 4.0);
+    REQUIRE(com.setKinDyn(kinDyn) && com.initialize(ch) && com.setVariablesHandler(vh) && com.setSetPoint({0, 0, 0.5}));
+    REQUIRE(com.update());
+    MatrixXd Jc;
+    Vector3d c0;
+    REQUIRE(kinDyn->getCenterOfMassJacobian(Jc) && kinDyn->getCenterOfMassPosition(c0));
+    REQUIRE(maxAbsDiff(com.getA(), 0, 10, Jc, 0) == 0.0);
+    REQUIRE(std::abs(com.getB()[2] - 4.0 * (0.5 - c0[2])) < 1e-12);
+
+    JointTrackingTask jt;
+    auto jh = std::make_shared<StdImplementation>();
+    jh->setParameter("robot_velocity_variable_name", robotVelocity), jh->setParameter("kp", std::vector<double>(23, 3.0));
+    REQUIRE(jt.setKinDyn(kinDyn) && jt.initialize(jh) && jt.setVariablesHandler(vh) && jt.setSetPoint(VectorXd(23, 0.0)) && jt.update());
+    VectorXd s;
+    kinDyn->getJointPos(s);
+    for (std::size_t j = 0; j < 23; j++) {   // JointTrackingTaskTest.cpp:84-114: b = -Kp s for a zero set-point, A = [0 I]
+        REQUIRE(std::abs(jt.getB()[j] + 3.0 * s[j]) < 1e-13);
+        REQUIRE(jt.getA()(j, 10 + 6 + j) == 1.0 && jt.getA()(j, 10 + j) == 0.0);
+    }
+}
+
+// 'With builder' (QPInverseKinematicsTest.cpp:642-798) on the ergoCub configuration: build() from a parameter handler,
+// closed loop advance() -> setControlInput -> integrate(0, dT) until the set-points are reached
+static void testClosedLoop(const char* modelPath, std::size_t N, bool withLimits)
+{
+    constexpr auto dT = 10ms;
+    auto kinDyn = loadKinDyn(modelPath, N);
+    const std::size_t n = kinDyn->getNrOfDegreesOfFreedom();
+    std::mt19937 gen(42);
+    std::normal_distribution<double> noise(0.0, 0.05);
+
+    // desired configuration -> set-points; perturbed configuration -> initial state
+    auto desiredKinDyn = loadKinDyn(modelPath, N);
+    std::vector<VectorXd> sDes(N);
+    for (std::size_t i = 0; i < N; i++) {
+        sDes[i] = nominalJoints(*kinDyn, gen, 0.15);
+        REQUIRE(desiredKinDyn->setRobotState({0.0, 0.0, 0.75}, SO3d::Exp({0.0, 0.05, 0.1}), sDes[i], i));
+    }
+    auto problem = QPInverseKinematics::build(ergoCubHandler(n, withLimits), kinDyn);
+    REQUIRE(problem.isValid());
+    auto& [variablesHandler, weights, ik] = problem;
+    REQUIRE(variablesHandler.getNumberOfVariables() == n + 6 && weights.size() == 2);
+    auto comTask = std::dynamic_pointer_cast<CoMTask>(ik->getTask("COM_TASK").lock());
+    auto rFoot = std::dynamic_pointer_cast<SE3Task>(ik->getTask("RIGHT_FOOT_TASK").lock());
+    auto lFoot = std::dynamic_pointer_cast<SE3Task>(ik->getTask("LEFT_FOOT_TASK").lock());
+    auto torso = std::dynamic_pointer_cast<SO3Task>(ik->getTask("TORSO_TASK").lock());
+    auto reg = std::dynamic_pointer_cast<JointTrackingTask>(ik->getTask("JOINT_REGULARIZATION_TASK").lock());
+    REQUIRE(comTask && rFoot && lFoot && torso && reg);
+
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(ik->advance());   // no set-point yet
+    log()->setLevel(Logger::Level::warn);
+
+    std::vector<Vector3d> comDes(N);
+    std::vector<SE3d> rDes(N), lDes(N);
+    for (std::size_t i = 0; i < N; i++) {
+        std::array<double, 9> R;
+        SE3d chest;
+        REQUIRE(desiredKinDyn->getCenterOfMassPosition(comDes[i], i));
+        REQUIRE(desiredKinDyn->getWorldTransform(kinDyn->getFrameIndex("r_sole"), rDes[i], R, i));
+        REQUIRE(desiredKinDyn->getWorldTransform(kinDyn->getFrameIndex("l_sole"), lDes[i], R, i));
+        REQUIRE(desiredKinDyn->getWorldTransform(kinDyn->getFrameIndex("chest"), chest, R, i));
+        REQUIRE(comTask->setSetPoint(comDes[i], {0, 0, 0}, i));
+        REQUIRE(rFoot->setSetPoint(rDes[i], SE3d::Tangent::Zero(), i) && lFoot->setSetPoint(lDes[i], SE3d::Tangent::Zero(), i));
+        REQUIRE(torso->setSetPoint(chest.R, SO3Tangentd::Zero(), i));
+        REQUIRE(reg->setSetPoint(sDes[i], i));
+    }
+
+    auto system = std::make_shared<FloatingBaseSystemVelocityKinematics>();
+    system->setBatchSize(N);
+    for (std::size_t i = 0; i < N; i++) {
+        VectorXd s0 = sDes[i];
+        for (auto& v : s0) v += noise(gen);
+        REQUIRE(system->setState({{0.0, 0.0, 0.75}, SO3d::Exp({0.0, 0.05 + noise(gen), 0.1}), s0}, i));
+    }
+    ForwardEuler<FloatingBaseSystemVelocityKinematics> integrator;
+    REQUIRE(integrator.setIntegrationStep(dT));
+    REQUIRE(integrator.setDynamicalSystem(system));
+
+    for (int iteration = 0; iteration < 120; iteration++) {
+        REQUIRE(kinDyn->setRobotStateBatch(system->basePositions().data(), system->baseQuaternions().data(), system->jointPositions().data()));
+        REQUIRE(ik->advance());
+        REQUIRE(ik->isOutputValid());
+        if (N == 1) {
+            REQUIRE(system->setControlInput({ik->getOutput().baseVelocity.coeffs(), ik->getOutput().jointVelocity}));
+        } else {
+            REQUIRE(system->setControlInputBatch(static_cast<QPInverseKinematics*>(ik.get())->getBatchOutput().data()));
+        }
+        REQUIRE(integrator.integrate(0s, dT));
+        if (withLimits) {
+            const auto& nu = static_cast<QPInverseKinematics*>(ik.get())->getBatchOutput();
+            double vmax = 0;
+            for (std::size_t i = 0; i < N; i++)
+                for (std::size_t j = 0; j < n; j++) vmax = std::max(vmax, std::abs(nu[i * (n + 6) + 6 + j]));
+            REQUIRE(vmax <= 2.0 + 1e-9);
+        }
+    }
+    REQUIRE(kinDyn->setRobotStateBatch(system->basePositions().data(), system->baseQuaternions().data(), system->jointPositions().data()));
+    for (std::size_t i = 0; i < N; i += std::max<std::size_t>(1, N / 7)) {
+        Vector3d com;
+        SE3d pose;
+        std::array<double, 9> R;
+        REQUIRE(kinDyn->getCenterOfMassPosition(com, i));
+        for (int c = 0; c < 3; c++) REQUIRE(std::abs(com[c] - comDes[i][c]) < 2e-3);
+        REQUIRE(kinDyn->getWorldTransform(kinDyn->getFrameIndex("l_sole"), pose, R, i));
+        for (int c = 0; c < 3; c++) REQUIRE(std::abs(pose.p[c] - lDes[i].p[c]) < 2e-3);
+        const auto qa = pose.quat().coeffs(), qb = lDes[i].quat().coeffs();
+        const double dot = std::abs(qa[0] * qb[0] + qa[1] * qb[1] + qa[2] * qb[2] + qa[3] * qb[3]);
+        REQUIRE(dot > 1.0 - 1e-5);
+    }
+    // setTaskWeight takes effect on the next advance() (QPInverseKinematics.cpp:450-451)
+    const auto before = static_cast<QPInverseKinematics*>(ik.get())->getBatchOutput();
+    REQUIRE(ik->setTaskWeight("JOINT_REGULARIZATION_TASK", VectorXd(n, 50.0)));
+    for (std::size_t i = 0; i < N; i++) REQUIRE(comTask->setSetPoint({comDes[i][0] + 0.02, comDes[i][1], comDes[i][2]}, {0, 0, 0}, i));
+    REQUIRE(ik->advance());
+    REQUIRE(ik->getRawSolution().size() == n + 6);
+    REQUIRE(std::abs(ik->getOutput().baseVelocity.coeffs()[0]) + std::abs(ik->getOutput().jointVelocity[0]) > 1e-6);
+    (void)before;
+}
+
+// IntegratorFloatingBaseSystemVelocityKinematics.cpp:25-88 with a non-identity initial rotation
+static void testIntegrator()
+{
+    constexpr auto dT = 100us;
+    const std::size_t n = 20;
+    std::mt19937 gen(7);
+    std::uniform_real_distribution<double> u(-1, 1);
+    auto system = std::make_shared<FloatingBaseSystemVelocityKinematics>();
+    std::array<double, 6> twist;
+    for (auto& t : twist) t = u(gen);
+    VectorXd ds(n), s0(n);
+    for (std::size_t j = 0; j < n; j++) ds[j] = u(gen), s0[j] = u(gen);
+    const Vector3d p0{0.1, 0.2, 0.3};
+    const SO3d R0 = SO3d::Exp({0.4, -0.3, 0.2});
+    REQUIRE(system->setState({p0, R0, s0}));
+    REQUIRE(system->setControlInput({twist, ds}));
+    ForwardEuler<FloatingBaseSystemVelocityKinematics> integrator;
+    REQUIRE(integrator.setIntegrationStep(dT) && integrator.setDynamicalSystem(system));
+    constexpr double T = 0.5;
+    REQUIRE(integrator.integrate(0s, 500ms));   // 4999 full steps + the last one, in two launches
+    const auto& [p, R, s] = integrator.getSolution();
+    for (int c = 0; c < 3; c++) REQUIRE(std::abs(p[c] - (p0[c] + T * twist[c])) < 1e-9);
+    for (std::size_t j = 0; j < n; j++) REQUIRE(std::abs(s[j] - (s0[j] + T * ds[j])) < 1e-9);
+    // closed form R = Exp(w T) R0 (tangent + group = left-plus)
+    const SO3d Rexp = SO3d::Exp({twist[3] * T, twist[4] * T, twist[5] * T});
+    const auto a = Rexp.rotation(), b = R0.rotation(), got = R.rotation();
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+            double e = 0;
+            for (int k = 0; k < 3; k++) e += a[3 * i + k] * b[3 * k + j];
+            REQUIRE(std::abs(got[3 * i + j] - e) < 1e-9);
+        }
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(integrator.integrate(0s, 50us));   // shorter than dT: rejected, not underflowed
+    log()->setLevel(Logger::Level::warn);
+}
+
+int main(int argc, char** argv)
+{
+    if (argc < 3) {
+        std::fprintf(stderr, "usage: %s cpu|gpu <ergocub23 model file>\n", argv[0]);
+        return 2;
+    }
+    const bool gpu = std::strcmp(argv[1], "gpu") == 0;
+    testParametersAndVariables();
+    testTaskInitializationAndAddTaskRules(argv[2]);
+    if (gpu) {
+        testTaskMatrices(argv[2]);
+        testClosedLoop(argv[2], 1, false);
+        testClosedLoop(argv[2], 1, true);
+        testClosedLoop(argv[2], 48, true);
+        testIntegrator();
+    }
+    std::printf("%s: %d checks, %d failures\n", gpu ? "gpu" : "cpu", g_checks, g_failures);
+    return g_failures == 0 ? 0 : 1;
+}

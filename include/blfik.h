@@ -216,6 +216,15 @@ int blfik_kinematics_noalloc(blfik_problem* problem, const int32_t* frames, int3
 int blfik_integrate(blfik_problem* problem, const double* nu, int32_t mem, double dt,
                     int32_t nsteps);
 
+/* Stateless form of the same integrator for callers that own the state (the reference's
+ * FloatingBaseSystemVelocityKinematics + ForwardEuler objects are independent of the IK,
+ * ForwardEuler.h:96-124): advances base_pos [N][3], base_quat [N][4], s [N][n] in place by nsteps Euler
+ * steps of dt under the held input nu [N][6+n].  mem = BLFIK_MEM_DEVICE works in place on `device`;
+ * BLFIK_MEM_HOST stages through temporary device buffers and returns when the result is back.      */
+int blfik_integrate_state(int32_t n_dofs, int64_t n_instances, double* base_pos, double* base_quat,
+                          double* s, const double* nu, double dt, int32_t nsteps, int32_t mem,
+                          int32_t device);
+
 /* ---- introspection for parity tests -------------------------------------------------- */
 typedef enum {
     BLFIK_DEBUG_H = 0,   /* [N][nv][nv]  Hessian  (QPInverseKinematics.cpp:442-454)      */
