@@ -34,6 +34,7 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 PER_GPU_INSTANCES = 65536
+METRIC = "IK ticks/sec (robot-instances x ticks) at 65,536 ergoCub batch on 1/2/4/8 B200"  # BASELINE.json: metric
 CONFIG_ID = 3
 
 
@@ -133,7 +134,7 @@ def run_reference(args, rank: int, world: int) -> None:
     wall = time.perf_counter() - t0
     value = sample * steps / sum(sample / r for r in rates)
     line = {
-        "impl": "reference", "metric": "IK ticks/s", "value": value, "unit": "ticks/s", "n_gpus": args.gpus, "steps": steps,
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "ticks/s", "n_gpus": args.gpus, "steps": steps,
         "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * wall / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"C3 ergoCub-23 IK tick (m=107 reference rows), bounded sample of {sample} instances per step",
@@ -265,7 +266,7 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         cpu_sample = 1024 * cores
         cpu_rate, cpu_bad = cpu_oracle_rate(w, inputs, min(cpu_sample, n_local), cores)
         line = {
-            "metric": "IK ticks/s", "value": ticks_total / (ms_dev * 1e-3), "unit": "ticks/s", "n_gpus": world,
+            "metric": METRIC, "value": ticks_total / (ms_dev * 1e-3), "unit": "ticks/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C3: ergoCub-23 IK tick, CoM + 2xSE3 feet + JointLimits + JointVelocityLimits (priority 0, "
