@@ -283,7 +283,7 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
                          "frac": achieved_tf / fp64_peak if fp64_peak else None, "traffic": None,
                          "peak_source": "measured live by blfik_measure_fp64_peak (dependency-free DFMA loop); "
                                         "MEASURED_PEAKS.json has no FP64 figure",
-                         "kernel": "blfik_tick_fast_kernel<29,20>" if fast else "blfik_tick_kernel", "flops_per_launch": flops_launch,
+                         "kernel": "blfik_tick_fast_kernel<29,18>" if fast else "blfik_tick_kernel", "flops_per_launch": flops_launch,
                          "mean_matvecs_per_tick": float(iters.mean()),
                          "hbm": {"achieved": bytes_launch / (kernel_ms * 1e-3) * 1e-9, "peak": hbm_peak, "unit": "GB/s",
                                  "frac": bytes_launch / (kernel_ms * 1e-3) * 1e-9 / hbm_peak, "peak_source": hbm_src,

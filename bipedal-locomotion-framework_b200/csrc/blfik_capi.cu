@@ -501,7 +501,8 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         if (nv <= 32 && K <= 32) {
             if (nv == 29) {
                 if (K <= 16) pick_fast<29, 16>(p);
-                else if (K <= 20) pick_fast<29, 20>(p);
+                else if (K <= 18) pick_fast<29, 18>(p);
+                else if (K <= 30) pick_fast<29, 30>(p);
                 else pick_fast<29, 32>(p);
             } else {
                 if (K <= 16) pick_fast<32, 16>(p);

@@ -31,6 +31,14 @@ __host__ __device__ constexpr int ld2odd(int n)
     return 2 * h;  // smallest 2*odd >= n: conflict-free for lane-strided 64/128-bit accesses, rows 16 B aligned
 }
 
+// FP64 tensor-core tile product C(8x8) += A(8x4) * B(4x8).  Fragments (g = lane >> 2, t = lane & 3):
+// a = A[g][t], b = B[t][g], {c0, c1} = C[g][2t], C[g][2t + 1].  Measured on B200: 37.1 TFLOP/s, above the 33.8 TFLOP/s
+// of a DFMA loop, at one issue slot per 256 FMAs (tcgen05 has no FP64 kind, so this legacy path is the FP64 tensor path).
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+{
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
 // per-warp shared memory (offsets in doubles; the host fills this in)
 struct FastLayout {
     int linkR, linkP, axisW, mcw;
@@ -212,29 +220,39 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
     constexpr int LDG = FastDims<NV, KP>::LDG;
     double* Gs = Us;   // G by columns, consumed before U is written
     bool ok = true;
-    // ---- G = E + B D^-1 B', row r by lane r (lanes >= KP shadow row 0)
+    // ---- G = E + (B D^-1) B' on the FP64 tensor path (DMMA m8n8k4): ncu showed this contraction issue-bound
+    // (34 % issue utilisation, 22 % FP64 pipe) as a row-per-lane DFMA loop; as 8x8 tiles it is 1/8 of the
+    // instructions.  Only the tiles on and below the diagonal are formed (the Cholesky reads the lower triangle).
     {
-        double brow[LDB];
-        const int myr = lane < KP ? lane : 0;
-        const double2* myrow = reinterpret_cast<const double2*>(Bm + myr * LDB);
-        const double2* dv = reinterpret_cast<const double2*>(dinv);
+        constexpr int RT = (KP + 7) / 8;   // row tiles of B
+        constexpr int KS = (NV + 3) / 4;   // k steps over the velocity variables
+        const int gr = lane >> 2, tc = lane & 3;
+        double af[RT][KS], bf[RT][KS];
 #pragma unroll
-        for (int jj = 0; jj < LDB / 2; jj++) {
-            const double2 b2 = myrow[jj], d2 = dv[jj];
-            brow[2 * jj] = b2.x * d2.x, brow[2 * jj + 1] = b2.y * d2.y;
-        }
-        const double er = evec[myr];
-#pragma unroll 1
-        for (int c = 0; c < KP; c++) {
-            const double2* oth = reinterpret_cast<const double2*>(Bm + c * LDB);
-            double a0 = (c == lane) ? er : 0.0, a1 = 0.0;
+        for (int s = 0; s < KS; s++) {
+            const int col = 4 * s + tc;
+            const double dv = (col < NV) ? dinv[col] : 0.0;
 #pragma unroll
-            for (int jj = 0; jj < LDB / 2; jj++) {
-                const double2 o2 = oth[jj];
-                a0 = fma(brow[2 * jj], o2.x, a0);
-                a1 = fma(brow[2 * jj + 1], o2.y, a1);
+            for (int i = 0; i < RT; i++) {
+                const int row = 8 * i + gr;
+                const double v = (row < KP && col < NV) ? Bm[row * LDB + col] : 0.0;
+                bf[i][s] = v, af[i][s] = v * dv;
             }
-            if (lane < KP) Gs[c * LDG + lane] = a0 + a1;
+        }
+#pragma unroll
+        for (int i = 0; i < RT; i++) {
+#pragma unroll
+            for (int j = 0; j <= i; j++) {
+                double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+                for (int s = 0; s < KS; s++) dmma884(c0, c1, af[i][s], bf[j][s]);
+                const int row = 8 * i + gr, col = 8 * j + 2 * tc;
+                if (row < KP) {
+                    const double er = evec[row];
+                    if (col < KP) Gs[col * LDG + row] = c0 + (row == col ? er : 0.0);
+                    if (col + 1 < KP) Gs[(col + 1) * LDG + row] = c1 + (row == col + 1 ? er : 0.0);
+                }
+            }
         }
     }
     __syncwarp();
@@ -314,17 +332,32 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
             const double2 t2 = myu[rr];
             u[2 * rr] = t2.x, u[2 * rr + 1] = t2.y;
         }
-#pragma unroll 1
-        for (int jx = 0; jx < NV; jx++) {
-            const double2* uj = reinterpret_cast<const double2*>(Us + jx * LDG);
-            double a0 = (jx == lane) ? dinv_i : 0.0, a1 = 0.0;
+        {   // N = D^-1 - U U' as 8x8 DMMA tiles; the A and B fragments of U U' are the same registers
+            constexpr int MT = (NV + 7) / 8;
+            constexpr int KS = (KP + 3) / 4;
+            const int gr = lane >> 2, tc = lane & 3;
+            double uf[MT][KS];
 #pragma unroll
-            for (int rr = 0; rr < KP / 2; rr++) {
-                const double2 t2 = uj[rr];
-                a0 = fma(-u[2 * rr], t2.x, a0);
-                a1 = fma(-u[2 * rr + 1], t2.y, a1);
+            for (int i = 0; i < MT; i++)
+#pragma unroll
+                for (int s = 0; s < KS; s++) {
+                    const int row = 8 * i + gr, col = 4 * s + tc;
+                    uf[i][s] = (row < NV && col < KP) ? Us[row * LDG + col] : 0.0;
+                }
+#pragma unroll
+            for (int i = 0; i < MT; i++) {
+#pragma unroll
+                for (int j = 0; j < MT; j++) {
+                    double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+                    for (int s = 0; s < KS; s++) dmma884(c0, c1, uf[i][s], uf[j][s]);
+                    const int row = 8 * i + gr, col = 8 * j + 2 * tc;
+                    if (row < NV && col < LDB) {
+                        const double dr = dinv[row];
+                        *reinterpret_cast<double2*>(Ns + row * LDB + col) = make_double2((row == col ? dr : 0.0) - c0, (row == col + 1 ? dr : 0.0) - c1);
+                    }
+                }
             }
-            if (lane < NV) Ns[lane * LDB + jx] = mine ? a0 + a1 : 0.0;
         }
         const double2* w2 = reinterpret_cast<const double2*>(wv);
         double a0 = 0.0, a1 = 0.0;
