@@ -213,7 +213,7 @@ struct blfik_problem {
     void (*fast_kernel)(const FastParams) = nullptr;
     FastLayout F;
     size_t fast_smem = 0;
-    int fast_grid = 0, fast_wpb = 4;
+    int fast_grid = 0, fast_wpb = 12;
     int max_as_iters = 6, max_polish_iters = 40, max_total_iters = 400;
 };
 
@@ -512,6 +512,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
             const size_t fper = (size_t)p->F.total * sizeof(double);
             int fw = (int)((sm_total - 3072) / (fper + 64));
             if (fw > 12) fw = 12;            // register file: 3 blocks x 4 warps at <= 168 registers per thread
+            if (fw < p->fast_wpb) p->fast_wpb = fw < 1 ? 1 : fw;   // one block per SM holding all its resident warps
             int fb = fw / p->fast_wpb;
             if (fb < 1) {
                 p->fast_kernel = nullptr;    // does not fit: generic kernel

@@ -383,7 +383,7 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
 }
 
 template <int NV, int KP>
-__global__ void __launch_bounds__(128, 3) blfik_tick_fast_kernel(const FastParams FP)
+__global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParams FP)
 {
     constexpr int LDB = FastDims<NV, KP>::LDB;
     constexpr int LDG = FastDims<NV, KP>::LDG;
@@ -417,7 +417,13 @@ __global__ void __launch_bounds__(128, 3) blfik_tick_fast_kernel(const FastParam
     WM wk;                               // view for the K1 helpers of blfik_device.cuh
     wk.linkR = linkR, wk.linkP = linkP, wk.axisW = axisW, wk.mcw = mcw;
 
-    for (long long robot = (long long)blockIdx.x * wpb + wib; robot < P.N; robot += (long long)gridDim.x * wpb) {
+    // The warps of a block walk through the long straight-line phases (K1/K2, setup) together: the kernel is
+    // instruction-fetch bound (ncu: stall_no_instruction is the top stall with 12 independent warps per SM), and
+    // warps that run the same code at the same time share the fetched lines.  Warps past the end of the batch
+    // shadow the last robot without writing anything, so that every warp reaches every barrier.
+    for (long long base0 = (long long)blockIdx.x * wpb; base0 < P.N; base0 += (long long)gridDim.x * wpb) {
+        const bool active = base0 + wib < P.N;
+        const long long robot = active ? base0 + wib : P.N - 1;
         double* bp = P.base_pos + 3 * robot;
         double* bq = P.base_quat + 4 * robot;
         double* s = P.s + (size_t)n * robot;
@@ -429,6 +435,7 @@ __global__ void __launch_bounds__(128, 3) blfik_tick_fast_kernel(const FastParam
         }
         int status = 2, iters_total = 0;
         for (int tick = 0; tick < P.nticks; tick++) {
+            __syncthreads();
             // ================================================================ K1
             k1_fk(m, wk, bp, bq, s, lane);
             // ================================================================ K2
@@ -523,7 +530,7 @@ __global__ void __launch_bounds__(128, 3) blfik_tick_fast_kernel(const FastParam
             const double gmax = warp_max(fabs(gd));
             __syncwarp();
 
-            if (P.dbg.H && tick == 0) {   // parity introspection only: materialise H, g, C_eq, b_eq, box
+            if (P.dbg.H && tick == 0 && active) {   // parity introspection only: materialise H, g, C_eq, b_eq, box
                 const int me = P.L.me;
                 if (mine) {
                     for (int jx = 0; jx < nv; jx++) {
@@ -548,6 +555,7 @@ __global__ void __launch_bounds__(128, 3) blfik_tick_fast_kernel(const FastParam
                 __syncwarp();
             }
 
+            __syncthreads();
             status = 1;
             int iters = 0;
             double nrow[NV];
@@ -698,19 +706,19 @@ __global__ void __launch_bounds__(128, 3) blfik_tick_fast_kernel(const FastParam
                 if (!done && status != 2) status = 1;
             }
             iters_total += iters;
-            if (mine) P.nu[(size_t)nv * robot + lane] = x;
-            if (P.flags & BLFIK_TICK_INTEGRATE) {
+            if (mine && active) P.nu[(size_t)nv * robot + lane] = x;
+            if ((P.flags & BLFIK_TICK_INTEGRATE) && active) {
                 rvec[lane] = mine ? x : 0.0;
                 __syncwarp();
                 k4_integrate(n, bp, bq, s, rvec, P.dt, lane);
             }
             __syncwarp();
         }
-        if (mine) {
+        if (mine && active) {
             P.wx[(size_t)nv * robot + lane] = x;
             if (joint) P.wz[(size_t)n * robot + lane - 6] = z, P.wy[(size_t)n * robot + lane - 6] = y;
         }
-        if (lane == 0) {
+        if (lane == 0 && active) {
             P.status[robot] = status;
             P.iters[robot] = iters_total;
         }
