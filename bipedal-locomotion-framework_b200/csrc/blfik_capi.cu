@@ -215,7 +215,53 @@ struct blfik_problem {
     size_t fast_smem = 0;
     int fast_grid = 0, fast_wpb = 12;
     int max_as_iters = 6, max_polish_iters = 40, max_total_iters = 400;
+    double* d_model_pack = nullptr;
+    int njump = 0, has_com = 0;
 };
+
+// Block-shared constants of the register-resident kernel: per-link records [nl][20] = Xr(9) Xp(3) axis(3) com(3) mass pad,
+// pointer-jumping tables [njump][32] (int), link_of_dof[32] + dof_of_link[32] (int), ancestor masks [nl] (u64), subtree masses [n].
+static std::vector<double> pack_model(const blfik_model& m, FastLayout& F, int& njump)
+{
+    const int n = m.n, nl = n + 1;
+    njump = 0;
+    while ((1 << njump) < m.maxdepth + 1) njump++;
+    std::vector<int> jump((size_t)(njump > 0 ? njump : 1) * 32, -1);
+    {
+        std::vector<int> cur(32, -1);
+        for (int k = 0; k < nl; k++) cur[k] = m.parent[k];
+        for (int st = 0; st < njump; st++) {
+            for (int k = 0; k < 32; k++) jump[st * 32 + k] = cur[k];
+            std::vector<int> nxt(32, -1);
+            for (int k = 0; k < 32; k++) nxt[k] = cur[k] >= 0 ? cur[cur[k]] : -1;
+            cur = nxt;
+        }
+    }
+    int o = 20 * nl;
+    o = (o + 1) & ~1;
+    F.sh_jump = o, o += (njump > 0 ? njump : 1) * 16;
+    F.sh_lod = o, o += 32;
+    F.sh_anc = o, o += nl;
+    F.sh_msub = o, o += n;
+    o = (o + 1) & ~1;
+    F.sh_model_len = o;
+    std::vector<double> pack(o, 0.0);
+    for (int k = 0; k < nl; k++) {
+        double* r = pack.data() + 20 * k;
+        for (int c = 0; c < 9; c++) r[c] = m.Xr[9 * k + c];
+        for (int c = 0; c < 3; c++) r[9 + c] = m.Xp[3 * k + c], r[12 + c] = m.axis[3 * k + c], r[15 + c] = m.com[3 * k + c];
+        r[18] = m.mass[k];
+    }
+    int* ji = reinterpret_cast<int*>(pack.data() + F.sh_jump);
+    for (size_t i = 0; i < jump.size(); i++) ji[i] = jump[i];
+    int* li = reinterpret_cast<int*>(pack.data() + F.sh_lod);
+    for (int j = 0; j < 32; j++) li[j] = j < n ? m.link_of_dof[j] : 0;
+    for (int k = 0; k < 32; k++) li[32 + k] = (k >= 1 && k < nl) ? m.dof[k] : 0;
+    unsigned long long* an = reinterpret_cast<unsigned long long*>(pack.data() + F.sh_anc);
+    for (int k = 0; k < nl; k++) an[k] = m.anc[k];
+    for (int j = 0; j < n; j++) pack[F.sh_msub + j] = m.msub[j];
+    return pack;
+}
 
 template <int NV, int KP>
 static FastLayout make_fast_layout(int nl)
@@ -247,6 +293,8 @@ static void pick_fast(blfik_problem* p)
 {
     p->fast_kernel = blfik_tick_fast_kernel<NV, KP>;
     p->F = make_fast_layout<NV, KP>(p->n + 1);
+    // the control-law buffer ([ntasks][12]) lives in the U region during K2
+    // (it always fits: ntasks * 12 <= 32 * 12 <= NV * LDG for every instantiation with NV >= 29, KP >= 16)
 }
 
 static int rows_of(const blfik_task_desc& d, int n)
@@ -383,6 +431,14 @@ static int refresh_tasks(blfik_problem* p)
         DevTask& d = dt[t];
         d.type = h.d.type, d.priority = h.d.priority, d.frame = h.d.frame, d.rows = h.rows, d.enabled = h.d.controller_enabled;
         d.sp_len = h.sp_len, d.row_offset = h.row_offset, d.brow = h.brow;
+        d.flink = 0, d.pad_ = 0;
+        for (int c = 0; c < 9; c++) d.Fr[c] = (c % 4 == 0) ? 1.0 : 0.0;
+        for (int c = 0; c < 3; c++) d.Fp[c] = 0.0;
+        if (h.d.frame >= 0 && h.d.frame < p->model->nf) {
+            d.flink = p->model->frame_link[h.d.frame];
+            for (int c = 0; c < 9; c++) d.Fr[c] = p->model->Fr[9 * h.d.frame + c];
+            for (int c = 0; c < 3; c++) d.Fp[c] = p->model->Fp[3 * h.d.frame + c];
+        }
         for (int c = 0; c < 3; c++) d.mask[c] = h.d.mask[c] != 0, d.kp_lin[c] = h.d.kp_linear[c], d.kp_ang[c] = h.d.kp_angular[c];
         auto up = [&](const std::vector<double>& v, double* dst) -> int {
             if (!v.empty()) CU(cudaMemcpyAsync(dst, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, p->stream));
@@ -509,15 +565,28 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
                 else if (K <= 20) pick_fast<32, 20>(p);
                 else pick_fast<32, 32>(p);
             }
+            std::vector<double> pack = pack_model(*model, p->F, p->njump);
+            p->F.sh_model = 0;
+            p->F.sh_tasks = p->F.sh_model_len;
+            p->F.sh_total = p->F.sh_tasks + (int)(((size_t)ntasks * sizeof(DevTask) + 15) / 16 * 2);
+            for (const HostTask& h : p->tasks) p->has_com |= h.d.type == BLFIK_TASK_COM;
+            const size_t fshared = (size_t)p->F.sh_total * sizeof(double);
             const size_t fper = (size_t)p->F.total * sizeof(double);
-            int fw = (int)((sm_total - 3072) / (fper + 64));
+            int fw = (int)((sm_total - 3072 - fshared) / (fper + 64));
             if (fw > 12) fw = 12;            // register file: 3 blocks x 4 warps at <= 168 registers per thread
             if (fw < p->fast_wpb) p->fast_wpb = fw < 1 ? 1 : fw;   // one block per SM holding all its resident warps
             int fb = fw / p->fast_wpb;
             if (fb < 1) {
                 p->fast_kernel = nullptr;    // does not fit: generic kernel
             } else {
-                p->fast_smem = (size_t)p->fast_wpb * fper;
+                p->fast_smem = (size_t)p->fast_wpb * fper + fshared;
+                if (ntasks * 12 > p->F.total - p->F.Us || ntasks > 32) p->fast_kernel = nullptr;   // control buffer must fit the U region
+                void* dp = nullptr;
+                if (cudaMalloc(&dp, pack.size() * sizeof(double)) != cudaSuccess) return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cudaMalloc failed"));
+                p->allocs.push_back(dp);
+                if (cudaMemcpy(dp, pack.data(), pack.size() * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess)
+                    return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cudaMemcpy failed"));
+                p->d_model_pack = static_cast<double*>(dp);
                 const long long fwant = (N + p->fast_wpb - 1) / p->fast_wpb;
                 const long long fcap = (long long)p->num_sms * fb;
                 p->fast_grid = (int)(fwant < fcap ? fwant : fcap);
@@ -735,6 +804,7 @@ extern "C" int blfik_tick(blfik_problem* p, int32_t nticks, double dt, uint32_t 
         FastParams FP;
         FP.T = P, FP.F = p->F, FP.nv = p->nv, FP.K = p->K;
         FP.max_as_iters = p->max_as_iters, FP.max_polish_iters = p->max_polish_iters, FP.max_total_iters = p->max_total_iters;
+        FP.model_pack = p->d_model_pack, FP.njump = p->njump, FP.has_com = p->has_com;
         p->fast_kernel<<<p->fast_grid, p->fast_wpb * 32, p->fast_smem, p->stream>>>(FP);
     } else {
         blfik_tick_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(P);

@@ -50,6 +50,8 @@ struct DevTask {
     const double* lower;
     double inv_dt;
     const double* setpoint;  // device [N][sp_len]
+    double Fr[9], Fp[3];     // the task frame relative to its link (copied from the model)
+    int flink, pad_;         // link the task frame is attached to
 };
 
 struct Settings {

@@ -56,6 +56,11 @@ struct FastLayout {
     int MA;     // alias: |A| x (|A| | 1) scratch for the active-set matrix (over the dead U region)
     int ma_cap; // largest |A| the alias can hold
     int total;
+    // block-shared region (before the per-warp slices)
+    int sh_model, sh_model_len;          // packed model constants: [nl][20] link records, then the tables below
+    int sh_jump, sh_lod, sh_anc, sh_msub;  // offsets inside the model pack (doubles)
+    int sh_tasks;                        // DevTask[ntasks]
+    int sh_total;
 };
 
 struct FastParams {
@@ -64,6 +69,9 @@ struct FastParams {
     int nv, K;          // actual sizes (<= NV, <= KP)
     int max_as_iters;   // active-set refinement steps per round
     int max_polish_iters;
+    const double* model_pack;  // device copy of the packed model constants (layout in FastLayout)
+    int njump;            // pointer-jumping steps = ceil(log2(tree depth + 1))
+    int has_com;          // at least one CoMTask
     int max_total_iters;  // per-tick budget of mat-vecs (ADMM + polish); exceeding it ends the solve with status 1
 };
 
@@ -72,71 +80,6 @@ struct FastDims {
     static constexpr int LDB = ld2odd(NV);
     static constexpr int LDG = ld2odd(KP);
 };
-
-// frame Jacobian written straight into selected rows of the task-row matrix: source row s (0-2 linear,
-// 3-5 angular) goes to row map[s] of dst, or nowhere if map[s] < 0.
-__device__ __forceinline__ void fast_frame_jac(const DevModel& m, const double* linkP, const double* axisW, int L, const double* pf,
-                                               double* dst, int ld, const int* map, int lane)
-{
-    const int nv = m.n + 6;
-    const unsigned long long anc = m.anc[L];
-    if (lane < nv) {
-        const int c = lane;
-        double lin[3] = {0, 0, 0}, ang[3] = {0, 0, 0};
-        if (c < 3) {
-            lin[c] = 1.0;
-        } else if (c < 6) {
-            const double r[3] = {pf[0] - linkP[0], pf[1] - linkP[1], pf[2] - linkP[2]};
-            ang[c - 3] = 1.0;
-            cross3(ang, r, lin);
-        } else if ((anc >> (c - 6)) & 1ull) {
-            const int k = m.link_of_dof[c - 6];
-            const double d[3] = {pf[0] - linkP[3 * k], pf[1] - linkP[3 * k + 1], pf[2] - linkP[3 * k + 2]};
-            ang[0] = axisW[3 * k], ang[1] = axisW[3 * k + 1], ang[2] = axisW[3 * k + 2];
-            cross3(ang, d, lin);
-        }
-#pragma unroll
-        for (int i = 0; i < 3; i++) {
-            if (map[i] >= 0) dst[map[i] * ld + c] = lin[i];
-            if (map[3 + i] >= 0) dst[map[3 + i] * ld + c] = ang[i];
-        }
-    }
-}
-
-__device__ __forceinline__ void fast_com_jac(const DevModel& m, const double* linkP, const double* axisW, const double* mcw,
-                                             const double* com, double* dst, int ld, const int* map, int lane)
-{
-    const int nv = m.n + 6;
-    if (lane < nv) {
-        const int c = lane;
-        double lin[3] = {0, 0, 0};
-        if (c < 3) {
-            lin[c] = 1.0;
-        } else if (c < 6) {
-            const double r[3] = {com[0] - linkP[0], com[1] - linkP[1], com[2] - linkP[2]};
-            double e[3] = {0, 0, 0};
-            e[c - 3] = 1.0;
-            cross3(e, r, lin);
-        } else {
-            const int j = c - 6;
-            const int kj = m.link_of_dof[j];
-            double mc[3] = {0, 0, 0};
-            for (int k = 1; k < m.nl; k++) {
-                if ((m.anc[k] >> j) & 1ull) {
-                    mc[0] += mcw[3 * k], mc[1] += mcw[3 * k + 1], mc[2] += mcw[3 * k + 2];
-                }
-            }
-            const double ms = m.msub[j];
-            const double d[3] = {(mc[0] - ms * linkP[3 * kj]) * m.inv_total_mass, (mc[1] - ms * linkP[3 * kj + 1]) * m.inv_total_mass,
-                                 (mc[2] - ms * linkP[3 * kj + 2]) * m.inv_total_mass};
-            const double a[3] = {axisW[3 * kj], axisW[3 * kj + 1], axisW[3 * kj + 2]};
-            cross3(a, d, lin);
-        }
-#pragma unroll
-        for (int i = 0; i < 3; i++)
-            if (map[i] >= 0) dst[map[i] * ld + c] = lin[i];
-    }
-}
 
 // y_i = xb_i + sum_j nrow[j] * v[j], v broadcast from shared memory two doubles per load
 template <int NV>
@@ -393,7 +336,23 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
     const DevModel& m = P.m;
     const Settings& st = P.st;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-    double* base = smem + (size_t)wib * F.total;
+    // block-shared constants: the packed model (per-link records, pointer-jumping tables, ancestor masks, subtree
+    // masses) and the task descriptors, staged once per block
+    for (int e = threadIdx.x; e < F.sh_model_len; e += blockDim.x) smem[F.sh_model + e] = FP.model_pack[e];
+    {
+        const double* tsrc = reinterpret_cast<const double*>(P.tasks);
+        const int tlen = P.ntasks * (int)(sizeof(DevTask) / sizeof(double));
+        for (int e = threadIdx.x; e < tlen; e += blockDim.x) smem[F.sh_tasks + e] = tsrc[e];
+    }
+    __syncthreads();
+    const double* s_link = smem + F.sh_model;                                      // [nl][20]
+    const int* s_jump = reinterpret_cast<const int*>(smem + F.sh_model + F.sh_jump);   // [njump][32]
+    const int* s_lod = reinterpret_cast<const int*>(smem + F.sh_model + F.sh_lod);     // link_of_dof[32]
+    const int* s_dol = s_lod + 32;                                                     // dof_of_link[32]
+    const unsigned long long* s_anc = reinterpret_cast<const unsigned long long*>(smem + F.sh_model + F.sh_anc);
+    const double* s_msub = smem + F.sh_model + F.sh_msub;
+    const DevTask* s_tasks = reinterpret_cast<const DevTask*>(smem + F.sh_tasks);
+    double* base = smem + F.sh_total + (size_t)wib * F.total;
     double* linkR = base + F.linkR;
     double* linkP = base + F.linkP;
     double* axisW = base + F.axisW;
@@ -414,8 +373,6 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
     const int n = m.n, nv = FP.nv, K = FP.K;
     const bool mine = lane < nv;         // this lane owns velocity variable `lane`
     const bool joint = mine && lane >= 6;
-    WM wk;                               // view for the K1 helpers of blfik_device.cuh
-    wk.linkR = linkR, wk.linkP = linkP, wk.axisW = axisW, wk.mcw = mcw;
 
     // The warps of a block walk through the long straight-line phases (K1/K2, setup) together: the kernel is
     // instruction-fetch bound (ncu: stall_no_instruction is the top stall with 12 independent warps per SM), and
@@ -437,66 +394,194 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
         for (int tick = 0; tick < P.nticks; tick++) {
             __syncthreads();
             // ================================================================ K1
-            k1_fk(m, wk, bp, bq, s, lane);
+            // One link per lane: local joint transform, then composition along the ancestor chain by pointer jumping
+            // (ceil(log2(depth + 1)) steps; the parent transform comes over warp shuffles, not shared memory).
+            const int nl = m.nl;
+            double com[3] = {0.0, 0.0, 0.0};
+            {
+                const double* lp = s_link + 20 * (lane < nl ? lane : 0);
+                double R[9], p[3];
+                if (lane == 0) {
+                    const double q[4] = {bq[0], bq[1], bq[2], bq[3]};
+                    quat_to_rot(q, R);
+                    p[0] = bp[0], p[1] = bp[1], p[2] = bp[2];
+                } else if (lane < nl) {
+                    const double a0 = lp[12], a1 = lp[13], a2 = lp[14];
+                    double sn, cs;
+                    sincos(s[s_dol[lane]], &sn, &cs);
+                    const double v = 1.0 - cs;
+                    double Rj[9], X[9];
+                    Rj[0] = cs + a0 * a0 * v, Rj[1] = a0 * a1 * v - a2 * sn, Rj[2] = a0 * a2 * v + a1 * sn;
+                    Rj[3] = a1 * a0 * v + a2 * sn, Rj[4] = cs + a1 * a1 * v, Rj[5] = a1 * a2 * v - a0 * sn;
+                    Rj[6] = a2 * a0 * v - a1 * sn, Rj[7] = a2 * a1 * v + a0 * sn, Rj[8] = cs + a2 * a2 * v;
+#pragma unroll
+                    for (int c = 0; c < 9; c++) X[c] = lp[c];
+                    mat3_mul(X, Rj, R);
+                    p[0] = lp[9], p[1] = lp[10], p[2] = lp[11];
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 9; c++) R[c] = (c % 4 == 0) ? 1.0 : 0.0;
+                    p[0] = p[1] = p[2] = 0.0;
+                }
+                for (int stp = 0; stp < FP.njump; stp++) {
+                    const int a = s_jump[stp * 32 + lane];
+                    const int src = a < 0 ? lane : a;
+                    double Ra[9], pa[3];
+#pragma unroll
+                    for (int c = 0; c < 9; c++) Ra[c] = __shfl_sync(kFull, R[c], src);
+#pragma unroll
+                    for (int c = 0; c < 3; c++) pa[c] = __shfl_sync(kFull, p[c], src);
+                    if (a >= 0) {
+                        double Rn[9], off[3];
+                        mat3_mul(Ra, R, Rn);
+                        mat3_vec(Ra, p, off);
+#pragma unroll
+                        for (int c = 0; c < 9; c++) R[c] = Rn[c];
+#pragma unroll
+                        for (int c = 0; c < 3; c++) p[c] = pa[c] + off[c];
+                    }
+                }
+                const double ax[3] = {lp[12], lp[13], lp[14]}, cl[3] = {lp[15], lp[16], lp[17]};
+                double aw[3], cw[3];
+                mat3_vec(R, ax, aw);
+                mat3_vec(R, cl, cw);
+                const double mk = lane < nl ? lp[18] : 0.0;
+                double mc[3];
+#pragma unroll
+                for (int c = 0; c < 3; c++) mc[c] = mk * (p[c] + cw[c]);
+                if (lane < nl) {
+#pragma unroll
+                    for (int c = 0; c < 9; c++) linkR[9 * lane + c] = R[c];
+#pragma unroll
+                    for (int c = 0; c < 3; c++) linkP[3 * lane + c] = p[c], axisW[3 * lane + c] = aw[c], mcw[3 * lane + c] = mc[c];
+                }
+                if (FP.has_com) {
+#pragma unroll
+                    for (int c = 0; c < 3; c++) com[c] = warp_sum(mc[c]) * m.inv_total_mass;
+                }
+            }
             // ================================================================ K2
             // zero the row matrix (padding rows / columns must read as zero)
             for (int e = lane; e < KP * LDB / 2; e += 32) reinterpret_cast<double2*>(Bm)[e] = make_double2(0.0, 0.0);
             if (lane < KP) cvec[lane] = 0.0, evec[lane] = 1.0;
             __syncwarp();
+            // data of this lane's own joint (column 6 + j of every Jacobian) and, for CoM tasks, its CoM column
+            const int jj = joint ? lane - 6 : 0;
+            const int kj = s_lod[jj];
+            const double oj[3] = {linkP[3 * kj], linkP[3 * kj + 1], linkP[3 * kj + 2]};
+            const double aj[3] = {axisW[3 * kj], axisW[3 * kj + 1], axisW[3 * kj + 2]};
+            const double pB[3] = {linkP[0], linkP[1], linkP[2]};
+            double comcol[3] = {0.0, 0.0, 0.0};
+            if (FP.has_com && mine) {
+                if (lane < 3) {
+                    comcol[lane] = 1.0;
+                } else if (lane < 6) {
+                    const double r[3] = {com[0] - pB[0], com[1] - pB[1], com[2] - pB[2]};
+                    double e[3] = {0.0, 0.0, 0.0};
+                    e[lane - 3] = 1.0;
+                    cross3(e, r, comcol);
+                } else {
+                    double mc[3] = {0.0, 0.0, 0.0};
+                    for (int k = 1; k < nl; k++)
+                        if ((s_anc[k] >> jj) & 1ull) mc[0] += mcw[3 * k], mc[1] += mcw[3 * k + 1], mc[2] += mcw[3 * k + 2];
+                    const double ms = s_msub[jj];
+                    const double d[3] = {(mc[0] - ms * oj[0]) * m.inv_total_mass, (mc[1] - ms * oj[1]) * m.inv_total_mass,
+                                         (mc[2] - ms * oj[2]) * m.inv_total_mass};
+                    cross3(aj, d, comcol);
+                }
+            }
+            // control laws: lane t evaluates dense task t (frame pose, R3 / SO(3) P-controllers) once, for everybody
+            double* tbuf = Us;   // [ntasks][12]: frame origin, linear control, angular control (U is not alive yet)
+            if (lane < P.ntasks) {
+                const DevTask& tk = s_tasks[lane];
+                const bool dense = tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM;
+                if (dense) {
+                    const double* sp = tk.setpoint + robot * tk.sp_len;
+                    const bool has_lin = tk.type != T_SO3, has_ang = tk.type == T_SE3 || tk.type == T_SO3;
+                    double Rf[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, pf[3] = {com[0], com[1], com[2]};
+                    if (tk.type != T_COM) {
+                        const int Lk = tk.flink;
+                        double Rl[9], off[3];
+#pragma unroll
+                        for (int c = 0; c < 9; c++) Rl[c] = linkR[9 * Lk + c];
+                        mat3_mul(Rl, tk.Fr, Rf);
+                        mat3_vec(Rl, tk.Fp, off);
+#pragma unroll
+                        for (int c = 0; c < 3; c++) pf[c] = linkP[3 * Lk + c] + off[c];
+                    }
+                    const int voff = tk.type == T_SE3 ? 7 : 3;
+                    const bool lin_on = tk.type == T_COM || tk.type == T_R3 || tk.enabled != 0;   // only SE3Task has a controller mode
+                    double bl[3] = {0.0, 0.0, 0.0}, ba[3];
+                    if (has_lin) {
+#pragma unroll
+                        for (int c = 0; c < 3; c++) bl[c] = lin_on ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pf[c]) : sp[voff + c];
+                    }
+                    double qd[4] = {0.0, 0.0, 0.0, 1.0}, wff[3] = {0.0, 0.0, 0.0};
+                    if (has_ang) {
+                        const int qo = tk.type == T_SE3 ? 3 : 0, wo = tk.type == T_SE3 ? 10 : 4;
+#pragma unroll
+                        for (int c = 0; c < 4; c++) qd[c] = sp[qo + c];
+#pragma unroll
+                        for (int c = 0; c < 3; c++) wff[c] = sp[wo + c];
+                    }
+                    so3_control(Rf, qd, wff, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), ba);
+#pragma unroll
+                    for (int c = 0; c < 3; c++) tbuf[12 * lane + c] = pf[c], tbuf[12 * lane + 3 + c] = bl[c], tbuf[12 * lane + 6 + c] = ba[c];
+                }
+            }
+            __syncwarp();
             double dh = 0.0, gd = 0.0, lo = -kInf, hi = kInf;   // diagonal weight, sum w b, joint box
             const double sj = joint ? s[lane - 6] : 0.0;
             for (int t = 0; t < P.ntasks; t++) {
-                const DevTask& tk = P.tasks[t];
-                const double* sp = tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr;
+                const DevTask& tk = s_tasks[t];
                 if (tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM) {
-                    int map[6] = {-1, -1, -1, -1, -1, -1};
-                    double bt[6];
-                    int rows = 0;
-                    if (tk.type == T_COM) {
-                        double com[3], acc[3] = {0, 0, 0};
-                        for (int k = lane; k < m.nl; k += 32) acc[0] += mcw[3 * k], acc[1] += mcw[3 * k + 1], acc[2] += mcw[3 * k + 2];
-#pragma unroll
-                        for (int c = 0; c < 3; c++) com[c] = warp_sum(acc[c]) * m.inv_total_mass;
+                    // row map: masked linear rows first, then the three angular rows (SE3Task.cpp:289-316)
+                    int map[6] = {-1, -1, -1, -1, -1, -1}, src = 0, rows = 0;
+                    if (tk.type != T_SO3) {
 #pragma unroll
                         for (int c = 0; c < 3; c++)
                             if (tk.mask[c]) {
-                                bt[rows] = sp[3 + c] + tk.kp_lin[c] * (sp[c] - com[c]);
+                                if (lane == rows) src = c;
                                 map[c] = tk.brow + rows++;
                             }
-                        fast_com_jac(m, linkP, axisW, mcw, com, Bm, LDB, map, lane);
-                    } else {
-                        double R[9], pf[3];
-                        k1_frame_pose(m, wk, tk.frame, R, pf);
-                        if (tk.type == T_SE3 || tk.type == T_R3) {
-                            const int voff = tk.type == T_SE3 ? 7 : 3;
+                    }
+                    if (tk.type == T_SE3 || tk.type == T_SO3) {
 #pragma unroll
-                            for (int c = 0; c < 3; c++)
-                                if (tk.mask[c]) {
-                                    bt[rows] = tk.enabled ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pf[c]) : sp[voff + c];
-                                    map[c] = tk.brow + rows++;
-                                }
+                        for (int c = 0; c < 3; c++) {
+                            if (lane == rows) src = 3 + c;
+                            map[3 + c] = tk.brow + rows++;
                         }
-                        if (tk.type == T_SE3 || tk.type == T_SO3) {
-                            const double* qd = tk.type == T_SE3 ? sp + 3 : sp;
-                            const double* wff = tk.type == T_SE3 ? sp + 10 : sp + 4;
-                            double qdl[4] = {qd[0], qd[1], qd[2], qd[3]}, wl[3] = {wff[0], wff[1], wff[2]}, out[3];
-                            so3_control(R, qdl, wl, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), out);
-#pragma unroll
-                            for (int c = 0; c < 3; c++) {
-                                bt[rows] = out[c];
-                                map[3 + c] = tk.brow + rows++;
+                    }
+                    if (mine) {
+                        double lin[3] = {0.0, 0.0, 0.0}, ang[3] = {0.0, 0.0, 0.0};
+                        if (tk.type == T_COM) {
+                            lin[0] = comcol[0], lin[1] = comcol[1], lin[2] = comcol[2];
+                        } else {
+                            const double pf[3] = {tbuf[12 * t], tbuf[12 * t + 1], tbuf[12 * t + 2]};
+                            if (lane < 3) {
+                                lin[lane] = 1.0;
+                            } else if (lane < 6) {
+                                const double r[3] = {pf[0] - pB[0], pf[1] - pB[1], pf[2] - pB[2]};
+                                ang[lane - 3] = 1.0;
+                                cross3(ang, r, lin);
+                            } else if ((s_anc[tk.flink] >> jj) & 1ull) {
+                                const double d[3] = {pf[0] - oj[0], pf[1] - oj[1], pf[2] - oj[2]};
+                                ang[0] = aj[0], ang[1] = aj[1], ang[2] = aj[2];
+                                cross3(aj, d, lin);
                             }
                         }
-                        fast_frame_jac(m, linkP, axisW, m.frame_link[tk.frame], pf, Bm, LDB, map, lane);
+#pragma unroll
+                        for (int i = 0; i < 3; i++) {
+                            if (map[i] >= 0) Bm[map[i] * LDB + lane] = lin[i];
+                            if (map[3 + i] >= 0) Bm[map[3 + i] * LDB + lane] = ang[i];
+                        }
                     }
                     if (lane < rows) {
-                        double bv = bt[0];
-#pragma unroll
-                        for (int r = 1; r < 6; r++) bv = (lane == r) ? bt[r] : bv;
-                        cvec[tk.brow + lane] = bv;
+                        cvec[tk.brow + lane] = tbuf[12 * t + 3 + src];
                         evec[tk.brow + lane] = tk.priority == 0 ? 0.0 : 1.0 / tk.weight[lane];
                     }
                 } else if (joint) {
+                    const double* sp = tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr;
                     const int j = lane - 6;
                     if (tk.type == T_JOINT_TRACKING) {
                         const double bj = sp[n + j] + tk.kp_joint[j] * (sp[j] - sj);
@@ -515,6 +600,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                     }
                 }
             }
+            __syncwarp();   // the control buffer lives in the U region: everybody is done with it before the setup writes G there
             // per-variable ADMM step: 0 (no bound), rho (box), 1e3 rho (pinned: lo == hi)
             const bool bounded = joint && (lo > -kInfHalf || hi < kInfHalf);
             const bool pinned = bounded && lo == hi;
