@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <new>
 #include <string>
 #include <vector>
@@ -271,7 +272,10 @@ static FastLayout make_fast_layout(int nl)
     int o = 0;
     auto take = [&](int cnt) { int r = o; o += (cnt + 1) & ~1; return r; };
     F.linkR = take(9 * nl), F.linkP = take(3 * nl), F.axisW = take(3 * nl), F.mcw = take(3 * nl);
-    F.LGt = take(KP * LDG + KP);    // + KP: the rotating elimination reads up to KP slots past a column
+    // the link arrays are dead after K2, L_G' is born in the setup: same memory
+    // (+ KP: the rotating elimination reads up to KP slots past a column)
+    F.LGt = F.linkR;
+    if (o < KP * LDG + KP) o = (KP * LDG + KP + 1) & ~1;
     F.Bm = take(KP * LDB);
     // link arrays, LGt and Bm are dead once U is known: the N rows (NV x LDB) live on top of them
     if (o < NV * LDB) o = (NV * LDB + 1) & ~1;
@@ -573,7 +577,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
             const size_t fshared = (size_t)p->F.sh_total * sizeof(double);
             const size_t fper = (size_t)p->F.total * sizeof(double);
             int fw = (int)((sm_total - 3072 - fshared) / (fper + 64));
-            if (fw > 12) fw = 12;            // register file: 3 blocks x 4 warps at <= 168 registers per thread
+            if (fw > 12) fw = 12;            // register file: one block of 12 warps at <= 168 registers per thread (16 warps at 128 spill and run slower)
             if (fw < p->fast_wpb) p->fast_wpb = fw < 1 ? 1 : fw;   // one block per SM holding all its resident warps
             int fb = fw / p->fast_wpb;
             if (fb < 1) {
@@ -805,6 +809,7 @@ extern "C" int blfik_tick(blfik_problem* p, int32_t nticks, double dt, uint32_t 
         FP.T = P, FP.F = p->F, FP.nv = p->nv, FP.K = p->K;
         FP.max_as_iters = p->max_as_iters, FP.max_polish_iters = p->max_polish_iters, FP.max_total_iters = p->max_total_iters;
         FP.model_pack = p->d_model_pack, FP.njump = p->njump, FP.has_com = p->has_com;
+        { const char* e = getenv("BLFIK_SYNC_PHASES"); FP.sync_phases = e ? atoi(e) : 1; }
         p->fast_kernel<<<p->fast_grid, p->fast_wpb * 32, p->fast_smem, p->stream>>>(FP);
     } else {
         blfik_tick_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(P);

@@ -72,6 +72,7 @@ struct FastParams {
     const double* model_pack;  // device copy of the packed model constants (layout in FastLayout)
     int njump;            // pointer-jumping steps = ceil(log2(tree depth + 1))
     int has_com;          // at least one CoMTask
+    int sync_phases;      // 1: the warps of a block enter K1 and the setup together (block barriers)
     int max_total_iters;  // per-tick budget of mat-vecs (ADMM + polish); exceeding it ends the solve with status 1
 };
 
@@ -170,25 +171,27 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
         constexpr int RT = (KP + 7) / 8;   // row tiles of B
         constexpr int KS = (NV + 3) / 4;   // k steps over the velocity variables
         const int gr = lane >> 2, tc = lane & 3;
-        double af[RT][KS], bf[RT][KS];
+        double bf[RT][KS], dvv[KS];
 #pragma unroll
         for (int s = 0; s < KS; s++) {
             const int col = 4 * s + tc;
-            const double dv = (col < NV) ? dinv[col] : 0.0;
+            dvv[s] = (col < NV) ? dinv[col] : 0.0;
 #pragma unroll
             for (int i = 0; i < RT; i++) {
                 const int row = 8 * i + gr;
-                const double v = (row < KP && col < NV) ? Bm[row * LDB + col] : 0.0;
-                bf[i][s] = v, af[i][s] = v * dv;
+                bf[i][s] = (row < KP && col < NV) ? Bm[row * LDB + col] : 0.0;
             }
         }
 #pragma unroll
         for (int i = 0; i < RT; i++) {
+            double ai[KS];
+#pragma unroll
+            for (int s = 0; s < KS; s++) ai[s] = bf[i][s] * dvv[s];
 #pragma unroll
             for (int j = 0; j <= i; j++) {
                 double c0 = 0.0, c1 = 0.0;
 #pragma unroll
-                for (int s = 0; s < KS; s++) dmma884(c0, c1, af[i][s], bf[j][s]);
+                for (int s = 0; s < KS; s++) dmma884(c0, c1, ai[s], bf[j][s]);
                 const int row = 8 * i + gr, col = 8 * j + 2 * tc;
                 if (row < KP) {
                     const double er = evec[row];
@@ -392,7 +395,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
         }
         int status = 2, iters_total = 0;
         for (int tick = 0; tick < P.nticks; tick++) {
-            __syncthreads();
+            if (FP.sync_phases) __syncthreads();
             // ================================================================ K1
             // One link per lane: local joint transform, then composition along the ancestor chain by pointer jumping
             // (ceil(log2(depth + 1)) steps; the parent transform comes over warp shuffles, not shared memory).
@@ -641,7 +644,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                 __syncwarp();
             }
 
-            __syncthreads();
+            if (FP.sync_phases) __syncthreads();
             status = 1;
             int iters = 0;
             double nrow[NV];
