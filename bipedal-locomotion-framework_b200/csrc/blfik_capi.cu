@@ -809,7 +809,8 @@ extern "C" int blfik_tick(blfik_problem* p, int32_t nticks, double dt, uint32_t 
         FP.T = P, FP.F = p->F, FP.nv = p->nv, FP.K = p->K;
         FP.max_as_iters = p->max_as_iters, FP.max_polish_iters = p->max_polish_iters, FP.max_total_iters = p->max_total_iters;
         FP.model_pack = p->d_model_pack, FP.njump = p->njump, FP.has_com = p->has_com;
-        { const char* e = getenv("BLFIK_SYNC_PHASES"); FP.sync_phases = e ? atoi(e) : 1; }
+        { const char* e = getenv("BLFIK_SYNC_PHASES"); FP.sync_phases = e ? atoi(e) : 0; }
+        { const char* e = getenv("BLFIK_PDAS_FIRST"); FP.pdas_first = e ? atoi(e) : 1; }
         p->fast_kernel<<<p->fast_grid, p->fast_wpb * 32, p->fast_smem, p->stream>>>(FP);
     } else {
         blfik_tick_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(P);

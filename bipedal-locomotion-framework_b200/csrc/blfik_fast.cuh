@@ -39,6 +39,20 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
     asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+// Phase alignment of the warps of a block (instruction-fetch sharing).  mode 1: the whole block; mode 2: only the
+// warps that share a sub-partition (warp w lives on sub-partition w % 4), through a named barrier, so that a slow
+// robot holds back two neighbours instead of the whole block; mode 0: none.
+__device__ __forceinline__ void phase_barrier(int mode, int wib, int wpb)
+{
+    if (mode == 1) {
+        __syncthreads();
+    } else if (mode == 2) {
+        const int grp = wib & 3;
+        const int cnt = ((wpb - grp + 3) >> 2) * 32;   // warps grp, grp + 4, ... of this block
+        asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(cnt) : "memory");
+    }
+}
+
 // per-warp shared memory (offsets in doubles; the host fills this in)
 struct FastLayout {
     int linkR, linkP, axisW, mcw;
@@ -72,6 +86,7 @@ struct FastParams {
     const double* model_pack;  // device copy of the packed model constants (layout in FastLayout)
     int njump;            // pointer-jumping steps = ceil(log2(tree depth + 1))
     int has_com;          // at least one CoMTask
+    int pdas_first;       // 1: try the rho-free active-set attempt before ADMM (see the kernel)
     int sync_phases;      // 1: the warps of a block enter K1 and the setup together (block barriers)
     int max_total_iters;  // per-tick budget of mat-vecs (ADMM + polish); exceeding it ends the solve with status 1
 };
@@ -377,10 +392,12 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
     const bool mine = lane < nv;         // this lane owns velocity variable `lane`
     const bool joint = mine && lane >= 6;
 
-    // The warps of a block walk through the long straight-line phases (K1/K2, setup) together: the kernel is
-    // instruction-fetch bound (ncu: stall_no_instruction is the top stall with 12 independent warps per SM), and
-    // warps that run the same code at the same time share the fetched lines.  Warps past the end of the batch
-    // shadow the last robot without writing anything, so that every warp reaches every barrier.
+    // Optional phase alignment (FP.sync_phases, env BLFIK_SYNC_PHASES): with the first, 120 KB version of this
+    // kernel stall_no_instruction was the top stall, and warps that enter the long straight-line phases (K1/K2,
+    // setup) together share the fetched lines.  After the code shrank, the barriers cost as much in load imbalance
+    // (robots need different numbers of iterations) as they save in fetches (measured: 2.09 ms with, 2.00 ms without),
+    // so they are off by default.  Warps past the end of the batch shadow the last robot without writing anything,
+    // so that every warp reaches every barrier when they are on.
     for (long long base0 = (long long)blockIdx.x * wpb; base0 < P.N; base0 += (long long)gridDim.x * wpb) {
         const bool active = base0 + wib < P.N;
         const long long robot = active ? base0 + wib : P.N - 1;
@@ -395,7 +412,19 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
         }
         int status = 2, iters_total = 0;
         for (int tick = 0; tick < P.nticks; tick++) {
-            if (FP.sync_phases) __syncthreads();
+          // Two attempts per tick.  Attempt 0 (FP.pdas_first): factorise WITHOUT the ADMM penalty (rho = 0), so the
+          // proximal steps contract by sigma / (sigma + lambda) ~ 1e-2 and each active-set guess is solved in 2-3
+          // mat-vecs; the active set is refined by primal-dual steps and accepted only with the KKT certificate.
+          // Attempt 1 (the fallback, and the only attempt when pdas_first = 0): OSQP-style ADMM with rho on the box
+          // rows predicts the active set, the same certified polish finishes.  The fallback redoes K1/K2 because the
+          // factorisation reuses their shared memory.
+          bool done = false;
+          int iters = 0;
+          status = 1;
+          const int first_attempt = FP.pdas_first ? 0 : 1;
+          for (int attempt = first_attempt; attempt < 2 && !done && status != 2; attempt++) {
+            const bool with_rho = attempt == 1;
+            if (attempt == first_attempt) phase_barrier(FP.sync_phases, wib, wpb);
             // ================================================================ K1
             // One link per lane: local joint transform, then composition along the ancestor chain by pointer jumping
             // (ceil(log2(depth + 1)) steps; the parent transform comes over warp shuffles, not shared memory).
@@ -607,11 +636,11 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
             // per-variable ADMM step: 0 (no bound), rho (box), 1e3 rho (pinned: lo == hi)
             const bool bounded = joint && (lo > -kInfHalf || hi < kInfHalf);
             const bool pinned = bounded && lo == hi;
-            const double rho_i = bounded ? (pinned ? 1e3 * st.rho : st.rho) : 0.0;
+            const double rho_i = (bounded && with_rho) ? (pinned ? 1e3 * st.rho : st.rho) : 0.0;
             const double D_i = mine ? st.sigma + rho_i + dh : 1.0;
             const double Q_i = mine ? st.sigma + rho_i : 0.0;
             const double dinv_i = 1.0 / D_i;
-            const double inv_rho = bounded ? 1.0 / rho_i : 0.0;
+            const double inv_rho = rho_i > 0.0 ? 1.0 / rho_i : 0.0;
             dinv[lane] = mine ? dinv_i : 0.0;
             if (LDB > 32 && lane < LDB - 32) dinv[32 + lane] = 0.0, rvec[32 + lane] = 0.0;
             const bool any_box = __any_sync(kFull, bounded);
@@ -619,7 +648,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
             const double gmax = warp_max(fabs(gd));
             __syncwarp();
 
-            if (P.dbg.H && tick == 0 && active) {   // parity introspection only: materialise H, g, C_eq, b_eq, box
+            if (P.dbg.H && tick == 0 && active && attempt == first_attempt) {   // parity introspection only: materialise H, g, C_eq, b_eq, box
                 const int me = P.L.me;
                 if (mine) {
                     for (int jx = 0; jx < nv; jx++) {
@@ -644,9 +673,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                 __syncwarp();
             }
 
-            if (FP.sync_phases) __syncthreads();
-            status = 1;
-            int iters = 0;
+            if (attempt == first_attempt) phase_barrier(FP.sync_phases, wib, wpb);
             double nrow[NV];
             double xb = 0.0;
             if (infeasible) {
@@ -668,11 +695,11 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                 double xp = x;
                 double mu_mine = 0.0;
                 int act = 0;   // 0 free, 1 lower, 2 upper, 3 pinned
-                bool done = false;
-                for (int round = 0; round < st.max_rounds && !done && iters < FP.max_total_iters; round++) {
+                const int max_rounds = with_rho ? st.max_rounds : 1;
+                for (int round = 0; round < max_rounds && !done && iters < FP.max_total_iters; round++) {
                     // ---- ADMM (skipped when there is no box row: the problem is a pure equality QP)
                     double rp = 0.0, rd = 0.0;
-                    if (any_box) {
+                    if (any_box && with_rho) {
                         for (int it = 0; it < st.admm_iters; it++) {
                             rvec[lane] = mine ? st.sigma * x + gd + (bounded ? rho_i * z - y : 0.0) : 0.0;
                             __syncwarp();
@@ -698,7 +725,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                             break;
                         }
                     }
-                    const bool admm_converged = any_box && rp <= st.eps && rd <= st.eps * (1.0 + gmax);
+                    const bool admm_converged = any_box && with_rho && rp <= st.eps && rd <= st.eps * (1.0 + gmax);
                     // ---- polish: OSQP's active-set rule, then primal-dual active-set refinement on the same N
                     act = 0;
                     if (bounded) {
@@ -794,6 +821,8 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                 }
                 if (!done && status != 2) status = 1;
             }
+            if (!any_box) break;   // a pure equality QP has no second attempt
+          }
             iters_total += iters;
             if (mine && active) P.nu[(size_t)nv * robot + lane] = x;
             if ((P.flags & BLFIK_TICK_INTEGRATE) && active) {
