@@ -190,13 +190,9 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         prob.tick(1, w.dt, integrate=True, warm_start=False)
 
     def e2e_step():
-        prob.set_state(*h_state)                       # pinned host -> device
-        for t, sp in enumerate(h_sp):
-            if sp is not None:
-                prob.set_setpoint(t, sp)
-        prob.tick(1, w.dt, integrate=True, warm_start=False)
-        prob.L.blfik_get_output(prob.handle, h_nu.data_ptr(), capi.MEM_HOST)   # device -> host (+ sync)
-        prob.L.blfik_get_status(prob.handle, h_status.data_ptr(), None, capi.MEM_HOST)
+        # the reference-facing call with HOST buffers: state + set-points in, nu + status out, copies pipelined with the tick
+        prob.tick_host(h_state[0], h_state[1], h_state[2], h_sp, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False,
+                       nchunks=args.chunks)
 
     def barrier():
         if world > 1:
@@ -280,7 +276,9 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
                     "d2h_bytes_per_step": int(n_local * (8 * nv + 4))},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
-                         "frac": achieved_tf / fp64_peak if fp64_peak else None, "traffic": None,
+                         "frac": achieved_tf / fp64_peak if fp64_peak else None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r1_v3_fast_kernel_ncu_summary.txt
+                         "traffic": 87.86e6 if (fast and n_local == 65536) else None,
                          "peak_source": "measured live by blfik_measure_fp64_peak (dependency-free DFMA loop); "
                                         "MEASURED_PEAKS.json has no FP64 figure",
                          "kernel": "blfik_tick_fast_kernel<29,18>" if fast else "blfik_tick_kernel", "flops_per_launch": flops_launch,
@@ -306,10 +304,11 @@ prob_settings = {"rho": 1.0, "sigma": 1e-2, "alpha": 1.6, "eps": 1e-7, "admm_ite
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--instances", type=int, default=PER_GPU_INSTANCES, help="instances per GPU")
+    ap.add_argument("--chunks", type=int, default=4, help="pipeline depth of the host-buffer (e2e) tick")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -321,7 +320,8 @@ def main() -> None:
         # convenience: relaunch under torchrun, one rank per GPU
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__),
-               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--instances", str(args.instances)]
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--instances", str(args.instances),
+               "--chunks", str(args.chunks)]
         raise SystemExit(subprocess.call(cmd))
     run_ours(args, rank, local_rank, world)
 

@@ -35,7 +35,7 @@ EXPORTS = [
     "blfik_count_unsolved", "blfik_kinematics", "blfik_integrate", "blfik_debug_enable", "blfik_debug_get",
     "blfik_num_dofs", "blfik_num_equality_rows", "blfik_num_instances", "blfik_sync", "blfik_get_stream",
     "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak", "blfik_kinematics_noalloc",
-    "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state",
+    "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state", "blfik_tick_host",
 ]
 
 
@@ -267,6 +267,24 @@ class Problem:
     def tick(self, nticks: int = 1, dt: float = 0.0, integrate: bool = False, warm_start: bool = False):
         flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0)
         _check(self.L.blfik_tick(self.handle, int(nticks), float(dt), flags))
+
+    def tick_host(self, base_pos, base_quat, s, setpoints, nu, status=None, dt: float = 0.0, integrate: bool = False,
+                  warm_start: bool = False, nchunks: int = 8):
+        """One tick with HOST inputs and outputs, copies pipelined with compute (``blfik_tick_host``).  Arrays are numpy
+        arrays or (pinned) torch CPU tensors; ``setpoints`` is a list with one batch (or None) per task."""
+        flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0)
+
+        def hp(a):
+            if a is None:
+                return None
+            ptr, dev = _ptr(a)
+            assert not dev, "blfik_tick_host takes host buffers"
+            return ptr.value
+
+        arr = (C.c_void_p * max(1, len(self.tasks)))(*[hp(sp) for sp in setpoints]) if setpoints is not None else None
+        self.L.blfik_tick_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_double, C.c_uint32, C.c_int32]
+        _check(self.L.blfik_tick_host(self.handle, hp(base_pos), hp(base_quat), hp(s), arr, hp(nu), hp(status), float(dt), flags, int(nchunks)))
 
     def get_output(self, out=None):
         if out is None:

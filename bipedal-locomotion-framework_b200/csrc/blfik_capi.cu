@@ -22,7 +22,7 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
     const WM w = carve(smem + (size_t)wib * P.L.total, P.L);
     const int n = P.m.n, nv = P.L.nv;
-    for (long long robot = (long long)blockIdx.x * wpb + wib; robot < P.N; robot += (long long)gridDim.x * wpb) {
+    for (long long robot = P.first + (long long)blockIdx.x * wpb + wib; robot < P.N; robot += (long long)gridDim.x * wpb) {
         double* bp = P.base_pos + 3 * robot;
         double* bq = P.base_quat + 4 * robot;
         double* s = P.s + (size_t)n * robot;
@@ -184,6 +184,8 @@ struct HostTask {
     double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
 };
 
+constexpr int kMaxChunks = 16;
+
 struct blfik_problem {
     const blfik_model* model = nullptr;
     int device = 0;
@@ -218,6 +220,9 @@ struct blfik_problem {
     int max_as_iters = 6, max_polish_iters = 40, max_total_iters = 400;
     double* d_model_pack = nullptr;
     int njump = 0, has_com = 0;
+    // pipelined host-buffer tick (blfik_tick_host)
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+    cudaEvent_t ev_in[16] = {}, ev_done[16] = {}, ev_start = nullptr;
 };
 
 // Block-shared constants of the register-resident kernel: per-link records [nl][20] = Xr(9) Xp(3) axis(3) com(3) mass pad,
@@ -643,6 +648,12 @@ extern "C" void blfik_problem_destroy(blfik_problem* p)
     cudaSetDevice(p->device);
     if (p->stream) cudaStreamSynchronize(p->stream);
     for (void* a : p->allocs) cudaFree(a);
+    if (p->h2d_stream) {
+        cudaStreamSynchronize(p->h2d_stream), cudaStreamSynchronize(p->d2h_stream);
+        for (int c = 0; c < kMaxChunks; c++) cudaEventDestroy(p->ev_in[c]), cudaEventDestroy(p->ev_done[c]);
+        cudaEventDestroy(p->ev_start);
+        cudaStreamDestroy(p->h2d_stream), cudaStreamDestroy(p->d2h_stream);
+    }
     if (p->own_stream && p->stream) cudaStreamDestroy(p->stream);
     delete p;
 }
@@ -786,38 +797,113 @@ extern "C" int blfik_debug_get(blfik_problem* p, int32_t what, double* out, int3
     return BLFIK_OK;
 }
 
-extern "C" int blfik_tick(blfik_problem* p, int32_t nticks, double dt, uint32_t flags)
+// one launch of the tick over robots [first, first + count) on `stream`
+static int launch_tick_range(blfik_problem* p, long long first, long long count, int32_t nticks, double dt, uint32_t flags, cudaStream_t stream)
 {
-    CHECK_P(p, "blfik_tick");
-    // the reference's advance() fails when a set-point was never set (SE3Task.cpp:245-249) and
-    // kinDyn must hold a state
-    if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_tick] the robot state has never been set");
-    for (size_t t = 0; t < p->tasks.size(); t++)
-        if (!p->tasks[t].setpoint_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_tick] the set point of task %d has not been set at least once", (int)t);
-    if (nticks < 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_tick] nticks must be >= 1");
-    if ((flags & BLFIK_TICK_INTEGRATE) && !(dt > 0)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_tick] dt must be positive when integrating");
-    int rc = refresh_tasks(p);
-    if (rc) return rc;
     TickParams P;
-    P.m = p->dm, P.tasks = p->d_tasks, P.ntasks = (int)p->tasks.size(), P.N = p->N;
-    P.base_pos = p->base_pos, P.base_quat = p->base_quat, P.s = p->s, P.nu = p->nu, P.wx = p->wx, P.wz = p->wz, P.wy = p->wy;
+    P.m = p->dm, P.tasks = p->d_tasks, P.ntasks = (int)p->tasks.size(), P.first = first, P.N = first + count;   // robots [first, N)
+    P.base_pos = p->base_pos, P.base_quat = p->base_quat, P.s = p->s;
+    P.nu = p->nu, P.wx = p->wx, P.wz = p->wz, P.wy = p->wy;
     P.status = p->status, P.iters = p->iters, P.st = p->st, P.nticks = nticks, P.dt = dt, P.flags = flags;
-    P.dbg = p->debug ? p->dbg : DebugOut{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    P.dbg = (p->debug && first == 0 && count == p->N) ? p->dbg : DebugOut{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     P.L = p->L;
     if (p->fast_kernel && p->path == 0) {
         FastParams FP;
         FP.T = P, FP.F = p->F, FP.nv = p->nv, FP.K = p->K;
         FP.max_as_iters = p->max_as_iters, FP.max_polish_iters = p->max_polish_iters, FP.max_total_iters = p->max_total_iters;
         FP.model_pack = p->d_model_pack, FP.njump = p->njump, FP.has_com = p->has_com;
-        { const char* e = getenv("BLFIK_SYNC_PHASES"); FP.sync_phases = e ? atoi(e) : 0; }
+        { const char* e = getenv("BLFIK_SYNC_PHASES"); FP.sync_phases = e ? atoi(e) : 2; }
         { const char* e = getenv("BLFIK_PDAS_FIRST"); FP.pdas_first = e ? atoi(e) : 1; }
-        p->fast_kernel<<<p->fast_grid, p->fast_wpb * 32, p->fast_smem, p->stream>>>(FP);
+        const long long want = (count + p->fast_wpb - 1) / p->fast_wpb;
+        p->fast_kernel<<<(int)(want < p->fast_grid ? want : p->fast_grid), p->fast_wpb * 32, p->fast_smem, stream>>>(FP);
     } else {
-        blfik_tick_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(P);
+        const long long want = (count + p->warps_per_block - 1) / p->warps_per_block;
+        blfik_tick_kernel<<<(int)(want < p->grid ? want : p->grid), p->warps_per_block * 32, p->smem_bytes, stream>>>(P);
     }
     CU(cudaGetLastError());
     p->launches++;
+    return BLFIK_OK;
+}
+
+static int check_tick_args(blfik_problem* p, int32_t nticks, double dt, uint32_t flags, const char* fn, bool need_inputs)
+{
+    // the reference's advance() fails when a set-point was never set (SE3Task.cpp:245-249) and kinDyn must hold a state
+    if (need_inputs) {
+        if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[%s] the robot state has never been set", fn);
+        for (size_t t = 0; t < p->tasks.size(); t++)
+            if (!p->tasks[t].setpoint_set) return fail(BLFIK_ERR_NOT_READY, "[%s] the set point of task %d has not been set at least once", fn, (int)t);
+    }
+    if (nticks < 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[%s] nticks must be >= 1", fn);
+    if ((flags & BLFIK_TICK_INTEGRATE) && !(dt > 0)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[%s] dt must be positive when integrating", fn);
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_tick(blfik_problem* p, int32_t nticks, double dt, uint32_t flags)
+{
+    CHECK_P(p, "blfik_tick");
+    int rc = check_tick_args(p, nticks, dt, flags, "blfik_tick", true);
+    if (rc) return rc;
+    if ((rc = refresh_tasks(p))) return rc;
+    if ((rc = launch_tick_range(p, 0, p->N, nticks, dt, flags, p->stream))) return rc;
     p->ticked = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_tick_host(blfik_problem* p, const double* base_pos, const double* base_quat, const double* s,
+                               const double* const* setpoints, double* nu, int32_t* status, double dt, uint32_t flags, int32_t nchunks)
+{
+    CHECK_P(p, "blfik_tick_host");
+    int rc = check_tick_args(p, 1, dt, flags, "blfik_tick_host", false);
+    if (rc) return rc;
+    if (!base_pos || !base_quat || !s || !nu) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_tick_host] null state or output buffer");
+    for (size_t t = 0; t < p->tasks.size(); t++)
+        if (p->tasks[t].sp_len && !(setpoints && setpoints[t]) && !p->tasks[t].setpoint_set)
+            return fail(BLFIK_ERR_NOT_READY, "[blfik_tick_host] the set point of task %d has not been set at least once", (int)t);
+    if (nchunks < 1) nchunks = 1;
+    if (nchunks > kMaxChunks) nchunks = kMaxChunks;
+    if ((long long)nchunks > p->N) nchunks = (int)p->N;
+    if ((rc = refresh_tasks(p))) return rc;
+    if (!p->h2d_stream) {
+        CU(cudaStreamCreateWithFlags(&p->h2d_stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&p->d2h_stream, cudaStreamNonBlocking));
+        for (int c = 0; c < kMaxChunks; c++) {
+            CU(cudaEventCreateWithFlags(&p->ev_in[c], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&p->ev_done[c], cudaEventDisableTiming));
+        }
+        CU(cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming));
+    }
+    // everything enqueued earlier on the problem's stream comes first
+    CU(cudaEventRecord(p->ev_start, p->stream));
+    CU(cudaStreamWaitEvent(p->h2d_stream, p->ev_start, 0));
+    CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_start, 0));
+    const int n = p->n, nv = p->nv;
+    for (int c = 0; c < nchunks; c++) {
+        const long long a = p->N * c / nchunks, b = p->N * (c + 1) / nchunks, cnt = b - a;
+        // chunk c: host -> device on the copy-in stream ...
+        CU(cudaMemcpyAsync(p->base_pos + 3 * a, base_pos + 3 * a, (size_t)cnt * 3 * sizeof(double), cudaMemcpyHostToDevice, p->h2d_stream));
+        CU(cudaMemcpyAsync(p->base_quat + 4 * a, base_quat + 4 * a, (size_t)cnt * 4 * sizeof(double), cudaMemcpyHostToDevice, p->h2d_stream));
+        CU(cudaMemcpyAsync(p->s + (size_t)n * a, s + (size_t)n * a, (size_t)cnt * n * sizeof(double), cudaMemcpyHostToDevice, p->h2d_stream));
+        for (size_t t = 0; t < p->tasks.size(); t++) {
+            HostTask& h = p->tasks[t];
+            if (h.sp_len && setpoints && setpoints[t])
+                CU(cudaMemcpyAsync(h.d_setpoint + (size_t)h.sp_len * a, setpoints[t] + (size_t)h.sp_len * a, (size_t)cnt * h.sp_len * sizeof(double),
+                                   cudaMemcpyHostToDevice, p->h2d_stream));
+        }
+        CU(cudaEventRecord(p->ev_in[c], p->h2d_stream));
+        // ... the tick on the compute stream ...
+        CU(cudaStreamWaitEvent(p->stream, p->ev_in[c], 0));
+        if ((rc = launch_tick_range(p, a, cnt, 1, dt, flags, p->stream))) return rc;
+        CU(cudaEventRecord(p->ev_done[c], p->stream));
+        // ... device -> host on the copy-out stream
+        CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_done[c], 0));
+        CU(cudaMemcpyAsync(nu + (size_t)nv * a, p->nu + (size_t)nv * a, (size_t)cnt * nv * sizeof(double), cudaMemcpyDeviceToHost, p->d2h_stream));
+        if (status) CU(cudaMemcpyAsync(status + a, p->status + a, (size_t)cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, p->d2h_stream));
+    }
+    for (size_t t = 0; t < p->tasks.size(); t++)
+        if (p->tasks[t].sp_len && setpoints && setpoints[t]) p->tasks[t].setpoint_set = true;
+    p->state_set = true, p->ticked = true;
+    CU(cudaStreamSynchronize(p->d2h_stream));
+    CU(cudaStreamSynchronize(p->stream));
     return BLFIK_OK;
 }
 

@@ -77,7 +77,7 @@ struct TickParams {
     DevModel m;
     const DevTask* tasks;
     int ntasks;
-    long long N;
+    long long first, N;                    // this launch covers robots [first, N)
     double *base_pos, *base_quat, *s;      // state (in/out)
     double* nu;                            // [N][nv] out
     double *wx, *wz, *wy;                  // warm start [N][nv], [N][n], [N][n]

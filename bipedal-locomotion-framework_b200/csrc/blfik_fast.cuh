@@ -398,7 +398,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
     // (robots need different numbers of iterations) as they save in fetches (measured: 2.09 ms with, 2.00 ms without),
     // so they are off by default.  Warps past the end of the batch shadow the last robot without writing anything,
     // so that every warp reaches every barrier when they are on.
-    for (long long base0 = (long long)blockIdx.x * wpb; base0 < P.N; base0 += (long long)gridDim.x * wpb) {
+    for (long long base0 = P.first + (long long)blockIdx.x * wpb; base0 < P.N; base0 += (long long)gridDim.x * wpb) {
         const bool active = base0 + wib < P.N;
         const long long robot = active ? base0 + wib : P.N - 1;
         double* bp = P.base_pos + 3 * robot;

@@ -172,6 +172,17 @@ int blfik_set_controller_mode(blfik_problem* problem, int32_t task, int32_t enab
  * BLFIK_TICK_INTEGRATE) repeated nticks times with the set-points held.  Asynchronous.   */
 int blfik_tick(blfik_problem* problem, int32_t nticks, double dt, uint32_t flags);
 
+/* The whole reference-facing tick for callers whose data live in HOST memory (what the reference's caller does
+ * per period: setRobotState + setSetPoint + advance + getOutput, QPInverseKinematicsTest.cpp:459-484), pipelined:
+ * the batch is cut into nchunks pieces and host->device copies, the tick and the device->host copies of
+ * consecutive pieces overlap on three streams.  setpoints[t] is the host batch of task t, or NULL to keep what
+ * the task already has (setpoints itself may be NULL); status may be NULL.  Returns when nu (and status) are
+ * complete.  Copies only overlap if the host buffers are page-locked (cudaHostAlloc / cudaHostRegister /
+ * torch pin_memory); with pageable memory the call is correct but serial.  One tick, cold or warm per flags.    */
+int blfik_tick_host(blfik_problem* problem, const double* base_pos, const double* base_quat,
+                    const double* s, const double* const* setpoints, double* nu, int32_t* status,
+                    double dt, uint32_t flags, int32_t nchunks);
+
 /* replaces QPInverseKinematics::getOutput() (QPInverseKinematics.cpp:553-556): nu [N][6+n] =
  * [base linear; base angular; joint velocity] per robot                                 */
 int blfik_get_output(blfik_problem* problem, double* nu, int32_t mem);

@@ -416,3 +416,38 @@ def test_full_size_properties_and_shard_invariance():
     p2.tick(1, w.dt)
     assert np.array_equal(p2.get_output(), nu[a:b])
     p2.close()
+
+
+def test_tick_host_pipelined_equals_plain_tick():
+    """blfik_tick_host (host buffers, chunked copy/compute pipeline) gives bit-identical results to set_* + tick + get_*,
+    for chunk counts that do and do not divide the batch, with pageable and with page-locked buffers."""
+    import torch
+    w = W.config(3)
+    N = 1000
+    inp = W.synth_inputs(w, N, 3)
+    model, ref = make(w.model, w.tasks, N)
+    ref.set_inputs(inp)
+    ref.tick(1, w.dt, integrate=True)
+    nu_ref = ref.get_output()
+    st_ref, _ = ref.get_status()
+    state_ref = ref.get_state()
+    for nchunks, pinned in ((1, False), (7, False), (8, True), (64, True)):
+        prob = capi.Problem(model, w.tasks, N)
+        conv = (lambda a: torch.from_numpy(a).pin_memory()) if pinned else (lambda a: a)
+        nu = conv(np.zeros((N, w.model.nv)))
+        st = conv(np.full(N, -1, dtype=np.int32))
+        prob.tick_host(conv(inp.base_pos), conv(inp.base_quat), conv(inp.s), [None if sp is None else conv(sp) for sp in inp.setpoints],
+                       nu, st, dt=w.dt, integrate=True, nchunks=nchunks)
+        nu_np = nu.numpy() if pinned else nu
+        st_np = st.numpy() if pinned else st
+        assert np.array_equal(nu_np, nu_ref) and np.array_equal(st_np, st_ref)
+        for a, b in zip(prob.get_state(), state_ref):
+            assert np.array_equal(a, b)
+        prob.close()
+    # error path: a set-point is missing and none was set before
+    prob = capi.Problem(model, w.tasks, N)
+    with pytest.raises(capi.BlfikError) as e:
+        prob.tick_host(inp.base_pos, inp.base_quat, inp.s, [None] * len(w.tasks), np.zeros((N, w.model.nv)), None, dt=w.dt)
+    assert e.value.code == -4
+    prob.close()
+    ref.close()
