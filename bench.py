@@ -189,10 +189,12 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         prob.set_state(*d_state)                       # device -> device restore of the initial state
         prob.tick(1, w.dt, integrate=True, warm_start=False)
 
+    h_packed = torch.from_numpy(prob.pack_inputs(inputs)).pin_memory()
+
     def e2e_step():
-        # the reference-facing call with HOST buffers: state + set-points in, nu + status out, copies pipelined with the tick
-        prob.tick_host(h_state[0], h_state[1], h_state[2], h_sp, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False,
-                       nchunks=args.chunks)
+        # the reference-facing call with HOST buffers: one packed record per robot (state + set-points) in, nu + status out,
+        # copies pipelined with the tick (blfik_tick_packed)
+        prob.tick_packed(h_packed, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False, nchunks=args.chunks)
 
     def barrier():
         if world > 1:

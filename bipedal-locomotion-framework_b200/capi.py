@@ -36,6 +36,7 @@ EXPORTS = [
     "blfik_num_dofs", "blfik_num_equality_rows", "blfik_num_instances", "blfik_sync", "blfik_get_stream",
     "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak", "blfik_kinematics_noalloc",
     "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state", "blfik_tick_host",
+    "blfik_packed_record_len", "blfik_packed_offset", "blfik_tick_packed",
 ]
 
 
@@ -285,6 +286,36 @@ class Problem:
         self.L.blfik_tick_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_double, C.c_uint32, C.c_int32]
         _check(self.L.blfik_tick_host(self.handle, hp(base_pos), hp(base_quat), hp(s), arr, hp(nu), hp(status), float(dt), flags, int(nchunks)))
+
+    # ---- packed host records: p(3) q(4) s(n) then the set-point of every task that has one
+    @property
+    def packed_record_len(self) -> int:
+        self.L.blfik_packed_record_len.argtypes = [C.c_void_p]
+        return int(self.L.blfik_packed_record_len(self.handle))
+
+    def packed_offset(self, task: int) -> int:
+        self.L.blfik_packed_offset.argtypes = [C.c_void_p, C.c_int32]
+        return int(self.L.blfik_packed_offset(self.handle, int(task)))
+
+    def pack_inputs(self, inp) -> np.ndarray:
+        """``workloads.Inputs`` -> [N][packed_record_len] host array."""
+        rec = np.empty((self.N, self.packed_record_len))
+        rec[:, 0:3], rec[:, 3:7], rec[:, 7:7 + self.n] = inp.base_pos, inp.base_quat, inp.s
+        for t, sp in enumerate(inp.setpoints):
+            if sp is not None:
+                o = self.packed_offset(t)
+                rec[:, o:o + sp.shape[1]] = sp
+        return rec
+
+    def tick_packed(self, records, nu, status=None, dt: float = 0.0, integrate: bool = False, warm_start: bool = False,
+                    nchunks: int = 8):
+        """One tick from packed HOST records (numpy or pinned torch CPU tensor), one copy per pipeline chunk."""
+        flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0)
+        (r, d0), (o, d1) = _ptr(records), _ptr(nu)
+        st = None if status is None else _ptr(status)[0]
+        assert not d0 and not d1, "blfik_tick_packed takes host buffers"
+        self.L.blfik_tick_packed.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_uint32, C.c_int32]
+        _check(self.L.blfik_tick_packed(self.handle, r, o, st, float(dt), flags, int(nchunks)))
 
     def get_output(self, out=None):
         if out is None:

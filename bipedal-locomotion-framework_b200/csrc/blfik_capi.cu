@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
         double* bp = P.base_pos + 3 * robot;
         double* bq = P.base_quat + 4 * robot;
         double* s = P.s + (size_t)n * robot;
+        if (P.packed) unpack_state(P, robot, bp, bq, s, n, lane);
         bool warm = (P.flags & BLFIK_TICK_WARM_START) != 0;
         if (warm) {
             for (int i = lane; i < nv; i += 32) {
@@ -178,7 +179,7 @@ struct blfik_model {
 struct HostTask {
     blfik_task_desc d;
     std::vector<double> kp_joint, weight, klim, upper, lower;
-    int rows = 0, sp_len = 0, row_offset = 0, brow = 0;
+    int rows = 0, sp_len = 0, row_offset = 0, brow = 0, pk_off = 0;
     bool setpoint_set = false;
     double* d_setpoint = nullptr;
     double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
@@ -217,12 +218,14 @@ struct blfik_problem {
     FastLayout F;
     size_t fast_smem = 0;
     int fast_grid = 0, fast_wpb = 12;
-    int max_as_iters = 6, max_polish_iters = 40, max_total_iters = 400;
+    int max_as_iters = 6, max_polish_iters = 40, max_total_iters = 200;
     double* d_model_pack = nullptr;
     int njump = 0, has_com = 0;
     // pipelined host-buffer tick (blfik_tick_host)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     cudaEvent_t ev_in[16] = {}, ev_done[16] = {}, ev_start = nullptr;
+    int packed_len = 0;              // doubles per packed input record: 7 + n + sum of set-point lengths
+    double* d_packed = nullptr;      // device copy of the packed records (allocated on first use)
 };
 
 // Block-shared constants of the register-resident kernel: per-link records [nl][20] = Xr(9) Xp(3) axis(3) com(3) mass pad,
@@ -440,7 +443,7 @@ static int refresh_tasks(blfik_problem* p)
         DevTask& d = dt[t];
         d.type = h.d.type, d.priority = h.d.priority, d.frame = h.d.frame, d.rows = h.rows, d.enabled = h.d.controller_enabled;
         d.sp_len = h.sp_len, d.row_offset = h.row_offset, d.brow = h.brow;
-        d.flink = 0, d.pad_ = 0;
+        d.flink = 0, d.pk_off = h.pk_off;
         for (int c = 0; c < 9; c++) d.Fr[c] = (c % 4 == 0) ? 1.0 : 0.0;
         for (int c = 0; c < 3; c++) d.Fp[c] = 0.0;
         if (h.d.frame >= 0 && h.d.frame < p->model->nf) {
@@ -532,6 +535,11 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         h.d.kp_joint = h.d.weight = h.d.klim = h.d.upper_limits = h.d.lower_limits = nullptr;  // owned copies only
         h.setpoint_set = h.sp_len == 0;
         p->tasks.push_back(std::move(h));
+    }
+    p->packed_len = 7 + n;
+    for (HostTask& h : p->tasks) {
+        h.pk_off = p->packed_len;
+        p->packed_len += h.sp_len;
     }
     if (me > 64) return bail(fail(BLFIK_ERR_UNSUPPORTED, "[blfik_problem_create] more than 64 dense equality rows (%d)", me));
     p->me = me;
@@ -798,7 +806,8 @@ extern "C" int blfik_debug_get(blfik_problem* p, int32_t what, double* out, int3
 }
 
 // one launch of the tick over robots [first, first + count) on `stream`
-static int launch_tick_range(blfik_problem* p, long long first, long long count, int32_t nticks, double dt, uint32_t flags, cudaStream_t stream)
+static int launch_tick_range(blfik_problem* p, long long first, long long count, int32_t nticks, double dt, uint32_t flags, cudaStream_t stream,
+                             const double* packed = nullptr)
 {
     TickParams P;
     P.m = p->dm, P.tasks = p->d_tasks, P.ntasks = (int)p->tasks.size(), P.first = first, P.N = first + count;   // robots [first, N)
@@ -807,6 +816,7 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
     P.status = p->status, P.iters = p->iters, P.st = p->st, P.nticks = nticks, P.dt = dt, P.flags = flags;
     P.dbg = (p->debug && first == 0 && count == p->N) ? p->dbg : DebugOut{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     P.L = p->L;
+    P.packed = packed, P.packed_len = p->packed_len;
     if (p->fast_kernel && p->path == 0) {
         FastParams FP;
         FP.T = P, FP.F = p->F, FP.nv = p->nv, FP.K = p->K;
@@ -814,6 +824,7 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         FP.model_pack = p->d_model_pack, FP.njump = p->njump, FP.has_com = p->has_com;
         { const char* e = getenv("BLFIK_SYNC_PHASES"); FP.sync_phases = e ? atoi(e) : 2; }
         { const char* e = getenv("BLFIK_PDAS_FIRST"); FP.pdas_first = e ? atoi(e) : 1; }
+        { const char* e = getenv("BLFIK_MAX_ITERS"); if (e) FP.max_total_iters = atoi(e); }
         const long long want = (count + p->fast_wpb - 1) / p->fast_wpb;
         p->fast_kernel<<<(int)(want < p->fast_grid ? want : p->fast_grid), p->fast_wpb * 32, p->fast_smem, stream>>>(FP);
     } else {
@@ -901,6 +912,57 @@ extern "C" int blfik_tick_host(blfik_problem* p, const double* base_pos, const d
     }
     for (size_t t = 0; t < p->tasks.size(); t++)
         if (p->tasks[t].sp_len && setpoints && setpoints[t]) p->tasks[t].setpoint_set = true;
+    p->state_set = true, p->ticked = true;
+    CU(cudaStreamSynchronize(p->d2h_stream));
+    CU(cudaStreamSynchronize(p->stream));
+    return BLFIK_OK;
+}
+
+extern "C" int32_t blfik_packed_record_len(const blfik_problem* p) { return p ? p->packed_len : -1; }
+
+extern "C" int32_t blfik_packed_offset(const blfik_problem* p, int32_t task)
+{
+    if (!p) return -1;
+    if (task < 0) return 0;   // the state: p(3) q(4) s(n)
+    if (task >= (int)p->tasks.size() || p->tasks[task].sp_len == 0) return -1;
+    return p->tasks[task].pk_off;
+}
+
+extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double* nu, int32_t* status, double dt, uint32_t flags, int32_t nchunks)
+{
+    CHECK_P(p, "blfik_tick_packed");
+    int rc = check_tick_args(p, 1, dt, flags, "blfik_tick_packed", false);
+    if (rc) return rc;
+    if (!records || !nu) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_tick_packed] null input or output buffer");
+    if (nchunks < 1) nchunks = 1;
+    if (nchunks > kMaxChunks) nchunks = kMaxChunks;
+    if ((long long)nchunks > p->N) nchunks = (int)p->N;
+    if ((rc = refresh_tasks(p))) return rc;
+    if (!p->d_packed && (rc = dev_alloc(p, (size_t)p->N * p->packed_len, &p->d_packed, false))) return rc;
+    if (!p->h2d_stream) {
+        CU(cudaStreamCreateWithFlags(&p->h2d_stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&p->d2h_stream, cudaStreamNonBlocking));
+        for (int c = 0; c < kMaxChunks; c++) {
+            CU(cudaEventCreateWithFlags(&p->ev_in[c], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&p->ev_done[c], cudaEventDisableTiming));
+        }
+        CU(cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming));
+    }
+    CU(cudaEventRecord(p->ev_start, p->stream));
+    CU(cudaStreamWaitEvent(p->h2d_stream, p->ev_start, 0));
+    CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_start, 0));
+    const int nv = p->nv, R = p->packed_len;
+    for (int c = 0; c < nchunks; c++) {
+        const long long a = p->N * c / nchunks, b = p->N * (c + 1) / nchunks, cnt = b - a;
+        CU(cudaMemcpyAsync(p->d_packed + (size_t)R * a, records + (size_t)R * a, (size_t)cnt * R * sizeof(double), cudaMemcpyHostToDevice, p->h2d_stream));
+        CU(cudaEventRecord(p->ev_in[c], p->h2d_stream));
+        CU(cudaStreamWaitEvent(p->stream, p->ev_in[c], 0));
+        if ((rc = launch_tick_range(p, a, cnt, 1, dt, flags, p->stream, p->d_packed))) return rc;
+        CU(cudaEventRecord(p->ev_done[c], p->stream));
+        CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_done[c], 0));
+        CU(cudaMemcpyAsync(nu + (size_t)nv * a, p->nu + (size_t)nv * a, (size_t)cnt * nv * sizeof(double), cudaMemcpyDeviceToHost, p->d2h_stream));
+        if (status) CU(cudaMemcpyAsync(status + a, p->status + a, (size_t)cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, p->d2h_stream));
+    }
     p->state_set = true, p->ticked = true;
     CU(cudaStreamSynchronize(p->d2h_stream));
     CU(cudaStreamSynchronize(p->stream));

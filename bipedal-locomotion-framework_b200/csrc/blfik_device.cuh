@@ -51,7 +51,8 @@ struct DevTask {
     double inv_dt;
     const double* setpoint;  // device [N][sp_len]
     double Fr[9], Fp[3];     // the task frame relative to its link (copied from the model)
-    int flink, pad_;         // link the task frame is attached to
+    int flink;               // link the task frame is attached to
+    int pk_off;              // offset of this task's set-point inside a packed input record
 };
 
 struct Settings {
@@ -78,6 +79,8 @@ struct TickParams {
     const DevTask* tasks;
     int ntasks;
     long long first, N;                    // this launch covers robots [first, N)
+    const double* packed;                  // optional packed input records [.][packed_len]: p(3) q(4) s(n) set-points...
+    int packed_len;
     double *base_pos, *base_quat, *s;      // state (in/out)
     double* nu;                            // [N][nv] out
     double *wx, *wz, *wy;                  // warm start [N][nv], [N][n], [N][n]
@@ -414,7 +417,7 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
     __syncwarp();
     for (int t = 0; t < P.ntasks; t++) {
         const DevTask& tk = P.tasks[t];
-        const double* sp = tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr;
+        const double* sp = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : (tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr);
         if (tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM) {
             double bt[6];
             int src[6];
@@ -872,6 +875,19 @@ __device__ __forceinline__ QpResult k3_solve(const TickParams& P, const WM& w, b
 }
 
 // ------------------------------------------------------------------ K4: ForwardEuler on R3 x SO(3) x R^n
+// packed input records carry the state too: unpack it into the state arrays before the tick reads them
+__device__ __forceinline__ void unpack_state(const TickParams& P, long long robot, double* bp, double* bq, double* s, int n, int lane)
+{
+    const double* rec = P.packed + (size_t)robot * P.packed_len;
+    for (int i = lane; i < 7 + n; i += 32) {
+        const double v = rec[i];
+        if (i < 3) bp[i] = v;
+        else if (i < 7) bq[i - 3] = v;
+        else s[i - 7] = v;
+    }
+    __syncwarp();
+}
+
 // p += v dt;  R <- exp(w dt) R (manif tangent + group = left-plus, ForwardEuler.h:82);  s += sdot dt
 __device__ __forceinline__ void k4_integrate(int n, double* bp, double* bq, double* s, const double* nu, double dt,
                                              int lane)

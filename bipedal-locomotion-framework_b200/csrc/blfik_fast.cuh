@@ -404,6 +404,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
         double* bp = P.base_pos + 3 * robot;
         double* bq = P.base_quat + 4 * robot;
         double* s = P.s + (size_t)n * robot;
+        if (P.packed && active) unpack_state(P, robot, bp, bq, s, n, lane);
         const bool warm_flag = (P.flags & BLFIK_TICK_WARM_START) != 0;
         double x = 0.0, z = 0.0, y = 0.0;
         if (warm_flag && mine) {
@@ -528,7 +529,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                 const DevTask& tk = s_tasks[lane];
                 const bool dense = tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM;
                 if (dense) {
-                    const double* sp = tk.setpoint + robot * tk.sp_len;
+                    const double* sp = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : tk.setpoint + robot * tk.sp_len;
                     const bool has_lin = tk.type != T_SO3, has_ang = tk.type == T_SE3 || tk.type == T_SO3;
                     double Rf[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, pf[3] = {com[0], com[1], com[2]};
                     if (tk.type != T_COM) {
@@ -613,7 +614,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                         evec[tk.brow + lane] = tk.priority == 0 ? 0.0 : 1.0 / tk.weight[lane];
                     }
                 } else if (joint) {
-                    const double* sp = tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr;
+                    const double* sp = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : (tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr);
                     const int j = lane - 6;
                     if (tk.type == T_JOINT_TRACKING) {
                         const double bj = sp[n + j] + tk.kp_joint[j] * (sp[j] - sj);

@@ -183,6 +183,17 @@ int blfik_tick_host(blfik_problem* problem, const double* base_pos, const double
                     const double* s, const double* const* setpoints, double* nu, int32_t* status,
                     double dt, uint32_t flags, int32_t nchunks);
 
+/* Same tick from ONE packed host record per robot, so that each pipeline chunk is a single host->device copy
+ * (with separate arrays the per-copy latency of ~10 small copies per chunk eats the overlap).  A record is
+ * blfik_packed_record_len() doubles: base position (3), base quaternion (4), joint positions (n), then the
+ * set-point of every task that has one, in task order; blfik_packed_offset(task) gives each offset (task = -1:
+ * the state, offset 0; tasks without a set-point: -1).  The state arrays of the problem are updated from the
+ * records (and advanced when BLFIK_TICK_INTEGRATE is set); the per-task set-point buffers are not touched.       */
+int32_t blfik_packed_record_len(const blfik_problem* problem);
+int32_t blfik_packed_offset(const blfik_problem* problem, int32_t task);
+int blfik_tick_packed(blfik_problem* problem, const double* records, double* nu, int32_t* status,
+                      double dt, uint32_t flags, int32_t nchunks);
+
 /* replaces QPInverseKinematics::getOutput() (QPInverseKinematics.cpp:553-556): nu [N][6+n] =
  * [base linear; base angular; joint velocity] per robot                                 */
 int blfik_get_output(blfik_problem* problem, double* nu, int32_t mem);

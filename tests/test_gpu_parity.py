@@ -451,3 +451,28 @@ def test_tick_host_pipelined_equals_plain_tick():
     assert e.value.code == -4
     prob.close()
     ref.close()
+
+
+@pytest.mark.parametrize("path", PATHS)
+def test_tick_packed_equals_plain_tick(path):
+    """blfik_tick_packed (one packed host record per robot, one copy per chunk) is bit-identical to the plain tick."""
+    w = W.config(3)
+    N = 777
+    inp = W.synth_inputs(w, N, 3)
+    model, ref = make(w.model, w.tasks, N, path)
+    ref.set_inputs(inp)
+    ref.tick(1, w.dt, integrate=True)
+    nu_ref, (st_ref, _), state_ref = ref.get_output(), ref.get_status(), ref.get_state()
+    assert ref.packed_record_len == 7 + 23 + 6 + 13 + 13 + 7 + 46
+    assert ref.packed_offset(-1) == 0 and ref.packed_offset(0) == 30 and ref.packed_offset(3) == -1
+    rec = ref.pack_inputs(inp)
+    for nchunks in (1, 5, 16):
+        prob = capi.Problem(model, w.tasks, N)
+        prob.set_kernel_path(path)
+        nu, st = np.zeros((N, w.model.nv)), np.full(N, -1, dtype=np.int32)
+        prob.tick_packed(rec, nu, st, dt=w.dt, integrate=True, nchunks=nchunks)
+        assert np.array_equal(nu, nu_ref) and np.array_equal(st, st_ref)
+        for a, b in zip(prob.get_state(), state_ref):
+            assert np.array_equal(a, b)
+        prob.close()
+    ref.close()
