@@ -37,6 +37,7 @@ EXPORTS = [
     "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak", "blfik_kinematics_noalloc",
     "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state", "blfik_tick_host",
     "blfik_packed_record_len", "blfik_packed_offset", "blfik_tick_packed",
+    "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time",
 ]
 
 
@@ -252,6 +253,22 @@ class Problem:
         for t, sp in enumerate(inp.setpoints):
             if sp is not None:
                 self.set_setpoint(t, _f64(sp))
+
+    def set_setpoint_trajectory(self, task: int, amplitude, period: float, phase):
+        """x_d(t) = x_0 + A sin(2 pi t / period + phase_i) on the device; amplitude = [linear(3), angular(3)], phase [N]."""
+        a, ph = _f64(np.asarray(amplitude, dtype=np.float64).reshape(6)), _f64(phase)
+        self.L.blfik_set_setpoint_trajectory.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_double, C.c_void_p, C.c_int32]
+        _check(self.L.blfik_set_setpoint_trajectory(self.handle, int(task), a.ctypes.data, float(period), ph.ctypes.data, MEM_HOST))
+
+    def set_time(self, t: float):
+        self.L.blfik_set_time.argtypes = [C.c_void_p, C.c_double]
+        _check(self.L.blfik_set_time(self.handle, float(t)))
+
+    @property
+    def time(self) -> float:
+        self.L.blfik_get_time.argtypes = [C.c_void_p]
+        self.L.blfik_get_time.restype = C.c_double
+        return float(self.L.blfik_get_time(self.handle))
 
     def set_weight(self, task: int, weight):
         w = _f64(weight)

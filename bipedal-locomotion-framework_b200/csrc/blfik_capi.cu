@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
         int iters = 0;
         for (int tick = 0; tick < P.nticks; tick++) {
             k1_fk(P.m, w, bp, bq, s, lane);
-            k2_assemble(P, w, robot, s, lane);
+            k2_assemble(P, w, robot, s, lane, P.t0 + tick * P.dt);
             if (P.dbg.H && tick == 0) {
                 const int me = P.L.me, LD = P.L.LD;
                 for (int i = lane; i < nv; i += 32) {
@@ -180,6 +180,8 @@ struct HostTask {
     blfik_task_desc d;
     std::vector<double> kp_joint, weight, klim, upper, lower;
     int rows = 0, sp_len = 0, row_offset = 0, brow = 0, pk_off = 0;
+    double traj_amp[6] = {0, 0, 0, 0, 0, 0}, traj_omega = 0.0;
+    double* d_traj_phase = nullptr;
     bool setpoint_set = false;
     double* d_setpoint = nullptr;
     double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
@@ -224,6 +226,7 @@ struct blfik_problem {
     // pipelined host-buffer tick (blfik_tick_host)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     cudaEvent_t ev_in[16] = {}, ev_done[16] = {}, ev_start = nullptr;
+    double time = 0.0;               // time of the next tick (advanced by integrating ticks; set-point trajectories)
     int packed_len = 0;              // doubles per packed input record: 7 + n + sum of set-point lengths
     double* d_packed = nullptr;      // device copy of the packed records (allocated on first use)
 };
@@ -444,6 +447,8 @@ static int refresh_tasks(blfik_problem* p)
         d.type = h.d.type, d.priority = h.d.priority, d.frame = h.d.frame, d.rows = h.rows, d.enabled = h.d.controller_enabled;
         d.sp_len = h.sp_len, d.row_offset = h.row_offset, d.brow = h.brow;
         d.flink = 0, d.pk_off = h.pk_off;
+        d.traj_phase = h.d_traj_phase, d.traj_omega = h.d_traj_phase ? h.traj_omega : 0.0;
+        for (int c = 0; c < 6; c++) d.traj_amp[c] = h.traj_amp[c];
         for (int c = 0; c < 9; c++) d.Fr[c] = (c % 4 == 0) ? 1.0 : 0.0;
         for (int c = 0; c < 3; c++) d.Fp[c] = 0.0;
         if (h.d.frame >= 0 && h.d.frame < p->model->nf) {
@@ -732,6 +737,36 @@ extern "C" int blfik_set_setpoint(blfik_problem* p, int32_t t, const double* dat
     return BLFIK_OK;
 }
 
+extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const double* amplitude, double period, const double* phase, int32_t mem)
+{
+    CHECK_P(p, "blfik_set_setpoint_trajectory");
+    CHECK_TASK(p, t, "blfik_set_setpoint_trajectory");
+    HostTask& h = p->tasks[t];
+    if (!is_dense(h.d.type)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_trajectory] task %d is not an SE3 / SO3 / R3 / CoM task", t);
+    if (!(period > 0)) {   // switch the generator off
+        h.traj_omega = 0.0;
+        p->tasks_dirty = true;
+        return BLFIK_OK;
+    }
+    if (!amplitude || !phase) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_trajectory] null amplitude or phase");
+    int rc;
+    if (!h.d_traj_phase && (rc = dev_alloc(p, (size_t)p->N, &h.d_traj_phase))) return rc;
+    CU(cudaMemcpyAsync(h.d_traj_phase, phase, (size_t)p->N * sizeof(double), kind_in(mem), p->stream));
+    for (int c = 0; c < 6; c++) h.traj_amp[c] = amplitude[c];
+    h.traj_omega = 6.283185307179586476925286766559 / period;
+    p->tasks_dirty = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_set_time(blfik_problem* p, double t)
+{
+    CHECK_P(p, "blfik_set_time");
+    p->time = t;
+    return BLFIK_OK;
+}
+
+extern "C" double blfik_get_time(const blfik_problem* p) { return p ? p->time : 0.0; }
+
 extern "C" int blfik_set_weight(blfik_problem* p, int32_t t, const double* weight)
 {
     CHECK_P(p, "blfik_set_weight");
@@ -817,6 +852,7 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
     P.dbg = (p->debug && first == 0 && count == p->N) ? p->dbg : DebugOut{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     P.L = p->L;
     P.packed = packed, P.packed_len = p->packed_len;
+    P.t0 = p->time;
     if (p->fast_kernel && p->path == 0) {
         FastParams FP;
         FP.T = P, FP.F = p->F, FP.nv = p->nv, FP.K = p->K;
@@ -856,6 +892,7 @@ extern "C" int blfik_tick(blfik_problem* p, int32_t nticks, double dt, uint32_t 
     if (rc) return rc;
     if ((rc = refresh_tasks(p))) return rc;
     if ((rc = launch_tick_range(p, 0, p->N, nticks, dt, flags, p->stream))) return rc;
+    if (flags & BLFIK_TICK_INTEGRATE) p->time += nticks * dt;
     p->ticked = true;
     return BLFIK_OK;
 }
@@ -913,6 +950,7 @@ extern "C" int blfik_tick_host(blfik_problem* p, const double* base_pos, const d
     for (size_t t = 0; t < p->tasks.size(); t++)
         if (p->tasks[t].sp_len && setpoints && setpoints[t]) p->tasks[t].setpoint_set = true;
     p->state_set = true, p->ticked = true;
+    if (flags & BLFIK_TICK_INTEGRATE) p->time += dt;
     CU(cudaStreamSynchronize(p->d2h_stream));
     CU(cudaStreamSynchronize(p->stream));
     return BLFIK_OK;
@@ -964,6 +1002,7 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
         if (status) CU(cudaMemcpyAsync(status + a, p->status + a, (size_t)cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, p->d2h_stream));
     }
     p->state_set = true, p->ticked = true;
+    if (flags & BLFIK_TICK_INTEGRATE) p->time += dt;
     CU(cudaStreamSynchronize(p->d2h_stream));
     CU(cudaStreamSynchronize(p->stream));
     return BLFIK_OK;

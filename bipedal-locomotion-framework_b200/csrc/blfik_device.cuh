@@ -51,6 +51,10 @@ struct DevTask {
     double inv_dt;
     const double* setpoint;  // device [N][sp_len]
     double Fr[9], Fp[3];     // the task frame relative to its link (copied from the model)
+    // optional on-device set-point trajectory: base set-point + amp * sin(omega t + phase_i) (omega = 0: off)
+    const double* traj_phase;   // device [N]
+    double traj_amp[6];         // linear (3) and angular (3, rotation vector) amplitudes
+    double traj_omega;
     int flink;               // link the task frame is attached to
     int pk_off;              // offset of this task's set-point inside a packed input record
 };
@@ -79,6 +83,7 @@ struct TickParams {
     const DevTask* tasks;
     int ntasks;
     long long first, N;                    // this launch covers robots [first, N)
+    double t0;                             // time of the first tick of this launch (set-point trajectories)
     const double* packed;                  // optional packed input records [.][packed_len]: p(3) q(4) s(n) set-points...
     int packed_len;
     double *base_pos, *base_quat, *s;      // state (in/out)
@@ -399,13 +404,43 @@ __device__ __forceinline__ void k1_com(const DevModel& m, const WM& w, double* c
     }
 }
 
+// Set-point of a task at time t when an on-device trajectory is attached (the set-point producers
+// that feed setSetPoint): x_d(t) = x_0 + A sin(w t + phi_i), feed-forward += A w cos(w t + phi_i); orientations move by
+// the world-frame rotation Exp(A_ang sin(.)) about a fixed axis, whose angular velocity is exactly A_ang w cos(.).
+// `spl` receives the full record (13 / 7 / 6 doubles); returns the pointer the control law should read.
+__device__ __forceinline__ const double* traj_eval(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
+{
+    if (tk.traj_omega == 0.0 || !sp) return sp;
+    for (int c = 0; c < tk.sp_len && c < 13; c++) spl[c] = sp[c];
+    double sn, cs;
+    sincos(tk.traj_omega * t + tk.traj_phase[robot], &sn, &cs);
+    const double wc = tk.traj_omega * cs;
+    const bool lin = tk.type == T_SE3 || tk.type == T_COM || tk.type == T_R3;
+    const int qo = tk.type == T_SE3 ? 3 : 0, vo = tk.type == T_SE3 ? 7 : 3, wo = tk.type == T_SE3 ? 10 : 4;
+    if (lin) {
+#pragma unroll
+        for (int c = 0; c < 3; c++) spl[c] += tk.traj_amp[c] * sn, spl[vo + c] += tk.traj_amp[c] * wc;
+    }
+    if (tk.type == T_SE3 || tk.type == T_SO3) {
+        const double phi[3] = {tk.traj_amp[3] * sn, tk.traj_amp[4] * sn, tk.traj_amp[5] * sn};
+        double dq[4], q0[4] = {spl[qo], spl[qo + 1], spl[qo + 2], spl[qo + 3]}, qn[4];
+        so3_exp(phi, dq);
+        quat_mul(dq, q0, qn);
+#pragma unroll
+        for (int c = 0; c < 4; c++) spl[qo + c] = qn[c];
+#pragma unroll
+        for (int c = 0; c < 3; c++) spl[wo + c] += tk.traj_amp[3 + c] * wc;
+    }
+    return spl;
+}
+
 // ------------------------------------------------------------------ K2: task assembly
 // Builds, in shared memory, what QPInverseKinematics::advance builds (QPInverseKinematics.cpp:442-491):
 // H, g from the priority-1 tasks; the dense equality rows (Cs, b) from the priority-0 SE3/CoM/SO3/R3 tasks;
 // and, because every inequality row of the reference is +-e_j' (JointLimitsTask.cpp:110-113,
 // JointVelocityLimitsTask.cpp), the intersection of those rows as a per-joint box [lo, hi].
 // A priority-0 JointTrackingTask (rows e_j' x = b_j) becomes lo = hi = b_j.
-__device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, long long robot, const double* s, int lane)
+__device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, long long robot, const double* s, int lane, double tnow)
 {
     const DevModel& m = P.m;
     const Layout& L = P.L;
@@ -419,9 +454,10 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
         const DevTask& tk = P.tasks[t];
         const double* sp = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : (tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr);
         if (tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM) {
-            double bt[6];
+            double bt[6], spl[13];
             int src[6];
             int rows = 0;
+            sp = traj_eval(tk, robot, tnow, sp, spl);
             if (tk.type == T_COM) {
                 double com[3];
                 k1_com(m, w, com, w.Jt, LD, lane);

@@ -529,7 +529,9 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                 const DevTask& tk = s_tasks[lane];
                 const bool dense = tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM;
                 if (dense) {
-                    const double* sp = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : tk.setpoint + robot * tk.sp_len;
+                    double spl[13];
+                    const double* sp = traj_eval(tk, robot, P.t0 + tick * P.dt,
+                                                 P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : tk.setpoint + robot * tk.sp_len, spl);
                     const bool has_lin = tk.type != T_SO3, has_ang = tk.type == T_SE3 || tk.type == T_SO3;
                     double Rf[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, pf[3] = {com[0], com[1], com[2]};
                     if (tk.type != T_COM) {

@@ -159,6 +159,19 @@ int blfik_get_state(blfik_problem* problem, double* base_pos, double* base_quat,
 int blfik_set_setpoint(blfik_problem* problem, int32_t task, const double* data, int32_t mem);
 int32_t blfik_setpoint_len(const blfik_problem* problem, int32_t task);
 
+/* On-device set-point producer for closed-loop rollouts (no single counterpart: it stands in for the planners /
+ * splines whose output the reference's callers pass to setSetPoint every period, e.g.
+ * utilities/balancing-position-control/script/blf-balancing-position-control.py:351-474, so that a multi-tick launch
+ * needs no host traffic).  The set-point of `task` at time t becomes
+ *     x_d(t) = x_0 + A sin(2 pi t / period + phase_i),   feed-forward += A (2 pi / period) cos(.),
+ * x_0 being what blfik_set_setpoint stored; amplitude = [linear A (3), angular A (3, rotation vector about a fixed
+ * world axis)], phase [N] per robot.  period <= 0 switches it off.  Time starts at 0 and advances by dt with every
+ * integrating tick (blfik_set_time / blfik_get_time).                                                      */
+int blfik_set_setpoint_trajectory(blfik_problem* problem, int32_t task, const double* amplitude,
+                                  double period, const double* phase, int32_t mem);
+int blfik_set_time(blfik_problem* problem, double t);
+double blfik_get_time(const blfik_problem* problem);
+
 /* replaces QPInverseKinematics::setTaskWeight (QPInverseKinematics.cpp:251-305); host pointer,
  * shared by the whole batch, takes effect on the next tick                             */
 int blfik_set_weight(blfik_problem* problem, int32_t task, const double* weight);

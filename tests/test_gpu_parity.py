@@ -476,3 +476,64 @@ def test_tick_packed_equals_plain_tick(path):
             assert np.array_equal(a, b)
         prob.close()
     ref.close()
+
+
+@pytest.mark.parametrize("path", PATHS)
+def test_setpoint_trajectories_closed_loop(path):
+    """C5-style closed loop: sinusoidal SE3 / CoM / SO3 target trajectories generated ON THE DEVICE, 1 kHz ticks with
+    ForwardEuler.  The oracle gets the same set-points evaluated on the host and re-solves every tick from the GPU's state;
+    a single multi-tick launch must reproduce the tick-by-tick run."""
+    w = W.config(5)
+    N, NT = 24, 30
+    dt, period = w.dt, 2.0
+    inp = W.synth_inputs(w, N, 5)
+    rng = np.random.default_rng(17)
+    amps = {0: [0.02, 0.01, 0.015, 0, 0, 0], 1: [0.05, 0.02, 0.03, 0.1, -0.05, 0.08], 2: [0.03, 0.05, 0.0, 0.0, 0.1, 0.05],
+            5: [0, 0, 0, 0.1, 0.05, -0.1]}
+    phases = {t: rng.uniform(0, 2 * np.pi, N) for t in amps}
+
+    def setpoints_at(t):
+        sps = [None if sp is None else sp.copy() for sp in inp.setpoints]
+        om = 2 * np.pi / period
+        for ti, a in amps.items():
+            a = np.asarray(a)
+            sn, cs = np.sin(om * t + phases[ti])[:, None], np.cos(om * t + phases[ti])[:, None]
+            ty = w.tasks[ti].type
+            if ty in (T.TASK_SE3, T.TASK_COM, T.TASK_R3):
+                vo = 7 if ty == T.TASK_SE3 else 3
+                sps[ti][:, 0:3] += a[:3] * sn
+                sps[ti][:, vo:vo + 3] += a[:3] * om * cs
+            if ty in (T.TASK_SE3, T.TASK_SO3):
+                qo, wo = (3, 10) if ty == T.TASK_SE3 else (0, 4)
+                sps[ti][:, qo:qo + 4] = W.quat_mul(W.so3_exp(a[3:] * sn), sps[ti][:, qo:qo + 4])
+                sps[ti][:, wo:wo + 3] += a[3:] * om * cs
+        return sps
+
+    model, prob = make(w.model, w.tasks, N, path)
+    model2, whole = make(w.model, w.tasks, N, path)
+    for pr in (prob, whole):
+        pr.set_inputs(inp)
+        for ti, a in amps.items():
+            pr.set_setpoint_trajectory(ti, a, period, phases[ti])
+    o = Oracle(w.model, w.tasks)
+    p, q, s = inp.base_pos.copy(), inp.base_quat.copy(), inp.s.copy()
+    for k in range(NT):
+        assert abs(prob.time - k * dt) < 1e-12
+        pr_, qr_, sr_ = p.copy(), q.copy(), s.copy()
+        nur, str_, _ = o.tick_batch(pr_, qr_, sr_, setpoints_at(k * dt), dt_integrate=dt)
+        prob.tick(1, dt, integrate=True, warm_start=True)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        p, q, s = prob.get_state()
+        ok = (st == 0) & (str_ == 0)
+        assert ok.mean() > 0.9
+        assert np.abs(nu - nur)[ok].max() <= TOL_NU
+        assert np.abs(s - (sr_ + (nu - nur)[:, 6:] * dt))[ok].max() <= TOL_STATE
+    whole.tick(NT, dt, integrate=True, warm_start=True)
+    for a, b in zip(whole.get_state(), (p, q, s)):
+        assert np.abs(a - b).max() <= 1e-11     # not bitwise: k * dt inside the launch vs dt added k times on the host
+    assert abs(whole.time - NT * dt) < 1e-12
+    prob.set_setpoint_trajectory(1, amps[1], 0.0, phases[1])       # period <= 0 switches the generator off
+    with pytest.raises(capi.BlfikError):
+        prob.set_setpoint_trajectory(6, amps[1], 1.0, phases[1])   # JointTrackingTask has no trajectory generator
+    prob.close(), whole.close()
