@@ -37,7 +37,7 @@ EXPORTS = [
     "blfik_set_stream", "blfik_launch_count", "blfik_last_error", "blfik_measure_fp64_peak", "blfik_kinematics_noalloc",
     "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state", "blfik_tick_host",
     "blfik_packed_record_len", "blfik_packed_offset", "blfik_tick_packed",
-    "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time",
+    "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time", "blfik_set_limits",
 ]
 
 
@@ -277,6 +277,11 @@ class Problem:
     def set_gains(self, task: int, kp_linear=None, kp_angular=None, kp_joint=None):
         a = [None if v is None else _f64(v) for v in (kp_linear, kp_angular, kp_joint)]
         _check(self.L.blfik_set_gains(self.handle, int(task), *[None if v is None else v.ctypes.data for v in a]))
+
+    def set_limits(self, task: int, upper=None, lower=None, klim=None, sampling_time: float = 0.0):
+        a = [None if v is None else _f64(v) for v in (upper, lower, klim)]
+        self.L.blfik_set_limits.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double]
+        _check(self.L.blfik_set_limits(self.handle, int(task), *[None if v is None else v.ctypes.data for v in a], float(sampling_time)))
 
     def set_controller_mode(self, task: int, enabled: bool):
         _check(self.L.blfik_set_controller_mode(self.handle, int(task), int(enabled)))

@@ -795,6 +795,30 @@ extern "C" int blfik_set_gains(blfik_problem* p, int32_t t, const double* kl, co
     return BLFIK_OK;
 }
 
+extern "C" int blfik_set_limits(blfik_problem* p, int32_t t, const double* upper, const double* lower, const double* klim, double sampling_time)
+{
+    CHECK_P(p, "blfik_set_limits");
+    CHECK_TASK(p, t, "blfik_set_limits");
+    HostTask& h = p->tasks[t];
+    if (!is_inequality(h.d.type)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_limits] task %d is not a JointLimitsTask / JointVelocityLimitsTask", t);
+    const int n = p->n;
+    if (upper) h.upper.assign(upper, upper + n);
+    if (lower) h.lower.assign(lower, lower + n);
+    if (h.d.type == BLFIK_TASK_JOINT_LIMITS) {
+        if (klim) {
+            for (int j = 0; j < n; j++)
+                if (!(klim[j] >= 0 && klim[j] <= 1)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_limits] klim must be in [0, 1]");   // JointLimitsTask.cpp:150-166
+            h.klim.assign(klim, klim + n);
+        }
+        if (sampling_time != 0.0) {
+            if (!(sampling_time > 0)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_limits] sampling_time must be positive");
+            h.d.sampling_time = sampling_time;
+        }
+    }
+    p->tasks_dirty = true;
+    return BLFIK_OK;
+}
+
 extern "C" int blfik_set_controller_mode(blfik_problem* p, int32_t t, int32_t enabled)
 {
     CHECK_P(p, "blfik_set_controller_mode");

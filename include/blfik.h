@@ -179,6 +179,10 @@ int blfik_set_weight(blfik_problem* problem, int32_t task, const double* weight)
 int blfik_set_gains(blfik_problem* problem, int32_t task, const double* kp_linear,
                     const double* kp_angular, const double* kp_joint);
 int blfik_set_controller_mode(blfik_problem* problem, int32_t task, int32_t enabled);
+/* replaces the upper_limits / lower_limits / klim / sampling_time keys of JointLimitsTask (JointLimitsTask.cpp:136-198)
+ * and JointVelocityLimitsTask (JointVelocityLimitsTask.cpp:111-124) after construction; NULL / 0 keeps a value        */
+int blfik_set_limits(blfik_problem* problem, int32_t task, const double* upper_limits,
+                     const double* lower_limits, const double* klim, double sampling_time);
 
 /* ---- the tick ---------------------------------------------------------------------- */
 /* replaces QPInverseKinematics::advance() (+ ForwardEuler::integrate(0, dt) when

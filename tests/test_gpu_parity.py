@@ -280,6 +280,28 @@ def test_set_weight_gains_and_controller_mode_take_effect():
     assert np.all(st == 0)
     assert np.abs(nu1 - nur).max() <= TOL_NU
     assert np.abs(nu1 - nu0).max() > 1e-3
+    # limits changed after construction (C3 carries the limit tasks)
+    w3 = W.config(3)
+    inp3 = W.synth_inputs(w3, N, 3)
+    m3, p3 = make(w3.model, w3.tasks, N)
+    p3.set_inputs(inp3)
+    t3 = [T.TaskSpec(**vars(t)) for t in w3.tasks]
+    t3[4].upper, t3[4].lower = np.full(23, 1.2), np.full(23, -1.5)
+    p3.set_limits(4, upper=t3[4].upper, lower=t3[4].lower)
+    t3[3].klim = np.full(23, 0.25)
+    p3.set_limits(3, klim=t3[3].klim)
+    p3.tick(1, w3.dt)
+    nu3 = p3.get_output()
+    st3, _ = p3.get_status()
+    nur3, str3, _ = Oracle(w3.model, t3).tick_batch(inp3.base_pos.copy(), inp3.base_quat.copy(), inp3.s.copy(), inp3.setpoints)
+    ok3 = (st3 == 0) & (str3 == 0)
+    assert ok3.mean() > 0.8 and np.abs(nu3 - nur3)[ok3].max() <= TOL_NU
+    assert nu3[ok3][:, 6:].max() <= 1.2 + 1e-9 and nu3[ok3][:, 6:].min() >= -1.5 - 1e-9
+    with pytest.raises(capi.BlfikError):
+        p3.set_limits(0, upper=np.ones(23))    # not a limits task
+    with pytest.raises(capi.BlfikError):
+        p3.set_limits(3, klim=np.full(23, 1.5))
+    p3.close()
     with pytest.raises(capi.BlfikError):
         prob.set_weight(0, np.ones(3))         # priority-0 task has no weight
     with pytest.raises(capi.BlfikError):
