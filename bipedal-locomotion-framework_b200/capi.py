@@ -330,8 +330,10 @@ class Problem:
         return rec
 
     def tick_packed(self, records, nu, status=None, dt: float = 0.0, integrate: bool = False, warm_start: bool = False,
-                    nchunks: int = 8):
-        """One tick from packed HOST records (numpy or pinned torch CPU tensor), one copy per pipeline chunk."""
+                    nchunks: int = 0):
+        """One tick from packed HOST records (numpy or pinned torch CPU tensor).  nchunks = 0: zero-copy (the kernel reads
+        pinned host memory directly; falls back to staged copies for pageable buffers); nchunks >= 1: that many
+        copy / compute / copy pipeline chunks."""
         flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0)
         (r, d0), (o, d1) = _ptr(records), _ptr(nu)
         st = None if status is None else _ptr(status)[0]

@@ -56,7 +56,10 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
             res = k3_solve(P, w, warm, lane);
             iters += res.iters;
             warm = (P.flags & BLFIK_TICK_WARM_START) != 0;
-            for (int i = lane; i < nv; i += 32) P.nu[(size_t)nv * robot + i] = w.x[i];
+            for (int i = lane; i < nv; i += 32) {
+                P.nu[(size_t)nv * robot + i] = w.x[i];
+                if (P.nu_host) P.nu_host[(size_t)nv * robot + i] = w.x[i];
+            }
             __syncwarp();
             if (P.flags & BLFIK_TICK_INTEGRATE) k4_integrate(n, bp, bq, s, w.x, P.dt, lane);
         }
@@ -69,6 +72,7 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
         }
         if (lane == 0) {
             P.status[robot] = res.status;
+            if (P.status_host) P.status_host[robot] = res.status;
             P.iters[robot] = iters;
         }
         __syncwarp();
@@ -866,7 +870,7 @@ extern "C" int blfik_debug_get(blfik_problem* p, int32_t what, double* out, int3
 
 // one launch of the tick over robots [first, first + count) on `stream`
 static int launch_tick_range(blfik_problem* p, long long first, long long count, int32_t nticks, double dt, uint32_t flags, cudaStream_t stream,
-                             const double* packed = nullptr)
+                             const double* packed = nullptr, double* nu_host = nullptr, int* status_host = nullptr)
 {
     TickParams P;
     P.m = p->dm, P.tasks = p->d_tasks, P.ntasks = (int)p->tasks.size(), P.first = first, P.N = first + count;   // robots [first, N)
@@ -876,6 +880,7 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
     P.dbg = (p->debug && first == 0 && count == p->N) ? p->dbg : DebugOut{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     P.L = p->L;
     P.packed = packed, P.packed_len = p->packed_len;
+    P.nu_host = nu_host, P.status_host = status_host;
     P.t0 = p->time;
     if (p->fast_kernel && p->path == 0) {
         FastParams FP;
@@ -996,7 +1001,35 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     int rc = check_tick_args(p, 1, dt, flags, "blfik_tick_packed", false);
     if (rc) return rc;
     if (!records || !nu) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_tick_packed] null input or output buffer");
-    if (nchunks < 1) nchunks = 1;
+    if (nchunks <= 0) {
+        // zero-copy: when every host buffer is page-locked and mapped into the device's address space (cudaHostAlloc /
+        // cudaHostRegister / torch pin_memory), the kernel reads the records and writes nu / status over PCIe itself,
+        // so the transfers overlap the computation robot by robot instead of chunk by chunk
+        const void* hp[3] = {records, nu, status};
+        void* dp[3] = {nullptr, nullptr, nullptr};
+        bool mapped = true;
+        for (int k = 0; k < 3 && mapped; k++) {
+            if (!hp[k]) continue;
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, hp[k]) != cudaSuccess || at.type != cudaMemoryTypeHost || !at.devicePointer) {
+                cudaGetLastError();
+                mapped = false;
+            } else {
+                dp[k] = at.devicePointer;
+            }
+        }
+        if (mapped) {
+            if ((rc = refresh_tasks(p))) return rc;
+            if ((rc = launch_tick_range(p, 0, p->N, 1, dt, flags, p->stream, static_cast<const double*>(dp[0]), static_cast<double*>(dp[1]),
+                                        static_cast<int*>(dp[2]))))
+                return rc;
+            p->state_set = true, p->ticked = true;
+            if (flags & BLFIK_TICK_INTEGRATE) p->time += dt;
+            CU(cudaStreamSynchronize(p->stream));
+            return BLFIK_OK;
+        }
+        nchunks = 2;   // pageable buffers: staged copies
+    }
     if (nchunks > kMaxChunks) nchunks = kMaxChunks;
     if ((long long)nchunks > p->N) nchunks = (int)p->N;
     if ((rc = refresh_tasks(p))) return rc;

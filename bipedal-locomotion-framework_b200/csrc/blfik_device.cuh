@@ -84,6 +84,8 @@ struct TickParams {
     int ntasks;
     long long first, N;                    // this launch covers robots [first, N)
     double t0;                             // time of the first tick of this launch (set-point trajectories)
+    double* nu_host;                       // optional second copy of nu / status written straight into mapped pinned host
+    int* status_host;                      //   memory (zero-copy host tick); null otherwise
     const double* packed;                  // optional packed input records [.][packed_len]: p(3) q(4) s(n) set-points...
     int packed_len;
     double *base_pos, *base_quat, *s;      // state (in/out)

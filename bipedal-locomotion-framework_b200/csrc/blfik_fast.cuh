@@ -827,7 +827,10 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
             if (!any_box) break;   // a pure equality QP has no second attempt
           }
             iters_total += iters;
-            if (mine && active) P.nu[(size_t)nv * robot + lane] = x;
+            if (mine && active) {
+                P.nu[(size_t)nv * robot + lane] = x;
+                if (P.nu_host) P.nu_host[(size_t)nv * robot + lane] = x;
+            }
             if ((P.flags & BLFIK_TICK_INTEGRATE) && active) {
                 rvec[lane] = mine ? x : 0.0;
                 __syncwarp();
@@ -841,6 +844,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
         }
         if (lane == 0 && active) {
             P.status[robot] = status;
+            if (P.status_host) P.status_host[robot] = status;
             P.iters[robot] = iters_total;
         }
         __syncwarp();

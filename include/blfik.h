@@ -205,7 +205,10 @@ int blfik_tick_host(blfik_problem* problem, const double* base_pos, const double
  * blfik_packed_record_len() doubles: base position (3), base quaternion (4), joint positions (n), then the
  * set-point of every task that has one, in task order; blfik_packed_offset(task) gives each offset (task = -1:
  * the state, offset 0; tasks without a set-point: -1).  The state arrays of the problem are updated from the
- * records (and advanced when BLFIK_TICK_INTEGRATE is set); the per-task set-point buffers are not touched.       */
+ * records (and advanced when BLFIK_TICK_INTEGRATE is set); the per-task set-point buffers are not touched.
+ * nchunks <= 0 selects zero-copy: if records, nu and status are page-locked and mapped (cudaHostAlloc /
+ * cudaHostRegister / torch pin_memory), ONE launch reads the records and writes the results over PCIe itself, so
+ * the transfers overlap the computation robot by robot; with pageable buffers it falls back to two staged chunks.  */
 int32_t blfik_packed_record_len(const blfik_problem* problem);
 int32_t blfik_packed_offset(const blfik_problem* problem, int32_t task);
 int blfik_tick_packed(blfik_problem* problem, const double* records, double* nu, int32_t* status,

@@ -487,13 +487,20 @@ def test_tick_packed_equals_plain_tick(path):
     nu_ref, (st_ref, _), state_ref = ref.get_output(), ref.get_status(), ref.get_state()
     assert ref.packed_record_len == 7 + 23 + 6 + 13 + 13 + 7 + 46
     assert ref.packed_offset(-1) == 0 and ref.packed_offset(0) == 30 and ref.packed_offset(3) == -1
+    import torch
     rec = ref.pack_inputs(inp)
-    for nchunks in (1, 5, 16):
+    for nchunks, pinned in ((1, False), (5, False), (16, False), (0, False), (0, True)):
         prob = capi.Problem(model, w.tasks, N)
         prob.set_kernel_path(path)
         nu, st = np.zeros((N, w.model.nv)), np.full(N, -1, dtype=np.int32)
-        prob.tick_packed(rec, nu, st, dt=w.dt, integrate=True, nchunks=nchunks)
+        if pinned:   # zero-copy: the kernel reads the records from, and writes nu / status to, pinned host memory
+            rec_t, nu_t, st_t = torch.from_numpy(rec).pin_memory(), torch.from_numpy(nu).pin_memory(), torch.from_numpy(st).pin_memory()
+            prob.tick_packed(rec_t, nu_t, st_t, dt=w.dt, integrate=True, nchunks=nchunks)
+            nu, st = nu_t.numpy(), st_t.numpy()
+        else:
+            prob.tick_packed(rec, nu, st, dt=w.dt, integrate=True, nchunks=nchunks)
         assert np.array_equal(nu, nu_ref) and np.array_equal(st, st_ref)
+        assert np.array_equal(prob.get_output(), nu_ref)
         for a, b in zip(prob.get_state(), state_ref):
             assert np.array_equal(a, b)
         prob.close()
