@@ -51,7 +51,8 @@ class TaskDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("priority", C.c_int32), ("frame", C.c_int32), ("mask", C.c_int32 * 3),
                 ("controller_enabled", C.c_int32), ("kp_linear", C.c_double * 3), ("kp_angular", C.c_double * 3),
                 ("kp_joint", c_double_p), ("weight", c_double_p), ("klim", c_double_p),
-                ("upper_limits", c_double_p), ("lower_limits", c_double_p), ("sampling_time", C.c_double)]
+                ("upper_limits", c_double_p), ("lower_limits", c_double_p), ("sampling_time", C.c_double),
+                ("ref_frame", C.c_int32), ("distance_threshold", C.c_double)]
 
 
 class SolverSettings(C.Structure):
@@ -191,6 +192,8 @@ def task_descs(tasks: Sequence[TaskSpec]):
         d.kp_joint, d.weight, d.klim = dp(t.kp_joint), dp(t.weight), dp(t.klim)
         d.upper_limits, d.lower_limits = dp(t.upper), dp(t.lower)
         d.sampling_time = float(t.sampling_time)
+        d.ref_frame = int(getattr(t, "ref_frame", -1))
+        d.distance_threshold = float(getattr(t, "threshold", 0.001))
     return arr, keep
 
 

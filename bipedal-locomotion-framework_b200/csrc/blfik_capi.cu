@@ -324,6 +324,8 @@ static int rows_of(const blfik_task_desc& d, int n)
     case BLFIK_TASK_COM: return nm;
     case BLFIK_TASK_R3: return nm;
     case BLFIK_TASK_SO3: return 3;
+    case BLFIK_TASK_DISTANCE: return 1;
+    case BLFIK_TASK_GRAVITY: return 2;
     case BLFIK_TASK_JOINT_TRACKING: return n;
     case BLFIK_TASK_JOINT_LIMITS: return 2 * n;
     case BLFIK_TASK_JOINT_VELOCITY_LIMITS: return 2 * n;
@@ -337,11 +339,14 @@ static int sp_len_of(int type, int n)
     case BLFIK_TASK_COM: return 6;
     case BLFIK_TASK_R3: return 6;
     case BLFIK_TASK_SO3: return 7;
+    case BLFIK_TASK_DISTANCE: return 1;
+    case BLFIK_TASK_GRAVITY: return 6;
     case BLFIK_TASK_JOINT_TRACKING: return 2 * n;
     default: return 0;
     }
 }
-static bool is_dense(int type) { return type == BLFIK_TASK_SE3 || type == BLFIK_TASK_COM || type == BLFIK_TASK_SO3 || type == BLFIK_TASK_R3; }
+static bool is_dense(int type) { return is_dense_type(type); }
+static bool has_frame(int type) { return type == BLFIK_TASK_SE3 || type == BLFIK_TASK_SO3 || type == BLFIK_TASK_R3 || type == BLFIK_TASK_DISTANCE || type == BLFIK_TASK_GRAVITY; }
 static bool is_inequality(int type) { return type == BLFIK_TASK_JOINT_LIMITS || type == BLFIK_TASK_JOINT_VELOCITY_LIMITS; }
 
 extern "C" const char* blfik_last_error(void) { return g_err.c_str(); }
@@ -455,6 +460,12 @@ static int refresh_tasks(blfik_problem* p)
         for (int c = 0; c < 6; c++) d.traj_amp[c] = h.traj_amp[c];
         for (int c = 0; c < 9; c++) d.Fr[c] = (c % 4 == 0) ? 1.0 : 0.0;
         for (int c = 0; c < 3; c++) d.Fp[c] = 0.0;
+        d.flink2 = -1, d.thr = h.d.distance_threshold > 0 ? h.d.distance_threshold : 0.001;
+        for (int c = 0; c < 3; c++) d.Fp2[c] = 0.0;
+        if (h.d.type == BLFIK_TASK_DISTANCE && h.d.ref_frame >= 0 && h.d.ref_frame < p->model->nf) {
+            d.flink2 = p->model->frame_link[h.d.ref_frame];
+            for (int c = 0; c < 3; c++) d.Fp2[c] = p->model->Fp[3 * h.d.ref_frame + c];
+        }
         if (h.d.frame >= 0 && h.d.frame < p->model->nf) {
             d.flink = p->model->frame_link[h.d.frame];
             for (int c = 0; c < 9; c++) d.Fr[c] = p->model->Fr[9 * h.d.frame + c];
@@ -512,7 +523,9 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
             return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: inequality tasks can only be hard constraints (priority 0)", t));
         if (h.d.priority == 1 && !h.d.weight)
             return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: a priority-1 task needs a weight", t));
-        if ((h.d.type == BLFIK_TASK_SE3 || h.d.type == BLFIK_TASK_SO3 || h.d.type == BLFIK_TASK_R3) && (h.d.frame < 0 || h.d.frame >= model->nf))
+        if (h.d.type == BLFIK_TASK_DISTANCE && h.d.ref_frame >= model->nf)
+            return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: reference frame index %d out of range", t, h.d.ref_frame));
+        if (has_frame(h.d.type) && (h.d.frame < 0 || h.d.frame >= model->nf))
             return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: frame index %d out of range", t, h.d.frame));
         if (h.rows == 0) return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: the mask selects no row", t));
         h.sp_len = sp_len_of(h.d.type, n);
@@ -746,7 +759,8 @@ extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const 
     CHECK_P(p, "blfik_set_setpoint_trajectory");
     CHECK_TASK(p, t, "blfik_set_setpoint_trajectory");
     HostTask& h = p->tasks[t];
-    if (!is_dense(h.d.type)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_trajectory] task %d is not an SE3 / SO3 / R3 / CoM task", t);
+    if (h.d.type != BLFIK_TASK_SE3 && h.d.type != BLFIK_TASK_SO3 && h.d.type != BLFIK_TASK_R3 && h.d.type != BLFIK_TASK_COM)
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_trajectory] task %d is not an SE3 / SO3 / R3 / CoM task", t);
     if (!(period > 0)) {   // switch the generator off
         h.traj_omega = 0.0;
         p->tasks_dirty = true;

@@ -17,7 +17,8 @@ constexpr double kInf = 1e30;       // OsqpEigen::INFTY
 constexpr double kInfHalf = 0.5e30;
 constexpr unsigned kFull = 0xffffffffu;
 
-enum TaskType : int { T_SE3 = 0, T_COM = 1, T_SO3 = 2, T_JOINT_TRACKING = 3, T_JOINT_LIMITS = 4, T_JOINT_VEL_LIMITS = 5, T_R3 = 6 };
+enum TaskType : int { T_SE3 = 0, T_COM = 1, T_SO3 = 2, T_JOINT_TRACKING = 3, T_JOINT_LIMITS = 4, T_JOINT_VEL_LIMITS = 5, T_R3 = 6, T_DISTANCE = 7, T_GRAVITY = 8 };
+__host__ __device__ inline bool is_dense_type(int t) { return t == T_SE3 || t == T_COM || t == T_SO3 || t == T_R3 || t == T_DISTANCE || t == T_GRAVITY; }
 
 struct DevModel {
     int n, nl, nf, maxdepth;
@@ -56,6 +57,9 @@ struct DevTask {
     double traj_amp[6];         // linear (3) and angular (3, rotation vector) amplitudes
     double traj_omega;
     int flink;               // link the task frame is attached to
+    int flink2;              // DistanceTask: link of the reference frame, -1 = the world origin
+    double Fp2[3];           // DistanceTask: origin of the reference frame in its link
+    double thr;              // DistanceTask: distance_numeric_threshold
     int pk_off;              // offset of this task's set-point inside a packed input record
 };
 
@@ -455,7 +459,7 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
     for (int t = 0; t < P.ntasks; t++) {
         const DevTask& tk = P.tasks[t];
         const double* sp = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : (tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr);
-        if (tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM) {
+        if (is_dense_type(tk.type)) {
             double bt[6], spl[13];
             int src[6];
             int rows = 0;
@@ -472,6 +476,35 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
                 double R[9], pf[3];
                 k1_frame_pose(m, w, tk.frame, R, pf);
                 k1_frame_jac(m, w, m.frame_link[tk.frame], pf, w.Jt, LD, lane);
+                if (tk.type == T_DISTANCE) {   // DistanceTask.cpp:178-229: A = d' J_lin / max(thr, |d|), b = kp (d_des - |d|)
+                    double pr[3] = {0.0, 0.0, 0.0};
+                    if (tk.flink2 >= 0) {       // relative to a reference frame: the row is u'(J_lin,target - J_lin,reference)
+                        double off[3];
+                        mat3_vec(w.linkR + 9 * tk.flink2, tk.Fp2, off);
+                        for (int c = 0; c < 3; c++) pr[c] = w.linkP[3 * tk.flink2 + c] + off[c];
+                        k1_frame_jac(m, w, tk.flink2, pr, w.A, LD, lane);   // w.A is free until the QP setup
+                    }
+                    const double dv[3] = {pf[0] - pr[0], pf[1] - pr[1], pf[2] - pr[2]};
+                    const double d = sqrt(dv[0] * dv[0] + dv[1] * dv[1] + dv[2] * dv[2]);
+                    const double inv = 1.0 / fmax(d, tk.thr);
+                    __syncwarp();
+                    for (int c = lane; c < nv; c += 32) {
+                        double v = 0.0;
+                        for (int k = 0; k < 3; k++) v += dv[k] * (w.Jt[k * LD + c] - (tk.flink2 >= 0 ? w.A[k * LD + c] : 0.0));
+                        w.Jt[5 * LD + c] = v * inv;   // row 5 (an unused angular row) carries the distance row
+                    }
+                    bt[0] = tk.kp_lin[0] * (sp[0] - d);
+                    src[0] = 5, rows = 1;
+                }
+                if (tk.type == T_GRAVITY) {    // GravityTask.cpp:149-185
+                    double zb[3] = {sp[0], sp[1], sp[2]}, fb[3] = {sp[3], sp[4], sp[5]}, z[3], ff[3];
+                    const double zn = rsqrt(zb[0] * zb[0] + zb[1] * zb[1] + zb[2] * zb[2]);
+                    zb[0] *= zn, zb[1] *= zn, zb[2] *= zn;
+                    mat3_vec(R, zb, z);
+                    mat3_vec(R, fb, ff);
+                    bt[0] = ff[0] + tk.kp_lin[0] * z[1], bt[1] = ff[1] - tk.kp_lin[0] * z[0];
+                    src[0] = 3, src[1] = 4, rows = 2;
+                }
                 if (tk.type == T_SE3 || tk.type == T_R3) {
                     const int voff = tk.type == T_SE3 ? 7 : 3;
                     for (int c = 0; c < 3; c++)

@@ -527,12 +527,12 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
             double* tbuf = Us;   // [ntasks][12]: frame origin, linear control, angular control (U is not alive yet)
             if (lane < P.ntasks) {
                 const DevTask& tk = s_tasks[lane];
-                const bool dense = tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM;
+                const bool dense = is_dense_type(tk.type);
                 if (dense) {
                     double spl[13];
                     const double* sp = traj_eval(tk, robot, P.t0 + tick * P.dt,
                                                  P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : tk.setpoint + robot * tk.sp_len, spl);
-                    const bool has_lin = tk.type != T_SO3, has_ang = tk.type == T_SE3 || tk.type == T_SO3;
+                    const bool has_lin = tk.type == T_SE3 || tk.type == T_R3 || tk.type == T_COM, has_ang = tk.type == T_SE3 || tk.type == T_SO3;
                     double Rf[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, pf[3] = {com[0], com[1], com[2]};
                     if (tk.type != T_COM) {
                         const int Lk = tk.flink;
@@ -560,8 +560,31 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                         for (int c = 0; c < 3; c++) wff[c] = sp[wo + c];
                     }
                     so3_control(Rf, qd, wff, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), ba);
+                    double aux[3] = {0.0, 0.0, 0.0};
+                    if (tk.type == T_DISTANCE) {   // DistanceTask.cpp:178-229: u = d / max(thr, |d|), b = kp (d_des - |d|)
+                        if (tk.flink2 >= 0) {
+                            double off[3];
+                            mat3_vec(linkR + 9 * tk.flink2, tk.Fp2, off);
 #pragma unroll
-                    for (int c = 0; c < 3; c++) tbuf[12 * lane + c] = pf[c], tbuf[12 * lane + 3 + c] = bl[c], tbuf[12 * lane + 6 + c] = ba[c];
+                            for (int c = 0; c < 3; c++) aux[c] = linkP[3 * tk.flink2 + c] + off[c];   // origin of the reference frame
+                        }
+                        const double dv[3] = {pf[0] - aux[0], pf[1] - aux[1], pf[2] - aux[2]};
+                        const double d = sqrt(dv[0] * dv[0] + dv[1] * dv[1] + dv[2] * dv[2]);
+                        const double inv = 1.0 / fmax(d, tk.thr);
+                        bl[0] = tk.kp_lin[0] * (sp[0] - d);
+#pragma unroll
+                        for (int c = 0; c < 3; c++) ba[c] = dv[c] * inv;   // the unit direction, reused by the row generation
+                    } else if (tk.type == T_GRAVITY) {   // GravityTask.cpp:149-185
+                        double zb[3] = {sp[0], sp[1], sp[2]}, fb[3] = {sp[3], sp[4], sp[5]}, z[3], ff[3];
+                        const double zn = rsqrt(zb[0] * zb[0] + zb[1] * zb[1] + zb[2] * zb[2]);
+                        zb[0] *= zn, zb[1] *= zn, zb[2] *= zn;
+                        mat3_vec(Rf, zb, z);
+                        mat3_vec(Rf, fb, ff);
+                        bl[0] = ff[0] + tk.kp_lin[0] * z[1], bl[1] = ff[1] - tk.kp_lin[0] * z[0];
+                    }
+#pragma unroll
+                    for (int c = 0; c < 3; c++)
+                        tbuf[12 * lane + c] = pf[c], tbuf[12 * lane + 3 + c] = bl[c], tbuf[12 * lane + 6 + c] = ba[c], tbuf[12 * lane + 9 + c] = aux[c];
                 }
             }
             __syncwarp();
@@ -569,10 +592,15 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
             const double sj = joint ? s[lane - 6] : 0.0;
             for (int t = 0; t < P.ntasks; t++) {
                 const DevTask& tk = s_tasks[t];
-                if (tk.type == T_SE3 || tk.type == T_SO3 || tk.type == T_R3 || tk.type == T_COM) {
+                if (is_dense_type(tk.type)) {
                     // row map: masked linear rows first, then the three angular rows (SE3Task.cpp:289-316)
                     int map[6] = {-1, -1, -1, -1, -1, -1}, src = 0, rows = 0;
-                    if (tk.type != T_SO3) {
+                    if (tk.type == T_DISTANCE) {          // one row: u'(J_lin,target - J_lin,reference), written through slot 0
+                        map[0] = tk.brow, rows = 1;
+                    } else if (tk.type == T_GRAVITY) {    // two rows: the first two angular rows
+                        if (lane == 1) src = 1;
+                        map[3] = tk.brow, map[4] = tk.brow + 1, rows = 2;
+                    } else if (tk.type != T_SO3) {
 #pragma unroll
                         for (int c = 0; c < 3; c++)
                             if (tk.mask[c]) {
@@ -603,6 +631,26 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                                 const double d[3] = {pf[0] - oj[0], pf[1] - oj[1], pf[2] - oj[2]};
                                 ang[0] = aj[0], ang[1] = aj[1], ang[2] = aj[2];
                                 cross3(aj, d, lin);
+                            }
+                            if (tk.type == T_DISTANCE) {
+                                // subtract the reference frame's linear column, then project on the unit direction u
+                                if (tk.flink2 >= 0) {
+                                    const double pr[3] = {tbuf[12 * t + 9], tbuf[12 * t + 10], tbuf[12 * t + 11]};
+                                    double l2[3] = {0.0, 0.0, 0.0};
+                                    if (lane < 3) {
+                                        l2[lane] = 1.0;
+                                    } else if (lane < 6) {
+                                        const double r[3] = {pr[0] - pB[0], pr[1] - pB[1], pr[2] - pB[2]};
+                                        double e[3] = {0.0, 0.0, 0.0};
+                                        e[lane - 3] = 1.0;
+                                        cross3(e, r, l2);
+                                    } else if ((s_anc[tk.flink2] >> jj) & 1ull) {
+                                        const double d2[3] = {pr[0] - oj[0], pr[1] - oj[1], pr[2] - oj[2]};
+                                        cross3(aj, d2, l2);
+                                    }
+                                    lin[0] -= l2[0], lin[1] -= l2[1], lin[2] -= l2[2];
+                                }
+                                lin[0] = tbuf[12 * t + 6] * lin[0] + tbuf[12 * t + 7] * lin[1] + tbuf[12 * t + 8] * lin[2];
                             }
                         }
 #pragma unroll

@@ -1,5 +1,5 @@
 /**
- * IK.h -- the IK:: classes of the reference with a batch dimension: IKLinearTask, SE3Task, CoMTask, SO3Task, R3Task,
+ * IK.h -- the IK:: classes of the reference with a batch dimension: IKLinearTask, SE3Task, CoMTask, SO3Task, R3Task, DistanceTask, GravityTask,
  * JointTrackingTask, JointLimitsTask, JointVelocityLimitsTask, IntegrationBasedIK{,State,Problem}, QPInverseKinematics.
  * Same class / method / parameter-key names and the same bool + log()->error convention as
  * the headers under src/IK/include/BipedalLocomotion/IK; N = 1 reproduces the reference semantics, N > 1 runs N robots per tick.
@@ -226,6 +226,51 @@ private:
     std::array<bool, 3> m_mask{true, true, true};
     std::size_t m_DoFs{3};
     BLF_REGISTER_IK_TASK(R3Task);
+};
+
+/** DistanceTask.h / DistanceTask.cpp:95-265: one row keeping |p_target - p_reference| at a desired value
+ *  (reference_frame_name "" = the world origin). */
+class DistanceTask : public IKLinearTask
+{
+public:
+    const char* className() const override { return "DistanceTask"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    bool setDesiredDistance(double desiredDistance, std::ptrdiff_t instance = -1);
+    bool setSetPoint(double desiredDistance, std::ptrdiff_t instance = -1) { return setDesiredDistance(desiredDistance, instance); }
+    /** distance of the inspected robot at the last update() (DistanceTask.cpp:251-254) */
+    double getDistance() const { return m_computedDistance; }
+    std::size_t size() const override { return 1; }
+    Type type() const override { return Type::equality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+    std::size_t setPointLength() const override { return 1; }
+
+private:
+    int m_targetFrameIndex{-1}, m_referenceFrameIndex{-1};
+    double m_kp{0.0}, m_distanceNumericThreshold{0.001}, m_computedDistance{0.0};
+    BLF_REGISTER_IK_TASK(DistanceTask);
+};
+
+/** GravityTask.h / GravityTask.cpp:76-250: two rows aligning the z axis of a frame with a desired direction given in that frame. */
+class GravityTask : public IKLinearTask
+{
+public:
+    const char* className() const override { return "GravityTask"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    bool setDesiredGravityDirectionInTargetFrame(const Vector3d& desiredGravityDirection, std::ptrdiff_t instance = -1);
+    bool setFeedForwardVelocityInTargetFrame(const Vector3d& feedforwardVelocity, std::ptrdiff_t instance = -1);
+    bool setSetPoint(const Vector3d& desiredGravityDirection, const Vector3d& feedforwardVelocity = {0, 0, 0}, std::ptrdiff_t instance = -1);
+    std::size_t size() const override { return 2; }
+    Type type() const override { return Type::equality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+    std::size_t setPointLength() const override { return 6; }
+
+private:
+    void storePart(const Vector3d& v, int first, std::ptrdiff_t instance);
+    int m_targetFrameIndex{-1};
+    double m_kp{0.0};
+    BLF_REGISTER_IK_TASK(GravityTask);
 };
 
 /** JointTrackingTask.cpp:29-210 */

@@ -594,6 +594,194 @@ bool R3Task::fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>
     return m_isInitialized;
 }
 
+// =================================================================== DistanceTask
+bool DistanceTask::initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler)
+{
+    constexpr auto errorPrefix = "[DistanceTask::initialize]";
+    std::shared_ptr<const ParametersHandler::IParametersHandler> ptr;
+    if (!commonInitialize(paramHandler, ptr)) return false;
+    if (!ptr->getParameter("kp", m_kp)) {
+        log()->error("{} Failed to get the proportional linear gain.", errorPrefix);
+        return false;
+    }
+    std::string referenceName, targetName;
+    ptr->getParameter("reference_frame_name", referenceName);   // optional, "" = the world origin (DistanceTask.cpp:131-137)
+    if (!ptr->getParameter("target_frame_name", targetName)) {
+        log()->error("{} Failed to get the end effector frame name.", errorPrefix);
+        return false;
+    }
+    ptr->getParameter("distance_numeric_threshold", m_distanceNumericThreshold);   // optional (DistanceTask.cpp:149-156)
+    m_referenceFrameIndex = -1;
+    if (!referenceName.empty() && (m_referenceFrameIndex = m_kinDyn->getFrameIndex(referenceName)) < 0) {
+        log()->error("{} The specified base name ({}) does not seem to exist.", errorPrefix, referenceName);
+        return false;
+    }
+    if ((m_targetFrameIndex = m_kinDyn->getFrameIndex(targetName)) < 0) {
+        log()->error("{} The specified target name ({}) does not seem to exist.", errorPrefix, targetName);
+        return false;
+    }
+    m_description = "Distance Task - target frame: " + targetName + ".";
+    m_isInitialized = true;
+    return true;
+}
+
+bool DistanceTask::setDesiredDistance(double desiredDistance, std::ptrdiff_t instance)
+{
+    if (!m_kinDyn) return false;
+    const double rec[1] = {std::abs(desiredDistance)};   // DistanceTask.cpp:240
+    storeSetPoint(rec, instance);
+    m_isSetPointSetAtLeastOnce = true;
+    return true;
+}
+
+bool DistanceTask::update()
+{
+    m_isValid = false;
+    if (!m_isInitialized) {
+        log()->error("[DistanceTask::update] The task is not initialized. Please call initialize method.");
+        return m_isValid;
+    }
+    if (!m_isSetPointSetAtLeastOnce) {
+        log()->error("[DistanceTask::update] The set point has not been set at least once.");
+        return m_isValid;
+    }
+    const int i = inspected();
+    if (i >= 0 && m_A.rows == size()) {
+        SE3d pose, poseRef;
+        std::array<double, 9> R;
+        System::MatrixXd J, Jref;
+        if (!m_kinDyn->getWorldTransform(m_targetFrameIndex, pose, R, i) || !m_kinDyn->getFrameFreeFloatingJacobian(m_targetFrameIndex, J, i)) {
+            log()->error("[DistanceTask::update] Unable to get the jacobian.");
+            return m_isValid;
+        }
+        Vector3d d = pose.p;
+        if (m_referenceFrameIndex >= 0) {
+            if (!m_kinDyn->getWorldTransform(m_referenceFrameIndex, poseRef, R, i) || !m_kinDyn->getFrameFreeFloatingJacobian(m_referenceFrameIndex, Jref, i)) {
+                log()->error("[DistanceTask::update] Unable to get the relative jacobian.");
+                return m_isValid;
+            }
+            for (int c = 0; c < 3; c++) d[c] -= poseRef.p[c];
+        }
+        m_computedDistance = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        const double den = std::max(m_distanceNumericThreshold, m_computedDistance);
+        for (std::size_t c = 0; c < J.cols; c++) {
+            double a = 0.0;
+            for (int r = 0; r < 3; r++) a += d[r] * (J(r, c) - (m_referenceFrameIndex >= 0 ? Jref(r, c) : 0.0));
+            m_A(0, m_robotVelocityVariable.offset + c) = a / den;
+        }
+        m_b[0] = m_kp * (m_sp[i] - m_computedDistance);
+    }
+    m_isValid = true;
+    return m_isValid;
+}
+
+bool DistanceTask::fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>&) const
+{
+    d = blfik_task_desc{};
+    d.type = BLFIK_TASK_DISTANCE, d.frame = m_targetFrameIndex, d.ref_frame = m_referenceFrameIndex, d.controller_enabled = 1;
+    d.distance_threshold = m_distanceNumericThreshold;
+    for (int c = 0; c < 3; c++) d.mask[c] = 1, d.kp_linear[c] = m_kp;
+    return m_isInitialized;
+}
+
+// =================================================================== GravityTask
+bool GravityTask::initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler)
+{
+    constexpr auto errorPrefix = "[GravityTask::initialize]";
+    std::shared_ptr<const ParametersHandler::IParametersHandler> ptr;
+    if (!commonInitialize(paramHandler, ptr)) return false;
+    if (!ptr->getParameter("kp", m_kp)) {
+        log()->error("{} Failed to get the proportional linear gain.", errorPrefix);
+        return false;
+    }
+    std::string targetName;
+    if (!ptr->getParameter("target_frame_name", targetName) || (m_targetFrameIndex = m_kinDyn->getFrameIndex(targetName)) < 0) {
+        log()->error("{} Failed to get the target frame name.", errorPrefix);
+        return false;
+    }
+    m_description = "Gravity Task - target frame: " + targetName + ".";
+    m_isInitialized = true;
+    return true;
+}
+
+void GravityTask::storePart(const Vector3d& v, int first, std::ptrdiff_t instance)
+{
+    const std::size_t N = m_kinDyn->getBatchSize();
+    if (m_sp.size() != 6 * N) {
+        m_sp.assign(6 * N, 0.0);
+        for (std::size_t i = 0; i < N; i++) m_sp[6 * i + 2] = 1.0;   // m_desiredZDirectionBody starts at e_z (GravityTask.cpp:71)
+    }
+    for (std::size_t i = 0; i < N; i++)
+        if (instance < 0 || static_cast<std::size_t>(instance) == i)
+            for (int c = 0; c < 3; c++) m_sp[6 * i + first + c] = v[c];
+    m_spVersion++;
+    m_isSetPointSetAtLeastOnce = true;
+}
+
+bool GravityTask::setDesiredGravityDirectionInTargetFrame(const Vector3d& g, std::ptrdiff_t instance)
+{
+    if (!m_kinDyn) return false;
+    const double nrm = std::sqrt(g[0] * g[0] + g[1] * g[1] + g[2] * g[2]);   // normalised as GravityTask.cpp:204-206
+    storePart(nrm > 0 ? Vector3d{g[0] / nrm, g[1] / nrm, g[2] / nrm} : g, 0, instance);
+    return true;
+}
+
+bool GravityTask::setFeedForwardVelocityInTargetFrame(const Vector3d& ff, std::ptrdiff_t instance)
+{
+    if (!m_kinDyn) return false;
+    storePart(ff, 3, instance);
+    return true;
+}
+
+bool GravityTask::setSetPoint(const Vector3d& g, const Vector3d& ff, std::ptrdiff_t instance)
+{
+    return setDesiredGravityDirectionInTargetFrame(g, instance) && setFeedForwardVelocityInTargetFrame(ff, instance);
+}
+
+bool GravityTask::update()
+{
+    m_isValid = false;
+    if (!m_isInitialized) {
+        log()->error("[GravityTask::update] The task is not initialized. Please call initialize method.");
+        return m_isValid;
+    }
+    if (!m_isSetPointSetAtLeastOnce) {
+        log()->error("[GravityTask::update] The set point has not been set at least once.");
+        return m_isValid;
+    }
+    const int i = inspected();
+    if (i >= 0 && m_A.rows == size()) {
+        SE3d pose;
+        std::array<double, 9> R;
+        System::MatrixXd J;
+        if (!m_kinDyn->getWorldTransform(m_targetFrameIndex, pose, R, i) || !m_kinDyn->getFrameFreeFloatingJacobian(m_targetFrameIndex, J, i)) {
+            log()->error("[GravityTask::update] Unable to get the frame jacobian.");
+            return m_isValid;
+        }
+        const double* sp = m_sp.data() + 6 * i;
+        double z[3], ff[3];
+        for (int r = 0; r < 3; r++) {
+            z[r] = R[3 * r] * sp[0] + R[3 * r + 1] * sp[1] + R[3 * r + 2] * sp[2];
+            ff[r] = R[3 * r] * sp[3] + R[3 * r + 1] * sp[4] + R[3 * r + 2] * sp[5];
+        }
+        // A = [1 0 0; 0 1 0] J_angular, b = ff_xy - kp [0 -1 0; 1 0 0] z  (GravityTask.cpp:56-62, 182-185)
+        setRow(m_A, 0, m_robotVelocityVariable.offset, J, 3);
+        setRow(m_A, 1, m_robotVelocityVariable.offset, J, 4);
+        m_b[0] = ff[0] + m_kp * z[1];
+        m_b[1] = ff[1] - m_kp * z[0];
+    }
+    m_isValid = true;
+    return m_isValid;
+}
+
+bool GravityTask::fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>&) const
+{
+    d = blfik_task_desc{};
+    d.type = BLFIK_TASK_GRAVITY, d.frame = m_targetFrameIndex, d.ref_frame = -1, d.controller_enabled = 1;
+    for (int c = 0; c < 3; c++) d.mask[c] = 1, d.kp_linear[c] = m_kp;
+    return m_isInitialized;
+}
+
 // =================================================================== JointTrackingTask
 bool JointTrackingTask::initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler)
 {

@@ -212,6 +212,29 @@ static void testTaskInitializationAndAddTaskRules(const char* modelPath)
     bad.addVariable("other", 29);
     REQUIRE_FALSE(ik.finalize(bad));                         // the robot velocity variable is not in the handler
 
+    // DistanceTask / GravityTask initialisation rules (DistanceTask.cpp:95-175, GravityTask.cpp:76-147)
+    {
+        DistanceTask dist;
+        auto dh = std::make_shared<StdImplementation>();
+        dh->setParameter("robot_velocity_variable_name", robotVelocity);
+        REQUIRE(dist.setKinDyn(kinDyn));
+        REQUIRE_FALSE(dist.initialize(dh));                  // kp missing
+        dh->setParameter("kp", 2.0);
+        REQUIRE_FALSE(dist.initialize(dh));                  // target_frame_name missing
+        dh->setParameter("target_frame_name", "l_hand_palm"), dh->setParameter("reference_frame_name", "not_a_frame");
+        REQUIRE_FALSE(dist.initialize(dh));                  // unknown reference frame
+        dh->setParameter("reference_frame_name", "");
+        REQUIRE(dist.initialize(dh) && dist.size() == 1 && dist.type() == IKLinearTask::Type::equality);
+        GravityTask grav;
+        auto gh = std::make_shared<StdImplementation>();
+        gh->setParameter("robot_velocity_variable_name", robotVelocity), gh->setParameter("kp", 2.0);
+        REQUIRE(grav.setKinDyn(kinDyn));
+        REQUIRE_FALSE(grav.initialize(gh));                  // target_frame_name missing
+        gh->setParameter("target_frame_name", "chest");
+        REQUIRE(grav.initialize(gh) && grav.size() == 2);
+        REQUIRE(IKLinearTaskFactory::createInstance("DistanceTask") != nullptr && IKLinearTaskFactory::createInstance("GravityTask") != nullptr);
+    }
+
     // integrator error conventions
     ForwardEuler<FloatingBaseSystemVelocityKinematics> integrator;
     REQUIRE_FALSE(integrator.integrate(0s, 10ms));           // no dynamical system
@@ -303,6 +326,50 @@ static void testTaskMatrices(const char* modelPath)
     for (std::size_t j = 0; j < 23; j++) {   // JointTrackingTaskTest.cpp:84-114: b = -Kp s for a zero set-point, A = [0 I]
         REQUIRE(std::abs(jt.getB()[j] + 3.0 * s[j]) < 1e-13);
         REQUIRE(jt.getA()(j, 10 + 6 + j) == 1.0 && jt.getA()(j, 10 + j) == 0.0);
+    }
+
+    // DistanceTaskTest.cpp / GravityTaskTest.cpp: A and b against the formulas of DistanceTask.cpp:196-243, GravityTask.cpp:160-199
+    DistanceTask dist;
+    auto dh = std::make_shared<StdImplementation>();
+    dh->setParameter("robot_velocity_variable_name", robotVelocity), dh->setParameter("kp", 2.5);
+    dh->setParameter("target_frame_name", "l_hand_palm"), dh->setParameter("reference_frame_name", "r_sole");
+    REQUIRE(dist.setKinDyn(kinDyn) && dist.initialize(dh) && dist.setVariablesHandler(vh));
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(dist.update());   // no set-point yet
+    log()->setLevel(Logger::Level::warn);
+    REQUIRE(dist.setDesiredDistance(-0.4) && dist.update());   // the sign is dropped (DistanceTask.cpp:240)
+    SE3d hand, sole;
+    MatrixXd Jh, Js;
+    REQUIRE(kinDyn->getWorldTransform(kinDyn->getFrameIndex("l_hand_palm"), hand, R) && kinDyn->getWorldTransform(kinDyn->getFrameIndex("r_sole"), sole, R));
+    REQUIRE(kinDyn->getFrameFreeFloatingJacobian(kinDyn->getFrameIndex("l_hand_palm"), Jh) && kinDyn->getFrameFreeFloatingJacobian(kinDyn->getFrameIndex("r_sole"), Js));
+    const Vector3d dv{hand.p[0] - sole.p[0], hand.p[1] - sole.p[1], hand.p[2] - sole.p[2]};
+    const double dn = std::sqrt(dv[0] * dv[0] + dv[1] * dv[1] + dv[2] * dv[2]);
+    REQUIRE(std::abs(dist.getDistance() - dn) < 1e-14 && std::abs(dist.getB()[0] - 2.5 * (0.4 - dn)) < 1e-13);
+    double worst = 0, baseCols = 0;
+    for (std::size_t c = 0; c < 29; c++) {
+        double a = 0;
+        for (int r = 0; r < 3; r++) a += dv[r] * (Jh(r, c) - Js(r, c));
+        worst = std::max(worst, std::abs(dist.getA()(0, 10 + c) - a / dn));
+        if (c < 6) baseCols = std::max(baseCols, std::abs(dist.getA()(0, 10 + c)));
+    }
+    REQUIRE(worst < 1e-14 && baseCols < 1e-14);   // a relative distance does not depend on the base (getRelativeJacobian has no base block)
+    GravityTask grav;
+    auto gh = std::make_shared<StdImplementation>();
+    gh->setParameter("robot_velocity_variable_name", robotVelocity), gh->setParameter("kp", 3.0), gh->setParameter("target_frame_name", "chest");
+    REQUIRE(grav.setKinDyn(kinDyn) && grav.initialize(gh) && grav.setVariablesHandler(vh));
+    REQUIRE(grav.setSetPoint({0.0, 0.6, 1.8}, {0.1, -0.2, 0.3}) && grav.update());
+    SE3d chest;
+    MatrixXd Jchest;
+    REQUIRE(kinDyn->getWorldTransform(kinDyn->getFrameIndex("chest"), chest, R) && kinDyn->getFrameFreeFloatingJacobian(kinDyn->getFrameIndex("chest"), Jchest));
+    REQUIRE(grav.getA().rows == 2 && maxAbsDiff(grav.getA(), 0, 10, Jchest, 3) == 0.0);
+    {
+        const double nz = std::sqrt(0.6 * 0.6 + 1.8 * 1.8), z[3] = {0.0, 0.6 / nz, 1.8 / nz}, f[3] = {0.1, -0.2, 0.3};
+        double zw[3], fw[3];
+        for (int r = 0; r < 3; r++) {
+            zw[r] = R[3 * r] * z[0] + R[3 * r + 1] * z[1] + R[3 * r + 2] * z[2];
+            fw[r] = R[3 * r] * f[0] + R[3 * r + 1] * f[1] + R[3 * r + 2] * f[2];
+        }
+        REQUIRE(std::abs(grav.getB()[0] - (fw[0] + 3.0 * zw[1])) < 1e-13 && std::abs(grav.getB()[1] - (fw[1] - 3.0 * zw[0])) < 1e-13);
     }
 }
 

@@ -32,9 +32,12 @@ TASK_JOINT_TRACKING = 3
 TASK_JOINT_LIMITS = 4
 TASK_JOINT_VELOCITY_LIMITS = 5
 TASK_R3 = 6
+TASK_DISTANCE = 7
+TASK_GRAVITY = 8
 
 TYPE_NAMES = {TASK_SE3: "SE3Task", TASK_COM: "CoMTask", TASK_SO3: "SO3Task", TASK_JOINT_TRACKING: "JointTrackingTask",
-              TASK_JOINT_LIMITS: "JointLimitsTask", TASK_JOINT_VELOCITY_LIMITS: "JointVelocityLimitsTask", TASK_R3: "R3Task"}
+              TASK_JOINT_LIMITS: "JointLimitsTask", TASK_JOINT_VELOCITY_LIMITS: "JointVelocityLimitsTask", TASK_R3: "R3Task",
+              TASK_DISTANCE: "DistanceTask", TASK_GRAVITY: "GravityTask"}
 
 
 def _vec3(v) -> np.ndarray:
@@ -62,14 +65,16 @@ class TaskSpec:
     upper: Optional[np.ndarray] = None
     lower: Optional[np.ndarray] = None
     sampling_time: float = 0.0
+    ref_frame: int = -1          # DistanceTask: reference frame (-1: the world origin)
+    threshold: float = 0.001     # DistanceTask: distance_numeric_threshold
 
     def rows(self, n: int) -> int:
         nm = int(sum(bool(m) for m in self.mask))
-        return {TASK_SE3: nm + 3, TASK_COM: nm, TASK_R3: nm, TASK_SO3: 3, TASK_JOINT_TRACKING: n,
+        return {TASK_SE3: nm + 3, TASK_COM: nm, TASK_R3: nm, TASK_SO3: 3, TASK_DISTANCE: 1, TASK_GRAVITY: 2, TASK_JOINT_TRACKING: n,
                 TASK_JOINT_LIMITS: 2 * n, TASK_JOINT_VELOCITY_LIMITS: 2 * n}[self.type]
 
     def setpoint_len(self, n: int) -> int:
-        return {TASK_SE3: 13, TASK_COM: 6, TASK_SO3: 7, TASK_R3: 6, TASK_JOINT_TRACKING: 2 * n,
+        return {TASK_SE3: 13, TASK_COM: 6, TASK_SO3: 7, TASK_R3: 6, TASK_DISTANCE: 1, TASK_GRAVITY: 6, TASK_JOINT_TRACKING: 2 * n,
                 TASK_JOINT_LIMITS: 0, TASK_JOINT_VELOCITY_LIMITS: 0}[self.type]
 
     @property
@@ -98,6 +103,23 @@ def so3_task(model: KinematicModel, name: str, frame_name: str, kp_angular, prio
 
 def r3_task(model: KinematicModel, name: str, frame_name: str, kp_linear, priority=0, weight=None, mask=(True, True, True)) -> TaskSpec:
     t = TaskSpec(name, TASK_R3, priority, model.frame_index(frame_name), tuple(mask), True, _vec3(kp_linear))
+    t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
+    return t
+
+
+def distance_task(model: KinematicModel, name: str, target_frame_name: str, kp: float, priority=1, weight=None,
+                  reference_frame_name: str = "", distance_numeric_threshold: float = 0.001) -> TaskSpec:
+    """keys: kp, target_frame_name, reference_frame_name (optional), distance_numeric_threshold (src/IK/src/DistanceTask.cpp:95-175)."""
+    t = TaskSpec(name, TASK_DISTANCE, priority, model.frame_index(target_frame_name), (True, True, True), True, _vec3(kp))
+    t.ref_frame = model.frame_index(reference_frame_name) if reference_frame_name else -1
+    t.threshold = float(distance_numeric_threshold)
+    t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
+    return t
+
+
+def gravity_task(model: KinematicModel, name: str, target_frame_name: str, kp: float, priority=1, weight=None) -> TaskSpec:
+    """keys: kp, target_frame_name (src/IK/src/GravityTask.cpp:76-147)."""
+    t = TaskSpec(name, TASK_GRAVITY, priority, model.frame_index(target_frame_name), (True, True, True), True, _vec3(kp))
     t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
     return t
 

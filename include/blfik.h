@@ -58,7 +58,9 @@ typedef enum {
     BLFIK_TASK_JOINT_TRACKING = 3,        /* src/IK/src/JointTrackingTask.cpp       */
     BLFIK_TASK_JOINT_LIMITS = 4,          /* src/IK/src/JointLimitsTask.cpp         */
     BLFIK_TASK_JOINT_VELOCITY_LIMITS = 5, /* src/IK/src/JointVelocityLimitsTask.cpp */
-    BLFIK_TASK_R3 = 6                     /* src/IK/src/R3Task.cpp                  */
+    BLFIK_TASK_R3 = 6,                    /* src/IK/src/R3Task.cpp                  */
+    BLFIK_TASK_DISTANCE = 7,              /* src/IK/src/DistanceTask.cpp            */
+    BLFIK_TASK_GRAVITY = 8                /* src/IK/src/GravityTask.cpp             */
 } blfik_task_type;
 
 /* where a caller-provided batch buffer lives */
@@ -110,6 +112,8 @@ typedef struct {
     const double* upper_limits; /* [n] JointLimitsTask (positions) / JointVelocityLimitsTask (velocities) */
     const double* lower_limits; /* [n]                                                  */
     double sampling_time;       /* "sampling_time" [s]      JointLimitsTask             */
+    int32_t ref_frame;          /* "reference_frame_name" of DistanceTask, -1 = world origin ("")   */
+    double distance_threshold;  /* "distance_numeric_threshold" of DistanceTask (0 -> 0.001)       */
 } blfik_task_desc;
 
 /* ADMM + polish parameters.  rho/sigma/alpha have OSQP's meaning (osqp v0.6.3); the
@@ -155,7 +159,9 @@ int blfik_get_state(blfik_problem* problem, double* base_pos, double* base_quat,
 /* replaces task->setSetPoint(...) (SE3Task.cpp:323-336, CoMTask.cpp:237-247, SO3Task.cpp:194-206,
  * JointTrackingTask.cpp:162-185, R3Task.cpp:245-256).  data is [N][len] with len:
  *   SE3: 13 = p_d(3) q_d(4) v_ff(3) w_ff(3)     CoM / R3: 6 = p_d(3) v_ff(3)
- *   SO3:  7 = q_d(4) w_ff(3)                    JointTracking: 2n = s_d(n) sdot_d(n)          */
+ *   SO3:  7 = q_d(4) w_ff(3)                    JointTracking: 2n = s_d(n) sdot_d(n)
+ *   Distance: 1 = desired distance (DistanceTask::setDesiredDistance; gain kp_linear[0], frame = target_frame_name)
+ *   Gravity:  6 = desired gravity direction in the target frame (3) + feed-forward (3)  (GravityTask::setSetPoint; kp_linear[0]) */
 int blfik_set_setpoint(blfik_problem* problem, int32_t task, const double* data, int32_t mem);
 int32_t blfik_setpoint_len(const blfik_problem* problem, int32_t task);
 

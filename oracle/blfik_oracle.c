@@ -233,6 +233,8 @@ int orc_setpoint_len(int type, int n)
     case ORC_TASK_SO3: return 7;             /* q_d(4) w_ff(3)                  */
     case ORC_TASK_R3: return 6;              /* p_d(3) v_ff(3)                  */
     case ORC_TASK_JOINT_TRACKING: return 2 * n; /* s_d(n) sdot_d(n)             */
+    case ORC_TASK_DISTANCE: return 1;        /* desired distance                 */
+    case ORC_TASK_GRAVITY: return 6;         /* z_des in the body (3) ff (3)     */
     default: return 0;
     }
 }
@@ -246,6 +248,8 @@ int orc_task_rows(const orc_task* t, int n)
     case ORC_TASK_COM: return mask_count(t->mask);
     case ORC_TASK_R3: return mask_count(t->mask);
     case ORC_TASK_SO3: return 3;
+    case ORC_TASK_DISTANCE: return 1;
+    case ORC_TASK_GRAVITY: return 2;
     case ORC_TASK_JOINT_TRACKING: return n;
     case ORC_TASK_JOINT_LIMITS: return 2 * n;
     case ORC_TASK_JOINT_VELOCITY_LIMITS: return 2 * n;
@@ -347,6 +351,39 @@ int orc_task_update(const orc_model* m, const orc_task* t, const double* link_R,
             memcpy(A + c * nv, Jd + (3 + c) * nv, sizeof(double) * nv);
         }
         if (Jd != J) free(Jd);
+        break;
+    }
+    case ORC_TASK_DISTANCE: { /* DistanceTask.cpp:178-229: A = p' J_lin / max(thr, |p|), b = kp (d_des - |p|) */
+        double J[6 * 64], J2[6 * 64], R[9], pt[3], pr[3] = {0, 0, 0};
+        if (nv > 64) return -1;
+        orc_frame_pose(m, link_R, link_p, t->frame, R, pt);
+        orc_frame_jacobian(m, link_R, link_p, t->frame, J);
+        if (t->ref_frame >= 0) {
+            /* relative position / relative Jacobian: d/dt |p_t - p_ref| = u'(v_t - v_ref), u = (p_t - p_ref)/d */
+            orc_frame_pose(m, link_R, link_p, t->ref_frame, R, pr);
+            orc_frame_jacobian(m, link_R, link_p, t->ref_frame, J2);
+            for (int i = 0; i < 3 * nv; i++) J[i] -= J2[i];
+        }
+        const double dv[3] = {pt[0] - pr[0], pt[1] - pr[1], pt[2] - pr[2]};
+        const double d = sqrt(dv[0] * dv[0] + dv[1] * dv[1] + dv[2] * dv[2]);
+        const double den = d > t->threshold ? d : t->threshold;
+        for (int c = 0; c < nv; c++) A[c] = (dv[0] * J[c] + dv[1] * J[nv + c] + dv[2] * J[2 * nv + c]) / den;
+        b[0] = t->kp_lin[0] * (sp[0] - d);
+        break;
+    }
+    case ORC_TASK_GRAVITY: { /* GravityTask.cpp:149-185: A = [1 0 0; 0 1 0] J_ang, b = (R ff)_{0,1} - kp [0 -1 0; 1 0 0] R z_des */
+        double J[6 * 64], R[9], pf[3], z[3], ff[3], zb[3] = {sp[0], sp[1], sp[2]};
+        if (nv > 64) return -1;
+        const double zn = sqrt(zb[0] * zb[0] + zb[1] * zb[1] + zb[2] * zb[2]);
+        for (int c = 0; c < 3; c++) zb[c] /= zn; /* setDesiredGravityDirectionInTargetFrame normalises (:187-194) */
+        orc_frame_pose(m, link_R, link_p, t->frame, R, pf);
+        orc_frame_jacobian(m, link_R, link_p, t->frame, J);
+        mat3_vec(R, zb, z);
+        mat3_vec(R, sp + 3, ff);
+        memcpy(A, J + 3 * nv, sizeof(double) * nv);
+        memcpy(A + nv, J + 4 * nv, sizeof(double) * nv);
+        b[0] = ff[0] + t->kp_lin[0] * z[1];
+        b[1] = ff[1] - t->kp_lin[0] * z[0];
         break;
     }
     case ORC_TASK_JOINT_TRACKING: /* JointTrackingTask.cpp:65-67 (A=[0 I]), :151 (b) */

@@ -50,7 +50,9 @@ enum {
     ORC_TASK_JOINT_TRACKING = 3,
     ORC_TASK_JOINT_LIMITS = 4,
     ORC_TASK_JOINT_VELOCITY_LIMITS = 5,
-    ORC_TASK_R3 = 6
+    ORC_TASK_R3 = 6,
+    ORC_TASK_DISTANCE = 7,
+    ORC_TASK_GRAVITY = 8
 };
 
 /* Kinematic tree, link 0 = floating base, parent[k] < k.  Link k (k>=1) is the
@@ -85,6 +87,8 @@ typedef struct {
     const double* upper;    /* [n]  JointLimitsTask / JointVelocityLimitsTask   */
     const double* lower;    /* [n]                                              */
     double sampling_time;   /* JointLimitsTask                                  */
+    int ref_frame;          /* DistanceTask: reference frame, -1 = world origin  */
+    double threshold;       /* DistanceTask: distance_numeric_threshold          */
 } orc_task;
 
 typedef struct {

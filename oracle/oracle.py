@@ -31,7 +31,8 @@ class OrcTask(C.Structure):
     _fields_ = [("type", C.c_int), ("priority", C.c_int), ("frame", C.c_int), ("mask", C.c_int * 3),
                 ("controller_enabled", C.c_int), ("kp_lin", C.c_double * 3), ("kp_ang", C.c_double * 3),
                 ("kp_joint", c_double_p), ("weight", c_double_p), ("klim", c_double_p),
-                ("upper", c_double_p), ("lower", c_double_p), ("sampling_time", C.c_double)]
+                ("upper", c_double_p), ("lower", c_double_p), ("sampling_time", C.c_double),
+                ("ref_frame", C.c_int), ("threshold", C.c_double)]
 
 
 class OrcSettings(C.Structure):
@@ -112,6 +113,8 @@ class Oracle:
             ct.kp_joint, ct.weight, ct.klim = keep(t.kp_joint), keep(t.weight), keep(t.klim)
             ct.upper, ct.lower = keep(t.upper), keep(t.lower)
             ct.sampling_time = float(t.sampling_time)
+            ct.ref_frame = int(getattr(t, 'ref_frame', -1))
+            ct.threshold = float(getattr(t, 'threshold', 0.001))
         self.ctasks = arr
         self.m = sum(t.rows(self.n) for t in self.tasks if t.priority == 0)
 

@@ -566,3 +566,135 @@ def test_setpoint_trajectories_closed_loop(path):
     with pytest.raises(capi.BlfikError):
         prob.set_setpoint_trajectory(6, amps[1], 1.0, phases[1])   # JointTrackingTask has no trajectory generator
     prob.close(), whole.close()
+
+
+def _ergo_distance_gravity_problem(hard):
+    """ergoCub-23 with the two rank-1 tasks of SURVEY 8(f) mixed into the C3 set: the left hand kept at a distance from the
+    right sole (DistanceTask with a reference frame), the right hand at a distance from the world origin, the chest kept
+    upright (GravityTask); as hard constraints they add rows to the equality block, as costs rows to the weighted stack."""
+    m = M.ergocub23()
+    n = m.n
+    prio = 0 if hard else 1
+    tasks = [T.se3_task(m, "lf", "l_sole", 5.0, 5.0), T.com_task(m, "com", 5.0, mask=(True, True, False)),
+             T.distance_task(m, "dist_hand", "l_hand_palm", 4.0, priority=prio, weight=None if hard else [7.0], reference_frame_name="r_sole"),
+             T.distance_task(m, "dist_origin", "r_hand_palm", 3.0, priority=1, weight=[2.0]),
+             T.gravity_task(m, "chest_up", "chest", 6.0, priority=prio, weight=None if hard else [3.0, 4.0]),
+             T.joint_tracking_task(m, "reg", np.full(n, 2.0), priority=1, weight=np.full(n, 0.5)),
+             T.joint_limits_task(m, "lim", np.full(n, 0.5), 0.01)]
+    return m, tasks
+
+
+@pytest.mark.parametrize("path", PATHS)
+@pytest.mark.parametrize("hard", [True, False])
+def test_distance_and_gravity_tasks_vs_oracle(hard, path):
+    """DistanceTask.cpp:196-243 and GravityTask.cpp:160-199 inside the tick: assembled H, g, equality rows within 1e-12
+    of the oracle's, nu within 1e-5, then a 20-tick closed loop in lock-step with the oracle."""
+    m, tasks = _ergo_distance_gravity_problem(hard)
+    n, N = m.n, 96
+    rng = np.random.default_rng(17)
+    w3 = W.config(3)
+    inp = W.synth_inputs(w3, N, 5)
+    p0, q0, s0 = inp.base_pos.copy(), inp.base_quat.copy(), inp.s.copy()
+    o = Oracle(m, tasks)
+    # set-points: the current pose of the foot and CoM plus a small offset, distances / attitude slightly off the current ones
+    sps = [np.zeros((N, 13)), np.zeros((N, 6)), np.zeros((N, 1)), np.zeros((N, 1)), np.zeros((N, 6)), np.zeros((N, 2 * n)), None]
+    for i in range(N):
+        R, P = o.fk(p0[i], q0[i], s0[i])
+        Rf, pf = o.frame_pose(R, P, tasks[0].frame)
+        sps[0][i, :3] = pf
+        sps[0][i, 3:7] = W.rot_to_quat(Rf[None])[0]
+        c, _ = o.com(R, P)
+        sps[1][i, :3] = c + rng.normal(0, 0.01, 3)
+        d = o.frame_pose(R, P, tasks[2].frame)[1] - o.frame_pose(R, P, tasks[2].ref_frame)[1]
+        sps[2][i, 0] = np.linalg.norm(d) + rng.normal(0, 0.02)
+        sps[3][i, 0] = np.linalg.norm(o.frame_pose(R, P, tasks[3].frame)[1]) + rng.normal(0, 0.02)
+        Rc, _ = o.frame_pose(R, P, tasks[4].frame)
+        sps[4][i, :3] = 1.7 * (Rc[2] + rng.normal(0, 0.03, 3))          # not normalised on purpose (GravityTask.cpp:204-206)
+        sps[4][i, 3:] = rng.normal(0, 0.05, 3)
+        sps[5][i, :n] = s0[i] + rng.normal(0, 0.05, n)
+    model, prob = make(m, tasks, N, path)
+    prob.set_state(p0, q0, s0)
+    for t, sp in enumerate(sps):
+        if sp is not None:
+            prob.set_setpoint(t, sp)
+    prob.debug_enable(True)
+    prob.tick(1, 0.01)
+    H, g = prob.debug_get(capi.DEBUG_H), prob.debug_get(capi.DEBUG_G)
+    Ce, be = prob.debug_get(capi.DEBUG_CEQ), prob.debug_get(capi.DEBUG_BEQ)
+    me = prob.me
+    assert me == (6 + 2 + 1 + 2 if hard else 8)
+    nu = prob.get_output()
+    st, _ = prob.get_status()
+    assert np.all(st == 0)
+    for i in range(0, N, 7):
+        Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [None if sp is None else sp[i] for sp in sps])
+        assert np.abs(H[i] - Ho).max() <= 1e-12 * (1 + np.abs(Ho).max())
+        assert np.abs(g[i] - go).max() <= 1e-12 * (1 + np.abs(go).max())
+        assert np.abs(Ce[i] - Co[:me]).max() <= TOL_KIN * (1 + np.abs(Co).max())
+        assert np.abs(be[i] - u[:me]).max() <= 1e-12 * (1 + np.abs(u[:me]).max())
+    prob.debug_enable(False)
+    nur, str_, _ = o.tick_batch(p0.copy(), q0.copy(), s0.copy(), sps)
+    assert np.all(str_ == 0) and np.abs(nu - nur).max() <= TOL_NU
+    # closed loop, the oracle re-solving each tick from the GPU's state
+    p, q, s = p0.copy(), q0.copy(), s0.copy()
+    for tick in range(20):
+        pr, qr, sr = p.copy(), q.copy(), s.copy()
+        nur, str_, _ = o.tick_batch(pr, qr, sr, sps, dt_integrate=0.01)
+        prob.tick(1, 0.01, integrate=True, warm_start=True)
+        nu = prob.get_output()
+        p, q, s = prob.get_state()
+        assert np.all(prob.get_status()[0] == 0) and np.all(str_ == 0)
+        assert np.abs(nu - nur).max() <= TOL_NU
+        assert np.abs(s - (sr + (nu - nur)[:, 6:] * 0.01)).max() <= TOL_STATE
+    # the controlled quantities moved towards their set-points
+    i = 0
+    R, P = o.fk(p[i], q[i], s[i])
+    d = o.frame_pose(R, P, tasks[2].frame)[1] - o.frame_pose(R, P, tasks[2].ref_frame)[1]
+    R0, P0 = o.fk(p0[i], q0[i], s0[i])
+    d0 = o.frame_pose(R0, P0, tasks[2].frame)[1] - o.frame_pose(R0, P0, tasks[2].ref_frame)[1]
+    assert abs(np.linalg.norm(d) - sps[2][i, 0]) < abs(np.linalg.norm(d0) - sps[2][i, 0])
+    prob.close()
+
+
+@pytest.mark.parametrize("hard", [True, False])
+def test_distance_gravity_reference_scenarios(hard):
+    """'QP-IK [Distance and Gravity tasks]' / '... Unconstrained' (QPInverseKinematicsTest.cpp:800-1063) on the GPU: 30 joints,
+    30 ticks of 10 ms, final distance within 2e-2 (relative) and body-frame gravity within 2e-2, in lock-step with the oracle
+    (the oracle re-solves every tick from the GPU's state)."""
+    sc = S.distance_gravity_scenario(30, hard=hard)
+    N = 4
+    n = sc.model.n
+    rng = np.random.default_rng(4)
+    p0 = np.tile(sc.p0, (N, 1)); q0 = np.tile(sc.q0, (N, 1)); s0 = sc.s0[None] + rng.normal(0, 0.02, (N, n))
+    s0[0] = sc.s0
+    model, prob = make(sc.model, sc.tasks, N)
+    prob.set_state(p0, q0, s0)
+    sps = S.tile_setpoints(sc, N)
+    for t, sp in enumerate(sps):
+        prob.set_setpoint(t, sp)
+    o = Oracle(sc.model, sc.tasks)
+    p, q, s = p0.copy(), q0.copy(), s0.copy()
+    for tick in range(S.TICKS):
+        pr, qr, sr = p.copy(), q.copy(), s.copy()
+        pb, qb, sb = p.copy(), q.copy(), s.copy()
+        nur, str_, _ = o.tick_batch(pr, qr, sr, sps, dt_integrate=S.DT)
+        prob.tick(1, S.DT, integrate=True, warm_start=True)
+        nu = prob.get_output()
+        p, q, s = prob.get_state()
+        assert np.all(prob.get_status()[0] == 0) and np.all(str_ == 0)
+        # three task rows leave half of the base twist free (the reference's QP has a singular Hessian there and OSQP returns
+        # whichever point its iteration reaches): the joint velocities are unique, the base twist is compared through the
+        # task rows and the cost instead
+        assert np.abs(nu - nur)[:, 6:].max() <= TOL_NU
+        for i in range(N):
+            H, g, C, l, u = o.assemble(pb[i], qb[i], sb[i], [sp[i] for sp in sps])
+            if hard:
+                assert np.abs(C[:3] @ nu[i] - u[:3]).max() <= 1e-6
+            f = lambda x: 0.5 * x @ H @ x + g @ x
+            assert abs(f(nu[i]) - f(nur[i])) <= 1e-8 * (1 + abs(f(nur[i])))
+    R, P = o.fk(p[0], q[0], s[0])
+    _, pd = o.frame_pose(R, P, sc.frame_distance)
+    Rg, _ = o.frame_pose(R, P, sc.frame_gravity)
+    assert abs(np.linalg.norm(pd) - sc.distance_des) <= 2e-2 * sc.distance_des
+    assert np.abs(Rg[2] - sc.gravity_des).max() < 2e-2
+    prob.close()

@@ -226,3 +226,65 @@ def test_icub_python_test_vector():
         assert status[0] == 0
         outs.append(nu[0])
     assert np.abs(outs[0] - outs[1]).max() > 1e-3
+
+
+def test_distance_and_gravity_task_rows(ergo):
+    """DistanceTaskTest.cpp / GravityTaskTest.cpp check A and b against the formulas of DistanceTask.cpp:196-243 and
+    GravityTask.cpp:160-199; here additionally A is checked as the derivative of the controlled quantity."""
+    m = ergo
+    rng = np.random.default_rng(9)
+    tasks = [T.distance_task(m, "d0", "l_hand_palm", 3.0, weight=[1.0]),
+             T.distance_task(m, "d1", "l_hand_palm", 2.0, weight=[1.0], reference_frame_name="r_sole"),
+             T.gravity_task(m, "g", "chest", 4.0, weight=[1.0, 1.0])]
+    o = Oracle(m, tasks)
+    p, q, s = random_state(m, rng)
+    R, P = o.fk(p, q, s)
+    Rt, pt = o.frame_pose(R, P, tasks[0].frame)
+    Rr, pr = o.frame_pose(R, P, tasks[1].ref_frame)
+    Jt, Jr = o.frame_jacobian(R, P, tasks[0].frame), o.frame_jacobian(R, P, tasks[1].ref_frame)
+    A, b = o.task_update(0, R, P, s, np.array([0.7]))
+    assert A.shape == (1, 6 + m.n)
+    assert np.allclose(A[0], pt @ Jt[:3] / np.linalg.norm(pt), atol=1e-13) and np.isclose(b[0], 3.0 * (0.7 - np.linalg.norm(pt)))
+    A, b = o.task_update(1, R, P, s, np.array([0.2]))
+    d = pt - pr
+    assert np.allclose(A[0], d @ (Jt[:3] - Jr[:3]) / np.linalg.norm(d), atol=1e-13) and np.isclose(b[0], 2.0 * (0.2 - np.linalg.norm(d)))
+    # d|d|/dt = A nu  (finite differences along a random velocity)
+    from helpers import perturb_state
+    nu = rng.normal(size=6 + m.n)
+    eps = 1e-6
+    p2, q2, s2 = perturb_state(p, q, s, nu, eps)
+    R2, P2 = o.fk(p2, q2, s2)
+    d2 = o.frame_pose(R2, P2, tasks[0].frame)[1] - o.frame_pose(R2, P2, tasks[1].ref_frame)[1]
+    assert abs((np.linalg.norm(d2) - np.linalg.norm(d)) / eps - A[0] @ nu) < 1e-5
+    # gravity: A = first two angular rows, b = (R ff)[:2] - kp [0 -1 0; 1 0 0] R z_des, z_des normalised
+    Rc, _ = o.frame_pose(R, P, tasks[2].frame)
+    z = np.array([0.3, -0.2, 2.0])
+    ff = rng.normal(size=3)
+    A, b = o.task_update(2, R, P, s, np.concatenate([z, ff]))
+    assert np.array_equal(A, o.frame_jacobian(R, P, tasks[2].frame)[3:5])
+    zn = Rc @ (z / np.linalg.norm(z))
+    assert np.allclose(b, (Rc @ ff)[:2] - 4.0 * np.array([-zn[1], zn[0]]), atol=1e-13)
+    # at the desired attitude (R z_des = e_z) the feedback vanishes
+    A, b = o.task_update(2, R, P, s, np.concatenate([Rc[2], np.zeros(3)]))
+    assert np.abs(b).max() < 1e-13
+    # below the numeric threshold the Jacobian is divided by the threshold (DistanceTask.cpp:232)
+    tasks[0].threshold = 10.0
+    o2 = Oracle(m, tasks)
+    A2, _ = o2.task_update(0, R, P, s, np.array([0.7]))
+    assert np.allclose(A2[0], pt @ Jt[:3] / 10.0, atol=1e-13)
+
+
+@pytest.mark.parametrize("hard", [True, False])
+def test_distance_gravity_closed_loop(hard):
+    """'QP-IK [Distance and Gravity tasks]' and '... Unconstrained' (QPInverseKinematicsTest.cpp:800-1063, tolerance 2e-2)."""
+    sc = S.distance_gravity_scenario(30, hard=hard)
+    o = Oracle(sc.model, sc.tasks)
+    p, q, s = sc.p0[None].copy(), sc.q0[None].copy(), sc.s0[None].copy()
+    for _ in range(S.TICKS):
+        nu, status, _ = o.tick_batch(p, q, s, S.tile_setpoints(sc, 1), dt_integrate=S.DT)
+        assert status[0] == 0
+    R, P = o.fk(p[0], q[0], s[0])
+    _, pd = o.frame_pose(R, P, sc.frame_distance)
+    Rg, _ = o.frame_pose(R, P, sc.frame_gravity)
+    assert abs(np.linalg.norm(pd) - sc.distance_des) <= 2e-2 * sc.distance_des
+    assert np.abs(Rg[2] - sc.gravity_des).max() < 2e-2
