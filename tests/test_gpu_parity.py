@@ -698,3 +698,26 @@ def test_distance_gravity_reference_scenarios(hard):
     assert abs(np.linalg.norm(pd) - sc.distance_des) <= 2e-2 * sc.distance_des
     assert np.abs(Rg[2] - sc.gravity_des).max() < 2e-2
     prob.close()
+
+
+@pytest.mark.parametrize("cid", [2, 3, 4])
+def test_uniqueness_condition_of_the_bench_workloads(cid):
+    """nu is only comparable where the optimum is unique, i.e. H > 0 on the null space of the equality
+    rows (the box rows can only shrink that space).  Checked on a sample of every bench workload from the H and C_eq the
+    kernel itself assembled: smallest eigenvalue of Z'HZ > 1e-8 and C_eq of full row rank."""
+    w = W.config(cid)
+    N = 512
+    inp = W.synth_inputs(w, N, cid)
+    model, prob = make(w.model, w.tasks, N)
+    prob.set_inputs(inp)
+    prob.debug_enable(True)
+    prob.tick(1, w.dt)
+    H, Ce = prob.debug_get(capi.DEBUG_H), prob.debug_get(capi.DEBUG_CEQ)
+    worst_eig, worst_sv = np.inf, np.inf
+    for i in range(0, N, 4):
+        U, sv, Vt = np.linalg.svd(Ce[i])
+        worst_sv = min(worst_sv, sv.min())
+        Z = Vt[len(sv):].T
+        worst_eig = min(worst_eig, np.linalg.eigvalsh(Z.T @ H[i] @ Z).min())
+    assert worst_sv > 1e-3 and worst_eig > 1e-8, (worst_sv, worst_eig)
+    prob.close()
