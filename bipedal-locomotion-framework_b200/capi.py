@@ -16,7 +16,7 @@ from .models import KinematicModel
 from .tasks import TaskSpec
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libblfik_cuda.so")
+LIB_PATH = os.environ.get("BLFIK_LIBRARY") or os.path.join(_HERE, "libblfik_cuda.so")   # BLFIK_LIBRARY: an alternative build (A/B timing)
 _lib = None
 
 MEM_HOST, MEM_DEVICE = 0, 1

@@ -207,6 +207,7 @@ struct blfik_problem {
     bool tasks_dirty = true;
     double *base_pos = nullptr, *base_quat = nullptr, *s = nullptr, *nu = nullptr, *wx = nullptr, *wz = nullptr, *wy = nullptr;
     int *status = nullptr, *iters = nullptr;
+    int* work_counter = nullptr;   // dynamic hand-out of robots in the register-resident kernel
     unsigned long long* d_count = nullptr;
     bool state_set = false, ticked = false;
     DebugOut dbg = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -311,6 +312,7 @@ template <int NV, int KP>
 static void pick_fast(blfik_problem* p)
 {
     p->fast_kernel = blfik_tick_fast_kernel<NV, KP>;
+    p->fast_wpb = FastDims<NV, KP>::WARPS;   // the kernel's launch bound
     p->F = make_fast_layout<NV, KP>(p->n + 1);
     // the control-law buffer ([ntasks][12]) lives in the U region during K2
     // (it always fits: ntasks * 12 <= 32 * 12 <= NV * LDG for every instantiation with NV >= 29, KP >= 16)
@@ -612,7 +614,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
             const size_t fshared = (size_t)p->F.sh_total * sizeof(double);
             const size_t fper = (size_t)p->F.total * sizeof(double);
             int fw = (int)((sm_total - 3072 - fshared) / (fper + 64));
-            if (fw > 12) fw = 12;            // register file: one block of 12 warps at <= 168 registers per thread (16 warps at 128 spill and run slower)
+            if (fw > p->fast_wpb) fw = p->fast_wpb;   // register file: the instantiation's launch bound (FastDims::WARPS)
             if (fw < p->fast_wpb) p->fast_wpb = fw < 1 ? 1 : fw;   // one block per SM holding all its resident warps
             int fb = fw / p->fast_wpb;
             if (fb < 1) {
@@ -659,7 +661,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
     if ((rc = dev_alloc(p, Ns * 3, &p->base_pos)) || (rc = dev_alloc(p, Ns * 4, &p->base_quat)) || (rc = dev_alloc(p, Ns * n, &p->s)) ||
         (rc = dev_alloc(p, Ns * p->nv, &p->nu)) || (rc = dev_alloc(p, Ns * p->nv, &p->wx)) || (rc = dev_alloc(p, Ns * n, &p->wz)) ||
         (rc = dev_alloc(p, Ns * n, &p->wy)) || (rc = dev_alloc(p, Ns, &p->status)) || (rc = dev_alloc(p, Ns, &p->iters)) ||
-        (rc = dev_alloc(p, 1, &p->d_count)) || (rc = dev_alloc(p, p->tasks.size(), &p->d_tasks)))
+        (rc = dev_alloc(p, 1, &p->d_count)) || (rc = dev_alloc(p, p->tasks.size(), &p->d_tasks)) || (rc = dev_alloc(p, 1, &p->work_counter)))
         return bail(rc);
     for (HostTask& h : p->tasks) {
         if (h.sp_len && (rc = dev_alloc(p, Ns * h.sp_len, &h.d_setpoint))) return bail(rc);
@@ -905,6 +907,12 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         { const char* e = getenv("BLFIK_PDAS_FIRST"); FP.pdas_first = e ? atoi(e) : 1; }
         { const char* e = getenv("BLFIK_MAX_ITERS"); if (e) FP.max_total_iters = atoi(e); }
         const long long want = (count + p->fast_wpb - 1) / p->fast_wpb;
+        static const int dynamic_env = [] { const char* e = getenv("BLFIK_DYNAMIC"); return e ? atoi(e) : 1; }();
+        FP.work_counter = nullptr;
+        if (dynamic_env && p->work_counter) {
+            FP.work_counter = p->work_counter;
+            CU(cudaMemsetAsync(p->work_counter, 0, sizeof(int), stream));
+        }
         p->fast_kernel<<<(int)(want < p->fast_grid ? want : p->fast_grid), p->fast_wpb * 32, p->fast_smem, stream>>>(FP);
     } else {
         const long long want = (count + p->warps_per_block - 1) / p->warps_per_block;

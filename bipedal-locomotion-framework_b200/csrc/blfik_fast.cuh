@@ -89,13 +89,47 @@ struct FastParams {
     int pdas_first;       // 1: try the rho-free active-set attempt before ADMM (see the kernel)
     int sync_phases;      // 1: the warps of a block enter K1 and the setup together (block barriers)
     int max_total_iters;  // per-tick budget of mat-vecs (ADMM + polish); exceeding it ends the solve with status 1
+    // Dynamic hand-out of robots: a team (the warps that meet at the phase barriers: a sub-partition group in sync
+    // mode 2, the block in mode 1, a single warp in mode 0) takes the next `team size` robots from a device counter
+    // instead of a fixed stride, so a team that drew expensive robots simply draws fewer.  The host zeroes the
+    // counter before the launch.  nullptr: static striding.
+    int* work_counter;
 };
 
 template <int NV, int KP>
 struct FastDims {
     static constexpr int LDB = ld2odd(NV);
     static constexpr int LDG = ld2odd(KP);
+    // Resident warps per SM (one block per SM).  The small instantiations run 16 warps at 128 registers with the row of N
+    // re-read from shared memory in every mat-vec (measured on C3: 1.31 ms against 1.37 ms for 12 warps with the row in
+    // registers); with more dense rows the 128-register build spills heavily (C4: 2.14 ms against 1.76 ms), so those
+    // keep 12 warps at 168 registers and the row of N in registers.
+    static constexpr int WARPS = (NV <= 29 && KP <= 18) ? 16 : 12;
+    static constexpr bool NROW_SMEM = WARPS > 12;
 };
+
+// y_i = xb_i + sum_j N[i][j] * v[j]: own row streamed from shared memory (rows are 16-byte aligned and an odd number of
+// 16-byte units apart, so the 128-bit loads of a warp are conflict-free), v broadcast
+template <int NV>
+__device__ __forceinline__ double fast_matvec_smem(const double* myrow, const double* v, double xb)
+{
+    double a0 = xb, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    const double2* v2 = reinterpret_cast<const double2*>(v);
+    const double2* n2 = reinterpret_cast<const double2*>(myrow);
+#pragma unroll
+    for (int jj = 0; jj < NV / 2; jj++) {
+        const double2 t = v2[jj], m = n2[jj];
+        if (jj & 1) {
+            a2 = fma(m.x, t.x, a2);
+            a3 = fma(m.y, t.y, a3);
+        } else {
+            a0 = fma(m.x, t.x, a0);
+            a1 = fma(m.y, t.y, a1);
+        }
+    }
+    if (NV & 1) a0 = fma(myrow[NV - 1], v[NV - 1], a0);
+    return (a0 + a1) + (a2 + a3);
+}
 
 // y_i = xb_i + sum_j nrow[j] * v[j], v broadcast from shared memory two doubles per load
 template <int NV>
@@ -331,7 +365,7 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
         xb = mine ? a0 + a1 : 0.0;
     }
     __syncwarp();
-    {
+    if constexpr (!FastDims<NV, KP>::NROW_SMEM) {
         const double2* myn = reinterpret_cast<const double2*>(Ns + (lane < NV ? lane : 0) * LDB);
 #pragma unroll
         for (int jj = 0; jj < NV / 2; jj++) {
@@ -344,7 +378,7 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
 }
 
 template <int NV, int KP>
-__global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParams FP)
+__global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fast_kernel(const FastParams FP)
 {
     constexpr int LDB = FastDims<NV, KP>::LDB;
     constexpr int LDG = FastDims<NV, KP>::LDG;
@@ -398,9 +432,35 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
     // (robots need different numbers of iterations) as they save in fetches (measured: 2.09 ms with, 2.00 ms without),
     // so they are off by default.  Warps past the end of the batch shadow the last robot without writing anything,
     // so that every warp reaches every barrier when they are on.
-    for (long long base0 = P.first + (long long)blockIdx.x * wpb; base0 < P.N; base0 += (long long)gridDim.x * wpb) {
-        const bool active = base0 + wib < P.N;
-        const long long robot = active ? base0 + wib : P.N - 1;
+    __shared__ int s_next[4][2];
+    const bool dynamic = FP.work_counter != nullptr;
+    long long base0 = P.first + (long long)blockIdx.x * wpb;
+    for (int trip = 0;; trip++) {
+        int member = wib;
+        if (dynamic) {
+            int v;
+            if (FP.sync_phases == 2) {
+                const int grp = wib & 3, cnt = (wpb - grp + 3) >> 2;
+                if (wib == grp && lane == 0) s_next[grp][trip & 1] = atomicAdd(FP.work_counter, cnt);
+                asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(cnt * 32) : "memory");
+                v = s_next[grp][trip & 1];
+                member = wib >> 2;
+            } else if (FP.sync_phases == 1) {
+                if (threadIdx.x == 0) s_next[0][trip & 1] = atomicAdd(FP.work_counter, wpb);
+                __syncthreads();
+                v = s_next[0][trip & 1];
+            } else {
+                v = lane == 0 ? atomicAdd(FP.work_counter, 1) : 0;
+                v = __shfl_sync(kFull, v, 0);
+                member = 0;
+            }
+            base0 = P.first + v;
+        } else if (trip > 0) {
+            base0 += (long long)gridDim.x * wpb;
+        }
+        if (base0 >= P.N) break;
+        const bool active = base0 + member < P.N;
+        const long long robot = active ? base0 + member : P.N - 1;
         double* bp = P.base_pos + 3 * robot;
         double* bq = P.base_quat + 4 * robot;
         double* s = P.s + (size_t)n * robot;
@@ -725,7 +785,8 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
             }
 
             if (attempt == first_attempt) phase_barrier(FP.sync_phases, wib, wpb);
-            double nrow[NV];
+            double nrow[NV];   // unused (and eliminated) when the row is streamed from shared memory
+            const double* myrow = Ns + (lane < NV ? lane : 0) * LDB;
             double xb = 0.0;
             if (infeasible) {
                 status = 2;
@@ -754,7 +815,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                         for (int it = 0; it < st.admm_iters; it++) {
                             rvec[lane] = mine ? st.sigma * x + gd + (bounded ? rho_i * z - y : 0.0) : 0.0;
                             __syncwarp();
-                            const double xt = fast_matvec<NV>(nrow, rvec, xb);
+                            const double xt = FastDims<NV, KP>::NROW_SMEM ? fast_matvec_smem<NV>(myrow, rvec, xb) : fast_matvec<NV>(nrow, rvec, xb);
                             __syncwarp();
                             const double xn = st.alpha * xt + (1.0 - st.alpha) * x;
                             rd = st.sigma * fabs(xn - x);
@@ -811,7 +872,7 @@ __global__ void __launch_bounds__(384, 1) blfik_tick_fast_kernel(const FastParam
                         for (int it = 0; it < FP.max_polish_iters; it++) {
                             rvec[lane] = mine ? Q_i * xp + gd : 0.0;
                             __syncwarp();
-                            double x1 = fast_matvec<NV>(nrow, rvec, xb);
+                            double x1 = FastDims<NV, KP>::NROW_SMEM ? fast_matvec_smem<NV>(myrow, rvec, xb) : fast_matvec<NV>(nrow, rvec, xb);
                             __syncwarp();
                             if (a > 0) {
                                 if (act) dA[rank] = x1 - bd;
