@@ -192,8 +192,10 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
     h_packed = torch.from_numpy(prob.pack_inputs(inputs)).pin_memory()
 
     def e2e_step():
-        # the reference-facing call with HOST buffers: one packed record per robot (state + set-points) in, nu + status out;
-        # the buffers are pinned, so the kernel streams them over PCIe itself (blfik_tick_packed, zero-copy)
+        # the reference-facing call with HOST buffers: one packed record per robot (state + set-points) in, nu + status out.
+        # --chunks k >= 1: the copy engine brings the records in k pieces while the kernels of the previous pieces run (on
+        # alternating streams) and write nu / status straight into the pinned host buffers; --chunks 0: the kernel also
+        # reads the records over PCIe itself (blfik_tick_packed zero-copy mode)
         prob.tick_packed(h_packed, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False, nchunks=args.chunks)
 
     def barrier():
@@ -272,7 +274,9 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
                        "instances_per_gpu": n_local, "instances_total": n_global, "dt": w.dt,
                        "parallelism": f"instance-sharded x{world}, no collective", "warm_start": False,
                        "solver": prob_settings, "l2": "256 MiB write between steps (untimed) flushes the 126 MB L2",
-                       "unsolved_instances": unsolved},
+                       "unsolved_instances": unsolved,
+                       "host_tick": ("blfik_tick_packed, zero-copy (kernel reads pinned host records over PCIe)" if args.chunks <= 0 else
+                                     f"blfik_tick_packed, {args.chunks} chunks: copy-engine H2D overlapped with the chunk kernels, results written to pinned host memory by the kernels")},
             "e2e": {"value": ticks_total / (ms_e2e * 1e-3), "unit": "ticks/s",
                     "h2d_bytes_per_step": int(8 * n_local * (7 + n + sp_doubles)),
                     "d2h_bytes_per_step": int(n_local * (8 * nv + 4))},
@@ -310,7 +314,8 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--instances", type=int, default=PER_GPU_INSTANCES, help="instances per GPU")
-    ap.add_argument("--chunks", type=int, default=0, help="host-buffer (e2e) tick: 0 = zero-copy from pinned memory, k >= 1 = k pipeline chunks")
+    ap.add_argument("--chunks", type=int, default=5,
+                    help="host-buffer (e2e) tick: k >= 1 = k pipeline chunks (H2D by the copy engine, chunk kernels on alternating streams, results written to the pinned host buffers by the kernels); 0 = zero-copy, the kernel reads the records over PCIe itself")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -192,6 +192,7 @@ struct HostTask {
 };
 
 constexpr int kMaxChunks = 16;
+constexpr int kCounterSlots = 8;   // work counters of the register-resident kernel, one per launch that may be in flight
 
 struct blfik_problem {
     const blfik_model* model = nullptr;
@@ -230,6 +231,7 @@ struct blfik_problem {
     int njump = 0, has_com = 0;
     // pipelined host-buffer tick (blfik_tick_host)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+    cudaStream_t chunk_stream[2] = {nullptr, nullptr};   // blfik_tick_packed: consecutive chunk kernels alternate, so one fills the SMs the other's tail leaves idle
     cudaEvent_t ev_in[16] = {}, ev_done[16] = {}, ev_start = nullptr;
     double time = 0.0;               // time of the next tick (advanced by integrating ticks; set-point trajectories)
     int packed_len = 0;              // doubles per packed input record: 7 + n + sum of set-point lengths
@@ -661,7 +663,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
     if ((rc = dev_alloc(p, Ns * 3, &p->base_pos)) || (rc = dev_alloc(p, Ns * 4, &p->base_quat)) || (rc = dev_alloc(p, Ns * n, &p->s)) ||
         (rc = dev_alloc(p, Ns * p->nv, &p->nu)) || (rc = dev_alloc(p, Ns * p->nv, &p->wx)) || (rc = dev_alloc(p, Ns * n, &p->wz)) ||
         (rc = dev_alloc(p, Ns * n, &p->wy)) || (rc = dev_alloc(p, Ns, &p->status)) || (rc = dev_alloc(p, Ns, &p->iters)) ||
-        (rc = dev_alloc(p, 1, &p->d_count)) || (rc = dev_alloc(p, p->tasks.size(), &p->d_tasks)) || (rc = dev_alloc(p, 1, &p->work_counter)))
+        (rc = dev_alloc(p, 1, &p->d_count)) || (rc = dev_alloc(p, p->tasks.size(), &p->d_tasks)) || (rc = dev_alloc(p, kCounterSlots, &p->work_counter)))
         return bail(rc);
     for (HostTask& h : p->tasks) {
         if (h.sp_len && (rc = dev_alloc(p, Ns * h.sp_len, &h.d_setpoint))) return bail(rc);
@@ -685,6 +687,8 @@ extern "C" void blfik_problem_destroy(blfik_problem* p)
         for (int c = 0; c < kMaxChunks; c++) cudaEventDestroy(p->ev_in[c]), cudaEventDestroy(p->ev_done[c]);
         cudaEventDestroy(p->ev_start);
         cudaStreamDestroy(p->h2d_stream), cudaStreamDestroy(p->d2h_stream);
+        for (int k = 0; k < 2; k++)
+            if (p->chunk_stream[k]) cudaStreamSynchronize(p->chunk_stream[k]), cudaStreamDestroy(p->chunk_stream[k]);
     }
     if (p->own_stream && p->stream) cudaStreamDestroy(p->stream);
     delete p;
@@ -886,7 +890,7 @@ extern "C" int blfik_debug_get(blfik_problem* p, int32_t what, double* out, int3
 
 // one launch of the tick over robots [first, first + count) on `stream`
 static int launch_tick_range(blfik_problem* p, long long first, long long count, int32_t nticks, double dt, uint32_t flags, cudaStream_t stream,
-                             const double* packed = nullptr, double* nu_host = nullptr, int* status_host = nullptr)
+                             const double* packed = nullptr, double* nu_host = nullptr, int* status_host = nullptr, int counter_slot = 0)
 {
     TickParams P;
     P.m = p->dm, P.tasks = p->d_tasks, P.ntasks = (int)p->tasks.size(), P.first = first, P.N = first + count;   // robots [first, N)
@@ -910,8 +914,8 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         static const int dynamic_env = [] { const char* e = getenv("BLFIK_DYNAMIC"); return e ? atoi(e) : 1; }();
         FP.work_counter = nullptr;
         if (dynamic_env && p->work_counter) {
-            FP.work_counter = p->work_counter;
-            CU(cudaMemsetAsync(p->work_counter, 0, sizeof(int), stream));
+            FP.work_counter = p->work_counter + counter_slot;   // launches that may overlap use different slots
+            CU(cudaMemsetAsync(FP.work_counter, 0, sizeof(int), stream));
         }
         p->fast_kernel<<<(int)(want < p->fast_grid ? want : p->fast_grid), p->fast_wpb * 32, p->fast_smem, stream>>>(FP);
     } else {
@@ -1069,16 +1073,40 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     CU(cudaStreamWaitEvent(p->h2d_stream, p->ev_start, 0));
     CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_start, 0));
     const int nv = p->nv, R = p->packed_len;
+    // results: when nu (and status) are mapped page-locked buffers the kernels write them straight to the host (posted
+    // PCIe writes, no latency to hide), otherwise they are copied back chunk by chunk
+    double* nu_map = nullptr;
+    int* status_map = nullptr;
+    {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, nu) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) nu_map = static_cast<double*>(at.devicePointer);
+        else cudaGetLastError();
+        if (status && nu_map) {
+            if (cudaPointerGetAttributes(&at, status) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) status_map = static_cast<int*>(at.devicePointer);
+            else cudaGetLastError(), nu_map = nullptr;
+        }
+    }
+    for (int k = 0; k < 2; k++) {
+        if (!p->chunk_stream[k]) CU(cudaStreamCreateWithFlags(&p->chunk_stream[k], cudaStreamNonBlocking));
+        CU(cudaStreamWaitEvent(p->chunk_stream[k], p->ev_start, 0));
+    }
+    // the first chunk is half the size of the others: nothing can run until it has arrived
+    auto bound = [&](int c) { return c <= 0 ? 0LL : (c >= nchunks ? p->N : p->N * (2 * c - 1) / (2 * nchunks - 1)); };
     for (int c = 0; c < nchunks; c++) {
-        const long long a = p->N * c / nchunks, b = p->N * (c + 1) / nchunks, cnt = b - a;
+        const long long a = bound(c), b = bound(c + 1), cnt = b - a;
+        if (cnt <= 0) continue;
+        cudaStream_t cs = p->chunk_stream[c & 1];
         CU(cudaMemcpyAsync(p->d_packed + (size_t)R * a, records + (size_t)R * a, (size_t)cnt * R * sizeof(double), cudaMemcpyHostToDevice, p->h2d_stream));
         CU(cudaEventRecord(p->ev_in[c], p->h2d_stream));
-        CU(cudaStreamWaitEvent(p->stream, p->ev_in[c], 0));
-        if ((rc = launch_tick_range(p, a, cnt, 1, dt, flags, p->stream, p->d_packed))) return rc;
-        CU(cudaEventRecord(p->ev_done[c], p->stream));
-        CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_done[c], 0));
-        CU(cudaMemcpyAsync(nu + (size_t)nv * a, p->nu + (size_t)nv * a, (size_t)cnt * nv * sizeof(double), cudaMemcpyDeviceToHost, p->d2h_stream));
-        if (status) CU(cudaMemcpyAsync(status + a, p->status + a, (size_t)cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, p->d2h_stream));
+        CU(cudaStreamWaitEvent(cs, p->ev_in[c], 0));
+        if ((rc = launch_tick_range(p, a, cnt, 1, dt, flags, cs, p->d_packed, nu_map, status_map, c % kCounterSlots))) return rc;
+        CU(cudaEventRecord(p->ev_done[c], cs));
+        CU(cudaStreamWaitEvent(p->stream, p->ev_done[c], 0));   // later work on the problem's stream is ordered after every chunk
+        if (!nu_map) {
+            CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_done[c], 0));
+            CU(cudaMemcpyAsync(nu + (size_t)nv * a, p->nu + (size_t)nv * a, (size_t)cnt * nv * sizeof(double), cudaMemcpyDeviceToHost, p->d2h_stream));
+            if (status) CU(cudaMemcpyAsync(status + a, p->status + a, (size_t)cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, p->d2h_stream));
+        }
     }
     p->state_set = true, p->ticked = true;
     if (flags & BLFIK_TICK_INTEGRATE) p->time += dt;
