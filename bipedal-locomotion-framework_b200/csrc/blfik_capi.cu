@@ -910,6 +910,7 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         { const char* e = getenv("BLFIK_SYNC_PHASES"); FP.sync_phases = e ? atoi(e) : 2; }
         { const char* e = getenv("BLFIK_PDAS_FIRST"); FP.pdas_first = e ? atoi(e) : 1; }
         { const char* e = getenv("BLFIK_MAX_ITERS"); if (e) FP.max_total_iters = atoi(e); }
+        { const char* e = getenv("BLFIK_MAX_AS"); if (e) FP.max_as_iters = atoi(e); }
         const long long want = (count + p->fast_wpb - 1) / p->fast_wpb;
         static const int dynamic_env = [] { const char* e = getenv("BLFIK_DYNAMIC"); return e ? atoi(e) : 1; }();
         FP.work_counter = nullptr;
