@@ -590,8 +590,12 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
     long long want = (N + wpb - 1) / wpb;
     long long cap = (long long)p->num_sms * blocks_per_sm;
     p->grid = (int)(want < cap ? want : cap);
-    if (cudaFuncSetAttribute(blfik_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes) != cudaSuccess ||
-        cudaFuncSetAttribute(blfik_kinematics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes) != cudaSuccess)
+    // The limit is a property of the kernel, not of this problem: several problems of different sizes share the kernels, so
+    // every one of them raises it to the device's opt-in maximum (a smaller, per-problem value would lower it for the others).
+    const int smem_optin = (int)prop.sharedMemPerBlockOptin - 1024;
+    if (p->smem_bytes > (size_t)smem_optin ||
+        cudaFuncSetAttribute(blfik_tick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) != cudaSuccess ||
+        cudaFuncSetAttribute(blfik_kinematics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) != cudaSuccess)
         return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cannot reserve %zu B of shared memory: %s", p->smem_bytes, cudaGetErrorString(cudaGetLastError())));
 
     // ---- register-resident kernel: pick the smallest instantiation that holds (nv, K)
@@ -633,7 +637,8 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
                 const long long fwant = (N + p->fast_wpb - 1) / p->fast_wpb;
                 const long long fcap = (long long)p->num_sms * fb;
                 p->fast_grid = (int)(fwant < fcap ? fwant : fcap);
-                if (cudaFuncSetAttribute((const void*)p->fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->fast_smem) != cudaSuccess)
+                if (p->fast_smem > (size_t)smem_optin ||
+                    cudaFuncSetAttribute((const void*)p->fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) != cudaSuccess)
                     return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cannot reserve %zu B of shared memory for the register-resident kernel: %s",
                                      p->fast_smem, cudaGetErrorString(cudaGetLastError())));
             }

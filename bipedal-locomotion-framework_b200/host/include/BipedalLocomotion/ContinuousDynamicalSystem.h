@@ -11,7 +11,10 @@
 #define BLF_B200_CONTINUOUS_DYNAMICAL_SYSTEM_H
 
 #include <BipedalLocomotion/Core.h>
+#include <BipedalLocomotion/System.h>
 #include <blfik.h>
+
+#include <map>
 
 #include <tuple>
 
@@ -219,6 +222,161 @@ private:
     std::shared_ptr<DynamicalSystem> m_dynamicalSystem;
     std::chrono::nanoseconds m_dT{0};
     int m_device{0};
+};
+
+/** FirstOrderSmoother.h:32-94, FirstOrderSmoother.cpp:18-140: dx = -a x + a u with a = 3 / settling_time, propagated by one
+ *  ForwardEuler step of `sampling_time` per advance().  Host-side: it smooths the few doubles of a task weight, which the
+ *  solver re-reads on every tick (QPInverseKinematics.cpp:450-451) -- shared by all robots of the batch. */
+class FirstOrderSmoother
+{
+public:
+    /** keys: settling_time [s] (double), sampling_time (chrono nanoseconds or seconds as double) */
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> handler)
+    {
+        constexpr auto logPrefix = "[FirstOrderSmoother::initialize]";
+        auto ptr = handler.lock();
+        if (ptr == nullptr) {
+            log()->error("{} Invalid parameter handler.", logPrefix);
+            return false;
+        }
+        if (!ptr->getParameter("settling_time", m_settlingTime)) {
+            log()->error("{} Unable to get the 'settling_time' parameter.", logPrefix);
+            return false;
+        }
+        std::chrono::nanoseconds samplingTime;
+        if (!ptr->getParameter("sampling_time", samplingTime)) {
+            log()->error("{} Unable to get the 'sampling_time' parameter.", logPrefix);
+            return false;
+        }
+        if (samplingTime <= std::chrono::nanoseconds::zero()) {   // FixedStepIntegrator::setIntegrationStep
+            log()->error("{} Unable to set the integration time step.", logPrefix);
+            return false;
+        }
+        m_dt = std::chrono::duration<double>(samplingTime).count();
+        m_isInitialized = true;
+        return true;
+    }
+    bool reset(const VectorXd& initialPoint)
+    {
+        m_isInitialStateSet = false;
+        if (!m_isInitialized) {
+            log()->error("[FirstOrderSmoother::reset] Please initialize the class before.");
+            return false;
+        }
+        m_state = initialPoint, m_output = initialPoint;
+        m_isInitialStateSet = true;
+        return true;
+    }
+    bool setInput(const VectorXd& input)
+    {
+        if (!m_isInitialized || !m_isInitialStateSet) {
+            log()->error("[FirstOrderSmoother::setInput] Please call initialize() and reset() before advance.");
+            return false;
+        }
+        m_input = input;
+        return true;
+    }
+    bool advance()
+    {
+        m_isOutputValid = false;
+        if (!m_isInitialized || !m_isInitialStateSet) {
+            log()->error("[FirstOrderSmoother::advance] Please call initialize() and reset() before advance.");
+            return false;
+        }
+        if (m_input.size() != m_state.size()) {   // LinearTimeInvariantSystem.cpp:58-63: the input was never set
+            log()->error("[FirstOrderSmoother::advance] Unable to propagate the dynamical system.");
+            return false;
+        }
+        const double a = 3.0 / m_settlingTime;
+        for (std::size_t i = 0; i < m_state.size(); i++) m_state[i] += m_dt * (a * m_input[i] - a * m_state[i]);
+        m_output = m_state;
+        m_isOutputValid = true;
+        return true;
+    }
+    const VectorXd& getOutput() const { return m_output; }
+    bool isOutputValid() const { return m_isOutputValid; }
+
+private:
+    double m_settlingTime{1.0}, m_dt{0.0};
+    VectorXd m_state, m_input, m_output;
+    bool m_isInitialized{false}, m_isInitialStateSet{false}, m_isOutputValid{false};
+};
+
+/** MultiStateWeightProvider.h:28-93, MultiStateWeightProvider.cpp:12-134: named weight vectors ("states") with a first-order
+ *  transition between them; plug it into QPInverseKinematics::addTask / setTaskWeight as the weight provider. */
+class MultiStateWeightProvider : public System::WeightProvider
+{
+public:
+    /** keys: settling_time, sampling_time, states (vector<string> of group names); each group: name, weight */
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> handler)
+    {
+        constexpr auto logPrefix = "[MultiStateWeightProvider::initialize]";
+        if (!m_smoother.initialize(handler)) {
+            log()->error("{} Unable to initialize the smoother.", logPrefix);
+            return false;
+        }
+        auto ptr = handler.lock();
+        if (ptr == nullptr) {
+            log()->error("{} Invalid parameter handler.", logPrefix);
+            return false;
+        }
+        std::vector<std::string> states;
+        if (!ptr->getParameter("states", states) || states.empty()) {
+            log()->error("{} Unable to get the parameter named 'states'.", logPrefix);
+            return false;
+        }
+        std::string name, firstState;
+        for (const auto& state : states) {
+            auto group = ptr->getGroup(state).lock();
+            if (group == nullptr) {
+                log()->error("{} Unable to get the group named '{}'.", logPrefix, state);
+                return false;
+            }
+            if (!group->getParameter("name", name)) {
+                log()->error("{} Unable to get the parameter named 'name' in the group named '{}'.", logPrefix, state);
+                return false;
+            }
+            if (!group->getParameter("weight", m_states[name])) {
+                log()->error("{} Unable to get the parameter named 'weight' in the group named '{}'.", logPrefix, state);
+                return false;
+            }
+            if (firstState.empty()) firstState = name;
+        }
+        const std::size_t size = m_states.begin()->second.size();
+        for (const auto& state : m_states)
+            if (state.second.size() != size) {
+                log()->error("{} The size of the weight associated to the state named '{}' does not match with the size of the weight "
+                             "associated to the state named '{}'.", logPrefix, state.first, m_states.begin()->first);
+                return false;
+            }
+        return this->reset(firstState);
+    }
+    bool reset(const std::string& state)
+    {
+        const auto weight = m_states.find(state);
+        if (weight == m_states.end()) {
+            log()->error("[MultiStateWeightProvider::reset] Unable to find the weight named '{}'", state);
+            return false;
+        }
+        return m_smoother.reset(weight->second);
+    }
+    bool setState(const std::string& state)
+    {
+        const auto weight = m_states.find(state);
+        if (weight == m_states.end()) {
+            log()->error("[MultiStateWeightProvider::setState] Unable to find the weight named '{}'", state);
+            return false;
+        }
+        return m_smoother.setInput(weight->second);
+    }
+    bool advance() { return m_smoother.advance(); }
+    const VectorXd& getOutput() const override { return m_smoother.getOutput(); }
+    /** like the reference (MultiStateWeightProvider.cpp:17-20): valid once advance() has run */
+    bool isOutputValid() const override { return m_smoother.isOutputValid(); }
+
+private:
+    FirstOrderSmoother m_smoother;
+    std::map<std::string, VectorXd> m_states;
 };
 
 }  // namespace ContinuousDynamicalSystem

@@ -383,6 +383,23 @@ public:
     blfik_problem* handle();
 };
 
+/** QPFixedBaseInverseKinematics.h:54-96, QPFixedBaseInverseKinematics.cpp:17-122: QPInverseKinematics plus a priority-0
+ *  SE3Task on the floating-base link with the controller disabled and a zero feed-forward ("base_se3_task"), i.e. the
+ *  base twist is constrained to zero. */
+class QPFixedBaseInverseKinematics : public QPInverseKinematics
+{
+    std::string m_baseLink;
+    std::shared_ptr<SE3Task> m_baseSE3Task;
+    bool m_isKinDynSet{false};
+
+public:
+    QPFixedBaseInverseKinematics();
+    ~QPFixedBaseInverseKinematics();
+    /** required keys: "robot_velocity_variable_name" (+ "verbosity", optional) */
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> handler) override;
+    bool setKinDyn(std::shared_ptr<KinDynBatch> kinDyn);
+};
+
 }  // namespace IK
 }  // namespace BipedalLocomotion
 

@@ -36,6 +36,8 @@ public:
     /** -1 if the frame does not exist (iDynTree::FRAME_INVALID_INDEX) */
     int getFrameIndex(const std::string& name) const;
     std::string getFrameName(int index) const;
+    /** name of the floating-base link frame (iDynTree::KinDynComputations::getFloatingBase); link 0 of the model */
+    const std::string& getFloatingBase() const { return m_floatingBase; }
     const VectorXd& jointLowerLimits() const { return m_qLower; }
     const VectorXd& jointUpperLimits() const { return m_qUpper; }
     const std::vector<std::string>& jointNames() const { return m_jointNames; }
@@ -69,6 +71,7 @@ private:
     std::size_t m_n{0}, m_N{1};
     int m_device{0};
     std::vector<std::string> m_jointNames, m_frameNames;
+    std::string m_floatingBase;
     VectorXd m_qLower, m_qUpper;
     std::vector<double> m_p, m_q, m_s;
     unsigned long m_version{1}, m_kinVersion{0};

@@ -1,5 +1,6 @@
 // blf_host.cpp -- implementation of the host classes (KinDynBatch, the IK tasks, QPInverseKinematics).
 // Every numerical step goes through the C ABI of include/blfik.h; nothing here computes kinematics or solves QPs.
+#include <BipedalLocomotion/ContinuousDynamicalSystem.h>
 #include <BipedalLocomotion/IK.h>
 
 #include <algorithm>
@@ -60,6 +61,12 @@ bool KinDynBatch::loadRobotModelFromFile(const std::string& path)
             double v;
             for (int i = 0; i < 9; i++) in >> v, Fr.push_back(v);
             for (int i = 0; i < 3; i++) in >> v, Fp.push_back(v);
+            if (l == 0 && m_floatingBase.empty()) {   // the link frame of link 0 (identity offset) names the floating base
+                const double* r = &Fr[Fr.size() - 9];
+                const double* t = &Fp[Fp.size() - 3];
+                if (r[0] == 1 && r[4] == 1 && r[8] == 1 && r[1] == 0 && r[2] == 0 && r[3] == 0 && r[5] == 0 && r[6] == 0 && r[7] == 0 && t[0] == 0 && t[1] == 0 && t[2] == 0)
+                    m_floatingBase = fname;
+            }
         } else if (tok == "limits") {
             std::string jname;
             std::array<double, 3> l;
@@ -1381,12 +1388,21 @@ IntegrationBasedIKProblem QPInverseKinematics::build(std::weak_ptr<const Paramet
         if (priority == 1) {   // :737-780
             std::string providerType = "ConstantWeightProvider";
             group->getParameter("weight_provider_type", providerType);
-            if (providerType != "ConstantWeightProvider") {
-                log()->error("{} The weight provider '{}' is not available (only ConstantWeightProvider is).", logPrefix, providerType);
+            std::shared_ptr<System::WeightProvider> provider;
+            bool providerOk = false;
+            if (providerType == "ConstantWeightProvider") {
+                auto constant = std::make_shared<System::ConstantWeightProvider>();
+                providerOk = constant->initialize(group);
+                provider = constant;
+            } else if (providerType == "MultiStateWeightProvider") {   // the other provider of the reference's factory
+                auto multi = std::make_shared<ContinuousDynamicalSystem::MultiStateWeightProvider>();
+                providerOk = multi->initialize(group);
+                provider = multi;
+            } else {
+                log()->error("{} The weight provider '{}' is not available.", logPrefix, providerType);
                 return IntegrationBasedIKProblem();
             }
-            auto provider = std::make_shared<System::ConstantWeightProvider>();
-            if (!provider->initialize(group)) {
+            if (!providerOk) {
                 log()->error("{} Unable to initialize the weight provider of the task '{}'.", logPrefix, taskGroupName);
                 return IntegrationBasedIKProblem();
             }
@@ -1406,6 +1422,63 @@ IntegrationBasedIKProblem QPInverseKinematics::build(std::weak_ptr<const Paramet
     }
     problem.ik = std::move(solver);
     return problem;
+}
+
+// =================================================================== QPFixedBaseInverseKinematics
+QPFixedBaseInverseKinematics::QPFixedBaseInverseKinematics() : m_baseSE3Task(std::make_shared<SE3Task>()) {}
+QPFixedBaseInverseKinematics::~QPFixedBaseInverseKinematics() = default;
+
+bool QPFixedBaseInverseKinematics::setKinDyn(std::shared_ptr<KinDynBatch> kinDyn)
+{
+    constexpr auto logPrefix = "[QPFixedBaseInverseKinematics::setKinDyn]";
+    if (kinDyn == nullptr) {
+        log()->error("{} The kinDyn object is not valid.", logPrefix);
+        return false;
+    }
+    if (!m_baseSE3Task->setKinDyn(kinDyn)) {
+        log()->error("{} Unable to set the kinDyn object for SE3Task on the base.", logPrefix);
+        return false;
+    }
+    m_baseLink = kinDyn->getFloatingBase();   // QPFixedBaseInverseKinematics.cpp:84
+    m_isKinDynSet = true;
+    return true;
+}
+
+bool QPFixedBaseInverseKinematics::initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> handler)
+{
+    constexpr auto logPrefix = "[QPFixedBaseInverseKinematics::initialize]";
+    if (!m_isKinDynSet) {
+        log()->error("{} The object kinDyn is not valid.", logPrefix);
+        return false;
+    }
+    auto ptr = handler.lock();
+    if (ptr == nullptr) {
+        log()->error("{} The parameter handler is not valid.", logPrefix);
+        return false;
+    }
+    // createBaseSE3Task (QPFixedBaseInverseKinematics.cpp:24-58): zero gains, controller disabled, zero feed-forward
+    std::string robotVelocityVariableName;
+    if (!ptr->getParameter("robot_velocity_variable_name", robotVelocityVariableName)) {
+        log()->error("{} Unable to get the parameter 'robot_velocity_variable_name'", logPrefix);
+        return false;
+    }
+    auto baseHandler = std::make_shared<ParametersHandler::StdImplementation>();
+    baseHandler->setParameter("robot_velocity_variable_name", robotVelocityVariableName);
+    baseHandler->setParameter("kp_linear", 0.0);
+    baseHandler->setParameter("kp_angular", 0.0);
+    baseHandler->setParameter("frame_name", m_baseLink);
+    if (!m_baseSE3Task->initialize(baseHandler)) {
+        log()->error("{} Error creating SE3task for the base.", logPrefix);
+        return false;
+    }
+    m_baseSE3Task->setTaskControllerMode(SE3Task::Mode::Disable);
+    m_baseSE3Task->setSetPoint(SE3d(), SE3d::Tangent::Zero());
+    if (!this->QPInverseKinematics::initialize(ptr)) {
+        log()->error("{} Unable to initialize QPInverseKinematics class.", logPrefix);
+        return false;
+    }
+    constexpr std::size_t highPriority = 0;
+    return this->addTask(m_baseSE3Task, "base_se3_task", highPriority);
 }
 
 }  // namespace IK

@@ -250,6 +250,71 @@ static void testTaskInitializationAndAddTaskRules(const char* modelPath)
     log()->setLevel(Logger::Level::warn);
 }
 
+// 'First order smoother' (tests/FirstOrderSmoother.cpp:22-100: step response against 1 - exp(-3 t / settling_time), 1e-2) and
+// 'Multistate weight provider' (tests/MultiStateWeightProvider.cpp:22-118: walking <-> stance within 1e-2 after 50 steps)
+static void testWeightProviders()
+{
+    using BipedalLocomotion::ContinuousDynamicalSystem::FirstOrderSmoother;
+    using BipedalLocomotion::ContinuousDynamicalSystem::MultiStateWeightProvider;
+    {
+        auto params = std::make_shared<StdImplementation>();
+        FirstOrderSmoother smoother;
+        log()->setLevel(Logger::Level::off);
+        REQUIRE_FALSE(smoother.initialize(params));              // settling_time missing
+        REQUIRE_FALSE(smoother.reset(VectorXd(2, 0.0)));         // not initialised
+        log()->setLevel(Logger::Level::warn);
+        params->setParameter("settling_time", 0.1), params->setParameter("sampling_time", std::chrono::nanoseconds(100us));
+        REQUIRE(smoother.initialize(params) && smoother.reset(VectorXd(2, 0.0)));
+        log()->setLevel(Logger::Level::off);
+        REQUIRE_FALSE(smoother.advance());                       // no input yet
+        log()->setLevel(Logger::Level::warn);
+        REQUIRE(smoother.setInput(VectorXd(2, 1.0)));
+        double worst = 0, settled = -1;
+        for (unsigned int i = 0; i < 1000; i++) {
+            const double t = 100e-6 * i, expected = 1.0 - std::exp(-30.0 * t);
+            worst = std::max(worst, std::abs(smoother.getOutput()[0] - expected));
+            if (settled < 0 && smoother.getOutput()[1] > 0.95) settled = t;
+            REQUIRE(smoother.advance());
+        }
+        REQUIRE(worst < 1e-2 && std::abs(settled - 0.1) < 1e-2);   // 5 % band reached at the settling time
+    }
+    {
+        const VectorXd walking{10, 100, 1000}, stance{50, 30, 20};
+        auto params = std::make_shared<StdImplementation>();
+        params->setParameter("settling_time", 0.1), params->setParameter("sampling_time", std::chrono::nanoseconds(10ms));
+        params->setParameter("states", std::vector<std::string>{"WALKING", "STANCE"});
+        auto pw = std::make_shared<StdImplementation>(), ps = std::make_shared<StdImplementation>();
+        pw->setParameter("name", "walking"), pw->setParameter("weight", walking);
+        ps->setParameter("name", "stance"), ps->setParameter("weight", stance);
+        REQUIRE(params->setGroup("WALKING", pw) && params->setGroup("STANCE", ps));
+        MultiStateWeightProvider provider;
+        REQUIRE(provider.initialize(params));
+        REQUIRE(provider.getOutput() == walking);
+        REQUIRE(provider.setState("stance"));
+        log()->setLevel(Logger::Level::off);
+        REQUIRE_FALSE(provider.setState("foo"));
+        log()->setLevel(Logger::Level::warn);
+        auto close = [](const VectorXd& a, const VectorXd& b, double rel) {
+            double d = 0, nb = 0;
+            for (std::size_t i = 0; i < a.size(); i++) d += (a[i] - b[i]) * (a[i] - b[i]), nb += b[i] * b[i];
+            return std::sqrt(d) <= rel * std::sqrt(nb);
+        };
+        for (unsigned int i = 0; i < 50; i++) REQUIRE(provider.advance());
+        REQUIRE(provider.isOutputValid() && close(provider.getOutput(), stance, 1e-2));
+        REQUIRE(provider.reset("stance") && provider.getOutput() == stance && provider.setState("walking"));
+        for (unsigned int i = 0; i < 50; i++) REQUIRE(provider.advance());
+        REQUIRE(close(provider.getOutput(), walking, 1e-2));
+        // states of different sizes are rejected (MultiStateWeightProvider.cpp:77-96)
+        auto ps2 = std::make_shared<StdImplementation>();
+        ps2->setParameter("name", "stance"), ps2->setParameter("weight", VectorXd{1, 2});
+        REQUIRE(params->setGroup("STANCE", ps2));
+        MultiStateWeightProvider bad;
+        log()->setLevel(Logger::Level::off);
+        REQUIRE_FALSE(bad.initialize(params));
+        log()->setLevel(Logger::Level::warn);
+    }
+}
+
 // ------------------------------------------------------------------------------------------ GPU
 static double maxAbsDiff(const MatrixXd& A, std::size_t r0, std::size_t c0, const MatrixXd& B, std::size_t br0)
 {
@@ -473,6 +538,76 @@ static void testClosedLoop(const char* modelPath, std::size_t N, bool withLimits
 }
 
 // IntegratorFloatingBaseSystemVelocityKinematics.cpp:25-88 with a non-identity initial rotation
+// QPFixedBaseInverseKinematics (QPFixedBaseInverseKinematicsTest.cpp: the base link is held by "base_se3_task", a hand reaches
+// a pose with the joints regularised): the base twist stays zero on every tick and the hand converges
+static void testFixedBase(const char* modelPath, std::size_t N)
+{
+    constexpr auto dT = 10ms;
+    auto kinDyn = loadKinDyn(modelPath, N);
+    const std::size_t n = kinDyn->getNrOfDegreesOfFreedom();
+    REQUIRE(kinDyn->getFloatingBase() == "root_link");
+    auto ikHandler = std::make_shared<StdImplementation>();
+    ikHandler->setParameter("robot_velocity_variable_name", robotVelocity);
+    QPFixedBaseInverseKinematics ik;
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(ik.initialize(ikHandler));   // setKinDyn first (QPFixedBaseInverseKinematics.cpp:96-100)
+    log()->setLevel(Logger::Level::warn);
+    REQUIRE(ik.setKinDyn(kinDyn) && ik.initialize(ikHandler));
+    REQUIRE(ik.getTaskNames().size() == 1 && ik.getTask("base_se3_task").lock() != nullptr);
+
+    auto hand = std::make_shared<SE3Task>();
+    auto hh = std::make_shared<StdImplementation>();
+    hh->setParameter("robot_velocity_variable_name", robotVelocity), hh->setParameter("frame_name", "l_hand_palm");
+    hh->setParameter("kp_linear", 5.0), hh->setParameter("kp_angular", 5.0);
+    REQUIRE(hand->setKinDyn(kinDyn) && hand->initialize(hh) && ik.addTask(hand, "hand", 0));
+    auto reg = std::make_shared<JointTrackingTask>();
+    auto rh = std::make_shared<StdImplementation>();
+    rh->setParameter("robot_velocity_variable_name", robotVelocity), rh->setParameter("kp", std::vector<double>(n, 1.0));
+    REQUIRE(reg->setKinDyn(kinDyn) && reg->initialize(rh) && ik.addTask(reg, "reg", 1, VectorXd(n, 1.0)));
+    VariablesHandler vh;
+    vh.addVariable(robotVelocity, n + 6);
+    REQUIRE(ik.finalize(vh));
+
+    std::mt19937 gen(11);
+    auto desired = loadKinDyn(modelPath, N);
+    auto system = std::make_shared<FloatingBaseSystemVelocityKinematics>();
+    system->setBatchSize(N);
+    std::vector<SE3d> handDes(N);
+    const Vector3d p0{0.1, -0.2, 0.8};
+    const SO3d R0 = SO3d::Exp({0.05, -0.1, 0.3});
+    for (std::size_t i = 0; i < N; i++) {
+        VectorXd sDes = nominalJoints(*kinDyn, gen, 0.2), s0 = sDes;
+        std::normal_distribution<double> noise(0.0, 0.08);
+        for (auto& v : s0) v += noise(gen);
+        std::array<double, 9> R;
+        REQUIRE(desired->setRobotState(p0, R0, sDes, i));
+        REQUIRE(desired->getWorldTransform(kinDyn->getFrameIndex("l_hand_palm"), handDes[i], R, i));
+        REQUIRE(hand->setSetPoint(handDes[i], SE3d::Tangent::Zero(), i) && reg->setSetPoint(sDes, i));
+        REQUIRE(system->setState({p0, R0, s0}, i));
+    }
+    ForwardEuler<FloatingBaseSystemVelocityKinematics> integrator;
+    REQUIRE(integrator.setIntegrationStep(dT) && integrator.setDynamicalSystem(system));
+    for (int iteration = 0; iteration < 150; iteration++) {
+        REQUIRE(kinDyn->setRobotStateBatch(system->basePositions().data(), system->baseQuaternions().data(), system->jointPositions().data()));
+        REQUIRE(ik.advance() && ik.isOutputValid());
+        const auto& nu = ik.getBatchOutput();
+        double baseTwist = 0;
+        for (std::size_t i = 0; i < N; i++)
+            for (int c = 0; c < 6; c++) baseTwist = std::max(baseTwist, std::abs(nu[i * (n + 6) + c]));
+        REQUIRE(baseTwist < 1e-9);
+        REQUIRE(system->setControlInputBatch(nu.data()));
+        REQUIRE(integrator.integrate(0s, dT));
+    }
+    REQUIRE(kinDyn->setRobotStateBatch(system->basePositions().data(), system->baseQuaternions().data(), system->jointPositions().data()));
+    for (std::size_t i = 0; i < N; i++) {
+        SE3d pose;
+        std::array<double, 9> R;
+        REQUIRE(kinDyn->getWorldTransform(kinDyn->getFrameIndex("l_hand_palm"), pose, R, i));
+        for (int c = 0; c < 3; c++) REQUIRE(std::abs(pose.p[c] - handDes[i].p[c]) < 2e-3);
+        for (int c = 0; c < 3; c++) REQUIRE(std::abs(system->basePositions()[3 * i + c] - p0[c]) < 1e-9);   // the base never moved
+    }
+}
+
 static void testIntegrator()
 {
     constexpr auto dT = 100us;
@@ -518,11 +653,14 @@ int main(int argc, char** argv)
     const bool gpu = std::strcmp(argv[1], "gpu") == 0;
     testParametersAndVariables();
     testTaskInitializationAndAddTaskRules(argv[2]);
+    testWeightProviders();
     if (gpu) {
         testTaskMatrices(argv[2]);
         testClosedLoop(argv[2], 1, false);
         testClosedLoop(argv[2], 1, true);
         testClosedLoop(argv[2], 48, true);
+        testFixedBase(argv[2], 1);
+        testFixedBase(argv[2], 5);
         testIntegrator();
     }
     std::printf("%s: %d checks, %d failures\n", gpu ? "gpu" : "cpu", g_checks, g_failures);

@@ -721,3 +721,36 @@ def test_uniqueness_condition_of_the_bench_workloads(cid):
         worst_eig = min(worst_eig, np.linalg.eigvalsh(Z.T @ H[i] @ Z).min())
     assert worst_sv > 1e-3 and worst_eig > 1e-8, (worst_sv, worst_eig)
     prob.close()
+
+
+def test_problems_of_different_sizes_coexist():
+    """The kernels' dynamic shared-memory limit is shared by every problem in the process: creating a smaller problem after
+    a larger one (same kernel instantiation) must not break the larger one's launches.  Both kernel paths."""
+    m = M.ergocub23()
+    n = m.n
+    big_tasks = [T.se3_task(m, "lf", "l_sole", 5.0, 5.0), T.se3_task(m, "rf", "r_sole", 5.0, 5.0),
+                 T.joint_tracking_task(m, "reg", np.ones(n), priority=1, weight=np.ones(n))]
+    small_tasks = [T.joint_tracking_task(m, "reg", np.ones(n), priority=1, weight=np.ones(n))]
+    w3 = W.config(3)
+    inp = W.synth_inputs(w3, 8, 3)
+    for path in PATHS:
+        model, big = make(m, big_tasks, 8, path)
+        big.set_state(inp.base_pos, inp.base_quat, inp.s)
+        big.set_setpoint(0, inp.setpoints[2]), big.set_setpoint(1, inp.setpoints[1]), big.set_setpoint(2, inp.setpoints[6])
+        big.tick(1, 0.01)
+        ref = big.get_output()
+        _, small = make(m, small_tasks, 8, path)       # fewer task descriptors -> smaller shared-memory request
+        small.set_state(inp.base_pos, inp.base_quat, inp.s)
+        small.set_setpoint(0, inp.setpoints[6])
+        small.tick(1, 0.01)
+        small.kinematics([0])
+        big.tick(1, 0.01)                              # must still launch
+        assert np.array_equal(big.get_output(), ref)
+        _, tree = make(M.random_tree(35, 3), [T.joint_tracking_task(M.random_tree(35, 3), "reg", np.ones(35), priority=1, weight=np.ones(35))], 4, path)
+        tree.set_state(np.zeros((4, 3)), np.tile([0.0, 0, 0, 1], (4, 1)), np.zeros((4, 35)))
+        tree.set_setpoint(0, np.zeros((4, 70)))
+        tree.tick(1, 0.01)                             # a larger generic-kernel problem ...
+        small.tick(1, 0.01)                            # ... and the smaller ones keep working
+        big.tick(1, 0.01)
+        assert np.array_equal(big.get_output(), ref)
+        big.close(), small.close(), tree.close()

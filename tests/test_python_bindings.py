@@ -1,0 +1,397 @@
+"""The Python surface (blf_b200.bindings), exercised the way the reference's own binding tests exercise theirs
+(bindings/python/IK/tests/test_QP_inverse_kinematics.py, bindings/python/ContinuousDynamicalSystem/tests/
+test_floating_base_system_kinematics.py, bindings/python/System/tests, bindings/python/ParametersHandler/tests).
+The CPU part covers the host logic (handlers, key / size / priority rules); everything that solves runs on the GPU."""
+import logging
+from datetime import timedelta
+
+import numpy as np
+import pytest
+
+import blf_b200  # noqa: F401
+import blf_b200.bindings as blf
+from blf_b200 import models as M
+from blf_b200.bindings import manif
+
+logging.getLogger("blf").setLevel(logging.CRITICAL)   # the error paths below are expected
+
+
+def get_kindyn(model=None, batch_size=1):
+    model = model or M.icub26()
+    return model.joint_names, blf.KinDynComputations(model, batch_size)
+
+
+# ------------------------------------------------------------------------------------------------ CPU: host logic
+def test_parameters_handler():
+    h = blf.parameters_handler.StdParametersHandler()
+    h.set_parameter_bool(name="b", value=True)
+    h.set_parameter_int(name="i", value=3)
+    h.set_parameter_float(name="f", value=1.5)
+    h.set_parameter_string(name="s", value="blf")
+    h.set_parameter_vector_float(name="vf", value=[1.0, 2.0])
+    h.set_parameter_vector_bool(name="vb", value=[True, False, True])
+    h.set_parameter_datetime(name="dt", value=timedelta(milliseconds=10))
+    assert h.get_parameter_bool("b") is True and h.get_parameter_int("i") == 3 and h.get_parameter_float("f") == 1.5
+    assert h.get_parameter_float("i") == 3.0                 # an int converts to a float, as in the C++ handler
+    assert h.get_parameter_string("s") == "blf" and list(h.get_parameter_vector_float("vf")) == [1.0, 2.0]
+    assert h.get_parameter_datetime("dt") == timedelta(milliseconds=10)
+    with pytest.raises(ValueError):
+        h.get_parameter_int("b")                             # a bool is not an int
+    with pytest.raises(ValueError):
+        h.get_parameter_string("missing")
+    g = blf.parameters_handler.StdParametersHandler()
+    g.set_parameter_int("x", 1)
+    assert h.set_group("G", g)
+    g.set_parameter_int("x", 2)                              # the group was cloned (StdImplementation::setGroup)
+    assert h.get_group("G").get_parameter_int("x") == 1
+    with pytest.raises(ValueError):
+        h.get_group("nope")
+    assert not h.is_empty()
+    h.clear()
+    assert h.is_empty()
+
+
+def test_variables_handler():
+    v = blf.system.VariablesHandler()
+    assert v.add_variable("a", 10) and v.add_variable("robotVelocity", 32) and not v.add_variable("a", 3)
+    var = v.get_variable("robotVelocity")
+    assert var.is_valid() and var.offset == 10 and var.size == 32 and v.get_number_of_variables() == 42
+    assert not v.get_variable("missing").is_valid()
+    h = blf.parameters_handler.StdParametersHandler()
+    h.set_parameter_vector_string("variables_name", ["x", "y"])
+    h.set_parameter_vector_int("variables_size", [2, 5])
+    v2 = blf.system.VariablesHandler()
+    assert v2.initialize(h) and v2.get_variable("y").offset == 2
+    h.set_parameter_vector_int("variables_size", [2])
+    assert not blf.system.VariablesHandler().initialize(h)
+
+
+def _handler(**kw):
+    h = blf.parameters_handler.StdParametersHandler()
+    h.set_parameter_string(name="robot_velocity_variable_name", value="robotVelocity")
+    for k, v in kw.items():
+        if isinstance(v, bool):
+            h.set_parameter_bool(k, v)
+        elif isinstance(v, float):
+            h.set_parameter_float(k, v)
+        elif isinstance(v, str):
+            h.set_parameter_string(k, v)
+        elif isinstance(v, timedelta):
+            h.set_parameter_datetime(k, v)
+        elif len(v) and isinstance(v[0], bool):
+            h.set_parameter_vector_bool(k, v)
+        else:
+            h.set_parameter_vector_float(k, v)
+    return h
+
+
+def test_task_initialisation_rules():
+    """the per-task tests of test_QP_inverse_kinematics.py:82-283 plus the failure branches of the C++ initialize()s"""
+    joints, kindyn = get_kindyn()
+    n = kindyn.getNrOfDegreesOfFreedom()
+    var = blf.system.VariablesHandler()
+    assert var.add_variable("robotVelocity", n + 6)
+    bad_var = blf.system.VariablesHandler()
+    assert bad_var.add_variable("robotVelocity", n + 5)
+
+    com = blf.ik.CoMTask()
+    assert not com.initialize(param_handler=_handler(kp_linear=10.0))          # set_kin_dyn first
+    assert com.set_kin_dyn(kindyn)
+    assert not com.initialize(param_handler=_handler())                        # kp_linear missing
+    assert com.initialize(param_handler=_handler(kp_linear=10.0))
+    assert com.set_variables_handler(variables_handler=var) and not com.set_variables_handler(variables_handler=bad_var)
+    assert com.set_set_point(position=np.array([1., 1., 1.5]), velocity=np.array([0., 0.5, 0.5]))
+    assert com.size() == 3 and com.type() == blf.ik.IKLinearTask.Type.equality
+
+    se3 = blf.ik.SE3Task()
+    assert se3.set_kin_dyn(kindyn)
+    assert not se3.initialize(param_handler=_handler(frame_name="not_a_frame", kp_linear=10.0, kp_angular=10.0))
+    assert not se3.initialize(param_handler=_handler(frame_name="r_sole", kp_linear=10.0))
+    assert se3.initialize(param_handler=_handler(frame_name="r_sole", kp_linear=10.0, kp_angular=[1.0, 2.0, 3.0], mask=[True, False, True]))
+    assert se3.size() == 5
+    assert se3.set_set_point(I_H_F=manif.SE3(position=[1.0, -2.0, 3.3], quaternion=[0, 0, -1, 0]), mixed_velocity=manif.SE3Tangent([0.0] * 6))
+
+    so3 = blf.ik.SO3Task()
+    assert so3.set_kin_dyn(kindyn) and so3.initialize(param_handler=_handler(frame_name="chest", kp_angular=5.0))
+    assert so3.set_set_point(I_R_F=manif.SO3(quaternion=[0, 0, -1, 0]), angular_velocity=manif.SO3Tangent([0.0] * 3))
+
+    jt = blf.ik.JointTrackingTask()
+    assert jt.set_kin_dyn(kindyn)
+    assert not jt.initialize(param_handler=_handler(kp=[5.0] * (n - 1)))       # size-checked (JointTrackingTask.cpp:100-110)
+    assert jt.initialize(param_handler=_handler(kp=[5.0] * n))
+    assert jt.set_set_point(joint_position=np.zeros(n)) and jt.set_set_point(joint_position=np.zeros(n), joint_velocity=np.ones(n))
+    assert not jt.set_set_point(joint_position=np.zeros(n - 1))
+
+    jl = blf.ik.JointLimitsTask()
+    assert jl.set_kin_dyn(kindyn)
+    base = dict(klim=[0.5] * n, upper_limits=np.full(n, 0.01), lower_limits=np.full(n, -0.01), sampling_time=timedelta(milliseconds=10))
+    assert not jl.initialize(param_handler=_handler(**base))                   # use_model_limits is mandatory
+    assert not jl.initialize(param_handler=_handler(use_model_limits=False, **{**base, "klim": [1.5] * n}))
+    assert not jl.initialize(param_handler=_handler(use_model_limits=False, **{**base, "sampling_time": timedelta(0)}))
+    assert jl.initialize(param_handler=_handler(use_model_limits=False, **base))
+    assert jl.type() == blf.ik.IKLinearTask.Type.inequality and jl.size() == 2 * n
+
+    jv = blf.ik.JointVelocityLimitsTask()
+    assert jv.set_kin_dyn(kindyn)
+    assert not jv.initialize(param_handler=_handler(upper_limits=np.ones(n)))
+    assert jv.initialize(param_handler=_handler(upper_limits=np.ones(n), lower_limits=-np.ones(n)))
+
+    dist = blf.ik.DistanceTask()
+    assert dist.set_kin_dyn(kindyn)
+    assert not dist.initialize(param_handler=_handler(target_frame_name="chest", reference_frame_name="nope", kp=5.0))
+    assert dist.initialize(param_handler=_handler(target_frame_name="chest", reference_frame_name="root_link", kp=5.0))
+    assert dist.set_desired_distance(desired_distance=-0.3) and dist.set_set_point(desired_distance=0.2)
+    assert dist._sp[0, 0] == 0.2
+
+    grav = blf.ik.GravityTask()
+    assert grav.set_kin_dyn(kindyn) and grav.initialize(param_handler=_handler(target_frame_name="chest", kp=5.0))
+    assert grav.set_set_point(desired_gravity_direction=[0.0, 3.0, 4.0], feedforward_velocity=[0.1, 0.2, 0.3])
+    assert np.allclose(grav._sp[0], [0.0, 0.6, 0.8, 0.1, 0.2, 0.3])
+
+    state = blf.ik.IntegrationBasedIKState()
+    state.joint_velocity = [0.1] * n
+    assert state.joint_velocity == pytest.approx([0.1] * n)
+
+
+def test_add_task_rules_and_custom_task():
+    """QPInverseKinematics::addTask (QPInverseKinematics.cpp:167-249) and the custom-task test (:12-56)"""
+    joints, kindyn = get_kindyn()
+    n = kindyn.getNrOfDegreesOfFreedom()
+    qp_ik = blf.ik.QPInverseKinematics()
+    jt = blf.ik.JointTrackingTask()
+    assert jt.set_kin_dyn(kindyn) and jt.initialize(param_handler=_handler(kp=[5.0] * n))
+    assert not qp_ik.add_task(task=jt, task_name="reg", priority=1, weight=[1.0] * n)     # initialize() first
+    assert not qp_ik.initialize(handler=blf.parameters_handler.StdParametersHandler())
+    assert qp_ik.initialize(handler=_handler())
+    assert not qp_ik.add_task(task=jt, task_name="reg", priority=1)                        # weight is mandatory
+    assert not qp_ik.add_task(task=jt, task_name="reg", priority=1, weight=[1.0] * (n - 1))
+    assert not qp_ik.add_task(task=jt, task_name="reg", priority=2, weight=[1.0] * n)
+    assert qp_ik.add_task(task=jt, task_name="reg", priority=1, weight=[1.0] * n)
+    assert not qp_ik.add_task(task=jt, task_name="reg", priority=1, weight=[1.0] * n)      # duplicate name
+    jv = blf.ik.JointVelocityLimitsTask()
+    assert jv.set_kin_dyn(kindyn) and jv.initialize(param_handler=_handler(upper_limits=np.ones(n), lower_limits=-np.ones(n)))
+    assert not qp_ik.add_task(task=jv, task_name="lim", priority=1, weight=[1.0] * 2 * n)  # inequality as a cost
+    assert qp_ik.add_task(task=jv, task_name="lim", priority=0)
+    assert qp_ik.get_task_names() == ["reg", "lim"] and qp_ik.get_task("reg") is jt and qp_ik.get_task("x") is None
+    assert not qp_ik.set_task_weight("lim", weight=[1.0] * 2 * n) and not qp_ik.set_task_weight("reg", weight=[1.0])
+    assert qp_ik.set_task_weight("reg", weight=[2.0] * n) and qp_ik.get_task_weight_provider("reg").get_output()[0] == 2.0
+    assert not qp_ik.advance() and not qp_ik.is_output_valid()                            # finalize() first
+
+    class CustomTask(blf.ik.IKLinearTask):
+        def set_variables_handler(self, variables_handler):
+            return variables_handler.get_variable("robotVelocity").is_valid()
+
+        def size(self):
+            return 10
+
+        def is_valid(self):
+            return True
+
+    qp2 = blf.ik.QPInverseKinematics()
+    assert qp2.initialize(handler=_handler())
+    var = blf.system.VariablesHandler()
+    assert var.add_variable("robotVelocity", 38)
+    assert qp2.add_task(CustomTask(), "custom_task", 0) and qp2.finalize(var)
+    assert not qp2.advance()      # a task with its own A and b is accepted by the interface but not solved by the batched kernels
+
+
+def test_manif_stand_in():
+    rng = np.random.default_rng(0)
+    w = rng.normal(size=3)
+    R = manif.SO3Tangent(w).exp()
+    assert np.allclose(R.log().coeffs(), w) and np.allclose(R.rotation() @ R.rotation().T, np.eye(3))
+    R0 = manif.SO3Tangent(rng.normal(size=3)).exp()
+    left = manif.SO3Tangent(w) + R0                            # left-plus: Exp(w) R0
+    assert np.allclose(left.rotation(), R.rotation() @ R0.rotation())
+    assert np.allclose((left - R0).coeffs(), (R0.inverse() * R * R0).log().coeffs())
+
+
+# ------------------------------------------------------------------------------------------------ GPU
+@pytest.mark.gpu
+def test_qp_inverse_kinematics_icub_vector():
+    """test_QP_inverse_kinematics.py:293-425 line by line: iCub with 32 joints, CoM + SE3(r_sole) hard, JointTracking soft;
+    advance() succeeds, and with new desiderata the solution changes."""
+    model = M.icub32()
+    joints_list, kindyn = get_kindyn(model)
+    n = kindyn.getNrOfDegreesOfFreedom()
+    assert n == 32
+    qp_ik = blf.ik.QPInverseKinematics()
+    assert qp_ik.initialize(handler=_handler())
+    joint_values = [0.4147046680648114, 0.020109925966605414, -0.008920202688283316, -0.9417931898020863, -0.5243497613177115,
+                    -0.021969353979888327, 0.41490863370740766, 0.019729971064546152, -0.00875663754461344, -0.942238731363784,
+                    -0.5245880299799013, -0.021615580177534933, 0.10368807143683698, -1.7513061346176159e-06, -3.762644846952276e-05,
+                    -0.1599473872698949, 0.4341604471687158, 0.18350557928473807, 0.5390720970077302, 6.0766272665334824e-05,
+                    -0.0010549820549572227, -6.457409077219657e-05, 0.0002255313408076292, 2.3204341497780863e-05, 5.920527253092593e-07,
+                    -0.1591984430641039, 0.4340643739146118, 0.18311274358002663, 0.5398797698508592, 5.367856260643534e-05,
+                    -0.0010455524092736824, 6.414366731688693e-05]
+    s = np.array(joint_values)
+    world_gravity = [0.0, 0.0, blf.math.StandardAccelerationOfGravitation]
+    assert kindyn.setRobotState(np.eye(4), s, [0.0] * 6, [0.0] * n, world_gravity)
+
+    com_task = blf.ik.CoMTask()
+    assert com_task.set_kin_dyn(kindyn) and com_task.initialize(param_handler=_handler(kp_linear=10.0))
+    assert com_task.set_set_point(position=np.array([0., 0., 0.53]), velocity=np.array([0., 0., 0.]))
+    assert qp_ik.add_task(task=com_task, task_name="Com_task", priority=0)
+
+    se3_task = blf.ik.SE3Task()
+    assert se3_task.set_kin_dyn(kindyn) and se3_task.initialize(param_handler=_handler(frame_name="r_sole", kp_linear=10.0, kp_angular=10.0))
+    assert se3_task.set_set_point(I_H_F=manif.SE3(position=[-0.02, 0.1, 0.0], quaternion=[0, 0, 0, 1]), mixed_velocity=manif.SE3Tangent([0.0] * 6))
+    assert qp_ik.add_task(task=se3_task, task_name="se3_task", priority=0)
+
+    joint_tracking_task = blf.ik.JointTrackingTask()
+    assert joint_tracking_task.set_kin_dyn(kindyn) and joint_tracking_task.initialize(param_handler=_handler(kp=[5.0] * n))
+    rng = np.random.default_rng(0)
+    assert joint_tracking_task.set_set_point(joint_position=s + rng.uniform(-5e-3, 5e-3, n))
+    assert qp_ik.add_task(task=joint_tracking_task, task_name="joint_tracking_task", priority=1, weight=[1.0] * n)
+
+    task_names = qp_ik.get_task_names()
+    assert len(task_names) == 3 and 'Com_task' in task_names and 'joint_tracking_task' in task_names and 'se3_task' in task_names
+    qp_ik_var_handler = blf.system.VariablesHandler()
+    assert qp_ik_var_handler.add_variable("robotVelocity", 38) is True
+    assert qp_ik.finalize(handler=qp_ik_var_handler)
+    assert qp_ik.advance()
+    state = qp_ik.get_output()
+    assert qp_ik.is_output_valid()
+    first_joint, first_base = state.joint_velocity.copy(), state.base_velocity.coeffs().copy()
+
+    # the hard constraints hold for the returned velocity: J_com nu = v*, J_sole nu = twist*
+    nu = qp_ik.get_raw_solution()
+    Jc, c = kindyn.getCenterOfMassJacobian(), kindyn.getCenterOfMassPosition()
+    assert np.abs(Jc @ nu - 10.0 * (np.array([0., 0., 0.53]) - c)).max() < 1e-8
+
+    assert com_task.set_set_point(position=np.array([0., 0., 0.5]), velocity=np.array([0., 0., 0.]))
+    assert se3_task.set_set_point(I_H_F=manif.SE3(position=[-0.02, 0.2, 0.0], quaternion=[0, 0, 0, 1]), mixed_velocity=manif.SE3Tangent([0.0] * 6))
+    assert joint_tracking_task.set_set_point(joint_position=s + rng.uniform(-5e-3, 5e-3, n))
+    assert qp_ik.advance()
+    updated_state = qp_ik.get_output()
+    assert qp_ik.is_output_valid()
+    assert first_joint != pytest.approx(updated_state.joint_velocity)
+    assert first_base != pytest.approx(updated_state.base_velocity.coeffs())
+
+
+@pytest.mark.gpu
+def test_floating_base_system_kinematics():
+    """test_floating_base_system_kinematics.py:9-48 (closed form, tolerance 1e-3) -- with a non-identity R0 so that the
+    left-plus convention is pinned, and a second run with a batch of states"""
+    tolerance = 1e-3
+    dt = 0.0001
+    simulation_time = 0.05
+    np.random.seed(42)
+    twist = np.random.uniform(-2, 2, (6))
+    joint_velocity = np.random.uniform(-2, 2, (23))
+    rotation0 = manif.SO3Tangent([0.3, -0.2, 0.5]).exp()
+    position0 = np.array([0.0, 0.0, 0.0])
+    joint_position0 = np.zeros(23)
+    system = blf.continuous_dynamical_system.FloatingBaseSystemVelocityKinematics()
+    system.state = position0, rotation0, joint_position0
+    assert system.set_control_input((twist, joint_velocity))
+    assert not system.set_control_input((twist, joint_velocity[:-1]))
+    integrator = blf.continuous_dynamical_system.FloatingBaseSystemVelocityKinematicsForwardEulerIntegrator()
+    assert not integrator.integrate(timedelta(seconds=0), timedelta(seconds=dt))     # no system yet
+    assert integrator.set_dynamical_system(system) and not integrator.set_dynamical_system(system)
+    integrator.integration_step = timedelta(seconds=dt)
+    assert not integrator.integrate(timedelta(seconds=dt), timedelta(seconds=0))
+    for i in range(0, int(simulation_time / dt), 25):
+        base_position, base_rotation, joint_position = integrator.get_solution()
+        t = i * dt
+        assert base_position == pytest.approx(position0 + t * twist[0:3], abs=tolerance)
+        exact = manif.SO3Tangent(twist[3:6] * t) + rotation0
+        assert base_rotation.rotation() == pytest.approx(exact.rotation(), abs=tolerance)
+        assert joint_position == pytest.approx(joint_position0 + t * joint_velocity, abs=tolerance)
+        assert integrator.integrate(timedelta(seconds=0), timedelta(seconds=25 * dt))
+
+
+@pytest.mark.gpu
+def test_build_closed_loop_batch_and_fixed_base():
+    """QPInverseKinematics.build from a parameter handler (QPInverseKinematicsTest.cpp:642-798) on a batch of 16 ergoCubs,
+    closed with the Python integrator; then QPFixedBaseInverseKinematics: zero base twist on every tick."""
+    model = M.ergocub23()
+    N = 16
+    _, kindyn = get_kindyn(model, N)
+    n = model.n
+    h = blf.parameters_handler.StdParametersHandler()
+    h.set_parameter_vector_string("tasks", ["COM_TASK", "LEFT_FOOT_TASK", "RIGHT_FOOT_TASK", "TORSO_TASK", "REG_TASK", "LIMITS_TASK"])
+    ik_group = _handler()
+    h.set_group("IK", ik_group)
+
+    def group(type_, priority, **kw):
+        g = _handler(**kw)
+        g.set_parameter_string("type", type_)
+        g.set_parameter_int("priority", priority)
+        return g
+    h.set_group("COM_TASK", group("CoMTask", 0, kp_linear=2.0))
+    h.set_group("LEFT_FOOT_TASK", group("SE3Task", 0, frame_name="l_sole", kp_linear=7.0, kp_angular=5.0))
+    h.set_group("RIGHT_FOOT_TASK", group("SE3Task", 0, frame_name="r_sole", kp_linear=7.0, kp_angular=5.0))
+    h.set_group("TORSO_TASK", group("SO3Task", 1, frame_name="chest", kp_angular=5.0, weight=[5.0, 5.0, 5.0]))
+    h.set_group("REG_TASK", group("JointTrackingTask", 1, kp=[5.0] * n, weight=[1.0] * n))
+    h.set_group("LIMITS_TASK", group("JointVelocityLimitsTask", 0, upper_limits=[2.0] * n, lower_limits=[-2.0] * n))
+    variables, weights, ik = blf.ik.QPInverseKinematics.build(param_handler=h, kin_dyn=kindyn)
+    assert ik is not None and set(weights) == {"TORSO_TASK", "REG_TASK"} and variables.get_number_of_variables() == n + 6
+
+    rng = np.random.default_rng(5)
+    from blf_b200 import workloads as W
+    s_des = np.clip(0.5 * (model.q_lower + model.q_upper)[None] + rng.uniform(-0.15, 0.15, (N, n)), model.q_lower, model.q_upper)
+    p0 = np.tile([0.0, 0.0, 0.75], (N, 1))
+    q0 = W.so3_exp(np.tile([0.0, 0.05, 0.1], (N, 1)))
+    desired = blf.KinDynComputations(model, N)
+    desired.set_robot_state_batch(p0, q0, s_des)
+    k = desired.batch_kinematics(["l_sole", "r_sole", "chest"], jac=False, com=True)
+    quat = W.rot_to_quat(k["frame_rot"].reshape(-1, 3, 3)).reshape(N, 3, 4)
+    zeros6 = np.zeros((N, 6))
+    assert ik.get_task("COM_TASK").set_set_point(position=k["com"])
+    assert ik.get_task("LEFT_FOOT_TASK").set_set_point(np.hstack([k["frame_pos"][:, 0], quat[:, 0], zeros6]))
+    assert ik.get_task("RIGHT_FOOT_TASK").set_set_point(np.hstack([k["frame_pos"][:, 1], quat[:, 1], zeros6]))
+    assert not ik.advance()                                    # TORSO / REG set-points still missing
+    assert ik.get_task("TORSO_TASK").set_set_point(np.hstack([quat[:, 2], np.zeros((N, 3))]))
+    assert ik.get_task("REG_TASK").set_set_point(joint_position=s_des)
+
+    system = blf.continuous_dynamical_system.FloatingBaseSystemVelocityKinematics()
+    system.state = p0.copy(), q0.copy(), s_des + rng.normal(0, 0.05, (N, n))
+    integrator = blf.continuous_dynamical_system.FloatingBaseSystemVelocityKinematicsForwardEulerIntegrator()
+    assert integrator.set_dynamical_system(system)
+    integrator.integration_step = timedelta(milliseconds=10)
+    for _ in range(120):
+        p, q, s = integrator.get_solution()
+        assert kindyn.set_robot_state_batch(p, q, s)
+        assert ik.advance() and ik.is_output_valid()
+        nu = ik.get_batch_output()
+        assert np.abs(nu[:, 6:]).max() <= 2.0 + 1e-9
+        assert system.set_control_input((nu[:, :6], nu[:, 6:]))
+        assert integrator.integrate(timedelta(0), timedelta(milliseconds=10))
+    p, q, s = integrator.get_solution()
+    kindyn.set_robot_state_batch(p, q, s)
+    kk = kindyn.batch_kinematics(["l_sole"], jac=False, com=True)
+    assert np.abs(kk["com"] - k["com"]).max() < 2e-3 and np.abs(kk["frame_pos"][:, 0] - k["frame_pos"][:, 0]).max() < 2e-3
+
+    # fixed base
+    fixed = blf.ik.QPFixedBaseInverseKinematics()
+    assert not fixed.initialize(handler=_handler())            # set_kin_dyn first
+    assert fixed.set_kin_dyn(kindyn) and fixed.initialize(handler=_handler())
+    assert fixed.get_task_names() == ["base_se3_task"]
+    hand = blf.ik.SE3Task()
+    assert hand.set_kin_dyn(kindyn) and hand.initialize(param_handler=_handler(frame_name="l_hand_palm", kp_linear=5.0, kp_angular=5.0))
+    reg = blf.ik.JointTrackingTask()
+    assert reg.set_kin_dyn(kindyn) and reg.initialize(param_handler=_handler(kp=[1.0] * n))
+    assert fixed.add_task(hand, "hand", 0) and fixed.add_task(reg, "reg", 1, weight=[1.0] * n)
+    var = blf.system.VariablesHandler()
+    assert var.add_variable("robotVelocity", n + 6) and fixed.finalize(var)
+    kh = desired.batch_kinematics(["l_hand_palm"], jac=False, com=False)
+    qh = W.rot_to_quat(kh["frame_rot"].reshape(-1, 3, 3))
+    assert hand.set_set_point(np.hstack([kh["frame_pos"][:, 0], qh, zeros6])) and reg.set_set_point(joint_position=s_des)
+    system2 = blf.continuous_dynamical_system.FloatingBaseSystemVelocityKinematics()
+    system2.state = p0.copy(), q0.copy(), s_des + rng.normal(0, 0.05, (N, n))
+    integrator2 = blf.continuous_dynamical_system.FloatingBaseSystemVelocityKinematicsForwardEulerIntegrator()
+    assert integrator2.set_dynamical_system(system2)
+    integrator2.integration_step = timedelta(milliseconds=10)
+    for _ in range(100):
+        p, q, s = integrator2.get_solution()
+        kindyn.set_robot_state_batch(p, q, s)
+        assert fixed.advance()
+        nu = fixed.get_batch_output()
+        assert np.abs(nu[:, :6]).max() < 1e-9
+        system2.set_control_input((nu[:, :6], nu[:, 6:]))
+        assert integrator2.integrate(timedelta(0), timedelta(milliseconds=10))
+    p, q, s = integrator2.get_solution()
+    kindyn.set_robot_state_batch(p, q, s)
+    assert np.abs(kindyn.batch_kinematics(["l_hand_palm"], jac=False, com=False)["frame_pos"] - kh["frame_pos"]).max() < 2e-3
+    assert np.abs(p - p0).max() < 1e-9
