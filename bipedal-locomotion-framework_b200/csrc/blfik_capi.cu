@@ -192,7 +192,7 @@ struct HostTask {
 };
 
 constexpr int kMaxChunks = 16;
-constexpr int kCounterSlots = 8;   // work counters of the register-resident kernel, one per launch that may be in flight
+constexpr int kCounterSlots = kMaxChunks;   // work counters of the register-resident kernel, one per launch that may be in flight
 
 struct blfik_problem {
     const blfik_model* model = nullptr;
@@ -231,7 +231,7 @@ struct blfik_problem {
     int njump = 0, has_com = 0;
     // pipelined host-buffer tick (blfik_tick_host)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
-    cudaStream_t chunk_stream[2] = {nullptr, nullptr};   // blfik_tick_packed: consecutive chunk kernels alternate, so one fills the SMs the other's tail leaves idle
+    cudaStream_t chunk_stream[4] = {nullptr, nullptr, nullptr, nullptr};   // blfik_tick_packed: consecutive chunk kernels alternate, so one fills the SMs the other's tail leaves idle
     cudaEvent_t ev_in[16] = {}, ev_done[16] = {}, ev_start = nullptr;
     double time = 0.0;               // time of the next tick (advanced by integrating ticks; set-point trajectories)
     int packed_len = 0;              // doubles per packed input record: 7 + n + sum of set-point lengths
@@ -692,7 +692,7 @@ extern "C" void blfik_problem_destroy(blfik_problem* p)
         for (int c = 0; c < kMaxChunks; c++) cudaEventDestroy(p->ev_in[c]), cudaEventDestroy(p->ev_done[c]);
         cudaEventDestroy(p->ev_start);
         cudaStreamDestroy(p->h2d_stream), cudaStreamDestroy(p->d2h_stream);
-        for (int k = 0; k < 2; k++)
+        for (int k = 0; k < 4; k++)
             if (p->chunk_stream[k]) cudaStreamSynchronize(p->chunk_stream[k]), cudaStreamDestroy(p->chunk_stream[k]);
     }
     if (p->own_stream && p->stream) cudaStreamDestroy(p->stream);
@@ -1083,7 +1083,8 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     // PCIe writes, no latency to hide), otherwise they are copied back chunk by chunk
     double* nu_map = nullptr;
     int* status_map = nullptr;
-    {
+    static const int host_write = [] { const char* e = getenv("BLFIK_HOST_WRITE"); return e ? atoi(e) : 1; }();
+    if (host_write) {
         cudaPointerAttributes at;
         if (cudaPointerGetAttributes(&at, nu) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) nu_map = static_cast<double*>(at.devicePointer);
         else cudaGetLastError();
@@ -1092,7 +1093,8 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
             else cudaGetLastError(), nu_map = nullptr;
         }
     }
-    for (int k = 0; k < 2; k++) {
+    static const int nstreams = [] { const char* e = getenv("BLFIK_CHUNK_STREAMS"); int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > 4 ? 4 : v); }();
+    for (int k = 0; k < nstreams; k++) {
         if (!p->chunk_stream[k]) CU(cudaStreamCreateWithFlags(&p->chunk_stream[k], cudaStreamNonBlocking));
         CU(cudaStreamWaitEvent(p->chunk_stream[k], p->ev_start, 0));
     }
@@ -1101,7 +1103,7 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     for (int c = 0; c < nchunks; c++) {
         const long long a = bound(c), b = bound(c + 1), cnt = b - a;
         if (cnt <= 0) continue;
-        cudaStream_t cs = p->chunk_stream[c & 1];
+        cudaStream_t cs = p->chunk_stream[c % nstreams];
         CU(cudaMemcpyAsync(p->d_packed + (size_t)R * a, records + (size_t)R * a, (size_t)cnt * R * sizeof(double), cudaMemcpyHostToDevice, p->h2d_stream));
         CU(cudaEventRecord(p->ev_in[c], p->h2d_stream));
         CU(cudaStreamWaitEvent(cs, p->ev_in[c], 0));
