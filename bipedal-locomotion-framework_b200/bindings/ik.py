@@ -387,6 +387,29 @@ class GravityTask(IKLinearTask):
         return T.gravity_task(self._kin_dyn.model(), name, self._target_name, self._kp, priority, weight)
 
 
+class AngularMomentumTask(IKLinearTask):
+    """AngularMomentumTask.cpp:67-135 (key mask, optional), :137-210"""
+    _sp_len = 3
+
+    def initialize(self, param_handler):
+        if not self._common_initialize(param_handler):
+            return False
+        m = param_handler._opt(param_handler.get_parameter_vector_bool, "mask")
+        self._mask3 = tuple(bool(x) for x in m) if (m is not None and len(m) == 3) else (True, True, True)
+        self._description = "Angular momentum task."
+        self._initialized = True
+        return True
+
+    def set_set_point(self, desired_angular_momentum, instance=None):
+        return self._store(_vec(desired_angular_momentum, 3), instance)
+
+    def size(self):
+        return sum(self._mask3)
+
+    def _spec(self, name, priority, weight):
+        return T.angular_momentum_task(self._kin_dyn.model(), name, priority, weight, self._mask3)
+
+
 class JointTrackingTask(IKLinearTask):
     """JointTrackingTask.cpp:90-112 (key kp, size-checked), :127-155, setSetPoint :157-210"""
 
@@ -498,7 +521,7 @@ class IntegrationBasedIKState:
         self.base_velocity = manif.SE3Tangent()
 
 
-_TASK_TYPES = {c.__name__: c for c in (SE3Task, CoMTask, SO3Task, R3Task, DistanceTask, GravityTask, JointTrackingTask,
+_TASK_TYPES = {c.__name__: c for c in (SE3Task, CoMTask, SO3Task, R3Task, DistanceTask, GravityTask, AngularMomentumTask, JointTrackingTask,
                                         JointLimitsTask, JointVelocityLimitsTask)}
 
 

@@ -44,7 +44,8 @@ EXPORTS = [
 class ModelDesc(C.Structure):
     _fields_ = [("n_dofs", C.c_int32), ("n_frames", C.c_int32), ("parent", c_int_p), ("dof", c_int_p),
                 ("X_rot", c_double_p), ("X_pos", c_double_p), ("axis", c_double_p), ("mass", c_double_p),
-                ("com", c_double_p), ("frame_link", c_int_p), ("frame_rot", c_double_p), ("frame_pos", c_double_p)]
+                ("com", c_double_p), ("frame_link", c_int_p), ("frame_rot", c_double_p), ("frame_pos", c_double_p),
+                ("inertia", c_double_p)]
 
 
 class TaskDesc(C.Structure):
@@ -156,11 +157,13 @@ class Model:
         self.km = km
         k = dict(parent=np.ascontiguousarray(km.parent, dtype=np.int32), dof=np.ascontiguousarray(km.dof, dtype=np.int32),
                  Xr=_f64(km.Xr), Xp=_f64(km.Xp), axis=_f64(km.axis), mass=_f64(km.mass), com=_f64(km.com),
-                 fl=np.ascontiguousarray(km.frame_link, dtype=np.int32), Fr=_f64(km.Fr), Fp=_f64(km.Fp))
+                 fl=np.ascontiguousarray(km.frame_link, dtype=np.int32), Fr=_f64(km.Fr), Fp=_f64(km.Fp),
+                 I6=_f64(np.stack([km.inertia[:, 0, 0], km.inertia[:, 0, 1], km.inertia[:, 0, 2], km.inertia[:, 1, 1],
+                                   km.inertia[:, 1, 2], km.inertia[:, 2, 2]], axis=1)))
         d = ModelDesc(km.n, len(km.frame_names), k["parent"].ctypes.data_as(c_int_p), k["dof"].ctypes.data_as(c_int_p),
                       k["Xr"].ctypes.data_as(c_double_p), k["Xp"].ctypes.data_as(c_double_p), k["axis"].ctypes.data_as(c_double_p),
                       k["mass"].ctypes.data_as(c_double_p), k["com"].ctypes.data_as(c_double_p), k["fl"].ctypes.data_as(c_int_p),
-                      k["Fr"].ctypes.data_as(c_double_p), k["Fp"].ctypes.data_as(c_double_p))
+                      k["Fr"].ctypes.data_as(c_double_p), k["Fp"].ctypes.data_as(c_double_p), k["I6"].ctypes.data_as(c_double_p))
         self.handle = C.c_void_p()
         _check(L.blfik_model_create(C.byref(d), C.byref(self.handle)))
 

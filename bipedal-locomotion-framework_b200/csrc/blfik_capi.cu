@@ -176,7 +176,7 @@ struct blfik_model {
     int n = 0, nf = 0, maxdepth = 0;
     std::vector<int> parent, dof, depth, link_of_dof, frame_link;
     std::vector<unsigned long long> anc;
-    std::vector<double> Xr, Xp, axis, mass, com, msub, Fr, Fp;
+    std::vector<double> Xr, Xp, axis, mass, com, msub, Fr, Fp, inertia;   // inertia: [nl][6], empty = point masses
     double total_mass = 0;
 };
 
@@ -330,6 +330,7 @@ static int rows_of(const blfik_task_desc& d, int n)
     case BLFIK_TASK_SO3: return 3;
     case BLFIK_TASK_DISTANCE: return 1;
     case BLFIK_TASK_GRAVITY: return 2;
+    case BLFIK_TASK_ANGULAR_MOMENTUM: return nm;
     case BLFIK_TASK_JOINT_TRACKING: return n;
     case BLFIK_TASK_JOINT_LIMITS: return 2 * n;
     case BLFIK_TASK_JOINT_VELOCITY_LIMITS: return 2 * n;
@@ -345,6 +346,7 @@ static int sp_len_of(int type, int n)
     case BLFIK_TASK_SO3: return 7;
     case BLFIK_TASK_DISTANCE: return 1;
     case BLFIK_TASK_GRAVITY: return 6;
+    case BLFIK_TASK_ANGULAR_MOMENTUM: return 3;
     case BLFIK_TASK_JOINT_TRACKING: return 2 * n;
     default: return 0;
     }
@@ -378,6 +380,7 @@ extern "C" int blfik_model_create(const blfik_model_desc* d, blfik_model** out)
     m->Xr.assign(d->X_rot, d->X_rot + 9 * nl), m->Xp.assign(d->X_pos, d->X_pos + 3 * nl);
     m->axis.assign(d->axis, d->axis + 3 * nl), m->mass.assign(d->mass, d->mass + nl), m->com.assign(d->com, d->com + 3 * nl);
     m->frame_link.assign(d->frame_link, d->frame_link + nf);
+    if (d->inertia) m->inertia.assign(d->inertia, d->inertia + 6 * nl);
     m->Fr.assign(d->frame_rot, d->frame_rot + 9 * nf), m->Fp.assign(d->frame_pos, d->frame_pos + 3 * nf);
     m->depth.assign(nl, 0), m->anc.assign(nl, 0ull), m->link_of_dof.assign(n, -1), m->msub.assign(n, 0.0);
     std::vector<char> seen(n, 0);
@@ -601,7 +604,10 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
     // ---- register-resident kernel: pick the smallest instantiation that holds (nv, K)
     {
         const int nv = p->nv, K = p->K;
-        if (nv <= 32 && K <= 32) {
+        bool angmom = false;
+        for (const HostTask& h : p->tasks) angmom |= h.d.type == BLFIK_TASK_ANGULAR_MOMENTUM;
+        // the centroidal momentum rows exist in the generic kernel only (the task is rare)
+        if (nv <= 32 && K <= 32 && !angmom) {
             if (nv == 29) {
                 if (K <= 16) pick_fast<29, 16>(p);
                 else if (K <= 18) pick_fast<29, 18>(p);
@@ -654,15 +660,15 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
     dm.n = n, dm.nl = n + 1, dm.nf = model->nf, dm.maxdepth = model->maxdepth, dm.inv_total_mass = 1.0 / model->total_mass;
     int *d_parent, *d_dof, *d_depth, *d_lod, *d_fl;
     unsigned long long* d_anc;
-    double *d_Xr, *d_Xp, *d_axis, *d_mass, *d_com, *d_msub, *d_Fr, *d_Fp;
+    double *d_Xr, *d_Xp, *d_axis, *d_mass, *d_com, *d_msub, *d_Fr, *d_Fp, *d_inertia;
     if ((rc = dev_upload(p, model->parent, &d_parent)) || (rc = dev_upload(p, model->dof, &d_dof)) || (rc = dev_upload(p, model->depth, &d_depth)) ||
         (rc = dev_upload(p, model->link_of_dof, &d_lod)) || (rc = dev_upload(p, model->frame_link, &d_fl)) || (rc = dev_upload(p, model->anc, &d_anc)) ||
         (rc = dev_upload(p, model->Xr, &d_Xr)) || (rc = dev_upload(p, model->Xp, &d_Xp)) || (rc = dev_upload(p, model->axis, &d_axis)) ||
         (rc = dev_upload(p, model->mass, &d_mass)) || (rc = dev_upload(p, model->com, &d_com)) || (rc = dev_upload(p, model->msub, &d_msub)) ||
-        (rc = dev_upload(p, model->Fr, &d_Fr)) || (rc = dev_upload(p, model->Fp, &d_Fp)))
+        (rc = dev_upload(p, model->Fr, &d_Fr)) || (rc = dev_upload(p, model->Fp, &d_Fp)) || (rc = dev_upload(p, model->inertia, &d_inertia)))
         return bail(rc);
     dm.parent = d_parent, dm.dof = d_dof, dm.depth = d_depth, dm.link_of_dof = d_lod, dm.frame_link = d_fl, dm.anc = d_anc;
-    dm.Xr = d_Xr, dm.Xp = d_Xp, dm.axis = d_axis, dm.mass = d_mass, dm.com = d_com, dm.msub = d_msub, dm.Fr = d_Fr, dm.Fp = d_Fp;
+    dm.Xr = d_Xr, dm.Xp = d_Xp, dm.axis = d_axis, dm.mass = d_mass, dm.com = d_com, dm.msub = d_msub, dm.Fr = d_Fr, dm.Fp = d_Fp, dm.inertia = d_inertia;
 
     const size_t Ns = (size_t)N;
     if ((rc = dev_alloc(p, Ns * 3, &p->base_pos)) || (rc = dev_alloc(p, Ns * 4, &p->base_quat)) || (rc = dev_alloc(p, Ns * n, &p->s)) ||

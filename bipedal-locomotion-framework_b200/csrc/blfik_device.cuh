@@ -17,8 +17,8 @@ constexpr double kInf = 1e30;       // OsqpEigen::INFTY
 constexpr double kInfHalf = 0.5e30;
 constexpr unsigned kFull = 0xffffffffu;
 
-enum TaskType : int { T_SE3 = 0, T_COM = 1, T_SO3 = 2, T_JOINT_TRACKING = 3, T_JOINT_LIMITS = 4, T_JOINT_VEL_LIMITS = 5, T_R3 = 6, T_DISTANCE = 7, T_GRAVITY = 8 };
-__host__ __device__ inline bool is_dense_type(int t) { return t == T_SE3 || t == T_COM || t == T_SO3 || t == T_R3 || t == T_DISTANCE || t == T_GRAVITY; }
+enum TaskType : int { T_SE3 = 0, T_COM = 1, T_SO3 = 2, T_JOINT_TRACKING = 3, T_JOINT_LIMITS = 4, T_JOINT_VEL_LIMITS = 5, T_R3 = 6, T_DISTANCE = 7, T_GRAVITY = 8, T_ANGMOM = 9 };
+__host__ __device__ inline bool is_dense_type(int t) { return t == T_SE3 || t == T_COM || t == T_SO3 || t == T_R3 || t == T_DISTANCE || t == T_GRAVITY || t == T_ANGMOM; }
 
 struct DevModel {
     int n, nl, nf, maxdepth;
@@ -37,6 +37,7 @@ struct DevModel {
     const int* frame_link;   // [nf]
     const double* Fr;        // [nf][9]
     const double* Fp;        // [nf][3]
+    const double* inertia;   // [nl][6] Ixx Ixy Ixz Iyy Iyz Izz about the link CoM, link frame (nullptr: point masses)
 };
 
 struct DevTask {
@@ -142,6 +143,11 @@ __device__ __forceinline__ void mat3_mul(const double* A, const double* B, doubl
     for (int i = 0; i < 3; i++)
 #pragma unroll
         for (int j = 0; j < 3; j++) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+}
+__device__ __forceinline__ void mat3T_vec(const double* A, const double* v, double* o)
+{
+#pragma unroll
+    for (int i = 0; i < 3; i++) o[i] = A[i] * v[0] + A[3 + i] * v[1] + A[6 + i] * v[2];
 }
 __device__ __forceinline__ void mat3_vec(const double* A, const double* v, double* o)
 {
@@ -410,6 +416,58 @@ __device__ __forceinline__ void k1_com(const DevModel& m, const WM& w, double* c
     }
 }
 
+// Angular rows of the centroidal momentum matrix in MIXED representation (iDynTree getCentroidalTotalMomentumJacobian,
+// rows 3..5; AngularMomentumTask.cpp:137-185): L = sum_k [ I_k^W w_k + m_k (c_k - c) x cdot_k ] about the CoM c.
+// Column of a DoF with world axis a through o: every link k distal to it turns with w_k = a, cdot_k = a x (c_k - o);
+// base angular columns: all links, a = e_i through p_B; base linear columns: sum m_k (c_k - c) x e_i = 0.
+__device__ __forceinline__ void k1_angmom(const DevModel& m, const WM& w, const double* com, double* dst, int ld, int lane)
+{
+    const int nv = m.n + 6;
+    for (int c = lane; c < nv; c += 32) {
+        double col[3] = {0.0, 0.0, 0.0};
+        if (c >= 3) {
+            double a[3] = {0.0, 0.0, 0.0}, o[3];
+            int j = -1;
+            if (c < 6) {
+                a[c - 3] = 1.0;
+                o[0] = w.linkP[0], o[1] = w.linkP[1], o[2] = w.linkP[2];
+            } else {
+                j = c - 6;
+                const int kj = m.link_of_dof[j];
+#pragma unroll
+                for (int i = 0; i < 3; i++) a[i] = w.axisW[3 * kj + i], o[i] = w.linkP[3 * kj + i];
+            }
+            for (int k = 0; k < m.nl; k++) {
+                if (j >= 0 && !((m.anc[k] >> j) & 1ull)) continue;
+                const double mk = m.mass[k];
+                const double* R = w.linkR + 9 * k;
+                if (m.inertia) {
+                    const double* I6 = m.inertia + 6 * k;
+                    double al[3], il[3], iw[3];
+                    mat3T_vec(R, a, al);
+                    il[0] = I6[0] * al[0] + I6[1] * al[1] + I6[2] * al[2];
+                    il[1] = I6[1] * al[0] + I6[3] * al[1] + I6[4] * al[2];
+                    il[2] = I6[2] * al[0] + I6[4] * al[1] + I6[5] * al[2];
+                    mat3_vec(R, il, iw);
+                    col[0] += iw[0], col[1] += iw[1], col[2] += iw[2];
+                }
+                if (mk > 0.0) {
+                    const double inv = 1.0 / mk;
+                    const double ck[3] = {w.mcw[3 * k] * inv, w.mcw[3 * k + 1] * inv, w.mcw[3 * k + 2] * inv};
+                    const double r[3] = {ck[0] - o[0], ck[1] - o[1], ck[2] - o[2]};
+                    const double d[3] = {ck[0] - com[0], ck[1] - com[1], ck[2] - com[2]};
+                    double v[3], t[3];
+                    cross3(a, r, v);
+                    cross3(d, v, t);
+                    col[0] += mk * t[0], col[1] += mk * t[1], col[2] += mk * t[2];
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++) dst[i * ld + c] = col[i];
+    }
+}
+
 // Set-point of a task at time t when an on-device trajectory is attached (the set-point producers
 // that feed setSetPoint): x_d(t) = x_0 + A sin(w t + phi_i), feed-forward += A w cos(w t + phi_i); orientations move by
 // the world-frame rotation Exp(A_ang sin(.)) about a fixed axis, whose angular velocity is exactly A_ang w cos(.).
@@ -464,7 +522,16 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
             int src[6];
             int rows = 0;
             sp = traj_eval(tk, robot, tnow, sp, spl);
-            if (tk.type == T_COM) {
+            if (tk.type == T_ANGMOM) {   // AngularMomentumTask.cpp:137-185: A = masked rows of the angular CMM, b = desired momentum
+                double com[3];
+                k1_com(m, w, com, nullptr, LD, lane);
+                k1_angmom(m, w, com, w.Jt, LD, lane);
+                for (int c = 0; c < 3; c++)
+                    if (tk.mask[c]) {
+                        bt[rows] = sp[c];
+                        src[rows++] = c;
+                    }
+            } else if (tk.type == T_COM) {
                 double com[3];
                 k1_com(m, w, com, w.Jt, LD, lane);
                 for (int c = 0; c < 3; c++)

@@ -1,5 +1,5 @@
 /**
- * IK.h -- the IK:: classes of the reference with a batch dimension: IKLinearTask, SE3Task, CoMTask, SO3Task, R3Task, DistanceTask, GravityTask,
+ * IK.h -- the IK:: classes of the reference with a batch dimension: IKLinearTask, SE3Task, CoMTask, SO3Task, R3Task, DistanceTask, GravityTask, AngularMomentumTask,
  * JointTrackingTask, JointLimitsTask, JointVelocityLimitsTask, IntegrationBasedIK{,State,Problem}, QPInverseKinematics.
  * Same class / method / parameter-key names and the same bool + log()->error convention as
  * the headers under src/IK/include/BipedalLocomotion/IK; N = 1 reproduces the reference semantics, N > 1 runs N robots per tick.
@@ -271,6 +271,27 @@ private:
     int m_targetFrameIndex{-1};
     double m_kp{0.0};
     BLF_REGISTER_IK_TASK(GravityTask);
+};
+
+/** AngularMomentumTask.h / AngularMomentumTask.cpp:44-230: A = (masked) rows 3..5 of the centroidal momentum matrix,
+ *  b = desired centroidal angular momentum; key: mask (optional).  The rows exist on the device only: update() checks
+ *  the state of the task, getA() is not materialised for this task. */
+class AngularMomentumTask : public IKLinearTask
+{
+public:
+    const char* className() const override { return "AngularMomentumTask"; }
+    bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
+    bool update() override;
+    bool setSetPoint(const Vector3d& desiredAngularMomentum, std::ptrdiff_t instance = -1);
+    std::size_t size() const override { return m_DoFs; }
+    Type type() const override { return Type::equality; }
+    bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
+    std::size_t setPointLength() const override { return 3; }
+
+private:
+    std::array<bool, 3> m_mask{true, true, true};
+    std::size_t m_DoFs{3};
+    BLF_REGISTER_IK_TASK(AngularMomentumTask);
 };
 
 /** JointTrackingTask.cpp:29-210 */

@@ -32,7 +32,7 @@ bool KinDynBatch::loadRobotModelFromFile(const std::string& path)
         return false;
     }
     std::vector<int> parent, dof, frameLink;
-    std::vector<double> Xr, Xp, axis, mass, com, Fr, Fp;
+    std::vector<double> Xr, Xp, axis, mass, com, Fr, Fp, inertia;
     std::vector<std::string> jointOfLink;
     std::map<std::string, std::array<double, 3>> limits;
     while (in >> tok) {
@@ -67,6 +67,12 @@ bool KinDynBatch::loadRobotModelFromFile(const std::string& path)
                 if (r[0] == 1 && r[4] == 1 && r[8] == 1 && r[1] == 0 && r[2] == 0 && r[3] == 0 && r[5] == 0 && r[6] == 0 && r[7] == 0 && t[0] == 0 && t[1] == 0 && t[2] == 0)
                     m_floatingBase = fname;
             }
+        } else if (tok == "inertia") {
+            std::string lname;
+            int k;
+            in >> lname >> k;
+            if (inertia.size() < static_cast<std::size_t>(6 * (k + 1))) inertia.resize(6 * (k + 1), 0.0);
+            for (int i = 0; i < 6; i++) in >> inertia[6 * k + i];
         } else if (tok == "limits") {
             std::string jname;
             std::array<double, 3> l;
@@ -89,6 +95,7 @@ bool KinDynBatch::loadRobotModelFromFile(const std::string& path)
     blfik_model_desc d;
     d.n_dofs = n, d.n_frames = nf, d.parent = parent.data(), d.dof = dof.data(), d.X_rot = Xr.data(), d.X_pos = Xp.data(), d.axis = axis.data();
     d.mass = mass.data(), d.com = com.data(), d.frame_link = frameLink.data(), d.frame_rot = Fr.data(), d.frame_pos = Fp.data();
+    d.inertia = inertia.size() == static_cast<std::size_t>(6 * (n + 1)) ? inertia.data() : nullptr;
     if (blfik_model_create(&d, &m_model) != BLFIK_OK) {
         log()->error("{} {}", logPrefix, blfik_last_error());
         return false;
@@ -786,6 +793,61 @@ bool GravityTask::fillDescriptor(blfik_task_desc& d, std::vector<std::vector<dou
     d = blfik_task_desc{};
     d.type = BLFIK_TASK_GRAVITY, d.frame = m_targetFrameIndex, d.ref_frame = -1, d.controller_enabled = 1;
     for (int c = 0; c < 3; c++) d.mask[c] = 1, d.kp_linear[c] = m_kp;
+    return m_isInitialized;
+}
+
+// =================================================================== AngularMomentumTask
+bool AngularMomentumTask::initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler)
+{
+    std::shared_ptr<const ParametersHandler::IParametersHandler> ptr;
+    if (!commonInitialize(paramHandler, ptr)) return false;
+    std::vector<bool> mask;
+    if (ptr->getParameter("mask", mask) && mask.size() == 3) {   // otherwise the default (all true) is used, :111-131
+        m_mask = {mask[0], mask[1], mask[2]};
+        m_DoFs = static_cast<std::size_t>(m_mask[0]) + m_mask[1] + m_mask[2];
+    } else {
+        log()->info("[AngularMomentumTask::initialize] Unable to find the mask parameter. The default value is used.");
+    }
+    m_description = "Angular momentum task.";
+    m_isInitialized = true;
+    return true;
+}
+
+bool AngularMomentumTask::setSetPoint(const Vector3d& L, std::ptrdiff_t instance)
+{
+    if (!m_kinDyn) return false;
+    const double rec[3] = {L[0], L[1], L[2]};
+    storeSetPoint(rec, instance);
+    m_isSetPointSetAtLeastOnce = true;
+    return true;
+}
+
+bool AngularMomentumTask::update()
+{
+    m_isValid = false;
+    if (!m_isInitialized) {
+        log()->error("[AngularMomentumTask::update] The task is not initialized. Please call initialize method.");
+        return m_isValid;
+    }
+    if (!m_isSetPointSetAtLeastOnce) {
+        log()->error("[AngularMomentumTask::update] The set point has not been set at least once.");
+        return m_isValid;
+    }
+    const int i = inspected();
+    if (i >= 0 && m_b.size() == size()) {   // b = masked desired momentum (:187-210)
+        std::size_t idx = 0;
+        for (int c = 0; c < 3; c++)
+            if (m_mask[c]) m_b[idx++] = m_sp[3 * i + c];
+    }
+    m_isValid = true;
+    return m_isValid;
+}
+
+bool AngularMomentumTask::fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>&) const
+{
+    d = blfik_task_desc{};
+    d.type = BLFIK_TASK_ANGULAR_MOMENTUM, d.frame = -1, d.ref_frame = -1, d.controller_enabled = 1;
+    for (int c = 0; c < 3; c++) d.mask[c] = m_mask[c];
     return m_isInitialized;
 }
 

@@ -23,7 +23,7 @@ from __future__ import annotations
 
 import dataclasses
 import math
-from typing import Dict, List, Sequence, Tuple
+from typing import Optional, Dict, List, Sequence, Tuple
 
 import numpy as np
 
@@ -57,6 +57,11 @@ class KinematicModel:
     q_lower: np.ndarray             # [n]
     q_upper: np.ndarray             # [n]
     q_nominal: np.ndarray           # [n]
+    inertia: Optional[np.ndarray] = None   # [n+1,3,3] rotational inertia about the link CoM, link frame (AngularMomentumTask)
+
+    def __post_init__(self):
+        if self.inertia is None:
+            self.inertia = np.zeros((len(self.joint_names) + 1, 3, 3))
 
     @property
     def n(self) -> int:
@@ -94,6 +99,10 @@ class KinematicModel:
             jn = self.joint_names[self.dof[k]] if k > 0 else "-"
             vals = [*self.Xr[k].ravel(), *self.Xp[k], *self.axis[k], self.mass[k], *self.com[k]]
             out.append(f"link {self.link_names[k]} {self.parent[k]} {self.dof[k]} {jn} " + " ".join(repr(float(v)) for v in vals))
+        for k in range(self.n + 1):
+            I = self.inertia[k]
+            vals = [I[0, 0], I[0, 1], I[0, 2], I[1, 1], I[1, 2], I[2, 2]]
+            out.append(f"inertia {self.link_names[k]} {k} " + " ".join(repr(float(v)) for v in vals))
         for f, fn in enumerate(self.frame_names):
             vals = [*self.Fr[f].ravel(), *self.Fp[f]]
             out.append(f"frame {fn} {self.frame_link[f]} " + " ".join(repr(float(v)) for v in vals))
@@ -123,6 +132,18 @@ class LinkDesc:
     name: str
     mass: float
     com: Tuple[float, float, float]
+    inertia: Optional[np.ndarray] = None   # 3x3 about the CoM in the link frame; None: default_inertia(mass, com)
+
+
+def default_inertia(mass: float, com) -> np.ndarray:
+    """Deterministic stand-in for a URDF <inertia>: a box with half extents 4 cm + |com| per axis, with mild products of
+    inertia so that the full symmetric tensor is exercised (positive definite by diagonal dominance)."""
+    h = 0.04 + np.abs(np.asarray(com, dtype=float))
+    d = mass / 3.0 * np.array([h[1] ** 2 + h[2] ** 2, h[0] ** 2 + h[2] ** 2, h[0] ** 2 + h[1] ** 2])
+    I = np.diag(d)
+    for (a, b), f in (((0, 1), 0.10), ((0, 2), -0.07), ((1, 2), 0.05)):
+        I[a, b] = I[b, a] = f * math.sqrt(d[a] * d[b])
+    return I
 
 
 @dataclasses.dataclass
@@ -155,6 +176,7 @@ def reduce_model(name: str, base_link: str, links: Sequence[LinkDesc], joints: S
     rl_axis: List[np.ndarray] = []
     rl_mass: List[float] = []
     rl_mcom: List[np.ndarray] = []
+    rl_IO: List[np.ndarray] = []   # rotational inertia about the reduced link's frame origin (parallel-axis sums)
     fr_out: List[Tuple[str, int, np.ndarray, np.ndarray]] = []
     frames_by_link: Dict[str, List[FrameDesc]] = {}
     for f in frames:
@@ -164,7 +186,7 @@ def reduce_model(name: str, base_link: str, links: Sequence[LinkDesc], joints: S
     def new_reduced_link(nm, parent, dof, Xr, Xp, axis):
         rl_names.append(nm), rl_parent.append(parent), rl_dof.append(dof)
         rl_Xr.append(Xr), rl_Xp.append(Xp), rl_axis.append(axis)
-        rl_mass.append(0.0), rl_mcom.append(np.zeros(3))
+        rl_mass.append(0.0), rl_mcom.append(np.zeros(3)), rl_IO.append(np.zeros((3, 3)))
         return len(rl_names) - 1
 
     # BFS so that parent index < child index
@@ -175,7 +197,10 @@ def reduce_model(name: str, base_link: str, links: Sequence[LinkDesc], joints: S
         lname, ridx, R_l, p_l = queue.pop(0)  # pose of this full link inside reduced link ridx
         ld = link_by_name[lname]
         rl_mass[ridx] += ld.mass
-        rl_mcom[ridx] = rl_mcom[ridx] + ld.mass * (R_l @ np.asarray(ld.com) + p_l)
+        c_l = R_l @ np.asarray(ld.com) + p_l
+        rl_mcom[ridx] = rl_mcom[ridx] + ld.mass * c_l
+        I_l = default_inertia(ld.mass, ld.com) if ld.inertia is None else np.asarray(ld.inertia, dtype=float)
+        rl_IO[ridx] = rl_IO[ridx] + R_l @ I_l @ R_l.T + ld.mass * (c_l @ c_l * np.eye(3) - np.outer(c_l, c_l))
         # every full link is also exposed as a frame (iDynTree: link frames are frames)
         fr_out.append((lname, ridx, R_l.copy(), p_l.copy()))
         for f in frames_by_link.get(lname, []):
@@ -195,6 +220,7 @@ def reduce_model(name: str, base_link: str, links: Sequence[LinkDesc], joints: S
     assert len(rl_names) == n + 1, "joints_list must only name joints reachable from the base"
     mass = np.array(rl_mass)
     com = np.array([mc / m if m > 0 else np.zeros(3) for mc, m in zip(rl_mcom, rl_mass)])
+    inertia = np.array([IO - m * (c @ c * np.eye(3) - np.outer(c, c)) for IO, m, c in zip(rl_IO, rl_mass, com)])
     model = KinematicModel(
         name=name, joint_names=list(joints_list), link_names=rl_names,
         parent=np.array(rl_parent, dtype=np.int32), dof=np.array(rl_dof, dtype=np.int32),
@@ -203,7 +229,7 @@ def reduce_model(name: str, base_link: str, links: Sequence[LinkDesc], joints: S
         Fr=np.array([f[2] for f in fr_out]), Fp=np.array([f[3] for f in fr_out]),
         q_lower=np.array([joint_by_name[j].lower for j in joints_list]),
         q_upper=np.array([joint_by_name[j].upper for j in joints_list]),
-        q_nominal=np.array([joint_by_name[j].nominal for j in joints_list]))
+        q_nominal=np.array([joint_by_name[j].nominal for j in joints_list]), inertia=inertia)
     model.validate()
     return model
 
@@ -353,10 +379,15 @@ def model_from_text(text: str) -> KinematicModel:
         v = [float(x) for x in l[3:]]
         Fr.append(np.array(v[0:9]).reshape(3, 3)); Fp.append(v[9:12])
     lim = {l[1]: [float(x) for x in l[2:5]] for l in limit_rows}
+    inertia = np.zeros((n + 1, 3, 3))
+    for l in lines:
+        if l[0] == "inertia":
+            k, v = int(l[2]), [float(x) for x in l[3:9]]
+            inertia[k] = [[v[0], v[1], v[2]], [v[1], v[3], v[4]], [v[2], v[4], v[5]]]
     m = KinematicModel(name, joint_names, lnames, np.array(parent, dtype=np.int32), np.array(dof, dtype=np.int32),
                        np.array(Xr), np.array(Xp, dtype=float), np.array(axis, dtype=float), np.array(mass), np.array(com, dtype=float),
                        fn, np.array(fl, dtype=np.int32), np.array(Fr), np.array(Fp, dtype=float),
                        np.array([lim[j][0] for j in joint_names]), np.array([lim[j][1] for j in joint_names]),
-                       np.array([lim[j][2] for j in joint_names]))
+                       np.array([lim[j][2] for j in joint_names]), inertia)
     m.validate()
     return m

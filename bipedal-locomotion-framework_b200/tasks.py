@@ -7,6 +7,7 @@ parameter-handler keys:
 * ``CoMTask``  -- ``kp_linear, mask``                               (src/IK/src/CoMTask.cpp:107-162)
 * ``SO3Task``  -- ``frame_name, kp_angular``                        (src/IK/src/SO3Task.cpp:67-151)
 * ``R3Task``   -- ``frame_name, kp_linear, mask``                   (src/IK/src/R3Task.cpp:60-176)
+* ``AngularMomentumTask`` -- ``mask``                               (src/IK/src/AngularMomentumTask.cpp:67-135)
 * ``JointTrackingTask`` -- ``kp``                                   (src/IK/src/JointTrackingTask.cpp:90-112)
 * ``JointLimitsTask``   -- ``klim, sampling_time, use_model_limits, upper_limits, lower_limits``
                                                                     (src/IK/src/JointLimitsTask.cpp:136-198)
@@ -34,10 +35,11 @@ TASK_JOINT_VELOCITY_LIMITS = 5
 TASK_R3 = 6
 TASK_DISTANCE = 7
 TASK_GRAVITY = 8
+TASK_ANGULAR_MOMENTUM = 9
 
 TYPE_NAMES = {TASK_SE3: "SE3Task", TASK_COM: "CoMTask", TASK_SO3: "SO3Task", TASK_JOINT_TRACKING: "JointTrackingTask",
               TASK_JOINT_LIMITS: "JointLimitsTask", TASK_JOINT_VELOCITY_LIMITS: "JointVelocityLimitsTask", TASK_R3: "R3Task",
-              TASK_DISTANCE: "DistanceTask", TASK_GRAVITY: "GravityTask"}
+              TASK_DISTANCE: "DistanceTask", TASK_GRAVITY: "GravityTask", TASK_ANGULAR_MOMENTUM: "AngularMomentumTask"}
 
 
 def _vec3(v) -> np.ndarray:
@@ -70,11 +72,11 @@ class TaskSpec:
 
     def rows(self, n: int) -> int:
         nm = int(sum(bool(m) for m in self.mask))
-        return {TASK_SE3: nm + 3, TASK_COM: nm, TASK_R3: nm, TASK_SO3: 3, TASK_DISTANCE: 1, TASK_GRAVITY: 2, TASK_JOINT_TRACKING: n,
+        return {TASK_SE3: nm + 3, TASK_COM: nm, TASK_R3: nm, TASK_SO3: 3, TASK_DISTANCE: 1, TASK_GRAVITY: 2, TASK_ANGULAR_MOMENTUM: nm, TASK_JOINT_TRACKING: n,
                 TASK_JOINT_LIMITS: 2 * n, TASK_JOINT_VELOCITY_LIMITS: 2 * n}[self.type]
 
     def setpoint_len(self, n: int) -> int:
-        return {TASK_SE3: 13, TASK_COM: 6, TASK_SO3: 7, TASK_R3: 6, TASK_DISTANCE: 1, TASK_GRAVITY: 6, TASK_JOINT_TRACKING: 2 * n,
+        return {TASK_SE3: 13, TASK_COM: 6, TASK_SO3: 7, TASK_R3: 6, TASK_DISTANCE: 1, TASK_GRAVITY: 6, TASK_ANGULAR_MOMENTUM: 3, TASK_JOINT_TRACKING: 2 * n,
                 TASK_JOINT_LIMITS: 0, TASK_JOINT_VELOCITY_LIMITS: 0}[self.type]
 
     @property
@@ -120,6 +122,14 @@ def distance_task(model: KinematicModel, name: str, target_frame_name: str, kp: 
 def gravity_task(model: KinematicModel, name: str, target_frame_name: str, kp: float, priority=1, weight=None) -> TaskSpec:
     """keys: kp, target_frame_name (src/IK/src/GravityTask.cpp:76-147)."""
     t = TaskSpec(name, TASK_GRAVITY, priority, model.frame_index(target_frame_name), (True, True, True), True, _vec3(kp))
+    t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
+    return t
+
+
+def angular_momentum_task(model: KinematicModel, name: str, priority=1, weight=None, mask=(True, True, True)) -> TaskSpec:
+    """key: mask (optional); A = rows 3..5 of the centroidal momentum matrix, b = desired angular momentum
+    (src/IK/src/AngularMomentumTask.cpp:67-185).  No gain: the set-point is the momentum itself."""
+    t = TaskSpec(name, TASK_ANGULAR_MOMENTUM, priority, -1, tuple(mask), True)
     t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
     return t
 

@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define BLFIK_VERSION 1
+#define BLFIK_VERSION 2
 #define BLFIK_INFTY 1e30 /* OsqpEigen::INFTY, QPInverseKinematics.cpp:481-482 */
 
 typedef enum {
@@ -60,7 +60,8 @@ typedef enum {
     BLFIK_TASK_JOINT_VELOCITY_LIMITS = 5, /* src/IK/src/JointVelocityLimitsTask.cpp */
     BLFIK_TASK_R3 = 6,                    /* src/IK/src/R3Task.cpp                  */
     BLFIK_TASK_DISTANCE = 7,              /* src/IK/src/DistanceTask.cpp            */
-    BLFIK_TASK_GRAVITY = 8                /* src/IK/src/GravityTask.cpp             */
+    BLFIK_TASK_GRAVITY = 8,               /* src/IK/src/GravityTask.cpp             */
+    BLFIK_TASK_ANGULAR_MOMENTUM = 9       /* src/IK/src/AngularMomentumTask.cpp     */
 } blfik_task_type;
 
 /* where a caller-provided batch buffer lives */
@@ -95,6 +96,8 @@ typedef struct {
     const int32_t* frame_link; /* [n_frames]                                            */
     const double* frame_rot;   /* [n_frames][9] link <- frame                           */
     const double* frame_pos;   /* [n_frames][3]                                         */
+    const double* inertia;     /* [n_dofs+1][6] Ixx Ixy Ixz Iyy Iyz Izz about the link CoM, link frame; NULL = point masses.
+                                  Only the AngularMomentumTask reads it (centroidal momentum matrix).             */
 } blfik_model_desc;
 
 /* One task; fields mirror the reference's parameter-handler keys. */
@@ -161,7 +164,8 @@ int blfik_get_state(blfik_problem* problem, double* base_pos, double* base_quat,
  *   SE3: 13 = p_d(3) q_d(4) v_ff(3) w_ff(3)     CoM / R3: 6 = p_d(3) v_ff(3)
  *   SO3:  7 = q_d(4) w_ff(3)                    JointTracking: 2n = s_d(n) sdot_d(n)
  *   Distance: 1 = desired distance (DistanceTask::setDesiredDistance; gain kp_linear[0], frame = target_frame_name)
- *   Gravity:  6 = desired gravity direction in the target frame (3) + feed-forward (3)  (GravityTask::setSetPoint; kp_linear[0]) */
+ *   Gravity:  6 = desired gravity direction in the target frame (3) + feed-forward (3)  (GravityTask::setSetPoint; kp_linear[0])
+ *   AngularMomentum: 3 = desired centroidal angular momentum (AngularMomentumTask::setSetPoint; rows selected by mask) */
 int blfik_set_setpoint(blfik_problem* problem, int32_t task, const double* data, int32_t mem);
 int32_t blfik_setpoint_len(const blfik_problem* problem, int32_t task);
 

@@ -222,6 +222,60 @@ void orc_com(const orc_model* m, const double* link_R, const double* link_p, dou
     free(cw);
 }
 
+/* Angular part of the centroidal momentum matrix (iDynTree::KinDynComputations::getCentroidalTotalMomentumJacobian rows
+ * 3..5 in MIXED representation; used by AngularMomentumTask.cpp:160-185), accumulated link by link from each link's own
+ * Jacobian at its centre of mass:  L = sum_k [ I_k^W J_w,k + m_k S(c_k - c) J_v,k ] nu.  (The GPU kernel evaluates the same
+ * matrix column by column over the links distal to each DoF.)                                                             */
+void orc_angular_momentum_matrix(const orc_model* m, const double* link_R, const double* link_p, double* A)
+{
+    const int nv = 6 + m->n, nl = m->n + 1;
+    double com[3];
+    orc_com(m, link_R, link_p, com, NULL);
+    memset(A, 0, sizeof(double) * 3 * nv);
+    double* Jk = (double*)malloc(sizeof(double) * 6 * nv);
+    for (int k = 0; k < nl; k++) {
+        /* Jacobian of link k at its CoM */
+        double off[3], ck[3];
+        mat3_vec(link_R + 9 * k, m->com + 3 * k, off);
+        for (int c = 0; c < 3; c++) ck[c] = link_p[3 * k + c] + off[c];
+        memset(Jk, 0, sizeof(double) * 6 * nv);
+        const double r[3] = {ck[0] - link_p[0], ck[1] - link_p[1], ck[2] - link_p[2]};
+        for (int c = 0; c < 3; c++) Jk[c * nv + c] = 1.0, Jk[(3 + c) * nv + 3 + c] = 1.0;
+        Jk[0 * nv + 4] = r[2], Jk[0 * nv + 5] = -r[1];
+        Jk[1 * nv + 3] = -r[2], Jk[1 * nv + 5] = r[0];
+        Jk[2 * nv + 3] = r[1], Jk[2 * nv + 4] = -r[0];
+        for (int a = k; a > 0; a = m->parent[a]) {
+            const int j = 6 + m->dof[a];
+            double aw[3], d[3], lin[3];
+            mat3_vec(link_R + 9 * a, m->axis + 3 * a, aw);
+            for (int c = 0; c < 3; c++) d[c] = ck[c] - link_p[3 * a + c];
+            cross3(aw, d, lin);
+            for (int c = 0; c < 3; c++) Jk[c * nv + j] = lin[c], Jk[(3 + c) * nv + j] = aw[c];
+        }
+        /* world inertia about the link CoM */
+        double Iw[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        if (m->inertia) {
+            const double* I6 = m->inertia + 6 * k;
+            const double Il[9] = {I6[0], I6[1], I6[2], I6[1], I6[3], I6[4], I6[2], I6[4], I6[5]};
+            double T[9], Rt[9];
+            const double* R = link_R + 9 * k;
+            for (int a = 0; a < 3; a++)
+                for (int b = 0; b < 3; b++) Rt[3 * a + b] = R[3 * b + a];
+            mat3_mul(R, Il, T);
+            mat3_mul(T, Rt, Iw);
+        }
+        const double d[3] = {ck[0] - com[0], ck[1] - com[1], ck[2] - com[2]};
+        const double mk = m->mass[k];
+        for (int c = 0; c < nv; c++) {
+            const double v[3] = {Jk[c], Jk[nv + c], Jk[2 * nv + c]}, w[3] = {Jk[3 * nv + c], Jk[4 * nv + c], Jk[5 * nv + c]};
+            double t[3];
+            cross3(d, v, t);
+            for (int i = 0; i < 3; i++) A[i * nv + c] += Iw[3 * i] * w[0] + Iw[3 * i + 1] * w[1] + Iw[3 * i + 2] * w[2] + mk * t[i];
+        }
+    }
+    free(Jk);
+}
+
 /* ------------------------------------------------------------------------- */
 /* K2: tasks                                                                  */
 /* ------------------------------------------------------------------------- */
@@ -235,6 +289,7 @@ int orc_setpoint_len(int type, int n)
     case ORC_TASK_JOINT_TRACKING: return 2 * n; /* s_d(n) sdot_d(n)             */
     case ORC_TASK_DISTANCE: return 1;        /* desired distance                 */
     case ORC_TASK_GRAVITY: return 6;         /* z_des in the body (3) ff (3)     */
+    case ORC_TASK_ANGULAR_MOMENTUM: return 3; /* desired centroidal angular momentum */
     default: return 0;
     }
 }
@@ -250,6 +305,7 @@ int orc_task_rows(const orc_task* t, int n)
     case ORC_TASK_SO3: return 3;
     case ORC_TASK_DISTANCE: return 1;
     case ORC_TASK_GRAVITY: return 2;
+    case ORC_TASK_ANGULAR_MOMENTUM: return mask_count(t->mask);
     case ORC_TASK_JOINT_TRACKING: return n;
     case ORC_TASK_JOINT_LIMITS: return 2 * n;
     case ORC_TASK_JOINT_VELOCITY_LIMITS: return 2 * n;
@@ -384,6 +440,19 @@ int orc_task_update(const orc_model* m, const orc_task* t, const double* link_R,
         memcpy(A + nv, J + 4 * nv, sizeof(double) * nv);
         b[0] = ff[0] + t->kp_lin[0] * z[1];
         b[1] = ff[1] - t->kp_lin[0] * z[0];
+        break;
+    }
+    case ORC_TASK_ANGULAR_MOMENTUM: { /* AngularMomentumTask.cpp:137-185: A = masked rows 3..5 of the CMM, b = desired momentum (:187-210) */
+        double Am[3 * 64];
+        if (nv > 64) return -1;
+        orc_angular_momentum_matrix(m, link_R, link_p, Am);
+        int idx = 0;
+        for (int c = 0; c < 3; c++) {
+            if (!t->mask[c]) continue;
+            b[idx] = sp[c];
+            memcpy(A + idx * nv, Am + c * nv, sizeof(double) * nv);
+            idx++;
+        }
         break;
     }
     case ORC_TASK_JOINT_TRACKING: /* JointTrackingTask.cpp:65-67 (A=[0 I]), :151 (b) */

@@ -52,7 +52,8 @@ enum {
     ORC_TASK_JOINT_VELOCITY_LIMITS = 5,
     ORC_TASK_R3 = 6,
     ORC_TASK_DISTANCE = 7,
-    ORC_TASK_GRAVITY = 8
+    ORC_TASK_GRAVITY = 8,
+    ORC_TASK_ANGULAR_MOMENTUM = 9
 };
 
 /* Kinematic tree, link 0 = floating base, parent[k] < k.  Link k (k>=1) is the
@@ -71,6 +72,7 @@ typedef struct {
     const int* frame_link; /* [nf]                                              */
     const double* Fr;      /* [nf][9] link <- frame rotation                    */
     const double* Fp;      /* [nf][3]                                           */
+    const double* inertia; /* [n+1][6] Ixx Ixy Ixz Iyy Iyz Izz about the link CoM, link frame; NULL = point masses */
 } orc_model;
 
 typedef struct {
@@ -134,6 +136,9 @@ void orc_frame_jacobian(const orc_model* m, const double* link_R, const double* 
                         double* J /* 6 x (6+n) row-major */);
 void orc_com(const orc_model* m, const double* link_R, const double* link_p, double com[3],
              double* Jcom /* 3 x (6+n) row-major, may be NULL */);
+
+/* angular rows (3 x nv) of the centroidal momentum matrix, MIXED representation: L = sum_k I_k^W w_k + m_k (c_k - c) x cdot_k */
+void orc_angular_momentum_matrix(const orc_model* m, const double* link_R, const double* link_p, double* A);
 
 /* ---- tasks + assembly ---- */
 /* A is rows x nv row-major, b is rows.  Returns rows, or -1 on error.          */

@@ -24,7 +24,8 @@ c_int_p = C.POINTER(C.c_int)
 class OrcModel(C.Structure):
     _fields_ = [("n", C.c_int), ("nf", C.c_int), ("parent", c_int_p), ("dof", c_int_p),
                 ("Xr", c_double_p), ("Xp", c_double_p), ("axis", c_double_p), ("mass", c_double_p),
-                ("com", c_double_p), ("frame_link", c_int_p), ("Fr", c_double_p), ("Fp", c_double_p)]
+                ("com", c_double_p), ("frame_link", c_int_p), ("Fr", c_double_p), ("Fp", c_double_p),
+                ("inertia", c_double_p)]
 
 
 class OrcTask(C.Structure):
@@ -85,10 +86,12 @@ class Oracle:
             Xr=np.ascontiguousarray(model.Xr, dtype=np.float64), Xp=np.ascontiguousarray(model.Xp, dtype=np.float64),
             axis=np.ascontiguousarray(model.axis, dtype=np.float64), mass=np.ascontiguousarray(model.mass, dtype=np.float64),
             com=np.ascontiguousarray(model.com, dtype=np.float64), fl=np.ascontiguousarray(model.frame_link, dtype=np.int32),
-            Fr=np.ascontiguousarray(model.Fr, dtype=np.float64), Fp=np.ascontiguousarray(model.Fp, dtype=np.float64))
+            Fr=np.ascontiguousarray(model.Fr, dtype=np.float64), Fp=np.ascontiguousarray(model.Fp, dtype=np.float64),
+            I6=np.ascontiguousarray(np.stack([model.inertia[:, 0, 0], model.inertia[:, 0, 1], model.inertia[:, 0, 2], model.inertia[:, 1, 1],
+                                              model.inertia[:, 1, 2], model.inertia[:, 2, 2]], axis=1), dtype=np.float64))
         k = self._keep
         self.cm = OrcModel(model.n, len(model.frame_names), _ip(k["parent"]), _ip(k["dof"]), _dp(k["Xr"]), _dp(k["Xp"]),
-                           _dp(k["axis"]), _dp(k["mass"]), _dp(k["com"]), _ip(k["fl"]), _dp(k["Fr"]), _dp(k["Fp"]))
+                           _dp(k["axis"]), _dp(k["mass"]), _dp(k["com"]), _ip(k["fl"]), _dp(k["Fr"]), _dp(k["Fp"]), _dp(k["I6"]))
         self.set_tasks(tasks)
 
     # ---- tasks
@@ -139,6 +142,11 @@ class Oracle:
         c = np.empty(3); J = np.empty((3, self.nv))
         self.L.orc_com(C.byref(self.cm), _dp(R), _dp(P), _dp(c), _dp(J))
         return c, J
+
+    def angular_momentum_matrix(self, R, P):
+        A = np.empty((3, self.nv))
+        self.L.orc_angular_momentum_matrix(C.byref(self.cm), _dp(R), _dp(P), _dp(A))
+        return A
 
     # ---- tasks / assembly
     def task_update(self, ti: int, R, P, s, setpoint):

@@ -754,3 +754,48 @@ def test_problems_of_different_sizes_coexist():
         big.tick(1, 0.01)
         assert np.array_equal(big.get_output(), ref)
         big.close(), small.close(), tree.close()
+
+
+@pytest.mark.parametrize("hard", [True, False])
+def test_angular_momentum_task_vs_oracle(hard):
+    """AngularMomentumTask.cpp:137-210 in the tick (generic kernel: the centroidal momentum rows are evaluated column by
+    column over the links distal to each DoF, the oracle accumulates them link by link): rows within 1e-12, nu within 1e-5,
+    and the returned velocity carries the requested angular momentum."""
+    m = M.ergocub23()
+    n, N = m.n, 64
+    prio = 0 if hard else 1
+    tasks = [T.se3_task(m, "lf", "l_sole", 5.0, 5.0), T.se3_task(m, "rf", "r_sole", 5.0, 5.0), T.com_task(m, "com", 5.0),
+             T.angular_momentum_task(m, "L", priority=prio, weight=None if hard else [4.0, 5.0], mask=(True, True, True) if hard else (True, False, True)),
+             T.joint_tracking_task(m, "reg", np.full(n, 2.0), priority=1, weight=np.full(n, 0.5))]
+    inp = W.synth_inputs(W.config(3), N, 7)
+    p0, q0, s0 = inp.base_pos, inp.base_quat, inp.s
+    rng = np.random.default_rng(8)
+    sps = [inp.setpoints[2], inp.setpoints[1], inp.setpoints[0], rng.normal(0, 0.05, (N, 3)), inp.setpoints[6]]
+    model, prob = make(m, tasks, N)
+    assert prob.kernel_path == 1                       # the register-resident kernel does not carry this task
+    prob.set_state(p0, q0, s0)
+    for t, sp in enumerate(sps):
+        prob.set_setpoint(t, sp)
+    prob.debug_enable(True)
+    prob.tick(1, 0.01)
+    H, g = prob.debug_get(capi.DEBUG_H), prob.debug_get(capi.DEBUG_G)
+    Ce, be = prob.debug_get(capi.DEBUG_CEQ), prob.debug_get(capi.DEBUG_BEQ)
+    nu = prob.get_output()
+    st, _ = prob.get_status()
+    o = Oracle(m, tasks)
+    me = prob.me
+    assert me == (18 if hard else 15)
+    for i in range(0, N, 5):
+        Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [sp[i] for sp in sps])
+        assert np.abs(H[i] - Ho).max() <= 1e-12 * (1 + np.abs(Ho).max())
+        assert np.abs(g[i] - go).max() <= 1e-12 * (1 + np.abs(go).max())
+        assert np.abs(Ce[i] - Co[:me]).max() <= TOL_KIN * (1 + np.abs(Co).max())
+        assert np.abs(be[i] - u[:me]).max() <= 1e-12 * (1 + np.abs(u[:me]).max())
+    nur, str_, _ = o.tick_batch(p0.copy(), q0.copy(), s0.copy(), sps)
+    ok = (st == 0) & (str_ == 0)
+    assert ok.mean() > 0.95 and np.abs(nu - nur)[ok].max() <= TOL_NU
+    if hard:
+        for i in np.flatnonzero(ok)[:8]:
+            R, P = o.fk(p0[i], q0[i], s0[i])
+            assert np.abs(o.angular_momentum_matrix(R, P) @ nu[i] - sps[3][i]).max() < 1e-8
+    prob.close()

@@ -288,3 +288,61 @@ def test_distance_gravity_closed_loop(hard):
     Rg, _ = o.frame_pose(R, P, sc.frame_gravity)
     assert abs(np.linalg.norm(pd) - sc.distance_des) <= 2e-2 * sc.distance_des
     assert np.abs(Rg[2] - sc.gravity_des).max() < 2e-2
+
+
+def _angular_momentum_numeric(o, m, p, q, s, nu, eps=1e-6):
+    """L about the CoM from first principles: link angular velocities and link-CoM velocities by central differences of the
+    forward kinematics along nu, L = sum_k R_k I_k R_k' w_k + m_k (c_k - c) x cdot_k."""
+    from helpers import perturb_state
+
+    def link_state(pp, qq, ss):
+        R, P = o.fk(pp, qq, ss)
+        R = np.asarray(R).reshape(-1, 3, 3); P = np.asarray(P).reshape(-1, 3)
+        return R, P + np.einsum('kij,kj->ki', R, m.com)
+    Rp, cp = link_state(*perturb_state(p, q, s, nu, eps))
+    Rm, cm = link_state(*perturb_state(p, q, s, nu, -eps))
+    R0, c0 = link_state(p, q, s)
+    com = (m.mass[:, None] * c0).sum(0) / m.mass.sum()
+    L = np.zeros(3)
+    for k in range(m.n + 1):
+        w = rot_log(Rp[k] @ Rm[k].T) / (2 * eps)          # world-frame angular velocity of link k
+        cdot = (cp[k] - cm[k]) / (2 * eps)
+        L += R0[k] @ m.inertia[k] @ R0[k].T @ w + m.mass[k] * np.cross(c0[k] - com, cdot)
+    return L
+
+
+def test_angular_momentum_task(ergo):
+    """AngularMomentumTask.cpp:137-210: A = rows 3..5 of the centroidal momentum matrix (masked), b = the desired momentum.
+    The matrix is checked against the momentum computed from first principles, its base-linear block is zero (momentum about
+    the CoM does not see a pure translation), and it is invariant under lumping (a model reduced to fewer joints and evaluated
+    with the removed joints at zero carries the same momentum for the same motion)."""
+    m = ergo
+    rng = np.random.default_rng(21)
+    tasks = [T.angular_momentum_task(m, "L", priority=0), T.angular_momentum_task(m, "Lxz", priority=1, weight=[2.0, 3.0], mask=(True, False, True))]
+    o = Oracle(m, tasks)
+    assert np.linalg.eigvalsh(m.inertia).min() > 0
+    p, q, s = random_state(m, rng)
+    R, P = o.fk(p, q, s)
+    A = o.angular_momentum_matrix(R, P)
+    assert np.abs(A[:, :3]).max() < 1e-13
+    for _ in range(3):
+        nu = rng.normal(size=6 + m.n)
+        assert np.abs(A @ nu - _angular_momentum_numeric(o, m, p, q, s, nu)).max() < 1e-6
+    sp = rng.normal(size=3)
+    A0, b0 = o.task_update(0, R, P, s, sp)
+    assert np.array_equal(A0, A) and np.array_equal(b0, sp)
+    A1, b1 = o.task_update(1, R, P, s, sp)
+    assert np.array_equal(A1, A[[0, 2]]) and np.array_equal(b1, sp[[0, 2]])
+    # lumping invariance: the 32-joint and the 26-joint iCub are the same robot when the six wrist joints rest at zero
+    m32, m26 = M.icub32(), M.icub26()
+    o32, o26 = Oracle(m32, [T.angular_momentum_task(m32, "L", priority=0)]), Oracle(m26, [T.angular_momentum_task(m26, "L", priority=0)])
+    s26 = rng.uniform(-0.4, 0.4, m26.n)
+    s32, nu26 = np.zeros(m32.n), rng.normal(size=6 + m26.n)
+    nu32 = np.zeros(6 + m32.n)
+    nu32[:6] = nu26[:6]
+    for j26, name in enumerate(m26.joint_names):
+        j32 = m32.joint_names.index(name)
+        s32[j32], nu32[6 + j32] = s26[j26], nu26[6 + j26]
+    R26, P26 = o26.fk(p, q, s26)
+    R32, P32 = o32.fk(p, q, s32)
+    assert np.abs(o26.angular_momentum_matrix(R26, P26) @ nu26 - o32.angular_momentum_matrix(R32, P32) @ nu32).max() < 1e-12

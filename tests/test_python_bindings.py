@@ -148,6 +148,10 @@ def test_task_initialisation_rules():
     assert grav.set_set_point(desired_gravity_direction=[0.0, 3.0, 4.0], feedforward_velocity=[0.1, 0.2, 0.3])
     assert np.allclose(grav._sp[0], [0.0, 0.6, 0.8, 0.1, 0.2, 0.3])
 
+    am = blf.ik.AngularMomentumTask()
+    assert am.set_kin_dyn(kindyn) and am.initialize(param_handler=_handler())
+    assert am.set_variables_handler(variables_handler=var) and am.set_set_point([0., 0., 0.]) and am.size() == 3
+
     state = blf.ik.IntegrationBasedIKState()
     state.joint_velocity = [0.1] * n
     assert state.joint_velocity == pytest.approx([0.1] * n)
