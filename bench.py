@@ -193,9 +193,9 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
 
     def e2e_step():
         # the reference-facing call with HOST buffers: one packed record per robot (state + set-points) in, nu + status out.
-        # --chunks k >= 1: the copy engine brings the records in k pieces while the kernels of the previous pieces run (on
-        # alternating streams) and write nu / status straight into the pinned host buffers; --chunks 0: the kernel also
-        # reads the records over PCIe itself (blfik_tick_packed zero-copy mode)
+        # --chunks k >= 1: one persistent launch starts at once and consumes the records while the copy engine streams them
+        # in (it polls an arrival word that the copy stream raises after every piece) and writes nu / status straight into
+        # the pinned host buffers; --chunks 0: the kernel also reads the records over PCIe itself (zero-copy mode)
         prob.tick_packed(h_packed, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False, nchunks=args.chunks)
 
     def barrier():
@@ -276,7 +276,9 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
                        "solver": prob_settings, "l2": "256 MiB write between steps (untimed) flushes the 126 MB L2",
                        "unsolved_instances": unsolved,
                        "host_tick": ("blfik_tick_packed, zero-copy (kernel reads pinned host records over PCIe)" if args.chunks <= 0 else
-                                     f"blfik_tick_packed, {args.chunks} chunks: copy-engine H2D overlapped with the chunk kernels, results written to pinned host memory by the kernels")},
+                                     "blfik_tick_packed, streaming input: one persistent launch consumes the packed records while the copy "
+                                     "engine delivers them in 16 pieces (arrival word raised by stream memory operations), results written "
+                                     "to pinned host memory by the kernel")},
             "e2e": {"value": ticks_total / (ms_e2e * 1e-3), "unit": "ticks/s",
                     "h2d_bytes_per_step": int(8 * n_local * (7 + n + sp_doubles)),
                     "d2h_bytes_per_step": int(n_local * (8 * nv + 4))},
@@ -315,7 +317,7 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--instances", type=int, default=PER_GPU_INSTANCES, help="instances per GPU")
     ap.add_argument("--chunks", type=int, default=5,
-                    help="host-buffer (e2e) tick: k >= 1 = k pipeline chunks (H2D by the copy engine, chunk kernels on alternating streams, results written to the pinned host buffers by the kernels); 0 = zero-copy, the kernel reads the records over PCIe itself")
+                    help="host-buffer (e2e) tick: k >= 1 = pipelined (pinned buffers: one persistent launch that consumes the records while the copy engine streams them in; otherwise k chunk launches); 0 = zero-copy, the kernel reads the records over PCIe itself")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

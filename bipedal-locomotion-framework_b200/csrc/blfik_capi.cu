@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <new>
 #include <string>
+#include <cstdint>
 #include <vector>
 
 using namespace blfik;
@@ -192,7 +193,8 @@ struct HostTask {
 };
 
 constexpr int kMaxChunks = 16;
-constexpr int kCounterSlots = kMaxChunks;   // work counters of the register-resident kernel, one per launch that may be in flight
+constexpr int kCounterSlots = kMaxChunks;
+constexpr int kMaxPieces = 64;      // pieces of the streaming-input mode   // work counters of the register-resident kernel, one per launch that may be in flight
 
 struct blfik_problem {
     const blfik_model* model = nullptr;
@@ -209,6 +211,9 @@ struct blfik_problem {
     double *base_pos = nullptr, *base_quat = nullptr, *s = nullptr, *nu = nullptr, *wx = nullptr, *wz = nullptr, *wy = nullptr;
     int *status = nullptr, *iters = nullptr;
     int* work_counter = nullptr;   // dynamic hand-out of robots in the register-resident kernel
+    bool streaming_launch = false; // set around the one launch of the streaming-input mode
+    int* d_arrived = nullptr;      // streaming-input mode of blfik_tick_packed: robots whose record is on the device; [1] = abort word
+    int* h_stream_ctl = nullptr;   // pinned + mapped: [0..kMaxPieces) cumulative robot counts (sources of the flag copies), [kMaxPieces] = abort
     unsigned long long* d_count = nullptr;
     bool state_set = false, ticked = false;
     DebugOut dbg = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -701,6 +706,7 @@ extern "C" void blfik_problem_destroy(blfik_problem* p)
         for (int k = 0; k < 4; k++)
             if (p->chunk_stream[k]) cudaStreamSynchronize(p->chunk_stream[k]), cudaStreamDestroy(p->chunk_stream[k]);
     }
+    if (p->h_stream_ctl) cudaFreeHost(p->h_stream_ctl);
     if (p->own_stream && p->stream) cudaStreamDestroy(p->stream);
     delete p;
 }
@@ -901,7 +907,8 @@ extern "C" int blfik_debug_get(blfik_problem* p, int32_t what, double* out, int3
 
 // one launch of the tick over robots [first, first + count) on `stream`
 static int launch_tick_range(blfik_problem* p, long long first, long long count, int32_t nticks, double dt, uint32_t flags, cudaStream_t stream,
-                             const double* packed = nullptr, double* nu_host = nullptr, int* status_host = nullptr, int counter_slot = 0)
+                             const double* packed = nullptr, double* nu_host = nullptr, int* status_host = nullptr, int counter_slot = 0,
+                             bool counter_zeroed = false)
 {
     TickParams P;
     P.m = p->dm, P.tasks = p->d_tasks, P.ntasks = (int)p->tasks.size(), P.first = first, P.N = first + count;   // robots [first, N)
@@ -927,7 +934,14 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         FP.work_counter = nullptr;
         if (dynamic_env && p->work_counter) {
             FP.work_counter = p->work_counter + counter_slot;   // launches that may overlap use different slots
-            CU(cudaMemsetAsync(FP.work_counter, 0, sizeof(int), stream));
+            if (!counter_zeroed) CU(cudaMemsetAsync(FP.work_counter, 0, sizeof(int), stream));
+        }
+        FP.arrived = nullptr, FP.abort_flag = nullptr, FP.abort_host = nullptr, FP.arrive_timeout = 0;
+        if (p->streaming_launch && FP.work_counter) {
+            FP.arrived = p->d_arrived, FP.abort_flag = p->d_arrived + 1;
+            CU(cudaHostGetDevicePointer((void**)&FP.abort_host, p->h_stream_ctl + kMaxPieces, 0));
+            static const long long timeout_env = [] { const char* e = getenv("BLFIK_ARRIVE_TIMEOUT"); return e ? atoll(e) : 4000000000LL; }();
+            FP.arrive_timeout = timeout_env;    // ~2 s of SM clocks: a copy that has not arrived by then never will
         }
         p->fast_kernel<<<(int)(want < p->fast_grid ? want : p->fast_grid), p->fast_wpb * 32, p->fast_smem, stream>>>(FP);
     } else {
@@ -1081,10 +1095,91 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
         }
         CU(cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming));
     }
+    if (p->work_counter) CU(cudaMemsetAsync(p->work_counter, 0, kCounterSlots * sizeof(int), p->stream));   // one reset for all chunk launches
     CU(cudaEventRecord(p->ev_start, p->stream));
     CU(cudaStreamWaitEvent(p->h2d_stream, p->ev_start, 0));
     CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_start, 0));
     const int nv = p->nv, R = p->packed_len;
+    // ---- streaming input: ONE persistent launch that starts at once and consumes the records as the copy engine delivers
+    // them (chunk launches lose a tail each: 5 launches of 13k robots take 2.3 ms of kernel time against 1.36 ms for one
+    // launch of 65k).  Needs the register-resident kernel with dynamic hand-out, page-locked records (a pure DMA on the
+    // copy stream) and mapped page-locked outputs.
+    static const int streaming_env = [] { const char* e = getenv("BLFIK_STREAMING"); return e ? atoi(e) : 1; }();
+    if (streaming_env && p->fast_kernel && p->path == 0 && p->work_counter && p->N < 0x7fffff00LL) {
+        cudaPointerAttributes at;
+        double* nu_dev = nullptr;
+        int* st_dev = nullptr;
+        bool ok = cudaPointerGetAttributes(&at, records) == cudaSuccess && at.type == cudaMemoryTypeHost;
+        if (ok) ok = cudaPointerGetAttributes(&at, nu) == cudaSuccess && at.type == cudaMemoryTypeHost && (nu_dev = static_cast<double*>(at.devicePointer));
+        if (ok && status) ok = cudaPointerGetAttributes(&at, status) == cudaSuccess && at.type == cudaMemoryTypeHost && (st_dev = static_cast<int*>(at.devicePointer));
+        cudaGetLastError();
+        static const int dyn = [] { const char* e = getenv("BLFIK_DYNAMIC"); return e ? atoi(e) : 1; }();
+        if (ok && dyn) {
+            if (!p->h_stream_ctl) {
+                CU(cudaHostAlloc((void**)&p->h_stream_ctl, (kMaxPieces + 1) * sizeof(int), cudaHostAllocMapped));
+                if ((rc = dev_alloc(p, 2, &p->d_arrived))) return rc;
+            }
+            // the arrival word is raised by a stream memory operation when the driver offers one (looked up through the runtime,
+            // libcuda is not linked), else by a 4-byte copy
+            typedef int (*write_value_fn)(cudaStream_t, unsigned long long, unsigned int, unsigned int);
+            static const write_value_fn write_value = [] {
+                const char* e = getenv("BLFIK_WRITE_VALUE");
+                if (e && atoi(e) == 0) return (write_value_fn) nullptr;
+                void* fn = nullptr;
+                cudaDriverEntryPointQueryResult qr;
+                if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &fn, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) {
+                    cudaGetLastError();
+                    fn = nullptr;
+                }
+                return (write_value_fn)fn;
+            }();
+            // pieces of about 2,048 robots (2 MB for C3: 40 us on the link), the first ones smaller so that work starts early
+            static const int ramp_env = [] { const char* e = getenv("BLFIK_RAMP"); return e ? atoi(e) : 0; }();
+            static const int pieces_env = [] { const char* e = getenv("BLFIK_PIECES"); return e ? atoi(e) : 0; }();
+            int npieces = pieces_env > 0 ? pieces_env : 16;   // measured best on C3 (8: 40.7, 12: 41.9, 16: 42.1, 24: 40.8 M ticks/s)
+            if (npieces > kMaxPieces) npieces = kMaxPieces;
+            if ((long long)npieces > p->N) npieces = (int)p->N;
+            p->h_stream_ctl[kMaxPieces] = 0;
+            CU(cudaMemsetAsync(p->d_arrived, 0, 2 * sizeof(int), p->stream));
+            CU(cudaEventRecord(p->ev_start, p->stream));
+            CU(cudaStreamWaitEvent(p->h2d_stream, p->ev_start, 0));
+            p->streaming_launch = true;
+            rc = launch_tick_range(p, 0, p->N, 1, dt, flags, p->stream, p->d_packed, nu_dev, st_dev, 0);
+            p->streaming_launch = false;
+            if (rc) return rc;
+            long long a = 0;
+            for (int c = 0; c < npieces; c++) {
+                // piece c ends at N * smoothstep((c + 1) / npieces): small pieces first (work starts early) and last (little is
+                // left to compute when the final piece lands), large ones in between (fewer stream operations)
+                const double f = (double)(c + 1) / npieces;
+                long long b = c + 1 == npieces ? p->N : (long long)((double)p->N * (ramp_env ? f * sqrt(f) : f * f * (3.0 - 2.0 * f)));
+                // A piece ends where a record starts on a 128-byte line (every 16 robots whatever the record length): the
+                // kernel never reads a line that a later piece still has to fill, so no stale copy of it can sit in an L1.
+                b = (b + 15) & ~15LL;
+                if (b <= a) b = a + 16;
+                if (b > p->N) b = p->N;
+                CU(cudaMemcpyAsync(p->d_packed + (size_t)R * a, records + (size_t)R * a, (size_t)(b - a) * R * sizeof(double), cudaMemcpyHostToDevice, p->h2d_stream));
+                p->h_stream_ctl[c] = (int)b;
+                static const int stall_env = [] { const char* e = getenv("BLFIK_TEST_STALL"); return e ? atoi(e) : 0; }();
+                if (stall_env && b >= p->N) {
+                    // test hook: the last piece is never announced -> the kernel must give up and the call must fail cleanly
+                } else if (write_value) {   // stream memory operation: a 32-bit store ordered after the copy, no DMA set-up
+                    if (write_value(p->h2d_stream, (unsigned long long)(uintptr_t)p->d_arrived, (unsigned int)b, 0u) != 0)
+                        return fail(BLFIK_ERR_CUDA, "[blfik_tick_packed] cuStreamWriteValue32 failed");
+                } else {
+                    CU(cudaMemcpyAsync(p->d_arrived, p->h_stream_ctl + c, sizeof(int), cudaMemcpyHostToDevice, p->h2d_stream));
+                }
+                a = b;
+                if (a >= p->N) break;
+            }
+            p->state_set = true, p->ticked = true;
+            if (flags & BLFIK_TICK_INTEGRATE) p->time += dt;
+            CU(cudaStreamSynchronize(p->h2d_stream));
+            CU(cudaStreamSynchronize(p->stream));
+            if (p->h_stream_ctl[kMaxPieces]) return fail(BLFIK_ERR_CUDA, "[blfik_tick_packed] the kernel gave up waiting for the input records (copy stream stalled)");
+            return BLFIK_OK;
+        }
+    }
     // results: when nu (and status) are mapped page-locked buffers the kernels write them straight to the host (posted
     // PCIe writes, no latency to hide), otherwise they are copied back chunk by chunk
     double* nu_map = nullptr;
@@ -1104,6 +1199,14 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
         if (!p->chunk_stream[k]) CU(cudaStreamCreateWithFlags(&p->chunk_stream[k], cudaStreamNonBlocking));
         CU(cudaStreamWaitEvent(p->chunk_stream[k], p->ev_start, 0));
     }
+    // BLFIK_TRACE=1: print the timeline of this call (copy arrival, kernel start / end per chunk) -- a debugging aid
+    static const int trace = [] { const char* e = getenv("BLFIK_TRACE"); return e ? atoi(e) : 0; }();
+    cudaEvent_t tr_start = nullptr, tr_in[kMaxChunks], tr_k0[kMaxChunks], tr_k1[kMaxChunks];
+    if (trace) {
+        CU(cudaEventCreate(&tr_start));
+        for (int c = 0; c < nchunks; c++) { CU(cudaEventCreate(&tr_in[c])); CU(cudaEventCreate(&tr_k0[c])); CU(cudaEventCreate(&tr_k1[c])); }
+        CU(cudaEventRecord(tr_start, p->h2d_stream));
+    }
     // the first chunk is half the size of the others: nothing can run until it has arrived
     auto bound = [&](int c) { return c <= 0 ? 0LL : (c >= nchunks ? p->N : p->N * (2 * c - 1) / (2 * nchunks - 1)); };
     for (int c = 0; c < nchunks; c++) {
@@ -1113,7 +1216,10 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
         CU(cudaMemcpyAsync(p->d_packed + (size_t)R * a, records + (size_t)R * a, (size_t)cnt * R * sizeof(double), cudaMemcpyHostToDevice, p->h2d_stream));
         CU(cudaEventRecord(p->ev_in[c], p->h2d_stream));
         CU(cudaStreamWaitEvent(cs, p->ev_in[c], 0));
-        if ((rc = launch_tick_range(p, a, cnt, 1, dt, flags, cs, p->d_packed, nu_map, status_map, c % kCounterSlots))) return rc;
+        if (trace) CU(cudaEventRecord(tr_in[c], p->h2d_stream));
+        if (trace) CU(cudaEventRecord(tr_k0[c], cs));
+        if ((rc = launch_tick_range(p, a, cnt, 1, dt, flags, cs, p->d_packed, nu_map, status_map, c % kCounterSlots, true))) return rc;
+        if (trace) CU(cudaEventRecord(tr_k1[c], cs));
         CU(cudaEventRecord(p->ev_done[c], cs));
         CU(cudaStreamWaitEvent(p->stream, p->ev_done[c], 0));   // later work on the problem's stream is ordered after every chunk
         if (!nu_map) {
@@ -1126,6 +1232,15 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     if (flags & BLFIK_TICK_INTEGRATE) p->time += dt;
     CU(cudaStreamSynchronize(p->d2h_stream));
     CU(cudaStreamSynchronize(p->stream));
+    if (trace) {
+        for (int c = 0; c < nchunks; c++) {
+            float a = 0, b = 0, d = 0;
+            cudaEventElapsedTime(&a, tr_start, tr_in[c]), cudaEventElapsedTime(&b, tr_start, tr_k0[c]), cudaEventElapsedTime(&d, tr_start, tr_k1[c]);
+            fprintf(stderr, "[blfik trace] chunk %d: %lld robots, copy done %.3f ms, kernel %.3f -> %.3f ms\n", c, (long long)(bound(c + 1) - bound(c)), a, b, d);
+            cudaEventDestroy(tr_in[c]), cudaEventDestroy(tr_k0[c]), cudaEventDestroy(tr_k1[c]);
+        }
+        cudaEventDestroy(tr_start);
+    }
     return BLFIK_OK;
 }
 

@@ -50,6 +50,10 @@ __device__ __forceinline__ void phase_barrier(int mode, int wib, int wpb)
         const int grp = wib & 3;
         const int cnt = ((wpb - grp + 3) >> 2) * 32;   // warps grp, grp + 4, ... of this block
         asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(cnt) : "memory");
+    } else if (mode == 3) {                            // pairs of warps of one sub-partition: grp, grp + 8
+        const int grp = wib & 7;
+        const int cnt = ((wpb - grp + 7) >> 3) * 32;
+        asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(cnt) : "memory");
     }
 }
 
@@ -94,7 +98,31 @@ struct FastParams {
     // instead of a fixed stride, so a team that drew expensive robots simply draws fewer.  The host zeroes the
     // counter before the launch.  nullptr: static striding.
     int* work_counter;
+    // Streaming input (blfik_tick_packed, one persistent launch while the copy engine is still bringing the records in):
+    // robots [first, first + *arrived) have their record on the device.  The copy stream raises *arrived after each piece
+    // (a 4-byte copy ordered after the data copy); a team that drew robots beyond it polls the word -- a wait on a DMA
+    // transfer, never on another kernel -- and gives up after arrive_timeout clocks (*abort_flag = 1, the host reports
+    // the failure).  nullptr: everything is already resident.
+    const int* arrived;
+    int* abort_flag;        // device word: a team gave up, the others stop fetching
+    int* abort_host;        // the same news in mapped host memory, read by the host after the launch
+    long long arrive_timeout;
 };
+
+// Leader-side wait of the streaming-input mode: returns false on time-out.
+__device__ __forceinline__ bool wait_arrived(const int* arrived, int need, long long timeout)
+{
+    int got;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(got) : "l"(arrived) : "memory");
+    if (got >= need) return true;
+    const long long t0 = clock64();
+    while (true) {
+        __nanosleep(200);
+        asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(got) : "l"(arrived) : "memory");
+        if (got >= need) return true;
+        if (clock64() - t0 > timeout) return false;
+    }
+}
 
 template <int NV, int KP>
 struct FastDims {
@@ -377,6 +405,22 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
     return ok;
 }
 
+// Next `cnt` robots for a team (index relative to FP.T.first); in the streaming-input mode the caller also waits until
+// their records are on the device.  A time-out ends the launch: every later fetch returns "past the end".
+__device__ __forceinline__ int fetch_robots(const FastParams& FP, int cnt, int count_total)
+{
+    const int v = atomicAdd(FP.work_counter, cnt);
+    if (FP.arrived && v < count_total) {
+        const int need = v + cnt < count_total ? v + cnt : count_total;
+        if (*reinterpret_cast<volatile int*>(FP.abort_flag) || !wait_arrived(FP.arrived, need, FP.arrive_timeout)) {
+            *reinterpret_cast<volatile int*>(FP.abort_flag) = 1;
+            *reinterpret_cast<volatile int*>(FP.abort_host) = 1;
+            return 0x7fffffff - 64;
+        }
+    }
+    return v;
+}
+
 template <int NV, int KP>
 __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fast_kernel(const FastParams FP)
 {
@@ -432,25 +476,27 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
     // (robots need different numbers of iterations) as they save in fetches (measured: 2.09 ms with, 2.00 ms without),
     // so they are off by default.  Warps past the end of the batch shadow the last robot without writing anything,
     // so that every warp reaches every barrier when they are on.
-    __shared__ int s_next[4][2];
+    __shared__ int s_next[8][2];
     const bool dynamic = FP.work_counter != nullptr;
+    const int count_total = (int)(P.N - P.first);
     long long base0 = P.first + (long long)blockIdx.x * wpb;
     for (int trip = 0;; trip++) {
         int member = wib;
         if (dynamic) {
             int v;
-            if (FP.sync_phases == 2) {
-                const int grp = wib & 3, cnt = (wpb - grp + 3) >> 2;
-                if (wib == grp && lane == 0) s_next[grp][trip & 1] = atomicAdd(FP.work_counter, cnt);
+            if (FP.sync_phases == 2 || FP.sync_phases == 3) {
+                const int sh = FP.sync_phases == 2 ? 2 : 3, msk = (1 << sh) - 1;
+                const int grp = wib & msk, cnt = (wpb - grp + msk) >> sh;
+                if (wib == grp && lane == 0) s_next[grp][trip & 1] = fetch_robots(FP, cnt, count_total);
                 asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(cnt * 32) : "memory");
                 v = s_next[grp][trip & 1];
-                member = wib >> 2;
+                member = wib >> sh;
             } else if (FP.sync_phases == 1) {
-                if (threadIdx.x == 0) s_next[0][trip & 1] = atomicAdd(FP.work_counter, wpb);
+                if (threadIdx.x == 0) s_next[0][trip & 1] = fetch_robots(FP, wpb, count_total);
                 __syncthreads();
                 v = s_next[0][trip & 1];
             } else {
-                v = lane == 0 ? atomicAdd(FP.work_counter, 1) : 0;
+                v = lane == 0 ? fetch_robots(FP, 1, count_total) : 0;
                 v = __shfl_sync(kFull, v, 0);
                 member = 0;
             }

@@ -799,3 +799,35 @@ def test_angular_momentum_task_vs_oracle(hard):
             R, P = o.fk(p0[i], q0[i], s0[i])
             assert np.abs(o.angular_momentum_matrix(R, P) @ nu[i] - sps[3][i]).max() < 1e-8
     prob.close()
+
+
+def test_streaming_host_tick_gives_up_cleanly_when_the_input_stalls():
+    """blfik_tick_packed's streaming mode polls an arrival word raised by the copy stream.  If a piece is never announced
+    (test hook BLFIK_TEST_STALL), the kernel must stop after its time-out instead of spinning for ever, and the call must
+    report the failure.  Runs in a child process because the switches are read once per process."""
+    import subprocess
+    import sys
+    code = r'''
+import sys; sys.path.insert(0, %r)
+import numpy as np, torch
+import blf_b200
+from blf_b200 import capi, workloads as W
+w = W.config(3); N = 4096
+inp = W.synth_inputs(w, N, 3)
+prob = capi.Problem(capi.Model(w.model), w.tasks, N)
+prob.set_inputs(inp)
+rec = torch.from_numpy(prob.pack_inputs(inp)).pin_memory()
+nu = torch.empty((N, w.model.n + 6), dtype=torch.float64).pin_memory()
+st = torch.empty(N, dtype=torch.int32).pin_memory()
+try:
+    prob.tick_packed(rec, nu, st, dt=w.dt, nchunks=4)
+    print("NO ERROR")
+except capi.BlfikError as e:
+    print("ERROR", e)
+''' % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, BLFIK_TEST_STALL="1", BLFIK_ARRIVE_TIMEOUT="200000000")   # 0.1 s of SM clocks
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
+    assert "ERROR" in r.stdout and "gave up waiting" in r.stdout, r.stdout + r.stderr
+    env.pop("BLFIK_TEST_STALL")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
+    assert "NO ERROR" in r.stdout, r.stdout + r.stderr
