@@ -212,6 +212,7 @@ struct blfik_problem {
     int *status = nullptr, *iters = nullptr;
     int* work_counter = nullptr;   // dynamic hand-out of robots in the register-resident kernel
     bool streaming_launch = false; // set around the one launch of the streaming-input mode
+    bool streaming_off = false;    // the mode timed out once (serialised execution): chunk launches from then on
     int* d_arrived = nullptr;      // streaming-input mode of blfik_tick_packed: robots whose record is on the device; [1] = abort word
     int* h_stream_ctl = nullptr;   // pinned + mapped: [0..kMaxPieces) cumulative robot counts (sources of the flag copies), [kMaxPieces] = abort
     unsigned long long* d_count = nullptr;
@@ -940,8 +941,8 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         if (p->streaming_launch && FP.work_counter) {
             FP.arrived = p->d_arrived, FP.abort_flag = p->d_arrived + 1;
             CU(cudaHostGetDevicePointer((void**)&FP.abort_host, p->h_stream_ctl + kMaxPieces, 0));
-            static const long long timeout_env = [] { const char* e = getenv("BLFIK_ARRIVE_TIMEOUT"); return e ? atoll(e) : 4000000000LL; }();
-            FP.arrive_timeout = timeout_env;    // ~2 s of SM clocks: a copy that has not arrived by then never will
+            static const long long timeout_env = [] { const char* e = getenv("BLFIK_ARRIVE_TIMEOUT"); return e ? atoll(e) : 500000000LL; }();
+            FP.arrive_timeout = timeout_env;    // ~0.25 s of SM clocks (the whole transfer takes ~1 ms): copies and kernels are not overlapping
         }
         p->fast_kernel<<<(int)(want < p->fast_grid ? want : p->fast_grid), p->fast_wpb * 32, p->fast_smem, stream>>>(FP);
     } else {
@@ -1105,7 +1106,7 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     // launch of 65k).  Needs the register-resident kernel with dynamic hand-out, page-locked records (a pure DMA on the
     // copy stream) and mapped page-locked outputs.
     static const int streaming_env = [] { const char* e = getenv("BLFIK_STREAMING"); return e ? atoi(e) : 1; }();
-    if (streaming_env && p->fast_kernel && p->path == 0 && p->work_counter && p->N < 0x7fffff00LL) {
+    if (streaming_env && !p->streaming_off && p->fast_kernel && p->path == 0 && p->work_counter && p->N < 0x7fffff00LL) {
         cudaPointerAttributes at;
         double* nu_dev = nullptr;
         int* st_dev = nullptr;
@@ -1176,8 +1177,14 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
             if (flags & BLFIK_TICK_INTEGRATE) p->time += dt;
             CU(cudaStreamSynchronize(p->h2d_stream));
             CU(cudaStreamSynchronize(p->stream));
-            if (p->h_stream_ctl[kMaxPieces]) return fail(BLFIK_ERR_CUDA, "[blfik_tick_packed] the kernel gave up waiting for the input records (copy stream stalled)");
-            return BLFIK_OK;
+            if (!p->h_stream_ctl[kMaxPieces]) return BLFIK_OK;
+            // The kernel gave up waiting: copies and kernels do not overlap here (a profiler or a debugger serialises them, or
+            // the copy stream is stalled).  Nothing is lost -- a packed tick rebuilds the state from the records -- so this
+            // call and the later ones of this problem use chunk launches, which only need stream order.
+            static const int strict_env = [] { const char* e = getenv("BLFIK_TEST_STALL"); return e ? atoi(e) : 0; }();
+            if (strict_env) return fail(BLFIK_ERR_CUDA, "[blfik_tick_packed] the kernel gave up waiting for the input records (copy stream stalled)");
+            p->streaming_off = true;
+            if (flags & BLFIK_TICK_INTEGRATE) p->time -= dt;
         }
     }
     // results: when nu (and status) are mapped page-locked buffers the kernels write them straight to the host (posted
