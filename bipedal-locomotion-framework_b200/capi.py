@@ -38,6 +38,7 @@ EXPORTS = [
     "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state", "blfik_tick_host",
     "blfik_packed_record_len", "blfik_packed_offset", "blfik_tick_packed",
     "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time", "blfik_set_limits",
+    "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len",
 ]
 
 
@@ -53,7 +54,8 @@ class TaskDesc(C.Structure):
                 ("controller_enabled", C.c_int32), ("kp_linear", C.c_double * 3), ("kp_angular", C.c_double * 3),
                 ("kp_joint", c_double_p), ("weight", c_double_p), ("klim", c_double_p),
                 ("upper_limits", c_double_p), ("lower_limits", c_double_p), ("sampling_time", C.c_double),
-                ("ref_frame", C.c_int32), ("distance_threshold", C.c_double)]
+                ("ref_frame", C.c_int32), ("distance_threshold", C.c_double),
+                ("use_position_exogenous_feedback", C.c_int32), ("use_orientation_exogenous_feedback", C.c_int32)]
 
 
 class SolverSettings(C.Structure):
@@ -197,6 +199,8 @@ def task_descs(tasks: Sequence[TaskSpec]):
         d.sampling_time = float(t.sampling_time)
         d.ref_frame = int(getattr(t, "ref_frame", -1))
         d.distance_threshold = float(getattr(t, "threshold", 0.001))
+        d.use_position_exogenous_feedback = int(bool(getattr(t, "exo_position", False)))
+        d.use_orientation_exogenous_feedback = int(bool(getattr(t, "exo_orientation", False)))
     return arr, keep
 
 
@@ -252,6 +256,11 @@ class Problem:
     def set_setpoint(self, task: int, data):
         ptr, dev = _ptr(data)
         _check(self.L.blfik_set_setpoint(self.handle, int(task), ptr, MEM_DEVICE if dev else MEM_HOST))
+
+    def set_feedback(self, task: int, data):
+        """exogenous feedback of an SE3 ([N,7] = p, q) or CoM ([N,3]) task created with the use_*_exogenous_feedback option"""
+        ptr, dev = _ptr(data)
+        _check(self.L.blfik_set_feedback(self.handle, int(task), ptr, MEM_DEVICE if dev else MEM_HOST))
 
     def set_inputs(self, inp):
         """``inp``: workloads.Inputs (host numpy)."""

@@ -184,7 +184,8 @@ struct blfik_model {
 struct HostTask {
     blfik_task_desc d;
     std::vector<double> kp_joint, weight, klim, upper, lower;
-    int rows = 0, sp_len = 0, row_offset = 0, brow = 0, pk_off = 0;
+    int rows = 0, sp_len = 0, row_offset = 0, brow = 0, pk_off = 0;   // sp_len: doubles per robot of the record (set-point + feedback)
+    int fb_len = 0;   // exogenous feedback behind the set-point: 7 (SE3: p, q), 3 (CoM: p) or 0
     double traj_amp[6] = {0, 0, 0, 0, 0, 0}, traj_omega = 0.0;
     double* d_traj_phase = nullptr;
     bool setpoint_set = false;
@@ -469,6 +470,8 @@ static int refresh_tasks(blfik_problem* p)
         d.type = h.d.type, d.priority = h.d.priority, d.frame = h.d.frame, d.rows = h.rows, d.enabled = h.d.controller_enabled;
         d.sp_len = h.sp_len, d.row_offset = h.row_offset, d.brow = h.brow;
         d.flink = 0, d.pk_off = h.pk_off;
+        d.exo_pos = h.d.use_position_exogenous_feedback != 0, d.exo_ori = h.d.use_orientation_exogenous_feedback != 0;
+        d.fb_off = h.sp_len - h.fb_len;
         d.traj_phase = h.d_traj_phase, d.traj_omega = h.d_traj_phase ? h.traj_omega : 0.0;
         for (int c = 0; c < 6; c++) d.traj_amp[c] = h.traj_amp[c];
         for (int c = 0; c < 9; c++) d.Fr[c] = (c % 4 == 0) ? 1.0 : 0.0;
@@ -542,6 +545,10 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
             return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: frame index %d out of range", t, h.d.frame));
         if (h.rows == 0) return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: the mask selects no row", t));
         h.sp_len = sp_len_of(h.d.type, n);
+        if (h.d.type == BLFIK_TASK_SE3 && (h.d.use_position_exogenous_feedback || h.d.use_orientation_exogenous_feedback)) h.fb_len = 7;
+        else if (h.d.type == BLFIK_TASK_COM && h.d.use_position_exogenous_feedback) h.fb_len = 3;
+        else h.d.use_position_exogenous_feedback = h.d.use_orientation_exogenous_feedback = 0;   // the other tasks have no such option
+        h.sp_len += h.fb_len;
         if (h.d.type == BLFIK_TASK_JOINT_TRACKING) {
             if (!h.d.kp_joint) return bail(fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_problem_create] task %d: JointTrackingTask needs kp", t));
             h.kp_joint.assign(h.d.kp_joint, h.d.kp_joint + n);
@@ -684,6 +691,11 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         return bail(rc);
     for (HostTask& h : p->tasks) {
         if (h.sp_len && (rc = dev_alloc(p, Ns * h.sp_len, &h.d_setpoint))) return bail(rc);
+        if (h.fb_len == 7) {   // the controllers' initial state: zero position, identity rotation (quaternion x, y, z, w)
+            const std::vector<double> ones(Ns, 1.0);
+            if (cudaMemcpy2D(h.d_setpoint + h.sp_len - 1, h.sp_len * sizeof(double), ones.data(), sizeof(double), sizeof(double), Ns, cudaMemcpyHostToDevice) != cudaSuccess)
+                return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cudaMemcpy2D failed: %s", cudaGetErrorString(cudaGetLastError())));
+        }
         if ((rc = dev_upload(p, h.kp_joint, &h.d_kp_joint)) || (rc = dev_upload(p, h.weight, &h.d_weight)) || (rc = dev_upload(p, h.klim, &h.d_klim)) ||
             (rc = dev_upload(p, h.upper, &h.d_upper)) || (rc = dev_upload(p, h.lower, &h.d_lower)))
             return bail(rc);
@@ -763,7 +775,7 @@ extern "C" int blfik_get_state(blfik_problem* p, double* bp, double* bq, double*
 extern "C" int32_t blfik_setpoint_len(const blfik_problem* p, int32_t t)
 {
     if (!p || t < 0 || t >= (int)p->tasks.size()) return -1;
-    return p->tasks[t].sp_len;
+    return p->tasks[t].sp_len - p->tasks[t].fb_len;
 }
 
 extern "C" int blfik_set_setpoint(blfik_problem* p, int32_t t, const double* data, int32_t mem)
@@ -773,9 +785,37 @@ extern "C" int blfik_set_setpoint(blfik_problem* p, int32_t t, const double* dat
     HostTask& h = p->tasks[t];
     if (h.sp_len == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint] task %d takes no set-point", t);
     if (!data) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint] null buffer");
-    CU(cudaMemcpyAsync(h.d_setpoint, data, (size_t)p->N * h.sp_len * sizeof(double), kind_in(mem), p->stream));
+    const int base = h.sp_len - h.fb_len;
+    if (h.fb_len == 0)
+        CU(cudaMemcpyAsync(h.d_setpoint, data, (size_t)p->N * h.sp_len * sizeof(double), kind_in(mem), p->stream));
+    else   // the record is wider than the set-point: strided rows
+        CU(cudaMemcpy2DAsync(h.d_setpoint, h.sp_len * sizeof(double), data, base * sizeof(double), base * sizeof(double), (size_t)p->N, kind_in(mem), p->stream));
     h.setpoint_set = true;
     return BLFIK_OK;
+}
+
+extern "C" int blfik_set_feedback(blfik_problem* p, int32_t t, const double* data, int32_t mem)
+{
+    CHECK_P(p, "blfik_set_feedback");
+    CHECK_TASK(p, t, "blfik_set_feedback");
+    HostTask& h = p->tasks[t];
+    if (h.fb_len == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_feedback] task %d does not use an exogenous feedback", t);
+    if (!data) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_feedback] null buffer");
+    CU(cudaMemcpy2DAsync(h.d_setpoint + (h.sp_len - h.fb_len), h.sp_len * sizeof(double), data, h.fb_len * sizeof(double), h.fb_len * sizeof(double),
+                         (size_t)p->N, kind_in(mem), p->stream));
+    return BLFIK_OK;
+}
+
+extern "C" int32_t blfik_feedback_len(const blfik_problem* p, int32_t t)
+{
+    if (!p || t < 0 || t >= (int)p->tasks.size()) return -1;
+    return p->tasks[t].fb_len;
+}
+
+extern "C" int32_t blfik_record_len(const blfik_problem* p, int32_t t)
+{
+    if (!p || t < 0 || t >= (int)p->tasks.size()) return -1;
+    return p->tasks[t].sp_len;
 }
 
 extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const double* amplitude, double period, const double* phase, int32_t mem)

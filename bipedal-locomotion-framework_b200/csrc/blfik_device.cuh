@@ -62,6 +62,8 @@ struct DevTask {
     double Fp2[3];           // DistanceTask: origin of the reference frame in its link
     double thr;              // DistanceTask: distance_numeric_threshold
     int pk_off;              // offset of this task's set-point inside a packed input record
+    int exo_pos, exo_ori;    // exogenous feedback (SE3Task.cpp:261-268, CoMTask.cpp:192-195): controller state from the record
+    int fb_off;              // where the feedback p(3) [q(4)] sits inside the record (= the set-point length)
 };
 
 struct Settings {
@@ -521,6 +523,7 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
             double bt[6], spl[13];
             int src[6];
             int rows = 0;
+            const double* sp0 = sp;   // the stored record (the exogenous feedback sits behind the set-point)
             sp = traj_eval(tk, robot, tnow, sp, spl);
             if (tk.type == T_ANGMOM) {   // AngularMomentumTask.cpp:137-185: A = masked rows of the angular CMM, b = desired momentum
                 double com[3];
@@ -534,6 +537,8 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
             } else if (tk.type == T_COM) {
                 double com[3];
                 k1_com(m, w, com, w.Jt, LD, lane);
+                if (tk.exo_pos)   // measured CoM instead of the model's (CoMTask.cpp:192-195)
+                    for (int c = 0; c < 3; c++) com[c] = sp0[tk.fb_off + c];
                 for (int c = 0; c < 3; c++)
                     if (tk.mask[c]) {  // CoMTask.cpp:194-203: b = v_ff + kp (p_d - p_com)
                         bt[rows] = sp[3 + c] + tk.kp_lin[c] * (sp[c] - com[c]);
@@ -574,9 +579,12 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
                 }
                 if (tk.type == T_SE3 || tk.type == T_R3) {
                     const int voff = tk.type == T_SE3 ? 7 : 3;
+                    double pc[3] = {pf[0], pf[1], pf[2]};
+                    if (tk.type == T_SE3 && tk.exo_pos)   // SE3Task.cpp:266-269
+                        for (int c = 0; c < 3; c++) pc[c] = sp0[tk.fb_off + c];
                     for (int c = 0; c < 3; c++)
                         if (tk.mask[c]) {  // SE3Task.cpp:276-316
-                            bt[rows] = tk.enabled ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pf[c]) : sp[voff + c];
+                            bt[rows] = tk.enabled ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pc[c]) : sp[voff + c];
                             src[rows++] = c;
                         }
                 }
@@ -584,6 +592,10 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
                     const double* qd = tk.type == T_SE3 ? sp + 3 : sp;
                     const double* wff = tk.type == T_SE3 ? sp + 10 : sp + 4;
                     double qdl[4] = {qd[0], qd[1], qd[2], qd[3]}, wl[3] = {wff[0], wff[1], wff[2]}, out[3];
+                    if (tk.type == T_SE3 && tk.exo_ori) {   // SE3Task.cpp:261-265: measured orientation
+                        const double qf[4] = {sp0[tk.fb_off + 3], sp0[tk.fb_off + 4], sp0[tk.fb_off + 5], sp0[tk.fb_off + 6]};
+                        quat_to_rot(qf, R);
+                    }
                     so3_control(R, qdl, wl, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), out);
                     for (int c = 0; c < 3; c++) bt[rows] = out[c], src[rows++] = 3 + c;
                 }

@@ -636,8 +636,8 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                 const bool dense = is_dense_type(tk.type);
                 if (dense) {
                     double spl[13];
-                    const double* sp = traj_eval(tk, robot, P.t0 + tick * P.dt,
-                                                 P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : tk.setpoint + robot * tk.sp_len, spl);
+                    const double* sp0 = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : tk.setpoint + robot * tk.sp_len;
+                    const double* sp = traj_eval(tk, robot, P.t0 + tick * P.dt, sp0, spl);
                     const bool has_lin = tk.type == T_SE3 || tk.type == T_R3 || tk.type == T_COM, has_ang = tk.type == T_SE3 || tk.type == T_SO3;
                     double Rf[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, pf[3] = {com[0], com[1], com[2]};
                     if (tk.type != T_COM) {
@@ -654,8 +654,14 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                     const bool lin_on = tk.type == T_COM || tk.type == T_R3 || tk.enabled != 0;   // only SE3Task has a controller mode
                     double bl[3] = {0.0, 0.0, 0.0}, ba[3];
                     if (has_lin) {
+                        // exogenous feedback (SE3Task.cpp:266-269, CoMTask.cpp:192-195): the controller compares the set-point
+                        // with the measured position stored behind it in the record; the rows still use the model's pf
+                        const bool exo = tk.exo_pos && (tk.type == T_SE3 || tk.type == T_COM);
 #pragma unroll
-                        for (int c = 0; c < 3; c++) bl[c] = lin_on ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pf[c]) : sp[voff + c];
+                        for (int c = 0; c < 3; c++) {
+                            const double pc = exo ? sp0[tk.fb_off + c] : pf[c];
+                            bl[c] = lin_on ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pc) : sp[voff + c];
+                        }
                     }
                     double qd[4] = {0.0, 0.0, 0.0, 1.0}, wff[3] = {0.0, 0.0, 0.0};
                     if (has_ang) {
@@ -665,7 +671,14 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
 #pragma unroll
                         for (int c = 0; c < 3; c++) wff[c] = sp[wo + c];
                     }
-                    so3_control(Rf, qd, wff, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), ba);
+                    if (tk.type == T_SE3 && tk.exo_ori) {   // SE3Task.cpp:261-265: measured orientation
+                        const double qf[4] = {sp0[tk.fb_off + 3], sp0[tk.fb_off + 4], sp0[tk.fb_off + 5], sp0[tk.fb_off + 6]};
+                        double Rc[9];
+                        quat_to_rot(qf, Rc);
+                        so3_control(Rc, qd, wff, tk.kp_ang, tk.enabled != 0, ba);
+                    } else {
+                        so3_control(Rf, qd, wff, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), ba);
+                    }
                     double aux[3] = {0.0, 0.0, 0.0};
                     if (tk.type == T_DISTANCE) {   // DistanceTask.cpp:178-229: u = d / max(thr, |d|), b = kp (d_des - |d|)
                         if (tk.flink2 >= 0) {

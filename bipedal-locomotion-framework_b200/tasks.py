@@ -3,8 +3,9 @@
 One ``TaskSpec`` per reference task object; the fields are the reference's
 parameter-handler keys:
 
-* ``SE3Task``  -- ``frame_name, kp_linear, kp_angular, mask``      (src/IK/src/SE3Task.cpp:114-214)
-* ``CoMTask``  -- ``kp_linear, mask``                               (src/IK/src/CoMTask.cpp:107-162)
+* ``SE3Task``  -- ``frame_name, kp_linear, kp_angular, mask, use_position_exogenous_feedback,
+  use_orientation_exogenous_feedback``                              (src/IK/src/SE3Task.cpp:114-214)
+* ``CoMTask``  -- ``kp_linear, mask, use_exogenous_feedback``       (src/IK/src/CoMTask.cpp:107-162)
 * ``SO3Task``  -- ``frame_name, kp_angular``                        (src/IK/src/SO3Task.cpp:67-151)
 * ``R3Task``   -- ``frame_name, kp_linear, mask``                   (src/IK/src/R3Task.cpp:60-176)
 * ``AngularMomentumTask`` -- ``mask``                               (src/IK/src/AngularMomentumTask.cpp:67-135)
@@ -69,11 +70,24 @@ class TaskSpec:
     sampling_time: float = 0.0
     ref_frame: int = -1          # DistanceTask: reference frame (-1: the world origin)
     threshold: float = 0.001     # DistanceTask: distance_numeric_threshold
+    exo_position: bool = False     # SE3Task use_position_exogenous_feedback / CoMTask use_exogenous_feedback
+    exo_orientation: bool = False  # SE3Task use_orientation_exogenous_feedback
 
     def rows(self, n: int) -> int:
         nm = int(sum(bool(m) for m in self.mask))
         return {TASK_SE3: nm + 3, TASK_COM: nm, TASK_R3: nm, TASK_SO3: 3, TASK_DISTANCE: 1, TASK_GRAVITY: 2, TASK_ANGULAR_MOMENTUM: nm, TASK_JOINT_TRACKING: n,
                 TASK_JOINT_LIMITS: 2 * n, TASK_JOINT_VELOCITY_LIMITS: 2 * n}[self.type]
+
+    def feedback_len(self) -> int:
+        """doubles of exogenous feedback appended to every set-point record: SE3 p(3) q(4), CoM p(3)"""
+        if self.type == TASK_SE3 and (self.exo_position or self.exo_orientation):
+            return 7
+        if self.type == TASK_COM and self.exo_position:
+            return 3
+        return 0
+
+    def record_len(self, n: int) -> int:
+        return self.setpoint_len(n) + self.feedback_len()
 
     def setpoint_len(self, n: int) -> int:
         return {TASK_SE3: 13, TASK_COM: 6, TASK_SO3: 7, TASK_R3: 6, TASK_DISTANCE: 1, TASK_GRAVITY: 6, TASK_ANGULAR_MOMENTUM: 3, TASK_JOINT_TRACKING: 2 * n,
@@ -85,14 +99,18 @@ class TaskSpec:
 
 
 def se3_task(model: KinematicModel, name: str, frame_name: str, kp_linear, kp_angular, priority=0,
-             weight=None, mask=(True, True, True)) -> TaskSpec:
+             weight=None, mask=(True, True, True), use_position_exogenous_feedback=False,
+             use_orientation_exogenous_feedback=False) -> TaskSpec:
     t = TaskSpec(name, TASK_SE3, priority, model.frame_index(frame_name), tuple(mask), True, _vec3(kp_linear), _vec3(kp_angular))
+    t.exo_position, t.exo_orientation = bool(use_position_exogenous_feedback), bool(use_orientation_exogenous_feedback)
     t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
     return t
 
 
-def com_task(model: KinematicModel, name: str, kp_linear, priority=0, weight=None, mask=(True, True, True)) -> TaskSpec:
+def com_task(model: KinematicModel, name: str, kp_linear, priority=0, weight=None, mask=(True, True, True),
+             use_exogenous_feedback=False) -> TaskSpec:
     t = TaskSpec(name, TASK_COM, priority, -1, tuple(mask), True, _vec3(kp_linear))
+    t.exo_position = bool(use_exogenous_feedback)
     t.weight = None if weight is None else np.asarray(weight, dtype=np.float64).copy()
     return t
 

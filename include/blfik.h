@@ -117,6 +117,8 @@ typedef struct {
     double sampling_time;       /* "sampling_time" [s]      JointLimitsTask             */
     int32_t ref_frame;          /* "reference_frame_name" of DistanceTask, -1 = world origin ("")   */
     double distance_threshold;  /* "distance_numeric_threshold" of DistanceTask (0 -> 0.001)       */
+    int32_t use_position_exogenous_feedback;    /* SE3Task key of the same name (SE3Task.cpp:206-214); CoMTask "use_exogenous_feedback" (CoMTask.cpp:116) */
+    int32_t use_orientation_exogenous_feedback; /* SE3Task key of the same name (SE3Task.cpp:196-204)                                               */
 } blfik_task_desc;
 
 /* ADMM + polish parameters.  rho/sigma/alpha have OSQP's meaning (osqp v0.6.3); the
@@ -168,6 +170,18 @@ int blfik_get_state(blfik_problem* problem, double* base_pos, double* base_quat,
  *   AngularMomentum: 3 = desired centroidal angular momentum (AngularMomentumTask::setSetPoint; rows selected by mask) */
 int blfik_set_setpoint(blfik_problem* problem, int32_t task, const double* data, int32_t mem);
 int32_t blfik_setpoint_len(const blfik_problem* problem, int32_t task);
+
+/* replaces task->setFeedback(...) (SE3Task.cpp:338-366, CoMTask.cpp:262-273) for a task created with
+ * use_position_exogenous_feedback / use_orientation_exogenous_feedback: the state the task's P-controllers compare the
+ * set-point with is what the caller measured instead of the pose kinDyn predicts (the Jacobian stays kinDyn's).
+ * data is [N][7] = p(3) q(4) for an SE3Task (the part whose flag is off is ignored), [N][3] for a CoMTask.
+ * Until the first call the feedback is the controllers' initial state: zero position, identity rotation.
+ * In the batch record of such a task (blfik_tick_host, blfik_tick_packed: blfik_record_len doubles per robot) the
+ * feedback follows the set-point.                                                                             */
+int blfik_set_feedback(blfik_problem* problem, int32_t task, const double* data, int32_t mem);
+int32_t blfik_feedback_len(const blfik_problem* problem, int32_t task);
+/* blfik_setpoint_len + blfik_feedback_len: doubles per robot of the task's record */
+int32_t blfik_record_len(const blfik_problem* problem, int32_t task);
 
 /* On-device set-point producer for closed-loop rollouts (no single counterpart: it stands in for the planners /
  * splines whose output the reference's callers pass to setSetPoint every period, e.g.

@@ -294,6 +294,14 @@ int orc_setpoint_len(int type, int n)
     }
 }
 
+int orc_task_setpoint_len(const orc_task* t, int n)
+{
+    int len = orc_setpoint_len(t->type, n);
+    if (t->type == ORC_TASK_SE3 && (t->exo_pos || t->exo_ori)) len += 7;
+    if (t->type == ORC_TASK_COM && t->exo_pos) len += 3;
+    return len;
+}
+
 static int mask_count(const int* mask) { return (mask[0] != 0) + (mask[1] != 0) + (mask[2] != 0); }
 
 int orc_task_rows(const orc_task* t, int n)
@@ -352,6 +360,11 @@ int orc_task_update(const orc_model* m, const orc_task* t, const double* link_R,
         double* Jd = (nv <= 64) ? J : (double*)malloc(sizeof(double) * 6 * nv);
         orc_frame_pose(m, link_R, link_p, t->frame, R, pf);
         orc_frame_jacobian(m, link_R, link_p, t->frame, Jd);
+        /* exogenous feedback (SE3Task.cpp:261-268, :338-366): the controllers' state is what the caller measured (record
+         * tail: p_fb(3) q_fb(4)) instead of the pose kinDyn predicts; the Jacobian is always kinDyn's */
+        if (t->exo_pos)
+            for (int c = 0; c < 3; c++) pf[c] = sp[13 + c];
+        if (t->exo_ori) orc_quat_to_rot(sp + 16, R);
         int idx = 0;
         for (int c = 0; c < 3; c++) {
             if (!t->mask[c]) continue;
@@ -386,6 +399,8 @@ int orc_task_update(const orc_model* m, const orc_task* t, const double* link_R,
         double Jc[3 * 64], com[3];
         double* Jd = (nv <= 64) ? Jc : (double*)malloc(sizeof(double) * 3 * nv);
         orc_com(m, link_R, link_p, com, Jd);
+        if (t->exo_pos) /* CoMTask.cpp:192-195, :262-273: measured CoM in the record tail */
+            for (int c = 0; c < 3; c++) com[c] = sp[6 + c];
         int idx = 0;
         for (int c = 0; c < 3; c++) {
             if (!t->mask[c]) continue;
@@ -937,7 +952,7 @@ int orc_tick_batch(const orc_model* m, const orc_task* tasks, int ntasks,
     for (long i = i0; i < i1; i++) {
         for (int tick = 0; tick < nticks; tick++) {
             for (int t = 0; t < ntasks; t++) {
-                const int len = orc_setpoint_len(tasks[t].type, n);
+                const int len = orc_task_setpoint_len(&tasks[t], n);
                 sp[t] = (setpoints && setpoints[t]) ? setpoints[t] + (size_t)i * len : NULL;
             }
             int rows = orc_assemble(m, tasks, ntasks, sp, base_pos + 3 * i, base_quat + 4 * i,

@@ -91,6 +91,8 @@ typedef struct {
     double sampling_time;   /* JointLimitsTask                                  */
     int ref_frame;          /* DistanceTask: reference frame, -1 = world origin  */
     double threshold;       /* DistanceTask: distance_numeric_threshold          */
+    int exo_pos;            /* SE3Task use_position_exogenous_feedback / CoMTask use_exogenous_feedback (SE3Task.cpp:196-213, CoMTask.cpp:116) */
+    int exo_ori;            /* SE3Task use_orientation_exogenous_feedback         */
 } orc_task;
 
 typedef struct {
@@ -118,6 +120,8 @@ void orc_parity_settings(orc_qp_settings* s);         /* eps 1e-7 + polish     *
 
 /* set-point record lengths per task type (doubles) */
 int orc_setpoint_len(int type, int n);
+/* record length of one task: the set-point, followed by the exogenous feedback (SE3: p(3) q(4); CoM: p(3)) when the task uses one */
+int orc_task_setpoint_len(const orc_task* t, int n);
 int orc_task_rows(const orc_task* t, int n);
 int orc_task_is_inequality(const orc_task* t);
 

@@ -33,7 +33,7 @@ class OrcTask(C.Structure):
                 ("controller_enabled", C.c_int), ("kp_lin", C.c_double * 3), ("kp_ang", C.c_double * 3),
                 ("kp_joint", c_double_p), ("weight", c_double_p), ("klim", c_double_p),
                 ("upper", c_double_p), ("lower", c_double_p), ("sampling_time", C.c_double),
-                ("ref_frame", C.c_int), ("threshold", C.c_double)]
+                ("ref_frame", C.c_int), ("threshold", C.c_double), ("exo_pos", C.c_int), ("exo_ori", C.c_int)]
 
 
 class OrcSettings(C.Structure):
@@ -118,6 +118,8 @@ class Oracle:
             ct.sampling_time = float(t.sampling_time)
             ct.ref_frame = int(getattr(t, 'ref_frame', -1))
             ct.threshold = float(getattr(t, 'threshold', 0.001))
+            ct.exo_pos = int(bool(getattr(t, 'exo_position', False)))
+            ct.exo_ori = int(bool(getattr(t, 'exo_orientation', False)))
         self.ctasks = arr
         self.m = sum(t.rows(self.n) for t in self.tasks if t.priority == 0)
 

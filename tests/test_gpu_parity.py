@@ -831,3 +831,76 @@ except capi.BlfikError as e:
     env.pop("BLFIK_TEST_STALL")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
     assert "NO ERROR" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("path", PATHS)
+def test_exogenous_feedback_vs_oracle(path):
+    """use_position_exogenous_feedback / use_orientation_exogenous_feedback (SE3Task.cpp:196-214, :261-268, :338-366) and
+    CoMTask's use_exogenous_feedback (CoMTask.cpp:116, :192-195): blfik_set_feedback supplies the measured pose, the assembled
+    right-hand sides and nu follow the oracle; before any feedback is set the controllers see zero position / identity; the
+    packed host tick carries the feedback behind the set-point."""
+    m = M.ergocub23()
+    n, N = m.n, 48
+    tasks = [T.se3_task(m, "lf", "l_sole", 5.0, 5.0, use_position_exogenous_feedback=True, use_orientation_exogenous_feedback=True),
+             T.se3_task(m, "rf", "r_sole", 5.0, 5.0, use_position_exogenous_feedback=True),
+             T.com_task(m, "com", 2.0, mask=(True, True, False), use_exogenous_feedback=True),
+             T.so3_task(m, "chest", "chest", 5.0, priority=1, weight=[5.0, 5.0, 5.0]),
+             T.joint_tracking_task(m, "reg", np.full(n, 5.0), priority=1, weight=np.ones(n))]
+    inp = W.synth_inputs(W.config(3), N, 11)
+    p0, q0, s0 = inp.base_pos, inp.base_quat, inp.s
+    rng = np.random.default_rng(12)
+    base = [inp.setpoints[2], inp.setpoints[1], inp.setpoints[0], inp.setpoints[5], inp.setpoints[6]]
+    o = Oracle(m, tasks)
+    # "measurements": the model's pose plus a small error
+    fb = [np.zeros((N, 7)), np.zeros((N, 7)), np.zeros((N, 3))]
+    for i in range(N):
+        R, P = o.fk(p0[i], q0[i], s0[i])
+        for k in (0, 1):
+            Rf, pf = o.frame_pose(R, P, tasks[k].frame)
+            fb[k][i, :3] = pf + rng.normal(0, 0.004, 3)
+            fb[k][i, 3:] = W.rot_to_quat((W.quat_to_rot(W.so3_exp(rng.normal(0, 0.01, (1, 3)))) @ Rf)[0][None])[0]
+        fb[2][i] = o.com(R, P)[0] + rng.normal(0, 0.004, 3)
+    model, prob = make(m, tasks, N, path)
+    assert [prob.L.blfik_feedback_len(prob.handle, t) for t in range(5)] == [7, 7, 3, 0, 0]
+    assert [prob.L.blfik_setpoint_len(prob.handle, t) for t in range(3)] == [13, 13, 6] and prob.L.blfik_record_len(prob.handle, 0) == 20
+    with pytest.raises(capi.BlfikError):
+        prob.set_feedback(3, np.zeros((N, 7)))           # the SO3 task has no such option
+    prob.set_state(p0, q0, s0)
+    for t, sp in enumerate(base):
+        prob.set_setpoint(t, sp)
+    me = prob.me
+    prob.debug_enable(True)
+
+    def check(records):
+        prob.tick(1, 0.01)
+        g, be = prob.debug_get(capi.DEBUG_G), prob.debug_get(capi.DEBUG_BEQ)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        for i in range(0, N, 5):
+            Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [r[i] for r in records])
+            assert np.abs(be[i] - u[:me]).max() <= 1e-12 * (1 + np.abs(u[:me]).max())
+            assert np.abs(g[i] - go).max() <= 1e-12 * (1 + np.abs(go).max())
+        nur, str_, _ = o.tick_batch(p0.copy(), q0.copy(), s0.copy(), records)
+        ok = (st == 0) & (str_ == 0)
+        assert ok.mean() > 0.9 and np.abs(nu - nur)[ok].max() <= TOL_NU
+        return nu
+    ident = np.tile([0.0, 0, 0, 0, 0, 0, 1.0], (N, 1))
+    # no feedback yet: zero position, identity rotation (the initial state of the reference's controllers)
+    check([np.hstack([base[0], ident]), np.hstack([base[1], ident]), np.hstack([base[2], np.zeros((N, 3))]), base[3], base[4]])
+    for t in range(3):
+        prob.set_feedback(t, fb[t])
+    records = [np.hstack([base[0], fb[0]]), np.hstack([base[1], fb[1]]), np.hstack([base[2], fb[2]]), base[3], base[4]]
+    nu = check(records)
+    prob.set_setpoint(0, base[0] + 0.0)                  # re-setting the set-point leaves the feedback in place
+    assert np.array_equal(check(records), nu)
+    prob.debug_enable(False)
+    # the packed host tick: feedback travels behind the set-point in the record
+    rec = np.empty((N, prob.packed_record_len))
+    rec[:, 0:3], rec[:, 3:7], rec[:, 7:7 + n] = p0, q0, s0
+    for t, r in enumerate(records):
+        off = prob.packed_offset(t)
+        rec[:, off:off + r.shape[1]] = r
+    nu2, st2 = np.empty((N, n + 6)), np.empty(N, dtype=np.int32)
+    prob.tick_packed(rec, nu2, st2, dt=0.01, nchunks=2)
+    assert np.array_equal(nu2, nu)
+    prob.close()

@@ -346,3 +346,36 @@ def test_angular_momentum_task(ergo):
     R26, P26 = o26.fk(p, q, s26)
     R32, P32 = o32.fk(p, q, s32)
     assert np.abs(o26.angular_momentum_matrix(R26, P26) @ nu26 - o32.angular_momentum_matrix(R32, P32) @ nu32).max() < 1e-12
+
+
+def test_exogenous_feedback_changes_b_only(ergo):
+    """SE3Task.cpp:261-268 / :338-366 and CoMTask.cpp:192-195 / :262-273: with use_*_exogenous_feedback the controllers compare
+    the set-point with the pose the caller measured (record tail), the Jacobian stays the model's."""
+    m = ergo
+    rng = np.random.default_rng(31)
+    plain = [T.se3_task(m, "f", "l_sole", [1.0, 2.0, 3.0], 4.0), T.com_task(m, "c", 2.0)]
+    exo = [T.se3_task(m, "f", "l_sole", [1.0, 2.0, 3.0], 4.0, use_position_exogenous_feedback=True, use_orientation_exogenous_feedback=True),
+           T.se3_task(m, "g", "l_sole", [1.0, 2.0, 3.0], 4.0, use_position_exogenous_feedback=True),
+           T.com_task(m, "c", 2.0, use_exogenous_feedback=True)]
+    assert exo[0].record_len(m.n) == 20 and exo[1].record_len(m.n) == 20 and exo[2].record_len(m.n) == 9 and plain[0].record_len(m.n) == 13
+    o, oe = Oracle(m, plain), Oracle(m, exo)
+    p, q, s = random_state(m, rng)
+    R, P = o.fk(p, q, s)
+    sp = np.concatenate([rng.normal(size=3), W.so3_exp(rng.normal(size=(1, 3)))[0], rng.normal(size=6)])
+    p_fb, q_fb = rng.normal(size=3), W.so3_exp(rng.normal(size=(1, 3)))[0]
+    A0, b0 = o.task_update(0, R, P, s, sp)
+    A1, b1 = oe.task_update(0, R, P, s, np.concatenate([sp, p_fb, q_fb]))
+    assert np.array_equal(A0, A1)
+    assert np.allclose(b1[:3], sp[7:10] + np.array([1.0, 2.0, 3.0]) * (sp[:3] - p_fb))
+    assert np.allclose(b1[3:], _so3_ctrl(W.quat_to_rot(q_fb[None])[0], sp[3:7], sp[10:13], np.full(3, 4.0)), atol=1e-12)
+    # position only: the angular part is the model's
+    A2, b2 = oe.task_update(1, R, P, s, np.concatenate([sp, p_fb, q_fb]))
+    assert np.allclose(b2[:3], b1[:3]) and np.allclose(b2[3:], b0[3:])
+    # feedback equal to the model's pose reproduces the plain task
+    Rf, pf = o.frame_pose(R, P, plain[0].frame)
+    _, b3 = oe.task_update(0, R, P, s, np.concatenate([sp, pf, W.rot_to_quat(Rf[None])[0]]))
+    assert np.allclose(b3, b0, atol=1e-12)
+    spc, c_fb = rng.normal(size=6), rng.normal(size=3)
+    Ac0, _ = o.task_update(1, R, P, s, spc)
+    Ac1, bc1 = oe.task_update(2, R, P, s, np.concatenate([spc, c_fb]))
+    assert np.array_equal(Ac0, Ac1) and np.allclose(bc1, spc[3:] + 2.0 * (spc[:3] - c_fb))
