@@ -33,6 +33,8 @@ class IKLinearTask:
         self._sp = None
         self._sp_version = 0
         self._gains_version = 0
+        self._fb = None            # exogenous feedback [N, _fb_len] (tasks created with a use_*_exogenous_feedback key)
+        self._fb_version = 0
         self._description = "Generic Linear Task Element"
 
     def set_kin_dyn(self, kin_dyn):
@@ -104,6 +106,20 @@ class IKLinearTask:
         self._set_point_set = True
         return True
 
+    _fb_len = 0
+    _fb_init = ()
+
+    def _store_feedback(self, values, first, instance=None):
+        """values: [k] (every robot, or robot `instance`) or [N, k], written at column `first` of the feedback record"""
+        N = self._kin_dyn.N
+        if self._fb is None:
+            self._fb = np.tile(np.asarray(self._fb_init, dtype=np.float64), (N, 1))
+        v = np.asarray(values, dtype=np.float64)
+        sel = slice(None) if (instance is None or v.ndim == 2) else instance
+        self._fb[sel, first:first + v.shape[-1]] = v
+        self._fb_version += 1
+        return True
+
     def _spec(self, name, priority, weight) -> T.TaskSpec:
         raise NotImplementedError
 
@@ -167,8 +183,29 @@ class SE3Task(IKLinearTask):
         if self._mask3 is None:
             log().error("[SE3Task::initialize] The size of the mask must be 3.")
             return False
+        # optional, default false (SE3Task.cpp:196-214)
+        self._exo_pos = bool(param_handler._opt(param_handler.get_parameter_bool, "use_position_exogenous_feedback") or False)
+        self._exo_ori = bool(param_handler._opt(param_handler.get_parameter_bool, "use_orientation_exogenous_feedback") or False)
+        self._fb_len = 7 if (self._exo_pos or self._exo_ori) else 0
+        self._fb_init = (0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 1.0)   # the controllers' initial state: p = 0, q = identity
         self._description = f"SE3Task Optimal Control Element - Frame name: {frame}."
         self._initialized = True
+        return True
+
+    def set_feedback(self, I_H_F=None, I_p_F=None, I_R_F=None, instance=None):
+        """SE3Task.cpp:338-366: measured pose (or only its position / rotation) for the controllers; a part whose
+        use_*_exogenous_feedback key is off is ignored.  Batch form: I_p_F [N,3], I_R_F [N,4] quaternions (x, y, z, w)."""
+        if isinstance(I_H_F, manif.SE3):
+            I_p_F, I_R_F = I_H_F.translation(), I_H_F.asSO3()
+        elif I_H_F is not None:
+            pose = np.asarray(I_H_F, dtype=np.float64)
+            I_p_F, I_R_F = pose[..., :3], pose[..., 3:7]
+        if self._kin_dyn is None:
+            return False
+        if I_p_F is not None and self._exo_pos:
+            self._store_feedback(_vec(I_p_F, 3), 0, instance)
+        if I_R_F is not None and self._exo_ori:
+            self._store_feedback(_vec(_quat_of(I_R_F), 4), 3, instance)
         return True
 
     def set_set_point(self, I_H_F, mixed_velocity=None, instance=None):
@@ -190,6 +227,7 @@ class SE3Task(IKLinearTask):
     def _spec(self, name, priority, weight):
         t = T.se3_task(self._kin_dyn.model(), name, self._kin_dyn.getFrameName(self._frame), self._kp_lin, self._kp_ang, priority, weight, self._mask3)
         t.controller_enabled = self._mode == SE3Task.Mode.Enable
+        t.exo_position, t.exo_orientation = self._exo_pos, self._exo_ori
         return t
 
 
@@ -208,8 +246,19 @@ class CoMTask(IKLinearTask):
         if self._mask3 is None:
             log().error("[CoMTask::initialize] The size of the mask must be 3.")
             return False
+        self._exo_pos = bool(param_handler._opt(param_handler.get_parameter_bool, "use_exogenous_feedback") or False)   # CoMTask.cpp:116-123
+        self._fb_len = 3 if self._exo_pos else 0
+        self._fb_init = (0.0, 0.0, 0.0)
         self._description = "CoM Task"
         self._initialized = True
+        return True
+
+    def set_feedback(self, feedback, instance=None):
+        """CoMTask.cpp:262-273: measured CoM; ignored unless use_exogenous_feedback"""
+        if self._kin_dyn is None:
+            return False
+        if self._exo_pos:
+            self._store_feedback(_vec(feedback, 3), 0, instance)
         return True
 
     def set_set_point(self, position, velocity=None, instance=None):
@@ -223,7 +272,7 @@ class CoMTask(IKLinearTask):
         return sum(self._mask3)
 
     def _spec(self, name, priority, weight):
-        return T.com_task(self._kin_dyn.model(), name, self._kp_lin, priority, weight, self._mask3)
+        return T.com_task(self._kin_dyn.model(), name, self._kp_lin, priority, weight, self._mask3, use_exogenous_feedback=self._exo_pos)
 
 
 class SO3Task(IKLinearTask):
@@ -651,6 +700,7 @@ class QPInverseKinematics:
                 return False
             for e, sp in zip(native, specs):
                 e["sp_version"], e["gains_version"], e["weight"] = -1, e["task"]._gains_version, None if sp.weight is None else np.array(sp.weight)
+                e["fb_version"] = 0
             self._kin_dyn, self._state_version = kd, -1
         self._finalized = True
         return True
@@ -674,6 +724,9 @@ class QPInverseKinematics:
             if task._sp_len and e["sp_version"] != task._sp_version:
                 prob.set_setpoint(t, task._sp)
                 e["sp_version"] = task._sp_version
+            if task._fb_len and task._fb is not None and e.get("fb_version", 0) != task._fb_version:
+                prob.set_feedback(t, task._fb)
+                e["fb_version"] = task._fb_version
             if e["provider"] is not None:
                 w = np.asarray(e["provider"].get_output(), dtype=np.float64)   # read on every tick (:450-451)
                 if e["weight"] is None or not np.array_equal(w, e["weight"]):

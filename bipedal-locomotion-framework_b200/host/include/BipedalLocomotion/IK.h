@@ -73,6 +73,10 @@ public:
     /** robot whose A and b are materialised by update() (getA / getB); -1 = none (default when N > 1) */
     void setInspectedInstance(int i) { m_inspect = i; }
     unsigned long gainsVersion() const { return m_gainsVersion; }
+    /** doubles per robot of the exogenous feedback (0: the task uses none); uploaded with blfik_set_feedback */
+    virtual std::size_t feedbackLength() const { return 0; }
+    const std::vector<double>& feedbackBuffer() const { return m_fb; }
+    unsigned long feedbackVersion() const { return m_fbVersion; }
 
 protected:
     bool commonInitialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler, std::shared_ptr<const ParametersHandler::IParametersHandler>& ptr)
@@ -101,6 +105,21 @@ protected:
             if (instance < 0 || static_cast<std::size_t>(instance) == i)
                 for (std::size_t c = 0; c < len; c++) m_sp[i * len + c] = rec[c];
         m_spVersion++;
+    }
+    /** writes `count` doubles at `first` of the feedback record of robot `instance` (-1: every robot); `init` is the
+     *  record a fresh buffer starts from (the controllers' initial state) */
+    void storeFeedback(const double* values, std::size_t first, std::size_t count, std::ptrdiff_t instance, const std::vector<double>& init)
+    {
+        const std::size_t len = feedbackLength(), N = m_kinDyn->getBatchSize();
+        if (m_fb.size() != N * len) {
+            m_fb.resize(N * len);
+            for (std::size_t i = 0; i < N; i++)
+                for (std::size_t c = 0; c < len; c++) m_fb[i * len + c] = init[c];
+        }
+        for (std::size_t i = 0; i < N; i++)
+            if (instance < 0 || static_cast<std::size_t>(instance) == i)
+                for (std::size_t c = 0; c < count; c++) m_fb[i * len + first + c] = values[c];
+        m_fbVersion++;
     }
     int inspected() const { return m_inspect >= 0 ? m_inspect : ((m_kinDyn && m_kinDyn->getBatchSize() == 1) ? 0 : -1); }
     static bool readGain3(const ParametersHandler::IParametersHandler& h, const std::string& key, Vector3d& out)
@@ -133,8 +152,8 @@ protected:
     System::VariablesHandler::VariableDescription m_robotVelocityVariable;
     std::size_t m_nVars{0};
     bool m_isInitialized{false}, m_isValid{false}, m_isSetPointSetAtLeastOnce{false};
-    std::vector<double> m_sp;
-    unsigned long m_spVersion{0}, m_gainsVersion{0};
+    std::vector<double> m_sp, m_fb;
+    unsigned long m_spVersion{0}, m_gainsVersion{0}, m_fbVersion{0};
     int m_inspect{-1};
 };
 
@@ -151,6 +170,11 @@ public:
     bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
     bool update() override;
     bool setSetPoint(const SE3d& I_H_F, const SE3d::Tangent& mixedVelocity = SE3d::Tangent::Zero(), std::ptrdiff_t instance = -1);
+    /** SE3Task.cpp:338-366: measured pose for the controllers; each part is used only if its use_*_exogenous_feedback key is set */
+    bool setFeedback(const SE3d& I_H_F, std::ptrdiff_t instance = -1);
+    bool setFeedback(const Vector3d& I_p_F, std::ptrdiff_t instance = -1);
+    bool setFeedback(const SO3d& I_R_F, std::ptrdiff_t instance = -1);
+    std::size_t feedbackLength() const override { return (m_usePositionExogenousFeedback || m_useOrientationExogenousFeedback) ? 7 : 0; }
     std::size_t size() const override { return m_linearDoFs + 3; }
     Type type() const override { return Type::equality; }
     void setTaskControllerMode(Mode mode) { m_controllerMode = mode, m_gainsVersion++; }
@@ -165,6 +189,7 @@ private:
     std::array<bool, 3> m_mask{true, true, true};
     std::size_t m_linearDoFs{3};
     Mode m_controllerMode{Mode::Enable};
+    bool m_usePositionExogenousFeedback{false}, m_useOrientationExogenousFeedback{false};
     BLF_REGISTER_IK_TASK(SE3Task);
 };
 
@@ -176,6 +201,9 @@ public:
     bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
     bool update() override;
     bool setSetPoint(const Vector3d& position, const Vector3d& velocity = {0, 0, 0}, std::ptrdiff_t instance = -1);
+    /** CoMTask.cpp:262-273: measured CoM for the controller; used only with use_exogenous_feedback */
+    bool setFeedback(const Vector3d& feedback, std::ptrdiff_t instance = -1);
+    std::size_t feedbackLength() const override { return m_useExogenousFeedback ? 3 : 0; }
     std::size_t size() const override { return m_DoFs; }
     Type type() const override { return Type::equality; }
     bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
@@ -185,6 +213,7 @@ private:
     Vector3d m_kpLinear{0, 0, 0};
     std::array<bool, 3> m_mask{true, true, true};
     std::size_t m_DoFs{3};
+    bool m_useExogenousFeedback{false};
     BLF_REGISTER_IK_TASK(CoMTask);
 };
 

@@ -338,8 +338,37 @@ bool SE3Task::initialize(std::weak_ptr<const ParametersHandler::IParametersHandl
         log()->error("{} The size of the mask must be 3.", errorPrefix);
         return false;
     }
+    // optional, default false (SE3Task.cpp:196-214)
+    m_useOrientationExogenousFeedback = m_usePositionExogenousFeedback = false;
+    ptr->getParameter("use_orientation_exogenous_feedback", m_useOrientationExogenousFeedback);
+    ptr->getParameter("use_position_exogenous_feedback", m_usePositionExogenousFeedback);
     m_description = "SE3Task Optimal Control Element - Frame name: " + m_frameName + ".";
     m_isInitialized = true;
+    return true;
+}
+
+static const std::vector<double> kIdentityPoseFeedback{0, 0, 0, 0, 0, 0, 1};   // controllers' initial state: p = 0, q = identity
+
+bool SE3Task::setFeedback(const SE3d& I_H_F, std::ptrdiff_t instance)
+{
+    return setFeedback(I_H_F.p, instance) && setFeedback(I_H_F.R, instance);
+}
+
+bool SE3Task::setFeedback(const Vector3d& I_p_F, std::ptrdiff_t instance)
+{
+    if (!m_kinDyn) return false;
+    if (m_usePositionExogenousFeedback) storeFeedback(I_p_F.data(), 0, 3, instance, kIdentityPoseFeedback);   // ignored otherwise (:345-353)
+    return true;
+}
+
+bool SE3Task::setFeedback(const SO3d& I_R_F, std::ptrdiff_t instance)
+{
+    if (!m_kinDyn) return false;
+    if (m_useOrientationExogenousFeedback) {
+        const auto q = I_R_F.quat().coeffs();
+        const double qq[4] = {q[0], q[1], q[2], q[3]};
+        storeFeedback(qq, 3, 4, instance, kIdentityPoseFeedback);
+    }
     return true;
 }
 
@@ -375,13 +404,19 @@ bool SE3Task::update()
         }
         const double* sp = m_sp.data() + 13 * i;
         const bool on = m_controllerMode == Mode::Enable;
+        // state of the controllers: the model's pose, or the caller's measurement (SE3Task.cpp:261-268)
+        const double* fb = m_fb.size() >= 7 * static_cast<std::size_t>(i + 1) ? m_fb.data() + 7 * i : kIdentityPoseFeedback.data();
+        Vector3d pc = pose.p;
+        Quaterniond qc = pose.R.quat();
+        if (m_usePositionExogenousFeedback) pc = {fb[0], fb[1], fb[2]};
+        if (m_useOrientationExogenousFeedback) qc = Quaterniond{fb[3], fb[4], fb[5], fb[6]};
         std::size_t idx = 0;
         for (int c = 0; c < 3; c++)
             if (m_mask[c]) {
-                m_b[idx] = on ? sp[7 + c] + m_kpLinear[c] * (sp[c] - pose.p[c]) : sp[7 + c];
+                m_b[idx] = on ? sp[7 + c] + m_kpLinear[c] * (sp[c] - pc[c]) : sp[7 + c];
                 setRow(m_A, idx++, m_robotVelocityVariable.offset, J, c);
             }
-        const Vector3d w = so3Control(Quaterniond{sp[3], sp[4], sp[5], sp[6]}, pose.R.quat(), {sp[10], sp[11], sp[12]}, m_kpAngular, on);
+        const Vector3d w = so3Control(Quaterniond{sp[3], sp[4], sp[5], sp[6]}, qc, {sp[10], sp[11], sp[12]}, m_kpAngular, on);
         for (int c = 0; c < 3; c++) {
             m_b[idx + c] = w[c];
             setRow(m_A, idx + c, m_robotVelocityVariable.offset, J, 3 + c);
@@ -395,6 +430,7 @@ bool SE3Task::fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>
 {
     d = blfik_task_desc{};
     d.type = BLFIK_TASK_SE3, d.frame = m_frameIndex, d.controller_enabled = m_controllerMode == Mode::Enable;
+    d.use_position_exogenous_feedback = m_usePositionExogenousFeedback, d.use_orientation_exogenous_feedback = m_useOrientationExogenousFeedback;
     for (int c = 0; c < 3; c++) d.mask[c] = m_mask[c], d.kp_linear[c] = m_kpLinear[c], d.kp_angular[c] = m_kpAngular[c];
     return m_isInitialized;
 }
@@ -413,8 +449,18 @@ bool CoMTask::initialize(std::weak_ptr<const ParametersHandler::IParametersHandl
         log()->error("{} The size of the mask must be 3.", errorPrefix);
         return false;
     }
+    m_useExogenousFeedback = false;   // optional (CoMTask.cpp:116-123)
+    ptr->getParameter("use_exogenous_feedback", m_useExogenousFeedback);
     m_description = "CoM Task";
     m_isInitialized = true;
+    return true;
+}
+
+bool CoMTask::setFeedback(const Vector3d& feedback, std::ptrdiff_t instance)
+{
+    if (!m_kinDyn) return false;
+    static const std::vector<double> zero{0, 0, 0};
+    if (m_useExogenousFeedback) storeFeedback(feedback.data(), 0, 3, instance, zero);   // ignored otherwise (:267-270)
     return true;
 }
 
@@ -447,6 +493,8 @@ bool CoMTask::update()
             return m_isValid;
         }
         const double* sp = m_sp.data() + 6 * i;
+        if (m_useExogenousFeedback)   // CoMTask.cpp:192-195: the measured CoM (zero until the first setFeedback)
+            for (int c = 0; c < 3; c++) com[c] = m_fb.size() >= 3 * static_cast<std::size_t>(i + 1) ? m_fb[3 * i + c] : 0.0;
         std::size_t idx = 0;
         for (int c = 0; c < 3; c++)
             if (m_mask[c]) {
@@ -462,6 +510,7 @@ bool CoMTask::fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>
 {
     d = blfik_task_desc{};
     d.type = BLFIK_TASK_COM, d.frame = -1, d.controller_enabled = 1;
+    d.use_position_exogenous_feedback = m_useExogenousFeedback;
     for (int c = 0; c < 3; c++) d.mask[c] = m_mask[c], d.kp_linear[c] = m_kpLinear[c];
     return m_isInitialized;
 }
@@ -1072,7 +1121,7 @@ struct QPInverseKinematics::Impl {
         std::size_t priority{0};
         std::shared_ptr<const System::WeightProviderPort> weightProvider;
         VectorXd uploadedWeight;
-        unsigned long uploadedSetPoint{~0ul}, uploadedGains{~0ul};
+        unsigned long uploadedSetPoint{~0ul}, uploadedGains{~0ul}, uploadedFeedback{0};
     };
     std::vector<TaskEntry> tasks;   // insertion order = row order of the constraint matrix (QPInverseKinematics.cpp:201,236)
     std::unordered_map<std::string, std::size_t> index;
@@ -1241,7 +1290,7 @@ bool QPInverseKinematics::finalize(const System::VariablesHandler& handler)
             e.uploadedWeight = e.weightProvider->getOutput();
             descs[t].weight = keepVector(keep, e.uploadedWeight);
         }
-        e.uploadedSetPoint = ~0ul, e.uploadedGains = e.task->gainsVersion();
+        e.uploadedSetPoint = ~0ul, e.uploadedGains = e.task->gainsVersion(), e.uploadedFeedback = 0;
     }
     if (!m_pimpl->kinDyn) {
         log()->error("{} No KinDyn object: build the solver with QPInverseKinematics::build or call setKinDyn through a task added by addTask.", logPrefix);
@@ -1339,6 +1388,10 @@ bool QPInverseKinematics::tick(double dt, uint32_t flags)
         if (e.task->setPointLength() > 0 && e.task->setPointVersion() != e.uploadedSetPoint) {
             if (blfik_set_setpoint(prob, static_cast<int32_t>(t), e.task->setPointBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the set-point");
             e.uploadedSetPoint = e.task->setPointVersion();
+        }
+        if (e.task->feedbackLength() > 0 && e.task->feedbackVersion() != e.uploadedFeedback) {   // setFeedback(...) since the last tick
+            if (blfik_set_feedback(prob, static_cast<int32_t>(t), e.task->feedbackBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the feedback");
+            e.uploadedFeedback = e.task->feedbackVersion();
         }
     }
     auto& kd = *pimpl->kinDyn;

@@ -393,6 +393,34 @@ static void testTaskMatrices(const char* modelPath)
         REQUIRE(jt.getA()(j, 10 + 6 + j) == 1.0 && jt.getA()(j, 10 + j) == 0.0);
     }
 
+    // exogenous feedback (SE3Task.cpp:196-214, :261-268, :338-366; CoMTask.cpp:116, :192-195, :262-273): b follows the measured
+    // pose, A stays the model's Jacobian; a part whose key is off is ignored
+    {
+        auto eh = std::make_shared<StdImplementation>();
+        eh->setParameter("robot_velocity_variable_name", robotVelocity), eh->setParameter("frame_name", "l_sole");
+        eh->setParameter("kp_linear", 2.0), eh->setParameter("kp_angular", 3.0), eh->setParameter("use_position_exogenous_feedback", true);
+        SE3Task exo;
+        REQUIRE(exo.setKinDyn(kinDyn) && exo.initialize(eh) && exo.setVariablesHandler(vh) && exo.setSetPoint(desired, ff));
+        REQUIRE(exo.feedbackLength() == 7 && task.feedbackLength() == 0);
+        REQUIRE(exo.update());
+        for (int c = 0; c < 3; c++) REQUIRE(std::abs(exo.getB()[c] - (ff.linear[c] + 2.0 * desired.p[c])) < 1e-12);   // no feedback yet: p = 0
+        const Vector3d measured{0.21, 0.12, 0.03};
+        REQUIRE(exo.setFeedback(SE3d(measured, SO3d::Exp({0.3, 0.2, 0.1}))) && exo.update());
+        REQUIRE(maxAbsDiff(exo.getA(), 0, 10, J, 0) == 0.0);
+        task.setTaskControllerMode(SE3Task::Mode::Enable);
+        REQUIRE(task.update());
+        for (int c = 0; c < 3; c++) {
+            REQUIRE(std::abs(exo.getB()[c] - (ff.linear[c] + 2.0 * (desired.p[c] - measured[c]))) < 1e-12);
+            REQUIRE(std::abs(exo.getB()[3 + c] - task.getB()[3 + c]) < 1e-12);   // orientation key off: the model's orientation
+        }
+        CoMTask exoCom;
+        auto ech = std::make_shared<StdImplementation>();
+        ech->setParameter("robot_velocity_variable_name", robotVelocity), ech->setParameter("kp_linear", 4.0), ech->setParameter("use_exogenous_feedback", true);
+        REQUIRE(exoCom.setKinDyn(kinDyn) && exoCom.initialize(ech) && exoCom.setVariablesHandler(vh) && exoCom.setSetPoint({0, 0, 0.5}));
+        REQUIRE(exoCom.setFeedback({0.01, -0.02, 0.45}) && exoCom.update());
+        REQUIRE(std::abs(exoCom.getB()[2] - 4.0 * (0.5 - 0.45)) < 1e-12 && std::abs(exoCom.getB()[0] + 4.0 * 0.01) < 1e-12);
+    }
+
     // DistanceTaskTest.cpp / GravityTaskTest.cpp: A and b against the formulas of DistanceTask.cpp:196-243, GravityTask.cpp:160-199
     DistanceTask dist;
     auto dh = std::make_shared<StdImplementation>();

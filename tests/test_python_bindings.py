@@ -111,6 +111,17 @@ def test_task_initialisation_rules():
     assert se3.size() == 5
     assert se3.set_set_point(I_H_F=manif.SE3(position=[1.0, -2.0, 3.3], quaternion=[0, 0, -1, 0]), mixed_velocity=manif.SE3Tangent([0.0] * 6))
 
+    exo = blf.ik.SE3Task()
+    assert exo.set_kin_dyn(kindyn) and exo.initialize(param_handler=_handler(frame_name="r_sole", kp_linear=10.0, kp_angular=10.0,
+                                                                             use_position_exogenous_feedback=True))
+    assert exo._spec("t", 0, None).record_len(n) == 20 and se3._spec("t", 0, None).record_len(n) == 13
+    assert exo.set_feedback(I_H_F=manif.SE3(position=[0.1, 0.2, 0.3], quaternion=[0, 0, 1, 0]))
+    assert np.allclose(exo._fb[0], [0.1, 0.2, 0.3, 0, 0, 0, 1])       # the orientation key is off: that part is ignored
+    assert se3.set_feedback(I_H_F=manif.SE3.Identity()) and se3._fb is None
+    exo_com = blf.ik.CoMTask()
+    assert exo_com.set_kin_dyn(kindyn) and exo_com.initialize(param_handler=_handler(kp_linear=10.0, use_exogenous_feedback=True))
+    assert exo_com.set_feedback([0.0, 0.1, 0.5]) and np.allclose(exo_com._fb[0], [0.0, 0.1, 0.5]) and com.set_feedback([0, 0, 0]) and com._fb is None
+
     so3 = blf.ik.SO3Task()
     assert so3.set_kin_dyn(kindyn) and so3.initialize(param_handler=_handler(frame_name="chest", kp_angular=5.0))
     assert so3.set_set_point(I_R_F=manif.SO3(quaternion=[0, 0, -1, 0]), angular_velocity=manif.SO3Tangent([0.0] * 3))
@@ -399,3 +410,45 @@ def test_build_closed_loop_batch_and_fixed_base():
     kindyn.set_robot_state_batch(p, q, s)
     assert np.abs(kindyn.batch_kinematics(["l_hand_palm"], jac=False, com=False)["frame_pos"] - kh["frame_pos"]).max() < 2e-3
     assert np.abs(p - p0).max() < 1e-9
+
+
+@pytest.mark.gpu
+def test_exogenous_feedback_through_the_bindings():
+    """set_feedback (bindings/python/IK/src/SE3Task.cpp, CoMTask.cpp): with the measured pose equal to the model's the solution
+    equals the plain tasks'; a shifted CoM measurement changes it by the controller law."""
+    model = M.ergocub23()
+    n = model.n
+
+    def solve(exo, com_fb=None):
+        _, kindyn = get_kindyn(model, 2)
+        H = np.eye(4)
+        H[:3, 3] = [0.0, 0.0, 0.75]
+        assert kindyn.setRobotState(H, model.q_nominal)
+        ik = blf.ik.QPInverseKinematics()
+        assert ik.initialize(handler=_handler())
+        foot = blf.ik.SE3Task()
+        assert foot.set_kin_dyn(kindyn) and foot.initialize(param_handler=_handler(frame_name="l_sole", kp_linear=5.0, kp_angular=5.0,
+                                                                                  use_position_exogenous_feedback=exo, use_orientation_exogenous_feedback=exo))
+        com = blf.ik.CoMTask()
+        assert com.set_kin_dyn(kindyn) and com.initialize(param_handler=_handler(kp_linear=3.0, use_exogenous_feedback=exo))
+        reg = blf.ik.JointTrackingTask()
+        assert reg.set_kin_dyn(kindyn) and reg.initialize(param_handler=_handler(kp=[1.0] * n))
+        pose, c = kindyn.getWorldTransform("l_sole"), kindyn.getCenterOfMassPosition()
+        from blf_b200 import workloads as W
+        q = W.rot_to_quat(pose[None, :3, :3])[0]
+        assert foot.set_set_point(manif.SE3(position=pose[:3, 3] + [0.01, 0.0, 0.0], quaternion=q))
+        assert com.set_set_point(position=c + [0.0, 0.01, 0.0]) and reg.set_set_point(joint_position=model.q_nominal)
+        if exo:
+            assert foot.set_feedback(I_H_F=manif.SE3(position=pose[:3, 3], quaternion=q))
+            assert com.set_feedback(c if com_fb is None else c + com_fb)
+        assert ik.add_task(foot, "foot", 0) and ik.add_task(com, "com", 0) and ik.add_task(reg, "reg", 1, weight=[1.0] * n)
+        var = blf.system.VariablesHandler()
+        assert var.add_variable("robotVelocity", n + 6) and ik.finalize(var) and ik.advance()
+        return ik.get_raw_solution().copy(), kindyn.getCenterOfMassJacobian()
+
+    nu_plain, Jc = solve(False)
+    nu_exo, _ = solve(True)
+    assert np.abs(nu_plain - nu_exo).max() < 1e-9
+    shift = np.array([0.0, 0.0, 0.02])
+    nu_shift, _ = solve(True, shift)
+    assert np.abs(Jc @ (nu_shift - nu_plain) + 3.0 * shift).max() < 1e-8      # J_com nu = v_ff + kp (p_d - p_measured)
