@@ -904,3 +904,47 @@ def test_exogenous_feedback_vs_oracle(path):
     prob.tick_packed(rec, nu2, st2, dt=0.01, nchunks=2)
     assert np.array_equal(nu2, nu)
     prob.close()
+
+
+def test_full_size_c5_rollout_properties():
+    """BASELINE.json config 5 at its per-GPU size: 8,192 ergoCubs x 1,000 closed-loop ticks at 1 kHz in ONE launch, sinusoidal
+    CoM / chest trajectories generated on the device, warm start.  Size-independent properties: quaternions stay unit, the
+    joints respect the velocity limits on the last tick and their position limits throughout (the limit task is a hard
+    constraint), the feet -- whose targets stand still -- do not drift, and the CoM follows its moving target."""
+    w = W.config(5)
+    N, NT = 8192, 1000
+    inp = W.synth_inputs(w, N, 5)
+    rng = np.random.default_rng(3)
+    period = 2.0
+    amp_com, amp_chest = [0.02, 0.015, 0.01, 0, 0, 0], [0, 0, 0, 0.08, 0.05, -0.06]
+    ph_com, ph_chest = rng.uniform(0, 2 * np.pi, N), rng.uniform(0, 2 * np.pi, N)
+    model, prob = make(w.model, w.tasks, N)
+    prob.set_inputs(inp)
+    prob.set_setpoint_trajectory(0, amp_com, period, ph_com)
+    prob.set_setpoint_trajectory(5, amp_chest, period, ph_chest)
+    k0 = prob.kinematics([w.tasks[1].frame, w.tasks[2].frame], jac=False, com=True)
+    prob.tick(NT, w.dt, integrate=True, warm_start=True)
+    assert abs(prob.time - NT * w.dt) < 1e-9
+    p, q, s = prob.get_state()
+    nu = prob.get_output()
+    st, it = prob.get_status()
+    good = st == 0
+    assert good.mean() > 0.995
+    assert np.abs(np.linalg.norm(q, axis=1) - 1.0).max() < 1e-12
+    assert np.all(np.isfinite(nu)) and np.abs(nu[good, 6:]).max() <= 2.0 + 1e-7
+    m = w.model
+    assert np.all(s[good] <= m.q_upper + 1e-6) and np.all(s[good] >= m.q_lower - 1e-6)
+    k1 = prob.kinematics([w.tasks[1].frame, w.tasks[2].frame], jac=False, com=True)
+    # feet: hard SE3 tasks with constant targets (the targets were the initial poses +- a few cm): they converge and stay
+    tgt = np.stack([inp.setpoints[1][:, :3], inp.setpoints[2][:, :3]], axis=1)
+    assert np.abs(k1["frame_pos"][good] - tgt[good]).max() < 2e-3
+    # CoM (x, y, z masked as in the workload): target at t_end
+    t_end = NT * w.dt
+    com_tgt = inp.setpoints[0][:, :3] + np.asarray(amp_com[:3]) * np.sin(2 * np.pi / period * t_end + ph_com)[:, None]
+    mask = np.array(w.tasks[0].mask, dtype=bool)
+    # kp = 2 /s and 1 s of simulated time: the initial offset decays to exp(-2) = 13.5 %, the feed-forward tracks the motion
+    com_tgt0 = inp.setpoints[0][:, :3] + np.asarray(amp_com[:3]) * np.sin(ph_com)[:, None]
+    e0 = np.abs((k0["com"] - com_tgt0)[good][:, mask]).max()
+    assert np.abs((k1["com"] - com_tgt)[good][:, mask]).max() < 0.15 * e0 + 5e-4
+    assert np.abs(k1["com"] - k0["com"]).max() > 1e-3          # and it did move
+    prob.close()
