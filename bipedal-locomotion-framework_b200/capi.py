@@ -38,7 +38,7 @@ EXPORTS = [
     "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state", "blfik_tick_host",
     "blfik_packed_record_len", "blfik_packed_offset", "blfik_tick_packed",
     "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time", "blfik_set_limits",
-    "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len",
+    "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk",
 ]
 
 
@@ -274,6 +274,13 @@ class Problem:
         a, ph = _f64(np.asarray(amplitude, dtype=np.float64).reshape(6)), _f64(phase)
         self.L.blfik_set_setpoint_trajectory.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_double, C.c_void_p, C.c_int32]
         _check(self.L.blfik_set_setpoint_trajectory(self.handle, int(task), a.ctypes.data, float(period), ph.ctypes.data, MEM_HOST))
+
+    def set_setpoint_minimum_jerk(self, task: int, target, duration: float):
+        """minimum-jerk move of the task's set-point from its stored value to ``target`` [N, setpoint_len] over ``duration`` s,
+        evaluated on the device (SO3Planner / two-knot QuinticSpline semantics); duration <= 0 switches it off"""
+        tg = None if target is None else _f64(target)
+        self.L.blfik_set_setpoint_minimum_jerk.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_double, C.c_int32]
+        _check(self.L.blfik_set_setpoint_minimum_jerk(self.handle, int(task), None if tg is None else tg.ctypes.data, float(duration), MEM_HOST))
 
     def set_time(self, t: float):
         self.L.blfik_set_time.argtypes = [C.c_void_p, C.c_double]

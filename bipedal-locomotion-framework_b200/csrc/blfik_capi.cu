@@ -188,6 +188,8 @@ struct HostTask {
     int fb_len = 0;   // exogenous feedback behind the set-point: 7 (SE3: p, q), 3 (CoM: p) or 0
     double traj_amp[6] = {0, 0, 0, 0, 0, 0}, traj_omega = 0.0;
     double* d_traj_phase = nullptr;
+    double* d_mj_target = nullptr;   // minimum-jerk generator: target set-points [N][set-point length]
+    double mj_t0 = 0.0, mj_T = 0.0;  // mj_T == 0: off
     bool setpoint_set = false;
     double* d_setpoint = nullptr;
     double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
@@ -474,6 +476,7 @@ static int refresh_tasks(blfik_problem* p)
         d.fb_off = h.sp_len - h.fb_len;
         d.traj_phase = h.d_traj_phase, d.traj_omega = h.d_traj_phase ? h.traj_omega : 0.0;
         for (int c = 0; c < 6; c++) d.traj_amp[c] = h.traj_amp[c];
+        d.mj_target = h.mj_T > 0.0 ? h.d_mj_target : nullptr, d.mj_t0 = h.mj_t0, d.mj_T = h.mj_T;
         for (int c = 0; c < 9; c++) d.Fr[c] = (c % 4 == 0) ? 1.0 : 0.0;
         for (int c = 0; c < 3; c++) d.Fp[c] = 0.0;
         d.flink2 = -1, d.thr = h.d.distance_threshold > 0 ? h.d.distance_threshold : 0.001;
@@ -818,6 +821,30 @@ extern "C" int32_t blfik_record_len(const blfik_problem* p, int32_t t)
     return p->tasks[t].sp_len;
 }
 
+extern "C" int blfik_set_setpoint_minimum_jerk(blfik_problem* p, int32_t t, const double* target, double duration, int32_t mem)
+{
+    CHECK_P(p, "blfik_set_setpoint_minimum_jerk");
+    CHECK_TASK(p, t, "blfik_set_setpoint_minimum_jerk");
+    HostTask& h = p->tasks[t];
+    if (h.d.type != BLFIK_TASK_SE3 && h.d.type != BLFIK_TASK_SO3 && h.d.type != BLFIK_TASK_R3 && h.d.type != BLFIK_TASK_COM)
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_minimum_jerk] task %d is not an SE3 / SO3 / R3 / CoM task", t);
+    if (!(duration > 0)) {   // SO3Planner::setRotations rejects a non-positive duration (SO3Planner.tpp:118-122); here it switches the generator off
+        h.mj_T = 0.0;
+        p->tasks_dirty = true;
+        return BLFIK_OK;
+    }
+    if (!target) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_minimum_jerk] null target");
+    if (!h.setpoint_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_set_setpoint_minimum_jerk] the initial set point of task %d has not been set", t);
+    const int base = h.sp_len - h.fb_len;
+    int rc;
+    if (!h.d_mj_target && (rc = dev_alloc(p, (size_t)p->N * base, &h.d_mj_target))) return rc;
+    CU(cudaMemcpyAsync(h.d_mj_target, target, (size_t)p->N * base * sizeof(double), kind_in(mem), p->stream));
+    h.mj_t0 = p->time, h.mj_T = duration;
+    h.traj_omega = 0.0;   // one generator per task
+    p->tasks_dirty = true;
+    return BLFIK_OK;
+}
+
 extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const double* amplitude, double period, const double* phase, int32_t mem)
 {
     CHECK_P(p, "blfik_set_setpoint_trajectory");
@@ -836,6 +863,7 @@ extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const 
     CU(cudaMemcpyAsync(h.d_traj_phase, phase, (size_t)p->N * sizeof(double), kind_in(mem), p->stream));
     for (int c = 0; c < 6; c++) h.traj_amp[c] = amplitude[c];
     h.traj_omega = 6.283185307179586476925286766559 / period;
+    h.mj_T = 0.0;   // one generator per task
     p->tasks_dirty = true;
     return BLFIK_OK;
 }

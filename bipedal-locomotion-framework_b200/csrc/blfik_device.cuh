@@ -62,6 +62,10 @@ struct DevTask {
     double Fp2[3];           // DistanceTask: origin of the reference frame in its link
     double thr;              // DistanceTask: distance_numeric_threshold
     int pk_off;              // offset of this task's set-point inside a packed input record
+    // optional minimum-jerk point-to-point generator (Planners::SO3Planner with zero boundary velocity / acceleration, and
+    // the quintic between two knots for positions): from the stored set-point to mj_target over [mj_t0, mj_t0 + mj_T]
+    const double* mj_target;    // device [N][set-point length], nullptr: off
+    double mj_t0, mj_T;
     int exo_pos, exo_ori;    // exogenous feedback (SE3Task.cpp:261-268, CoMTask.cpp:192-195): controller state from the record
     int fb_off;              // where the feedback p(3) [q(4)] sits inside the record (= the set-point length)
 };
@@ -476,6 +480,43 @@ __device__ __forceinline__ void k1_angmom(const DevModel& m, const WM& w, const 
 // `spl` receives the full record (13 / 7 / 6 doubles); returns the pointer the control law should read.
 __device__ __forceinline__ const double* traj_eval(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
 {
+    if (tk.mj_target && sp) {
+        // s(tau) = 10 tau^3 - 15 tau^4 + 6 tau^5 (SO3Planner.tpp:96-105 with zero boundary conditions), time clamped to the
+        // segment as SO3Planner::advance does (:289-292): x(t) = x0 + s (x1 - x0), R(t) = Exp(s Log(R1 R0^-1)) R0 -- the
+        // inertial-frame ("Right trivialization") form that matches the MIXED angular velocity, w(t) = sdot Log(R1 R0^-1)
+        const int base = tk.fb_off;   // set-point length
+        for (int c = 0; c < base && c < 13; c++) spl[c] = sp[c];
+        const double* tg = tk.mj_target + (size_t)robot * base;
+        double tau = (t - tk.mj_t0) / tk.mj_T;
+        tau = fmin(fmax(tau, 0.0), 1.0);
+        const double t2 = tau * tau, t3 = t2 * tau;
+        const double sv = t3 * (10.0 - 15.0 * tau + 6.0 * t2);
+        const double sd = (tau > 0.0 && tau < 1.0) ? 30.0 * t2 * (1.0 - 2.0 * tau + t2) / tk.mj_T : 0.0;
+        const bool lin = tk.type == T_SE3 || tk.type == T_COM || tk.type == T_R3;
+        const int qo = tk.type == T_SE3 ? 3 : 0, vo = tk.type == T_SE3 ? 7 : 3, wo = tk.type == T_SE3 ? 10 : 4;
+        if (lin) {
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                const double d = tg[c] - sp[c];
+                spl[c] = sp[c] + sv * d, spl[vo + c] = sp[vo + c] + sd * d;
+            }
+        }
+        if (tk.type == T_SE3 || tk.type == T_SO3) {
+            const double q0[4] = {sp[qo], sp[qo + 1], sp[qo + 2], sp[qo + 3]}, q0i[4] = {-q0[0], -q0[1], -q0[2], q0[3]};
+            const double q1[4] = {tg[qo], tg[qo + 1], tg[qo + 2], tg[qo + 3]};
+            double qe[4], dist[3], dq[4], qn[4];
+            quat_mul(q1, q0i, qe);
+            so3_log(qe, dist);
+            const double ph[3] = {sv * dist[0], sv * dist[1], sv * dist[2]};
+            so3_exp(ph, dq);
+            quat_mul(dq, q0, qn);
+#pragma unroll
+            for (int c = 0; c < 4; c++) spl[qo + c] = qn[c];
+#pragma unroll
+            for (int c = 0; c < 3; c++) spl[wo + c] = sp[wo + c] + sd * dist[c];
+        }
+        return spl;
+    }
     if (tk.traj_omega == 0.0 || !sp) return sp;
     for (int c = 0; c < tk.sp_len && c < 13; c++) spl[c] = sp[c];
     double sn, cs;

@@ -193,6 +193,17 @@ int32_t blfik_record_len(const blfik_problem* problem, int32_t task);
  * integrating tick (blfik_set_time / blfik_get_time).                                                      */
 int blfik_set_setpoint_trajectory(blfik_problem* problem, int32_t task, const double* amplitude,
                                   double period, const double* phase, int32_t mem);
+
+/* Minimum-jerk point-to-point set-point producer on the device: what the reference's callers obtain from
+ * Planners::SO3Planner<Right> for rotations (SO3Planner.tpp:96-105, 205-252 with zero boundary velocity and acceleration)
+ * and from a two-knot QuinticSpline for positions, and then pass to setSetPoint every period.  From the stored set-point
+ * x_0 (blfik_set_setpoint) to target [N][blfik_setpoint_len] over `duration` seconds starting at the problem's current
+ * time, with s(tau) = 10 tau^3 - 15 tau^4 + 6 tau^5:
+ *     p(t) = p_0 + s (p_1 - p_0),  R(t) = Exp(s Log(R_1 R_0^-1)) R_0,  feed-forward += sdot (p_1 - p_0) / sdot Log(R_1 R_0^-1);
+ * before the start and after the end the time is clamped (SO3Planner::advance, :289-292).  Only the pose part of
+ * `target` is read.  duration <= 0 switches it off; it replaces a sinusoidal generator on the same task and vice versa. */
+int blfik_set_setpoint_minimum_jerk(blfik_problem* problem, int32_t task, const double* target,
+                                    double duration, int32_t mem);
 int blfik_set_time(blfik_problem* problem, double t);
 double blfik_get_time(const blfik_problem* problem);
 

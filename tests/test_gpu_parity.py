@@ -948,3 +948,88 @@ def test_full_size_c5_rollout_properties():
     assert np.abs((k1["com"] - com_tgt)[good][:, mask]).max() < 0.15 * e0 + 5e-4
     assert np.abs(k1["com"] - k0["com"]).max() > 1e-3          # and it did move
     prob.close()
+
+
+def _min_jerk_setpoint(ty, sp0, tg, tau, T_):
+    """host restatement of the on-device generator (SO3Planner.tpp:96-105, 205-252 with zero boundary conditions)"""
+    tau = np.clip(tau, 0.0, 1.0)
+    sv = 10 * tau ** 3 - 15 * tau ** 4 + 6 * tau ** 5
+    sd = 30 * tau ** 2 * (1 - tau) ** 2 / T_ if 0.0 < tau < 1.0 else 0.0
+    out = sp0.copy()
+    if ty in (T.TASK_SE3, T.TASK_COM, T.TASK_R3):
+        vo = 7 if ty == T.TASK_SE3 else 3
+        d = tg[:, :3] - sp0[:, :3]
+        out[:, :3] = sp0[:, :3] + sv * d
+        out[:, vo:vo + 3] = sp0[:, vo:vo + 3] + sd * d
+    if ty in (T.TASK_SE3, T.TASK_SO3):
+        qo, wo = (3, 10) if ty == T.TASK_SE3 else (0, 4)
+        q0, q1 = sp0[:, qo:qo + 4], tg[:, qo:qo + 4]
+        q0i = q0 * np.array([-1.0, -1.0, -1.0, 1.0])
+        from helpers import rot_log
+        dist = np.array([rot_log(W.quat_to_rot(W.quat_mul(q1[i:i + 1], q0i[i:i + 1]))[0]) for i in range(len(q0))])
+        out[:, qo:qo + 4] = W.quat_mul(W.so3_exp(sv * dist), q0)
+        out[:, wo:wo + 3] = sp0[:, wo:wo + 3] + sd * dist
+    return out
+
+
+@pytest.mark.parametrize("path", PATHS)
+def test_minimum_jerk_setpoint_generator(path):
+    """blfik_set_setpoint_minimum_jerk: the CoM, a foot (SE3) and the chest (SO3) move from their stored set-points to new
+    targets along s(tau) = 10 tau^3 - 15 tau^4 + 6 tau^5 (Planners::SO3Planner / two-knot QuinticSpline with zero boundary
+    velocity and acceleration), evaluated on the device.  The oracle gets the same set-points evaluated on the host and
+    re-solves every tick from the GPU's state; after the end the set-point rests at the target; one multi-tick launch
+    reproduces the tick-by-tick run."""
+    w = W.config(5)
+    N, NT, dur = 16, 40, 0.03
+    dt = w.dt
+    inp = W.synth_inputs(w, N, 5)
+    rng = np.random.default_rng(23)
+    moved = {0: None, 1: None, 5: None}
+    for ti in moved:
+        tg = inp.setpoints[ti].copy()
+        ty = w.tasks[ti].type
+        if ty in (T.TASK_SE3, T.TASK_COM):
+            tg[:, :3] += rng.uniform(-0.002, 0.002, (N, 3))       # 2 mm in 30 ms: peak 0.12 m/s, inside the velocity limits
+        if ty in (T.TASK_SE3, T.TASK_SO3):
+            qo = 3 if ty == T.TASK_SE3 else 0
+            tg[:, qo:qo + 4] = W.quat_mul(W.so3_exp(rng.uniform(-0.01, 0.01, (N, 3))), tg[:, qo:qo + 4])
+        moved[ti] = tg
+
+    def setpoints_at(t):
+        sps = [None if sp is None else sp.copy() for sp in inp.setpoints]
+        for ti, tg in moved.items():
+            sps[ti] = _min_jerk_setpoint(w.tasks[ti].type, inp.setpoints[ti], tg, t / dur, dur)
+        return sps
+
+    model, prob = make(w.model, w.tasks, N, path)
+    _, whole = make(w.model, w.tasks, N, path)
+    with pytest.raises(capi.BlfikError):
+        prob.set_setpoint_minimum_jerk(0, moved[0], dur)          # the initial set-point comes first
+    for pr in (prob, whole):
+        pr.set_inputs(inp)
+        for ti, tg in moved.items():
+            pr.set_setpoint_minimum_jerk(ti, tg, dur)
+    with pytest.raises(capi.BlfikError):
+        prob.set_setpoint_minimum_jerk(6, inp.setpoints[6], dur)  # joint tasks have no such generator
+    o = Oracle(w.model, w.tasks)
+    p, q, s = inp.base_pos.copy(), inp.base_quat.copy(), inp.s.copy()
+    for k in range(NT):
+        pr_, qr_, sr_ = p.copy(), q.copy(), s.copy()
+        nur, str_, _ = o.tick_batch(pr_, qr_, sr_, setpoints_at(k * dt), dt_integrate=dt)
+        prob.tick(1, dt, integrate=True, warm_start=True)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        p, q, s = prob.get_state()
+        ok = (st == 0) & (str_ == 0)
+        assert ok.mean() > 0.9
+        assert np.abs(nu - nur)[ok].max() <= TOL_NU
+    assert NT * dt > dur          # the last ticks ran with the set-point resting at the target
+    end = setpoints_at(NT * dt)
+    for ti, tg in moved.items():
+        assert np.abs(end[ti] - tg).max() < 1e-12
+    whole.tick(NT, dt, integrate=True, warm_start=True)
+    pw, qw, sw = whole.get_state()
+    assert np.abs(sw - s).max() < 1e-9 and np.abs(pw - p).max() < 1e-9
+    # switching the generator off leaves the stored (initial) set-point in force
+    prob.set_setpoint_minimum_jerk(0, None, 0.0)
+    prob.close(), whole.close()
