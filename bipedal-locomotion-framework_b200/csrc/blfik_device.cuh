@@ -478,7 +478,15 @@ __device__ __forceinline__ void k1_angmom(const DevModel& m, const WM& w, const 
 // that feed setSetPoint): x_d(t) = x_0 + A sin(w t + phi_i), feed-forward += A w cos(w t + phi_i); orientations move by
 // the world-frame rotation Exp(A_ang sin(.)) about a fixed axis, whose angular velocity is exactly A_ang w cos(.).
 // `spl` receives the full record (13 / 7 / 6 doubles); returns the pointer the control law should read.
+__device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long long robot, double t, const double* sp, double* spl);
+// The generators are rare and long: the common case (none attached) stays a test and a branch, the evaluation itself is an
+// out-of-line call so that its registers do not weigh on the tick kernels.
 __device__ __forceinline__ const double* traj_eval(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
+{
+    if ((!tk.mj_target && tk.traj_omega == 0.0) || !sp) return sp;
+    return traj_eval_slow(tk, robot, t, sp, spl);
+}
+__device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
 {
     if (tk.mj_target && sp) {
         // s(tau) = 10 tau^3 - 15 tau^4 + 6 tau^5 (SO3Planner.tpp:96-105 with zero boundary conditions), time clamped to the

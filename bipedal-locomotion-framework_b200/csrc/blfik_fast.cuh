@@ -671,14 +671,11 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
 #pragma unroll
                         for (int c = 0; c < 3; c++) wff[c] = sp[wo + c];
                     }
-                    if (tk.type == T_SE3 && tk.exo_ori) {   // SE3Task.cpp:261-265: measured orientation
+                    if (tk.type == T_SE3 && tk.exo_ori) {   // SE3Task.cpp:261-265: measured orientation (Rf is not used again for an SE3 task)
                         const double qf[4] = {sp0[tk.fb_off + 3], sp0[tk.fb_off + 4], sp0[tk.fb_off + 5], sp0[tk.fb_off + 6]};
-                        double Rc[9];
-                        quat_to_rot(qf, Rc);
-                        so3_control(Rc, qd, wff, tk.kp_ang, tk.enabled != 0, ba);
-                    } else {
-                        so3_control(Rf, qd, wff, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), ba);
+                        quat_to_rot(qf, Rf);
                     }
+                    so3_control(Rf, qd, wff, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), ba);
                     double aux[3] = {0.0, 0.0, 0.0};
                     if (tk.type == T_DISTANCE) {   // DistanceTask.cpp:178-229: u = d / max(thr, |d|), b = kp (d_des - |d|)
                         if (tk.flink2 >= 0) {
