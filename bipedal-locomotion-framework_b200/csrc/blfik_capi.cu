@@ -319,10 +319,10 @@ static FastLayout make_fast_layout(int nl)
     return F;
 }
 
-template <int NV, int KP>
+template <int NV, int KP, bool AM = false>
 static void pick_fast(blfik_problem* p)
 {
-    p->fast_kernel = blfik_tick_fast_kernel<NV, KP>;
+    p->fast_kernel = blfik_tick_fast_kernel<NV, KP, AM>;
     p->fast_wpb = FastDims<NV, KP>::WARPS;   // the kernel's launch bound
     p->F = make_fast_layout<NV, KP>(p->n + 1);
     // the control-law buffer ([ntasks][12]) lives in the U region during K2
@@ -622,9 +622,12 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         const int nv = p->nv, K = p->K;
         bool angmom = false;
         for (const HostTask& h : p->tasks) angmom |= h.d.type == BLFIK_TASK_ANGULAR_MOMENTUM;
-        // the centroidal momentum rows exist in the generic kernel only (the task is rare)
-        if (nv <= 32 && K <= 32 && !angmom) {
-            if (nv == 29) {
+        if (nv <= 32 && K <= 32) {
+            if (angmom) {
+                // the centroidal momentum rows live in their own instantiations (largest row count only: the task is rare)
+                if (nv == 29) pick_fast<29, 32, true>(p);
+                else pick_fast<32, 32, true>(p);
+            } else if (nv == 29) {
                 if (K <= 16) pick_fast<29, 16>(p);
                 else if (K <= 18) pick_fast<29, 18>(p);
                 else if (K <= 30) pick_fast<29, 30>(p);
@@ -638,7 +641,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
             p->F.sh_model = 0;
             p->F.sh_tasks = p->F.sh_model_len;
             p->F.sh_total = p->F.sh_tasks + (int)(((size_t)ntasks * sizeof(DevTask) + 15) / 16 * 2);
-            for (const HostTask& h : p->tasks) p->has_com |= h.d.type == BLFIK_TASK_COM;
+            for (const HostTask& h : p->tasks) p->has_com |= h.d.type == BLFIK_TASK_COM || h.d.type == BLFIK_TASK_ANGULAR_MOMENTUM;   // both need the CoM
             const size_t fshared = (size_t)p->F.sh_total * sizeof(double);
             const size_t fper = (size_t)p->F.total * sizeof(double);
             int fw = (int)((sm_total - 3072 - fshared) / (fper + 64));

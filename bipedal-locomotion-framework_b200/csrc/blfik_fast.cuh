@@ -405,6 +405,53 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
     return ok;
 }
 
+// Column `lane` of the angular rows of the centroidal momentum matrix (AngularMomentumTask.cpp:137-185; same formula as
+// k1_angmom of the generic kernel): sum over the links distal to the DoF of I_k^W a + m_k (c_k - c) x (a x (c_k - o)).
+// Rare task, long loop: kept out of line so that its registers do not weigh on the tick kernel.
+__device__ __noinline__ void fast_angmom_column(const double* s_link, const double* inertia, const unsigned long long* s_anc,
+                                                const int* s_lod, const double* linkR, const double* linkP,
+                                                const double* axisW, const double* mcw, const double* com, int nl, int lane,
+                                                double* col)
+{
+    col[0] = col[1] = col[2] = 0.0;
+    if (lane < 3) return;   // a translation of the whole robot carries no momentum about its centre of mass
+    double a[3] = {0.0, 0.0, 0.0}, o[3];
+    int j = -1;
+    if (lane < 6) {
+        a[lane - 3] = 1.0;
+        o[0] = linkP[0], o[1] = linkP[1], o[2] = linkP[2];
+    } else {
+        j = lane - 6;
+        const int kj = s_lod[j];
+        for (int i = 0; i < 3; i++) a[i] = axisW[3 * kj + i], o[i] = linkP[3 * kj + i];
+    }
+    for (int k = 0; k < nl; k++) {
+        if (j >= 0 && !((s_anc[k] >> j) & 1ull)) continue;
+        const double mk = s_link[20 * k + 18];
+        const double* R = linkR + 9 * k;
+        if (inertia) {
+            const double* I6 = inertia + 6 * k;
+            double al[3], il[3], iw[3];
+            mat3T_vec(R, a, al);
+            il[0] = I6[0] * al[0] + I6[1] * al[1] + I6[2] * al[2];
+            il[1] = I6[1] * al[0] + I6[3] * al[1] + I6[4] * al[2];
+            il[2] = I6[2] * al[0] + I6[4] * al[1] + I6[5] * al[2];
+            mat3_vec(R, il, iw);
+            col[0] += iw[0], col[1] += iw[1], col[2] += iw[2];
+        }
+        if (mk > 0.0) {
+            const double inv = 1.0 / mk;
+            const double ck[3] = {mcw[3 * k] * inv, mcw[3 * k + 1] * inv, mcw[3 * k + 2] * inv};
+            const double r[3] = {ck[0] - o[0], ck[1] - o[1], ck[2] - o[2]};
+            const double d[3] = {ck[0] - com[0], ck[1] - com[1], ck[2] - com[2]};
+            double v[3], t[3];
+            cross3(a, r, v);
+            cross3(d, v, t);
+            col[0] += mk * t[0], col[1] += mk * t[1], col[2] += mk * t[2];
+        }
+    }
+}
+
 // Next `cnt` robots for a team (index relative to FP.T.first); in the streaming-input mode the caller also waits until
 // their records are on the device.  A time-out ends the launch: every later fetch returns "past the end".
 __device__ __forceinline__ int fetch_robots(const FastParams& FP, int cnt, int count_total)
@@ -421,7 +468,9 @@ __device__ __forceinline__ int fetch_robots(const FastParams& FP, int cnt, int c
     return v;
 }
 
-template <int NV, int KP>
+// AM: the problem holds an AngularMomentumTask.  A separate instantiation, because even an out-of-line call in the row
+// generation costs the common kernels 8 % (registers live across the call are spilled: 1.32 -> 1.43 ms on C3).
+template <int NV, int KP, bool AM = false>
 __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fast_kernel(const FastParams FP)
 {
     constexpr int LDB = FastDims<NV, KP>::LDB;
@@ -640,7 +689,7 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                     const double* sp = traj_eval(tk, robot, P.t0 + tick * P.dt, sp0, spl);
                     const bool has_lin = tk.type == T_SE3 || tk.type == T_R3 || tk.type == T_COM, has_ang = tk.type == T_SE3 || tk.type == T_SO3;
                     double Rf[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, pf[3] = {com[0], com[1], com[2]};
-                    if (tk.type != T_COM) {
+                    if (tk.type != T_COM && tk.type != T_ANGMOM) {
                         const int Lk = tk.flink;
                         double Rl[9], off[3];
 #pragma unroll
@@ -690,6 +739,8 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                         bl[0] = tk.kp_lin[0] * (sp[0] - d);
 #pragma unroll
                         for (int c = 0; c < 3; c++) ba[c] = dv[c] * inv;   // the unit direction, reused by the row generation
+                    } else if (tk.type == T_ANGMOM) {    // AngularMomentumTask.cpp:187-210: b is the desired momentum itself
+                        bl[0] = sp[0], bl[1] = sp[1], bl[2] = sp[2];
                     } else if (tk.type == T_GRAVITY) {   // GravityTask.cpp:149-185
                         double zb[3] = {sp[0], sp[1], sp[2]}, fb[3] = {sp[3], sp[4], sp[5]}, z[3], ff[3];
                         const double zn = rsqrt(zb[0] * zb[0] + zb[1] * zb[1] + zb[2] * zb[2]);
@@ -735,6 +786,8 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                         double lin[3] = {0.0, 0.0, 0.0}, ang[3] = {0.0, 0.0, 0.0};
                         if (tk.type == T_COM) {
                             lin[0] = comcol[0], lin[1] = comcol[1], lin[2] = comcol[2];
+                        } else if (AM && tk.type == T_ANGMOM) {
+                            if constexpr (AM) fast_angmom_column(s_link, m.inertia, s_anc, s_lod, linkR, linkP, axisW, mcw, com, nl, lane, lin);
                         } else {
                             const double pf[3] = {tbuf[12 * t], tbuf[12 * t + 1], tbuf[12 * t + 2]};
                             if (lane < 3) {

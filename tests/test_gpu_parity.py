@@ -756,10 +756,11 @@ def test_problems_of_different_sizes_coexist():
         big.close(), small.close(), tree.close()
 
 
+@pytest.mark.parametrize("path", PATHS)
 @pytest.mark.parametrize("hard", [True, False])
-def test_angular_momentum_task_vs_oracle(hard):
-    """AngularMomentumTask.cpp:137-210 in the tick (generic kernel: the centroidal momentum rows are evaluated column by
-    column over the links distal to each DoF, the oracle accumulates them link by link): rows within 1e-12, nu within 1e-5,
+def test_angular_momentum_task_vs_oracle(hard, path):
+    """AngularMomentumTask.cpp:137-210 in the tick (both kernels evaluate the centroidal momentum rows column by column over
+    the links distal to each DoF, the oracle accumulates them link by link): rows within 1e-12, nu within 1e-5,
     and the returned velocity carries the requested angular momentum."""
     m = M.ergocub23()
     n, N = m.n, 64
@@ -771,8 +772,8 @@ def test_angular_momentum_task_vs_oracle(hard):
     p0, q0, s0 = inp.base_pos, inp.base_quat, inp.s
     rng = np.random.default_rng(8)
     sps = [inp.setpoints[2], inp.setpoints[1], inp.setpoints[0], rng.normal(0, 0.05, (N, 3)), inp.setpoints[6]]
-    model, prob = make(m, tasks, N)
-    assert prob.kernel_path == 1                       # the register-resident kernel does not carry this task
+    model, prob = make(m, tasks, N, path)
+    assert prob.kernel_path == (2 if path == 0 else 1)
     prob.set_state(p0, q0, s0)
     for t, sp in enumerate(sps):
         prob.set_setpoint(t, sp)
