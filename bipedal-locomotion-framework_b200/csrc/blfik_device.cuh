@@ -696,17 +696,21 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
 // recomputes the pivot redundantly so that one __syncwarp per column suffices.  Pivots below
 // `floor_` are clamped (rank-deficient equality rows behave like OSQP's delta-regularised ones).
 // Returns false if a pivot is not finite.
-__device__ __forceinline__ bool chol_inplace(double* M, int n, int ld, double floor_, int lane)
+// drop = true: a row whose pivot falls below the floor depends on the previous ones; it is left out (zero column, zero
+// diagonal) and the callers skip it.
+__device__ __forceinline__ bool chol_inplace(double* M, int n, int ld, double floor_, int lane, bool drop = false)
 {
     bool ok = true;
     for (int k = 0; k < n; k++) {
         double piv = M[k * ld + k];
         for (int j = 0; j < k; j++) piv -= M[k * ld + j] * M[k * ld + j];
+        bool dropped = false;
         if (!(piv > floor_)) {
             if (!(piv == piv)) ok = false;
             piv = floor_;
+            dropped = drop;
         }
-        const double d = sqrt(piv), inv = 1.0 / d;
+        const double d = dropped ? 0.0 : sqrt(piv), inv = dropped ? 0.0 : 1.0 / d;
         double vals[2];
         int cnt = 0;
         for (int i = lane; i < n; i += 32, cnt++) {
@@ -788,13 +792,14 @@ __device__ __forceinline__ bool qp_setup(const Layout& L, const WM& w, double si
         smax = warp_max(smax);
         __syncwarp();
         // S6: S = Ls Ls'
-        ok = chol_inplace(w.Ss, me, LDE, 1e-14 * smax + 1e-300, lane) && ok;
+        ok = chol_inplace(w.Ss, me, LDE, 1e-14 * smax + 1e-300, lane, true) && ok;   // dependent equality rows are dropped
         // S7: V = Y Ls^-T, row i by lane i (in place)
         for (int i = lane; i < nv; i += 32) {
             for (int r = 0; r < me; r++) {
                 double v = w.Ym[i * LDE + r];
                 for (int c = 0; c < r; c++) v -= w.Ss[r * LDE + c] * w.Ym[i * LDE + c];
-                w.Ym[i * LDE + r] = v / w.Ss[r * LDE + r];
+                const double dg = w.Ss[r * LDE + r];
+                w.Ym[i * LDE + r] = dg != 0.0 ? v / dg : 0.0;
             }
         }
         __syncwarp();
@@ -821,8 +826,17 @@ __device__ __forceinline__ bool qp_setup(const Layout& L, const WM& w, double si
     // wb = Ls^-1 b (forward substitution, one entry finalised per step)
     for (int r = lane; r < me; r += 32) w.wb[r] = bvec[r];
     __syncwarp();
+    // a dropped row must also be consistent: what is left of its right-hand side has to vanish (else status 2)
+    double bmax = 0.0;
+    for (int r = lane; r < me; r += 32) bmax = fmax(bmax, fabs(bvec[r]));
+    const double btol = 1e-8 * (1.0 + warp_max(bmax));
+    bool inconsistent = false;
     for (int c = 0; c < me; c++) {
-        if (lane == (c & 31)) w.wb[c] = w.wb[c] / w.Ss[c * LDE + c];
+        if (lane == (c & 31)) {
+            const double dg = w.Ss[c * LDE + c];
+            if (dg == 0.0 && fabs(w.wb[c]) > btol) inconsistent = true;
+            w.wb[c] = dg != 0.0 ? w.wb[c] / dg : 0.0;
+        }
         __syncwarp();
         const double wc = w.wb[c];
         for (int r = lane; r < me; r += 32)
@@ -835,6 +849,7 @@ __device__ __forceinline__ bool qp_setup(const Layout& L, const WM& w, double si
         w.xb[i] = v;
     }
     __syncwarp();
+    if (__any_sync(kFull, inconsistent)) ok = false;
     return ok;
 }
 

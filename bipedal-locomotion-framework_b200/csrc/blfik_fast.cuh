@@ -241,6 +241,7 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
     constexpr int LDG = FastDims<NV, KP>::LDG;
     double* Gs = Us;   // G by columns, consumed before U is written
     bool ok = true;
+    [[maybe_unused]] bool clamped = false;   // KP == 32 only (no spare lane for the riding right-hand side)
     // ---- G = E + (B D^-1) B' on the FP64 tensor path (DMMA m8n8k4): ncu showed this contraction issue-bound
     // (34 % issue utilisation, 22 % FP64 pipe) as a row-per-lane DFMA loop; as 8x8 tiles it is 1/8 of the
     // instructions.  Only the tiles on and below the diagonal are formed (the Cholesky reads the lower triangle).
@@ -285,6 +286,16 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
         const int myr = lane < KP ? lane : 0;
 #pragma unroll
         for (int j = 0; j < KP; j++) gA[j] = Gs[j * LDG + myr];
+        // With a spare lane (KP < 32) the right-hand side b rides along as one more row of the matrix: the same updates turn
+        // it into L^-1 b step by step, so when a pivot is clamped (an equality row that depends on the previous ones) its
+        // element 0 is what is left of that row's right-hand side.  It must vanish -- consistent duplicates are harmless, the
+        // clamp acts like OSQP's regularised polish -- else the rows contradict each other, there is no feasible point and
+        // the reference's advance() fails (QPInverseKinematics.cpp:518-523): status 2.
+        if (KP < 32 && lane == KP) {
+#pragma unroll
+            for (int j = 0; j < KP; j++) gA[j] = cvec[j];
+        }
+        constexpr double kInconsistent = 1e-7;   // [m/s, rad/s]: exact duplicates leave ~1e-15, contradicting targets their difference
         const double floor_ = 1e-14 * warp_max(lane < KP ? Gs[myr * LDG + myr] : 0.0) + 1e-300;
         __syncwarp();
 #pragma unroll 1
@@ -292,7 +303,8 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
             {
                 double piv = __shfl_sync(kFull, gA[0], k);
                 if (!(piv > floor_)) {
-                    if (!(piv == piv)) ok = false;
+                    if (!(piv == piv) || (KP < 32 && lane == KP && fabs(gA[0]) > kInconsistent)) ok = false;
+                    if (KP == 32) clamped = true;
                     piv = floor_;
                 }
                 const double rinv = rsqrt(piv);
@@ -305,7 +317,8 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
                 const int k1 = k + 1;
                 double piv = __shfl_sync(kFull, gB[0], k1);
                 if (!(piv > floor_)) {
-                    if (!(piv == piv)) ok = false;
+                    if (!(piv == piv) || (KP < 32 && lane == KP && fabs(gB[0]) > kInconsistent)) ok = false;
+                    if (KP == 32) clamped = true;
                     piv = floor_;
                 }
                 const double rinv = rsqrt(piv);
@@ -346,6 +359,26 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
         }
     }
     __syncwarp();
+    if constexpr (KP == 32) {
+        if (clamped) {
+            // No spare lane carried b through the factorisation: check the same thing after the fact.  Every iterate is
+            // x = N r + x_b with C_eq N = 0, so the equality residual of whatever the solve returns is C_eq x_b - b.
+            double xbl = 0.0;
+            if (mine)
+                for (int r = 0; r < KP; r++) xbl = fma(Us[lane * LDG + r], wv[r], xbl);
+            __syncwarp();
+            LGt[lane] = xbl;   // L_G is not needed any more
+            __syncwarp();
+            bool bad = false;
+            if (evec[lane] == 0.0) {
+                double res = -cvec[lane];
+                for (int j = 0; j < nv; j++) res = fma(Bm[lane * LDB + j], LGt[j], res);
+                bad = !(fabs(res) <= 1e-6 * (1.0 + fabs(cvec[lane])));
+            }
+            if (__any_sync(kFull, bad)) ok = false;
+            __syncwarp();
+        }
+    }
     // ---- N = D^-1 - U U' (row i by lane i, into Ns), x_b = U w
     {
         double u[KP];
@@ -402,7 +435,7 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
         }
         if (NV & 1) nrow[NV - 1] = Ns[(lane < NV ? lane : 0) * LDB + NV - 1];
     }
-    return ok;
+    return __all_sync(kFull, ok);   // the consistency verdict is held by one lane
 }
 
 // Column `lane` of the angular rows of the centroidal momentum matrix (AngularMomentumTask.cpp:137-185; same formula as

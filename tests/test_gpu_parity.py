@@ -1034,3 +1034,167 @@ def test_minimum_jerk_setpoint_generator(path):
     # switching the generator off leaves the stored (initial) set-point in force
     prob.set_setpoint_minimum_jerk(0, None, 0.0)
     prob.close(), whole.close()
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_random_task_mixes_vs_oracle(seed):
+    """Randomised problems: a random revolute tree (14..40 joints, so both kernels are reached), a random mix of hard and weighted
+    SE3 / R3 / SO3 / CoM / Distance / Gravity / AngularMomentum tasks with random masks and gains, joint tracking as the
+    regulariser, optional limit tasks.  Where both solvers certify a solution and the optimum is unique, nu agrees within 1e-5
+    and the assembled equality rows / gradient within 1e-12."""
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.choice([14, 18, 23, 26, 30, 36, 40]))
+    m = M.random_tree(n, seed=50 + seed, extra_frames=6)
+    N = 24
+    while True:   # five frames on five different links (two hard tasks on one link would repeat its angular rows)
+        frames = list(rng.choice(np.arange(1, len(m.frame_names)), size=5, replace=False))
+        if len({int(m.frame_link[int(f)]) for f in frames}) == 5:
+            break
+    fname = lambda i: m.frame_names[int(frames[i])]
+    mask = lambda: tuple(bool(b) for b in (rng.random(3) < 0.75)) if rng.random() < 0.5 else (True, True, True)
+
+    def nz(mk):
+        return mk if any(mk) else (True, False, True)
+    tasks = [T.se3_task(m, "se3_hard", fname(0), rng.uniform(2, 8), rng.uniform(2, 8), priority=0, mask=nz(mask()))]   # pins the base
+    kinds = list(rng.choice(["r3", "so3", "com", "distance", "gravity", "angmom", "se3"], size=int(rng.integers(2, 5)), replace=False))
+    for k, kind in enumerate(kinds):
+        prio = int(rng.random() < 0.6)
+        fr = fname(1 + k % 4)
+        if kind == "r3":
+            mk = nz(mask())
+            tasks.append(T.r3_task(m, f"r3_{k}", fr, rng.uniform(1, 6), priority=prio, weight=rng.uniform(1, 10, sum(mk)) if prio else None, mask=mk))
+        elif kind == "so3":
+            tasks.append(T.so3_task(m, f"so3_{k}", fr, rng.uniform(1, 6), priority=prio, weight=rng.uniform(1, 10, 3) if prio else None))
+        elif kind == "com":
+            mk = nz(mask())
+            tasks.append(T.com_task(m, f"com_{k}", rng.uniform(1, 6), priority=prio, weight=rng.uniform(1, 10, sum(mk)) if prio else None, mask=mk))
+        elif kind == "distance":
+            ref = fname((k + 2) % 5) if rng.random() < 0.5 else ""
+            if ref == fr:
+                ref = ""
+            tasks.append(T.distance_task(m, f"dist_{k}", fr, rng.uniform(1, 6), priority=1, weight=rng.uniform(1, 10, 1), reference_frame_name=ref))
+        elif kind == "gravity":
+            tasks.append(T.gravity_task(m, f"grav_{k}", fr, rng.uniform(1, 6), priority=1, weight=rng.uniform(1, 10, 2)))
+        elif kind == "angmom":
+            mk = nz(mask())
+            tasks.append(T.angular_momentum_task(m, f"L_{k}", priority=1, weight=rng.uniform(0.5, 5, sum(mk)), mask=mk))
+        else:
+            tasks.append(T.se3_task(m, f"se3_{k}", fr, rng.uniform(1, 6), rng.uniform(1, 6), priority=1, weight=rng.uniform(1, 10, 6)))
+    tasks.append(T.joint_tracking_task(m, "reg", rng.uniform(1, 5, n), priority=1, weight=rng.uniform(0.5, 2, n)))
+    if rng.random() < 0.6:
+        tasks.append(T.joint_velocity_limits_task(m, "vlim", np.full(n, 3.0), np.full(n, -3.0)))
+    if rng.random() < 0.5:
+        tasks.append(T.joint_limits_task(m, "plim", np.full(n, 0.5), 0.01, use_model_limits=True))
+    T.validate_tasks(m, tasks)
+
+    p0 = rng.uniform(-0.5, 0.5, (N, 3))
+    q0 = W.so3_exp(rng.uniform(-0.5, 0.5, (N, 3)))
+    s0 = rng.uniform(-0.5, 0.5, (N, n))
+    o = Oracle(m, tasks)
+    sps = []
+    for t in tasks:
+        L = t.setpoint_len(n)
+        sp = np.zeros((N, L)) if L else None
+        for i in range(N):
+            if sp is None:
+                break
+            R, P = o.fk(p0[i], q0[i], s0[i])
+            if t.type in (T.TASK_SE3, T.TASK_R3, T.TASK_SO3):
+                Rf, pf = o.frame_pose(R, P, t.frame)
+                qd = W.rot_to_quat((W.quat_to_rot(W.so3_exp(rng.normal(0, 0.05, (1, 3)))) @ Rf)[0][None])[0]
+                if t.type == T.TASK_SE3:
+                    sp[i] = np.concatenate([pf + rng.normal(0, 0.02, 3), qd, rng.normal(0, 0.05, 6)])
+                elif t.type == T.TASK_R3:
+                    sp[i] = np.concatenate([pf + rng.normal(0, 0.02, 3), rng.normal(0, 0.05, 3)])
+                else:
+                    sp[i] = np.concatenate([qd, rng.normal(0, 0.05, 3)])
+            elif t.type == T.TASK_COM:
+                sp[i] = np.concatenate([o.com(R, P)[0] + rng.normal(0, 0.02, 3), rng.normal(0, 0.05, 3)])
+            elif t.type == T.TASK_DISTANCE:
+                sp[i, 0] = rng.uniform(0.2, 0.8)
+            elif t.type == T.TASK_GRAVITY:
+                sp[i] = np.concatenate([rng.normal(size=3), rng.normal(0, 0.05, 3)])
+            elif t.type == T.TASK_ANGULAR_MOMENTUM:
+                sp[i] = rng.normal(0, 0.05, 3)
+            else:
+                sp[i] = np.concatenate([s0[i] + rng.normal(0, 0.05, n), rng.normal(0, 0.05, n)])
+        sps.append(sp)
+    model, prob = make(m, tasks, N)
+    prob.set_state(p0, q0, s0)
+    for t, sp in enumerate(sps):
+        if sp is not None:
+            prob.set_setpoint(t, sp)
+    prob.debug_enable(True)
+    prob.tick(1, 0.01)
+    nu = prob.get_output()
+    st, _ = prob.get_status()
+    g, Ce, be = prob.debug_get(capi.DEBUG_G), prob.debug_get(capi.DEBUG_CEQ), prob.debug_get(capi.DEBUG_BEQ)
+    H = prob.debug_get(capi.DEBUG_H)
+    me = prob.me
+    nur, str_, _ = o.tick_batch(p0.copy(), q0.copy(), s0.copy(), sps)
+    if (str_ == 0).sum() < N // 2:
+        # e.g. two hard orientation tasks on neighbouring links: the stacked rows lose rank and the random right-hand sides
+        # are inconsistent -- the reference's QP is infeasible too; the assembled rows are still compared below
+        assert (st != 0).sum() >= N // 2, "the oracle finds the problem infeasible, the GPU certifies solutions"
+    checked = 0
+    for i in range(N):
+        Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [None if sp is None else sp[i] for sp in sps])
+        assert np.abs(g[i] - go).max() <= 1e-11 * (1 + np.abs(go).max())
+        assert np.abs(H[i] - Ho).max() <= 1e-11 * (1 + np.abs(Ho).max())
+        assert np.abs(Ce[i] - Co[:me]).max() <= 1e-11 * (1 + np.abs(Co).max()) and np.abs(be[i] - u[:me]).max() <= 1e-11 * (1 + np.abs(u[:me]).max())
+        if st[i] == 0 and str_[i] == 0:
+            sv = np.linalg.svd(Ce[i], compute_uv=False)
+            Z = np.linalg.svd(Ce[i])[2][me:].T
+            if sv.min() > 1e-3 and np.linalg.eigvalsh(Z.T @ H[i] @ Z).min() > 1e-6:     # unique optimum (SURVEY 8 C.6)
+                assert np.abs(nu[i] - nur[i]).max() <= TOL_NU, (i, kinds, prob.kernel_path)
+                checked += 1
+    assert checked >= N // 2 or (str_ == 0).sum() < N // 2, (checked, kinds, n, prob.kernel_path)
+    prob.close()
+
+
+@pytest.mark.parametrize("big", [False, True])
+@pytest.mark.parametrize("path", PATHS)
+def test_dependent_equality_rows_consistent_and_contradicting(path, big):
+    """Two hard tasks on the same frame repeat its Jacobian rows (rank-deficient C_eq).  With the same target the QP is the
+    single-task one (OSQP solves it; here the dependent pivots are clamped) -- with different targets there is no feasible
+    point, the reference's advance() fails (QPInverseKinematics.cpp:518-523), and the tick must say so (status 2) instead of
+    certifying a point that violates the constraints."""
+    m = M.ergocub23()
+    n, N = m.n, 32
+    one = [T.se3_task(m, "lf", "l_sole", 5.0, 5.0), T.com_task(m, "com", 2.0),
+           T.joint_tracking_task(m, "reg", np.full(n, 5.0), priority=1, weight=np.ones(n))]
+    inp = W.synth_inputs(W.config(3), N, 13)
+    sp_foot, sp_com, sp_reg = inp.setpoints[2], inp.setpoints[0], inp.setpoints[6]
+    extra, extra_sp = [], []
+    if big:   # 32 dense rows: the instantiation without a spare lane, which checks the equality residual after the fact
+        extra = [T.se3_task(m, "rf", "r_sole", 5.0, 5.0, priority=1, weight=[3.0] * 6), T.se3_task(m, "lh", "l_hand_palm", 1.0, 1.0, priority=1, weight=[0.1] * 6),
+                 T.se3_task(m, "rh", "r_hand_palm", 1.0, 1.0, priority=1, weight=[0.1] * 6), T.gravity_task(m, "up", "chest", 2.0, weight=[1.0, 1.0])]
+        o = Oracle(m, extra)
+        hands = np.zeros((2, N, 13))
+        for i in range(N):
+            R, P = o.fk(inp.base_pos[i], inp.base_quat[i], inp.s[i])
+            for k in (1, 2):
+                Rf, pf = o.frame_pose(R, P, extra[k].frame)
+                hands[k - 1, i] = np.concatenate([pf, W.rot_to_quat(Rf[None])[0], np.zeros(6)])
+        extra_sp = [inp.setpoints[1], hands[0], hands[1], np.tile([0.0, 0.0, 1.0, 0.0, 0.0, 0.0], (N, 1))]
+    one = one + extra
+    two = [one[0], T.r3_task(m, "lf_again", "l_sole", 5.0)] + one[1:]
+    same = np.hstack([sp_foot[:, :3], sp_foot[:, 7:10]])
+    other = same.copy()
+    other[:, 0] += 0.01                                    # 1 cm apart: contradicting velocities of 5 cm/s
+    _, p1 = make(m, one, N, path)
+    _, p2 = make(m, two, N, path)
+    for pr in (p1, p2):
+        pr.set_state(inp.base_pos, inp.base_quat, inp.s)
+    p1.set_setpoint(0, sp_foot), p1.set_setpoint(1, sp_com), p1.set_setpoint(2, sp_reg)
+    p2.set_setpoint(0, sp_foot), p2.set_setpoint(1, same), p2.set_setpoint(2, sp_com), p2.set_setpoint(3, sp_reg)
+    for k, sp in enumerate(extra_sp):
+        p1.set_setpoint(3 + k, sp), p2.set_setpoint(4 + k, sp)
+    p1.tick(1, 0.01), p2.tick(1, 0.01)
+    st1, st2 = p1.get_status()[0], p2.get_status()[0]
+    assert np.all(st1 == 0) and np.all(st2 == 0)
+    assert np.abs(p1.get_output() - p2.get_output()).max() < 1e-7
+    p2.set_setpoint(1, other)
+    p2.tick(1, 0.01)
+    assert np.all(p2.get_status()[0] == 2)
+    p1.close(), p2.close()
