@@ -792,7 +792,7 @@ __device__ __forceinline__ bool qp_setup(const Layout& L, const WM& w, double si
         smax = warp_max(smax);
         __syncwarp();
         // S6: S = Ls Ls'
-        ok = chol_inplace(w.Ss, me, LDE, 1e-14 * smax + 1e-300, lane, true) && ok;   // dependent equality rows are dropped
+        ok = chol_inplace(w.Ss, me, LDE, 1e-11 * smax + 1e-300, lane, true) && ok;   // dependent equality rows are dropped
         // S7: V = Y Ls^-T, row i by lane i (in place)
         for (int i = lane; i < nv; i += 32) {
             for (int r = 0; r < me; r++) {

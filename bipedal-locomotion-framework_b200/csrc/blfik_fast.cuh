@@ -182,12 +182,15 @@ __device__ __forceinline__ double fast_matvec(const double (&nrow)[NV], const do
 
 // In-place inverse of the a x a SPD matrix M (row stride ld) in shared memory by Gauss-Jordan sweeps,
 // row t by lane t.  a <= 32.  Returns false if a pivot is not positive.
-__device__ __forceinline__ bool fast_small_inverse(double* M, int a, int ld, int lane)
+// `floor`: pivots at or below it mean that the equality rows leave (a combination of) the selected joints no freedom:
+// N[A,A] is then singular up to rounding noise and its "inverse" would scatter that noise over the whole solution.
+// (N[j][j] <= 1 / D_j, so the floor of row k is 1e-10 / D of the joint it stands for.)
+__device__ __forceinline__ bool fast_small_inverse(double* M, int a, int ld, int lane, const double* dinv, const int* idx)
 {
     bool ok = true;
     for (int k = 0; k < a; k++) {
         const double p = M[k * ld + k];
-        if (!(p > 0.0)) ok = false;
+        if (!(p > 1e-10 * dinv[idx[k]])) ok = false;
         const double ip = 1.0 / p;
         __syncwarp();
         if (lane == k) {
@@ -296,7 +299,9 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
             for (int j = 0; j < KP; j++) gA[j] = cvec[j];
         }
         constexpr double kInconsistent = 1e-7;   // [m/s, rad/s]: exact duplicates leave ~1e-15, contradicting targets their difference
-        const double floor_ = 1e-14 * warp_max(lane < KP ? Gs[myr * LDG + myr] : 0.0) + 1e-300;
+        // 1e-11: an exactly dependent row leaves a pivot of rounding noise, about 1e-14 of the largest diagonal entry after the
+        // accumulations; a pivot this small in a full-rank set would mean singular values 3e-6 apart, beyond FP64 reach anyway
+        const double floor_ = 1e-11 * warp_max(lane < KP ? Gs[myr * LDG + myr] : 0.0) + 1e-300;
         __syncwarp();
 #pragma unroll 1
         for (int k = 0; k < KP; k += 2) {
@@ -1004,7 +1009,9 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                                 for (int uu = 0; uu < a; uu++) MA[lane * mld + uu] = Ns[ri * LDB + idxA[uu]];
                             }
                             __syncwarp();
-                            small_ok = fast_small_inverse(MA, a, mld, lane);
+                            // a joint whose N[j][j] is 1e-10 of its 1 / D_j is fixed by the equality rows and cannot
+                            // be pinned to a bound: this active set has no solution, ADMM (and its verdict) takes over
+                            small_ok = fast_small_inverse(MA, a, mld, lane, dinv, idxA);
                             small_ok = __all_sync(kFull, small_ok);
                         }
                         if (!small_ok) break;

@@ -1036,7 +1036,7 @@ def test_minimum_jerk_setpoint_generator(path):
     prob.close(), whole.close()
 
 
-@pytest.mark.parametrize("seed", range(10))
+@pytest.mark.parametrize("seed", range(int(os.environ.get("BLFIK_FUZZ_SEEDS", "10"))))
 def test_random_task_mixes_vs_oracle(seed):
     """Randomised problems: a random revolute tree (14..40 joints, so both kernels are reached), a random mix of hard and weighted
     SE3 / R3 / SO3 / CoM / Distance / Gravity / AngularMomentum tasks with random masks and gains, joint tracking as the
@@ -1135,7 +1135,13 @@ def test_random_task_mixes_vs_oracle(seed):
     if (str_ == 0).sum() < N // 2:
         # e.g. two hard orientation tasks on neighbouring links: the stacked rows lose rank and the random right-hand sides
         # are inconsistent -- the reference's QP is infeasible too; the assembled rows are still compared below
-        assert (st != 0).sum() >= N // 2, "the oracle finds the problem infeasible, the GPU certifies solutions"
+        # ... unless the GPU's points really are feasible (the oracle's ADMM also gives up on feasible but badly conditioned
+        # problems): every point the GPU certifies must satisfy the reference's constraint stack
+        for i in np.flatnonzero(st == 0):
+            Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [None if sp is None else sp[i] for sp in sps])
+            cx = Co @ nu[i]
+            viol = max((cx - u).max(), (l - cx).max())
+            assert viol <= 1e-6 * (1 + np.abs(cx).max()), ("the GPU certifies an infeasible point", i, viol, kinds)
     checked = 0
     for i in range(N):
         Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [None if sp is None else sp[i] for sp in sps])
@@ -1145,8 +1151,27 @@ def test_random_task_mixes_vs_oracle(seed):
         if st[i] == 0 and str_[i] == 0:
             sv = np.linalg.svd(Ce[i], compute_uv=False)
             Z = np.linalg.svd(Ce[i])[2][me:].T
-            if sv.min() > 1e-3 and np.linalg.eigvalsh(Z.T @ H[i] @ Z).min() > 1e-6:     # unique optimum
-                assert np.abs(nu[i] - nur[i]).max() <= TOL_NU, (i, kinds, prob.kernel_path)
+            lam = np.linalg.eigvalsh(Z.T @ H[i] @ Z).min()
+            if sv.min() > 1e-3 and lam > 1e-6:     # unique optimum
+                # nu is only as well determined as the flattest direction of the reduced Hessian allows: a KKT residual of
+                # 1e-6 (the solvers stop at 1e-7) moves the optimum by 1e-6 / lambda_min
+                tol = max(TOL_NU, 1e-6 / lam)
+                if np.abs(nu[i] - nur[i]).max() > tol:
+                    # the oracle stops at OSQP's eps 1e-7 when its polish is rejected, which can leave 1e-4 in nu on an
+                    # ill-conditioned instance: the referee is then the exact active-set solution of the oracle's QP
+                    from helpers import solve_qp_active_set
+                    x_exact = solve_qp_active_set(Ho, go, Co, l, u)
+                    assert np.abs(nu[i] - x_exact).max() <= tol, (i, kinds, prob.kernel_path, np.abs(nur[i] - x_exact).max(), lam)
+                    f = lambda x_: 0.5 * x_ @ Ho @ x_ + go @ x_
+                    assert f(nu[i]) - f(x_exact) <= 1e-8 * (1 + abs(f(x_exact)))
+                checked += 1
+            elif sv.min() > 1e-3:
+                # flat directions (e.g. a masked hard SE3 task leaves part of the base twist free): compare the cost instead
+                f = lambda x_: 0.5 * x_ @ Ho @ x_ + go @ x_
+                if abs(f(nu[i]) - f(nur[i])) > 1e-7 * (1 + abs(f(nur[i]))):
+                    from helpers import solve_qp_active_set      # referee, as above
+                    x_exact = solve_qp_active_set(Ho, go, Co, l, u)
+                    assert f(nu[i]) - f(x_exact) <= 1e-7 * (1 + abs(f(x_exact))), (i, kinds, prob.kernel_path, f(nur[i]) - f(x_exact))
                 checked += 1
     assert checked >= N // 2 or (str_ == 0).sum() < N // 2, (checked, kinds, n, prob.kernel_path)
     prob.close()
