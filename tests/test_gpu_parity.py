@@ -1223,3 +1223,79 @@ def test_dependent_equality_rows_consistent_and_contradicting(path, big):
     p2.tick(1, 0.01)
     assert np.all(p2.get_status()[0] == 2)
     p1.close(), p2.close()
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("BLFIK_FUZZ_SEEDS", "6"))))
+def test_random_closed_loops_vs_oracle(seed):
+    """Randomised closed loops: a random tree and task mix as above (hard SE3 + weighted tasks + limits), 12 integrating ticks with
+    warm start, the oracle re-solving each tick from the GPU's state; then the same run as ONE multi-tick launch and as
+    packed host ticks must land on the same state."""
+    rng = np.random.default_rng(5000 + seed)
+    n = int(rng.choice([12, 17, 23, 26, 34]))
+    m = M.random_tree(n, seed=200 + seed, extra_frames=4)
+    N, NT, dt = 12, 12, 0.01
+    while True:
+        frames = list(rng.choice(np.arange(1, len(m.frame_names)), size=3, replace=False))
+        if len({int(m.frame_link[int(f)]) for f in frames}) == 3:
+            break
+    fname = lambda i: m.frame_names[int(frames[i])]
+    tasks = [T.se3_task(m, "hard", fname(0), 5.0, 5.0, priority=0),
+             T.com_task(m, "com", 3.0, priority=1, weight=rng.uniform(2, 10, 3)),
+             T.r3_task(m, "reach", fname(1), 4.0, priority=1, weight=rng.uniform(1, 5, 3)),
+             T.so3_task(m, "orient", fname(2), 4.0, priority=1, weight=rng.uniform(1, 5, 3)),
+             T.joint_tracking_task(m, "reg", rng.uniform(1, 5, n), priority=1, weight=rng.uniform(0.5, 2, n)),
+             T.joint_velocity_limits_task(m, "vlim", np.full(n, 1.0), np.full(n, -1.0)),
+             T.joint_limits_task(m, "plim", np.full(n, 0.5), dt, use_model_limits=True)]
+    p0 = rng.uniform(-0.5, 0.5, (N, 3))
+    q0 = W.so3_exp(rng.uniform(-0.5, 0.5, (N, 3)))
+    s0 = rng.uniform(-0.4, 0.4, (N, n))
+    o = Oracle(m, tasks)
+    sps = [np.zeros((N, 13)), np.zeros((N, 6)), np.zeros((N, 6)), np.zeros((N, 7)), np.zeros((N, 2 * n)), None, None]
+    for i in range(N):
+        R, P = o.fk(p0[i], q0[i], s0[i])
+        Rf, pf = o.frame_pose(R, P, tasks[0].frame)
+        sps[0][i] = np.concatenate([pf + rng.normal(0, 0.01, 3), W.rot_to_quat(Rf[None])[0], np.zeros(6)])
+        sps[1][i, :3] = o.com(R, P)[0] + rng.normal(0, 0.02, 3)
+        sps[2][i, :3] = o.frame_pose(R, P, tasks[2].frame)[1] + rng.normal(0, 0.03, 3)
+        Ro, _ = o.frame_pose(R, P, tasks[3].frame)
+        sps[3][i, :4] = W.rot_to_quat((W.quat_to_rot(W.so3_exp(rng.normal(0, 0.1, (1, 3)))) @ Ro)[0][None])[0]
+        sps[4][i, :n] = s0[i] + rng.normal(0, 0.05, n)
+    model, prob = make(m, tasks, N)
+    _, whole = make(m, tasks, N)
+    _, packed = make(m, tasks, N)
+    for pr in (prob, whole, packed):
+        pr.set_state(p0, q0, s0)
+        for t, sp in enumerate(sps):
+            if sp is not None:
+                pr.set_setpoint(t, sp)
+    p, q, s = p0.copy(), q0.copy(), s0.copy()
+    alive = np.ones(N, dtype=bool)
+    for k in range(NT):
+        pr_, qr_, sr_ = p.copy(), q.copy(), s.copy()
+        nur, str_, _ = o.tick_batch(pr_, qr_, sr_, sps, dt_integrate=dt)
+        prob.tick(1, dt, integrate=True, warm_start=True)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        alive &= (st == 0) & (str_ == 0)
+        assert np.abs(nu - nur)[alive].max(initial=0.0) <= 5 * TOL_NU      # the oracle itself is only eps 1e-7 accurate
+        p, q, s = prob.get_state()
+        assert np.abs(np.linalg.norm(q, axis=1) - 1).max() < 1e-13
+    assert alive.sum() >= N // 2
+    whole.tick(NT, dt, integrate=True, warm_start=True)
+    pw, qw, sw = whole.get_state()
+    assert np.abs(sw - s)[alive].max() < 1e-9 and np.abs(pw - p)[alive].max() < 1e-9
+    # packed host ticks: every tick gets the state back from the host record, so feed the previous result forward
+    ph, qh, sh = p0.copy(), q0.copy(), s0.copy()
+    nu_h, st_h = np.empty((N, n + 6)), np.empty(N, dtype=np.int32)
+    rec = np.empty((N, packed.packed_record_len))
+    for t, sp in enumerate(sps):
+        if sp is not None:
+            off = packed.packed_offset(t)
+            rec[:, off:off + sp.shape[1]] = sp
+    for k in range(NT):
+        rec[:, 0:3], rec[:, 3:7], rec[:, 7:7 + n] = ph, qh, sh
+        packed.tick_packed(rec, nu_h, st_h, dt=dt, integrate=True, warm_start=True, nchunks=2)
+        ph, qh, sh = packed.get_state()
+    assert np.abs(sh - s)[alive].max() < 1e-9 and np.abs(ph - p)[alive].max() < 1e-9
+    for pr in (prob, whole, packed):
+        pr.close()
