@@ -1299,3 +1299,74 @@ def test_random_closed_loops_vs_oracle(seed):
     assert np.abs(sh - s)[alive].max() < 1e-9 and np.abs(ph - p)[alive].max() < 1e-9
     for pr in (prob, whole, packed):
         pr.close()
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("BLFIK_FUZZ_SEEDS", "8"))))
+def test_random_options_and_batch_sizes_vs_oracle(seed):
+    """Randomised options on ergoCub / iCub-26: odd batch sizes (1, 3, 17, ... robots: partly filled teams and blocks), exogenous
+    feedback on the feet and the CoM, a foot with its controller disabled, then new weights / gains / velocity limits /
+    controller mode set through the ABI between ticks -- the oracle is rebuilt with the modified task descriptions."""
+    rng = np.random.default_rng(9000 + seed)
+    m = M.ergocub23() if seed % 2 == 0 else M.icub26()
+    n = m.n
+    N = int(rng.choice([1, 2, 3, 5, 17, 33, 63, 100]))
+    exo = [bool(rng.random() < 0.5) for _ in range(3)]
+    tasks = [T.se3_task(m, "lf", "l_sole", 5.0, 5.0, use_position_exogenous_feedback=exo[0], use_orientation_exogenous_feedback=exo[0] and rng.random() < 0.5),
+             T.se3_task(m, "rf", "r_sole", 4.0, 6.0, priority=1, weight=rng.uniform(5, 20, 6), use_position_exogenous_feedback=exo[1]),
+             T.com_task(m, "com", 3.0, mask=(True, True, bool(rng.random() < 0.5)), use_exogenous_feedback=exo[2]),
+             T.so3_task(m, "chest", "chest", 5.0, priority=1, weight=rng.uniform(1, 10, 3)),
+             T.joint_tracking_task(m, "reg", rng.uniform(1, 5, n), priority=1, weight=rng.uniform(0.5, 2, n)),
+             T.joint_velocity_limits_task(m, "vlim", np.full(n, 2.0), np.full(n, -2.0))]
+    tasks[1].controller_enabled = bool(rng.random() < 0.7)
+    p0 = np.tile([0.0, 0.0, 0.7], (N, 1)) + rng.uniform(-0.1, 0.1, (N, 3))
+    q0 = W.so3_exp(rng.uniform(-0.2, 0.2, (N, 3)))
+    s0 = np.clip(m.q_nominal[None] + rng.uniform(-0.2, 0.2, (N, n)), m.q_lower, m.q_upper)
+    o = Oracle(m, tasks)
+    base = [np.zeros((N, 13)), np.zeros((N, 13)), np.zeros((N, 6)), np.zeros((N, 7)), np.zeros((N, 2 * n)), None]
+    fb = [np.zeros((N, 7)), np.zeros((N, 7)), np.zeros((N, 3))]
+    for i in range(N):
+        R, P = o.fk(p0[i], q0[i], s0[i])
+        for k in (0, 1):
+            Rf, pf = o.frame_pose(R, P, tasks[k].frame)
+            base[k][i] = np.concatenate([pf + rng.normal(0, 0.01, 3), W.rot_to_quat(Rf[None])[0], rng.normal(0, 0.02, 6)])
+            fb[k][i] = np.concatenate([pf + rng.normal(0, 0.003, 3), W.rot_to_quat((W.quat_to_rot(W.so3_exp(rng.normal(0, 0.01, (1, 3)))) @ Rf)[0][None])[0]])
+        c = o.com(R, P)[0]
+        base[2][i, :3], fb[2][i] = c + rng.normal(0, 0.01, 3), c + rng.normal(0, 0.003, 3)
+        Rc, _ = o.frame_pose(R, P, tasks[3].frame)
+        base[3][i, :4] = W.rot_to_quat(Rc[None])[0]
+        base[4][i, :n] = s0[i] + rng.normal(0, 0.03, n)
+
+    def records():
+        return [np.hstack([base[k], fb[k]]) if tasks[k].feedback_len() else base[k] for k in range(3)] + [base[3], base[4], None]
+
+    model, prob = make(m, tasks, N, seed % 3 == 2)
+    prob.set_state(p0, q0, s0)
+    for t in range(5):
+        prob.set_setpoint(t, base[t])
+    for k in range(3):
+        if tasks[k].feedback_len():
+            prob.set_feedback(k, fb[k])
+    prob.set_controller_mode(1, tasks[1].controller_enabled)
+
+    def check():
+        prob.tick(1, 0.01)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        nur, str_, _ = Oracle(m, tasks).tick_batch(p0.copy(), q0.copy(), s0.copy(), records())
+        ok = (st == 0) & (str_ == 0)
+        assert ok.sum() >= max(1, (3 * N) // 4), (st, str_)
+        assert np.abs(nu - nur)[ok].max() <= 2 * TOL_NU
+    check()
+    # change things through the ABI, mirror them in the task descriptions
+    tasks[1].weight = rng.uniform(5, 20, 6)
+    prob.set_weight(1, tasks[1].weight)
+    tasks[0].kp_linear, tasks[0].kp_angular = rng.uniform(2, 8, 3), rng.uniform(2, 8, 3)
+    prob.set_gains(0, kp_linear=tasks[0].kp_linear, kp_angular=tasks[0].kp_angular)
+    tasks[4].kp_joint = rng.uniform(1, 5, n)
+    prob.set_gains(4, kp_joint=tasks[4].kp_joint)
+    tasks[5].upper, tasks[5].lower = np.full(n, 1.5), np.full(n, -1.2)
+    prob.set_limits(5, upper=tasks[5].upper, lower=tasks[5].lower)
+    tasks[1].controller_enabled = not tasks[1].controller_enabled
+    prob.set_controller_mode(1, tasks[1].controller_enabled)
+    check()
+    prob.close()
