@@ -568,7 +568,8 @@ void orc_parity_settings(orc_qp_settings* s)
 {
     orc_default_settings(s);
     s->eps_abs = 1e-7, s->eps_rel = 1e-7;
-    s->polish = 1;
+    s->polish = 12; /* 1 = OSQP's single polish; > 1 = that many tries with active-set refinement in between */
+    s->polish_refine_iter = 10; /* OSQP: 3; the regularised KKT solve needs more on ill-conditioned instances */
 }
 
 /* in-place lower Cholesky of an n x n row-major SPD matrix; 0 on success */
@@ -711,21 +712,25 @@ static void set_rho_vec(const qp_data* d, double rho, double* rho_vec)
 /* OSQP polish (polish.c): active set from (z, y), regularised KKT solve with
  * iterative refinement against the unregularised system.  Returns 0 when the
  * polished point improves both residuals (and overwrites x, y, z).            */
+/* `aflag` (may be NULL): on entry, if aflag[0] != 2, the active set to use (-1 lower, +1 upper, 0 free per row; equality
+ * rows are always active) instead of OSQP's rule; on a rejected candidate it receives the refined guess (violated rows
+ * added, rows with a wrong-sign multiplier dropped) so that the caller can try again -- a primal-dual active-set step. */
 static int qp_polish(const qp_data* d, const orc_qp_settings* st, double* x, double* y, double* z,
                      double r_prim_admm, double r_dual_admm, double* r_prim_out,
-                     double* r_dual_out)
+                     double* r_dual_out, int* aflag)
 {
     const int nv = d->nv, m = d->m;
     int* act = (int*)malloc(sizeof(int) * (m + 1));
     double* rhs_b = (double*)malloc(sizeof(double) * (m + 1));
     int* sgn = (int*)malloc(sizeof(int) * (m + 1));
     int ma = 0;
+    const int given = aflag && m > 0 && aflag[0] != 2;
     for (int i = 0; i < m; i++) {
         if (d->l[i] == d->u[i]) {
             act[ma] = i, rhs_b[ma] = d->l[i], sgn[ma] = 0, ma++;
-        } else if (z[i] - d->l[i] < -y[i]) {
+        } else if (given ? aflag[i] < 0 : (z[i] - d->l[i] < -y[i])) {
             act[ma] = i, rhs_b[ma] = d->l[i], sgn[ma] = -1, ma++;
-        } else if (d->u[i] - z[i] < y[i]) {
+        } else if (given ? aflag[i] > 0 : (d->u[i] - z[i] < y[i])) {
             act[ma] = i, rhs_b[ma] = d->u[i], sgn[ma] = 1, ma++;
         }
     }
@@ -781,6 +786,18 @@ static int qp_polish(const qp_data* d, const orc_qp_settings* st, double* x, dou
         }
         ok = sign_ok && (rp == rp) && (rd == rd) && rp <= fmax(r_prim_admm, 1e-10)
              && rd <= fmax(r_dual_admm, 1e-10);
+        if (!ok && aflag && rp == rp) { /* refined active set for the next try */
+            for (int i = 0; i < m; i++) aflag[i] = 0;
+            for (int r = 0; r < ma; r++)
+                if (sgn[r] != 0 && !((sgn[r] < 0 && sol[nv + r] > 1e-9) || (sgn[r] > 0 && sol[nv + r] < -1e-9))) aflag[act[r]] = sgn[r];
+            for (int i = 0; i < m; i++) {
+                if (d->l[i] == d->u[i]) continue;
+                double v = 0;
+                for (int j = 0; j < nv; j++) v += d->C[i * nv + j] * xp[j];
+                if (v < d->l[i] - 1e-9 * (1 + fabs(d->l[i]))) aflag[i] = -1;
+                if (v > d->u[i] + 1e-9 * (1 + fabs(d->u[i]))) aflag[i] = 1;
+            }
+        }
         if (ok) {
             memcpy(x, xp, sizeof(double) * nv);
             memcpy(y, yp, sizeof(double) * m);
@@ -878,11 +895,21 @@ int orc_qp_solve(int nv, int m, const double* H, const double* g, const double* 
         qp_residuals(&d, x, y, z, Cx, &rp, &rd, &ps, &ds);
         inf.r_prim = rp, inf.r_dual = rd;
         if (st->polish) {
+            /* OSQP polishes once; the parity settings add primal-dual active-set steps (st->polish > 1 tries in total) so
+             * that a rejected first guess does not leave the answer at ADMM accuracy -- on an ill-conditioned instance
+             * eps 1e-7 residuals can mean 1e-4 in x, and the oracle has to stand for "the optimum to KKT <= 1e-9" */
             double rpp, rdp;
-            if (qp_polish(&d, st, x, y, z, rp, rd, &rpp, &rdp) == 0) {
-                inf.polished = 1;
-                inf.r_prim = rpp, inf.r_dual = rdp;
+            int* aflag = st->polish > 1 && m > 0 ? (int*)malloc(sizeof(int) * m) : NULL;
+            if (aflag) aflag[0] = 2;
+            for (int attempt = 0; attempt < st->polish; attempt++) {
+                if (qp_polish(&d, st, x, y, z, rp, rd, &rpp, &rdp, aflag) == 0) {
+                    inf.polished = 1;
+                    inf.r_prim = rpp, inf.r_dual = rdp;
+                    break;
+                }
+                if (!aflag || aflag[0] == 2) break;
             }
+            free(aflag);
         }
     }
 done:

@@ -101,7 +101,7 @@ typedef struct {
     int max_iter;
     int check_termination;   /* every k iterations                              */
     int adaptive_rho_interval; /* 0 = off                                       */
-    int polish;              /* 1 = OSQP-style polishing                        */
+    int polish;              /* 0 off, 1 = OSQP-style polishing, k > 1 = up to k tries with active-set refinement in between */
     double delta;            /* polish regularisation                           */
     int polish_refine_iter;
     int warm_start;

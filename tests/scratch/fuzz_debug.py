@@ -4,7 +4,7 @@ src=open('/root/repo/tests/test_gpu_parity.py').read()
 i0=src.index("def test_random_task_mixes_vs_oracle"); body=src[i0:]
 from blf_b200 import models as M, tasks as T, workloads as W, capi
 from oracle.oracle import Oracle
-pre=body[:body.index("    model, prob = make(m, tasks, N)")]
+pre=body[:body.index("    model, prob = make(m, tasks, N, int(os.environ")]
 ns=dict(np=np,M=M,T=T,W=W,Oracle=Oracle,os=os)
 exec(pre.replace("def test_random_task_mixes_vs_oracle(seed):","def build(seed):")+"    return m,tasks,o,sps,p0,q0,s0,kinds\n",ns)
 for seed in [int(a) for a in sys.argv[1:]]:
