@@ -20,7 +20,7 @@ LIB_PATH = os.environ.get("BLFIK_LIBRARY") or os.path.join(_HERE, "libblfik_cuda
 _lib = None
 
 MEM_HOST, MEM_DEVICE = 0, 1
-TICK_INTEGRATE, TICK_WARM_START = 1, 2
+TICK_INTEGRATE, TICK_WARM_START, TICK_NO_FEEDFORWARD = 1, 2, 4
 DEBUG_H, DEBUG_G, DEBUG_CEQ, DEBUG_BEQ, DEBUG_LO, DEBUG_HI = range(6)
 
 c_double_p = C.POINTER(C.c_double)
@@ -39,6 +39,7 @@ EXPORTS = [
     "blfik_packed_record_len", "blfik_packed_offset", "blfik_tick_packed",
     "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time", "blfik_set_limits",
     "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk",
+    "blfik_packed_record_len_ex", "blfik_packed_offset_ex", "blfik_packed_part_len",
 ]
 
 
@@ -341,22 +342,38 @@ class Problem:
         self.L.blfik_packed_offset.argtypes = [C.c_void_p, C.c_int32]
         return int(self.L.blfik_packed_offset(self.handle, int(task)))
 
-    def pack_inputs(self, inp) -> np.ndarray:
-        """``workloads.Inputs`` -> [N][packed_record_len] host array."""
-        rec = np.empty((self.N, self.packed_record_len))
+    def pack_inputs(self, inp, compact: bool = False) -> np.ndarray:
+        """``workloads.Inputs`` -> [N][record length] host array.  compact: the layout of BLFIK_TICK_NO_FEEDFORWARD (pose part
+        of every set-point only); raises if a feed-forward term that would be dropped is not zero."""
+        fl = TICK_NO_FEEDFORWARD if compact else 0
+        L = self.L
+        L.blfik_packed_record_len_ex.argtypes = [C.c_void_p, C.c_uint32]
+        L.blfik_packed_offset_ex.argtypes = [C.c_void_p, C.c_int32, C.c_uint32]
+        L.blfik_packed_part_len.argtypes = [C.c_void_p, C.c_int32, C.c_uint32]
+        rec = np.zeros((self.N, int(L.blfik_packed_record_len_ex(self.handle, fl))))
         rec[:, 0:3], rec[:, 3:7], rec[:, 7:7 + self.n] = inp.base_pos, inp.base_quat, inp.s
         for t, sp in enumerate(inp.setpoints):
-            if sp is not None:
-                o = self.packed_offset(t)
+            if sp is None:
+                continue
+            o = int(L.blfik_packed_offset_ex(self.handle, t, fl))
+            if not compact:
                 rec[:, o:o + sp.shape[1]] = sp
+                continue
+            base = int(L.blfik_packed_part_len(self.handle, t, fl)) - int(L.blfik_feedback_len(self.handle, t))
+            full = int(L.blfik_setpoint_len(self.handle, t))
+            if np.any(sp[:, base:full] != 0.0):
+                raise ValueError(f"task {t}: the compact record drops non-zero feed-forward terms")
+            rec[:, o:o + base] = sp[:, :base]
+            if sp.shape[1] > full:   # exogenous feedback travels behind the pose part
+                rec[:, o + base:o + base + sp.shape[1] - full] = sp[:, full:]
         return rec
 
     def tick_packed(self, records, nu, status=None, dt: float = 0.0, integrate: bool = False, warm_start: bool = False,
-                    nchunks: int = 0):
+                    nchunks: int = 0, compact: bool = False):
         """One tick from packed HOST records (numpy or pinned torch CPU tensor).  nchunks = 0: zero-copy (the kernel reads
         pinned host memory directly; falls back to staged copies for pageable buffers); nchunks >= 1: that many
         copy / compute / copy pipeline chunks."""
-        flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0)
+        flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0) | (TICK_NO_FEEDFORWARD if compact else 0)
         (r, d0), (o, d1) = _ptr(records), _ptr(nu)
         st = None if status is None else _ptr(status)[0]
         assert not d0 and not d1, "blfik_tick_packed takes host buffers"

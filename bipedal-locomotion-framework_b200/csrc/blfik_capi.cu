@@ -186,6 +186,7 @@ struct HostTask {
     std::vector<double> kp_joint, weight, klim, upper, lower;
     int rows = 0, sp_len = 0, row_offset = 0, brow = 0, pk_off = 0;   // sp_len: doubles per robot of the record (set-point + feedback)
     int fb_len = 0;   // exogenous feedback behind the set-point: 7 (SE3: p, q), 3 (CoM: p) or 0
+    int base_c = 0, pk_off_c = 0;   // compact packed layout: doubles of the pose part, offset inside the record
     double traj_amp[6] = {0, 0, 0, 0, 0, 0}, traj_omega = 0.0;
     double* d_traj_phase = nullptr;
     double* d_mj_target = nullptr;   // minimum-jerk generator: target set-points [N][set-point length]
@@ -244,6 +245,7 @@ struct blfik_problem {
     cudaEvent_t ev_in[16] = {}, ev_done[16] = {}, ev_start = nullptr;
     double time = 0.0;               // time of the next tick (advanced by integrating ticks; set-point trajectories)
     int packed_len = 0;              // doubles per packed input record: 7 + n + sum of set-point lengths
+    int packed_len_c = 0;            // the same in the compact layout (BLFIK_TICK_NO_FEEDFORWARD)
     double* d_packed = nullptr;      // device copy of the packed records (allocated on first use)
 };
 
@@ -360,6 +362,21 @@ static int sp_len_of(int type, int n)
     default: return 0;
     }
 }
+// pose part of a set-point (what is left when the feed-forward terms are dropped)
+static int base_compact_of(int type, int n)
+{
+    switch (type) {
+    case BLFIK_TASK_SE3: return 7;
+    case BLFIK_TASK_COM: return 3;
+    case BLFIK_TASK_R3: return 3;
+    case BLFIK_TASK_SO3: return 4;
+    case BLFIK_TASK_DISTANCE: return 1;
+    case BLFIK_TASK_GRAVITY: return 3;
+    case BLFIK_TASK_ANGULAR_MOMENTUM: return 3;
+    case BLFIK_TASK_JOINT_TRACKING: return n;
+    default: return 0;
+    }
+}
 static bool is_dense(int type) { return is_dense_type(type); }
 static bool has_frame(int type) { return type == BLFIK_TASK_SE3 || type == BLFIK_TASK_SO3 || type == BLFIK_TASK_R3 || type == BLFIK_TASK_DISTANCE || type == BLFIK_TASK_GRAVITY; }
 static bool is_inequality(int type) { return type == BLFIK_TASK_JOINT_LIMITS || type == BLFIK_TASK_JOINT_VELOCITY_LIMITS; }
@@ -471,7 +488,7 @@ static int refresh_tasks(blfik_problem* p)
         DevTask& d = dt[t];
         d.type = h.d.type, d.priority = h.d.priority, d.frame = h.d.frame, d.rows = h.rows, d.enabled = h.d.controller_enabled;
         d.sp_len = h.sp_len, d.row_offset = h.row_offset, d.brow = h.brow;
-        d.flink = 0, d.pk_off = h.pk_off;
+        d.flink = 0, d.pk_off = h.pk_off, d.pk_off_c = h.pk_off_c, d.base_c = h.base_c;
         d.exo_pos = h.d.use_position_exogenous_feedback != 0, d.exo_ori = h.d.use_orientation_exogenous_feedback != 0;
         d.fb_off = h.sp_len - h.fb_len;
         d.traj_phase = h.d_traj_phase, d.traj_omega = h.d_traj_phase ? h.traj_omega : 0.0;
@@ -581,10 +598,13 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         h.setpoint_set = h.sp_len == 0;
         p->tasks.push_back(std::move(h));
     }
-    p->packed_len = 7 + n;
+    p->packed_len = p->packed_len_c = 7 + n;
     for (HostTask& h : p->tasks) {
         h.pk_off = p->packed_len;
         p->packed_len += h.sp_len;
+        h.base_c = base_compact_of(h.d.type, n);
+        h.pk_off_c = p->packed_len_c;
+        p->packed_len_c += h.sp_len ? h.base_c + h.fb_len : 0;
     }
     if (me > 64) return bail(fail(BLFIK_ERR_UNSUPPORTED, "[blfik_problem_create] more than 64 dense equality rows (%d)", me));
     p->me = me;
@@ -989,7 +1009,8 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
     P.status = p->status, P.iters = p->iters, P.st = p->st, P.nticks = nticks, P.dt = dt, P.flags = flags;
     P.dbg = (p->debug && first == 0 && count == p->N) ? p->dbg : DebugOut{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     P.L = p->L;
-    P.packed = packed, P.packed_len = p->packed_len;
+    P.packed = packed, P.compact = (packed && (flags & BLFIK_TICK_NO_FEEDFORWARD)) ? 1 : 0;
+    P.packed_len = P.compact ? p->packed_len_c : p->packed_len;
     P.nu_host = nu_host, P.status_host = status_host;
     P.t0 = p->time;
     if (p->fast_kernel && p->path == 0) {
@@ -1111,6 +1132,28 @@ extern "C" int blfik_tick_host(blfik_problem* p, const double* base_pos, const d
 
 extern "C" int32_t blfik_packed_record_len(const blfik_problem* p) { return p ? p->packed_len : -1; }
 
+extern "C" int32_t blfik_packed_record_len_ex(const blfik_problem* p, uint32_t flags)
+{
+    if (!p) return -1;
+    return (flags & BLFIK_TICK_NO_FEEDFORWARD) ? p->packed_len_c : p->packed_len;
+}
+
+extern "C" int32_t blfik_packed_offset_ex(const blfik_problem* p, int32_t task, uint32_t flags)
+{
+    if (!p) return -1;
+    if (task < 0) return 0;
+    if (task >= (int)p->tasks.size() || p->tasks[task].sp_len == 0) return -1;
+    return (flags & BLFIK_TICK_NO_FEEDFORWARD) ? p->tasks[task].pk_off_c : p->tasks[task].pk_off;
+}
+
+extern "C" int32_t blfik_packed_part_len(const blfik_problem* p, int32_t task, uint32_t flags)
+{
+    if (!p || task < 0 || task >= (int)p->tasks.size()) return -1;
+    const HostTask& h = p->tasks[task];
+    if (h.sp_len == 0) return 0;
+    return (flags & BLFIK_TICK_NO_FEEDFORWARD) ? h.base_c + h.fb_len : h.sp_len;
+}
+
 extern "C" int32_t blfik_packed_offset(const blfik_problem* p, int32_t task)
 {
     if (!p) return -1;
@@ -1171,7 +1214,7 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     CU(cudaEventRecord(p->ev_start, p->stream));
     CU(cudaStreamWaitEvent(p->h2d_stream, p->ev_start, 0));
     CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_start, 0));
-    const int nv = p->nv, R = p->packed_len;
+    const int nv = p->nv, R = (flags & BLFIK_TICK_NO_FEEDFORWARD) ? p->packed_len_c : p->packed_len;
     // ---- streaming input: ONE persistent launch that starts at once and consumes the records as the copy engine delivers
     // them (chunk launches lose a tail each: 5 launches of 13k robots take 2.3 ms of kernel time against 1.36 ms for one
     // launch of 65k).  Needs the register-resident kernel with dynamic hand-out, page-locked records (a pure DMA on the

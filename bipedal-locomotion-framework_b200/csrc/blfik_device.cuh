@@ -62,6 +62,8 @@ struct DevTask {
     double Fp2[3];           // DistanceTask: origin of the reference frame in its link
     double thr;              // DistanceTask: distance_numeric_threshold
     int pk_off;              // offset of this task's set-point inside a packed input record
+    int pk_off_c;            // the same in the compact layout (no feed-forward terms: pose part, then the feedback)
+    int base_c;              // doubles of the pose part in the compact layout (SE3 7, CoM / R3 3, SO3 4, joints n, ...)
     // optional minimum-jerk point-to-point generator (Planners::SO3Planner with zero boundary velocity / acceleration, and
     // the quintic between two knots for positions): from the stored set-point to mj_target over [mj_t0, mj_t0 + mj_T]
     const double* mj_target;    // device [N][set-point length], nullptr: off
@@ -99,6 +101,7 @@ struct TickParams {
     int* status_host;                      //   memory (zero-copy host tick); null otherwise
     const double* packed;                  // optional packed input records [.][packed_len]: p(3) q(4) s(n) set-points...
     int packed_len;
+    int compact;                           // 1: packed records in the compact layout (BLFIK_TICK_NO_FEEDFORWARD)
     double *base_pos, *base_quat, *s;      // state (in/out)
     double* nu;                            // [N][nv] out
     double *wx, *wz, *wy;                  // warm start [N][nv], [N][n], [N][n]
@@ -474,6 +477,20 @@ __device__ __forceinline__ void k1_angmom(const DevModel& m, const WM& w, const 
     }
 }
 
+// Record of task `tk` for `robot`: from a packed input record (full or compact layout) or from the task's own buffer.
+__device__ __forceinline__ const double* task_record(const TickParams& P, const DevTask& tk, long long robot)
+{
+    if (P.packed) return P.packed + (size_t)robot * P.packed_len + (P.compact ? tk.pk_off_c : tk.pk_off);
+    return tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr;
+}
+// Compact records carry only the pose part of a set-point (the reference's setSetPoint(pose) with its default zero
+// velocity); `out` receives the full dense record (<= 13 doubles) with the feed-forward entries zeroed.
+__device__ __forceinline__ void expand_compact(const DevTask& tk, const double* rec, double* out)
+{
+    const int full = tk.fb_off;   // length of the full set-point
+    for (int c = 0; c < full && c < 13; c++) out[c] = c < tk.base_c ? rec[c] : 0.0;
+}
+
 // Set-point of a task at time t when an on-device trajectory is attached (the set-point producers
 // that feed setSetPoint): x_d(t) = x_0 + A sin(w t + phi_i), feed-forward += A w cos(w t + phi_i); orientations move by
 // the world-frame rotation Exp(A_ang sin(.)) about a fixed axis, whose angular velocity is exactly A_ang w cos(.).
@@ -567,12 +584,18 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
     __syncwarp();
     for (int t = 0; t < P.ntasks; t++) {
         const DevTask& tk = P.tasks[t];
-        const double* sp = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : (tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr);
+        const double* sp = task_record(P, tk, robot);
+        const bool compact = P.packed && P.compact;
         if (is_dense_type(tk.type)) {
-            double bt[6], spl[13];
+            double bt[6], spl[13], spx[13];
             int src[6];
             int rows = 0;
-            const double* sp0 = sp;   // the stored record (the exogenous feedback sits behind the set-point)
+            // the exogenous feedback sits behind the set-point: re-based so that sp0[tk.fb_off + c] addresses it in both layouts
+            const double* sp0 = compact ? sp - (tk.fb_off - tk.base_c) : sp;
+            if (compact) {
+                expand_compact(tk, sp, spx);
+                sp = spx;
+            }
             sp = traj_eval(tk, robot, tnow, sp, spl);
             if (tk.type == T_ANGMOM) {   // AngularMomentumTask.cpp:137-185: A = masked rows of the angular CMM, b = desired momentum
                 double com[3];
@@ -671,7 +694,7 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
             for (int j = lane; j < n; j += 32) {
                 const int i = 6 + j;
                 if (tk.type == T_JOINT_TRACKING) {  // JointTrackingTask.cpp:151
-                    const double bj = sp[n + j] + tk.kp_joint[j] * (sp[j] - s[j]);
+                    const double bj = (compact ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - s[j]);
                     if (tk.priority == 1) {
                         w.Hs[i * LD + i] += tk.weight[j];
                         w.g[i] -= tk.weight[j] * bj;

@@ -723,8 +723,15 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                 const bool dense = is_dense_type(tk.type);
                 if (dense) {
                     double spl[13];
-                    const double* sp0 = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : tk.setpoint + robot * tk.sp_len;
-                    const double* sp = traj_eval(tk, robot, P.t0 + tick * P.dt, sp0, spl);
+                    const double* rec = task_record(P, tk, robot);
+                    const bool compact = P.packed && P.compact;
+                    // the exogenous feedback sits behind the set-point: sp0[tk.fb_off + c] addresses it in both layouts
+                    const double* sp0 = compact ? rec - (tk.fb_off - tk.base_c) : rec;
+                    if (compact) {   // pose part only: the full record is rebuilt with zero feed-forward entries
+                        expand_compact(tk, rec, spl);
+                        rec = spl;
+                    }
+                    const double* sp = traj_eval(tk, robot, P.t0 + tick * P.dt, rec, spl);
                     const bool has_lin = tk.type == T_SE3 || tk.type == T_R3 || tk.type == T_COM, has_ang = tk.type == T_SE3 || tk.type == T_SO3;
                     double Rf[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, pf[3] = {com[0], com[1], com[2]};
                     if (tk.type != T_COM && tk.type != T_ANGMOM) {
@@ -871,10 +878,10 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                         evec[tk.brow + lane] = tk.priority == 0 ? 0.0 : 1.0 / tk.weight[lane];
                     }
                 } else if (joint) {
-                    const double* sp = P.packed ? P.packed + (size_t)robot * P.packed_len + tk.pk_off : (tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr);
+                    const double* sp = task_record(P, tk, robot);
                     const int j = lane - 6;
                     if (tk.type == T_JOINT_TRACKING) {
-                        const double bj = sp[n + j] + tk.kp_joint[j] * (sp[j] - sj);
+                        const double bj = ((P.packed && P.compact) ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - sj);
                         if (tk.priority == 1) {
                             dh += tk.weight[j];
                             gd += tk.weight[j] * bj;

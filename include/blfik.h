@@ -76,6 +76,7 @@ typedef enum {
 
 /* flags of blfik_tick */
 #define BLFIK_TICK_INTEGRATE 1u   /* apply ForwardEuler after each solve (closed loop)           */
+#define BLFIK_TICK_NO_FEEDFORWARD 4u /* blfik_tick_packed only: compact records, see there                 */
 #define BLFIK_TICK_WARM_START 2u  /* start ADMM from the previous tick's (x, z, y) (reference does,
                                      QPInverseKinematics.cpp:494-509)                             */
 
@@ -246,6 +247,16 @@ int blfik_tick_host(blfik_problem* problem, const double* base_pos, const double
  * the transfers overlap the computation robot by robot; with pageable buffers it falls back to two staged chunks.  */
 int32_t blfik_packed_record_len(const blfik_problem* problem);
 int32_t blfik_packed_offset(const blfik_problem* problem, int32_t task);
+/* BLFIK_TICK_NO_FEEDFORWARD in the flags of blfik_tick_packed selects the COMPACT record: every set-point shrinks to its
+ * pose part -- SE3: p(3) q(4); CoM / R3: p(3); SO3: q(4); JointTracking: s_d(n); Distance 1; Gravity: direction(3);
+ * AngularMomentum 3 -- followed by the task's exogenous feedback if it has one, and all feed-forward terms are zero.
+ * That is the reference's setSetPoint(pose) with its default zero velocity argument (SE3Task.h, CoMTask.h,
+ * JointTrackingTask::setSetPoint(jointPosition), JointTrackingTask.cpp:157-160); for ergoCub C3 a record shrinks from
+ * 920 to 592 bytes, which matters when the host link is the bound (8 GPUs on one host).  The _ex queries describe
+ * either layout (flags = 0 or BLFIK_TICK_NO_FEEDFORWARD); blfik_packed_part_len is the number of doubles of one task.   */
+int32_t blfik_packed_record_len_ex(const blfik_problem* problem, uint32_t flags);
+int32_t blfik_packed_offset_ex(const blfik_problem* problem, int32_t task, uint32_t flags);
+int32_t blfik_packed_part_len(const blfik_problem* problem, int32_t task, uint32_t flags);
 int blfik_tick_packed(blfik_problem* problem, const double* records, double* nu, int32_t* status,
                       double dt, uint32_t flags, int32_t nchunks);
 

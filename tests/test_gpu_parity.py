@@ -1370,3 +1370,56 @@ def test_random_options_and_batch_sizes_vs_oracle(seed):
     prob.set_controller_mode(1, tasks[1].controller_enabled)
     check()
     prob.close()
+
+
+@pytest.mark.parametrize("path", PATHS)
+def test_compact_packed_records_equal_full_ones(path):
+    """BLFIK_TICK_NO_FEEDFORWARD: records that carry only the pose part of every set-point (the reference's setSetPoint(pose)
+    with its default zero velocity) give bit-identical results to full records whose feed-forward entries are zero -- with and
+    without exogenous feedback behind the set-points, in every host-tick mode -- and packing refuses to drop a non-zero term."""
+    w = W.config(3)
+    N = 300
+    inp = W.synth_inputs(w, N, 3)
+    model, prob = make(w.model, w.tasks, N, path)
+    prob.set_inputs(inp)
+    full, compact = prob.pack_inputs(inp), prob.pack_inputs(inp, compact=True)
+    n = w.model.n
+    assert full.shape[1] == 7 + n + 13 + 13 + 6 + 7 + 2 * n and compact.shape[1] == 7 + n + 7 + 7 + 3 + 4 + n
+    out = {}
+    for name, rec, c in (("full", full, False), ("compact", compact, True)):
+        for nchunks in (0, 1, 3):
+            nu, st = np.empty((N, n + 6)), np.empty(N, dtype=np.int32)
+            prob.tick_packed(rec, nu, st, dt=w.dt, integrate=True, nchunks=nchunks, compact=c)
+            out[(name, nchunks)] = (nu.copy(), st.copy(), [a.copy() for a in prob.get_state()])
+    ref = out[("full", 1)]
+    for key, (nu, st, state) in out.items():
+        assert np.array_equal(nu, ref[0]) and np.array_equal(st, ref[1]), key
+        assert all(np.array_equal(a, b) for a, b in zip(state, ref[2])), key
+    bad = inp.slice(0, N)
+    bad.setpoints[0] = bad.setpoints[0].copy()
+    bad.setpoints[0][3, 4] = 0.01                                   # a CoM feed-forward velocity
+    with pytest.raises(ValueError):
+        prob.pack_inputs(bad, compact=True)
+    prob.close()
+    # with exogenous feedback: the measured pose follows the pose part
+    m = w.model
+    tasks = [T.se3_task(m, "lf", "l_sole", 5.0, 5.0, use_position_exogenous_feedback=True, use_orientation_exogenous_feedback=True),
+             T.com_task(m, "com", 2.0, use_exogenous_feedback=True),
+             T.joint_tracking_task(m, "reg", np.full(n, 5.0), priority=1, weight=np.ones(n))]
+    rng = np.random.default_rng(2)
+    sps = [np.hstack([inp.setpoints[2], inp.setpoints[2][:, :7] + rng.normal(0, 1e-3, (N, 7))]),
+           np.hstack([inp.setpoints[0], inp.setpoints[0][:, :3] + rng.normal(0, 1e-3, (N, 3))]), inp.setpoints[6]]
+    sps[0][:, 16:20] /= np.linalg.norm(sps[0][:, 16:20], axis=1, keepdims=True)
+    _, p2 = make(m, tasks, N, path)
+    import copy
+    inp2 = copy.copy(inp)
+    inp2.setpoints = sps
+    full2, compact2 = p2.pack_inputs(inp2), p2.pack_inputs(inp2, compact=True)
+    assert full2.shape[1] == 7 + n + 20 + 9 + 2 * n and compact2.shape[1] == 7 + n + 14 + 6 + n
+    res = []
+    for rec, c in ((full2, False), (compact2, True)):
+        nu, st = np.empty((N, n + 6)), np.empty(N, dtype=np.int32)
+        p2.tick_packed(rec, nu, st, dt=w.dt, nchunks=2, compact=c)
+        res.append((nu.copy(), st.copy()))
+    assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]) and np.all(res[0][1] == 0)
+    p2.close()
