@@ -189,14 +189,25 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         prob.set_state(*d_state)                       # device -> device restore of the initial state
         prob.tick(1, w.dt, integrate=True, warm_start=False)
 
-    h_packed = torch.from_numpy(prob.pack_inputs(inputs)).pin_memory()
+    # The set-points of this workload carry no feed-forward velocities ("feed-forward twist 0 (open loop)"), which is
+    # the reference's setSetPoint(pose) with its default zero velocity: the host records then hold the pose part only
+    # (BLFIK_TICK_NO_FEEDFORWARD).  pack_inputs(compact=True) refuses if any dropped entry is non-zero.
+    compact = not args.full_records
+    if compact:
+        try:
+            packed_np = prob.pack_inputs(inputs, compact=True)
+        except ValueError:
+            compact = False
+    if not compact:
+        packed_np = prob.pack_inputs(inputs)
+    h_packed = torch.from_numpy(packed_np).pin_memory()
 
     def e2e_step():
         # the reference-facing call with HOST buffers: one packed record per robot (state + set-points) in, nu + status out.
         # --chunks k >= 1: one persistent launch starts at once and consumes the records while the copy engine streams them
         # in (it polls an arrival word that the copy stream raises after every piece) and writes nu / status straight into
         # the pinned host buffers; --chunks 0: the kernel also reads the records over PCIe itself (zero-copy mode)
-        prob.tick_packed(h_packed, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False, nchunks=args.chunks)
+        prob.tick_packed(h_packed, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False, nchunks=args.chunks, compact=compact)
 
     def barrier():
         if world > 1:
@@ -275,12 +286,14 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
                        "parallelism": f"instance-sharded x{world}, no collective", "warm_start": False,
                        "solver": prob_settings, "l2": "256 MiB write between steps (untimed) flushes the 126 MB L2",
                        "unsolved_instances": unsolved,
+                       "host_records": ("compact: state + pose part of every set-point, feed-forward terms are zero and not sent "
+                                        f"({h_packed.shape[1] * 8} B per robot)" if compact else f"full ({h_packed.shape[1] * 8} B per robot)"),
                        "host_tick": ("blfik_tick_packed, zero-copy (kernel reads pinned host records over PCIe)" if args.chunks <= 0 else
                                      "blfik_tick_packed, streaming input: one persistent launch consumes the packed records while the copy "
                                      "engine delivers them in 16 pieces (arrival word raised by stream memory operations), results written "
                                      "to pinned host memory by the kernel")},
             "e2e": {"value": ticks_total / (ms_e2e * 1e-3), "unit": "ticks/s",
-                    "h2d_bytes_per_step": int(8 * n_local * (7 + n + sp_doubles)),
+                    "h2d_bytes_per_step": int(h_packed.numel() * 8),
                     "d2h_bytes_per_step": int(n_local * (8 * nv + 4))},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
@@ -316,6 +329,7 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--instances", type=int, default=PER_GPU_INSTANCES, help="instances per GPU")
+    ap.add_argument("--full-records", action="store_true", help="host-buffer (e2e) tick: send full records (with the zero feed-forward terms) instead of compact ones")
     ap.add_argument("--chunks", type=int, default=5,
                     help="host-buffer (e2e) tick: k >= 1 = pipelined (pinned buffers: one persistent launch that consumes the records while the copy engine streams them in; otherwise k chunk launches); 0 = zero-copy, the kernel reads the records over PCIe itself")
     args = ap.parse_args()
@@ -330,7 +344,7 @@ def main() -> None:
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__),
                "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--instances", str(args.instances),
-               "--chunks", str(args.chunks)]
+               "--chunks", str(args.chunks)] + (["--full-records"] if args.full_records else [])
         raise SystemExit(subprocess.call(cmd))
     run_ours(args, rank, local_rank, world)
 
