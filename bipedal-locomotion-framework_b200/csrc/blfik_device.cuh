@@ -872,6 +872,16 @@ __device__ __forceinline__ bool qp_setup(const Layout& L, const WM& w, double si
         w.xb[i] = v;
     }
     __syncwarp();
+    if (!polish && me > 0) {
+        // Every iterate is N r + x_b with C N = 0, so C x_b - b is the equality residual of whatever the solve returns.  A
+        // dependent row whose pivot happened to stay above the floor (rounding noise) slips through the test above: this
+        // one catches contradicting rows whatever the factorisation made of them.
+        for (int r = lane; r < me; r += 32) {
+            double res = -bvec[r];
+            for (int j = 0; j < nv; j++) res += w.Cs[r * LD + j] * w.xb[j];
+            if (!(fabs(res) <= 1e-6 * (1.0 + fabs(bvec[r])))) inconsistent = true;
+        }
+    }
     if (__any_sync(kFull, inconsistent)) ok = false;
     return ok;
 }

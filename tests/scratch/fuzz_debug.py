@@ -10,7 +10,7 @@ exec(pre.replace("def test_random_task_mixes_vs_oracle(seed):","def build(seed):
 for seed in [int(a) for a in sys.argv[1:]]:
     m,tasks,o,sps,p0,q0,s0,kinds=ns['build'](seed)
     N=len(p0)
-    prob=capi.Problem(capi.Model(m),tasks,N)
+    prob=capi.Problem(capi.Model(m),tasks,N); prob.set_kernel_path(int(os.environ.get("KPATH","0")))
     prob.set_state(p0,q0,s0)
     for t,sp in enumerate(sps):
         if sp is not None: prob.set_setpoint(t,sp)
