@@ -298,7 +298,7 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": achieved_tf / fp64_peak if fp64_peak else None,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r1_v5_fast_kernel_ncu_summary.txt
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r1_v6_fast_kernel_ncu_summary.txt
                          "traffic": 89.11e6 if (fast and n_local == 65536) else None,
                          "peak_source": "measured live by blfik_measure_fp64_peak (dependency-free DFMA loop); "
                                         "MEASURED_PEAKS.json has no FP64 figure",
