@@ -299,7 +299,7 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
             "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": achieved_tf / fp64_peak if fp64_peak else None,
                          # dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r1_v6_fast_kernel_ncu_summary.txt
-                         "traffic": 89.11e6 if (fast and n_local == 65536) else None,
+                         "traffic": 90.45e6 if (fast and n_local == 65536) else None,
                          "peak_source": "measured live by blfik_measure_fp64_peak (dependency-free DFMA loop); "
                                         "MEASURED_PEAKS.json has no FP64 figure",
                          "kernel": "blfik_tick_fast_kernel<29,18>" if fast else "blfik_tick_kernel", "flops_per_launch": flops_launch,
