@@ -129,6 +129,66 @@ __global__ void __launch_bounds__(256) blfik_integrate_kernel(int n, long long N
                          nu + (size_t)(n + 6) * robot, dt, lane);
 }
 
+// Coefficients of the quintic splines of one task (Math::QuinticSpline, QuinticSpline.h:266-415), one thread per robot and
+// coordinate.  The interior-knot system is block tridiagonal with 2 x 2 blocks that depend on the knot times only, so the
+// host eliminates the blocks once (fac[i] = L_i, M_i = L_i D'_{i-1}^-1, D'_i^-1, U_i) and a thread runs the two sweeps on
+// its own right-hand side.  The sweeps keep their intermediates in the coefficient slots the thread owns:
+// coef[robot][interval][k][coordinate], interval j starting at knot j.
+__global__ void __launch_bounds__(128) blfik_spline_coefficients_kernel(long long N, int nk, const double* __restrict__ times,
+                                                                        const double* __restrict__ fac, const double* __restrict__ x,
+                                                                        const double* __restrict__ bc, double* __restrict__ coef)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= N * 3) return;
+    const long long robot = idx / 3;
+    const int c = (int)(idx - robot * 3);
+    const double* xr = x + (size_t)robot * nk * 3 + c;
+    double* cf = coef + (size_t)robot * (nk - 1) * 18 + c;
+    double v0 = 0.0, a0 = 0.0, vf = 0.0, af = 0.0;
+    if (bc) {
+        const double* b = bc + (size_t)robot * 12 + c;
+        v0 = b[0], a0 = b[3], vf = b[6], af = b[9];
+    }
+    const int m = nk - 2;
+    double p0 = 0.0, p1 = 0.0;
+    for (int i = 0; i < m; i++) {   // forward sweep: r'_i = r_i - M_i r'_{i-1}
+        const double Tp = times[i + 1] - times[i], Tn = times[i + 2] - times[i + 1];
+        const double dp = xr[3 * (i + 1)] - xr[3 * i], dn = xr[3 * (i + 2)] - xr[3 * (i + 1)];
+        const double ip = 1.0 / Tp, in = 1.0 / Tn;
+        double r0 = 60.0 * (dn * in * in * in - dp * ip * ip * ip);
+        double r1 = -360.0 * (dp * ip * ip * ip * ip + dn * in * in * in * in);
+        const double* f = fac + 16 * i;
+        if (i == 0) r0 -= f[0] * v0 + f[1] * a0, r1 -= f[2] * v0 + f[3] * a0;
+        if (i == m - 1) r0 -= f[12] * vf + f[13] * af, r1 -= f[14] * vf + f[15] * af;
+        if (i > 0) {
+            const double t0 = r0 - (f[4] * p0 + f[5] * p1), t1 = r1 - (f[6] * p0 + f[7] * p1);
+            r0 = t0, r1 = t1;
+        }
+        cf[18 * (i + 1) + 9] = r0, cf[18 * (i + 1) + 12] = r1;
+        p0 = r0, p1 = r1;
+    }
+    double vn = vf, an = af;
+    for (int i = m - 1; i >= 0; i--) {   // back substitution: (v, a)_i = D'_i^-1 (r'_i - U_i (v, a)_{i+1})
+        const double* f = fac + 16 * i;
+        double r0 = cf[18 * (i + 1) + 9], r1 = cf[18 * (i + 1) + 12];
+        if (i < m - 1) r0 -= f[12] * vn + f[13] * an, r1 -= f[14] * vn + f[15] * an;
+        vn = f[8] * r0 + f[9] * r1, an = f[10] * r0 + f[11] * r1;
+        cf[18 * (i + 1) + 3] = vn, cf[18 * (i + 1) + 6] = 0.5 * an;
+    }
+    cf[3] = v0, cf[6] = 0.5 * a0;
+    for (int j = 0; j < nk - 1; j++) {   // the interval polynomials from their two end states
+        const double T = times[j + 1] - times[j], iT = 1.0 / T;
+        const double x0 = xr[3 * j], d = xr[3 * (j + 1)] - x0;
+        const double vs = cf[18 * j + 3], as = 2.0 * cf[18 * j + 6];
+        const double ve = j + 1 <= nk - 2 ? cf[18 * (j + 1) + 3] : vf, ae = j + 1 <= nk - 2 ? 2.0 * cf[18 * (j + 1) + 6] : af;
+        const double iT3 = iT * iT * iT;
+        cf[18 * j] = x0;
+        cf[18 * j + 9] = 0.5 * iT3 * (20.0 * d - (8.0 * ve + 12.0 * vs) * T - (3.0 * as - ae) * T * T);
+        cf[18 * j + 12] = 0.5 * iT3 * iT * (-30.0 * d + (14.0 * ve + 16.0 * vs) * T + (3.0 * as - 2.0 * ae) * T * T);
+        cf[18 * j + 15] = 0.5 * iT3 * iT * iT * (12.0 * d - 6.0 * (ve + vs) * T - (as - ae) * T * T);
+    }
+}
+
 __global__ void blfik_count_unsolved_kernel(const int* status, long long N, unsigned long long* out)
 {
     unsigned long long c = 0;
@@ -191,6 +251,8 @@ struct HostTask {
     double* d_traj_phase = nullptr;
     double* d_mj_target = nullptr;   // minimum-jerk generator: target set-points [N][set-point length]
     double mj_t0 = 0.0, mj_T = 0.0;  // mj_T == 0: off
+    int sp_nk = 0, sp_cap = 0;       // quintic-spline generator: knots in force (0: off), knots the buffers hold
+    double *d_sp_times = nullptr, *d_sp_fac = nullptr, *d_sp_coef = nullptr;
     bool setpoint_set = false;
     double* d_setpoint = nullptr;
     double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
@@ -494,6 +556,8 @@ static int refresh_tasks(blfik_problem* p)
         d.traj_phase = h.d_traj_phase, d.traj_omega = h.d_traj_phase ? h.traj_omega : 0.0;
         for (int c = 0; c < 6; c++) d.traj_amp[c] = h.traj_amp[c];
         d.mj_target = h.mj_T > 0.0 ? h.d_mj_target : nullptr, d.mj_t0 = h.mj_t0, d.mj_T = h.mj_T;
+        d.sp_nk = h.sp_nk, d.sp_times = h.d_sp_times, d.sp_coef = h.d_sp_coef;
+        d.gen = (d.traj_omega != 0.0 ? 1 : 0) | (d.mj_target ? 2 : 0) | (h.sp_nk >= 2 ? 4 : 0);
         for (int c = 0; c < 9; c++) d.Fr[c] = (c % 4 == 0) ? 1.0 : 0.0;
         for (int c = 0; c < 3; c++) d.Fp[c] = 0.0;
         d.flink2 = -1, d.thr = h.d.distance_threshold > 0 ? h.d.distance_threshold : 0.001;
@@ -737,6 +801,7 @@ extern "C" void blfik_problem_destroy(blfik_problem* p)
     cudaSetDevice(p->device);
     if (p->stream) cudaStreamSynchronize(p->stream);
     for (void* a : p->allocs) cudaFree(a);
+    for (HostTask& h : p->tasks) cudaFree(h.d_sp_times), cudaFree(h.d_sp_fac), cudaFree(h.d_sp_coef);
     if (p->h2d_stream) {
         cudaStreamSynchronize(p->h2d_stream), cudaStreamSynchronize(p->d2h_stream);
         for (int c = 0; c < kMaxChunks; c++) cudaEventDestroy(p->ev_in[c]), cudaEventDestroy(p->ev_done[c]);
@@ -868,6 +933,105 @@ extern "C" int blfik_set_setpoint_minimum_jerk(blfik_problem* p, int32_t t, cons
     return BLFIK_OK;
 }
 
+// 2 x 2 helpers for the block elimination of the spline system
+static void m22_mul(const double* a, const double* b, double* o)
+{
+    o[0] = a[0] * b[0] + a[1] * b[2], o[1] = a[0] * b[1] + a[1] * b[3];
+    o[2] = a[2] * b[0] + a[3] * b[2], o[3] = a[2] * b[1] + a[3] * b[3];
+}
+static bool m22_inv(const double* a, double* o)
+{
+    const double det = a[0] * a[3] - a[1] * a[2];
+    const double scale = std::fabs(a[0] * a[3]) + std::fabs(a[1] * a[2]);
+    if (!(std::fabs(det) > 1e-13 * scale)) return false;
+    o[0] = a[3] / det, o[1] = -a[1] / det, o[2] = -a[2] / det, o[3] = a[0] / det;
+    return true;
+}
+
+extern "C" int blfik_set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_knots, const double* times, const double* positions,
+                                         const double* boundary, int32_t mem)
+{
+    CHECK_P(p, "blfik_set_setpoint_spline");
+    CHECK_TASK(p, t, "blfik_set_setpoint_spline");
+    HostTask& h = p->tasks[t];
+    if (h.d.type != BLFIK_TASK_SE3 && h.d.type != BLFIK_TASK_R3 && h.d.type != BLFIK_TASK_COM)
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] task %d is not an SE3 / R3 / CoM task", t);
+    if (n_knots == 0) {   // switch the generator off
+        h.sp_nk = 0;
+        p->tasks_dirty = true;
+        return BLFIK_OK;
+    }
+    if (n_knots < 2)   // Spline.h:338-342
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] the number of knots has to be at least 2");
+    if (n_knots > BLFIK_MAX_SPLINE_KNOTS)
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] at most %d knots", BLFIK_MAX_SPLINE_KNOTS);
+    if (!times || !positions) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] null times or positions");
+    if (!h.setpoint_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_set_setpoint_spline] the set point of task %d has not been set", t);
+    for (int i = 0; i + 1 < n_knots; i++) {
+        if (times[i + 1] == times[i])   // Spline.h:444-448
+            return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] two consecutive knots have the same time coordinate");
+        if (!(times[i + 1] > times[i])) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] the knot times must increase");
+    }
+    // block elimination of the interior-knot system (times only): per interior knot L, M = L D'^-1 of the previous knot, D'^-1, U
+    const int m = n_knots - 2;
+    std::vector<double> fac((size_t)16 * (m > 0 ? m : 1), 0.0);
+    double Dprev_inv[4] = {0, 0, 0, 0}, Uprev[4] = {0, 0, 0, 0};
+    for (int i = 0; i < m; i++) {
+        const double Tp = times[i + 1] - times[i], Tn = times[i + 2] - times[i + 1];
+        double* f = &fac[(size_t)16 * i];
+        const double L[4] = {-24.0 / (Tp * Tp), -3.0 / Tp, -168.0 / (Tp * Tp * Tp), -24.0 / (Tp * Tp)};
+        double D[4] = {-36.0 / (Tp * Tp) + 36.0 / (Tn * Tn), 9.0 / Tp + 9.0 / Tn,
+                       -192.0 / (Tp * Tp * Tp) - 192.0 / (Tn * Tn * Tn), 36.0 / (Tp * Tp) - 36.0 / (Tn * Tn)};
+        const double U[4] = {24.0 / (Tn * Tn), -3.0 / Tn, -168.0 / (Tn * Tn * Tn), 24.0 / (Tn * Tn)};
+        for (int k = 0; k < 4; k++) f[k] = L[k], f[12 + k] = U[k];
+        if (i > 0) {
+            double MU[4];
+            m22_mul(L, Dprev_inv, f + 4);
+            m22_mul(f + 4, Uprev, MU);
+            for (int k = 0; k < 4; k++) D[k] -= MU[k];
+        }
+        if (!m22_inv(D, f + 8)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] the knot times give a singular spline system");
+        for (int k = 0; k < 4; k++) Dprev_inv[k] = f[8 + k], Uprev[k] = U[k];
+    }
+    if (n_knots > h.sp_cap) {
+        CU(cudaStreamSynchronize(p->stream));   // a tick in flight may still read the old buffers
+        cudaFree(h.d_sp_times), cudaFree(h.d_sp_fac), cudaFree(h.d_sp_coef);
+        h.d_sp_times = h.d_sp_fac = h.d_sp_coef = nullptr, h.sp_cap = 0, h.sp_nk = 0;
+        p->tasks_dirty = true;
+        CU(cudaMalloc((void**)&h.d_sp_times, (size_t)n_knots * sizeof(double)));
+        CU(cudaMalloc((void**)&h.d_sp_fac, (size_t)16 * n_knots * sizeof(double)));
+        CU(cudaMalloc((void**)&h.d_sp_coef, (size_t)p->N * (n_knots - 1) * 18 * sizeof(double)));
+        h.sp_cap = n_knots;
+    }
+    const size_t npos = (size_t)p->N * n_knots * 3, nbc = (size_t)p->N * 12;
+    const double *d_x = positions, *d_bc = boundary;
+    double* stage = nullptr;
+    if (mem != BLFIK_MEM_DEVICE) {
+        CU(cudaMalloc((void**)&stage, (npos + nbc) * sizeof(double)));
+        cudaMemcpyAsync(stage, positions, npos * sizeof(double), cudaMemcpyHostToDevice, p->stream);
+        if (boundary) cudaMemcpyAsync(stage + npos, boundary, nbc * sizeof(double), cudaMemcpyHostToDevice, p->stream);
+        d_x = stage, d_bc = boundary ? stage + npos : nullptr;
+    }
+    cudaMemcpyAsync(h.d_sp_times, times, (size_t)n_knots * sizeof(double), cudaMemcpyHostToDevice, p->stream);
+    cudaMemcpyAsync(h.d_sp_fac, fac.data(), fac.size() * sizeof(double), cudaMemcpyHostToDevice, p->stream);
+    const long long threads = (long long)p->N * 3;
+    blfik_spline_coefficients_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, p->stream>>>(p->N, n_knots, h.d_sp_times, h.d_sp_fac, d_x, d_bc,
+                                                                                             h.d_sp_coef);
+    p->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (stage) {   // the pageable sources (times, fac, positions) are consumed before this returns
+        if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+        cudaFree(stage);
+    } else if (e == cudaSuccess) {
+        e = cudaStreamSynchronize(p->stream);   // times and fac are host vectors that die with this call
+    }
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_set_setpoint_spline] %s", cudaGetErrorString(e));
+    h.sp_nk = n_knots;
+    h.traj_omega = 0.0;   // the sinusoidal generator stands alone; the minimum-jerk one keeps the orientation of an SE3 task
+    p->tasks_dirty = true;
+    return BLFIK_OK;
+}
+
 extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const double* amplitude, double period, const double* phase, int32_t mem)
 {
     CHECK_P(p, "blfik_set_setpoint_trajectory");
@@ -886,7 +1050,7 @@ extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const 
     CU(cudaMemcpyAsync(h.d_traj_phase, phase, (size_t)p->N * sizeof(double), kind_in(mem), p->stream));
     for (int c = 0; c < 6; c++) h.traj_amp[c] = amplitude[c];
     h.traj_omega = 6.283185307179586476925286766559 / period;
-    h.mj_T = 0.0;   // one generator per task
+    h.mj_T = 0.0, h.sp_nk = 0;   // this generator stands alone
     p->tasks_dirty = true;
     return BLFIK_OK;
 }

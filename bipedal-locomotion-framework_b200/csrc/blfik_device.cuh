@@ -70,6 +70,12 @@ struct DevTask {
     double mj_t0, mj_T;
     int exo_pos, exo_ori;    // exogenous feedback (SE3Task.cpp:261-268, CoMTask.cpp:192-195): controller state from the record
     int fb_off;              // where the feedback p(3) [q(4)] sits inside the record (= the set-point length)
+    int gen;                 // attached set-point generators: 1 sinusoidal, 2 minimum jerk, 4 quintic spline (0: none)
+    // optional multi-knot quintic spline for the linear part (Math::QuinticSpline, Spline.h / QuinticSpline.h): knot times
+    // shared by the robots, one polynomial per interval and robot, coefficients [N][sp_nk - 1][6][3] in interval-local time
+    int sp_nk;
+    const double* sp_times;  // device [sp_nk]
+    const double* sp_coef;   // device, written by blfik_spline_coefficients_kernel
 };
 
 struct Settings {
@@ -500,12 +506,42 @@ __device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long lon
 // out-of-line call so that its registers do not weigh on the tick kernels.
 __device__ __forceinline__ const double* traj_eval(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
 {
-    if ((!tk.mj_target && tk.traj_omega == 0.0) || !sp) return sp;
+    if (tk.gen == 0 || !sp) return sp;
     return traj_eval_slow(tk, robot, t, sp, spl);
+}
+// Linear part of the set-point from the task's quintic spline: position = the spline, feed-forward = stored + its derivative.
+// Outside the knots the end states hold, derivative included (Spline.h:607-625).
+__device__ __forceinline__ void spline_eval(const DevTask& tk, long long robot, double t, const double* sp, double* spl, int vo)
+{
+    const int nk = tk.sp_nk;
+    int seg = 0;
+    double tl = 0.0;
+    if (t >= tk.sp_times[nk - 1]) {
+        seg = nk - 2, tl = tk.sp_times[nk - 1] - tk.sp_times[nk - 2];
+    } else if (t >= tk.sp_times[0]) {
+        int lo = 0, hi = nk - 1;          // times[lo] <= t < times[hi]
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (t >= tk.sp_times[mid]) lo = mid; else hi = mid;
+        }
+        seg = lo, tl = t - tk.sp_times[lo];
+    }
+    const double* c = tk.sp_coef + ((size_t)robot * (nk - 1) + seg) * 18;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const double c1 = c[3 + k], c2 = c[6 + k], c3 = c[9 + k], c4 = c[12 + k], c5 = c[15 + k];
+        spl[k] = c[k] + tl * (c1 + tl * (c2 + tl * (c3 + tl * (c4 + tl * c5))));
+        spl[vo + k] = sp[vo + k] + c1 + tl * (2.0 * c2 + tl * (3.0 * c3 + tl * (4.0 * c4 + tl * 5.0 * c5)));
+    }
 }
 __device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
 {
-    if (tk.mj_target && sp) {
+    if ((tk.gen & 4) && !(tk.gen & 2)) {
+        for (int c = 0; c < tk.fb_off && c < 13; c++) spl[c] = sp[c];
+        spline_eval(tk, robot, t, sp, spl, tk.type == T_SE3 ? 7 : 3);
+        return spl;
+    }
+    if (tk.gen & 2) {
         // s(tau) = 10 tau^3 - 15 tau^4 + 6 tau^5 (SO3Planner.tpp:96-105 with zero boundary conditions), time clamped to the
         // segment as SO3Planner::advance does (:289-292): x(t) = x0 + s (x1 - x0), R(t) = Exp(s Log(R1 R0^-1)) R0 -- the
         // inertial-frame ("Right trivialization") form that matches the MIXED angular velocity, w(t) = sdot Log(R1 R0^-1)
@@ -519,7 +555,9 @@ __device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long lon
         const double sd = (tau > 0.0 && tau < 1.0) ? 30.0 * t2 * (1.0 - 2.0 * tau + t2) / tk.mj_T : 0.0;
         const bool lin = tk.type == T_SE3 || tk.type == T_COM || tk.type == T_R3;
         const int qo = tk.type == T_SE3 ? 3 : 0, vo = tk.type == T_SE3 ? 7 : 3, wo = tk.type == T_SE3 ? 10 : 4;
-        if (lin) {
+        if (lin && (tk.gen & 4)) {   // the spline moves the origin, this generator the orientation (swing foot)
+            spline_eval(tk, robot, t, sp, spl, vo);
+        } else if (lin) {
 #pragma unroll
             for (int c = 0; c < 3; c++) {
                 const double d = tg[c] - sp[c];
@@ -542,7 +580,7 @@ __device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long lon
         }
         return spl;
     }
-    if (tk.traj_omega == 0.0 || !sp) return sp;
+    if (!(tk.gen & 1)) return sp;
     for (int c = 0; c < tk.sp_len && c < 13; c++) spl[c] = sp[c];
     double sn, cs;
     sincos(tk.traj_omega * t + tk.traj_phase[robot], &sn, &cs);

@@ -205,6 +205,27 @@ int blfik_set_setpoint_trajectory(blfik_problem* problem, int32_t task, const do
  * `target` is read.  duration <= 0 switches it off; it replaces a sinusoidal generator on the same task and vice versa. */
 int blfik_set_setpoint_minimum_jerk(blfik_problem* problem, int32_t task, const double* target,
                                     double duration, int32_t mem);
+
+/* Multi-knot quintic spline as set-point producer on the device, for the linear part of an SE3 / CoM / R3 task: what the
+ * reference's callers obtain from Math::QuinticSpline<Eigen::Vector3d> (src/Math/include/BipedalLocomotion/Math/Spline.h:
+ * setKnots :323-383, setInitialConditions / setFinalConditions :385-436, evaluatePoint :594-644; QuinticSpline.h:266-415)
+ * and pass to setSetPoint every period (e.g. Planners::SwingFootPlanner, the CoM trajectory of the balancing application).
+ *   times      host [n_knots], strictly increasing, on the problem's clock (blfik_set_time / blfik_get_time), shared by
+ *              the robots;
+ *   positions  [N][n_knots][3], the knots of every robot;
+ *   boundary   [N][4][3]: velocity and acceleration at the first knot, velocity and acceleration at the last one
+ *              (NULL: all zero);
+ * `mem` tells where positions and boundary live.  The velocities and accelerations at the interior knots are those that
+ * make the third and fourth derivative continuous (the reference's linear system, solved here on the device for all
+ * robots at once).  At a tick with time t the position of the set-point is the spline, its feed-forward velocity the stored
+ * one plus the spline's derivative; before the first knot and from the last knot on the end states hold, derivative
+ * included, as Spline::evaluatePoint does.  The orientation of an SE3 task keeps what drives it: the stored set-point or
+ * the minimum-jerk generator (swing foot: spline for the origin, SO3Planner for the orientation).  n_knots == 0 switches
+ * the spline off; n_knots == 1 and equal consecutive times are refused as by the reference; it replaces a sinusoidal
+ * generator on the same task and vice versa.                                                                     */
+#define BLFIK_MAX_SPLINE_KNOTS 1024
+int blfik_set_setpoint_spline(blfik_problem* problem, int32_t task, int32_t n_knots, const double* times,
+                              const double* positions, const double* boundary, int32_t mem);
 int blfik_set_time(blfik_problem* problem, double t);
 double blfik_get_time(const blfik_problem* problem);
 

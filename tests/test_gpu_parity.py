@@ -1036,6 +1036,102 @@ def test_minimum_jerk_setpoint_generator(path):
     prob.close(), whole.close()
 
 
+@pytest.mark.parametrize("path", PATHS)
+def test_quintic_spline_setpoint_generator(path):
+    """blfik_set_setpoint_spline: the CoM follows a five-knot quintic spline with non-zero boundary velocity and
+    acceleration, a foot (SE3) a three-knot one (lift, apex, landing) while the minimum-jerk generator turns it -- the
+    reference's Math::QuinticSpline + SO3Planner pair, both evaluated on the device.  Checked (a) on the assembled
+    equality right-hand side at chosen times (before the first knot, on knots, inside intervals, after the end) against
+    the oracle fed with the host spline (oracle/spline.py), (b) in a lock-step closed loop, (c) one multi-tick launch
+    against the tick-by-tick run, (d) on the refusals of Spline::setKnots."""
+    from oracle.spline import quintic_spline_coefficients, spline_evaluate
+    w = W.config(5)
+    N, NT = 16, 40
+    dt = w.dt
+    inp = W.synth_inputs(w, N, 5)
+    rng = np.random.default_rng(29)
+    t_com = np.array([0.002, 0.009, 0.013, 0.024, 0.030])
+    t_foot = np.array([0.0, 0.014, 0.028])
+    x_com = inp.setpoints[0][:, None, :3] + np.cumsum(rng.uniform(-0.0005, 0.0005, (N, 5, 3)), axis=1)
+    bc_com = np.stack([rng.uniform(-0.02, 0.02, (N, 3)), rng.uniform(-1.0, 1.0, (N, 3)), np.zeros((N, 3)), np.zeros((N, 3))], axis=1)
+    x_foot = np.repeat(inp.setpoints[1][:, None, :3], 3, axis=1)
+    x_foot[:, 1] += [0.0005, 0.0, 0.001]
+    x_foot[:, 2] += [0.001, 0.0, 0.0]
+    x_foot[:, 1:] += rng.uniform(-1e-4, 1e-4, (N, 2, 3))
+    foot_target = inp.setpoints[1].copy()
+    foot_target[:, 3:7] = W.quat_mul(W.so3_exp(rng.uniform(-0.01, 0.01, (N, 3))), foot_target[:, 3:7])
+    dur = t_foot[-1]
+    co_com = [quintic_spline_coefficients(t_com, x_com[i], *bc_com[i])[0] for i in range(N)]
+    co_foot = [quintic_spline_coefficients(t_foot, x_foot[i])[0] for i in range(N)]
+
+    def setpoints_at(t):
+        sps = [None if sp is None else sp.copy() for sp in inp.setpoints]
+        sps[1] = _min_jerk_setpoint(T.TASK_SE3, inp.setpoints[1], foot_target, t / dur, dur)   # orientation part
+        for i in range(N):
+            pos, vel, _ = spline_evaluate(t_com, co_com[i], t)
+            sps[0][i, :3], sps[0][i, 3:6] = pos, inp.setpoints[0][i, 3:6] + vel
+            pos, vel, _ = spline_evaluate(t_foot, co_foot[i], t)
+            sps[1][i, :3], sps[1][i, 7:10] = pos, inp.setpoints[1][i, 7:10] + vel
+        return sps
+
+    model, prob = make(w.model, w.tasks, N, path)
+    _, whole = make(w.model, w.tasks, N, path)
+    with pytest.raises(capi.BlfikError):
+        prob.set_setpoint_spline(0, t_com, x_com, bc_com)            # the set-point comes first
+    for pr in (prob, whole):
+        pr.set_inputs(inp)
+        pr.set_setpoint_minimum_jerk(1, foot_target, dur)
+        pr.set_setpoint_spline(0, t_com, x_com, bc_com)
+        pr.set_setpoint_spline(1, t_foot, x_foot)
+    for bad in (lambda: prob.set_setpoint_spline(6, t_foot, x_foot),                      # joint tasks have no such generator
+                lambda: prob.set_setpoint_spline(5, t_foot, x_foot),                      # nor has SO3
+                lambda: prob.set_setpoint_spline(0, t_foot[:1], x_foot[:, :1]),           # Spline.h:338-342
+                lambda: prob.set_setpoint_spline(0, [0.0, 0.01, 0.01], x_foot),           # Spline.h:444-448
+                lambda: prob.set_setpoint_spline(0, [0.0, 0.02, 0.01], x_foot)):
+        with pytest.raises(capi.BlfikError):
+            bad()
+    o = Oracle(w.model, w.tasks)
+    me = prob.me
+    # (a) the assembled right-hand side at chosen times
+    prob.debug_enable(True)
+    for t in (-0.004, 0.0, 0.002, 0.0055, 0.009, 0.014, 0.0291, 0.030, 0.05):
+        prob.set_time(t)
+        prob.tick(1, dt, integrate=False)
+        be = prob.debug_get(capi.DEBUG_BEQ)
+        sps = setpoints_at(t)
+        for i in range(0, N, 3):
+            _, _, _, _, u = o.assemble(inp.base_pos[i], inp.base_quat[i], inp.s[i], [None if sp is None else sp[i] for sp in sps])
+            assert np.abs(be[i] - u[:me]).max() <= 1e-10 * (1 + np.abs(u[:me]).max()), t
+    prob.debug_enable(False)
+    prob.set_time(0.0)
+    # (b) lock step
+    p, q, s = inp.base_pos.copy(), inp.base_quat.copy(), inp.s.copy()
+    for k in range(NT):
+        pr_, qr_, sr_ = p.copy(), q.copy(), s.copy()
+        nur, str_, _ = o.tick_batch(pr_, qr_, sr_, setpoints_at(k * dt), dt_integrate=dt)
+        prob.tick(1, dt, integrate=True, warm_start=True)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        p, q, s = prob.get_state()
+        ok = (st == 0) & (str_ == 0)
+        assert ok.mean() > 0.9
+        assert np.abs(nu - nur)[ok].max() <= TOL_NU
+    assert NT * dt > t_com[-1]
+    # (c) one launch of NT ticks
+    whole.tick(NT, dt, integrate=True, warm_start=True)
+    pw, qw, sw = whole.get_state()
+    assert np.abs(sw - s).max() < 1e-9 and np.abs(pw - p).max() < 1e-9
+    # a longer spline on the same task regrows the buffers; switching it off leaves the other generator in force
+    t_long = np.linspace(0.0, 0.04, 33)
+    x_long = inp.setpoints[1][:, None, :3] + 1e-4 * np.sin(40.0 * t_long)[None, :, None] * np.ones((N, 1, 3))
+    prob.set_setpoint_spline(1, t_long, x_long)
+    prob.tick(1, dt, integrate=False)
+    prob.set_setpoint_spline(1, None, None)
+    prob.set_setpoint_spline(0, None, None)
+    prob.tick(1, dt, integrate=False)
+    prob.close(), whole.close()
+
+
 @pytest.mark.parametrize("seed", range(int(os.environ.get("BLFIK_FUZZ_SEEDS", "10"))))
 def test_random_task_mixes_vs_oracle(seed):
     """Randomised problems: a random revolute tree (14..40 joints, so both kernels are reached), a random mix of hard and weighted
