@@ -106,6 +106,56 @@ class IKLinearTask:
         self._set_point_set = True
         return True
 
+    _spline_ok = False         # SE3Task, CoMTask, R3Task: the origin of the set-point can follow a quintic spline on the device
+
+    def set_set_point_spline(self, spline, positions=None, boundary=None):
+        """Batch extension (no counterpart in the reference, where a Math::QuinticSpline is evaluated on the host and its
+        point passed to setSetPoint every period): the origin of this task's set-point follows a quintic spline evaluated on
+        the device at the solver's time (QPInverseKinematics.set_time; blfik_set_setpoint_spline).  ``spline`` is a
+        ``math.QuinticSpline`` (every robot the same trajectory), a list of N of them with the same knot times, or the knot
+        times [n_knots] together with ``positions`` [N, n_knots, 3] and ``boundary`` [N, 4, 3]; None switches it off."""
+        name = type(self).__name__
+        if not self._spline_ok:
+            log().error("[%s::setSetPointSpline] The task has no position set-point a spline could drive.", name)
+            return False
+        if spline is None:
+            self._spline, self._spline_version = None, self._spline_version + 1
+            return True
+        N = self._kin_dyn.N
+        if hasattr(spline, "knots") or (isinstance(spline, (list, tuple)) and len(spline) and hasattr(spline[0], "knots")):
+            group = [spline] * N if hasattr(spline, "knots") else list(spline)
+            if len(group) != N:
+                log().error("[%s::setSetPointSpline] One spline per robot is expected. Expected: %d. Given: %d.", name, N, len(group))
+                return False
+            parts = [g.knots() for g in group]
+            if any(k[0] is None or k[1] is None or k[1].shape[1] != 3 for k in parts):
+                log().error("[%s::setSetPointSpline] Every spline needs its knots set, in R^3.", name)
+                return False
+            if any(len(k[0]) != len(parts[0][0]) or np.any(k[0] != parts[0][0]) for k in parts):
+                log().error("[%s::setSetPointSpline] The splines of the robots must share their knot times.", name)
+                return False
+            times = parts[0][0]
+            positions = np.stack([k[1] for k in parts])
+            boundary = np.stack([np.zeros((4, 3)) if k[2] is None else k[2] for k in parts])
+        else:
+            times = np.asarray(spline, dtype=np.float64).reshape(-1)
+            positions = np.asarray(positions, dtype=np.float64)
+            boundary = None if boundary is None else np.asarray(boundary, dtype=np.float64)
+            if positions.shape != (N, len(times), 3) or (boundary is not None and boundary.shape != (N, 4, 3)):
+                log().error("[%s::setSetPointSpline] positions must be [N, n_knots, 3] and boundary [N, 4, 3].", name)
+                return False
+        if len(times) < 2:
+            log().error("[Spline::setKnots] The number of knots has to be at least 2.")
+            return False
+        if np.any(np.diff(times) <= 0.0):
+            log().error("[Splines::computePhasesDuration] Two consecutive points have the same time coordinate, or the times decrease.")
+            return False
+        self._spline, self._spline_version = (times.copy(), positions.copy(), None if boundary is None else boundary.copy()), self._spline_version + 1
+        return True
+
+    _spline = None
+    _spline_version = 0
+
     _fb_len = 0
     _fb_init = ()
 
@@ -159,6 +209,7 @@ def _quat_of(R):
 class SE3Task(IKLinearTask):
     """SE3Task.cpp:114-214 (keys frame_name, kp_linear, kp_angular, mask), :231-321 (update), :251-258 (controller mode)"""
     _sp_len = 13
+    _spline_ok = True
 
     class Mode:
         Enable, Disable = "Enable", "Disable"
@@ -234,6 +285,7 @@ class SE3Task(IKLinearTask):
 class CoMTask(IKLinearTask):
     """CoMTask.cpp:107-162 (keys kp_linear, mask), :171-235"""
     _sp_len = 6
+    _spline_ok = True
 
     def initialize(self, param_handler):
         if not self._common_initialize(param_handler):
@@ -311,6 +363,7 @@ class SO3Task(IKLinearTask):
 class R3Task(IKLinearTask):
     """R3Task.cpp:60-176 (keys frame_name, kp_linear, mask), :178-243"""
     _sp_len = 6
+    _spline_ok = True
 
     def initialize(self, param_handler):
         if not self._common_initialize(param_handler):
@@ -700,7 +753,7 @@ class QPInverseKinematics:
                 return False
             for e, sp in zip(native, specs):
                 e["sp_version"], e["gains_version"], e["weight"] = -1, e["task"]._gains_version, None if sp.weight is None else np.array(sp.weight)
-                e["fb_version"] = 0
+                e["fb_version"] = e["spline_version"] = 0
             self._kin_dyn, self._state_version = kd, -1
         self._finalized = True
         return True
@@ -724,6 +777,16 @@ class QPInverseKinematics:
             if task._sp_len and e["sp_version"] != task._sp_version:
                 prob.set_setpoint(t, task._sp)
                 e["sp_version"] = task._sp_version
+            if task._spline_ok and e.get("spline_version", 0) != task._spline_version:
+                try:
+                    if task._spline is None:
+                        prob.set_setpoint_spline(t, None, None)
+                    else:
+                        prob.set_setpoint_spline(t, *task._spline)
+                except capi.BlfikError as err:
+                    log().error("%s Unable to set the spline of the task named %s: %s", prefix, e["name"], err)
+                    return False
+                e["spline_version"] = task._spline_version
             if task._fb_len and task._fb is not None and e.get("fb_version", 0) != task._fb_version:
                 prob.set_feedback(t, task._fb)
                 e["fb_version"] = task._fb_version
@@ -764,6 +827,14 @@ class QPInverseKinematics:
         return None if self._nu is None else self._nu[0]
 
     # ---- batch extensions
+    def set_time(self, t):
+        """time at which the on-device set-point generators (set_set_point_spline) are evaluated by the next advance()"""
+        if self._problem is None:
+            log().error("[QPInverseKinematics::setTime] Please call finalize() first.")
+            return False
+        self._problem.set_time(t.total_seconds() if hasattr(t, "total_seconds") else float(t))
+        return True
+
     def get_batch_output(self):
         """[N, 6 + n] velocities of the last advance()"""
         return self._nu

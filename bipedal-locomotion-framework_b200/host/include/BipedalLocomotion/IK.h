@@ -10,6 +10,7 @@
 #define BLF_B200_IK_H
 
 #include <BipedalLocomotion/KinDynBatch.h>
+#include <BipedalLocomotion/Math.h>
 
 namespace BipedalLocomotion
 {
@@ -77,6 +78,60 @@ public:
     virtual std::size_t feedbackLength() const { return 0; }
     const std::vector<double>& feedbackBuffer() const { return m_fb; }
     unsigned long feedbackVersion() const { return m_fbVersion; }
+    /** SE3Task, CoMTask, R3Task: the origin of the set-point can follow a quintic spline evaluated on the device at the
+     *  solver's time (QPInverseKinematics::setTime; blfik_set_setpoint_spline) instead of a Math::QuinticSpline evaluated
+     *  on the host whose point goes to setSetPoint every period.  One spline per robot, all with the same knot times. */
+    virtual bool acceptsSetPointSpline() const { return false; }
+    bool setSetPointSpline(const std::vector<Math::QuinticSpline<Vector3d>>& splines)
+    {
+        const std::size_t N = m_kinDyn ? m_kinDyn->getBatchSize() : 0;
+        if (!acceptsSetPointSpline()) {
+            log()->error("[{}::setSetPointSpline] The task has no position set-point a spline could drive.", className());
+            return false;
+        }
+        if (splines.size() != N) {
+            log()->error("[{}::setSetPointSpline] One spline per robot is expected. Expected: {}. Given: {}.", className(), N, splines.size());
+            return false;
+        }
+        const auto& first = splines.front().knots();
+        if (first.size() < 2) {
+            log()->error("[Spline::setKnots] The number of knots has to be at least 2.");
+            return false;
+        }
+        std::vector<double> times(first.size()), pos(N * first.size() * 3), bc(N * 12, 0.0);
+        for (std::size_t k = 0; k < first.size(); k++) times[k] = std::chrono::duration<double>(first[k].time).count();
+        for (std::size_t i = 0; i < N; i++) {
+            const auto& kn = splines[i].knots();
+            if (kn.size() != first.size()) {
+                log()->error("[{}::setSetPointSpline] The splines of the robots must share their knot times.", className());
+                return false;
+            }
+            for (std::size_t k = 0; k < kn.size(); k++) {
+                if (kn[k].time != first[k].time) {
+                    log()->error("[{}::setSetPointSpline] The splines of the robots must share their knot times.", className());
+                    return false;
+                }
+                for (int c = 0; c < 3; c++) pos[(i * kn.size() + k) * 3 + c] = kn[k].position[c];
+            }
+            Math::QuinticSpline<Vector3d>::DerivativeBoundaryConditions ic, fc;
+            if (splines[i].boundaryConditions(ic, fc))
+                for (int c = 0; c < 3; c++)
+                    bc[i * 12 + c] = ic.velocity[c], bc[i * 12 + 3 + c] = ic.acceleration[c], bc[i * 12 + 6 + c] = fc.velocity[c], bc[i * 12 + 9 + c] = fc.acceleration[c];
+        }
+        for (std::size_t k = 0; k + 1 < times.size(); k++)
+            if (!(times[k + 1] > times[k])) {
+                log()->error("[Splines::computePhasesDuration] Two consecutive points have the same time coordinate, or the times decrease.");
+                return false;
+            }
+        m_splineTimes = std::move(times), m_splinePositions = std::move(pos), m_splineBoundary = std::move(bc);
+        m_splineVersion++;
+        return true;
+    }
+    void clearSetPointSpline() { m_splineTimes.clear(), m_splineVersion++; }
+    const std::vector<double>& splineTimes() const { return m_splineTimes; }
+    const std::vector<double>& splinePositions() const { return m_splinePositions; }
+    const std::vector<double>& splineBoundary() const { return m_splineBoundary; }
+    unsigned long splineVersion() const { return m_splineVersion; }
 
 protected:
     bool commonInitialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler, std::shared_ptr<const ParametersHandler::IParametersHandler>& ptr)
@@ -152,8 +207,8 @@ protected:
     System::VariablesHandler::VariableDescription m_robotVelocityVariable;
     std::size_t m_nVars{0};
     bool m_isInitialized{false}, m_isValid{false}, m_isSetPointSetAtLeastOnce{false};
-    std::vector<double> m_sp, m_fb;
-    unsigned long m_spVersion{0}, m_gainsVersion{0}, m_fbVersion{0};
+    std::vector<double> m_sp, m_fb, m_splineTimes, m_splinePositions, m_splineBoundary;
+    unsigned long m_spVersion{0}, m_gainsVersion{0}, m_fbVersion{0}, m_splineVersion{0};
     int m_inspect{-1};
 };
 
@@ -167,6 +222,7 @@ class SE3Task : public IKLinearTask
 public:
     enum class Mode { Enable, Disable };
     const char* className() const override { return "SE3Task"; }
+    bool acceptsSetPointSpline() const override { return true; }
     bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
     bool update() override;
     bool setSetPoint(const SE3d& I_H_F, const SE3d::Tangent& mixedVelocity = SE3d::Tangent::Zero(), std::ptrdiff_t instance = -1);
@@ -198,6 +254,7 @@ class CoMTask : public IKLinearTask
 {
 public:
     const char* className() const override { return "CoMTask"; }
+    bool acceptsSetPointSpline() const override { return true; }
     bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
     bool update() override;
     bool setSetPoint(const Vector3d& position, const Vector3d& velocity = {0, 0, 0}, std::ptrdiff_t instance = -1);
@@ -241,6 +298,7 @@ class R3Task : public IKLinearTask
 {
 public:
     const char* className() const override { return "R3Task"; }
+    bool acceptsSetPointSpline() const override { return true; }
     bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
     bool update() override;
     bool setSetPoint(const Vector3d& I_p_F, const Vector3d& velocity = {0, 0, 0}, std::ptrdiff_t instance = -1);
@@ -430,6 +488,9 @@ public:
     const std::vector<int32_t>& getBatchStatus() const;
     /** advance() and apply ForwardEuler on the device in the same launch; the new state is written back into kinDyn */
     bool advanceAndIntegrate(std::chrono::nanoseconds dT);
+    /** time at which the on-device set-point generators (IKLinearTask::setSetPointSpline) are evaluated by the next advance();
+     *  advanceAndIntegrate moves it on by dT */
+    bool setTime(std::chrono::nanoseconds t);
     blfik_problem* handle();
 };
 

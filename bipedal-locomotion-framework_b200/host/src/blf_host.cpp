@@ -1121,7 +1121,7 @@ struct QPInverseKinematics::Impl {
         std::size_t priority{0};
         std::shared_ptr<const System::WeightProviderPort> weightProvider;
         VectorXd uploadedWeight;
-        unsigned long uploadedSetPoint{~0ul}, uploadedGains{~0ul}, uploadedFeedback{0};
+        unsigned long uploadedSetPoint{~0ul}, uploadedGains{~0ul}, uploadedFeedback{0}, uploadedSpline{0};
     };
     std::vector<TaskEntry> tasks;   // insertion order = row order of the constraint matrix (QPInverseKinematics.cpp:201,236)
     std::unordered_map<std::string, std::size_t> index;
@@ -1290,7 +1290,7 @@ bool QPInverseKinematics::finalize(const System::VariablesHandler& handler)
             e.uploadedWeight = e.weightProvider->getOutput();
             descs[t].weight = keepVector(keep, e.uploadedWeight);
         }
-        e.uploadedSetPoint = ~0ul, e.uploadedGains = e.task->gainsVersion(), e.uploadedFeedback = 0;
+        e.uploadedSetPoint = ~0ul, e.uploadedGains = e.task->gainsVersion(), e.uploadedFeedback = 0, e.uploadedSpline = 0;
     }
     if (!m_pimpl->kinDyn) {
         log()->error("{} No KinDyn object: build the solver with QPInverseKinematics::build or call setKinDyn through a task added by addTask.", logPrefix);
@@ -1389,6 +1389,14 @@ bool QPInverseKinematics::tick(double dt, uint32_t flags)
             if (blfik_set_setpoint(prob, static_cast<int32_t>(t), e.task->setPointBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the set-point");
             e.uploadedSetPoint = e.task->setPointVersion();
         }
+        if (e.task->acceptsSetPointSpline() && e.task->splineVersion() != e.uploadedSpline) {   // setSetPointSpline(...) since the last tick
+            const auto& tm = e.task->splineTimes();
+            const int rc = tm.empty() ? blfik_set_setpoint_spline(prob, static_cast<int32_t>(t), 0, nullptr, nullptr, nullptr, BLFIK_MEM_HOST)
+                                      : blfik_set_setpoint_spline(prob, static_cast<int32_t>(t), static_cast<int32_t>(tm.size()), tm.data(),
+                                                                  e.task->splinePositions().data(), e.task->splineBoundary().data(), BLFIK_MEM_HOST);
+            if (rc != BLFIK_OK) return fail("Unable to set the set-point spline");
+            e.uploadedSpline = e.task->splineVersion();
+        }
         if (e.task->feedbackLength() > 0 && e.task->feedbackVersion() != e.uploadedFeedback) {   // setFeedback(...) since the last tick
             if (blfik_set_feedback(prob, static_cast<int32_t>(t), e.task->feedbackBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the feedback");
             e.uploadedFeedback = e.task->feedbackVersion();
@@ -1421,6 +1429,14 @@ const VectorXd& QPInverseKinematics::getRawSolution() const { return m_pimpl->ra
 const std::vector<double>& QPInverseKinematics::getBatchOutput() const { return m_pimpl->nu; }
 const std::vector<int32_t>& QPInverseKinematics::getBatchStatus() const { return m_pimpl->status; }
 blfik_problem* QPInverseKinematics::handle() { return m_pimpl->problem; }
+bool QPInverseKinematics::setTime(std::chrono::nanoseconds t)
+{
+    if (!m_pimpl->problem) {
+        log()->error("[QPInverseKinematics::setTime] Please call finalize() first.");
+        return false;
+    }
+    return blfik_set_time(m_pimpl->problem, std::chrono::duration<double>(t).count()) == BLFIK_OK;
+}
 
 std::weak_ptr<QPInverseKinematics::Task> QPInverseKinematics::getTask(const std::string& name) const
 {

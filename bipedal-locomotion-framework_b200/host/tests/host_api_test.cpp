@@ -568,6 +568,172 @@ static void testClosedLoop(const char* modelPath, std::size_t N, bool withLimits
 // IntegratorFloatingBaseSystemVelocityKinematics.cpp:25-88 with a non-identity initial rotation
 // QPFixedBaseInverseKinematics (QPFixedBaseInverseKinematicsTest.cpp: the base link is held by "base_se3_task", a hand reaches
 // a pose with the joints regularised): the base twist stays zero on every tick and the hand converges
+// src/Math/tests/SplineTest.cpp:21-167 "Quintic spline" replayed: 100 knots on a random quintic in R^4 between 320 ms and 642 s;
+// the spline returns the polynomial, its first and its second derivative (isApprox 1e-5), through evaluatePoint, advance and
+// evaluateOrderedPoints.
+static void testSplines()
+{
+    using BipedalLocomotion::Math::QuinticSpline;
+    constexpr std::size_t numberOfPoints = 100;
+    constexpr std::chrono::nanoseconds initTime = 320ms, finalTime = 2s + 640s;
+    constexpr std::chrono::nanoseconds dT = (finalTime - initTime) / (numberOfPoints - 1);
+    constexpr double tolerance = 1e-5;
+    std::mt19937 gen(5);
+    std::uniform_real_distribution<double> uni(-1.0, 1.0);
+    double c[6][4];
+    for (auto& row : c)
+        for (double& v : row) v = uni(gen);
+    auto poly = [&](double t, int order) {
+        VectorXd out(4, 0.0);
+        for (int k = 0; k < 4; k++)
+            for (int i = order; i < 6; i++) {
+                double f = 1.0;
+                for (int j = 0; j < order; j++) f *= i - j;
+                out[k] += f * c[i][k] * std::pow(t, i - order);
+            }
+        return out;
+    };
+    auto approx = [&](const VectorXd& a, const VectorXd& b) {   // Eigen's isApprox
+        double d = 0, na = 0, nb = 0;
+        for (std::size_t k = 0; k < a.size(); k++) d += (a[k] - b[k]) * (a[k] - b[k]), na += a[k] * a[k], nb += b[k] * b[k];
+        return d <= tolerance * tolerance * std::min(na, nb);
+    };
+    std::vector<VectorXd> knots;
+    std::vector<std::chrono::nanoseconds> time;
+    for (std::size_t i = 0; i < numberOfPoints; i++) {
+        time.push_back(dT * i + initTime);
+        knots.push_back(poly(std::chrono::duration<double>(time.back()).count(), 0));
+    }
+    const double initT = std::chrono::duration<double>(initTime).count(), lastT = std::chrono::duration<double>(time.back()).count();
+    QuinticSpline<VectorXd> spline;
+    VectorXd position, velocity, acceleration;
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(spline.evaluatePoint(1s, position));                                        // no knots
+    REQUIRE_FALSE(spline.setKnots({knots[0]}, {time[0]}));                                    // Spline.h:338-342
+    REQUIRE_FALSE(spline.setKnots(knots, std::vector<std::chrono::nanoseconds>(time.begin(), time.end() - 1)));
+    REQUIRE(spline.setKnots(knots, time));
+    REQUIRE_FALSE(spline.evaluatePoint(1s, position));                                        // no boundary conditions
+    REQUIRE_FALSE(spline.setInitialConditions(VectorXd(4, 0.0), VectorXd(3, 0.0)));
+    REQUIRE_FALSE(spline.setAdvanceTimeStep(0ns));
+    log()->setLevel(Logger::Level::warn);
+    REQUIRE(spline.setInitialConditions({poly(initT, 1), poly(initT, 2)}));
+    REQUIRE(spline.setFinalConditions({poly(lastT, 1), poly(lastT, 2)}));
+    constexpr std::size_t pointsToCheckNumber = 1000;
+    const std::chrono::nanoseconds dTCheckPoints = (time.back() - initTime) / pointsToCheckNumber;
+    bool allClose = true;
+    for (std::size_t i = 0; i < pointsToCheckNumber; i++) {
+        const std::chrono::nanoseconds t = dTCheckPoints * i + initTime;
+        const double td = std::chrono::duration<double>(t).count();
+        allClose = allClose && spline.evaluatePoint(t, position, velocity, acceleration);
+        allClose = allClose && approx(poly(td, 0), position) && approx(poly(td, 1), velocity) && approx(poly(td, 2), acceleration);
+    }
+    REQUIRE(allClose);
+    // "Advance capabilities"
+    REQUIRE_FALSE(spline.isOutputValid());
+    REQUIRE(spline.setAdvanceTimeStep(dTCheckPoints));
+    allClose = true;
+    for (std::size_t i = 0; i < pointsToCheckNumber; i++) {
+        const double td = std::chrono::duration<double>(dTCheckPoints * i + initTime).count();
+        allClose = allClose && spline.advance() && spline.isOutputValid();
+        const auto& traj = spline.getOutput();
+        allClose = allClose && approx(poly(td, 0), traj.position) && approx(poly(td, 1), traj.velocity) && approx(poly(td, 2), traj.acceleration);
+    }
+    REQUIRE(allClose);
+    // "Query from a vector of times"
+    std::vector<std::chrono::nanoseconds> timeVector;
+    for (std::size_t i = 0; i < pointsToCheckNumber; i++) timeVector.push_back(dTCheckPoints * i + initTime);
+    std::vector<VectorXd> pv, vv, av;
+    REQUIRE(spline.evaluateOrderedPoints(timeVector, pv, vv, av));
+    allClose = true;
+    for (std::size_t i = 0; i < pointsToCheckNumber; i++) {
+        const double td = std::chrono::duration<double>(timeVector[i]).count();
+        allClose = allClose && approx(poly(td, 0), pv[i]) && approx(poly(td, 1), vv[i]) && approx(poly(td, 2), av[i]);
+    }
+    REQUIRE(allClose);
+    // outside the knots the end states hold (Spline.h:607-625); two equal times are refused (:444-448)
+    REQUIRE(spline.evaluatePoint(0ns, position, velocity) && approx(knots.front(), position) && approx(poly(initT, 1), velocity));
+    REQUIRE(spline.evaluatePoint(finalTime + 10s, position, velocity) && approx(knots.back(), position) && approx(poly(lastT, 1), velocity));
+    QuinticSpline<Vector3d> twin;
+    REQUIRE(twin.setKnots({Vector3d{0, 0, 0}, Vector3d{1, 0, 0}, Vector3d{2, 0, 0}}, {0ms, 500ms, 500ms}));
+    REQUIRE(twin.setInitialConditions(Vector3d{0, 0, 0}, Vector3d{0, 0, 0}) && twin.setFinalConditions(Vector3d{0, 0, 0}, Vector3d{0, 0, 0}));
+    Vector3d p3;
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(twin.evaluatePoint(200ms, p3));
+    log()->setLevel(Logger::Level::warn);
+}
+
+// IKLinearTask::setSetPointSpline: the hand of N fixed-base robots follows one spline per robot, evaluated on the device at
+// the solver's time; the solution equals the reference's way (evaluate on the host, setSetPoint, advance) at every time.
+static void testSetPointSpline(const char* modelPath, std::size_t N)
+{
+    using BipedalLocomotion::Math::QuinticSpline;
+    auto make = [&](std::shared_ptr<KinDynBatch>& kinDyn, std::shared_ptr<SE3Task>& hand, QPFixedBaseInverseKinematics& ik) {
+        kinDyn = loadKinDyn(modelPath, N);
+        const std::size_t n = kinDyn->getNrOfDegreesOfFreedom();
+        auto ikHandler = std::make_shared<StdImplementation>();
+        ikHandler->setParameter("robot_velocity_variable_name", robotVelocity);
+        REQUIRE(ik.setKinDyn(kinDyn) && ik.initialize(ikHandler));
+        hand = std::make_shared<SE3Task>();
+        auto hh = std::make_shared<StdImplementation>();
+        hh->setParameter("robot_velocity_variable_name", robotVelocity), hh->setParameter("frame_name", "l_hand_palm");
+        hh->setParameter("kp_linear", 5.0), hh->setParameter("kp_angular", 5.0);
+        REQUIRE(hand->setKinDyn(kinDyn) && hand->initialize(hh) && ik.addTask(hand, "hand", 0));
+        auto reg = std::make_shared<JointTrackingTask>();
+        auto rh = std::make_shared<StdImplementation>();
+        rh->setParameter("robot_velocity_variable_name", robotVelocity), rh->setParameter("kp", std::vector<double>(n, 1.0));
+        REQUIRE(reg->setKinDyn(kinDyn) && reg->initialize(rh) && ik.addTask(reg, "reg", 1, VectorXd(n, 1.0)));
+        VariablesHandler vh;
+        vh.addVariable(robotVelocity, n + 6);
+        REQUIRE(ik.finalize(vh));
+        std::mt19937 gen(3);
+        for (std::size_t i = 0; i < N; i++) {
+            const VectorXd s = nominalJoints(*kinDyn, gen, 0.2);
+            REQUIRE(kinDyn->setRobotState({0.0, 0.0, 0.7}, SO3d::Identity(), s, i) && reg->setSetPoint(s, i));
+        }
+    };
+    std::shared_ptr<KinDynBatch> kdDev, kdHost;
+    std::shared_ptr<SE3Task> handDev, handHost;
+    QPFixedBaseInverseKinematics ikDev, ikHost;
+    make(kdDev, handDev, ikDev), make(kdHost, handHost, ikHost);
+    std::mt19937 gen(17);
+    std::uniform_real_distribution<double> uni(-0.01, 0.01);
+    std::vector<QuinticSpline<Vector3d>> splines(N);
+    std::vector<SE3d> pose(N);
+    const std::vector<std::chrono::nanoseconds> time{0ms, 300ms, 450ms, 1000ms};
+    for (std::size_t i = 0; i < N; i++) {
+        std::array<double, 9> R;
+        REQUIRE(kdDev->getWorldTransform(kdDev->getFrameIndex("l_hand_palm"), pose[i], R, i));
+        REQUIRE(handDev->setSetPoint(pose[i], SE3d::Tangent::Zero(), i));
+        std::vector<Vector3d> knots(4, pose[i].translation());
+        for (std::size_t k = 1; k < 4; k++)
+            for (int c = 0; c < 3; c++) knots[k][c] += uni(gen) * k;
+        REQUIRE(splines[i].setKnots(knots, time));
+        REQUIRE(splines[i].setInitialConditions(Vector3d{uni(gen), uni(gen), uni(gen)}, Vector3d{0, 0, 0}));
+        REQUIRE(splines[i].setFinalConditions(Vector3d{0, 0, 0}, Vector3d{0, 0, 0}));
+    }
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(handDev->setSetPointSpline(std::vector<QuinticSpline<Vector3d>>(N + 1)));   // one per robot
+    REQUIRE_FALSE(std::make_shared<SO3Task>()->setSetPointSpline(splines));                   // no position set-point
+    log()->setLevel(Logger::Level::warn);
+    REQUIRE(handDev->setSetPointSpline(splines));
+    double worst = 0.0;
+    for (const std::chrono::nanoseconds t : {-100ms, 0ms, 120ms, 300ms, 777ms, 1000ms, 1400ms}) {
+        REQUIRE(ikDev.setTime(t) && ikDev.advance());
+        for (std::size_t i = 0; i < N; i++) {
+            Vector3d p, v;
+            REQUIRE(splines[i].evaluatePoint(t, p, v));
+            SE3d::Tangent ff = SE3d::Tangent::Zero();
+            ff.linear = v;
+            REQUIRE(handHost->setSetPoint(SE3d(p, pose[i].R), ff, i));
+        }
+        REQUIRE(ikHost.advance());
+        for (std::size_t k = 0; k < ikDev.getBatchOutput().size(); k++) worst = std::max(worst, std::abs(ikDev.getBatchOutput()[k] - ikHost.getBatchOutput()[k]));
+    }
+    REQUIRE(worst < 1e-8);
+    handDev->clearSetPointSpline();
+    REQUIRE(ikDev.advance());
+}
+
 static void testFixedBase(const char* modelPath, std::size_t N)
 {
     constexpr auto dT = 10ms;
@@ -682,6 +848,7 @@ int main(int argc, char** argv)
     testParametersAndVariables();
     testTaskInitializationAndAddTaskRules(argv[2]);
     testWeightProviders();
+    testSplines();
     if (gpu) {
         testTaskMatrices(argv[2]);
         testClosedLoop(argv[2], 1, false);
@@ -689,6 +856,7 @@ int main(int argc, char** argv)
         testClosedLoop(argv[2], 48, true);
         testFixedBase(argv[2], 1);
         testFixedBase(argv[2], 5);
+        testSetPointSpline(argv[2], 3);
         testIntegrator();
     }
     std::printf("%s: %d checks, %d failures\n", gpu ? "gpu" : "cpu", g_checks, g_failures);

@@ -452,3 +452,110 @@ def test_exogenous_feedback_through_the_bindings():
     shift = np.array([0.0, 0.0, 0.02])
     nu_shift, _ = solve(True, shift)
     assert np.abs(Jc @ (nu_shift - nu_plain) + 3.0 * shift).max() < 1e-8      # J_com nu = v_ff + kp (p_d - p_measured)
+
+
+# ------------------------------------------------------------------------------------------------ Math: splines
+def _quintic(c, t, k=0):
+    return sum(c[i] * np.prod(np.arange(i, i - k, -1)) * t ** (i - k) for i in range(k, 6))
+
+
+def test_quintic_spline():
+    """bindings/python/Math/tests/test_quintic_spline.py replayed: 100 knots on a random quintic between 0.32 s and 2.64 s, the
+    spline returns the polynomial and its derivatives (atol 1e-5) -- plus the advance() / evaluate_ordered_points sections
+    and the refusals of src/Math/tests/SplineTest.cpp."""
+    rng = np.random.default_rng(11)
+    number_of_points, init_time, final_time = 100, 0.32, 2.64
+    dT = (final_time - init_time) / (number_of_points - 1)
+    coefficients = [rng.random((4, 1)) for _ in range(6)]
+    time = [init_time + dT * i for i in range(number_of_points)]
+    knots = [_quintic(coefficients, t) for t in time]
+    spline = blf.math.QuinticSpline()
+    position, velocity, acceleration = np.zeros(4), np.zeros(4), np.zeros(4)
+    assert not spline.evaluate_point(1.0, position)                                     # no knots yet
+    assert not spline.set_knots(knots[:1], time[:1]) and not spline.set_knots(knots, time[:-1])
+    assert spline.set_knots(knots, time)
+    assert not spline.evaluate_point(1.0, position)                                     # no boundary conditions yet
+    assert not spline.set_initial_conditions(np.zeros(4), np.zeros(3))
+    assert spline.set_initial_conditions(_quintic(coefficients, init_time, 1), _quintic(coefficients, init_time, 2))
+    assert spline.set_final_conditions(_quintic(coefficients, final_time, 1), _quintic(coefficients, final_time, 2))
+    points_to_check_number = 10000
+    dT_check_points = (final_time - init_time) / points_to_check_number
+    for i in range(0, points_to_check_number, 3):
+        t = dT_check_points * i + init_time
+        assert spline.evaluate_point(t, position, velocity, acceleration)
+        assert np.allclose(_quintic(coefficients, t).T[0], position, atol=1e-5)
+        assert np.allclose(_quintic(coefficients, t, 1).T[0], velocity, atol=1e-5)
+        assert np.allclose(_quintic(coefficients, t, 2).T[0], acceleration, atol=1e-5)
+    # "Advance capabilities"
+    assert not spline.is_output_valid()
+    assert not spline.set_advance_time_step(timedelta(0)) and spline.set_advance_time_step(timedelta(seconds=dT_check_points * 50))
+    for i in range(0, points_to_check_number, 50):
+        t = dT_check_points * i + init_time
+        assert spline.advance() and spline.is_output_valid()
+        assert np.allclose(_quintic(coefficients, t).T[0], spline.get_output().position, atol=1e-5)
+        assert np.allclose(_quintic(coefficients, t, 1).T[0], spline.get_output().velocity, atol=1e-5)
+    # "Query from a vector of times", and timedelta arguments as in the reference's binding
+    ts = [dT_check_points * i + init_time for i in range(0, points_to_check_number, 97)]
+    ok, ps, vs, acs = spline.evaluate_ordered_points(ts)
+    assert ok and all(np.allclose(_quintic(coefficients, t).T[0], p, atol=1e-5) for t, p in zip(ts, ps))
+    assert all(np.allclose(_quintic(coefficients, t, 2).T[0], a, atol=1e-5) for t, a in zip(ts, acs))
+    assert spline.evaluate_point(timedelta(seconds=1.0), position)
+    assert np.allclose(_quintic(coefficients, 1.0).T[0], position, atol=1e-5)
+    # two consecutive knots with the same time are refused when the coefficients are computed (Spline.h:444-448)
+    twin = blf.math.QuinticSpline()
+    assert twin.set_knots(knots[:3], [0.0, 0.5, 0.5])
+    assert twin.set_initial_conditions(np.zeros(4), np.zeros(4)) and twin.set_final_conditions(np.zeros(4), np.zeros(4))
+    assert not twin.evaluate_point(0.2, position)
+
+
+@pytest.mark.gpu
+def test_set_point_spline_through_the_bindings():
+    """The batch extension set_set_point_spline: the CoM task of three robots follows one QuinticSpline object per robot on
+    the device; at every queried time the solution equals the one obtained the reference's way (evaluate the spline on the
+    host, set_set_point, advance)."""
+    model = M.ergocub23()
+    n, N = model.n, 3
+
+    def make():
+        _, kindyn = get_kindyn(model, N)
+        H = np.eye(4)
+        H[:3, 3] = [0.0, 0.0, 0.75]
+        assert kindyn.setRobotState(H, model.q_nominal)
+        ik = blf.ik.QPInverseKinematics()
+        assert ik.initialize(handler=_handler())
+        com = blf.ik.CoMTask()
+        assert com.set_kin_dyn(kindyn) and com.initialize(param_handler=_handler(kp_linear=3.0))
+        reg = blf.ik.JointTrackingTask()
+        assert reg.set_kin_dyn(kindyn) and reg.initialize(param_handler=_handler(kp=[1.0] * n))
+        c = kindyn.getCenterOfMassPosition()
+        assert com.set_set_point(position=c) and reg.set_set_point(joint_position=model.q_nominal)
+        assert ik.add_task(com, "com", 0) and ik.add_task(reg, "reg", 1, weight=[1.0] * n)
+        var = blf.system.VariablesHandler()
+        assert var.add_variable("robotVelocity", n + 6) and ik.finalize(var)
+        return ik, com, c
+
+    rng = np.random.default_rng(4)
+    ik_dev, com_dev, c = make()
+    ik_host, com_host, _ = make()
+    times = [0.0, 0.3, 0.5, 1.0]
+    splines = []
+    for i in range(N):
+        sp = blf.math.QuinticSpline()
+        assert sp.set_knots([c + rng.uniform(-0.01, 0.01, 3) * k for k in range(4)], times)
+        assert sp.set_initial_conditions(rng.uniform(-0.01, 0.01, 3), np.zeros(3)) and sp.set_final_conditions(np.zeros(3), np.zeros(3))
+        splines.append(sp)
+    reg_only = blf.ik.JointTrackingTask()
+    assert not reg_only.set_set_point_spline(splines[0])
+    assert not com_dev.set_set_point_spline(splines[:2])                # one per robot
+    assert com_dev.set_set_point_spline(splines)
+    pos, vel = np.zeros(3), np.zeros(3)
+    for t in (-0.1, 0.0, 0.12, 0.3, 0.77, 1.0, 1.4):
+        assert ik_dev.set_time(t) and ik_dev.advance()
+        for i in range(N):
+            assert splines[i].evaluate_point(t, pos, vel)
+            assert com_host.set_set_point(position=pos, velocity=vel, instance=i)
+        assert ik_host.advance()
+        assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
+    assert com_dev.set_set_point_spline(None) and ik_dev.advance()
+    assert com_host.set_set_point(position=c) and ik_host.advance()
+    assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
