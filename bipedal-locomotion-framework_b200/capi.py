@@ -38,7 +38,7 @@ EXPORTS = [
     "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state", "blfik_tick_host",
     "blfik_packed_record_len", "blfik_packed_offset", "blfik_tick_packed",
     "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time", "blfik_set_limits",
-    "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline",
+    "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline", "blfik_evaluate_setpoint",
     "blfik_packed_record_len_ex", "blfik_packed_offset_ex", "blfik_packed_part_len",
 ]
 
@@ -300,6 +300,15 @@ class Problem:
             raise ValueError(f"boundary must be [N, 4, 3], got {bc.shape}")
         _check(self.L.blfik_set_setpoint_spline(self.handle, int(task), len(tm), tm.ctypes.data, x.ctypes.data,
                                                 None if bc is None else bc.ctypes.data, MEM_HOST))
+
+    def evaluate_setpoint(self, task: int, time: float) -> np.ndarray:
+        """[N, setpoint_len] set-point of ``task`` as a tick at ``time`` reads it (stored set-point + attached generators)"""
+        self.L.blfik_setpoint_len.argtypes = [C.c_void_p, C.c_int32]
+        self.L.blfik_setpoint_len.restype = C.c_int32
+        out = np.empty((self.N, int(self.L.blfik_setpoint_len(self.handle, int(task)))))
+        self.L.blfik_evaluate_setpoint.argtypes = [C.c_void_p, C.c_int32, C.c_double, C.c_void_p, C.c_int32]
+        _check(self.L.blfik_evaluate_setpoint(self.handle, int(task), float(time), out.ctypes.data, MEM_HOST))
+        return out
 
     def set_time(self, t: float):
         self.L.blfik_set_time.argtypes = [C.c_void_p, C.c_double]

@@ -189,6 +189,18 @@ __global__ void __launch_bounds__(128) blfik_spline_coefficients_kernel(long lon
     }
 }
 
+// The set-point a tick at time t reads: the stored record with the attached generators applied, one thread per robot.
+__global__ void __launch_bounds__(128) blfik_evaluate_setpoint_kernel(const DevTask* tasks, int t, long long N, double time, double* out)
+{
+    const long long robot = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (robot >= N) return;
+    const DevTask& tk = tasks[t];
+    const double* sp = tk.setpoint + (size_t)robot * tk.sp_len;
+    double spl[13];
+    const double* use = traj_eval(tk, robot, time, sp, spl);
+    for (int c = 0; c < tk.fb_off; c++) out[(size_t)robot * tk.fb_off + c] = use[c];
+}
+
 __global__ void blfik_count_unsolved_kernel(const int* status, long long N, unsigned long long* out)
 {
     unsigned long long c = 0;
@@ -1052,6 +1064,35 @@ extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const 
     h.traj_omega = 6.283185307179586476925286766559 / period;
     h.mj_T = 0.0, h.sp_nk = 0;   // this generator stands alone
     p->tasks_dirty = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_evaluate_setpoint(blfik_problem* p, int32_t t, double time, double* out, int32_t mem)
+{
+    CHECK_P(p, "blfik_evaluate_setpoint");
+    CHECK_TASK(p, t, "blfik_evaluate_setpoint");
+    HostTask& h = p->tasks[t];
+    if (!out) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_evaluate_setpoint] null output");
+    if (h.sp_len == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_evaluate_setpoint] task %d takes no set point", t);
+    if (!h.setpoint_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_evaluate_setpoint] the set point of task %d has not been set", t);
+    int rc = refresh_tasks(p);
+    if (rc) return rc;
+    const size_t len = (size_t)(h.sp_len - h.fb_len) * p->N;
+    double* dst = out;
+    double* stage = nullptr;
+    if (mem != BLFIK_MEM_DEVICE) {
+        CU(cudaMalloc((void**)&stage, len * sizeof(double)));
+        dst = stage;
+    }
+    blfik_evaluate_setpoint_kernel<<<(unsigned)((p->N + 127) / 128), 128, 0, p->stream>>>(p->d_tasks, t, p->N, time, dst);
+    p->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (stage) {
+        if (e == cudaSuccess) e = cudaMemcpyAsync(out, stage, len * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+        cudaFree(stage);
+    }
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_evaluate_setpoint] %s", cudaGetErrorString(e));
     return BLFIK_OK;
 }
 

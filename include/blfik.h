@@ -226,6 +226,11 @@ int blfik_set_setpoint_minimum_jerk(blfik_problem* problem, int32_t task, const 
 #define BLFIK_MAX_SPLINE_KNOTS 1024
 int blfik_set_setpoint_spline(blfik_problem* problem, int32_t task, int32_t n_knots, const double* times,
                               const double* positions, const double* boundary, int32_t mem);
+/* The set-point of a task as a tick at `time` reads it: the stored set-point (blfik_set_setpoint) with the attached
+ * generators applied, out [N][blfik_setpoint_len(task)].  What the reference's callers log next to the measured pose (the
+ * output of their spline / planner, e.g. Spline::getOutput, Spline.h:248-254, before it goes to setSetPoint); no solver
+ * state is touched.  Host-tick records (blfik_tick_packed) are not consulted: this reads what blfik_set_setpoint stored. */
+int blfik_evaluate_setpoint(blfik_problem* problem, int32_t task, double time, double* out, int32_t mem);
 int blfik_set_time(blfik_problem* problem, double t);
 double blfik_get_time(const blfik_problem* problem);
 

@@ -1132,6 +1132,49 @@ def test_quintic_spline_setpoint_generator(path):
     prob.close(), whole.close()
 
 
+@pytest.mark.parametrize("seed", range(6))
+def test_generators_evaluated_setpoints_vs_oracle(seed):
+    """blfik_evaluate_setpoint against the host restatements, directly on the set-point (no solve in between): quintic
+    splines with 2 ... 40 uneven knots and random boundary conditions (oracle/spline.py) on the CoM and a foot, the
+    minimum-jerk generator on the foot's orientation and on the torso, at random times inside and outside the knots."""
+    from oracle.spline import quintic_spline_coefficients, spline_evaluate
+    rng = np.random.default_rng(100 + seed)
+    w = W.config(5)
+    N = 7
+    inp = W.synth_inputs(w, N, 5)
+    model, prob = make(w.model, w.tasks, N, 0)
+    prob.set_inputs(inp)
+    nk = [2, 3, 5, 9, 17, 40][seed]
+    t0 = rng.uniform(-1.0, 1.0)
+    times = t0 + np.concatenate([[0.0], np.cumsum(rng.uniform(0.002, 0.3, nk - 1))])
+    dur = 0.4
+    target = {1: inp.setpoints[1].copy(), 5: inp.setpoints[5].copy()}
+    target[1][:, 3:7] = W.quat_mul(W.so3_exp(rng.uniform(-0.5, 0.5, (N, 3))), target[1][:, 3:7])
+    target[5][:, 0:4] = W.quat_mul(W.so3_exp(rng.uniform(-0.5, 0.5, (N, 3))), target[5][:, 0:4])
+    prob.set_time(t0)
+    for ti in (1, 5):
+        prob.set_setpoint_minimum_jerk(ti, target[ti], dur)
+    knots, bcs = {}, {}
+    for ti in (0, 1):
+        knots[ti] = inp.setpoints[ti][:, None, :3] + np.cumsum(rng.uniform(-0.05, 0.05, (N, nk, 3)), axis=1)
+        bcs[ti] = rng.uniform(-0.5, 0.5, (N, 4, 3))
+        prob.set_setpoint_spline(ti, times, knots[ti], bcs[ti])
+    co = {ti: [quintic_spline_coefficients(times, knots[ti][i], *bcs[ti][i])[0] for i in range(N)] for ti in (0, 1)}
+    scale = {ti: max(1.0, np.abs(np.diff(knots[ti], axis=1)).max() / np.diff(times).min()) for ti in (0, 1)}
+    for t in np.concatenate([[times[0] - 0.1, times[0], times[-1], times[-1] + 0.2], times[:3], rng.uniform(times[0], times[-1], 12)]):
+        got = {ti: prob.evaluate_setpoint(ti, t) for ti in (0, 1, 5, 6)}
+        assert np.array_equal(got[6], inp.setpoints[6])                                  # no generator: the stored set-point
+        mj = {ti: _min_jerk_setpoint(w.tasks[ti].type, inp.setpoints[ti], target[ti], (t - t0) / dur, dur) for ti in (1, 5)}
+        assert np.abs(got[5] - mj[5]).max() < 1e-12
+        assert np.abs(got[1][:, 3:7] - mj[1][:, 3:7]).max() < 1e-12 and np.abs(got[1][:, 10:13] - mj[1][:, 10:13]).max() < 1e-11
+        for ti, vo in ((0, 3), (1, 7)):
+            for i in range(N):
+                pos, vel, _ = spline_evaluate(times, co[ti][i], t)
+                assert np.abs(got[ti][i, :3] - pos).max() <= 1e-11 * (1.0 + np.abs(pos).max()), (ti, t)
+                assert np.abs(got[ti][i, vo:vo + 3] - inp.setpoints[ti][i, vo:vo + 3] - vel).max() <= 1e-9 * scale[ti], (ti, t)
+    prob.close()
+
+
 @pytest.mark.parametrize("seed", range(int(os.environ.get("BLFIK_FUZZ_SEEDS", "10"))))
 def test_random_task_mixes_vs_oracle(seed):
     """Randomised problems: a random revolute tree (14..40 joints, so both kernels are reached), a random mix of hard and weighted
