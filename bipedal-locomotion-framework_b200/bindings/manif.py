@@ -29,8 +29,10 @@ class SO3Tangent:
         k = 0.5 - th * th / 48.0 if th < 1e-8 else np.sin(th / 2) / th
         return SO3(quaternion=np.concatenate([k * self._c, [np.cos(th / 2)]]))
 
-    def __add__(self, X: "SO3") -> "SO3":       # left-plus
-        return self.exp() * X
+    def __add__(self, X):
+        if isinstance(X, SO3Tangent):           # tangent + tangent
+            return SO3Tangent(self._c + X._c)
+        return self.exp() * X                   # left-plus: Exp(tau) * X
 
     def __mul__(self, s: float):
         return SO3Tangent(self._c * s)
@@ -46,6 +48,14 @@ class SO3:
     @staticmethod
     def Identity():
         return SO3()
+
+    @staticmethod
+    def Random(rng=None):
+        q = (rng or np.random.default_rng()).normal(size=4)
+        return SO3(quaternion=q)
+
+    def __add__(self, tau: "SO3Tangent") -> "SO3":   # right-plus: X * Exp(tau)
+        return self * tau.exp()
 
     def quat(self):
         return self._q

@@ -99,6 +99,23 @@ struct SO3d {
         const double k = th > 1e-8 ? std::sin(0.5 * th) / th : 0.5 - th * th / 48.0;
         return SO3d(Quaterniond{k * phi[0], k * phi[1], k * phi[2], std::cos(0.5 * th)});
     }
+    SO3d inverse() const { return SO3d(Quaterniond{-q.x, -q.y, -q.z, q.w}); }
+    /** composition: (*this) * o */
+    SO3d operator*(const SO3d& o) const
+    {
+        const Quaterniond &a = q, &b = o.q;
+        return SO3d(Quaterniond{a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y, a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x,
+                                a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w, a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z});
+    }
+    /** manif SO3::log as a rotation vector */
+    Vector3d Log() const
+    {
+        const double s = q.w < 0 ? -1.0 : 1.0;
+        const double x = s * q.x, y = s * q.y, z = s * q.z, w = s * q.w;
+        const double n = std::sqrt(x * x + y * y + z * z);
+        const double k = n < 1e-10 ? 2.0 / w * (1.0 - n * n / (3.0 * w * w)) : 2.0 * std::atan2(n, w) / n;
+        return {k * x, k * y, k * z};
+    }
     std::array<double, 9> rotation() const
     {
         const double x = q.x, y = q.y, z = q.z, w = q.w;

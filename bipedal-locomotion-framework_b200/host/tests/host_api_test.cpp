@@ -4,6 +4,7 @@
 //   host_api_test gpu <model.txt>    checks that run the CUDA path (task A/b identities, closed loop, batch, integrator)
 #include <BipedalLocomotion/ContinuousDynamicalSystem.h>
 #include <BipedalLocomotion/IK.h>
+#include <BipedalLocomotion/Planners.h>
 
 #include <cstdlib>
 #include <cstring>
@@ -662,6 +663,69 @@ static void testSplines()
     log()->setLevel(Logger::Level::warn);
 }
 
+// src/Planners/tests/SO3PlannerTest.cpp:21-167 replayed: the rotation integrates its own velocity (right-plus for the body-fixed
+// planner, left-plus for the inertial one), the velocity its acceleration, both ends are met (tolerance 1e-3).
+template <class Planner> static void so3PlannerSection(bool body, bool initialVelocity)
+{
+    using namespace BipedalLocomotion::Planners;
+    std::mt19937 gen(21);
+    std::normal_distribution<double> nrm(0.0, 1.0);
+    auto randomRotation = [&]() { return SO3d(Quaterniond{nrm(gen), nrm(gen), nrm(gen), nrm(gen)}); };
+    const SO3d R0 = randomRotation(), R1 = randomRotation();
+    constexpr std::chrono::nanoseconds T = 1s, dT = 100us;
+    constexpr double tolerance = 1e-3, h = 100e-6;
+    auto near = [&](const SO3d& a, const SO3d& b) { const Vector3d e = (b.inverse() * a).Log(); return std::sqrt(e[0] * e[0] + e[1] * e[1] + e[2] * e[2]) < tolerance; };
+    auto nearV = [&](const Vector3d& a, const Vector3d& b) { return std::abs(a[0] - b[0]) < tolerance && std::abs(a[1] - b[1]) < tolerance && std::abs(a[2] - b[2]) < tolerance; };
+    Planner planner;
+    SO3Tangentd v0;
+    if (initialVelocity) {
+        const Vector3d d = (R1 * R0.inverse()).Log();
+        v0.w = {2 * d[0], 2 * d[1], 2 * d[2]};
+    }
+    SO3d rotation;
+    SO3Tangentd velocity, acceleration;
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(planner.setRotations(R0, R1, 0s));
+    REQUIRE(planner.setRotations(R0, R1, T));
+    REQUIRE_FALSE(planner.evaluatePoint(0s, rotation, velocity, acceleration));   // boundary conditions missing
+    REQUIRE_FALSE(planner.advance());
+    log()->setLevel(Logger::Level::warn);
+    REQUIRE(planner.setInitialConditions(v0, SO3Tangentd::Zero()) && planner.setFinalConditions(SO3Tangentd::Zero(), SO3Tangentd::Zero()));
+    REQUIRE(planner.evaluatePoint(0s, rotation, velocity, acceleration));
+    REQUIRE(near(rotation, R0) && nearV(velocity.w, v0.w) && nearV(acceleration.w, {0, 0, 0}));
+    bool ok = true;
+    for (std::size_t i = 1; i < static_cast<std::size_t>(T / dT); i++) {
+        const SO3d step = SO3d::Exp({velocity.w[0] * h, velocity.w[1] * h, velocity.w[2] * h});
+        const SO3d predicted = body ? rotation * step : step * rotation;
+        const Vector3d predictedVelocity{velocity.w[0] + acceleration.w[0] * h, velocity.w[1] + acceleration.w[1] * h, velocity.w[2] + acceleration.w[2] * h};
+        ok = ok && planner.evaluatePoint(i * dT, rotation, velocity, acceleration);
+        ok = ok && near(predicted, rotation) && nearV(predictedVelocity, velocity.w);
+    }
+    REQUIRE(ok);
+    REQUIRE(planner.evaluatePoint(T, rotation, velocity, acceleration));
+    REQUIRE(near(rotation, R1) && nearV(velocity.w, {0, 0, 0}) && nearV(acceleration.w, {0, 0, 0}));
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(planner.evaluatePoint(T + 1ms, rotation, velocity, acceleration));   // SO3Planner.tpp:178-184
+    const Vector3d d = (R1 * R0.inverse()).Log();
+    SO3Tangentd skew;
+    skew.w = {d[1] * 0.3 - d[2] * 0.2, d[2] * 1.0 - d[0] * 0.3, d[0] * 0.2 - d[1] * 1.0};   // d x (1, 0.2, 0.3)-like: not along d
+    Planner refused;
+    REQUIRE(refused.setRotations(R0, R1, T) && refused.setInitialConditions(skew, SO3Tangentd::Zero()) && refused.setFinalConditions(SO3Tangentd::Zero(), SO3Tangentd::Zero()));
+    REQUIRE_FALSE(refused.evaluatePoint(500ms, rotation, velocity, acceleration));
+    log()->setLevel(Logger::Level::warn);
+    REQUIRE(planner.setAdvanceTimeStep(250ms) && planner.isOutputValid());
+    for (int i = 0; i < 6; i++) REQUIRE(planner.advance());
+    REQUIRE(near(planner.getOutput().rotation, R1));
+}
+
+static void testSO3Planner()
+{
+    using namespace BipedalLocomotion::Planners;
+    so3PlannerSection<SO3PlannerBody>(true, false);
+    so3PlannerSection<SO3PlannerInertial>(false, false);
+    so3PlannerSection<SO3PlannerInertial>(false, true);
+}
+
 // IKLinearTask::setSetPointSpline: the hand of N fixed-base robots follows one spline per robot, evaluated on the device at
 // the solver's time; the solution equals the reference's way (evaluate on the host, setSetPoint, advance) at every time.
 static void testSetPointSpline(const char* modelPath, std::size_t N)
@@ -849,6 +913,7 @@ int main(int argc, char** argv)
     testTaskInitializationAndAddTaskRules(argv[2]);
     testWeightProviders();
     testSplines();
+    testSO3Planner();
     if (gpu) {
         testTaskMatrices(argv[2]);
         testClosedLoop(argv[2], 1, false);

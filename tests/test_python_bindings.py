@@ -559,3 +559,89 @@ def test_set_point_spline_through_the_bindings():
     assert com_dev.set_set_point_spline(None) and ik_dev.advance()
     assert com_host.set_set_point(position=c) and ik_host.advance()
     assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
+
+
+# ------------------------------------------------------------------------------------------------ Planners: SO3Planner
+@pytest.mark.parametrize("kind", ["body", "inertial", "inertial_v0"])
+def test_so3_planner(kind):
+    """src/Planners/tests/SO3PlannerTest.cpp:21-167 replayed: between two random rotations over 1 s, sampled every 100 us, the
+    rotation integrates its own velocity (right-plus for the body-fixed planner, left-plus for the inertial one), the velocity
+    its acceleration, and both ends are met at rest (tolerance 1e-3); third section: a non-zero initial velocity along the
+    displacement."""
+    rng = np.random.default_rng(8)
+    R0, R1 = manif.SO3.Random(rng), manif.SO3.Random(rng)
+    T, dT, tol = 1.0, 100e-6, 1e-3
+    planner = blf.planners.SO3PlannerBody() if kind == "body" else blf.planners.SO3PlannerInertial()
+    assert not planner.set_rotations(R0, R1, 0.0)
+    assert planner.set_rotations(R0, R1, timedelta(seconds=T))
+    assert planner.evaluate_point(0.0) is False                                  # boundary conditions missing
+    v0 = manif.SO3Tangent.Zero()
+    if kind == "inertial_v0":
+        v0 = (R1 * R0.inverse()).log() * 2.0
+    assert planner.set_initial_conditions(v0, manif.SO3Tangent.Zero())
+    assert planner.set_final_conditions(manif.SO3Tangent.Zero(), manif.SO3Tangent.Zero())
+    st = planner.evaluate_point(0.0)
+    near = lambda A, B: np.linalg.norm((A - B).coeffs()) < tol
+    assert near(st.rotation, R0) and np.allclose(st.velocity.coeffs(), v0.coeffs(), atol=tol) and np.allclose(st.acceleration.coeffs(), 0, atol=tol)
+    for i in range(1, int(round(T / dT))):
+        step = st.velocity * dT
+        predicted = (st.rotation + step) if kind == "body" else (step + st.rotation)
+        predicted_velocity = st.velocity + st.acceleration * dT
+        st = planner.evaluate_point(i * dT)
+        assert near(predicted, st.rotation)
+        assert np.allclose(predicted_velocity.coeffs(), st.velocity.coeffs(), atol=tol)
+    st = planner.evaluate_point(T)
+    assert near(st.rotation, R1) and np.allclose(st.velocity.coeffs(), 0, atol=tol) and np.allclose(st.acceleration.coeffs(), 0, atol=tol)
+    assert planner.evaluate_point(T + 0.1) is False and planner.evaluate_point(-0.1) is False   # :178-184
+    # a boundary velocity that is not along the displacement is refused (:89-99)
+    skew = blf.planners.SO3PlannerInertial()
+    assert skew.set_rotations(R0, R1, T)
+    d = (R1 * R0.inverse()).log().coeffs()
+    assert skew.set_initial_conditions(manif.SO3Tangent(np.cross(d, [1.0, 0.3, -0.2])), manif.SO3Tangent.Zero())
+    assert skew.set_final_conditions(manif.SO3Tangent.Zero(), manif.SO3Tangent.Zero())
+    assert skew.evaluate_point(0.5) is False
+    # advance()
+    assert not planner.advance() and planner.set_advance_time_step(timedelta(seconds=0.25)) and planner.is_output_valid()
+    for _ in range(6):
+        assert planner.advance()
+    assert near(planner.get_output().rotation, R1)
+    pv = blf.planners.SO3PlannerInertial.project_tangent_vector(R0, R1, manif.SO3Tangent([0.3, -0.1, 0.2]))
+    assert np.linalg.norm(np.cross(pv.coeffs(), d)) < 1e-12
+
+
+@pytest.mark.gpu
+def test_device_minimum_jerk_generator_is_the_inertial_so3_planner():
+    """blfik_set_setpoint_minimum_jerk on an SO3 task == SO3PlannerInertial with zero boundary conditions, sample by sample
+    (rotation and angular velocity), read back with blfik_evaluate_setpoint."""
+    from blf_b200 import capi, tasks as T, workloads as W
+    model = M.ergocub23()
+    task = T.so3_task(model, "chest", "chest", [5.0, 5.0, 5.0], priority=1, weight=[1.0, 1.0, 1.0])
+    reg = T.joint_tracking_task(model, "reg", [1.0] * model.n, priority=1, weight=[1.0] * model.n)
+    N, dur, t0 = 5, 0.8, 2.5
+    rng = np.random.default_rng(2)
+    R0 = [manif.SO3.Random(rng) for _ in range(N)]
+    R1 = [manif.SO3.Random(rng) for _ in range(N)]
+    cm = capi.Model(model)
+    prob = capi.Problem(cm, [task, reg], N)
+    sp = np.zeros((N, 7))
+    sp[:, :4] = [r.quat() for r in R0]
+    prob.set_setpoint(0, sp)
+    tg = sp.copy()
+    tg[:, :4] = [r.quat() for r in R1]
+    prob.set_time(t0)
+    prob.set_setpoint_minimum_jerk(0, tg, dur)
+    planners = []
+    for a, b in zip(R0, R1):
+        p = blf.planners.SO3PlannerInertial()
+        assert p.set_rotations(a, b, dur)
+        assert p.set_initial_conditions(manif.SO3Tangent.Zero(), manif.SO3Tangent.Zero())
+        assert p.set_final_conditions(manif.SO3Tangent.Zero(), manif.SO3Tangent.Zero())
+        planners.append(p)
+    for tau in (0.0, 0.1, 0.37, 0.5, 0.93, 1.0):
+        got = prob.evaluate_setpoint(0, t0 + tau * dur)
+        for i, p in enumerate(planners):
+            st = p.evaluate_point(tau * dur)
+            q = st.rotation.quat()
+            assert min(np.abs(got[i, :4] - q).max(), np.abs(got[i, :4] + q).max()) < 1e-12
+            assert np.abs(got[i, 4:7] - st.velocity.coeffs()).max() < 1e-11
+    prob.close()
