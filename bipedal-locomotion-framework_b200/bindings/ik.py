@@ -108,12 +108,13 @@ class IKLinearTask:
 
     _spline_ok = False         # SE3Task, CoMTask, R3Task: the origin of the set-point can follow a quintic spline on the device
 
-    def set_set_point_spline(self, spline, positions=None, boundary=None):
+    def set_set_point_spline(self, spline, positions=None, boundary=None, cubic=False):
         """Batch extension (no counterpart in the reference, where a Math::QuinticSpline is evaluated on the host and its
         point passed to setSetPoint every period): the origin of this task's set-point follows a quintic spline evaluated on
         the device at the solver's time (QPInverseKinematics.set_time; blfik_set_setpoint_spline).  ``spline`` is a
-        ``math.QuinticSpline`` (every robot the same trajectory), a list of N of them with the same knot times, or the knot
-        times [n_knots] together with ``positions`` [N, n_knots, 3] and ``boundary`` [N, 4, 3]; None switches it off."""
+        ``math.QuinticSpline`` or ``math.CubicSpline`` (every robot the same trajectory), a list of N of them with the same
+        knot times, or the knot times [n_knots] together with ``positions`` [N, n_knots, 3] and ``boundary`` [N, 4, 3]
+        ([N, 2, 3] with ``cubic=True``); None switches it off."""
         name = type(self).__name__
         if not self._spline_ok:
             log().error("[%s::setSetPointSpline] The task has no position set-point a spline could drive.", name)
@@ -134,15 +135,21 @@ class IKLinearTask:
             if any(len(k[0]) != len(parts[0][0]) or np.any(k[0] != parts[0][0]) for k in parts):
                 log().error("[%s::setSetPointSpline] The splines of the robots must share their knot times.", name)
                 return False
+            if any(g._cubic != group[0]._cubic for g in group):
+                log().error("[%s::setSetPointSpline] The splines of the robots must be of one kind.", name)
+                return False
+            cubic = group[0]._cubic
             times = parts[0][0]
             positions = np.stack([k[1] for k in parts])
             boundary = np.stack([np.zeros((4, 3)) if k[2] is None else k[2] for k in parts])
+            if cubic:
+                boundary = np.ascontiguousarray(boundary[:, [0, 2]])     # velocities only
         else:
             times = np.asarray(spline, dtype=np.float64).reshape(-1)
             positions = np.asarray(positions, dtype=np.float64)
             boundary = None if boundary is None else np.asarray(boundary, dtype=np.float64)
-            if positions.shape != (N, len(times), 3) or (boundary is not None and boundary.shape != (N, 4, 3)):
-                log().error("[%s::setSetPointSpline] positions must be [N, n_knots, 3] and boundary [N, 4, 3].", name)
+            if positions.shape != (N, len(times), 3) or (boundary is not None and boundary.shape != (N, 2 if cubic else 4, 3)):
+                log().error("[%s::setSetPointSpline] positions must be [N, n_knots, 3] and boundary [N, 4, 3] ([N, 2, 3] for a cubic spline).", name)
                 return False
         if len(times) < 2:
             log().error("[Spline::setKnots] The number of knots has to be at least 2.")
@@ -150,7 +157,7 @@ class IKLinearTask:
         if np.any(np.diff(times) <= 0.0):
             log().error("[Splines::computePhasesDuration] Two consecutive points have the same time coordinate, or the times decrease.")
             return False
-        self._spline, self._spline_version = (times.copy(), positions.copy(), None if boundary is None else boundary.copy()), self._spline_version + 1
+        self._spline, self._spline_version = (times.copy(), positions.copy(), None if boundary is None else boundary.copy(), bool(cubic)), self._spline_version + 1
         return True
 
     _spline = None

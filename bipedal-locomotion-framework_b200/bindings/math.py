@@ -205,6 +205,8 @@ class QuinticSpline:
     def get_output(self):
         return self._point
 
+    _cubic = False
+
     # ---- batch extension: what blfik_set_setpoint_spline needs from one trajectory
     def knots(self):
         """(times [n], positions [n, dim], boundary [4, dim]); None where unset"""
@@ -212,3 +214,55 @@ class QuinticSpline:
         if self._ic is not None and self._fc is not None:
             bc = _np.stack([self._ic[0], self._ic[1], self._fc[0], self._fc[1]])
         return self._times, self._knots, bc
+
+
+class CubicSpline(QuinticSpline):
+    """Math::CubicSpline<Eigen::VectorXd> (CubicSpline.h:26-330): same interface; the knot velocities make the acceleration
+    continuous, the boundary accelerations are accepted and not used (as in the reference)."""
+    _cubic = True
+
+    def _compute_coefficients(self):
+        prefix = "[Spline::computeCoefficients]"
+        if self._coeffs is not None:
+            return True
+        if self._knots is None:
+            _log().error("%s Please set the knots before computing the coefficients.", prefix)
+            return False
+        dim = self._knots.shape[1]
+        for what, bc in (("initial", self._ic), ("final", self._fc)):
+            if bc is None or bc[0].size != dim or bc[1].size != dim:
+                _log().error("[Spline::setBoundaryVelocitiesAndAcceleration] The size of the %s velocity or acceleration is different from "
+                             "the expected one. Expected: %d.", what, dim)
+                _log().error("%s Unable to set the boundary conditions related to the velocity and acceleration.", prefix)
+                return False
+        T = _np.diff(self._times)
+        if _np.any(T == 0.0):
+            _log().error("[Splines::computePhasesDuration] Two consecutive points have the same time coordinate.")
+            _log().error("%s Unable to compute the phase duration.", prefix)
+            return False
+        x, n = self._knots, len(self._times)
+        v = _np.zeros_like(x)
+        v[0], v[-1] = self._ic[0], self._fc[0]
+        m = n - 2
+        if m > 0:
+            # 2/Tp v_{i-1} + 4 (1/Tp + 1/Tn) v_i + 2/Tn v_{i+1} = 6 (dp/Tp^2 + dn/Tn^2): tridiagonal, eliminated in place
+            Tp, Tn = T[:-1], T[1:]
+            lo, di, up = 2 / Tp, 4 / Tp + 4 / Tn, 2 / Tn
+            r = 6 * ((x[1:-1] - x[:-2]) / Tp[:, None] ** 2 + (x[2:] - x[1:-1]) / Tn[:, None] ** 2)
+            r[0] -= lo[0] * v[0]
+            r[-1] -= up[-1] * v[-1]
+            for i in range(1, m):
+                w = lo[i] / di[i - 1]
+                di[i] -= w * up[i - 1]
+                r[i] -= w * r[i - 1]
+            sol = _np.zeros_like(r)
+            sol[-1] = r[-1] / di[-1]
+            for i in range(m - 2, -1, -1):
+                sol[i] = (r[i] - up[i] * sol[i + 1]) / di[i]
+            v[1:-1] = sol
+        Tc = T[:, None]
+        d = x[1:] - x[:-1]
+        zero = _np.zeros_like(d)
+        self._coeffs = _np.stack([x[:-1], v[:-1], (3 * d - (2 * v[:-1] + v[1:]) * Tc) / Tc ** 2, (-2 * d + (v[:-1] + v[1:]) * Tc) / Tc ** 3,
+                                  zero, zero], axis=1)
+        return True

@@ -38,7 +38,7 @@ EXPORTS = [
     "blfik_set_kernel_path", "blfik_get_kernel_path", "blfik_integrate_state", "blfik_tick_host",
     "blfik_packed_record_len", "blfik_packed_offset", "blfik_tick_packed",
     "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time", "blfik_set_limits",
-    "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline", "blfik_evaluate_setpoint",
+    "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline", "blfik_set_setpoint_cubic_spline", "blfik_evaluate_setpoint",
     "blfik_packed_record_len_ex", "blfik_packed_offset_ex", "blfik_packed_part_len",
 ]
 
@@ -283,23 +283,24 @@ class Problem:
         self.L.blfik_set_setpoint_minimum_jerk.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_double, C.c_int32]
         _check(self.L.blfik_set_setpoint_minimum_jerk(self.handle, int(task), None if tg is None else tg.ctypes.data, float(duration), MEM_HOST))
 
-    def set_setpoint_spline(self, task: int, times, positions, boundary=None):
+    def set_setpoint_spline(self, task: int, times, positions, boundary=None, cubic=False):
         """quintic spline through ``positions`` [N, n_knots, 3] at ``times`` [n_knots] (the problem's clock) for the linear part
         of an SE3 / CoM / R3 task, evaluated on the device at every tick (Math::QuinticSpline semantics); ``boundary``
         [N, 4, 3] = velocity, acceleration at the first knot, velocity, acceleration at the last (None: zero);
-        ``times=None`` switches it off"""
-        self.L.blfik_set_setpoint_spline.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
+        ``times=None`` switches it off.  ``cubic=True``: Math::CubicSpline instead, ``boundary`` [N, 2, 3] = velocity at the
+        first and at the last knot"""
+        fn = self.L.blfik_set_setpoint_cubic_spline if cubic else self.L.blfik_set_setpoint_spline
+        fn.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
         if times is None:
-            _check(self.L.blfik_set_setpoint_spline(self.handle, int(task), 0, None, None, None, MEM_HOST))
+            _check(fn(self.handle, int(task), 0, None, None, None, MEM_HOST))
             return
         tm, x = _f64(times).reshape(-1), _f64(positions)
         if x.shape != (self.N, len(tm), 3):
             raise ValueError(f"positions must be [N, n_knots, 3] = {(self.N, len(tm), 3)}, got {x.shape}")
         bc = None if boundary is None else _f64(boundary)
-        if bc is not None and bc.shape != (self.N, 4, 3):
-            raise ValueError(f"boundary must be [N, 4, 3], got {bc.shape}")
-        _check(self.L.blfik_set_setpoint_spline(self.handle, int(task), len(tm), tm.ctypes.data, x.ctypes.data,
-                                                None if bc is None else bc.ctypes.data, MEM_HOST))
+        if bc is not None and bc.shape != (self.N, 2 if cubic else 4, 3):
+            raise ValueError(f"boundary must be [N, {2 if cubic else 4}, 3], got {bc.shape}")
+        _check(fn(self.handle, int(task), len(tm), tm.ctypes.data, x.ctypes.data, None if bc is None else bc.ctypes.data, MEM_HOST))
 
     def evaluate_setpoint(self, task: int, time: float) -> np.ndarray:
         """[N, setpoint_len] set-point of ``task`` as a tick at ``time`` reads it (stored set-point + attached generators)"""

@@ -189,6 +189,55 @@ __global__ void __launch_bounds__(128) blfik_spline_coefficients_kernel(long lon
     }
 }
 
+// The same for Math::CubicSpline (CubicSpline.h:77-330): the knot velocities make the acceleration continuous, a scalar
+// tridiagonal system per robot and coordinate; fac[i] = l_i, m_i = l_i / d'_{i-1}, 1 / d'_i, u_i at offsets 0, 4, 8, 12.  The
+// cubic of every interval is stored as a quintic with c_4 = c_5 = 0, so the tick evaluates both kinds with the same code.
+// bc: [N][2][3], velocity at the first and at the last knot.
+__global__ void __launch_bounds__(128) blfik_cubic_spline_coefficients_kernel(long long N, int nk, const double* __restrict__ times,
+                                                                              const double* __restrict__ fac, const double* __restrict__ x,
+                                                                              const double* __restrict__ bc, double* __restrict__ coef)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= N * 3) return;
+    const long long robot = idx / 3;
+    const int c = (int)(idx - robot * 3);
+    const double* xr = x + (size_t)robot * nk * 3 + c;
+    double* cf = coef + (size_t)robot * (nk - 1) * 18 + c;
+    double v0 = 0.0, vf = 0.0;
+    if (bc) v0 = bc[(size_t)robot * 6 + c], vf = bc[(size_t)robot * 6 + 3 + c];
+    const int m = nk - 2;
+    double prev = 0.0;
+    for (int i = 0; i < m; i++) {
+        const double ip = 1.0 / (times[i + 1] - times[i]), in = 1.0 / (times[i + 2] - times[i + 1]);
+        const double dp = xr[3 * (i + 1)] - xr[3 * i], dn = xr[3 * (i + 2)] - xr[3 * (i + 1)];
+        const double* f = fac + 16 * i;
+        double r = 6.0 * (dp * ip * ip + dn * in * in);
+        if (i == 0) r -= f[0] * v0;
+        if (i == m - 1) r -= f[12] * vf;
+        if (i > 0) r -= f[4] * prev;
+        cf[18 * (i + 1) + 9] = r;
+        prev = r;
+    }
+    double vn = vf;
+    for (int i = m - 1; i >= 0; i--) {
+        const double* f = fac + 16 * i;
+        double r = cf[18 * (i + 1) + 9];
+        if (i < m - 1) r -= f[12] * vn;
+        vn = f[8] * r;
+        cf[18 * (i + 1) + 3] = vn;
+    }
+    cf[3] = v0;
+    for (int j = 0; j < nk - 1; j++) {
+        const double T = times[j + 1] - times[j], iT = 1.0 / T;
+        const double x0 = xr[3 * j], d = xr[3 * (j + 1)] - x0;
+        const double vs = cf[18 * j + 3], ve = j + 1 <= nk - 2 ? cf[18 * (j + 1) + 3] : vf;
+        cf[18 * j] = x0;
+        cf[18 * j + 6] = (3.0 * d - (2.0 * vs + ve) * T) * iT * iT;
+        cf[18 * j + 9] = (-2.0 * d + (vs + ve) * T) * iT * iT * iT;
+        cf[18 * j + 12] = 0.0, cf[18 * j + 15] = 0.0;
+    }
+}
+
 // The set-point a tick at time t reads: the stored record with the attached generators applied, one thread per robot.
 __global__ void __launch_bounds__(128) blfik_evaluate_setpoint_kernel(const DevTask* tasks, int t, long long N, double time, double* out)
 {
@@ -960,8 +1009,8 @@ static bool m22_inv(const double* a, double* o)
     return true;
 }
 
-extern "C" int blfik_set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_knots, const double* times, const double* positions,
-                                         const double* boundary, int32_t mem)
+static int set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_knots, const double* times, const double* positions,
+                               const double* boundary, int32_t mem, bool cubic)
 {
     CHECK_P(p, "blfik_set_setpoint_spline");
     CHECK_TASK(p, t, "blfik_set_setpoint_spline");
@@ -995,6 +1044,17 @@ extern "C" int blfik_set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_
         double D[4] = {-36.0 / (Tp * Tp) + 36.0 / (Tn * Tn), 9.0 / Tp + 9.0 / Tn,
                        -192.0 / (Tp * Tp * Tp) - 192.0 / (Tn * Tn * Tn), 36.0 / (Tp * Tp) - 36.0 / (Tn * Tn)};
         const double U[4] = {24.0 / (Tn * Tn), -3.0 / Tn, -168.0 / (Tn * Tn * Tn), 24.0 / (Tn * Tn)};
+        if (cubic) {   // scalar system: 2/Tp v_{i-1} + 4 (1/Tp + 1/Tn) v_i + 2/Tn v_{i+1} = 6 (dp/Tp^2 + dn/Tn^2)
+            double d = 4.0 / Tp + 4.0 / Tn;
+            f[0] = 2.0 / Tp, f[12] = 2.0 / Tn;
+            if (i > 0) {
+                f[4] = f[0] * Dprev_inv[0];
+                d -= f[4] * Uprev[0];
+            }
+            f[8] = 1.0 / d;   // strictly diagonally dominant: d >= 2/Tp + 2/Tn > 0 after the elimination
+            Dprev_inv[0] = f[8], Uprev[0] = f[12];
+            continue;
+        }
         for (int k = 0; k < 4; k++) f[k] = L[k], f[12 + k] = U[k];
         if (i > 0) {
             double MU[4];
@@ -1015,7 +1075,7 @@ extern "C" int blfik_set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_
         CU(cudaMalloc((void**)&h.d_sp_coef, (size_t)p->N * (n_knots - 1) * 18 * sizeof(double)));
         h.sp_cap = n_knots;
     }
-    const size_t npos = (size_t)p->N * n_knots * 3, nbc = (size_t)p->N * 12;
+    const size_t npos = (size_t)p->N * n_knots * 3, nbc = (size_t)p->N * (cubic ? 6 : 12);
     const double *d_x = positions, *d_bc = boundary;
     double* stage = nullptr;
     if (mem != BLFIK_MEM_DEVICE) {
@@ -1027,8 +1087,12 @@ extern "C" int blfik_set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_
     cudaMemcpyAsync(h.d_sp_times, times, (size_t)n_knots * sizeof(double), cudaMemcpyHostToDevice, p->stream);
     cudaMemcpyAsync(h.d_sp_fac, fac.data(), fac.size() * sizeof(double), cudaMemcpyHostToDevice, p->stream);
     const long long threads = (long long)p->N * 3;
-    blfik_spline_coefficients_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, p->stream>>>(p->N, n_knots, h.d_sp_times, h.d_sp_fac, d_x, d_bc,
-                                                                                             h.d_sp_coef);
+    if (cubic)
+        blfik_cubic_spline_coefficients_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, p->stream>>>(p->N, n_knots, h.d_sp_times, h.d_sp_fac,
+                                                                                                       d_x, d_bc, h.d_sp_coef);
+    else
+        blfik_spline_coefficients_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, p->stream>>>(p->N, n_knots, h.d_sp_times, h.d_sp_fac, d_x,
+                                                                                                 d_bc, h.d_sp_coef);
     p->launches++;
     cudaError_t e = cudaGetLastError();
     if (stage) {   // the pageable sources (times, fac, positions) are consumed before this returns
@@ -1042,6 +1106,18 @@ extern "C" int blfik_set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_
     h.traj_omega = 0.0;   // the sinusoidal generator stands alone; the minimum-jerk one keeps the orientation of an SE3 task
     p->tasks_dirty = true;
     return BLFIK_OK;
+}
+
+extern "C" int blfik_set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_knots, const double* times, const double* positions,
+                                         const double* boundary, int32_t mem)
+{
+    return set_setpoint_spline(p, t, n_knots, times, positions, boundary, mem, false);
+}
+
+extern "C" int blfik_set_setpoint_cubic_spline(blfik_problem* p, int32_t t, int32_t n_knots, const double* times, const double* positions,
+                                               const double* boundary, int32_t mem)
+{
+    return set_setpoint_spline(p, t, n_knots, times, positions, boundary, mem, true);
 }
 
 extern "C" int blfik_set_setpoint_trajectory(blfik_problem* p, int32_t t, const double* amplitude, double period, const double* phase, int32_t mem)

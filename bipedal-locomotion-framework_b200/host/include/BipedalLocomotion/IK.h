@@ -82,7 +82,7 @@ public:
      *  solver's time (QPInverseKinematics::setTime; blfik_set_setpoint_spline) instead of a Math::QuinticSpline evaluated
      *  on the host whose point goes to setSetPoint every period.  One spline per robot, all with the same knot times. */
     virtual bool acceptsSetPointSpline() const { return false; }
-    bool setSetPointSpline(const std::vector<Math::QuinticSpline<Vector3d>>& splines)
+    template <class SplineType> bool setSetPointSpline(const std::vector<SplineType>& splines)   // Math::QuinticSpline<Vector3d> or Math::CubicSpline<Vector3d>
     {
         const std::size_t N = m_kinDyn ? m_kinDyn->getBatchSize() : 0;
         if (!acceptsSetPointSpline()) {
@@ -98,7 +98,8 @@ public:
             log()->error("[Spline::setKnots] The number of knots has to be at least 2.");
             return false;
         }
-        std::vector<double> times(first.size()), pos(N * first.size() * 3), bc(N * 12, 0.0);
+        constexpr std::size_t nbc = SplineType::isCubic ? 6 : 12;   // the cubic spline takes the two end velocities only
+        std::vector<double> times(first.size()), pos(N * first.size() * 3), bc(N * nbc, 0.0);
         for (std::size_t k = 0; k < first.size(); k++) times[k] = std::chrono::duration<double>(first[k].time).count();
         for (std::size_t i = 0; i < N; i++) {
             const auto& kn = splines[i].knots();
@@ -113,10 +114,14 @@ public:
                 }
                 for (int c = 0; c < 3; c++) pos[(i * kn.size() + k) * 3 + c] = kn[k].position[c];
             }
-            Math::QuinticSpline<Vector3d>::DerivativeBoundaryConditions ic, fc;
+            typename SplineType::DerivativeBoundaryConditions ic, fc;
             if (splines[i].boundaryConditions(ic, fc))
-                for (int c = 0; c < 3; c++)
-                    bc[i * 12 + c] = ic.velocity[c], bc[i * 12 + 3 + c] = ic.acceleration[c], bc[i * 12 + 6 + c] = fc.velocity[c], bc[i * 12 + 9 + c] = fc.acceleration[c];
+                for (int c = 0; c < 3; c++) {
+                    if (SplineType::isCubic)
+                        bc[i * 6 + c] = ic.velocity[c], bc[i * 6 + 3 + c] = fc.velocity[c];
+                    else
+                        bc[i * 12 + c] = ic.velocity[c], bc[i * 12 + 3 + c] = ic.acceleration[c], bc[i * 12 + 6 + c] = fc.velocity[c], bc[i * 12 + 9 + c] = fc.acceleration[c];
+                }
         }
         for (std::size_t k = 0; k + 1 < times.size(); k++)
             if (!(times[k + 1] > times[k])) {
@@ -124,6 +129,7 @@ public:
                 return false;
             }
         m_splineTimes = std::move(times), m_splinePositions = std::move(pos), m_splineBoundary = std::move(bc);
+        m_splineCubic = SplineType::isCubic;
         m_splineVersion++;
         return true;
     }
@@ -131,6 +137,7 @@ public:
     const std::vector<double>& splineTimes() const { return m_splineTimes; }
     const std::vector<double>& splinePositions() const { return m_splinePositions; }
     const std::vector<double>& splineBoundary() const { return m_splineBoundary; }
+    bool splineIsCubic() const { return m_splineCubic; }
     unsigned long splineVersion() const { return m_splineVersion; }
 
 protected:
@@ -210,6 +217,7 @@ protected:
     std::vector<double> m_sp, m_fb, m_splineTimes, m_splinePositions, m_splineBoundary;
     unsigned long m_spVersion{0}, m_gainsVersion{0}, m_fbVersion{0}, m_splineVersion{0};
     int m_inspect{-1};
+    bool m_splineCubic{false};
 };
 
 using IKLinearTaskFactory = System::Factory<IKLinearTask>;

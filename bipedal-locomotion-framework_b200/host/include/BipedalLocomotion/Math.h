@@ -220,9 +220,66 @@ private:
     DerivativeBoundaryConditions m_initialConditions, m_finalConditions;
 };
 
+/** CubicSpline.h:26-330: the knot velocities make the acceleration continuous; the boundary accelerations handed to
+ *  setInitialConditions / setFinalConditions are accepted and not used, as in the reference. */
+template <typename T> class CubicSpline : public Spline<T>
+{
+public:
+    static constexpr bool isCubic = true;
+
+private:
+    void updatePolynomialCoefficients(std::size_t i) final
+    {
+        const auto& k0 = this->m_knots[i];
+        const auto& k1 = this->m_knots[i + 1];
+        const double d = detail::seconds(k1.time - k0.time);
+        const std::size_t dim = k0.position.size();
+        std::vector<T>& c = this->m_coefficients[i];
+        c.assign(6, k0.position);
+        for (std::size_t k = 0; k < dim; k++) {
+            const double dx = k1.position[k] - k0.position[k], v0 = k0.velocity[k], v1 = k1.velocity[k];
+            c[1][k] = v0;
+            c[2][k] = (3.0 * dx - (2.0 * v0 + v1) * d) / (d * d);
+            c[3][k] = (-2.0 * dx + (v0 + v1) * d) / (d * d * d);
+            c[4][k] = 0.0, c[5][k] = 0.0;
+        }
+    }
+    void computeIntermediateQuantities() final
+    {
+        // 2/Tp v_{i-1} + 4 (1/Tp + 1/Tn) v_i + 2/Tn v_{i+1} = 6 (dp/Tp^2 + dn/Tn^2) at every interior knot i
+        auto& kn = this->m_knots;
+        const std::size_t m = kn.size() - 2, dim = kn.front().position.size();
+        std::vector<double> di(m), up(m), r(m * dim);
+        for (std::size_t i = 0; i < m; i++) {
+            const double Tp = detail::seconds(kn[i + 1].time - kn[i].time), Tn = detail::seconds(kn[i + 2].time - kn[i + 1].time);
+            const double lo = 2.0 / Tp;
+            di[i] = 4.0 / Tp + 4.0 / Tn, up[i] = 2.0 / Tn;
+            const double w = i > 0 ? lo / di[i - 1] : 0.0;
+            if (i > 0) di[i] -= w * up[i - 1];
+            for (std::size_t k = 0; k < dim; k++) {
+                double v = 6.0 * ((kn[i + 1].position[k] - kn[i].position[k]) / (Tp * Tp) + (kn[i + 2].position[k] - kn[i + 1].position[k]) / (Tn * Tn));
+                if (i == 0) v -= lo * kn[0].velocity[k];
+                if (i == m - 1) v -= up[i] * kn[m + 1].velocity[k];
+                if (i > 0) v -= w * r[(i - 1) * dim + k];
+                r[i * dim + k] = v;
+            }
+        }
+        for (std::size_t i = m; i-- > 0;)
+            for (std::size_t k = 0; k < dim; k++) {
+                double v = r[i * dim + k];
+                if (i + 1 < m) v -= up[i] * kn[i + 2].velocity[k];
+                kn[i + 1].velocity[k] = v / di[i];
+            }
+    }
+};
+
 /** QuinticSpline.h:26-415 */
 template <typename T> class QuinticSpline : public Spline<T>
 {
+public:
+    static constexpr bool isCubic = false;
+
+private:
     void updatePolynomialCoefficients(std::size_t i) final
     {
         const auto& k0 = this->m_knots[i];

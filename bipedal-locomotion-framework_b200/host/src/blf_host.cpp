@@ -1391,9 +1391,10 @@ bool QPInverseKinematics::tick(double dt, uint32_t flags)
         }
         if (e.task->acceptsSetPointSpline() && e.task->splineVersion() != e.uploadedSpline) {   // setSetPointSpline(...) since the last tick
             const auto& tm = e.task->splineTimes();
-            const int rc = tm.empty() ? blfik_set_setpoint_spline(prob, static_cast<int32_t>(t), 0, nullptr, nullptr, nullptr, BLFIK_MEM_HOST)
-                                      : blfik_set_setpoint_spline(prob, static_cast<int32_t>(t), static_cast<int32_t>(tm.size()), tm.data(),
-                                                                  e.task->splinePositions().data(), e.task->splineBoundary().data(), BLFIK_MEM_HOST);
+            const auto set = e.task->splineIsCubic() ? blfik_set_setpoint_cubic_spline : blfik_set_setpoint_spline;
+            const int rc = tm.empty() ? set(prob, static_cast<int32_t>(t), 0, nullptr, nullptr, nullptr, BLFIK_MEM_HOST)
+                                      : set(prob, static_cast<int32_t>(t), static_cast<int32_t>(tm.size()), tm.data(), e.task->splinePositions().data(),
+                                            e.task->splineBoundary().data(), BLFIK_MEM_HOST);
             if (rc != BLFIK_OK) return fail("Unable to set the set-point spline");
             e.uploadedSpline = e.task->splineVersion();
         }

@@ -226,6 +226,12 @@ int blfik_set_setpoint_minimum_jerk(blfik_problem* problem, int32_t task, const 
 #define BLFIK_MAX_SPLINE_KNOTS 1024
 int blfik_set_setpoint_spline(blfik_problem* problem, int32_t task, int32_t n_knots, const double* times,
                               const double* positions, const double* boundary, int32_t mem);
+/* The same with Math::CubicSpline<Eigen::Vector3d> (CubicSpline.h:77-330, the default interpolation of
+ * Planners::SwingFootPlanner): knot velocities from the continuity of the acceleration; boundary [N][2][3] = velocity at
+ * the first and at the last knot (NULL: zero) -- the boundary accelerations a caller hands to the reference's class are
+ * not used by it.  A task has one spline: this replaces a quintic one and vice versa; n_knots == 0 switches it off. */
+int blfik_set_setpoint_cubic_spline(blfik_problem* problem, int32_t task, int32_t n_knots, const double* times,
+                                    const double* positions, const double* boundary, int32_t mem);
 /* The set-point of a task as a tick at `time` reads it: the stored set-point (blfik_set_setpoint) with the attached
  * generators applied, out [N][blfik_setpoint_len(task)].  What the reference's callers log next to the measured pose (the
  * output of their spline / planner, e.g. Spline::getOutput, Spline.h:248-254, before it goes to setSetPoint); no solver

@@ -79,6 +79,46 @@ def quintic_spline_coefficients(times, x, v0=None, a0=None, vf=None, af=None):
     return coeffs, v, a
 
 
+def cubic_spline_coefficients(times, x, v0=None, vf=None):
+    """Math::CubicSpline (CubicSpline.h:77-93 the interval polynomial, :95-330 the knot velocities from the continuity of the
+    acceleration: 2/Tp v_{i-1} + 4 (1/Tp + 1/Tn) v_i + 2/Tn v_{i+1} = 6 (dp/Tp^2 + dn/Tn^2)).  Returns the same layout as the
+    quintic, [n-1, 6, ...] with c_4 = c_5 = 0, and the knot velocities."""
+    times = np.asarray(times, dtype=np.float64)
+    x = np.asarray(x, dtype=np.float64)
+    n = len(times)
+    if n < 2 or x.shape[0] != n:
+        raise ValueError("at least two knots, one time per knot (Spline.h:338-349)")
+    T = np.diff(times)
+    if np.any(T == 0.0):
+        raise ValueError("two consecutive knots have the same time (Spline.h:444-448)")
+    z = np.zeros(x.shape[1:])
+    v = np.zeros_like(x)
+    v[0], v[-1] = (z if v0 is None else np.asarray(v0, dtype=np.float64)), (z if vf is None else np.asarray(vf, dtype=np.float64))
+    m = n - 2
+    if m > 0:
+        A = np.zeros((m, m))
+        r = np.zeros((m,) + x.shape[1:])
+        for i in range(m):
+            Tp, Tn = T[i], T[i + 1]
+            A[i, i] = 4.0 / Tp + 4.0 / Tn
+            r[i] = 6.0 * ((x[i + 1] - x[i]) / Tp ** 2 + (x[i + 2] - x[i + 1]) / Tn ** 2)
+            if i > 0:
+                A[i, i - 1] = 2.0 / Tp
+            else:
+                r[i] -= 2.0 / Tp * v[0]
+            if i < m - 1:
+                A[i, i + 1] = 2.0 / Tn
+            else:
+                r[i] -= 2.0 / Tn * v[-1]
+        v[1:-1] = np.linalg.solve(A, r.reshape(m, -1)).reshape(r.shape)
+    Tc = T.reshape((-1,) + (1,) * (x.ndim - 1))
+    d = x[1:] - x[:-1]
+    zero = np.zeros_like(d)
+    coeffs = np.stack([x[:-1], v[:-1], (3.0 * d - (2.0 * v[:-1] + v[1:]) * Tc) / Tc ** 2, (-2.0 * d + (v[:-1] + v[1:]) * Tc) / Tc ** 3,
+                       zero, zero], axis=1)
+    return coeffs, v
+
+
 def spline_evaluate(times, coeffs, t):
     """position, velocity, acceleration at time t (Spline.h:271-320, 594-644)."""
     times = np.asarray(times, dtype=np.float64)

@@ -1135,10 +1135,11 @@ def test_quintic_spline_setpoint_generator(path):
 @pytest.mark.parametrize("seed", range(6))
 def test_generators_evaluated_setpoints_vs_oracle(seed):
     """blfik_evaluate_setpoint against the host restatements, directly on the set-point (no solve in between): quintic
-    splines with 2 ... 40 uneven knots and random boundary conditions (oracle/spline.py) on the CoM and a foot, the
+    and cubic splines with 2 ... 40 uneven knots and random boundary conditions (oracle/spline.py) on the CoM and a foot, the
     minimum-jerk generator on the foot's orientation and on the torso, at random times inside and outside the knots."""
-    from oracle.spline import quintic_spline_coefficients, spline_evaluate
+    from oracle.spline import cubic_spline_coefficients, quintic_spline_coefficients, spline_evaluate
     rng = np.random.default_rng(100 + seed)
+    cubic = seed % 2 == 1          # Math::CubicSpline on the odd seeds
     w = W.config(5)
     N = 7
     inp = W.synth_inputs(w, N, 5)
@@ -1157,9 +1158,12 @@ def test_generators_evaluated_setpoints_vs_oracle(seed):
     knots, bcs = {}, {}
     for ti in (0, 1):
         knots[ti] = inp.setpoints[ti][:, None, :3] + np.cumsum(rng.uniform(-0.05, 0.05, (N, nk, 3)), axis=1)
-        bcs[ti] = rng.uniform(-0.5, 0.5, (N, 4, 3))
-        prob.set_setpoint_spline(ti, times, knots[ti], bcs[ti])
-    co = {ti: [quintic_spline_coefficients(times, knots[ti][i], *bcs[ti][i])[0] for i in range(N)] for ti in (0, 1)}
+        bcs[ti] = rng.uniform(-0.5, 0.5, (N, 2 if cubic else 4, 3))
+        if cubic and ti == 0:
+            prob.set_setpoint_spline(ti, times, knots[ti], rng.uniform(-0.5, 0.5, (N, 4, 3)))   # replaced by the cubic one below
+        prob.set_setpoint_spline(ti, times, knots[ti], bcs[ti], cubic=cubic)
+    make_co = cubic_spline_coefficients if cubic else quintic_spline_coefficients
+    co = {ti: [make_co(times, knots[ti][i], *bcs[ti][i])[0] for i in range(N)] for ti in (0, 1)}
     scale = {ti: max(1.0, np.abs(np.diff(knots[ti], axis=1)).max() / np.diff(times).min()) for ti in (0, 1)}
     for t in np.concatenate([[times[0] - 0.1, times[0], times[-1], times[-1] + 0.2], times[:3], rng.uniform(times[0], times[-1], 12)]):
         got = {ti: prob.evaluate_setpoint(ti, t) for ti in (0, 1, 5, 6)}

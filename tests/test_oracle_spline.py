@@ -4,7 +4,7 @@ define the spline (C4 at the interior knots, boundary conditions, clamping outsi
 import numpy as np
 import pytest
 
-from oracle.spline import quintic_spline_coefficients, spline_evaluate
+from oracle.spline import cubic_spline_coefficients, quintic_spline_coefficients, spline_evaluate
 
 
 def _poly(c, t, k=0):
@@ -64,3 +64,30 @@ def test_two_knots_at_rest_is_the_minimum_jerk_profile_and_bad_knots_are_refused
         quintic_spline_coefficients([0.0], x[:1])
     with pytest.raises(ValueError):
         quintic_spline_coefficients([0.0, 0.0], x)
+
+
+def test_cubic_spline_through_samples_of_a_cubic_is_that_cubic():
+    """SplineTest.cpp "Cubic spline" (:185-330): 100 knots on a random cubic in R^4 between 320 ms and 642 s; position and
+    velocity are checked (isApprox 1e-5); plus C2 at the interior knots of an uneven spline and the clamped end velocities."""
+    rng = np.random.default_rng(9)
+    c = np.concatenate([rng.uniform(-1.0, 1.0, (4, 4)), np.zeros((2, 4))])
+    times = 0.32 + (642.0 - 0.32) / 99 * np.arange(100)
+    x = np.stack([_poly(c, t) for t in times])
+    co, _ = cubic_spline_coefficients(times, x, _poly(c, times[0], 1), _poly(c, times[-1], 1))
+    for i in range(0, 1000, 7):
+        t = 0.32 + (times[-1] - 0.32) / 1000 * i
+        pos, vel, _ = spline_evaluate(times, co, t)
+        for got, k in ((pos, 0), (vel, 1)):
+            want = _poly(c, t, k)
+            assert np.linalg.norm(got - want) <= 1e-5 * min(np.linalg.norm(got), np.linalg.norm(want))
+    times = np.sort(np.concatenate([[0.0, 2.0], rng.uniform(0.05, 1.95, 6)]))
+    x = rng.uniform(-1, 1, (8, 3))
+    va, vb = rng.uniform(-1, 1, 3), rng.uniform(-1, 1, 3)
+    co, v = cubic_spline_coefficients(times, x, va, vb)
+    T = np.diff(times)
+    der = lambda cc, t, k: sum(np.prod(np.arange(i, i - k, -1)) * cc[i] * t ** (i - k) for i in range(k, 6))
+    for i in range(6):
+        for k in range(0, 3):
+            assert np.abs(der(co[i], T[i], k) - der(co[i + 1], 0.0, k)).max() < 1e-9, (i, k)
+    assert np.abs(der(co[0], 0.0, 1) - va).max() < 1e-13 and np.abs(der(co[-1], T[-1], 1) - vb).max() < 1e-10
+    assert np.all(co[:, 4:] == 0.0)

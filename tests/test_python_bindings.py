@@ -645,3 +645,23 @@ def test_device_minimum_jerk_generator_is_the_inertial_so3_planner():
             assert min(np.abs(got[i, :4] - q).max(), np.abs(got[i, :4] + q).max()) < 1e-12
             assert np.abs(got[i, 4:7] - st.velocity.coeffs()).max() < 1e-11
     prob.close()
+
+
+def test_cubic_spline():
+    """src/Math/tests/SplineTest.cpp "Cubic spline" (:185-330) through the Python class: knots on a random cubic, position and
+    velocity reproduced; the acceleration is continuous across the knots."""
+    rng = np.random.default_rng(13)
+    coefficients = [rng.random((4, 1)) for _ in range(4)] + [np.zeros((4, 1))] * 2
+    init_time, final_time = 0.32, 2.64
+    time = [init_time + (final_time - init_time) / 99 * i for i in range(100)]
+    spline = blf.math.CubicSpline()
+    assert spline.set_knots([_quintic(coefficients, t) for t in time], time)
+    assert spline.set_initial_conditions(_quintic(coefficients, init_time, 1), _quintic(coefficients, init_time, 2))
+    assert spline.set_final_conditions(_quintic(coefficients, final_time, 1), _quintic(coefficients, final_time, 2))
+    position, velocity, acceleration = np.zeros(4), np.zeros(4), np.zeros(4)
+    for i in range(0, 10000, 7):
+        t = init_time + (final_time - init_time) / 1e4 * i
+        assert spline.evaluate_point(t, position, velocity, acceleration)
+        assert np.allclose(_quintic(coefficients, t).T[0], position, atol=1e-5)
+        assert np.allclose(_quintic(coefficients, t, 1).T[0], velocity, atol=1e-5)
+        assert np.allclose(_quintic(coefficients, t, 2).T[0], acceleration, atol=1e-4)
