@@ -3,6 +3,7 @@
 #include "../../include/blfik.h"
 #include "blfik_device.cuh"
 #include "blfik_fast.cuh"
+#include "blfik_eq.cuh"
 
 #include <cstdarg>
 #include <cstdio>
@@ -350,6 +351,11 @@ struct blfik_problem {
     bool own_stream = false;
     int warps_per_block = 4, grid = 148;
     size_t smem_bytes = 0;
+    // equality-only kernel (blfik_eq.cuh): problems without inequality rows that the register-resident kernel cannot hold
+    bool eq_kernel = false;
+    Layout Leq;
+    int eq_wpb = 8, eq_grid = 148;
+    size_t eq_smem = 0;
     int num_sms = 148;
     long long launches = 0;
     // register-resident kernel (blfik_fast.cuh), used when nv <= 32 and K <= 32
@@ -582,11 +588,33 @@ static int dev_alloc(blfik_problem* p, size_t count, T** out, bool zero = true)
     return BLFIK_OK;
 }
 
+// Row layout of the equality-only kernel (blfik_eq.cuh): B (K x LD) in Cs, G / its Cholesky factor in Ss, its inverse in Ym,
+// the diagonal cost in Hs (a vector here), no nv x nv matrix at all.  A keeps six rows: DistanceTask builds the Jacobian of
+// its reference frame there.
+static Layout make_layout_eq(int n, int me, int K)
+{
+    Layout L;
+    const int nv = n + 6, nl = n + 1;
+    L.nv = nv, L.me = me, L.K = K;
+    L.LD = (nv & 1) ? nv : nv + 1;
+    L.LDE = (K & 1) ? K : K + 1;
+    int o = 0;
+    auto take = [&](int cnt) { int r = o; o += (cnt + 1) & ~1; return r; };
+    L.linkR = take(9 * nl), L.linkP = take(3 * nl), L.axisW = take(3 * nl), L.mcw = take(3 * nl);
+    L.Hs = take(nv), L.A = take(6 * L.LD), L.B = 0;
+    L.Cs = take(K * L.LD), L.Ym = take(K * L.LDE), L.Wm = 0, L.Ss = take(K * L.LDE), L.Jt = take(6 * L.LD);
+    L.g = take(nv), L.b = take(K), L.lo = take(nv), L.hi = take(nv), L.x = take(nv), L.z = 0, L.y = 0;
+    L.r = take(nv), L.xb = 0, L.wb = take(K), L.lam = take(K), L.gp = take(nv), L.bp = take(K), L.bd = take(K), L.t = 0;
+    L.act = 0;
+    L.total = o;
+    return L;
+}
+
 static Layout make_layout(int n, int me)
 {
     Layout L;
     const int nv = n + 6, nl = n + 1;
-    L.nv = nv, L.me = me;
+    L.nv = nv, L.me = me, L.K = 0;
     L.LD = (nv & 1) ? nv : nv + 1;
     L.LDE = (me & 1) ? me : me + 1;
     int o = 0;
@@ -811,6 +839,28 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
                     cudaFuncSetAttribute((const void*)p->fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) != cudaSuccess)
                     return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cannot reserve %zu B of shared memory for the register-resident kernel: %s",
                                      p->fast_smem, cudaGetErrorString(cudaGetLastError())));
+            }
+        }
+    }
+
+    // ---- equality-only kernel: no box (inequality tasks, priority-0 joint tracking), at most 64 dense rows
+    if (!p->fast_kernel && p->K >= 1 && p->K <= 64) {
+        bool box = false;
+        for (const HostTask& h : p->tasks)
+            box |= is_inequality(h.d.type) || (h.d.type == BLFIK_TASK_JOINT_TRACKING && h.d.priority == 0);
+        if (!box) {
+            p->Leq = make_layout_eq(n, me, p->K);
+            const size_t eper = (size_t)p->Leq.total * sizeof(double);
+            int ew = (int)((sm_total - 2048) / (eper + 64));
+            if (ew > 16) ew = 16;                      // register file: 256 threads per block at <= 128 registers
+            int ewpb = ew >= 8 ? 8 : (ew >= 4 ? 4 : (ew >= 2 ? 2 : 1));
+            if (ew >= 1 && (size_t)ewpb * eper <= (size_t)smem_optin &&
+                cudaFuncSetAttribute(blfik_tick_eq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) == cudaSuccess) {
+                p->eq_kernel = true;
+                p->eq_wpb = ewpb, p->eq_smem = (size_t)ewpb * eper;
+                const long long ewant = (N + ewpb - 1) / ewpb;
+                const long long ecap = (long long)p->num_sms * (ew / ewpb);
+                p->eq_grid = (int)(ewant < ecap ? ewant : ecap);
             }
         }
     }
@@ -1318,6 +1368,10 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
             FP.arrive_timeout = timeout_env;    // ~0.25 s of SM clocks (the whole transfer takes ~1 ms): copies and kernels are not overlapping
         }
         p->fast_kernel<<<(int)(want < p->fast_grid ? want : p->fast_grid), p->fast_wpb * 32, p->fast_smem, stream>>>(FP);
+    } else if (p->eq_kernel && p->path == 0 && !P.dbg.H) {   // the debug read-back wants H: the generic kernel forms it
+        P.L = p->Leq;
+        const long long want = (count + p->eq_wpb - 1) / p->eq_wpb;
+        blfik_tick_eq_kernel<<<(int)(want < p->eq_grid ? want : p->eq_grid), p->eq_wpb * 32, p->eq_smem, stream>>>(P);
     } else {
         const long long want = (count + p->warps_per_block - 1) / p->warps_per_block;
         blfik_tick_kernel<<<(int)(want < p->grid ? want : p->grid), p->warps_per_block * 32, p->smem_bytes, stream>>>(P);
@@ -1657,7 +1711,7 @@ extern "C" int blfik_set_kernel_path(blfik_problem* p, int32_t path)
 extern "C" int32_t blfik_get_kernel_path(const blfik_problem* p)
 {
     if (!p) return -1;
-    return (p->fast_kernel && p->path == 0) ? 2 : 1;
+    return (p->fast_kernel && p->path == 0) ? 2 : ((p->eq_kernel && p->path == 0) ? 3 : 1);
 }
 
 extern "C" int blfik_get_output(blfik_problem* p, double* nu, int32_t mem)

@@ -86,6 +86,7 @@ struct Settings {
 // shared-memory layout of one warp, in doubles (computed on the host)
 struct Layout {
     int nv, me, LD, LDE;
+    int K;                                 // dense task rows, equality + cost (row layout of the equality-only kernel)
     int linkR, linkP, axisW, mcw;          // kinematics
     int Hs, A, B, Cs, Ym, Wm, Ss, Jt;      // matrices
     int g, b, lo, hi, x, z, y, r, xb, wb, lam, gp, bp, bd, t;  // vectors
@@ -610,13 +611,19 @@ __device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long lon
 // and, because every inequality row of the reference is +-e_j' (JointLimitsTask.cpp:110-113,
 // JointVelocityLimitsTask.cpp), the intersection of those rows as a per-joint box [lo, hi].
 // A priority-0 JointTrackingTask (rows e_j' x = b_j) becomes lo = hi = b_j.
+// ROWS = true (the equality-only kernel, blfik_eq.cuh) keeps the problem in factored form instead of forming H: every dense
+// row, priority 0 or 1, goes to row tk.brow + r of w.Cs (cost rows scaled by the square root of their weight, w.bd marks
+// them with 1), its right-hand side to w.b, and w.Hs is the vector of the diagonal cost terms (JointTrackingTask weights).
+template <bool ROWS = false>
 __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, long long robot, const double* s, int lane, double tnow)
 {
     const DevModel& m = P.m;
     const Layout& L = P.L;
     const int nv = L.nv, LD = L.LD, n = m.n;
     for (int i = lane; i < nv; i += 32) {
-        for (int j = 0; j < nv; j++) w.Hs[i * LD + j] = 0.0;
+        if (ROWS) w.Hs[i] = 0.0;
+        else
+            for (int j = 0; j < nv; j++) w.Hs[i * LD + j] = 0.0;
         w.g[i] = 0.0, w.lo[i] = -kInf, w.hi[i] = kInf;
     }
     __syncwarp();
@@ -711,7 +718,13 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
                 }
             }
             __syncwarp();
-            if (tk.priority == 0) {
+            if (ROWS) {
+                for (int r = 0; r < rows; r++) {
+                    const double sc = tk.priority == 0 ? 1.0 : sqrt(tk.weight[r]);
+                    for (int c = lane; c < nv; c += 32) w.Cs[(tk.brow + r) * LD + c] = sc * w.Jt[src[r] * LD + c];
+                    if (lane == 0) w.b[tk.brow + r] = sc * bt[r], w.bd[tk.brow + r] = tk.priority == 0 ? 0.0 : 1.0;
+                }
+            } else if (tk.priority == 0) {
                 for (int r = 0; r < rows; r++) {
                     for (int c = lane; c < nv; c += 32) w.Cs[(tk.row_offset + r) * LD + c] = w.Jt[src[r] * LD + c];
                     if (lane == 0) w.b[tk.row_offset + r] = bt[r];
@@ -734,7 +747,7 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
                 if (tk.type == T_JOINT_TRACKING) {  // JointTrackingTask.cpp:151
                     const double bj = (compact ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - s[j]);
                     if (tk.priority == 1) {
-                        w.Hs[i * LD + i] += tk.weight[j];
+                        w.Hs[ROWS ? i : i * LD + i] += tk.weight[j];
                         w.g[i] -= tk.weight[j] * bj;
                     } else {
                         w.lo[i] = fmax(w.lo[i], bj), w.hi[i] = fmin(w.hi[i], bj);
