@@ -1267,6 +1267,10 @@ def test_random_task_mixes_vs_oracle(seed):
     for t, sp in enumerate(sps):
         if sp is not None:
             prob.set_setpoint(t, sp)
+    eq_path = prob.kernel_path == 3
+    if eq_path:   # the equality-only kernel never forms H: its answer first, then the generic kernel's matrices for the checks below
+        prob.tick(1, 0.01)
+        nu_eq, st_eq = prob.get_output(), prob.get_status()[0]
     prob.debug_enable(True)
     prob.tick(1, 0.01)
     nu = prob.get_output()
@@ -1274,6 +1278,9 @@ def test_random_task_mixes_vs_oracle(seed):
     g, Ce, be = prob.debug_get(capi.DEBUG_G), prob.debug_get(capi.DEBUG_CEQ), prob.debug_get(capi.DEBUG_BEQ)
     H = prob.debug_get(capi.DEBUG_H)
     me = prob.me
+    if eq_path:
+        assert np.array_equal(st_eq == 2, st == 2), "the two kernels disagree on which problems are infeasible"
+        nu, st = nu_eq, st_eq
     nur, str_, _ = o.tick_batch(p0.copy(), q0.copy(), s0.copy(), sps)
     if (str_ == 0).sum() < N // 2:
         # e.g. two hard orientation tasks on neighbouring links: the stacked rows lose rank and the random right-hand sides
@@ -1566,3 +1573,127 @@ def test_compact_packed_records_equal_full_ones(path):
         res.append((nu.copy(), st.copy()))
     assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]) and np.all(res[0][1] == 0)
     p2.close()
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_equality_only_kernel_on_wide_models(seed):
+    """blfik_tick_eq_kernel (kernel path 3): models with more than 32 velocity variables and no inequality rows -- BASELINE
+    configs[0] / [1] are of this class.  A random tree with 34 ... 44 joints, hard SE3 + masked hard CoM, weighted SO3 / R3 /
+    SE3 / Gravity / Distance rows with exogenous feedback on the CoM, joint regularisation: (a) nu against the oracle (exact
+    active-set referee when the oracle's polish was rejected) and against the generic kernel, (b) a duplicated hard row
+    with the same / a contradicting target, (c) twelve integrating ticks in lock step with the oracle, one launch of twelve
+    ticks, and the packed host tick with full and compact records."""
+    rng = np.random.default_rng(400 + seed)
+    n = [34, 38, 41, 44][seed]
+    m = M.random_tree(n, seed=70 + seed, extra_frames=6)
+    N, dt = 40, 0.01
+    while True:
+        frames = list(rng.choice(np.arange(1, len(m.frame_names)), size=5, replace=False))
+        if len({int(m.frame_link[int(f)]) for f in frames}) == 5:
+            break
+    fname = lambda i: m.frame_names[int(frames[i])]
+    tasks = [T.se3_task(m, "foot", fname(0), 4.0, 3.0, priority=0),
+             T.com_task(m, "com", 2.0, priority=0, mask=(True, True, False), use_exogenous_feedback=seed % 2 == 1),
+             T.so3_task(m, "chest", fname(1), 3.0, priority=1, weight=[2.0, 1.0, 4.0]),
+             T.r3_task(m, "hand", fname(2), 2.0, priority=1, weight=[5.0, 5.0, 5.0]),
+             T.se3_task(m, "hand2", fname(3), 2.0, 2.0, priority=1, weight=[1.0, 2.0, 3.0, 0.5, 0.5, 0.5]),
+             T.gravity_task(m, "up", fname(4), 2.0, weight=[1.0, 1.0]),
+             T.distance_task(m, "dist", fname(2), 1.5, priority=1, weight=[3.0], reference_frame_name=fname(4)),
+             T.joint_tracking_task(m, "reg", rng.uniform(1, 5, n), priority=1, weight=rng.uniform(0.5, 2, n))]
+    T.validate_tasks(m, tasks)
+    p0 = rng.uniform(-0.5, 0.5, (N, 3))
+    q0 = W.so3_exp(rng.uniform(-0.5, 0.5, (N, 3)))
+    s0 = rng.uniform(-0.5, 0.5, (N, n))
+    o = Oracle(m, tasks)
+    sps = []
+    for t in tasks:
+        sp = np.zeros((N, t.record_len(n)))
+        for i in range(N):
+            R, P = o.fk(p0[i], q0[i], s0[i])
+            if t.type in (T.TASK_SE3, T.TASK_R3, T.TASK_SO3):
+                Rf, pf = o.frame_pose(R, P, t.frame)
+                qd = W.rot_to_quat((W.quat_to_rot(W.so3_exp(rng.normal(0, 0.05, (1, 3)))) @ Rf)[0][None])[0]
+                sp[i] = {T.TASK_SE3: np.concatenate([pf + rng.normal(0, 0.02, 3), qd, np.zeros(6)]),
+                         T.TASK_R3: np.concatenate([pf + rng.normal(0, 0.02, 3), np.zeros(3)]),
+                         T.TASK_SO3: np.concatenate([qd, np.zeros(3)])}[t.type]
+            elif t.type == T.TASK_COM:
+                c = o.com(R, P)[0]
+                sp[i, :6] = np.concatenate([c + rng.normal(0, 0.02, 3), np.zeros(3)])
+                if t.exo_position:
+                    sp[i, 6:9] = c + rng.normal(0, 0.005, 3)       # the measured CoM
+            elif t.type == T.TASK_DISTANCE:
+                sp[i, 0] = rng.uniform(0.2, 0.8)
+            elif t.type == T.TASK_GRAVITY:
+                sp[i] = np.concatenate([[0.05, -0.05, 1.0], np.zeros(3)])
+            else:
+                sp[i] = np.concatenate([s0[i] + rng.normal(0, 0.05, n), np.zeros(n)])
+        sps.append(sp)
+
+    def fresh(task_list, records, path=0):
+        _, pr = make(m, task_list, N, path)
+        pr.set_state(p0, q0, s0)
+        for t, sp in enumerate(records):
+            pr.set_setpoint(t, np.ascontiguousarray(sp[:, :task_list[t].setpoint_len(n)]))
+            if task_list[t].feedback_len():
+                pr.set_feedback(t, np.ascontiguousarray(sp[:, task_list[t].setpoint_len(n):]))
+        return pr
+
+    # (a) one tick
+    prob, generic = fresh(tasks, sps), fresh(tasks, sps, 1)
+    assert prob.kernel_path == 3 and generic.kernel_path == 1
+    prob.tick(1, dt), generic.tick(1, dt)
+    nu, st = prob.get_output(), prob.get_status()[0]
+    assert np.all(st == 0) and np.all(generic.get_status()[0] == 0)
+    assert np.abs(nu - generic.get_output()).max() <= 1e-7
+    nur, str_, _ = o.tick_batch(p0.copy(), q0.copy(), s0.copy(), sps)
+    from helpers import solve_qp_active_set
+    for i in range(N):
+        ref = nur[i]
+        if str_[i] != 0 or np.abs(nu[i] - ref).max() > TOL_NU:
+            Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [sp[i] for sp in sps])
+            ref = solve_qp_active_set(Ho, go, Co, l, u)
+        assert np.abs(nu[i] - ref).max() <= TOL_NU, i
+    # (b) the foot's linear rows once more: the same target changes nothing, a different one leaves no feasible point
+    two = tasks[:1] + [T.r3_task(m, "foot_again", fname(0), 4.0, priority=0)] + tasks[1:]
+    same = np.hstack([sps[0][:, :3], sps[0][:, 7:10]])
+    dup = fresh(two, sps[:1] + [same] + sps[1:])
+    assert dup.kernel_path == 3
+    dup.tick(1, dt)
+    assert np.all(dup.get_status()[0] == 0) and np.abs(dup.get_output() - nu).max() < 1e-7
+    other = same.copy()
+    other[:, 1] += 0.01
+    dup.set_setpoint(1, other)
+    dup.tick(1, dt)
+    assert np.all(dup.get_status()[0] == 2)
+    dup.close(), generic.close()
+    # (c) closed loop
+    NT = 12
+    whole, packed = fresh(tasks, sps), fresh(tasks, sps)
+    p, q, s = p0.copy(), q0.copy(), s0.copy()
+    for k in range(NT):
+        pr_, qr_, sr_ = p.copy(), q.copy(), s.copy()
+        nur, str_, _ = o.tick_batch(pr_, qr_, sr_, sps, dt_integrate=dt)
+        prob.tick(1, dt, integrate=True, warm_start=k % 2 == 1)          # the warm start changes the path, not the answer
+        nu = prob.get_output()
+        p, q, s = prob.get_state()
+        ok = (prob.get_status()[0] == 0) & (str_ == 0)
+        assert ok.mean() > 0.9 and np.abs(nu - nur)[ok].max() <= TOL_NU
+        assert np.abs(s - sr_)[ok].max() <= 1e-7 and np.abs(np.linalg.norm(q, axis=1) - 1).max() < 1e-12
+    whole.tick(NT, dt, integrate=True)
+    pw, qw, sw = whole.get_state()
+    assert np.abs(sw - s).max() < 1e-8 and np.abs(pw - p).max() < 1e-8
+    inp = W.Inputs(p0, q0, s0, sps) if hasattr(W, "Inputs") else None
+    if inp is not None:
+        res = []
+        for compact in (False, True):
+            packed.set_state(p0, q0, s0)
+            rec = packed.pack_inputs(inp, compact=compact)
+            out, sto = np.empty((N, n + 6)), np.empty(N, dtype=np.int32)
+            packed.tick_packed(rec, out, sto, dt=dt, integrate=True, nchunks=2, compact=compact)
+            res.append((out.copy(), sto.copy(), packed.get_state()[2].copy()))
+        assert np.array_equal(res[0][0], res[1][0]) and np.all(res[0][1] == 0) and np.array_equal(res[0][2], res[1][2])
+        one = fresh(tasks, sps)
+        one.tick(1, dt, integrate=True)
+        assert np.abs(res[0][0] - one.get_output()).max() < 1e-12
+        one.close()
+    prob.close(), whole.close(), packed.close()
