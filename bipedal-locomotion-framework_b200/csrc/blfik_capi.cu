@@ -588,10 +588,12 @@ static int dev_alloc(blfik_problem* p, size_t count, T** out, bool zero = true)
     return BLFIK_OK;
 }
 
-// Row layout of the equality-only kernel (blfik_eq.cuh): B (K x LD) in Cs, G / its Cholesky factor in Ss, its inverse in Ym,
-// the diagonal cost in Hs (a vector here), no nv x nv matrix at all.  A keeps six rows: DistanceTask builds the Jacobian of
-// its reference frame there.
-static Layout make_layout_eq(int n, int me, int K)
+// Row layout of the equality-only kernel (blfik_eq.cuh): B (K x LD) in Cs, the diagonal cost in Hs (a vector here), no
+// nv x nv matrix at all.  What only K1 / K2 touch (link poses, the task Jacobian scratch Jt, the unused box, and A, where a
+// DistanceTask with a reference frame builds that frame's Jacobian) shares its words with what only K3 touches (G and its
+// Cholesky factor in Ss, the inverse factor in Ym, the iteration vectors): the two phases never overlap, and the smaller
+// footprint is what decides how many robots an SM holds.
+static Layout make_layout_eq(int n, int me, int K, bool needs_A)
 {
     Layout L;
     const int nv = n + 6, nl = n + 1;
@@ -600,13 +602,21 @@ static Layout make_layout_eq(int n, int me, int K)
     L.LDE = (K & 1) ? K : K + 1;
     int o = 0;
     auto take = [&](int cnt) { int r = o; o += (cnt + 1) & ~1; return r; };
+    // both phases
+    L.Cs = take(K * L.LD), L.Hs = take(nv), L.g = take(nv), L.b = take(K), L.bd = take(K);
+    const int shared0 = o;
+    // K1 / K2 only
     L.linkR = take(9 * nl), L.linkP = take(3 * nl), L.axisW = take(3 * nl), L.mcw = take(3 * nl);
-    L.Hs = take(nv), L.A = take(6 * L.LD), L.B = 0;
-    L.Cs = take(K * L.LD), L.Ym = take(K * L.LDE), L.Wm = 0, L.Ss = take(K * L.LDE), L.Jt = take(6 * L.LD);
-    L.g = take(nv), L.b = take(K), L.lo = take(nv), L.hi = take(nv), L.x = take(nv), L.z = 0, L.y = 0;
-    L.r = take(nv), L.xb = 0, L.wb = take(K), L.lam = take(K), L.gp = take(nv), L.bp = take(K), L.bd = take(K), L.t = 0;
-    L.act = 0;
-    L.total = o;
+    L.Jt = take(6 * L.LD), L.lo = take(nv), L.hi = take(nv);
+    L.A = needs_A ? take(6 * L.LD) : L.Jt;
+    const int end12 = o;
+    // K3 only, over the same words
+    o = shared0;
+    L.Ss = take(K * L.LDE), L.Ym = take(K * L.LDE);
+    L.x = take(nv), L.r = take(nv), L.gp = take(nv), L.wb = take(K), L.lam = take(K), L.bp = take(K);
+    const int end3 = o;
+    L.B = L.Wm = L.z = L.y = L.xb = L.t = L.act = 0;
+    L.total = end12 > end3 ? end12 : end3;
     return L;
 }
 
@@ -849,11 +859,15 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         for (const HostTask& h : p->tasks)
             box |= is_inequality(h.d.type) || (h.d.type == BLFIK_TASK_JOINT_TRACKING && h.d.priority == 0);
         if (!box) {
-            p->Leq = make_layout_eq(n, me, p->K);
+            bool needs_A = false;
+            for (const HostTask& h : p->tasks) needs_A |= h.d.type == BLFIK_TASK_DISTANCE && h.d.ref_frame >= 0;
+            p->Leq = make_layout_eq(n, me, p->K, needs_A);
             const size_t eper = (size_t)p->Leq.total * sizeof(double);
             int ew = (int)((sm_total - 2048) / (eper + 64));
-            if (ew > 16) ew = 16;                      // register file: 256 threads per block at <= 128 registers
-            int ewpb = ew >= 8 ? 8 : (ew >= 4 ? 4 : (ew >= 2 ? 2 : 1));
+            if (ew > 16) ew = 16;                      // register file: two blocks of 256 threads at <= 128 registers
+            int ewpb = 1;                              // block size (<= 8 warps) that leaves the fewest warps of the SM unused
+            for (int c = 1; c <= 8; c++)
+                if ((ew / c) * c >= (ew / ewpb) * ewpb) ewpb = c;
             if (ew >= 1 && (size_t)ewpb * eper <= (size_t)smem_optin &&
                 cudaFuncSetAttribute(blfik_tick_eq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) == cudaSuccess) {
                 p->eq_kernel = true;

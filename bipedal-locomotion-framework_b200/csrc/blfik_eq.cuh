@@ -24,13 +24,10 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     const int nv = L.nv, K = L.K, LD = L.LD, LDE = L.LDE;
     const double sigma = P.st.sigma;
     QpResult res = {0, 0};
-    double gnorm = 0.0;
     for (int i = lane; i < nv; i += 32) {
         w.gp[i] = 1.0 / (w.Hs[i] + sigma);
         w.x[i] = warm ? P.wx[(size_t)nv * robot + i] : 0.0;
-        gnorm = fmax(gnorm, fabs(w.g[i]));
     }
-    gnorm = warp_max(gnorm);
     __syncwarp();
     // G, lower triangle, one entry per lane and pass
     const int ntri = K * (K + 1) / 2;
@@ -114,13 +111,12 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     }
     bad = __any_sync(kFull, bad);
     res.status = (!ok || bad) ? 2 : (converged ? 0 : 1);
-    (void)gnorm;
     return res;
 }
 
 // Same contract as blfik_tick_kernel (K1 -> K2 -> K3 -> K4, `nticks` times per launch); P.L is the row layout built by
 // make_layout_eq on the host.
-__global__ void __launch_bounds__(256) blfik_tick_eq_kernel(const TickParams P)
+__global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams P)
 {
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;

@@ -10,7 +10,8 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "bipedal-locomotion-framework_b200", "libblfik_cuda.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEEP = sys.argv[1:] or ["fast_kernelILi29ELi18", "blfik_tick_kernel", "blfik_kinematics_kernel", "blfik_integrate_kernel"]
+KEEP = sys.argv[1:] or ["fast_kernelILi29ELi18", "blfik_tick_kernel", "blfik_tick_eq_kernel", "blfik_kinematics_kernel", "blfik_integrate_kernel",
+                       "blfik_spline_coefficients_kernel", "blfik_cubic_spline_coefficients_kernel"]
 
 
 def main():
