@@ -7,10 +7,11 @@
 //     min 1/2 x'(D0 + Bc'Bc) x + (g0 - Bc'bc)'x   s.t.  Be x = be
 // D0 the diagonal cost (joint regularisation), Bc the dense cost rows scaled by sqrt(weight), Be the equality rows.  It is
 // never formed as H: with B = [Be; Bc] stacked in task order (K rows), E = diag(0 on equality rows, 1 on cost rows) and the
-// proximal term sigma/2 |x - x_k|^2 that makes D = D0 + sigma invertible (D0 is zero on the base columns), one step is
-//     G z = B D^-1 q - [be; bc],   G = E + B D^-1 B'  (K x K, SPD),   x_{k+1} = D^-1 (q - B'z),   q = sigma x_k - g0
+// proximal term 1/2 (x - x_k)' R (x - x_k), R = max(D0, sigma) - D0 (sigma on the base columns, where D0 is zero, nothing on a
+// variable whose own cost already exceeds sigma), that makes D = D0 + R invertible, one step is
+//     G z = B D^-1 q - [be; bc],   G = E + B D^-1 B'  (K x K, SPD),   x_{k+1} = D^-1 (q - B'z),   q = R x_k - g0
 // (z = the multipliers of the equality rows and the residuals Bc x - bc of the cost rows).  G is factored once per tick and
-// inverted in place (K <= 64); the steps repeat until x stops moving -- sigma |x_{k+1} - x_k| is the stationarity residual of
+// inverted (K <= 64); the steps repeat until x stops moving -- R |x_{k+1} - x_k| is the stationarity residual of
 // the original problem, and Be x = be holds at every step.  Dependent equality rows are dropped by the factorisation as in
 // the generic kernel and the equality residual is checked at the end (status 2 if they contradict each other).
 #pragma once
@@ -24,8 +25,11 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     const int nv = L.nv, K = L.K, LD = L.LD, LDE = L.LDE;
     const double sigma = P.st.sigma;
     QpResult res = {0, 0};
+    // proximal weight per variable: only where the diagonal cost is missing (the base columns) or below sigma; w.Hs becomes it
     for (int i = lane; i < nv; i += 32) {
-        w.gp[i] = 1.0 / (w.Hs[i] + sigma);
+        const double d0 = w.Hs[i], d = fmax(d0, sigma);
+        w.gp[i] = 1.0 / d;
+        w.Hs[i] = d - d0;
         w.x[i] = warm ? P.wx[(size_t)nv * robot + i] : 0.0;
     }
     __syncwarp();
@@ -64,12 +68,12 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     bool converged = false;
     int it = 0;
     for (; it < max_steps && !converged; it++) {
-        for (int i = lane; i < nv; i += 32) w.r[i] = sigma * w.x[i] - w.g[i];
+        for (int i = lane; i < nv; i += 32) w.r[i] = w.gp[i] * (w.Hs[i] * w.x[i] - w.g[i]);   // D^-1 q
         __syncwarp();
         for (int k = lane; k < K; k += 32) {
             const double* bk = w.Cs + k * LD;
             double v = -w.b[k];
-            for (int i = 0; i < nv; i++) v += bk[i] * w.gp[i] * w.r[i];
+            for (int i = 0; i < nv; i++) v += bk[i] * w.r[i];
             w.wb[k] = v;
         }
         __syncwarp();
@@ -87,9 +91,9 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
         __syncwarp();
         double step = 0.0, xmax = 0.0;
         for (int i = lane; i < nv; i += 32) {
-            double v = w.r[i];
-            for (int k = 0; k < K; k++) v -= w.Cs[k * LD + i] * w.lam[k];
-            v *= w.gp[i];
+            double bz = 0.0;
+            for (int k = 0; k < K; k++) bz += w.Cs[k * LD + i] * w.lam[k];
+            const double v = w.r[i] - w.gp[i] * bz;
             step = fmax(step, fabs(v - w.x[i]));
             xmax = fmax(xmax, fabs(v));
             w.x[i] = v;
