@@ -613,9 +613,10 @@ static Layout make_layout_eq(int n, int me, int K, bool needs_A)
     // K3 only, over the same words
     o = shared0;
     L.Ss = take(K * L.LDE), L.Ym = take(K * L.LDE);
-    L.x = take(nv), L.r = take(nv), L.gp = take(nv), L.wb = take(K), L.lam = take(K), L.bp = take(K);
+    L.x = take(nv), L.r = take(nv), L.gp = take(nv), L.wb = take(K), L.lam = take(K), L.bp = take(K), L.t = take(K);
+    L.act = take((nv + 1) / 2 + 1);
     const int end3 = o;
-    L.B = L.Wm = L.z = L.y = L.xb = L.t = L.act = 0;
+    L.B = L.Wm = L.z = L.y = L.xb = 0;
     L.total = end12 > end3 ? end12 : end3;
     return L;
 }

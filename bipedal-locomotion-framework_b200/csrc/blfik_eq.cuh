@@ -16,6 +16,7 @@
 // the generic kernel and the equality residual is checked at the end (status 2 if they contradict each other).
 #pragma once
 #include "blfik_device.cuh"
+#include "blfik_fast.cuh"   // dmma884
 
 namespace blfik {
 
@@ -25,35 +26,84 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     const int nv = L.nv, K = L.K, LD = L.LD, LDE = L.LDE;
     const double sigma = P.st.sigma;
     QpResult res = {0, 0};
-    // proximal weight per variable: only where the diagonal cost is missing (the base columns) or below sigma; w.Hs becomes it
-    for (int i = lane; i < nv; i += 32) {
-        const double d0 = w.Hs[i], d = fmax(d0, sigma);
-        w.gp[i] = 1.0 / d;
-        w.Hs[i] = d - d0;
-        w.x[i] = warm ? P.wx[(size_t)nv * robot + i] : 0.0;
+    // Proximal weight per variable, R_i = max(D0_i, sigma) - D0_i: only where the diagonal cost is missing (the base columns) or
+    // below sigma.  D^-1 q = rho x_k + pc with rho = R / D (w.Hs from here on) and the constant pc = -D^-1 g0 (w.r), so a step
+    // moves nothing but the few variables F with rho > 0 (listed in w.act): the steps run on those and z, and the other
+    // variables are evaluated once at the end.
+    int nF = 0;
+    for (int base = 0; base < nv; base += 32) {
+        const int i = base + lane;
+        bool f = false;
+        if (i < nv) {
+            const double d0 = w.Hs[i], d = fmax(d0, sigma), dinv = 1.0 / d;
+            w.gp[i] = dinv;
+            w.Hs[i] = (d - d0) * dinv;
+            w.r[i] = -dinv * w.g[i];
+            w.x[i] = warm ? P.wx[(size_t)nv * robot + i] : 0.0;
+            f = d > d0;
+        }
+        const unsigned m = __ballot_sync(kFull, f);
+        if (f) w.act[nF + __popc(m & ((1u << lane) - 1u))] = i;
+        nF += __popc(m);
     }
     __syncwarp();
-    // G, lower triangle, one entry per lane and pass
-    const int ntri = K * (K + 1) / 2;
+    // G = E + (B D^-1) B' as 8 x 8 tiles on the FP64 tensor path (DMMA m8n8k4, as in the register-resident kernel), tiles on
+    // and below the diagonal only: one instruction per 256 multiply-adds where the lane-per-entry loop spent 1,500 per robot
     double gmax = 0.0;
-    for (int p = lane; p < ntri; p += 32) {
-        int k = (int)((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
-        while (k * (k + 1) / 2 > p) k--;
-        while ((k + 1) * (k + 2) / 2 <= p) k++;
-        const int l = p - k * (k + 1) / 2;
-        const double* bk = w.Cs + k * LD;
-        const double* bl = w.Cs + l * LD;
-        double v = 0.0;
-        for (int i = 0; i < nv; i++) v += bk[i] * bl[i] * w.gp[i];
-        if (k == l) {
-            v += w.bd[k];
-            gmax = fmax(gmax, v);
+    {
+        const int gr = lane >> 2, tc = lane & 3;
+        const int RT = (K + 7) >> 3, KS = (nv + 3) >> 2;
+        for (int ti = 0; ti < RT; ti++) {
+            const int row = 8 * ti + gr;
+            const double* ba = w.Cs + (row < K ? row : 0) * LD;
+            for (int tj = 0; tj <= ti; tj++) {
+                const int rowb = 8 * tj + gr;
+                const double* bb = w.Cs + (rowb < K ? rowb : 0) * LD;
+                double c0 = 0.0, c1 = 0.0;
+                for (int s = 0; s < KS; s++) {
+                    const int col = 4 * s + tc;
+                    const bool in = col < nv;
+                    const double a = (in && row < K) ? ba[col] * w.gp[col] : 0.0;
+                    const double b = (in && rowb < K) ? bb[col] : 0.0;
+                    dmma884(c0, c1, a, b);
+                }
+                const int col = 8 * tj + 2 * tc;
+                if (row < K) {
+                    if (col < K) {
+                        if (row == col) c0 += w.bd[row], gmax = fmax(gmax, c0);
+                        w.Ss[row * LDE + col] = c0;
+                    }
+                    if (col + 1 < K) {
+                        if (row == col + 1) c1 += w.bd[row], gmax = fmax(gmax, c1);
+                        w.Ss[row * LDE + col + 1] = c1;
+                    }
+                }
+            }
         }
-        w.Ss[k * LDE + l] = v;
     }
     gmax = warp_max(gmax);
     __syncwarp();
-    bool ok = chol_inplace(w.Ss, K, LDE, 1e-11 * gmax + 1e-300, lane, true);
+    // G = L L', right-looking, row i by lane; a pivot below the floor marks a row that depends on the previous ones: it is
+    // left out (zero column, zero diagonal) exactly as chol_inplace(..., drop = true) does
+    bool ok = true;
+    {
+        const double floor_ = 1e-11 * gmax + 1e-300;
+        for (int k = 0; k < K; k++) {
+            const double piv = w.Ss[k * LDE + k];
+            const bool dropped = !(piv > floor_);
+            if (dropped && !(piv == piv)) ok = false;
+            const double d = dropped ? 0.0 : sqrt(piv), inv = dropped ? 0.0 : 1.0 / d;
+            __syncwarp();
+            for (int i = k + 1 + lane; i < K; i += 32) w.Ss[i * LDE + k] *= inv;
+            if (lane == 0) w.Ss[k * LDE + k] = d;
+            __syncwarp();
+            for (int i = k + 1 + lane; i < K; i += 32) {
+                const double lik = w.Ss[i * LDE + k];
+                for (int j = k + 1; j <= i; j++) w.Ss[i * LDE + j] -= lik * w.Ss[j * LDE + k];
+            }
+            __syncwarp();
+        }
+    }
     // Linv = L^-1 (lower), column c by lane; a dropped row (zero diagonal) leaves its row and column zero
     for (int c = lane; c < K; c += 32) {
         for (int i = 0; i < K; i++) {
@@ -64,45 +114,59 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
         }
     }
     __syncwarp();
+    for (int k = lane; k < K; k += 32) {   // constant part of the right-hand side: B pc - [be; bc]
+        const double* bk = w.Cs + k * LD;
+        double v = -w.b[k];
+        for (int c = 0; c < nv; c++) v += bk[c] * w.r[c];
+        w.wb[k] = v;
+    }
+    __syncwarp();
     const int max_steps = 60;
     bool converged = false;
     int it = 0;
     for (; it < max_steps && !converged; it++) {
-        for (int i = lane; i < nv; i += 32) w.r[i] = w.gp[i] * (w.Hs[i] * w.x[i] - w.g[i]);   // D^-1 q
-        __syncwarp();
         for (int k = lane; k < K; k += 32) {
             const double* bk = w.Cs + k * LD;
-            double v = -w.b[k];
-            for (int i = 0; i < nv; i++) v += bk[i] * w.r[i];
-            w.wb[k] = v;
-        }
-        __syncwarp();
-        for (int k = lane; k < K; k += 32) {
-            double v = 0.0;
-            for (int j = 0; j <= k; j++) v += w.Ym[k * LDE + j] * w.wb[j];
+            double v = w.wb[k];
+            for (int f = 0; f < nF; f++) {
+                const int c = w.act[f];
+                v += bk[c] * w.Hs[c] * w.x[c];
+            }
             w.bp[k] = v;
         }
         __syncwarp();
         for (int k = lane; k < K; k += 32) {
             double v = 0.0;
-            for (int j = k; j < K; j++) v += w.Ym[j * LDE + k] * w.bp[j];
+            for (int j = 0; j <= k; j++) v += w.Ym[k * LDE + j] * w.bp[j];
+            w.t[k] = v;
+        }
+        __syncwarp();
+        for (int k = lane; k < K; k += 32) {
+            double v = 0.0;
+            for (int j = k; j < K; j++) v += w.Ym[j * LDE + k] * w.t[j];
             w.lam[k] = v;
         }
         __syncwarp();
-        double step = 0.0, xmax = 0.0;
-        for (int i = lane; i < nv; i += 32) {
+        bool settled = true, finite = true;
+        for (int f = lane; f < nF; f += 32) {
+            const int c = w.act[f];
             double bz = 0.0;
-            for (int k = 0; k < K; k++) bz += w.Cs[k * LD + i] * w.lam[k];
-            const double v = w.r[i] - w.gp[i] * bz;
-            step = fmax(step, fabs(v - w.x[i]));
-            xmax = fmax(xmax, fabs(v));
-            w.x[i] = v;
+            for (int k = 0; k < K; k++) bz += w.Cs[k * LD + c] * w.lam[k];
+            const double v = w.Hs[c] * w.x[c] + w.r[c] - w.gp[c] * bz;
+            settled = settled && (fabs(v - w.x[c]) <= 1e-10 * (1.0 + fabs(v)));
+            finite = finite && (v == v);
+            w.x[c] = v;
         }
-        step = warp_max(step), xmax = warp_max(xmax);
-        __syncwarp();
-        if (!(step == step)) break;   // NaN
-        converged = step <= 1e-10 * (1.0 + xmax);
+        converged = __all_sync(kFull, settled);
+        if (!__all_sync(kFull, finite)) break;
     }
+    // every variable from the last z (one more step for those of F)
+    for (int c = lane; c < nv; c += 32) {
+        double bz = 0.0;
+        for (int k = 0; k < K; k++) bz += w.Cs[k * LD + c] * w.lam[k];
+        w.x[c] = w.Hs[c] * w.x[c] + w.r[c] - w.gp[c] * bz;
+    }
+    __syncwarp();
     res.iters = it;
     // equality residual: exact at every step unless rows were dropped as dependent and contradict the kept ones
     bool bad = false;
