@@ -1686,12 +1686,14 @@ def test_equality_only_kernel_on_wide_models(seed):
     if inp is not None:
         res = []
         for compact in (False, True):
-            packed.set_state(p0, q0, s0)
-            rec = packed.pack_inputs(inp, compact=compact)
-            out, sto = np.empty((N, n + 6)), np.empty(N, dtype=np.int32)
-            packed.tick_packed(rec, out, sto, dt=dt, integrate=True, nchunks=2, compact=compact)
-            res.append((out.copy(), sto.copy(), packed.get_state()[2].copy()))
-        assert np.array_equal(res[0][0], res[1][0]) and np.all(res[0][1] == 0) and np.array_equal(res[0][2], res[1][2])
+            for nchunks in (2, 0, 5):          # staged copies, zero-copy, the streaming default (chunk launches for this kernel)
+                packed.set_state(p0, q0, s0)
+                rec = packed.pack_inputs(inp, compact=compact)
+                out, sto = np.empty((N, n + 6)), np.empty(N, dtype=np.int32)
+                packed.tick_packed(rec, out, sto, dt=dt, integrate=True, nchunks=nchunks, compact=compact)
+                res.append((out.copy(), sto.copy(), packed.get_state()[2].copy()))
+        for r in res[1:]:
+            assert np.array_equal(res[0][0], r[0]) and np.all(r[1] == 0) and np.array_equal(res[0][2], r[2])
         one = fresh(tasks, sps)
         one.tick(1, dt, integrate=True)
         assert np.abs(res[0][0] - one.get_output()).max() < 1e-12
