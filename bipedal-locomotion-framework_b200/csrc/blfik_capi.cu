@@ -593,21 +593,23 @@ static int dev_alloc(blfik_problem* p, size_t count, T** out, bool zero = true)
 // DistanceTask with a reference frame builds that frame's Jacobian) shares its words with what only K3 touches (G and its
 // Cholesky factor in Ss, the inverse factor in Ym, the iteration vectors): the two phases never overlap, and the smaller
 // footprint is what decides how many robots an SM holds.
-static Layout make_layout_eq(int n, int me, int K, bool needs_A)
+static Layout make_layout_eq(int n, int me, int K, bool needs_A, bool box)
 {
     Layout L;
     const int nv = n + 6, nl = n + 1;
-    L.nv = nv, L.me = me, L.K = K;
+    L.nv = nv, L.me = me, L.K = K, L.box = box ? 1 : 0;
     L.LD = (nv & 1) ? nv : nv + 1;
     L.LDE = (K & 1) ? K : K + 1;
     int o = 0;
     auto take = [&](int cnt) { int r = o; o += (cnt + 1) & ~1; return r; };
     // both phases
     L.Cs = take(K * L.LD), L.Hs = take(nv), L.g = take(nv), L.b = take(K), L.bd = take(K);
+    if (box) L.lo = take(nv), L.hi = take(nv);
     const int shared0 = o;
     // K1 / K2 only
     L.linkR = take(9 * nl), L.linkP = take(3 * nl), L.axisW = take(3 * nl), L.mcw = take(3 * nl);
-    L.Jt = take(6 * L.LD), L.lo = take(nv), L.hi = take(nv);
+    L.Jt = take(6 * L.LD);
+    if (!box) L.lo = take(nv), L.hi = take(nv);
     L.A = needs_A ? take(6 * L.LD) : L.Jt;
     const int end12 = o;
     // K3 only, over the same words
@@ -615,8 +617,9 @@ static Layout make_layout_eq(int n, int me, int K, bool needs_A)
     L.Ss = take(K * L.LDE), L.Ym = take(K * L.LDE);
     L.x = take(nv), L.r = take(nv), L.gp = take(nv), L.wb = take(K), L.lam = take(K), L.bp = take(K), L.t = take(K);
     L.act = take((nv + 1) / 2 + 1);
+    L.z = take(nv), L.y = take(nv), L.xb = take(nv);   // rho, the active-set codes, the codes proposed by the pivoting rule
     const int end3 = o;
-    L.B = L.Wm = L.z = L.y = L.xb = 0;
+    L.B = L.Wm = 0;
     L.total = end12 > end3 ? end12 : end3;
     return L;
 }
@@ -625,7 +628,7 @@ static Layout make_layout(int n, int me)
 {
     Layout L;
     const int nv = n + 6, nl = n + 1;
-    L.nv = nv, L.me = me, L.K = 0;
+    L.nv = nv, L.me = me, L.K = 0, L.box = 0;
     L.LD = (nv & 1) ? nv : nv + 1;
     L.LDE = (me & 1) ? me : me + 1;
     int o = 0;
@@ -854,15 +857,16 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         }
     }
 
-    // ---- equality-only kernel: no box (inequality tasks, priority-0 joint tracking), at most 64 dense rows
+    // ---- factored-form kernel for what the register-resident one cannot hold: at most 64 dense rows
     if (!p->fast_kernel && p->K >= 1 && p->K <= 64) {
         bool box = false;
         for (const HostTask& h : p->tasks)
             box |= is_inequality(h.d.type) || (h.d.type == BLFIK_TASK_JOINT_TRACKING && h.d.priority == 0);
-        if (!box) {
+        static const int box_env = [] { const char* e = getenv("BLFIK_EQ_BOX"); return e ? atoi(e) : 1; }();
+        if (!box || box_env) {
             bool needs_A = false;
             for (const HostTask& h : p->tasks) needs_A |= h.d.type == BLFIK_TASK_DISTANCE && h.d.ref_frame >= 0;
-            p->Leq = make_layout_eq(n, me, p->K, needs_A);
+            p->Leq = make_layout_eq(n, me, p->K, needs_A, box);
             const size_t eper = (size_t)p->Leq.total * sizeof(double);
             int ew = (int)((sm_total - 2048) / (eper + 64));
             if (ew > 16) ew = 16;                      // register file: two blocks of 256 threads at <= 128 registers

@@ -87,6 +87,7 @@ struct Settings {
 struct Layout {
     int nv, me, LD, LDE;
     int K;                                 // dense task rows, equality + cost (row layout of the equality-only kernel)
+    int box;                               // that kernel: 1 if a task bounds the joint velocities (lo / hi live through K3)
     int linkR, linkP, axisW, mcw;          // kinematics
     int Hs, A, B, Cs, Ym, Wm, Ss, Jt;      // matrices
     int g, b, lo, hi, x, z, y, r, xb, wb, lam, gp, bp, bd, t;  // vectors

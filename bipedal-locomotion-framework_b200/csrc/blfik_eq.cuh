@@ -20,27 +20,34 @@
 
 namespace blfik {
 
-__device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w, bool warm, long long robot, int lane)
+// One solve with the variables marked in w.y (0 free; +1 / -1 / 2: fixed at the upper / lower bound / at lo = hi) held at
+// their bounds: they leave D^-1 (w.gp = 0), keep their value through w.r, and enter the right-hand side of the rows like any
+// other known term.  Leaves x in w.x and z in w.lam; false if a pivot was not finite.
+__device__ __forceinline__ bool eq_solve_fixed(const TickParams& P, const WM& w, int lane, int& steps, bool& converged)
 {
     const Layout& L = P.L;
     const int nv = L.nv, K = L.K, LD = L.LD, LDE = L.LDE;
     const double sigma = P.st.sigma;
-    QpResult res = {0, 0};
-    // Proximal weight per variable, R_i = max(D0_i, sigma) - D0_i: only where the diagonal cost is missing (the base columns) or
-    // below sigma.  D^-1 q = rho x_k + pc with rho = R / D (w.Hs from here on) and the constant pc = -D^-1 g0 (w.r), so a step
-    // moves nothing but the few variables F with rho > 0 (listed in w.act): the steps run on those and z, and the other
-    // variables are evaluated once at the end.
+    // Proximal weight per free variable, R_i = max(D0_i, sigma) - D0_i: only where the diagonal cost is missing (the base columns)
+    // or below sigma.  D^-1 q = rho x_k + pc with rho = R / D (w.z) and the constant pc = -D^-1 g0 (w.r), so a step moves nothing
+    // but the few variables F with rho > 0 (listed in w.act): the steps run on those and z, and the other variables are
+    // evaluated once at the end.
     int nF = 0;
     for (int base = 0; base < nv; base += 32) {
         const int i = base + lane;
         bool f = false;
         if (i < nv) {
-            const double d0 = w.Hs[i], d = fmax(d0, sigma), dinv = 1.0 / d;
-            w.gp[i] = dinv;
-            w.Hs[i] = (d - d0) * dinv;
-            w.r[i] = -dinv * w.g[i];
-            w.x[i] = warm ? P.wx[(size_t)nv * robot + i] : 0.0;
-            f = d > d0;
+            const double code = L.box ? w.y[i] : 0.0;
+            if (code != 0.0) {
+                const double v = code > 0.0 && code < 2.0 ? w.hi[i] : w.lo[i];
+                w.gp[i] = 0.0, w.z[i] = 0.0, w.r[i] = v, w.x[i] = v;
+            } else {
+                const double d0 = w.Hs[i], d = fmax(d0, sigma), dinv = 1.0 / d;
+                w.gp[i] = dinv;
+                w.z[i] = (d - d0) * dinv;
+                w.r[i] = -dinv * w.g[i];
+                f = d > d0;
+            }
         }
         const unsigned m = __ballot_sync(kFull, f);
         if (f) w.act[nF + __popc(m & ((1u << lane) - 1u))] = i;
@@ -122,7 +129,7 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     }
     __syncwarp();
     const int max_steps = 60;
-    bool converged = false;
+    converged = false;
     int it = 0;
     for (; it < max_steps && !converged; it++) {
         for (int k = lane; k < K; k += 32) {
@@ -130,7 +137,7 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
             double v = w.wb[k];
             for (int f = 0; f < nF; f++) {
                 const int c = w.act[f];
-                v += bk[c] * w.Hs[c] * w.x[c];
+                v += bk[c] * w.z[c] * w.x[c];
             }
             w.bp[k] = v;
         }
@@ -152,7 +159,7 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
             const int c = w.act[f];
             double bz = 0.0;
             for (int k = 0; k < K; k++) bz += w.Cs[k * LD + c] * w.lam[k];
-            const double v = w.Hs[c] * w.x[c] + w.r[c] - w.gp[c] * bz;
+            const double v = w.z[c] * w.x[c] + w.r[c] - w.gp[c] * bz;
             settled = settled && (fabs(v - w.x[c]) <= 1e-10 * (1.0 + fabs(v)));
             finite = finite && (v == v);
             w.x[c] = v;
@@ -164,10 +171,99 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     for (int c = lane; c < nv; c += 32) {
         double bz = 0.0;
         for (int k = 0; k < K; k++) bz += w.Cs[k * LD + c] * w.lam[k];
-        w.x[c] = w.Hs[c] * w.x[c] + w.r[c] - w.gp[c] * bz;
+        w.x[c] = w.z[c] * w.x[c] + w.r[c] - w.gp[c] * bz;
     }
     __syncwarp();
-    res.iters = it;
+    steps += it;
+    return ok;
+}
+
+// The QP of one tick.  Without a box (L.box == 0) it is the single solve above.  With one (JointLimitsTask,
+// JointVelocityLimitsTask, a priority-0 JointTrackingTask) the active set is found by block principal pivoting: every solve is
+// followed by the test of the complementarity conditions -- a free joint outside its bounds is fixed there, a fixed joint whose
+// multiplier has the wrong sign is released -- all at once while the number of violations keeps falling (the primal-dual
+// active-set step of the register-resident kernel), one joint at a time, lowest index first, when it stalls (Murty's least-index
+// rule, the safeguard of Judice and Pires that makes the pivoting finite on a strictly convex problem).  No violation left is
+// the KKT certificate: primal feasible, dual feasible, stationary to the tolerance of the steps.
+__device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w, bool warm, long long robot, int lane)
+{
+    const Layout& L = P.L;
+    const int nv = L.nv, K = L.K, LD = L.LD, n = nv - 6;
+    QpResult res = {0, 0};
+    bool infeasible_box = false;
+    double gs = 0.0;
+    for (int i = lane; i < nv; i += 32) {
+        w.x[i] = warm ? P.wx[(size_t)nv * robot + i] : 0.0;
+        gs = fmax(gs, fabs(w.g[i]));
+        if (L.box) {
+            double code = 0.0;
+            if (i >= 6) {
+                if (w.lo[i] > w.hi[i]) infeasible_box = true;
+                if (w.lo[i] >= w.hi[i]) code = 2.0;
+                else if (warm) {
+                    const double c = P.wy[(size_t)n * robot + i - 6];
+                    code = (c == 1.0 && w.hi[i] < kInfHalf) ? 1.0 : ((c == -1.0 && w.lo[i] > -kInfHalf) ? -1.0 : 0.0);
+                }
+            }
+            w.y[i] = code;
+        }
+    }
+    gs = warp_max(gs);
+    if (__any_sync(kFull, infeasible_box)) {
+        res.status = 2;
+        return res;
+    }
+    __syncwarp();
+    bool ok = true, converged = false, certified = false;
+    const int max_pivots = L.box ? 12 + 2 * n : 1;
+    int best = 1 << 30, stall = 0;
+    for (int piv = 0; piv < max_pivots; piv++) {
+        ok = eq_solve_fixed(P, w, lane, res.iters, converged) && ok;
+        if (!L.box) {
+            certified = true;
+            break;
+        }
+        if (!converged) break;
+        // complementarity: new code per joint
+        int ninf = 0, first = nv;
+        for (int base = 0; base < nv; base += 32) {
+            const int i = base + lane;
+            bool flip = false;
+            double ncode = 0.0;
+            if (i >= 6 && i < nv) {
+                const double code = w.y[i];
+                ncode = code;
+                if (code == 0.0) {
+                    const double v = w.x[i];
+                    if (v > w.hi[i] + 1e-9 * (1.0 + fabs(w.hi[i]))) ncode = 1.0;
+                    else if (v < w.lo[i] - 1e-9 * (1.0 + fabs(w.lo[i]))) ncode = -1.0;
+                } else if (code != 2.0) {
+                    double rg = w.Hs[i] * w.x[i] + w.g[i];     // gradient of the Lagrangian without the bound's own multiplier
+                    for (int k = 0; k < K; k++) rg += w.Cs[k * LD + i] * w.lam[k];
+                    const double tol = 1e-9 * (1.0 + gs);
+                    if ((code > 0.0 && rg > tol) || (code < 0.0 && rg < -tol)) ncode = 0.0;
+                }
+                flip = ncode != code;
+            }
+            const unsigned m = __ballot_sync(kFull, flip);
+            if (m && first == nv) first = base + __ffs(m) - 1;
+            ninf += __popc(m);
+            if (i < nv) w.xb[i] = ncode;   // parked until the rule below decides which flips happen
+        }
+        __syncwarp();
+        if (ninf == 0) {
+            certified = true;
+            break;
+        }
+        if (ninf < best) best = ninf, stall = 0;
+        else stall++;
+        if (stall <= 2) {
+            for (int i = lane; i < nv; i += 32) w.y[i] = w.xb[i];
+        } else if (lane == 0) {
+            w.y[first] = w.xb[first];
+        }
+        __syncwarp();
+    }
     // equality residual: exact at every step unless rows were dropped as dependent and contradict the kept ones
     bool bad = false;
     for (int k = lane; k < K; k += 32) {
@@ -178,7 +274,7 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
         if (!(fabs(v) <= 1e-6 * (1.0 + fabs(w.b[k])))) bad = true;
     }
     bad = __any_sync(kFull, bad);
-    res.status = (!ok || bad) ? 2 : (converged ? 0 : 1);
+    res.status = (!ok || bad) ? 2 : ((certified && converged) ? 0 : 1);
     return res;
 }
 
@@ -211,9 +307,9 @@ __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams 
             __syncwarp();
             if (P.flags & BLFIK_TICK_INTEGRATE) k4_integrate(n, bp, bq, s, w.x, P.dt, lane);
         }
-        for (int i = lane; i < n; i += 32) {   // the inequality part of the warm start does not exist here
+        for (int i = lane; i < n; i += 32) {   // warm start of the next launch: the active set (wy), the joint part of x (wz)
             P.wz[(size_t)n * robot + i] = w.x[6 + i];
-            P.wy[(size_t)n * robot + i] = 0.0;
+            P.wy[(size_t)n * robot + i] = P.L.box ? w.y[6 + i] : 0.0;
         }
         if (lane == 0) {
             P.status[robot] = res.status;
