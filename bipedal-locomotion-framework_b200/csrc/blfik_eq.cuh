@@ -215,7 +215,7 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     }
     __syncwarp();
     bool ok = true, converged = false, certified = false;
-    const int max_pivots = L.box ? 12 + 2 * n : 1;
+    const int max_pivots = L.box ? 32 : 1;   // a feasible problem needs a handful; the bound is what an infeasible one costs
     int best = 1 << 30, stall = 0;
     for (int piv = 0; piv < max_pivots; piv++) {
         ok = eq_solve_fixed(P, w, lane, res.iters, converged) && ok;

@@ -6,7 +6,7 @@ import blf_b200
 from blf_b200 import capi, tasks as T, workloads as W
 from oracle.oracle import Oracle
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
-vmax = float(sys.argv[2]) if len(sys.argv) > 2 else 0.5
+vmax = float(sys.argv[2]) if len(sys.argv) > 2 else 3.0
 w = W.config(2)
 m, n = w.model, w.model.n
 tasks = list(w.tasks) + [T.joint_velocity_limits_task(m, "vlim", np.full(n, vmax), np.full(n, -vmax)),
