@@ -1,9 +1,9 @@
-// blfik_eq.cuh -- the tick for problems WITHOUT inequality rows (no JointLimitsTask / JointVelocityLimitsTask, no priority-0
-// JointTrackingTask) on models too wide for the register-resident kernel: 32 < nv <= 64 or more than 32 dense rows.
+// blfik_eq.cuh -- the tick for models too wide for the register-resident kernel: 32 < nv <= 64 or more than 32 dense rows.
 // BASELINE.json configs[0] and [1] are of this class (iCubGazeboV2_5 with 32 joints: SE3 feet + CoM as constraints, joint
-// regularisation as cost).  One warp per robot, everything in that warp's shared memory.
+// regularisation as cost).  One warp per robot, everything in that warp's shared memory, the QP in factored form.
 //
-// With no inequality the QP of QPInverseKinematics::advance (QPInverseKinematics.cpp:442-546) is one linear solve:
+// Without inequality rows (no JointLimitsTask / JointVelocityLimitsTask, no priority-0 JointTrackingTask) the QP of
+// QPInverseKinematics::advance (QPInverseKinematics.cpp:442-546) is one linear solve (eq_solve_fixed with nothing fixed):
 //     min 1/2 x'(D0 + Bc'Bc) x + (g0 - Bc'bc)'x   s.t.  Be x = be
 // D0 the diagonal cost (joint regularisation), Bc the dense cost rows scaled by sqrt(weight), Be the equality rows.  It is
 // never formed as H: with B = [Be; Bc] stacked in task order (K rows), E = diag(0 on equality rows, 1 on cost rows) and the

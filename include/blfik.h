@@ -369,12 +369,12 @@ int blfik_sync(blfik_problem* problem);
 void* blfik_get_stream(blfik_problem* problem);
 int blfik_set_stream(blfik_problem* problem, void* cuda_stream);
 /* Three kernels implement the tick: a register-resident one for nv <= 32 velocity variables and <= 32
- * dense task rows (all ergoCub / iCub-26 configurations); one for wider problems without inequality rows
- * (no JointLimitsTask / JointVelocityLimitsTask, <= 64 dense rows: the 32-joint iCubGazeboV2_5 configurations),
- * which keeps the QP in factored form; and a generic shared-memory one for everything else.
+ * dense task rows (all ergoCub / iCub-26 configurations); one for wider problems (<= 64 dense rows: the
+ * 32-joint iCubGazeboV2_5 configurations, with or without limit tasks), which keeps the QP in factored form;
+ * and a generic shared-memory one for everything else.
  * path 0 = choose automatically (default), 1 = force the generic kernel (parity tests run both).
  * blfik_get_kernel_path returns 2 when the next tick runs the register-resident kernel, 3 for the
- * equality-only kernel, else 1.
+ * factored-form kernel, else 1.
  * No reference counterpart (the reference has a single OSQP code path).                     */
 int blfik_set_kernel_path(blfik_problem* problem, int32_t path);
 int32_t blfik_get_kernel_path(const blfik_problem* problem);
