@@ -223,8 +223,8 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
             certified = true;
             break;
         }
-        if (!converged) break;
-        // complementarity: new code per joint
+        // complementarity: new code per joint (also from steps that have not settled: an over-full set on the way makes the
+        // rows nearly dependent and the steps slow; only the certificate needs them converged)
         int ninf = 0, first = nv;
         for (int base = 0; base < nv; base += 32) {
             const int i = base + lane;
@@ -252,7 +252,7 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
         }
         __syncwarp();
         if (ninf == 0) {
-            certified = true;
+            certified = converged;
             break;
         }
         if (ninf < best) best = ninf, stall = 0;
@@ -274,7 +274,8 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
         if (!(fabs(v) <= 1e-6 * (1.0 + fabs(w.b[k])))) bad = true;
     }
     bad = __any_sync(kFull, bad);
-    res.status = (!ok || bad) ? 2 : ((certified && converged) ? 0 : 1);
+    // contradicting rows count only under a certified set: a set abandoned on the way may hold joints that no solution fixes
+    res.status = !ok ? 2 : (certified ? (bad ? 2 : 0) : 1);
     return res;
 }
 

@@ -184,13 +184,16 @@ __device__ __forceinline__ double fast_matvec(const double (&nrow)[NV], const do
 // row t by lane t.  a <= 32.  Returns false if a pivot is not positive.
 // `floor`: pivots at or below it mean that the equality rows leave (a combination of) the selected joints no freedom:
 // N[A,A] is then singular up to rounding noise and its "inverse" would scatter that noise over the whole solution.
-// (N[j][j] <= 1 / D_j, so the floor of row k is 1e-10 / D of the joint it stands for.)
+// (N[j][j] <= 1 / D_j, so the floor of row k is 1e-6 / D of the joint it stands for.  N = D^-1 - U U' carries the rounding of a
+// factorisation whose condition number reaches 1e7 .. 1e8 when the equality rows are nearly dependent -- an absolute error of
+// about 1e-8 / D; with the former floor of 1e-10 a joint that those rows all but fix passed, and the correction through
+// 1 / N[j][j] put the "certified" point 0.2 off the equality rows (fuzz seed 680: sigma_min(C_eq) = 5e-3).)
 __device__ __forceinline__ bool fast_small_inverse(double* M, int a, int ld, int lane, const double* dinv, const int* idx)
 {
     bool ok = true;
     for (int k = 0; k < a; k++) {
         const double p = M[k * ld + k];
-        if (!(p > 1e-10 * dinv[idx[k]])) ok = false;
+        if (!(p > 1e-6 * dinv[idx[k]])) ok = false;
         const double ip = 1.0 / p;
         __syncwarp();
         if (lane == k) {
@@ -1016,7 +1019,7 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                                 for (int uu = 0; uu < a; uu++) MA[lane * mld + uu] = Ns[ri * LDB + idxA[uu]];
                             }
                             __syncwarp();
-                            // a joint whose N[j][j] is 1e-10 of its 1 / D_j is fixed by the equality rows and cannot
+                            // a joint whose N[j][j] is 1e-6 of its 1 / D_j is fixed by the equality rows and cannot
                             // be pinned to a bound: this active set has no solution, ADMM (and its verdict) takes over
                             small_ok = fast_small_inverse(MA, a, mld, lane, dinv, idxA);
                             small_ok = __all_sync(kFull, small_ok);
@@ -1041,9 +1044,13 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                                 __syncwarp();
                                 if (mine)
                                     for (int uu = 0; uu < a; uu++) x1 = fma(-Ns[lane * LDB + idxA[uu]], muA[uu], x1);
-                                if (act) x1 = bd, mu_mine = muA[rank];
                             }
+                            // measured before the pinned joints are set to their bounds: there x1 - xp is what the correction
+                            // left of x1 - bound, which only vanishes if the equality rows allow this active set (a nearly
+                            // singular N[A,A] otherwise passes the floor of fast_small_inverse and the certificate below would
+                            // accept a point that is off the equality rows)
                             dx = mine ? Q_i * fabs(x1 - xp) : 0.0;
+                            if (a > 0 && act) x1 = bd, mu_mine = muA[rank];
                             xp = mine ? x1 : 0.0;
                             iters++;
                             if ((it & 1) == 1 || it + 1 == FP.max_polish_iters) {

@@ -1293,7 +1293,8 @@ def test_random_task_mixes_vs_oracle(seed):
             Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [None if sp is None else sp[i] for sp in sps])
             cx = Co @ nu[i]
             viol = max((cx - u).max(), (l - cx).max())
-            assert viol <= 1e-6 * (1 + np.abs(cx).max()), ("the GPU certifies an infeasible point", i, viol, kinds)
+            assert viol <= 1e-6 * (1 + np.abs(cx).max()), ("the GPU certifies an infeasible point", i, viol, kinds, n, prob.kernel_path, eq_path,
+                                                          int(np.argmax(np.maximum(cx - u, l - cx))), me)
     checked = 0
     for i in range(N):
         Ho, go, Co, l, u = o.assemble(p0[i], q0[i], s0[i], [None if sp is None else sp[i] for sp in sps])
