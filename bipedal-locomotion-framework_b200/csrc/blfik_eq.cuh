@@ -304,13 +304,15 @@ __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams 
                 P.nu[(size_t)nv * robot + i] = w.x[i];
                 P.wx[(size_t)nv * robot + i] = w.x[i];
                 if (P.nu_host) P.nu_host[(size_t)nv * robot + i] = w.x[i];
+                // the active set of this tick seeds the next one, also inside a multi-tick launch (w.y does not survive K1 / K2)
+                if (P.L.box && i >= 6) P.wy[(size_t)n * robot + i - 6] = w.y[i];
             }
             __syncwarp();
             if (P.flags & BLFIK_TICK_INTEGRATE) k4_integrate(n, bp, bq, s, w.x, P.dt, lane);
         }
-        for (int i = lane; i < n; i += 32) {   // warm start of the next launch: the active set (wy), the joint part of x (wz)
+        for (int i = lane; i < n; i += 32) {   // warm start of the next launch: the joint part of x (wz); the active set is in wy
             P.wz[(size_t)n * robot + i] = w.x[6 + i];
-            P.wy[(size_t)n * robot + i] = P.L.box ? w.y[6 + i] : 0.0;
+            if (!P.L.box) P.wy[(size_t)n * robot + i] = 0.0;
         }
         if (lane == 0) {
             P.status[robot] = res.status;
