@@ -99,7 +99,7 @@ __device__ __forceinline__ bool eq_solve_fixed(const TickParams& P, const WM& w,
             const double piv = w.Ss[k * LDE + k];
             const bool dropped = !(piv > floor_);
             if (dropped && !(piv == piv)) ok = false;
-            const double d = dropped ? 0.0 : sqrt(piv), inv = dropped ? 0.0 : 1.0 / d;
+            const double inv = dropped ? 0.0 : rsqrt(piv), d = piv * inv;   // one reciprocal square root instead of sqrt and a division
             __syncwarp();
             for (int i = k + 1 + lane; i < K; i += 32) w.Ss[i * LDE + k] *= inv;
             if (lane == 0) w.Ss[k * LDE + k] = d;
