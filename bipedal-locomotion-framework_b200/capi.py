@@ -469,7 +469,7 @@ class Problem:
 
     @property
     def kernel_path(self) -> int:
-        """2 = register-resident kernel, 1 = generic kernel."""
+        """2 = register-resident kernel, 3 = factored-form kernel (33 to 64 velocity variables), 1 = generic kernel."""
         return int(self.L.blfik_get_kernel_path(self.handle))
 
     @property
