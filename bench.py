@@ -287,7 +287,7 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         achieved_tf = flops_launch / (kernel_ms * 1e-3) * 1e-12
         bytes_launch = algorithmic_bytes_per_tick(n, sp_doubles) * n_local
         cores = os.cpu_count() or 1
-        cpu_sample = 1024 * cores
+        cpu_sample = 4096 * cores   # 65,536 instances on a 16-core box: about 20 s of CPU work at the GPU run's accuracy
         cpu_rate, cpu_bad = cpu_oracle_rate(w, inputs, min(cpu_sample, n_local), cores)
         cpu_stock = cpu_oracle_rate(w, inputs, min(cpu_sample, n_local), cores, osqp_defaults=True)[0]
         line = {
