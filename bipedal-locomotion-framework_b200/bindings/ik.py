@@ -163,6 +163,34 @@ class IKLinearTask:
     _spline = None
     _spline_version = 0
 
+    def set_set_point_minimum_jerk(self, target, duration):
+        """Batch extension (the reference evaluates a Planners::SO3Planner / a two-knot QuinticSpline on the host every period and
+        passes the point to setSetPoint): from the stored set-point to ``target`` -- set-point records [N, len] or one [len] for
+        every robot, of which the pose part is read -- along the minimum-jerk profile over ``duration`` (seconds or timedelta),
+        evaluated on the device from the solver's time at the next advance() on (blfik_set_setpoint_minimum_jerk; equals
+        ``planners.SO3PlannerInertial`` with zero boundary conditions for the rotation).  SE3 / SO3 / CoM / R3 tasks; a
+        non-positive duration switches it off."""
+        name = type(self).__name__
+        if not (self._spline_ok or isinstance(self, SO3Task)):
+            log().error("[%s::setSetPointMinimumJerk] The task has no pose set-point such a generator could drive.", name)
+            return False
+        T_ = duration.total_seconds() if hasattr(duration, "total_seconds") else float(duration)
+        if T_ <= 0:
+            self._min_jerk, self._min_jerk_version = None, self._min_jerk_version + 1
+            return True
+        N = self._kin_dyn.N
+        rec = np.asarray(target, dtype=np.float64)
+        if rec.ndim == 1:
+            rec = np.tile(rec, (N, 1))
+        if rec.shape != (N, self._sp_len):
+            log().error("[%s::setSetPointMinimumJerk] The target must be a set-point record. Expected shape: %s. Given: %s.", name, (N, self._sp_len), rec.shape)
+            return False
+        self._min_jerk, self._min_jerk_version = (np.ascontiguousarray(rec), T_), self._min_jerk_version + 1
+        return True
+
+    _min_jerk = None
+    _min_jerk_version = 0
+
     _fb_len = 0
     _fb_init = ()
 
@@ -760,7 +788,7 @@ class QPInverseKinematics:
                 return False
             for e, sp in zip(native, specs):
                 e["sp_version"], e["gains_version"], e["weight"] = -1, e["task"]._gains_version, None if sp.weight is None else np.array(sp.weight)
-                e["fb_version"] = e["spline_version"] = 0
+                e["fb_version"] = e["spline_version"] = e["min_jerk_version"] = 0
             self._kin_dyn, self._state_version = kd, -1
         self._finalized = True
         return True
@@ -784,6 +812,16 @@ class QPInverseKinematics:
             if task._sp_len and e["sp_version"] != task._sp_version:
                 prob.set_setpoint(t, task._sp)
                 e["sp_version"] = task._sp_version
+            if e.get("min_jerk_version", 0) != task._min_jerk_version:
+                try:
+                    if task._min_jerk is None:
+                        prob.set_setpoint_minimum_jerk(t, None, 0.0)
+                    else:
+                        prob.set_setpoint_minimum_jerk(t, *task._min_jerk)
+                except capi.BlfikError as err:
+                    log().error("%s Unable to set the minimum-jerk generator of the task named %s: %s", prefix, e["name"], err)
+                    return False
+                e["min_jerk_version"] = task._min_jerk_version
             if task._spline_ok and e.get("spline_version", 0) != task._spline_version:
                 try:
                     if task._spline is None:

@@ -134,6 +134,33 @@ public:
         return true;
     }
     void clearSetPointSpline() { m_splineTimes.clear(), m_splineVersion++; }
+    /** From the stored set-point to `targetRecords` ([N][setPointLength()], of which the pose part is read) along the
+     *  minimum-jerk profile over `duration`, evaluated on the device from the solver's time at the next advance() on
+     *  (blfik_set_setpoint_minimum_jerk; for the rotation this is Planners::SO3PlannerInertial with zero boundary conditions).
+     *  SE3 / SO3 / CoM / R3 tasks; a non-positive duration switches it off. */
+    virtual bool acceptsMinimumJerk() const { return acceptsSetPointSpline(); }
+    bool setSetPointMinimumJerk(const std::vector<double>& targetRecords, std::chrono::nanoseconds duration)
+    {
+        if (!acceptsMinimumJerk()) {
+            log()->error("[{}::setSetPointMinimumJerk] The task has no pose set-point such a generator could drive.", className());
+            return false;
+        }
+        if (duration <= std::chrono::nanoseconds::zero()) {
+            m_minJerkDuration = 0.0, m_minJerkVersion++;
+            return true;
+        }
+        const std::size_t N = m_kinDyn ? m_kinDyn->getBatchSize() : 0;
+        if (targetRecords.size() != N * setPointLength()) {
+            log()->error("[{}::setSetPointMinimumJerk] One set-point record per robot is expected. Expected size: {}. Given size: {}.", className(),
+                         N * setPointLength(), targetRecords.size());
+            return false;
+        }
+        m_minJerkTarget = targetRecords, m_minJerkDuration = std::chrono::duration<double>(duration).count(), m_minJerkVersion++;
+        return true;
+    }
+    const std::vector<double>& minimumJerkTarget() const { return m_minJerkTarget; }
+    double minimumJerkDuration() const { return m_minJerkDuration; }
+    unsigned long minimumJerkVersion() const { return m_minJerkVersion; }
     const std::vector<double>& splineTimes() const { return m_splineTimes; }
     const std::vector<double>& splinePositions() const { return m_splinePositions; }
     const std::vector<double>& splineBoundary() const { return m_splineBoundary; }
@@ -218,6 +245,9 @@ protected:
     unsigned long m_spVersion{0}, m_gainsVersion{0}, m_fbVersion{0}, m_splineVersion{0};
     int m_inspect{-1};
     bool m_splineCubic{false};
+    std::vector<double> m_minJerkTarget;
+    double m_minJerkDuration{0.0};
+    unsigned long m_minJerkVersion{0};
 };
 
 using IKLinearTaskFactory = System::Factory<IKLinearTask>;
@@ -287,6 +317,7 @@ class SO3Task : public IKLinearTask
 {
 public:
     const char* className() const override { return "SO3Task"; }
+    bool acceptsMinimumJerk() const override { return true; }
     bool initialize(std::weak_ptr<const ParametersHandler::IParametersHandler> paramHandler) override;
     bool update() override;
     bool setSetPoint(const SO3d& I_R_F, const SO3Tangentd& angularVelocity = SO3Tangentd::Zero(), std::ptrdiff_t instance = -1);

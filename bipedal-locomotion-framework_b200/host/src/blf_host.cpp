@@ -1121,7 +1121,7 @@ struct QPInverseKinematics::Impl {
         std::size_t priority{0};
         std::shared_ptr<const System::WeightProviderPort> weightProvider;
         VectorXd uploadedWeight;
-        unsigned long uploadedSetPoint{~0ul}, uploadedGains{~0ul}, uploadedFeedback{0}, uploadedSpline{0};
+        unsigned long uploadedSetPoint{~0ul}, uploadedGains{~0ul}, uploadedFeedback{0}, uploadedSpline{0}, uploadedMinJerk{0};
     };
     std::vector<TaskEntry> tasks;   // insertion order = row order of the constraint matrix (QPInverseKinematics.cpp:201,236)
     std::unordered_map<std::string, std::size_t> index;
@@ -1290,7 +1290,7 @@ bool QPInverseKinematics::finalize(const System::VariablesHandler& handler)
             e.uploadedWeight = e.weightProvider->getOutput();
             descs[t].weight = keepVector(keep, e.uploadedWeight);
         }
-        e.uploadedSetPoint = ~0ul, e.uploadedGains = e.task->gainsVersion(), e.uploadedFeedback = 0, e.uploadedSpline = 0;
+        e.uploadedSetPoint = ~0ul, e.uploadedGains = e.task->gainsVersion(), e.uploadedFeedback = 0, e.uploadedSpline = 0, e.uploadedMinJerk = 0;
     }
     if (!m_pimpl->kinDyn) {
         log()->error("{} No KinDyn object: build the solver with QPInverseKinematics::build or call setKinDyn through a task added by addTask.", logPrefix);
@@ -1388,6 +1388,12 @@ bool QPInverseKinematics::tick(double dt, uint32_t flags)
         if (e.task->setPointLength() > 0 && e.task->setPointVersion() != e.uploadedSetPoint) {
             if (blfik_set_setpoint(prob, static_cast<int32_t>(t), e.task->setPointBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the set-point");
             e.uploadedSetPoint = e.task->setPointVersion();
+        }
+        if (e.task->acceptsMinimumJerk() && e.task->minimumJerkVersion() != e.uploadedMinJerk) {   // setSetPointMinimumJerk(...) since the last tick
+            const double T = e.task->minimumJerkDuration();
+            if (blfik_set_setpoint_minimum_jerk(prob, static_cast<int32_t>(t), T > 0 ? e.task->minimumJerkTarget().data() : nullptr, T, BLFIK_MEM_HOST) != BLFIK_OK)
+                return fail("Unable to set the minimum-jerk generator");
+            e.uploadedMinJerk = e.task->minimumJerkVersion();
         }
         if (e.task->acceptsSetPointSpline() && e.task->splineVersion() != e.uploadedSpline) {   // setSetPointSpline(...) since the last tick
             const auto& tm = e.task->splineTimes();

@@ -801,6 +801,49 @@ static void testSetPointSpline(const char* modelPath, std::size_t N)
     REQUIRE(worst < 1e-8);
     handDev->clearSetPointSpline();
     REQUIRE(ikDev.advance());
+    // setSetPointMinimumJerk: from the stored pose to a turned and shifted one over 0.4 s; the device generator against
+    // SO3PlannerInertial (rotation) and the two-knot minimum-jerk profile (position) evaluated on the host
+    {
+        using namespace BipedalLocomotion::Planners;
+        std::vector<double> target(N * 13, 0.0);
+        std::vector<SO3PlannerInertial> planners(N);
+        std::vector<Vector3d> shift(N);
+        for (std::size_t i = 0; i < N; i++) {
+            const SO3d R1 = SO3d::Exp({0.1 * (i + 1), -0.05, 0.2}) * pose[i].R;
+            shift[i] = {0.01 * (i + 1), -0.02, 0.015};
+            const auto q = R1.quat().coeffs();
+            for (int c = 0; c < 3; c++) target[i * 13 + c] = pose[i].translation()[c] + shift[i][c];
+            for (int c = 0; c < 4; c++) target[i * 13 + 3 + c] = q[c];
+            REQUIRE(planners[i].setRotations(pose[i].R, R1, 400ms));
+            REQUIRE(planners[i].setInitialConditions(SO3Tangentd::Zero(), SO3Tangentd::Zero()) && planners[i].setFinalConditions(SO3Tangentd::Zero(), SO3Tangentd::Zero()));
+            REQUIRE(handHost->setSetPoint(pose[i], SE3d::Tangent::Zero(), i));
+        }
+        log()->setLevel(Logger::Level::off);
+        REQUIRE_FALSE(std::make_shared<JointTrackingTask>()->setSetPointMinimumJerk(target, 400ms));
+        REQUIRE_FALSE(handDev->setSetPointMinimumJerk(std::vector<double>(5, 0.0), 400ms));
+        log()->setLevel(Logger::Level::warn);
+        REQUIRE(handDev->setSetPointMinimumJerk(target, 400ms));
+        REQUIRE(ikDev.setTime(3s) && ikDev.advance() && ikHost.advance());   // tau = 0
+        double worstMj = 0.0;
+        for (const std::chrono::nanoseconds dtau : {100ms, 250ms, 400ms, 700ms}) {
+            REQUIRE(ikDev.setTime(3s + dtau) && ikDev.advance());
+            const double tau = std::min(1.0, std::chrono::duration<double>(dtau).count() / 0.4);
+            const double sv = tau * tau * tau * (10.0 - 15.0 * tau + 6.0 * tau * tau), sd = tau < 1.0 ? 30.0 * tau * tau * (1 - tau) * (1 - tau) / 0.4 : 0.0;
+            for (std::size_t i = 0; i < N; i++) {
+                SO3PlannerState st;
+                REQUIRE(planners[i].evaluatePoint(std::min(dtau, std::chrono::nanoseconds(400ms)), st));
+                SE3d::Tangent ff = SE3d::Tangent::Zero();
+                Vector3d p = pose[i].translation();
+                for (int c = 0; c < 3; c++) p[c] += sv * shift[i][c], ff.linear[c] = sd * shift[i][c];
+                ff.angular = st.velocity.w;
+                REQUIRE(handHost->setSetPoint(SE3d(p, st.rotation), ff, i));
+            }
+            REQUIRE(ikHost.advance());
+            for (std::size_t k = 0; k < ikDev.getBatchOutput().size(); k++) worstMj = std::max(worstMj, std::abs(ikDev.getBatchOutput()[k] - ikHost.getBatchOutput()[k]));
+        }
+        REQUIRE(worstMj < 1e-8);
+        REQUIRE(handDev->setSetPointMinimumJerk({}, 0ns) && ikDev.advance());
+    }
 }
 
 static void testFixedBase(const char* modelPath, std::size_t N)

@@ -559,6 +559,21 @@ def test_set_point_spline_through_the_bindings():
     assert com_dev.set_set_point_spline(None) and ik_dev.advance()
     assert com_host.set_set_point(position=c) and ik_host.advance()
     assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
+    # the minimum-jerk generator through the task: from c to c + d over 0.5 s, starting at the solver's time of the next advance
+    d = np.array([0.01, -0.02, 0.005])
+    assert not reg_only.set_set_point_minimum_jerk(np.zeros(6), 0.5)
+    assert com_dev.set_set_point_minimum_jerk(np.concatenate([c + d, np.zeros(3)]), timedelta(seconds=0.5))
+    assert ik_dev.set_time(2.0) and ik_dev.advance()                     # tau = 0: still at c
+    assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
+    for tau in (0.3, 0.8, 1.0, 1.7):
+        sv = 10 * min(tau, 1.0) ** 3 - 15 * min(tau, 1.0) ** 4 + 6 * min(tau, 1.0) ** 5
+        sd = 30 * tau ** 2 * (1 - tau) ** 2 / 0.5 if tau < 1.0 else 0.0
+        assert ik_dev.set_time(2.0 + 0.5 * tau) and ik_dev.advance()
+        assert com_host.set_set_point(position=c + sv * d, velocity=sd * d) and ik_host.advance()
+        assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
+    assert com_dev.set_set_point_minimum_jerk(None, 0.0) and ik_dev.advance()
+    assert com_host.set_set_point(position=c) and ik_host.advance()
+    assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
 
 
 # ------------------------------------------------------------------------------------------------ Planners: SO3Planner
