@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
             }
         }
         QpResult res = {2, 0};
-        int iters = 0;
+        int iters = 0, worst = 0;
         for (int tick = 0; tick < P.nticks; tick++) {
             k1_fk(P.m, w, bp, bq, s, lane);
             k2_assemble(P, w, robot, s, lane, P.t0 + tick * P.dt);
@@ -57,12 +57,18 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
             }
             res = k3_solve(P, w, warm, lane);
             iters += res.iters;
+            worst = res.status > worst ? res.status : worst;
+            if (res.status == 2) {   // no velocity to report (the reference's advance() fails): hold still
+                for (int i = lane; i < nv; i += 32) w.x[i] = 0.0;
+                __syncwarp();
+            }
             warm = (P.flags & BLFIK_TICK_WARM_START) != 0;
             for (int i = lane; i < nv; i += 32) {
                 P.nu[(size_t)nv * robot + i] = w.x[i];
                 if (P.nu_host) P.nu_host[(size_t)nv * robot + i] = w.x[i];
             }
             __syncwarp();
+            if (res.status == 2) break;   // a failed tick ends this robot's rollout: its state stays where the failure happened
             if (P.flags & BLFIK_TICK_INTEGRATE) k4_integrate(n, bp, bq, s, w.x, P.dt, lane);
         }
         for (int i = lane; i < nv; i += 32) {
@@ -73,8 +79,8 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
             }
         }
         if (lane == 0) {
-            P.status[robot] = res.status;
-            if (P.status_host) P.status_host[robot] = res.status;
+            P.status[robot] = worst;   // the worst tick of the launch, not the last one
+            if (P.status_host) P.status_host[robot] = worst;
             P.iters[robot] = iters;
         }
         __syncwarp();
@@ -1653,6 +1659,12 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
             if (strict_env) return fail(BLFIK_ERR_CUDA, "[blfik_tick_packed] the kernel gave up waiting for the input records (copy stream stalled)");
             p->streaming_off = true;
             if (flags & BLFIK_TICK_INTEGRATE) p->time -= dt;
+            // the aborted launch has drawn from counter slot 0 (every team that gave up still added its share): the chunk
+            // launches below assume zeroed counters
+            if (p->work_counter) CU(cudaMemsetAsync(p->work_counter, 0, kCounterSlots * sizeof(int), p->stream));
+            CU(cudaEventRecord(p->ev_start, p->stream));
+            CU(cudaStreamWaitEvent(p->h2d_stream, p->ev_start, 0));
+            CU(cudaStreamWaitEvent(p->d2h_stream, p->ev_start, 0));
         }
     }
     // results: when nu (and status) are mapped page-locked buffers the kernels write them straight to the host (posted
@@ -1822,7 +1834,8 @@ extern "C" int blfik_kinematics(blfik_problem* p, const int32_t* frames, int32_t
 static __device__ __align__(256) unsigned char g_noalloc_scratch[BLFIK_NOALLOC_SCRATCH_BYTES];
 
 static constexpr int kMaxDevices = 64;
-static unsigned char* g_noalloc_ptr[kMaxDevices];  // device address per device ordinal, 0 = not looked up yet
+static unsigned char* g_noalloc_ptr[kMaxDevices];  // device address per device ordinal, 0 = not looked up yet (host threads that
+                                                   // race on the first look-up all store the same value)
 
 // Device address of the staging array on `device`, which must be the current device.
 static int noalloc_scratch(int device, unsigned char** out)
@@ -1870,7 +1883,10 @@ extern "C" int blfik_kinematics_noalloc(blfik_problem* p, const int32_t* frames,
     size_t off = 0;
     int* d_frames = reinterpret_cast<int*>(base);
     off += round256(nf * sizeof(int));
-    if (nframes) CU(cudaMemcpyAsync(d_frames, frames, nf * sizeof(int), cudaMemcpyHostToDevice, p->stream));
+    // From here on work may be in flight on the staging array: errors are collected, not returned on the spot, so that the
+    // call always reaches the stream synchronisation below before it hands the array to the next caller.
+    cudaError_t e = cudaSuccess;
+    if (nframes) e = cudaMemcpyAsync(d_frames, frames, nf * sizeof(int), cudaMemcpyHostToDevice, p->stream);
     for (Buf& b : bufs) {
         if (!b.user) continue;
         if (mem == BLFIK_MEM_DEVICE) b.dev = b.user;
@@ -1879,19 +1895,23 @@ extern "C" int blfik_kinematics_noalloc(blfik_problem* p, const int32_t* frames,
             off += round256(b.bytes);
         }
     }
-    KinParams K;
-    K.m = p->dm, K.N = p->N, K.base_pos = p->base_pos, K.base_quat = p->base_quat, K.s = p->s, K.frames = d_frames, K.nframes = nframes;
-    K.frame_pos = bufs[0].user ? bufs[0].dev : nullptr, K.frame_rot = bufs[1].user ? bufs[1].dev : nullptr;
-    K.frame_jac = bufs[2].user ? bufs[2].dev : nullptr, K.com = bufs[3].user ? bufs[3].dev : nullptr, K.com_jac = bufs[4].user ? bufs[4].dev : nullptr;
-    K.L = p->L;
-    blfik_kinematics_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(K);
-    CU(cudaGetLastError());
-    p->launches++;
-    if (mem != BLFIK_MEM_DEVICE)
+    if (e == cudaSuccess) {
+        KinParams K;
+        K.m = p->dm, K.N = p->N, K.base_pos = p->base_pos, K.base_quat = p->base_quat, K.s = p->s, K.frames = d_frames, K.nframes = nframes;
+        K.frame_pos = bufs[0].user ? bufs[0].dev : nullptr, K.frame_rot = bufs[1].user ? bufs[1].dev : nullptr;
+        K.frame_jac = bufs[2].user ? bufs[2].dev : nullptr, K.com = bufs[3].user ? bufs[3].dev : nullptr, K.com_jac = bufs[4].user ? bufs[4].dev : nullptr;
+        K.L = p->L;
+        blfik_kinematics_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(K);
+        e = cudaGetLastError();
+        p->launches++;
+    }
+    if (e == cudaSuccess && mem != BLFIK_MEM_DEVICE)
         for (Buf& b : bufs)
-            if (b.user) CU(cudaMemcpyAsync(b.user, b.dev, b.bytes, cudaMemcpyDeviceToHost, p->stream));
-    // the staging array is free for the next caller only once everything has left it
-    CU(cudaStreamSynchronize(p->stream));
+            if (b.user && e == cudaSuccess) e = cudaMemcpyAsync(b.user, b.dev, b.bytes, cudaMemcpyDeviceToHost, p->stream);
+    // the staging array is free for the next caller only once everything has left it -- also after a failure
+    const cudaError_t es = cudaStreamSynchronize(p->stream);
+    if (e == cudaSuccess) e = es;
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_kinematics_noalloc] %s", cudaGetErrorString(e));
     return BLFIK_OK;
 }
 

@@ -220,7 +220,9 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     for (int piv = 0; piv < max_pivots; piv++) {
         ok = eq_solve_fixed(P, w, lane, res.iters, converged) && ok;
         if (!L.box) {
-            certified = true;
+            // the equality rows hold at every step by construction; what the step cap can leave unfinished is the cost
+            // (a cost weight far below sigma contracts slowly), and then the tick must not claim SOLVED
+            certified = converged;
             break;
         }
         // complementarity: new code per joint (also from steps that have not settled: an over-full set on the way makes the
@@ -294,12 +296,17 @@ __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams 
         if (P.packed) unpack_state(P, robot, bp, bq, s, n, lane);
         bool warm = (P.flags & BLFIK_TICK_WARM_START) != 0;
         QpResult res = {2, 0};
-        int iters = 0;
+        int iters = 0, worst = 0;
         for (int tick = 0; tick < P.nticks; tick++) {
             k1_fk(P.m, w, bp, bq, s, lane);
             k2_assemble<true>(P, w, robot, s, lane, P.t0 + tick * P.dt);
             res = k3_solve_eq(P, w, warm, robot, lane);
             iters += res.iters;
+            worst = res.status > worst ? res.status : worst;
+            if (res.status == 2) {   // no velocity to report (the reference's advance() fails): hold still
+                for (int i = lane; i < nv; i += 32) w.x[i] = 0.0;
+                __syncwarp();
+            }
             for (int i = lane; i < nv; i += 32) {
                 P.nu[(size_t)nv * robot + i] = w.x[i];
                 P.wx[(size_t)nv * robot + i] = w.x[i];
@@ -308,6 +315,7 @@ __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams 
                 if (P.L.box && i >= 6) P.wy[(size_t)n * robot + i - 6] = w.y[i];
             }
             __syncwarp();
+            if (res.status == 2) break;   // a failed tick ends this robot's rollout: its state stays where the failure happened
             if (P.flags & BLFIK_TICK_INTEGRATE) k4_integrate(n, bp, bq, s, w.x, P.dt, lane);
         }
         for (int i = lane; i < n; i += 32) {   // warm start of the next launch: the joint part of x (wz); the active set is in wy
@@ -315,8 +323,8 @@ __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams 
             if (!P.L.box) P.wy[(size_t)n * robot + i] = 0.0;
         }
         if (lane == 0) {
-            P.status[robot] = res.status;
-            if (P.status_host) P.status_host[robot] = res.status;
+            P.status[robot] = worst;   // the worst tick of the launch, not the last one
+            if (P.status_host) P.status_host[robot] = worst;
             P.iters[robot] = iters;
         }
         __syncwarp();

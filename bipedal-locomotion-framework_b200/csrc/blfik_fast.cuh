@@ -607,7 +607,8 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
             x = P.wx[(size_t)nv * robot + lane];
             if (joint) z = P.wz[(size_t)n * robot + lane - 6], y = P.wy[(size_t)n * robot + lane - 6];
         }
-        int status = 2, iters_total = 0;
+        int status = 2, iters_total = 0, worst = 0;
+        bool dead = false;
         for (int tick = 0; tick < P.nticks; tick++) {
           // Two attempts per tick.  Attempt 0 (FP.pdas_first): factorise WITHOUT the ADMM penalty (rho = 0), so the
           // proximal steps contract by sigma / (sigma + lambda) ~ 1e-2 and each active-set guess is solved in 2-3
@@ -1099,11 +1100,17 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
             if (!any_box) break;   // a pure equality QP has no second attempt
           }
             iters_total += iters;
+            // A failed tick ends this robot's rollout: no velocity to report (the reference's advance() fails), the state stays
+            // where the failure happened.  The warp still walks through the remaining ticks -- its team meets at the phase
+            // barriers of every tick -- but reports nothing from them.
+            if (dead) status = 2;
+            worst = status > worst ? status : worst;
+            if (status == 2) x = 0.0, dead = true;
             if (mine && active) {
                 P.nu[(size_t)nv * robot + lane] = x;
                 if (P.nu_host) P.nu_host[(size_t)nv * robot + lane] = x;
             }
-            if ((P.flags & BLFIK_TICK_INTEGRATE) && active) {
+            if ((P.flags & BLFIK_TICK_INTEGRATE) && active && !dead) {
                 rvec[lane] = mine ? x : 0.0;
                 __syncwarp();
                 k4_integrate(n, bp, bq, s, rvec, P.dt, lane);
@@ -1115,8 +1122,8 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
             if (joint) P.wz[(size_t)n * robot + lane - 6] = z, P.wy[(size_t)n * robot + lane - 6] = y;
         }
         if (lane == 0 && active) {
-            P.status[robot] = status;
-            if (P.status_host) P.status_host[robot] = status;
+            P.status[robot] = worst;   // the worst tick of the launch, not the last one
+            if (P.status_host) P.status_host[robot] = worst;
             P.iters[robot] = iters_total;
         }
         __syncwarp();

@@ -254,7 +254,12 @@ int blfik_set_limits(blfik_problem* problem, int32_t task, const double* upper_l
 
 /* ---- the tick ---------------------------------------------------------------------- */
 /* replaces QPInverseKinematics::advance() (+ ForwardEuler::integrate(0, dt) when
- * BLFIK_TICK_INTEGRATE) repeated nticks times with the set-points held.  Asynchronous.   */
+ * BLFIK_TICK_INTEGRATE) repeated nticks times with the set-points held.  Asynchronous.
+ * Status of a launch: the WORST tick of each robot (0 < 1 < 2), not the last one.  A tick that ends FAILED
+ * (the reference's advance() returns false there, QPInverseKinematics.cpp:511-523, and its caller stops
+ * integrating) ends that robot's rollout: its nu is zero, its state stays where the failure happened and the
+ * remaining ticks of the launch leave it alone.  MAX_ITER ("solved inaccurate") is accepted like the reference
+ * accepts it: the tick's velocity is reported and integrated.                                              */
 int blfik_tick(blfik_problem* problem, int32_t nticks, double dt, uint32_t flags);
 
 /* The whole reference-facing tick for callers whose data live in HOST memory (what the reference's caller does

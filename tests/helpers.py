@@ -58,3 +58,19 @@ def solve_qp_active_set(H, g, C, l, u, tol=1e-10, max_iter=200):
     r = minimize(lambda x: 0.5 * x @ H @ x + g @ x, x0, jac=lambda x: H @ x + g, constraints=cons, method="SLSQP",
                  options={"ftol": 1e-15, "maxiter": 500})
     return r.x
+
+
+def referee(H, g, C, l, u):
+    """Exact verdict on one instance of the reference's QP (min 1/2 x'Hx + g'x, l <= Cx <= u), independent of both solvers:
+    feasibility by scipy's HiGHS linear programme, the optimum by SLSQP.  Returns (feasible, x or None)."""
+    from scipy.optimize import linprog
+    nv = H.shape[0]
+    eq = l == u
+    fin_u, fin_l = (~eq) & (u < 1e29), (~eq) & (l > -1e29)
+    A_ub = np.vstack([C[fin_u], -C[fin_l]]) if (fin_u.any() or fin_l.any()) else None
+    b_ub = np.concatenate([u[fin_u], -l[fin_l]]) if A_ub is not None else None
+    r = linprog(np.zeros(nv), A_ub=A_ub, b_ub=b_ub, A_eq=C[eq] if eq.any() else None, b_eq=u[eq] if eq.any() else None,
+                bounds=[(None, None)] * nv, method="highs")
+    if r.status == 2:
+        return False, None
+    return True, solve_qp_active_set(H, g, C, l, u)
