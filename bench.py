@@ -280,7 +280,7 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
             pass
         hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
         K = sum(t.rows(n) for t in w.tasks if t.type in (0, 1, 2, 6))
-        fast = prob.kernel_path == 2
+        fast = prob.kernel_path in (2, 4)
         flops_launch = algorithmic_flops_per_tick(n, prob.me, K, iters.astype(np.float64), fast, prob_settings["admm_iters"],
                                                   prob_settings["polish_iters"])
         kernel_ms = ms_dev / args.steps

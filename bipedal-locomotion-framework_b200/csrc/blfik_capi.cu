@@ -4,6 +4,9 @@
 #include "blfik_device.cuh"
 #include "blfik_fast.cuh"
 #include "blfik_eq.cuh"
+#include "blfik_split.cuh"
+#include "blfik_assemble.cuh"
+#include "blfik_inst.h"
 
 #include <cstdarg>
 #include <cstdio>
@@ -374,6 +377,15 @@ struct blfik_problem {
     int max_as_iters = 6, max_polish_iters = 40, max_total_iters = 200;
     double* d_model_pack = nullptr;
     int njump = 0, has_com = 0;
+    // two-launch path (blfik_split.cuh): assemble (one thread per robot) -> QP records -> solve (one warp per robot)
+    void (*solve_kernel)(const SolveParams) = nullptr;
+    int rec_len = 0, rec_off_c = 0, rec_off_v = 0, rec_kp = 0;
+    void (*asm_kernel)(const AsmParams) = nullptr;
+    int solve_wpb = 1;
+    size_t solve_smem = 0, asm_smem = 0;
+    int pack_len = 0, asm_threads = 128, asm_D = 0, asm_nevents = 0;
+    int* d_asm_events = nullptr;
+    double* d_qp = nullptr;          // [N][rec_len], allocated by the first tick that takes this path
     // pipelined host-buffer tick (blfik_tick_host)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     cudaStream_t chunk_stream[4] = {nullptr, nullptr, nullptr, nullptr};   // blfik_tick_packed: consecutive chunk kernels alternate, so one fills the SMs the other's tail leaves idle
@@ -461,6 +473,12 @@ static void pick_fast(blfik_problem* p)
 {
     p->fast_kernel = blfik_tick_fast_kernel<NV, KP, AM>;
     p->fast_wpb = FastDims<NV, KP>::WARPS;   // the kernel's launch bound
+    p->solve_kernel = blfik_solve_kernel<NV, KP>;
+    p->rec_len = QpRec<NV, KP>::LEN, p->rec_off_c = QpRec<NV, KP>::cvec, p->rec_off_v = QpRec<NV, KP>::vec;
+    p->rec_kp = KP;
+    p->asm_kernel = blfik_assemble_kernel<KP>;
+    p->solve_wpb = SolveDims<NV, KP>::WPB;
+    p->solve_smem = (size_t)SolveDims<NV, KP>::WPB * SolveLayout<NV, KP>::TOTAL * sizeof(double);
     p->F = make_fast_layout<NV, KP>(p->n + 1);
     // the control-law buffer ([ntasks][12]) lives in the U region during K2
     // (it always fits: ntasks * 12 <= 32 * 12 <= NV * LDG for every instantiation with NV >= 29, KP >= 16)
@@ -859,7 +877,49 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
                     cudaFuncSetAttribute((const void*)p->fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) != cudaSuccess)
                     return bail(fail(BLFIK_ERR_CUDA, "[blfik_problem_create] cannot reserve %zu B of shared memory for the register-resident kernel: %s",
                                      p->fast_smem, cudaGetErrorString(cudaGetLastError())));
+                // the two-launch path shares the packed model; its kernels size their own shared memory
+                p->pack_len = p->F.sh_model_len;
+                {
+                    // depth-first walk of the tree for the assemble kernel: visit a link, its subtree, then close it
+                    const int nl = n + 1;
+                    std::vector<std::vector<int>> kids(nl);
+                    for (int k = 1; k < nl; k++) kids[model->parent[k]].push_back(k);
+                    std::vector<int> ev;
+                    std::vector<std::pair<int, size_t>> stack;   // (link, next child)
+                    stack.push_back({0, 0});
+                    while (!stack.empty()) {
+                        auto& top = stack.back();
+                        if (top.second < kids[top.first].size()) {
+                            const int c = kids[top.first][top.second++];
+                            ev.push_back((0 << 16) | (model->depth[c] << 8) | c);
+                            stack.push_back({c, 0});
+                        } else {
+                            if (top.first != 0) ev.push_back((1 << 16) | (model->depth[top.first] << 8) | top.first);
+                            stack.pop_back();
+                        }
+                    }
+                    p->asm_nevents = (int)ev.size(), p->asm_D = model->maxdepth + 1;
+                    const int tile_doubles = 4 * 32 * (p->rec_kp | 1);   // one [32][KP | 1] staging tile per warp
+                    int ndense = 0;
+                    bool unsupported = false;
+                    for (const HostTask& h : p->tasks) {
+                        ndense += is_dense(h.d.type);
+                        unsupported |= h.d.type == BLFIK_TASK_DISTANCE || h.d.type == BLFIK_TASK_ANGULAR_MOMENTUM;
+                    }
+                    const size_t fixed = (size_t)p->pack_len + ((size_t)ntasks * sizeof(DevTask) + 7) / 8 + (ev.size() + 1) / 2 + 1 + 4 * (size_t)ntasks;
+                    p->asm_threads = 128;
+                    p->asm_smem = (fixed + (size_t)tile_doubles) * sizeof(double);
+                    int rc2 = BLFIK_OK;
+                    if (!p->fast_kernel || unsupported || ndense > kAsmMaxDense || p->asm_D > kAsmMaxDepth || p->asm_smem > (size_t)smem_optin || p->solve_smem > (size_t)smem_optin ||
+                        (rc2 = dev_upload(p, ev, &p->d_asm_events)) != BLFIK_OK ||
+                        cudaFuncSetAttribute((const void*)p->asm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) != cudaSuccess ||
+                        cudaFuncSetAttribute((const void*)p->solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->solve_smem) != cudaSuccess) {
+                        cudaGetLastError();
+                        p->solve_kernel = nullptr;
+                    }
+                }
             }
+            if (!p->fast_kernel) p->solve_kernel = nullptr;
         }
     }
 
@@ -1369,7 +1429,39 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
     P.packed_len = P.compact ? p->packed_len_c : p->packed_len;
     P.nu_host = nu_host, P.status_host = status_host;
     P.t0 = p->time;
-    if (p->fast_kernel && p->path == 0) {
+    if (p->solve_kernel && p->path == 0 && !P.dbg.H && !p->streaming_launch) {
+        // two launches per tick (blfik_split.cuh): K1 + K2 one thread per robot, K3 + K4 one warp per robot
+        if (!p->d_qp) {
+            int rc = dev_alloc(p, (size_t)p->N * p->rec_len, &p->d_qp, false);
+            if (rc) return rc;
+        }
+        AsmParams A;
+        A.T = P, A.qp = p->d_qp, A.rec_len = p->rec_len, A.K = p->K, A.off_c = p->rec_off_c, A.off_v = p->rec_off_v;
+        A.model_pack = p->d_model_pack, A.pack_len = p->pack_len;
+        A.sh_jump = p->F.sh_jump, A.sh_lod = p->F.sh_lod, A.sh_anc = p->F.sh_anc, A.sh_msub = p->F.sh_msub;
+        A.events = p->d_asm_events, A.nevents = p->asm_nevents;
+        SolveParams S;
+        S.T = P, S.qp = p->d_qp, S.prefetch_ahead = p->num_sms * 16, S.nv = p->nv, S.K = p->K;
+        for (int r = 0; r < 32; r++) S.evec[r] = 1.0;
+        for (const HostTask& h : p->tasks)
+            if (is_dense(h.d.type))
+                for (int r = 0; r < h.rows; r++) S.evec[h.brow + r] = h.d.priority == 0 ? 0.0 : 1.0 / h.weight[r];
+        S.max_as_iters = p->max_as_iters, S.max_polish_iters = p->max_polish_iters, S.max_total_iters = p->max_total_iters;
+        { const char* e = getenv("BLFIK_PDAS_FIRST"); S.pdas_first = e ? atoi(e) : 1; }
+        { const char* e = getenv("BLFIK_MAX_ITERS"); if (e) S.max_total_iters = atoi(e); }
+        { const char* e = getenv("BLFIK_MAX_AS"); if (e) S.max_as_iters = atoi(e); }
+        const int agrid = (int)((count + p->asm_threads - 1) / p->asm_threads), sgrid = (int)((count + p->solve_wpb - 1) / p->solve_wpb);
+        for (int tick = 0; tick < nticks; tick++) {
+            A.tick = S.tick = tick;
+            A.tnow = p->time + tick * dt;
+            p->asm_kernel<<<agrid, p->asm_threads, p->asm_smem, stream>>>(A);
+            p->solve_kernel<<<sgrid, p->solve_wpb * 32, p->solve_smem, stream>>>(S);
+            p->launches += 2;
+        }
+        CU(cudaGetLastError());
+        return BLFIK_OK;
+    }
+    if (p->fast_kernel && (p->path == 0 || p->path == 2)) {
         FastParams FP;
         FP.T = P, FP.F = p->F, FP.nv = p->nv, FP.K = p->K;
         FP.max_as_iters = p->max_as_iters, FP.max_polish_iters = p->max_polish_iters, FP.max_total_iters = p->max_total_iters;
@@ -1393,7 +1485,7 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
             FP.arrive_timeout = timeout_env;    // ~0.25 s of SM clocks (the whole transfer takes ~1 ms): copies and kernels are not overlapping
         }
         p->fast_kernel<<<(int)(want < p->fast_grid ? want : p->fast_grid), p->fast_wpb * 32, p->fast_smem, stream>>>(FP);
-    } else if (p->eq_kernel && p->path == 0 && !P.dbg.H) {   // the debug read-back wants H: the generic kernel forms it
+    } else if (p->eq_kernel && p->path != 1 && !P.dbg.H) {   // the debug read-back wants H: the generic kernel forms it
         P.L = p->Leq;
         const long long want = (count + p->eq_wpb - 1) / p->eq_wpb;
         blfik_tick_eq_kernel<<<(int)(want < p->eq_grid ? want : p->eq_grid), p->eq_wpb * 32, p->eq_smem, stream>>>(P);
@@ -1580,7 +1672,7 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     // launch of 65k).  Needs the register-resident kernel with dynamic hand-out, page-locked records (a pure DMA on the
     // copy stream) and mapped page-locked outputs.
     static const int streaming_env = [] { const char* e = getenv("BLFIK_STREAMING"); return e ? atoi(e) : 1; }();
-    if (streaming_env && !p->streaming_off && p->fast_kernel && p->path == 0 && p->work_counter && p->N < 0x7fffff00LL) {
+    if (streaming_env && !p->streaming_off && p->fast_kernel && (p->path == 2 || (p->path == 0 && !p->solve_kernel)) && p->work_counter && p->N < 0x7fffff00LL) {
         cudaPointerAttributes at;
         double* nu_dev = nullptr;
         int* st_dev = nullptr;
@@ -1734,7 +1826,7 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
 extern "C" int blfik_set_kernel_path(blfik_problem* p, int32_t path)
 {
     CHECK_P(p, "blfik_set_kernel_path");
-    if (path != 0 && path != 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_kernel_path] path must be 0 (auto) or 1 (generic kernel)");
+    if (path < 0 || path > 2) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_kernel_path] path must be 0 (auto), 1 (generic kernel) or 2 (fused register-resident kernel)");
     p->path = path;
     return BLFIK_OK;
 }
@@ -1742,7 +1834,9 @@ extern "C" int blfik_set_kernel_path(blfik_problem* p, int32_t path)
 extern "C" int32_t blfik_get_kernel_path(const blfik_problem* p)
 {
     if (!p) return -1;
-    return (p->fast_kernel && p->path == 0) ? 2 : ((p->eq_kernel && p->path == 0) ? 3 : 1);
+    if (p->path == 1) return 1;
+    if (p->solve_kernel && p->path == 0) return 4;
+    return p->fast_kernel ? 2 : (p->eq_kernel ? 3 : 1);
 }
 
 extern "C" int blfik_get_output(blfik_problem* p, double* nu, int32_t mem)

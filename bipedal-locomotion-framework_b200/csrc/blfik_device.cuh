@@ -503,7 +503,7 @@ __device__ __forceinline__ void expand_compact(const DevTask& tk, const double* 
 // that feed setSetPoint): x_d(t) = x_0 + A sin(w t + phi_i), feed-forward += A w cos(w t + phi_i); orientations move by
 // the world-frame rotation Exp(A_ang sin(.)) about a fixed axis, whose angular velocity is exactly A_ang w cos(.).
 // `spl` receives the full record (13 / 7 / 6 doubles); returns the pointer the control law should read.
-__device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long long robot, double t, const double* sp, double* spl);
+static __device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long long robot, double t, const double* sp, double* spl);
 // The generators are rare and long: the common case (none attached) stays a test and a branch, the evaluation itself is an
 // out-of-line call so that its registers do not weigh on the tick kernels.
 __device__ __forceinline__ const double* traj_eval(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
@@ -536,7 +536,7 @@ __device__ __forceinline__ void spline_eval(const DevTask& tk, long long robot, 
         spl[vo + k] = sp[vo + k] + c1 + tl * (2.0 * c2 + tl * (3.0 * c3 + tl * (4.0 * c4 + tl * 5.0 * c5)));
     }
 }
-__device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
+static __device__ __noinline__ const double* traj_eval_slow(const DevTask& tk, long long robot, double t, const double* sp, double* spl)
 {
     if ((tk.gen & 4) && !(tk.gen & 2)) {
         for (int c = 0; c < tk.fb_off && c < 13; c++) spl[c] = sp[c];

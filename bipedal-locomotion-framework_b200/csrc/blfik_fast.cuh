@@ -449,7 +449,7 @@ __device__ __forceinline__ bool fast_setup(const double* Bm, double* Us, double*
 // Column `lane` of the angular rows of the centroidal momentum matrix (AngularMomentumTask.cpp:137-185; same formula as
 // k1_angmom of the generic kernel): sum over the links distal to the DoF of I_k^W a + m_k (c_k - c) x (a x (c_k - o)).
 // Rare task, long loop: kept out of line so that its registers do not weigh on the tick kernel.
-__device__ __noinline__ void fast_angmom_column(const double* s_link, const double* inertia, const unsigned long long* s_anc,
+static __device__ __noinline__ void fast_angmom_column(const double* s_link, const double* inertia, const unsigned long long* s_anc,
                                                 const int* s_lod, const double* linkR, const double* linkP,
                                                 const double* axisW, const double* mcw, const double* com, int nl, int lane,
                                                 double* col)

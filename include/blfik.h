@@ -373,13 +373,16 @@ int blfik_sync(blfik_problem* problem);
 /* the problem's cudaStream_t (as void*); set_stream makes later work use the caller's stream */
 void* blfik_get_stream(blfik_problem* problem);
 int blfik_set_stream(blfik_problem* problem, void* cuda_stream);
-/* Three kernels implement the tick: a register-resident one for nv <= 32 velocity variables and <= 32
- * dense task rows (all ergoCub / iCub-26 configurations); one for wider problems (<= 64 dense rows: the
- * 32-joint iCubGazeboV2_5 configurations, with or without limit tasks), which keeps the QP in factored form;
- * and a generic shared-memory one for everything else.
- * path 0 = choose automatically (default), 1 = force the generic kernel (parity tests run both).
- * blfik_get_kernel_path returns 2 when the next tick runs the register-resident kernel, 3 for the
- * factored-form kernel, else 1.
+/* Four code paths implement the tick.  For nv <= 32 velocity variables and <= 32 dense task rows (all ergoCub /
+ * iCub-26 configurations): the two-launch path -- K1 + K2 one thread per robot, K3 + K4 one warp per robot, the QP of
+ * every robot handed over through device memory (blfik_split.cuh; allocates N x ~5.5 KB on the first tick) -- and the
+ * older fused register-resident kernel (one launch; also what the debug read-back and the zero-copy host tick use).  For
+ * wider problems (<= 64 dense rows: the 32-joint iCubGazeboV2_5 configurations, with or without limit tasks) a kernel
+ * that keeps the QP in factored form; and a generic shared-memory kernel for everything else.
+ * path 0 = choose automatically (default), 1 = force the generic kernel, 2 = prefer the fused register-resident kernel
+ * over the two-launch path (parity tests run all three).
+ * blfik_get_kernel_path returns what the next tick runs: 4 two-launch path, 2 fused register-resident kernel,
+ * 3 factored-form kernel, 1 generic kernel.
  * No reference counterpart (the reference has a single OSQP code path).                     */
 int blfik_set_kernel_path(blfik_problem* problem, int32_t path);
 int32_t blfik_get_kernel_path(const blfik_problem* problem);

@@ -21,15 +21,16 @@ GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 def make(w_model, tasks, N, path=0):
-    """path 0: automatic kernel choice (register-resident kernel when nv <= 32 and <= 32 dense rows);
-    path 1: force the generic shared-memory kernel.  Parity tests run both."""
+    """path 0: automatic kernel choice (the two-launch assemble / solve path when nv <= 32 and <= 32 dense rows, the
+    factored-form kernel for wider problems); path 1: force the generic shared-memory kernel; path 2: the fused
+    register-resident kernel where it applies.  Parity tests run all three."""
     model = capi.Model(w_model)
     prob = capi.Problem(model, tasks, N)
     prob.set_kernel_path(path)
     return model, prob
 
 
-PATHS = [0, 1]
+PATHS = [0, 1, 2]
 
 
 def oracle_box(o, C, l, u, me, n):
@@ -105,7 +106,7 @@ def test_k3_solution_vs_oracle(cid, N, path):
     w = W.config(cid)
     inp = W.synth_inputs(w, N, cid)
     model, prob = make(w.model, w.tasks, N, path)
-    assert prob.kernel_path == (1 if path == 1 else (2 if w.model.nv <= 32 else 3))   # C1 / C2: 38 variables, no inequality rows
+    assert prob.kernel_path == (1 if path == 1 else ((4 if path == 0 else 2) if w.model.nv <= 32 else 3))   # C1 / C2: 38 variables, no inequality rows
     prob.set_inputs(inp)
     prob.tick(1, w.dt)
     nu = prob.get_output()
@@ -571,9 +572,11 @@ w = W.config(3); N = 20000
 inp = W.synth_inputs(w, N, 3)
 model = capi.Model(w.model)
 ref = capi.Problem(model, w.tasks, N)
+ref.set_kernel_path(2)
 ref.set_inputs(inp); ref.tick(1, w.dt)
 nu_ref, st_ref = ref.get_output(), ref.get_status()[0]
 prob = capi.Problem(model, w.tasks, N)
+prob.set_kernel_path(2)   # the streaming-input mode belongs to the fused register-resident kernel
 rec = torch.from_numpy(prob.pack_inputs(inp)).pin_memory()
 for call in range(2):
     nu = torch.full((N, w.model.n + 6), -7.0, dtype=torch.float64).pin_memory()
@@ -852,7 +855,7 @@ def test_angular_momentum_task_vs_oracle(hard, path):
     rng = np.random.default_rng(8)
     sps = [inp.setpoints[2], inp.setpoints[1], inp.setpoints[0], rng.normal(0, 0.05, (N, 3)), inp.setpoints[6]]
     model, prob = make(m, tasks, N, path)
-    assert prob.kernel_path == (2 if path == 0 else 1)
+    assert prob.kernel_path == {0: 2, 1: 1, 2: 2}[path]   # an AngularMomentumTask keeps the fused kernel (the assemble kernel does not build its rows)
     prob.set_state(p0, q0, s0)
     for t, sp in enumerate(sps):
         prob.set_setpoint(t, sp)
@@ -895,6 +898,7 @@ from blf_b200 import capi, workloads as W
 w = W.config(3); N = 4096
 inp = W.synth_inputs(w, N, 3)
 prob = capi.Problem(capi.Model(w.model), w.tasks, N)
+prob.set_kernel_path(2)   # the streaming-input mode belongs to the fused register-resident kernel
 prob.set_inputs(inp)
 rec = torch.from_numpy(prob.pack_inputs(inp)).pin_memory()
 nu = torch.empty((N, w.model.n + 6), dtype=torch.float64).pin_memory()
@@ -974,6 +978,10 @@ def test_exogenous_feedback_vs_oracle(path):
     prob.set_setpoint(0, base[0] + 0.0)                  # re-setting the set-point leaves the feedback in place
     assert np.array_equal(check(records), nu)
     prob.debug_enable(False)
+    prob.tick(1, 0.01)                                   # the debug read-back runs the fused kernel: the same tick without it
+    nu_plain = prob.get_output()
+    assert np.abs(nu_plain - nu).max() <= 1e-8
+    nu = nu_plain
     # the packed host tick: feedback travels behind the set-point in the record
     rec = np.empty((N, prob.packed_record_len))
     rec[:, 0:3], rec[:, 3:7], rec[:, 7:7 + n] = p0, q0, s0

@@ -15,8 +15,9 @@ spec.loader.exec_module(nbl)
 
 def main():
     rep, so, kernel, units = sys.argv[1], sys.argv[2], sys.argv[3], float(sys.argv[4])
-    table = nbl.line_table(so, kernel)
-    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    mangled = sys.argv[5] if len(sys.argv) > 5 else kernel   # substring of the mangled name when `kernel` matches several instantiations
+    table = nbl.line_table(so, mangled)
+    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", f"regex:{kernel}", "-c", "1"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     hdr = rows[1]
     iA, iI, iS = hdr.index("Address"), hdr.index("Instructions Executed"), hdr.index("# Samples")

@@ -16,8 +16,9 @@ from collections import defaultdict
 def line_table(so, kernel):
     d = tempfile.mkdtemp()
     subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=d, capture_output=True)
-    cubin = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
-    txt = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(d, cubin)], capture_output=True, text=True).stdout.splitlines()
+    txt = []   # the library is built from several translation units: one cubin each
+    for cubin in sorted(f for f in os.listdir(d) if f.endswith(".cubin")):
+        txt += subprocess.run(["nvdisasm", "-g", "-c", os.path.join(d, cubin)], capture_output=True, text=True).stdout.splitlines()
     table, cur, inside = {}, None, False
     for ln in txt:
         if ln.startswith(".text."):
