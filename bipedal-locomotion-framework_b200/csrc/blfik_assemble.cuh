@@ -85,14 +85,26 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
     const unsigned valid = __ballot_sync(kFull, active);
     if (valid == 0u) return;
     double* wq = A.qp + (size_t)wfirst * A.rec_len;
-    // the 32 x LEN doubles the lanes have put into their tile rows go to doubles [off, off + LEN) of the 32 records
+    // The 32 x LEN doubles the lanes have put into their tile rows go to doubles [off, off + LEN) of the 32 records: sixteen
+    // lanes per robot write sixteen consecutive doubles (two robots per store instruction), and what is left of a row beyond
+    // a multiple of sixteen goes out lane by lane.
+    const int fl_e = lane & 15, fl_h = lane >> 4;
     auto flush = [&](int off, auto len_tag) {
         constexpr int LEN = decltype(len_tag)::value;
         __syncwarp();
-#pragma unroll 2
-        for (int idx = lane; idx < 32 * LEN; idx += 32) {
-            const int r = idx / LEN, e = idx - r * LEN;
-            if ((valid >> r) & 1u) wq[(size_t)r * A.rec_len + off + e] = tile[r * TS + e];
+#pragma unroll
+        for (int pass = 0; pass < LEN / 16; pass++) {
+            double* dst = wq + (size_t)fl_h * A.rec_len + off + 16 * pass + fl_e;
+            const double* src = tile + fl_h * TS + 16 * pass + fl_e;
+#pragma unroll 4
+            for (int rr = 0; rr < 32; rr += 2) {
+                if ((valid >> (rr + fl_h)) & 1u) *dst = *src;
+                dst += 2 * (size_t)A.rec_len, src += 2 * TS;
+            }
+        }
+        if (active) {
+#pragma unroll
+            for (int e = LEN / 16 * 16; e < LEN; e++) wq[(size_t)lane * A.rec_len + off + e] = trow[e];
         }
         __syncwarp();
     };
