@@ -162,11 +162,27 @@ def run_reference(args, rank: int, world: int) -> None:
 
 
 # ------------------------------------------------------------------ our arm
+def workload_plan(args, world: int):
+    """(config id, instances per GPU, scaling) of this run.  Default: C3, 65,536 instances PER GPU (weak), the line the driver
+    records.  BASELINE.json's other shapes: C2 4,096 instances on one GPU; C3 strong: 65,536 in total; C4 262,144 over 8 GPUs =
+    32,768 per GPU; C5 65,536 over 8 GPUs (8,192 per GPU), 1,000-tick closed-loop launches."""
+    cid = args.config
+    scaling = args.scaling or {2: "strong", 3: "weak", 4: "weak", 5: "strong"}[cid]
+    base = {2: 4096, 3: 65536, 4: 32768, 5: 65536}[cid]
+    if args.instances:
+        n_local = args.instances
+    elif scaling == "weak":
+        n_local = base
+    else:
+        n_local = max(1, base // world)
+    return cid, n_local, scaling
+
+
 def run_ours(args, rank: int, local_rank: int, world: int) -> None:
     import torch
     import torch.distributed as dist
     import blf_b200  # noqa: F401
-    from blf_b200 import capi, workloads as W
+    from blf_b200 import capi, workloads as W, tasks as T
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
@@ -174,73 +190,104 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
     if world > 1 and not dist.is_initialized():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    w = W.config(CONFIG_ID)
+    cid, n_local, scaling = workload_plan(args, world)
+    w = W.config(cid)
     n, nv = w.model.n, w.model.n + 6
-    n_local = args.instances
     n_global = n_local * world
     lo, hi = W.shard_range(n_global, rank, world)
     # global synthetic batch, sliced by instance range: data of instance i are independent of `world`
-    inputs = W.synth_inputs(w, n_global, CONFIG_ID).slice(lo, hi)
+    if args.inputs == "survey":   # SURVEY.md 8d as written: joints over the inner 80 % of their range, +-5 cm / +-0.1 rad, CoM +-3 cm
+        inputs = W.synth_inputs_survey(w, n_global, cid).slice(lo, hi)
+    else:
+        inputs = W.synth_inputs(w, n_global, cid).slice(lo, hi)
+    rollout = cid == 5
+    nticks = 1000 if rollout else 1
 
     model = capi.Model(w.model)
     prob = capi.Problem(model, w.tasks, n_local, device=local_rank)
     stream = torch.cuda.ExternalStream(prob.stream, device=local_rank)
-
     dev = torch.device("cuda", local_rank)
     d_state = [torch.from_numpy(a).to(dev) for a in (inputs.base_pos, inputs.base_quat, inputs.s)]
-    h_state = [torch.from_numpy(a).pin_memory() for a in (inputs.base_pos, inputs.base_quat, inputs.s)]
-    h_sp = [None if sp is None else torch.from_numpy(sp).pin_memory() for sp in inputs.setpoints]
     h_nu = torch.empty((n_local, nv), dtype=torch.float64).pin_memory()
     h_status = torch.empty(n_local, dtype=torch.int32).pin_memory()
     sp_doubles = sum(0 if sp is None else sp.shape[1] for sp in inputs.setpoints)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 
     prob.set_inputs(inputs)
+    if rollout:
+        # C5: "random SE3 target trajectories" generated on the device (sinusoids of 0.05 m / 0.1 rad, period 2 s,
+        # random phase), closed loop, warm-started, nothing crosses the host link inside a launch
+        rng = np.random.Generator(np.random.Philox(key=W.SEED + 50))
+        phases = rng.uniform(0.0, 2.0 * np.pi, size=(n_global, len(w.tasks)))[lo:hi]
+        for t, task in enumerate(w.tasks):
+            if task.type == T.TASK_SE3:
+                prob.set_setpoint_trajectory(t, [0.05, 0.05, 0.05, 0.1, 0.1, 0.1], 2.0, np.ascontiguousarray(phases[:, t]))
     prob.sync()
 
     def device_step():
+        prob.set_time(0.0)
         prob.set_state(*d_state)                       # device -> device restore of the initial state
-        prob.tick(1, w.dt, integrate=True, warm_start=False)
+        prob.tick(nticks, w.dt, integrate=True, warm_start=rollout)
 
-    # The set-points of this workload carry no feed-forward velocities ("feed-forward twist 0 (open loop)"), which is
-    # the reference's setSetPoint(pose) with its default zero velocity: the host records then hold the pose part only
-    # (BLFIK_TICK_NO_FEEDFORWARD).  pack_inputs(compact=True) refuses if any dropped entry is non-zero.
+    # Host records.  The set-points of the open-loop configs carry no feed-forward velocities ("feed-forward twist 0
+    # (open loop)"), which is the reference's setSetPoint(pose) with its default zero velocity: the records then hold the pose
+    # part only (BLFIK_TICK_NO_FEEDFORWARD; pack_inputs refuses if a dropped entry is non-zero).  A set-point that is the same
+    # vector for every robot -- the postural JointTrackingTask target, q_nominal -- is handed over once
+    # (blfik_set_setpoint_shared) and is not part of the records at all.
     compact = not args.full_records
+    shared = []
+    if not args.no_shared and not rollout:
+        for t, sp in enumerate(inputs.setpoints):
+            if sp is not None and w.tasks[t].type == T.TASK_JOINT_TRACKING and np.all(sp == sp[0]):
+                shared.append(t)
+    e2e_prob = capi.Problem(model, w.tasks, n_local, device=local_rank) if shared else prob
+    if shared:
+        e2e_prob.set_inputs(inputs)
+        for t in shared:
+            e2e_prob.set_setpoint_shared(t, inputs.setpoints[t][0])
     if compact:
         try:
-            packed_np = prob.pack_inputs(inputs, compact=True)
+            packed_np = e2e_prob.pack_inputs(inputs, compact=True)
         except ValueError:
             compact = False
     if not compact:
-        packed_np = prob.pack_inputs(inputs)
+        packed_np = e2e_prob.pack_inputs(inputs)
     h_packed = torch.from_numpy(packed_np).pin_memory()
 
     def e2e_step():
-        # the reference-facing call with HOST buffers: one packed record per robot (state + set-points) in, nu + status out.
-        # --chunks k >= 1: one persistent launch starts at once and consumes the records while the copy engine streams them
-        # in (it polls an arrival word that the copy stream raises after every piece) and writes nu / status straight into
-        # the pinned host buffers; --chunks 0: the kernel also reads the records over PCIe itself (zero-copy mode)
-        prob.tick_packed(h_packed, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False, nchunks=args.chunks, compact=compact)
+        if rollout:
+            # the closed-loop rollout has no per-tick host traffic by design; end to end = initial state in (pinned host ->
+            # device), the 1,000-tick launch, final state + last nu + status out
+            prob.set_time(0.0)
+            prob.set_state(inputs.base_pos, inputs.base_quat, inputs.s)
+            prob.tick(nticks, w.dt, integrate=True, warm_start=True)
+            prob.get_state()
+            prob.get_output(h_nu)
+            prob.get_status()
+        else:
+            # the reference-facing call with HOST buffers: one packed record per robot (state + set-points) in, nu + status out
+            e2e_prob.tick_packed(h_packed, h_nu, h_status, dt=w.dt, integrate=True, warm_start=False, nchunks=args.chunks, compact=compact)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(step_fn, steps):
+    def timed(step_fn, steps, st=stream):
         total = 0.0
         for _ in range(steps):
             flush.fill_(1)                            # evict L2 (126 MB) between steps, untimed
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
+            e0.record(st)
             step_fn()
-            e1.record(stream)
+            e1.record(st)
             e1.synchronize()
             total += e0.elapsed_time(e1)
         return total
 
-    for _ in range(max(3, args.warmup)):
+    steps = args.steps if not rollout else max(1, min(args.steps, 10))
+    for _ in range(max(3, args.warmup) if not rollout else 1):
         device_step()
     prob.sync()
 
@@ -249,27 +296,46 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         sampler.start()
     launches0 = prob.launch_count
     barrier()
-    ms_dev = timed(device_step, args.steps)
+    ms_dev = timed(device_step, steps)
     barrier()
     launches = prob.launch_count - launches0
     status, iters = prob.get_status()
     unsolved = int((status != 0).sum())
+    nu_dev = prob.get_output()
 
-    for _ in range(2):
+    # per-kernel durations of the two-launch path, CUDA events on the launching stream (a separate pass: the events sit
+    # between the kernels)
+    k_asm = k_solve = None
+    if prob.kernel_path == 4 and not rollout:
+        prob.kernel_timing(True)
+        ta, tb = [], []
+        for _ in range(min(steps, 20)):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            device_step()
+            a_ms, b_ms = prob.kernel_times()
+            ta.append(a_ms), tb.append(b_ms)
+        prob.kernel_timing(False)
+        k_asm, k_solve = float(np.mean(ta)), float(np.mean(tb))
+
+    e2e_stream = torch.cuda.ExternalStream(e2e_prob.stream, device=local_rank)
+    for _ in range(2 if not rollout else 1):
         e2e_step()
     barrier()
-    ms_e2e = timed(e2e_step, args.steps)
+    ms_e2e = timed(e2e_step, steps, e2e_stream)
     barrier()
     clocks = sampler.stop() if sampler else None
+    # the numbers the end-to-end path delivered, against the device-resident step's (same inputs, same cold start)
+    e2e_ok = bool(np.array_equal(h_status.numpy(), status)) and bool(np.array_equal(h_nu.numpy(), nu_dev))
 
-    t = torch.tensor([ms_dev, ms_e2e, float(unsolved)], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_dev, ms_e2e, float(unsolved), 0.0 if e2e_ok else 1.0], dtype=torch.float64, device=dev)
     if world > 1:
         tmax = t.clone()
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone()
         dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        ms_dev, ms_e2e, unsolved = float(tmax[0]), float(tmax[1]), int(tsum[2])
-    ticks_total = n_global * args.steps
+        ms_dev, ms_e2e, unsolved, e2e_ok = float(tmax[0]), float(tmax[1]), int(tsum[2]), float(tsum[3]) == 0.0
+    ticks_total = n_global * steps * nticks
 
     if rank == 0:
         fp64_peak = capi.measure_fp64_peak(local_rank, 300.0)
@@ -279,50 +345,70 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         except Exception:
             pass
         hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-        K = sum(t.rows(n) for t in w.tasks if t.type in (0, 1, 2, 6))
-        fast = prob.kernel_path in (2, 4)
-        flops_launch = algorithmic_flops_per_tick(n, prob.me, K, iters.astype(np.float64), fast, prob_settings["admm_iters"],
-                                                  prob_settings["polish_iters"])
-        kernel_ms = ms_dev / args.steps
+        K = sum(tk.rows(n) for tk in w.tasks if tk.type in (0, 1, 2, 6))
+        kp = prob.kernel_path
+        fast = kp in (2, 4)
+        it64 = iters.astype(np.float64) / nticks
+        flops_tick = algorithmic_flops_per_tick(n, prob.me, K, it64, fast, prob_settings["admm_iters"], prob_settings["polish_iters"])
+        flops_kin = (4000.0 + 60.0 * n + 6.0 * n) * n_local
+        step_ms = ms_dev / steps
+        if k_solve:   # the dominant kernel of the two-launch path: K3 + K4; its flops are the tick's minus kinematics / assembly
+            kernel_name, kernel_ms, flops_launch = f"blfik_solve_kernel<{nv},{18 if K <= 18 else 32}>", k_solve, flops_tick - flops_kin
+        else:
+            kernel_name = {1: "blfik_tick_kernel", 2: "blfik_tick_fast_kernel", 3: "blfik_tick_eq_kernel", 4: "blfik_solve_kernel"}[kp]
+            kernel_ms, flops_launch = step_ms / nticks, flops_tick
         achieved_tf = flops_launch / (kernel_ms * 1e-3) * 1e-12
-        bytes_launch = algorithmic_bytes_per_tick(n, sp_doubles) * n_local
+        bytes_tick = algorithmic_bytes_per_tick(n, sp_doubles) * n_local
         cores = os.cpu_count() or 1
-        cpu_sample = 4096 * cores   # 65,536 instances on a 16-core box: about 20 s of CPU work at the GPU run's accuracy
-        cpu_rate, cpu_bad = cpu_oracle_rate(w, inputs, min(cpu_sample, n_local), cores)
-        cpu_stock = cpu_oracle_rate(w, inputs, min(cpu_sample, n_local), cores, osqp_defaults=True)[0]
+        cpu_sample = min(4096 * cores, n_local)   # 65,536 instances on a 16-core box: about 20 s of CPU work at the GPU run's accuracy
+        cpu_rate, cpu_bad = cpu_oracle_rate(w, inputs, cpu_sample, cores)
+        cpu_stock = cpu_oracle_rate(w, inputs, cpu_sample, cores, osqp_defaults=True)[0]
+        # issue roofline: the warp-instructions of this step's kernels against what the schedulers can issue (4 per clock and SM)
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
         line = {
             "metric": METRIC, "value": ticks_total / (ms_dev * 1e-3), "unit": "ticks/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "C3: ergoCub-23 IK tick, CoM + 2xSE3 feet + JointLimits + JointVelocityLimits (priority 0, "
-                                   "m=107 reference rows) + SO3 chest + JointTracking (priority 1), then ForwardEuler",
-                       "instances_per_gpu": n_local, "instances_total": n_global, "dt": w.dt,
-                       "parallelism": f"instance-sharded x{world}, no collective", "warm_start": False,
+            "steps": steps, "warmup": max(3, args.warmup), "ms_per_step": ms_dev / steps,
+            "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"C{cid}: {w.description}" + (", 1,000-tick closed-loop launches (ForwardEuler on the device, "
+                                   "sinusoidal SE3 targets generated on the device, warm start)" if rollout else ", then ForwardEuler"),
+                       "config_id": cid, "instances_per_gpu": n_local, "instances_total": n_global, "ticks_per_step": nticks, "dt": w.dt,
+                       "inputs": ("SURVEY 8d distribution as written (joints over the inner 80 % of their range, +-5 cm / +-0.1 rad, CoM "
+                                  "+-3 cm)" if args.inputs == "survey" else "workloads.synth_inputs (nominal +-0.25 rad, +-3 cm / +-0.06 rad, CoM +-2 cm)"),
+                       "parallelism": f"instance-sharded x{world}, no collective", "warm_start": rollout,
                        "solver": prob_settings, "l2": "256 MiB write between steps (untimed) flushes the 126 MB L2",
-                       "unsolved_instances": unsolved,
-                       "host_records": ("compact: state + pose part of every set-point, feed-forward terms are zero and not sent "
-                                        f"({h_packed.shape[1] * 8} B per robot)" if compact else f"full ({h_packed.shape[1] * 8} B per robot)"),
-                       "host_tick": ("blfik_tick_packed, zero-copy (kernel reads pinned host records over PCIe)" if args.chunks <= 0 else
-                                     "blfik_tick_packed, streaming input: one persistent launch consumes the packed records while the copy "
-                                     "engine delivers them in 16 pieces (arrival word raised by stream memory operations), results written "
-                                     "to pinned host memory by the kernel")},
+                       "unsolved_instances": unsolved, "kernel_path": kp,
+                       "host_records": ("no per-tick host traffic (closed loop on the device)" if rollout else
+                                        (f"compact ({h_packed.shape[1] * 8} B per robot): state + pose part of every set-point" if compact
+                                         else f"full ({h_packed.shape[1] * 8} B per robot)") +
+                                        (f"; batch-shared set-points sent once, not per step: tasks {shared}" if shared else "")),
+                       "host_tick": ("initial state in, one 1,000-tick launch, final state + nu + status out" if rollout else
+                                     f"blfik_tick_packed, {args.chunks} pipeline chunks: record copies (copy engine), assemble + solve "
+                                     "kernels per chunk on alternating streams, results written to pinned host memory by the kernel")},
             "e2e": {"value": ticks_total / (ms_e2e * 1e-3), "unit": "ticks/s",
-                    "h2d_bytes_per_step": int(h_packed.numel() * 8),
-                    "d2h_bytes_per_step": int(n_local * (8 * nv + 4))},
+                    "h2d_bytes_per_step": int(h_packed.numel() * 8) if not rollout else int(n_local * (7 + n) * 8),
+                    "d2h_bytes_per_step": int(n_local * (8 * nv + 4)) + (int(n_local * (7 + n) * 8) if rollout else 0)},
+            "e2e_matches_device": e2e_ok if not rollout else None,
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": achieved_tf / fp64_peak if fp64_peak else None,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r1_v6_fast_kernel_ncu_summary.txt
-                         "traffic": 90.45e6 if (fast and n_local == 65536) else None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch of that kernel (profiles/r2_*_ncu_summary.txt)
+                         "traffic": NCU_TRAFFIC.get((kernel_name.split("<")[0], cid, n_local)),
                          "peak_source": "measured live by blfik_measure_fp64_peak (dependency-free DFMA loop); "
                                         "MEASURED_PEAKS.json has no FP64 figure",
-                         "kernel": "blfik_tick_fast_kernel<29,18>" if fast else "blfik_tick_kernel", "flops_per_launch": flops_launch,
-                         "mean_matvecs_per_tick": float(iters.mean()),
-                         "hbm": {"achieved": bytes_launch / (kernel_ms * 1e-3) * 1e-9, "peak": hbm_peak, "unit": "GB/s",
-                                 "frac": bytes_launch / (kernel_ms * 1e-3) * 1e-9 / hbm_peak, "peak_source": hbm_src,
-                                 "bytes_per_launch": bytes_launch}},
+                         "kernel": kernel_name, "kernel_ms": kernel_ms, "kernel_timing": "CUDA events on the launching stream around the kernel"
+                                   if k_solve else "CUDA events around the step", "flops_per_launch": flops_launch,
+                         "kernels_ms": {"blfik_assemble_kernel": k_asm, "blfik_solve_kernel": k_solve} if k_solve else None,
+                         "mean_matvecs_per_tick": float(it64.mean()),
+                         "whole_step": {"achieved": flops_tick / (step_ms / nticks * 1e-3) * 1e-12,
+                                        "frac": flops_tick / (step_ms / nticks * 1e-3) * 1e-12 / fp64_peak if fp64_peak else None},
+                         "issue": {"note": "warp-instructions of one step (ncu smsp__inst_executed.sum of both kernels, profiles/) over the "
+                                           "issue rate 4 x SMs x SM clock", "warp_instructions": NCU_INSTR.get((cid, n_local)),
+                                   "floor_ms": (NCU_INSTR[(cid, n_local)] / (4 * 148 * sm_mhz * 1e6) * 1e3) if (cid, n_local) in NCU_INSTR else None},
+                         "hbm": {"achieved": bytes_tick / (step_ms / nticks * 1e-3) * 1e-9, "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": bytes_tick / (step_ms / nticks * 1e-3) * 1e-9 / hbm_peak, "peak_source": hbm_src,
+                                 "bytes_per_launch": bytes_tick}},
             "cpu_baseline": {"value": cpu_rate, "unit": "ticks/s", "cores": cores, "kind": "port",
-                             "sample": f"{min(cpu_sample, n_local)} instances x 1 tick of the same workload, CPU oracle "
+                             "sample": f"{cpu_sample} instances x 1 tick of the same workload, CPU oracle "
                                        f"(eps 1e-7 + polish, cold start), {cpu_bad} unsolved",
                              "osqp_defaults_value": cpu_stock,
                              "osqp_defaults_note": "same sample at the settings the unmodified reference runs with (OSQP defaults: eps 1e-3, "
@@ -330,10 +416,16 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
             "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
+    if e2e_prob is not prob:
+        e2e_prob.close()
     prob.close()
     if world > 1:
         dist.destroy_process_group()
 
+
+# ncu captures of the shipped build (profiles/): DRAM bytes of one launch and warp-instructions of one step, keyed by workload
+NCU_TRAFFIC = {}
+NCU_INSTR = {}
 
 prob_settings = {"rho": 1.0, "sigma": 1e-2, "alpha": 1.6, "eps": 1e-7, "admm_iters": 10, "max_rounds": 8,
                  "polish_iters": 4, "eq_iters": 5}
@@ -345,7 +437,11 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--instances", type=int, default=PER_GPU_INSTANCES, help="instances per GPU")
+    ap.add_argument("--instances", type=int, default=0, help="instances per GPU (default: what the configuration prescribes)")
+    ap.add_argument("--config", type=int, default=CONFIG_ID, choices=[2, 3, 4, 5], help="BASELINE.json configuration (default 3, the headline)")
+    ap.add_argument("--scaling", default=None, choices=["weak", "strong"], help="weak: fixed instances per GPU; strong: fixed total (defaults per configuration)")
+    ap.add_argument("--inputs", default="default", choices=["default", "survey"], help="synthetic input distribution (survey: SURVEY.md 8d as written)")
+    ap.add_argument("--no-shared", action="store_true", help="host-buffer (e2e) tick: send the batch-shared set-points with every record")
     ap.add_argument("--full-records", action="store_true", help="host-buffer (e2e) tick: send full records (with the zero feed-forward terms) instead of compact ones")
     ap.add_argument("--chunks", type=int, default=5,
                     help="host-buffer (e2e) tick: k >= 1 = pipelined (pinned buffers: one persistent launch that consumes the records while the copy engine streams them in; otherwise k chunk launches); 0 = zero-copy, the kernel reads the records over PCIe itself")
@@ -358,10 +454,12 @@ def main() -> None:
         return
     if world == 1 and args.gpus > 1:
         # convenience: relaunch under torchrun, one rank per GPU
-        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+        cmd = ([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__),
                "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--instances", str(args.instances),
-               "--chunks", str(args.chunks)] + (["--full-records"] if args.full_records else [])
+               "--chunks", str(args.chunks), "--config", str(args.config), "--inputs", args.inputs] +
+               (["--scaling", args.scaling] if args.scaling else []) + (["--full-records"] if args.full_records else []) +
+               (["--no-shared"] if args.no_shared else []))
         raise SystemExit(subprocess.call(cmd))
     run_ours(args, rank, local_rank, world)
 

@@ -40,6 +40,7 @@ EXPORTS = [
     "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time", "blfik_set_limits",
     "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline", "blfik_set_setpoint_cubic_spline", "blfik_evaluate_setpoint",
     "blfik_packed_record_len_ex", "blfik_packed_offset_ex", "blfik_packed_part_len",
+    "blfik_set_setpoint_shared", "blfik_kernel_timing", "blfik_get_kernel_times",
 ]
 
 
@@ -258,6 +259,24 @@ class Problem:
         ptr, dev = _ptr(data)
         _check(self.L.blfik_set_setpoint(self.handle, int(task), ptr, MEM_DEVICE if dev else MEM_HOST))
 
+    def set_setpoint_shared(self, task: int, record):
+        """one set-point for every robot of the batch (a single record of setpoint_len doubles); the task then leaves the packed
+        host records.  set_setpoint goes back to one set-point per robot."""
+        r = _f64(np.asarray(record, dtype=np.float64).reshape(-1))
+        self.L.blfik_set_setpoint_shared.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+        _check(self.L.blfik_set_setpoint_shared(self.handle, int(task), r.ctypes.data, MEM_HOST))
+
+    def kernel_timing(self, enabled: bool = True):
+        self.L.blfik_kernel_timing.argtypes = [C.c_void_p, C.c_int32]
+        _check(self.L.blfik_kernel_timing(self.handle, int(bool(enabled))))
+
+    def kernel_times(self):
+        """(assemble ms, solve ms) of the last full-batch tick on the two-launch path (kernel_timing must be on)"""
+        a, b = C.c_double(0.0), C.c_double(0.0)
+        self.L.blfik_get_kernel_times.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        _check(self.L.blfik_get_kernel_times(self.handle, C.byref(a), C.byref(b)))
+        return float(a.value), float(b.value)
+
     def set_feedback(self, task: int, data):
         """exogenous feedback of an SE3 ([N,7] = p, q) or CoM ([N,3]) task created with the use_*_exogenous_feedback option"""
         ptr, dev = _ptr(data)
@@ -384,6 +403,8 @@ class Problem:
             if sp is None:
                 continue
             o = int(L.blfik_packed_offset_ex(self.handle, t, fl))
+            if o < 0:      # batch-shared set-point: not part of the records
+                continue
             if not compact:
                 rec[:, o:o + sp.shape[1]] = sp
                 continue

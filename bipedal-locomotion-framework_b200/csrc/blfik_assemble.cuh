@@ -123,7 +123,6 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
         for (int i = 0; i < 4; i++) bq[i] = pr[3 + i];
         for (int j = 0; j < n; j++) s[j] = pr[7 + j];
     }
-    const bool compact = P.packed && P.compact;
 
     // frame pose of the dense tasks attached to link k (pose R, p): control law -> right-hand sides, origin kept for the columns
     auto frames_on_link = [&](int k, const double* R, const double* p) {
@@ -138,6 +137,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
             for (int c = 0; c < 3; c++) pf[c] = p[c] + off[c], PF(mp[6], c) = pf[c];
             double spl[13];
             const double* recsp = task_record(P, tk, robot);
+            const bool compact = task_compact(P, tk);
             // the exogenous feedback sits behind the set-point: sp0[tk.fb_off + c] addresses it in both layouts
             const double* sp0 = compact ? recsp - (tk.fb_off - tk.base_c) : recsp;
             if (compact) {   // pose part only: the full record is rebuilt with zero feed-forward entries
@@ -270,6 +270,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
         if (mp[7] < 0 || tk.type != T_COM) continue;
         double spl[13];
         const double* recsp = task_record(P, tk, robot);
+        const bool compact = task_compact(P, tk);
         const double* sp0 = compact ? recsp - (tk.fb_off - tk.base_c) : recsp;
         if (compact) {
             expand_compact(tk, recsp, spl);
@@ -325,7 +326,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
                     if (s_map[8 * t + 7] >= 0) continue;
                     if (tk.type == T_JOINT_TRACKING) {
                         const double* sp = task_record(P, tk, robot);
-                        const double bj = (compact ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - sj);
+                        const double bj = (task_compact(P, tk) ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - sj);
                         if (tk.priority == 1) {
                             dh += tk.weight[j];
                             gd += tk.weight[j] * bj;

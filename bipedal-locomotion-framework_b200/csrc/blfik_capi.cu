@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(128) blfik_evaluate_setpoint_kernel(const DevT
     const long long robot = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (robot >= N) return;
     const DevTask& tk = tasks[t];
-    const double* sp = tk.setpoint + (size_t)robot * tk.sp_len;
+    const double* sp = tk.setpoint + (size_t)robot * tk.sp_stride;
     double spl[13];
     const double* use = traj_eval(tk, robot, time, sp, spl);
     for (int c = 0; c < tk.fb_off; c++) out[(size_t)robot * tk.fb_off + c] = use[c];
@@ -325,6 +325,7 @@ struct HostTask {
     int sp_nk = 0, sp_cap = 0;       // quintic-spline generator: knots in force (0: off), knots the buffers hold
     double *d_sp_times = nullptr, *d_sp_fac = nullptr, *d_sp_coef = nullptr;
     bool setpoint_set = false;
+    bool shared = false;             // batch-shared set-point: one record for all robots, not part of the packed records
     double* d_setpoint = nullptr;
     double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
 };
@@ -386,6 +387,8 @@ struct blfik_problem {
     int pack_len = 0, asm_threads = 128, asm_D = 0, asm_nevents = 0;
     int* d_asm_events = nullptr;
     double* d_qp = nullptr;          // [N][rec_len], allocated by the first tick that takes this path
+    bool timing = false;             // blfik_kernel_timing: events around the two kernels of the last full-batch tick
+    cudaEvent_t ev_t[3] = {nullptr, nullptr, nullptr};
     // pipelined host-buffer tick (blfik_tick_host)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     cudaStream_t chunk_stream[4] = {nullptr, nullptr, nullptr, nullptr};   // blfik_tick_packed: consecutive chunk kernels alternate, so one fills the SMs the other's tail leaves idle
@@ -482,6 +485,26 @@ static void pick_fast(blfik_problem* p)
     p->F = make_fast_layout<NV, KP>(p->n + 1);
     // the control-law buffer ([ntasks][12]) lives in the U region during K2
     // (it always fits: ntasks * 12 <= 32 * 12 <= NV * LDG for every instantiation with NV >= 29, KP >= 16)
+}
+
+static int base_compact_of(int type, int n);
+// Offsets of the tasks inside a packed input record, full and compact layout.  Tasks without a set-point and tasks whose
+// set-point is batch-shared take no room (offset -1).
+static void layout_packed(blfik_problem* p)
+{
+    const int n = p->n;
+    p->packed_len = p->packed_len_c = 7 + n;
+    for (HostTask& h : p->tasks) {
+        h.base_c = base_compact_of(h.d.type, n);
+        if (h.sp_len == 0 || h.shared) {
+            h.pk_off = h.pk_off_c = -1;
+            continue;
+        }
+        h.pk_off = p->packed_len;
+        p->packed_len += h.sp_len;
+        h.pk_off_c = p->packed_len_c;
+        p->packed_len_c += h.base_c + h.fb_len;
+    }
 }
 
 static int rows_of(const blfik_task_desc& d, int n)
@@ -680,6 +703,7 @@ static int refresh_tasks(blfik_problem* p)
         d.flink = 0, d.pk_off = h.pk_off, d.pk_off_c = h.pk_off_c, d.base_c = h.base_c;
         d.exo_pos = h.d.use_position_exogenous_feedback != 0, d.exo_ori = h.d.use_orientation_exogenous_feedback != 0;
         d.fb_off = h.sp_len - h.fb_len;
+        d.sp_stride = h.shared ? 0 : h.sp_len;
         d.traj_phase = h.d_traj_phase, d.traj_omega = h.d_traj_phase ? h.traj_omega : 0.0;
         for (int c = 0; c < 6; c++) d.traj_amp[c] = h.traj_amp[c];
         d.mj_target = h.mj_T > 0.0 ? h.d_mj_target : nullptr, d.mj_t0 = h.mj_t0, d.mj_T = h.mj_T;
@@ -789,14 +813,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         h.setpoint_set = h.sp_len == 0;
         p->tasks.push_back(std::move(h));
     }
-    p->packed_len = p->packed_len_c = 7 + n;
-    for (HostTask& h : p->tasks) {
-        h.pk_off = p->packed_len;
-        p->packed_len += h.sp_len;
-        h.base_c = base_compact_of(h.d.type, n);
-        h.pk_off_c = p->packed_len_c;
-        p->packed_len_c += h.sp_len ? h.base_c + h.fb_len : 0;
-    }
+    layout_packed(p);
     if (me > 64) return bail(fail(BLFIK_ERR_UNSUPPORTED, "[blfik_problem_create] more than 64 dense equality rows (%d)", me));
     p->me = me;
     p->L = make_layout(n, me);
@@ -1007,6 +1024,8 @@ extern "C" void blfik_problem_destroy(blfik_problem* p)
             if (p->chunk_stream[k]) cudaStreamSynchronize(p->chunk_stream[k]), cudaStreamDestroy(p->chunk_stream[k]);
     }
     if (p->h_stream_ctl) cudaFreeHost(p->h_stream_ctl);
+    for (int k = 0; k < 3; k++)
+        if (p->ev_t[k]) cudaEventDestroy(p->ev_t[k]);
     if (p->own_stream && p->stream) cudaStreamDestroy(p->stream);
     delete p;
 }
@@ -1073,10 +1092,34 @@ extern "C" int blfik_set_setpoint(blfik_problem* p, int32_t t, const double* dat
     if (h.sp_len == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint] task %d takes no set-point", t);
     if (!data) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint] null buffer");
     const int base = h.sp_len - h.fb_len;
+    if (h.shared) {   // back to one set-point per robot
+        h.shared = false;
+        layout_packed(p);
+        p->tasks_dirty = true;
+    }
     if (h.fb_len == 0)
         CU(cudaMemcpyAsync(h.d_setpoint, data, (size_t)p->N * h.sp_len * sizeof(double), kind_in(mem), p->stream));
     else   // the record is wider than the set-point: strided rows
         CU(cudaMemcpy2DAsync(h.d_setpoint, h.sp_len * sizeof(double), data, base * sizeof(double), base * sizeof(double), (size_t)p->N, kind_in(mem), p->stream));
+    h.setpoint_set = true;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_set_setpoint_shared(blfik_problem* p, int32_t t, const double* data, int32_t mem)
+{
+    CHECK_P(p, "blfik_set_setpoint_shared");
+    CHECK_TASK(p, t, "blfik_set_setpoint_shared");
+    HostTask& h = p->tasks[t];
+    if (h.sp_len == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_shared] task %d takes no set-point", t);
+    if (h.fb_len != 0) return fail(BLFIK_ERR_UNSUPPORTED, "[blfik_set_setpoint_shared] task %d carries an exogenous feedback per robot", t);
+    if (!data) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_shared] null buffer");
+    CU(cudaMemcpyAsync(h.d_setpoint, data, (size_t)h.sp_len * sizeof(double), kind_in(mem), p->stream));
+    if (mem == BLFIK_MEM_HOST) CU(cudaStreamSynchronize(p->stream));   // the caller's buffer may be pageable and short-lived
+    if (!h.shared) {
+        h.shared = true;
+        layout_packed(p);
+        p->tasks_dirty = true;
+    }
     h.setpoint_set = true;
     return BLFIK_OK;
 }
@@ -1454,8 +1497,12 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         for (int tick = 0; tick < nticks; tick++) {
             A.tick = S.tick = tick;
             A.tnow = p->time + tick * dt;
+            const bool timed = p->timing && tick == nticks - 1 && count == p->N;
+            if (timed) CU(cudaEventRecord(p->ev_t[0], stream));
             p->asm_kernel<<<agrid, p->asm_threads, p->asm_smem, stream>>>(A);
+            if (timed) CU(cudaEventRecord(p->ev_t[1], stream));
             p->solve_kernel<<<sgrid, p->solve_wpb * 32, p->solve_smem, stream>>>(S);
+            if (timed) CU(cudaEventRecord(p->ev_t[2], stream));
             p->launches += 2;
         }
         CU(cudaGetLastError());
@@ -1594,7 +1641,7 @@ extern "C" int32_t blfik_packed_offset_ex(const blfik_problem* p, int32_t task, 
 {
     if (!p) return -1;
     if (task < 0) return 0;
-    if (task >= (int)p->tasks.size() || p->tasks[task].sp_len == 0) return -1;
+    if (task >= (int)p->tasks.size() || p->tasks[task].sp_len == 0 || p->tasks[task].shared) return -1;
     return (flags & BLFIK_TICK_NO_FEEDFORWARD) ? p->tasks[task].pk_off_c : p->tasks[task].pk_off;
 }
 
@@ -1602,7 +1649,7 @@ extern "C" int32_t blfik_packed_part_len(const blfik_problem* p, int32_t task, u
 {
     if (!p || task < 0 || task >= (int)p->tasks.size()) return -1;
     const HostTask& h = p->tasks[task];
-    if (h.sp_len == 0) return 0;
+    if (h.sp_len == 0 || h.shared) return 0;
     return (flags & BLFIK_TICK_NO_FEEDFORWARD) ? h.base_c + h.fb_len : h.sp_len;
 }
 
@@ -1610,7 +1657,7 @@ extern "C" int32_t blfik_packed_offset(const blfik_problem* p, int32_t task)
 {
     if (!p) return -1;
     if (task < 0) return 0;   // the state: p(3) q(4) s(n)
-    if (task >= (int)p->tasks.size() || p->tasks[task].sp_len == 0) return -1;
+    if (task >= (int)p->tasks.size() || p->tasks[task].sp_len == 0 || p->tasks[task].shared) return -1;
     return p->tasks[task].pk_off;
 }
 
@@ -2114,6 +2161,28 @@ extern "C" int32_t blfik_num_dofs(const blfik_problem* p) { return p ? p->n : -1
 extern "C" int32_t blfik_num_equality_rows(const blfik_problem* p) { return p ? p->me : -1; }
 extern "C" int64_t blfik_num_instances(const blfik_problem* p) { return p ? p->N : -1; }
 extern "C" int64_t blfik_launch_count(const blfik_problem* p) { return p ? p->launches : -1; }
+
+extern "C" int blfik_kernel_timing(blfik_problem* p, int32_t enabled)
+{
+    CHECK_P(p, "blfik_kernel_timing");
+    if (enabled && !p->ev_t[0])
+        for (int k = 0; k < 3; k++) CU(cudaEventCreate(&p->ev_t[k]));
+    p->timing = enabled != 0;
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_get_kernel_times(blfik_problem* p, double* ms_assemble, double* ms_solve)
+{
+    CHECK_P(p, "blfik_get_kernel_times");
+    if (!p->timing || !p->solve_kernel || p->path != 0) return fail(BLFIK_ERR_NOT_READY, "[blfik_get_kernel_times] timing is off or the two-launch path is not in use");
+    CU(cudaEventSynchronize(p->ev_t[2]));
+    float a = 0.f, b = 0.f;
+    CU(cudaEventElapsedTime(&a, p->ev_t[0], p->ev_t[1]));
+    CU(cudaEventElapsedTime(&b, p->ev_t[1], p->ev_t[2]));
+    if (ms_assemble) *ms_assemble = a;
+    if (ms_solve) *ms_solve = b;
+    return BLFIK_OK;
+}
 
 extern "C" int blfik_sync(blfik_problem* p)
 {

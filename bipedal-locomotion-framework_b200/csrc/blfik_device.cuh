@@ -70,6 +70,7 @@ struct DevTask {
     double mj_t0, mj_T;
     int exo_pos, exo_ori;    // exogenous feedback (SE3Task.cpp:261-268, CoMTask.cpp:192-195): controller state from the record
     int fb_off;              // where the feedback p(3) [q(4)] sits inside the record (= the set-point length)
+    int sp_stride;           // doubles between consecutive robots in `setpoint`: sp_len, or 0 for a batch-shared set-point
     int gen;                 // attached set-point generators: 1 sinusoidal, 2 minimum jerk, 4 quintic spline (0: none)
     // optional multi-knot quintic spline for the linear part (Math::QuinticSpline, Spline.h / QuinticSpline.h): knot times
     // shared by the robots, one polynomial per interval and robot, coefficients [N][sp_nk - 1][6][3] in interval-local time
@@ -488,9 +489,12 @@ __device__ __forceinline__ void k1_angmom(const DevModel& m, const WM& w, const 
 // Record of task `tk` for `robot`: from a packed input record (full or compact layout) or from the task's own buffer.
 __device__ __forceinline__ const double* task_record(const TickParams& P, const DevTask& tk, long long robot)
 {
-    if (P.packed) return P.packed + (size_t)robot * P.packed_len + (P.compact ? tk.pk_off_c : tk.pk_off);
-    return tk.setpoint ? tk.setpoint + robot * tk.sp_len : nullptr;
+    // a batch-shared set-point (blfik_set_setpoint_shared) is not part of the packed records: pk_off < 0
+    if (P.packed && tk.pk_off >= 0) return P.packed + (size_t)robot * P.packed_len + (P.compact ? tk.pk_off_c : tk.pk_off);
+    return tk.setpoint ? tk.setpoint + robot * tk.sp_stride : nullptr;
 }
+// the record of this task comes from a packed array in the compact layout
+__device__ __forceinline__ bool task_compact(const TickParams& P, const DevTask& tk) { return P.packed && P.compact && tk.pk_off >= 0; }
 // Compact records carry only the pose part of a set-point (the reference's setSetPoint(pose) with its default zero
 // velocity); `out` receives the full dense record (<= 13 doubles) with the feed-forward entries zeroed.
 __device__ __forceinline__ void expand_compact(const DevTask& tk, const double* rec, double* out)
@@ -631,7 +635,7 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
     for (int t = 0; t < P.ntasks; t++) {
         const DevTask& tk = P.tasks[t];
         const double* sp = task_record(P, tk, robot);
-        const bool compact = P.packed && P.compact;
+        const bool compact = task_compact(P, tk);
         if (is_dense_type(tk.type)) {
             double bt[6], spl[13], spx[13];
             int src[6];

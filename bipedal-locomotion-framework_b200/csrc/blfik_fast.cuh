@@ -728,7 +728,7 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                 if (dense) {
                     double spl[13];
                     const double* rec = task_record(P, tk, robot);
-                    const bool compact = P.packed && P.compact;
+                    const bool compact = task_compact(P, tk);
                     // the exogenous feedback sits behind the set-point: sp0[tk.fb_off + c] addresses it in both layouts
                     const double* sp0 = compact ? rec - (tk.fb_off - tk.base_c) : rec;
                     if (compact) {   // pose part only: the full record is rebuilt with zero feed-forward entries
@@ -885,7 +885,7 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                     const double* sp = task_record(P, tk, robot);
                     const int j = lane - 6;
                     if (tk.type == T_JOINT_TRACKING) {
-                        const double bj = ((P.packed && P.compact) ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - sj);
+                        const double bj = (task_compact(P, tk) ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - sj);
                         if (tk.priority == 1) {
                             dh += tk.weight[j];
                             gd += tk.weight[j] * bj;

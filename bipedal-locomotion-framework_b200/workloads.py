@@ -200,6 +200,42 @@ def synth_inputs(w: Workload, N: int, cid: int = 0, seed: int = SEED, jr: float 
                   [None if sp is None else np.ascontiguousarray(sp) for sp in sps])
 
 
+def synth_inputs_survey(w: Workload, N: int, cid: int = 0, seed: int = SEED) -> Inputs:
+    """The distribution of SURVEY.md 8d as written: s ~ U(s- + 0.1 d, s+ - 0.1 d) per joint, frame targets = current pose o
+    (dp ~ U(-5 cm, 5 cm)^3, dR = exp(U(-0.1, 0.1)^3)), CoM target = current CoM + U(-3 cm, 3 cm)^3.  Harder than synth_inputs: a
+    larger share of the instances sits at a velocity limit or is infeasible under them."""
+    m = w.model
+    rng = np.random.Generator(np.random.Philox(key=seed + 100 + cid))
+    d = m.q_upper - m.q_lower
+    s = m.q_lower + (0.1 + 0.8 * rng.uniform(size=(N, m.n))) * d
+    base = synth_inputs(w, N, cid, seed=seed, jr=0.0, pr=0.05, ar=0.1, cr=0.03)   # draws p, q and the deltas; the targets are rebuilt below
+    p, q = base.base_pos, base.base_quat
+    link_R, link_p = fk_batch(m, p, q, s)
+    sps: List[Optional[np.ndarray]] = []
+    for t in w.tasks:
+        if t.type in (T.TASK_SE3, T.TASK_SO3, T.TASK_R3):
+            Rf, pf = frame_pose_batch(m, link_R, link_p, t.frame)
+            dq = so3_exp(rng.uniform(-0.1, 0.1, size=(N, 3)))
+            dp = rng.uniform(-0.05, 0.05, size=(N, 3))
+            qd = quat_mul(rot_to_quat(Rf), dq)
+            pd = pf + np.einsum("nij,nj->ni", Rf, dp)
+            if t.type == T.TASK_SE3:
+                sps.append(np.concatenate([pd, qd, np.zeros((N, 6))], axis=1))
+            elif t.type == T.TASK_SO3:
+                sps.append(np.concatenate([qd, np.zeros((N, 3))], axis=1))
+            else:
+                sps.append(np.concatenate([pd, np.zeros((N, 3))], axis=1))
+        elif t.type == T.TASK_COM:
+            c = com_batch(m, link_R, link_p)
+            sps.append(np.concatenate([c + rng.uniform(-0.03, 0.03, size=(N, 3)), np.zeros((N, 3))], axis=1))
+        elif t.type == T.TASK_JOINT_TRACKING:
+            sps.append(np.concatenate([np.broadcast_to(m.q_nominal, (N, m.n)), np.zeros((N, m.n))], axis=1))
+        else:
+            sps.append(None)
+    return Inputs(np.ascontiguousarray(p), np.ascontiguousarray(q), np.ascontiguousarray(s),
+                  [None if sp is None else np.ascontiguousarray(sp) for sp in sps])
+
+
 def shard_range(N: int, rank: int, world: int) -> Tuple[int, int]:
     """Contiguous block of instance indices owned by ``rank``."""
     return (N * rank) // world, (N * (rank + 1)) // world

@@ -296,6 +296,13 @@ int32_t blfik_packed_offset_ex(const blfik_problem* problem, int32_t task, uint3
 int32_t blfik_packed_part_len(const blfik_problem* problem, int32_t task, uint32_t flags);
 int blfik_tick_packed(blfik_problem* problem, const double* records, double* nu, int32_t* status,
                       double dt, uint32_t flags, int32_t nchunks);
+/* A set-point that is the same for every robot of the batch (one record of blfik_setpoint_len doubles): what a caller
+ * gets in the reference by handing the same vector to every instance's setSetPoint, e.g. the postural
+ * JointTrackingTask::setSetPoint(jointPosition) of a regularisation task (JointTrackingTask.cpp:157-160).  The task then
+ * reads that one record for all robots, and it leaves the packed host records (blfik_packed_offset returns -1 for it and
+ * blfik_packed_record_len shrinks): for ergoCub C3 the postural set-point is 184 of the 592 bytes a compact record holds.
+ * blfik_set_setpoint on the task goes back to one set-point per robot.  Not available for tasks with exogenous feedback. */
+int blfik_set_setpoint_shared(blfik_problem* problem, int32_t task, const double* data, int32_t mem);
 
 /* replaces QPInverseKinematics::getOutput() (QPInverseKinematics.cpp:553-556): nu [N][6+n] =
  * [base linear; base angular; joint velocity] per robot                                 */
@@ -386,6 +393,11 @@ int blfik_set_stream(blfik_problem* problem, void* cuda_stream);
  * No reference counterpart (the reference has a single OSQP code path).                     */
 int blfik_set_kernel_path(blfik_problem* problem, int32_t path);
 int32_t blfik_get_kernel_path(const blfik_problem* problem);
+/* Measurement utility (no reference counterpart): with timing enabled, the last full-batch blfik_tick on the two-launch
+ * path is bracketed by CUDA events on the problem's stream; blfik_get_kernel_times waits for it and returns the duration
+ * of the assemble kernel (K1 + K2) and of the solve kernel (K3 + K4) in milliseconds.  bench.py's roofline uses it.   */
+int blfik_kernel_timing(blfik_problem* problem, int32_t enabled);
+int blfik_get_kernel_times(blfik_problem* problem, double* ms_assemble, double* ms_solve);
 /* number of kernel launches issued so far by this problem                                */
 int64_t blfik_launch_count(const blfik_problem* problem);
 const char* blfik_last_error(void);
