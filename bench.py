@@ -443,7 +443,7 @@ def main() -> None:
     ap.add_argument("--inputs", default="default", choices=["default", "survey"], help="synthetic input distribution (survey: SURVEY.md 8d as written)")
     ap.add_argument("--no-shared", action="store_true", help="host-buffer (e2e) tick: send the batch-shared set-points with every record")
     ap.add_argument("--full-records", action="store_true", help="host-buffer (e2e) tick: send full records (with the zero feed-forward terms) instead of compact ones")
-    ap.add_argument("--chunks", type=int, default=5,
+    ap.add_argument("--chunks", type=int, default=8,
                     help="host-buffer (e2e) tick: k >= 1 = pipelined (pinned buffers: one persistent launch that consumes the records while the copy engine streams them in; otherwise k chunk launches); 0 = zero-copy, the kernel reads the records over PCIe itself")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

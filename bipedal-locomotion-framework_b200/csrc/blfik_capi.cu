@@ -391,6 +391,8 @@ struct blfik_problem {
     cudaEvent_t ev_t[3] = {nullptr, nullptr, nullptr};
     // pipelined host-buffer tick (blfik_tick_host)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+    cudaStream_t asm_stream[4] = {nullptr, nullptr, nullptr, nullptr};     // blfik_tick_packed on the two-launch path: high-priority streams of the assemble kernels
+    cudaEvent_t ev_asm[16] = {};
     cudaStream_t chunk_stream[4] = {nullptr, nullptr, nullptr, nullptr};   // blfik_tick_packed: consecutive chunk kernels alternate, so one fills the SMs the other's tail leaves idle
     cudaEvent_t ev_in[16] = {}, ev_done[16] = {}, ev_start = nullptr;
     double time = 0.0;               // time of the next tick (advanced by integrating ticks; set-point trajectories)
@@ -1022,6 +1024,10 @@ extern "C" void blfik_problem_destroy(blfik_problem* p)
         cudaStreamDestroy(p->h2d_stream), cudaStreamDestroy(p->d2h_stream);
         for (int k = 0; k < 4; k++)
             if (p->chunk_stream[k]) cudaStreamSynchronize(p->chunk_stream[k]), cudaStreamDestroy(p->chunk_stream[k]);
+        for (int k = 0; k < 4; k++)
+            if (p->asm_stream[k]) cudaStreamSynchronize(p->asm_stream[k]), cudaStreamDestroy(p->asm_stream[k]);
+        for (int c = 0; c < kMaxChunks; c++)
+            if (p->ev_asm[c]) cudaEventDestroy(p->ev_asm[c]);
     }
     if (p->h_stream_ctl) cudaFreeHost(p->h_stream_ctl);
     for (int k = 0; k < 3; k++)
@@ -1459,7 +1465,7 @@ extern "C" int blfik_debug_get(blfik_problem* p, int32_t what, double* out, int3
 // one launch of the tick over robots [first, first + count) on `stream`
 static int launch_tick_range(blfik_problem* p, long long first, long long count, int32_t nticks, double dt, uint32_t flags, cudaStream_t stream,
                              const double* packed = nullptr, double* nu_host = nullptr, int* status_host = nullptr, int counter_slot = 0,
-                             bool counter_zeroed = false)
+                             bool counter_zeroed = false, cudaStream_t asm_stream = nullptr, cudaEvent_t asm_done = nullptr)
 {
     TickParams P;
     P.m = p->dm, P.tasks = p->d_tasks, P.ntasks = (int)p->tasks.size(), P.first = first, P.N = first + count;   // robots [first, N)
@@ -1499,7 +1505,16 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
             A.tnow = p->time + tick * dt;
             const bool timed = p->timing && tick == nticks - 1 && count == p->N;
             if (timed) CU(cudaEventRecord(p->ev_t[0], stream));
-            p->asm_kernel<<<agrid, p->asm_threads, p->asm_smem, stream>>>(A);
+            if (asm_stream && asm_done) {
+                // Host-tick pipeline: the assemble kernel of this chunk runs on a high-priority stream, so that its few blocks
+                // are scheduled ahead of the solve blocks of the previous chunks (its duration is the latency of one thread's
+                // walk, whatever the chunk size: it must overlap the other chunks' work, not queue behind it)
+                p->asm_kernel<<<agrid, p->asm_threads, p->asm_smem, asm_stream>>>(A);
+                CU(cudaEventRecord(asm_done, asm_stream));
+                CU(cudaStreamWaitEvent(stream, asm_done, 0));
+            } else {
+                p->asm_kernel<<<agrid, p->asm_threads, p->asm_smem, stream>>>(A);
+            }
             if (timed) CU(cudaEventRecord(p->ev_t[1], stream));
             p->solve_kernel<<<sgrid, p->solve_wpb * 32, p->solve_smem, stream>>>(S);
             if (timed) CU(cudaEventRecord(p->ev_t[2], stream));
@@ -1820,7 +1835,10 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
             else cudaGetLastError(), nu_map = nullptr;
         }
     }
-    static const int nstreams = [] { const char* e = getenv("BLFIK_CHUNK_STREAMS"); int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > 4 ? 4 : v); }();
+    // solve kernels of consecutive chunks alternate over these streams; measured on C3 (two-launch path, 8 chunks): 38.5 M
+    // ticks/s with 2 streams, 47.7 M with 4 (a chunk's solve must not queue behind an earlier chunk's assemble latency)
+    static const int nstreams_env = [] { const char* e = getenv("BLFIK_CHUNK_STREAMS"); int v = e ? atoi(e) : 0; return v < 0 ? 0 : (v > 4 ? 4 : v); }();
+    const int nstreams = nstreams_env ? nstreams_env : ((p->solve_kernel && p->path == 0) ? 4 : 2);
     for (int k = 0; k < nstreams; k++) {
         if (!p->chunk_stream[k]) CU(cudaStreamCreateWithFlags(&p->chunk_stream[k], cudaStreamNonBlocking));
         CU(cudaStreamWaitEvent(p->chunk_stream[k], p->ev_start, 0));
@@ -1833,8 +1851,24 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
         for (int c = 0; c < nchunks; c++) { CU(cudaEventCreate(&tr_in[c])); CU(cudaEventCreate(&tr_k0[c])); CU(cudaEventCreate(&tr_k1[c])); }
         CU(cudaEventRecord(tr_start, p->h2d_stream));
     }
-    // the first chunk is half the size of the others: nothing can run until it has arrived
-    auto bound = [&](int c) { return c <= 0 ? 0LL : (c >= nchunks ? p->N : p->N * (2 * c - 1) / (2 * nchunks - 1)); };
+    const bool split = p->solve_kernel && p->path == 0 && !p->debug;
+    if (split && !p->asm_stream[0]) {
+        int lo_pri = 0, hi_pri = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+        for (int k = 0; k < 4; k++) CU(cudaStreamCreateWithPriority(&p->asm_stream[k], cudaStreamNonBlocking, hi_pri));
+        for (int c = 0; c < kMaxChunks; c++) CU(cudaEventCreateWithFlags(&p->ev_asm[c], cudaEventDisableTiming));
+    }
+    // The first chunk is half the size of the others: nothing can run until it has arrived.  On the two-launch path the last
+    // chunks shrink as well (what runs after the final copy is one assemble latency plus the last chunk's solve).
+    auto bound = [&](int c) {
+        if (c <= 0) return 0LL;
+        if (c >= nchunks) return (long long)p->N;
+        if (split && nchunks >= 4) {
+            const double f = (double)c / nchunks;
+            return (long long)((double)p->N * f * f * (3.0 - 2.0 * f)) & ~15LL;   // smoothstep, on multiples of 16 robots
+        }
+        return p->N * (2 * c - 1) / (2 * nchunks - 1);
+    };
     for (int c = 0; c < nchunks; c++) {
         const long long a = bound(c), b = bound(c + 1), cnt = b - a;
         if (cnt <= 0) continue;
@@ -1844,7 +1878,10 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
         CU(cudaStreamWaitEvent(cs, p->ev_in[c], 0));
         if (trace) CU(cudaEventRecord(tr_in[c], p->h2d_stream));
         if (trace) CU(cudaEventRecord(tr_k0[c], cs));
-        if ((rc = launch_tick_range(p, a, cnt, 1, dt, flags, cs, p->d_packed, nu_map, status_map, c % kCounterSlots, true))) return rc;
+        if (split) CU(cudaStreamWaitEvent(p->asm_stream[c % 4], p->ev_in[c], 0));
+        if ((rc = launch_tick_range(p, a, cnt, 1, dt, flags, cs, p->d_packed, nu_map, status_map, c % kCounterSlots, true,
+                                    split ? p->asm_stream[c % 4] : nullptr, split ? p->ev_asm[c] : nullptr)))
+            return rc;
         if (trace) CU(cudaEventRecord(tr_k1[c], cs));
         CU(cudaEventRecord(p->ev_done[c], cs));
         CU(cudaStreamWaitEvent(p->stream, p->ev_done[c], 0));   // later work on the problem's stream is ordered after every chunk

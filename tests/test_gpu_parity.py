@@ -1805,3 +1805,49 @@ def test_equality_only_kernel_on_wide_models(seed):
         assert np.array_equal(res[0][1], one.get_status()[0]) and np.abs(res[0][0] - one.get_output())[res[0][1] == 0].max() < 1e-12
         one.close()
     prob.close(), whole.close(), packed.close()
+
+
+def test_batch_shared_setpoint_equals_per_robot_setpoints():
+    """blfik_set_setpoint_shared: one record for the whole batch gives bit-identical results to the same record repeated for
+    every robot, in the plain tick and in the packed host tick (full and compact records, where the shared task has left the
+    record); set_setpoint brings the per-robot set-point back."""
+    w = W.config(3)
+    N = 1500
+    inp = W.synth_inputs(w, N, 3)
+    model = capi.Model(w.model)
+    t_reg = 6
+    assert w.tasks[t_reg].type == T.TASK_JOINT_TRACKING and np.all(inp.setpoints[t_reg] == inp.setpoints[t_reg][0])
+    for path in PATHS:
+        ref = capi.Problem(model, w.tasks, N)
+        ref.set_kernel_path(path)
+        ref.set_inputs(inp)
+        ref.tick(1, w.dt, integrate=True)
+        nu_ref, (st_ref, _), state_ref = ref.get_output(), ref.get_status(), ref.get_state()
+        ref.close()
+        prob = capi.Problem(model, w.tasks, N)
+        prob.set_kernel_path(path)
+        full_len = prob.packed_record_len
+        prob.set_inputs(inp)
+        prob.set_setpoint_shared(t_reg, inp.setpoints[t_reg][0])
+        assert prob.packed_offset(t_reg) == -1 and prob.packed_record_len == full_len - 2 * w.model.n
+        prob.tick(1, w.dt, integrate=True)
+        assert np.array_equal(prob.get_output(), nu_ref) and np.array_equal(prob.get_status()[0], st_ref), path
+        for compact in (False, True):
+            rec = prob.pack_inputs(inp, compact=compact)
+            assert rec.shape[1] == (7 + 23 + 7 + 7 + 3 + 4 if compact else full_len - 2 * w.model.n)
+            nu, st = np.empty((N, w.model.nv)), np.empty(N, dtype=np.int32)
+            prob.tick_packed(rec, nu, st, dt=w.dt, integrate=True, nchunks=3, compact=compact)
+            assert np.array_equal(nu, nu_ref) and np.array_equal(st, st_ref), (path, compact)
+            for a, b in zip(prob.get_state(), state_ref):
+                assert np.array_equal(a, b)
+        # a different shared record changes the answer; the per-robot set-point comes back with set_setpoint
+        prob.set_state(inp.base_pos, inp.base_quat, inp.s)
+        prob.set_setpoint_shared(t_reg, inp.setpoints[t_reg][0] + 0.05)
+        prob.tick(1, w.dt)
+        assert np.abs(prob.get_output() - nu_ref).max() > 1e-3
+        prob.set_setpoint(t_reg, inp.setpoints[t_reg])
+        assert prob.packed_record_len == full_len
+        prob.set_state(inp.base_pos, inp.base_quat, inp.s)
+        prob.tick(1, w.dt, integrate=True)
+        assert np.array_equal(prob.get_output(), nu_ref)
+        prob.close()
