@@ -161,6 +161,42 @@ def run_reference(args, rank: int, world: int) -> None:
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------ the reference-named C++ call
+def host_api_leg(w, inputs, devices, steps, warmup, compact, nu_ref=None, status_ref=None, warm_start=False):
+    """C3 through QPInverseKinematics::advance() of the C++ host layer (bipedal-locomotion-framework_b200/host/bench/host_bench.cpp):
+    a single process drives all `devices`; the batch of `inputs` is what it is given (the caller sizes it)."""
+    import tempfile
+    host = os.path.join(ROOT, "bipedal-locomotion-framework_b200", "host")
+    exe = os.path.join(host, "bench", "host_bench")
+    model_file = os.path.join(ROOT, "tests", "golden", "ergocub23.model.txt")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", host, "-s"])
+    sp = inputs.setpoints
+    order = [0, 1, 2, 5, 6]   # CoM, right foot, left foot, chest, postural (workloads.config(3) task indices)
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "inputs.bin"), os.path.join(td, "nu.bin")
+        with open(fin, "wb") as f:
+            np.array([inputs.base_pos.shape[0], w.model.n], dtype=np.int64).tofile(f)
+            for a in [inputs.base_pos, inputs.base_quat, inputs.s] + [sp[t] for t in order]:
+                np.ascontiguousarray(a, dtype=np.float64).tofile(f)
+        r = subprocess.run([exe, model_file, fin, str(steps), str(warmup), ",".join(str(d) for d in devices), "1" if compact else "0", "1" if warm_start else "0", fout],
+                           capture_output=True, text=True, timeout=1200)
+        if r.returncode != 0:
+            return {"error": f"host_bench exited with {r.returncode}: {(r.stdout + r.stderr)[-400:]}"}
+        out = json.loads(r.stdout.strip().splitlines()[-1])
+        if nu_ref is not None:
+            N, nv = nu_ref.shape
+            raw = np.fromfile(fout, dtype=np.uint8)
+            nu = raw[:N * nv * 8].view(np.float64).reshape(N, nv)
+            st = raw[N * nv * 8:].view(np.int32)
+            ok = (st == 0) & (status_ref == 0)
+            # the C++ layer adds the tasks in the order of its parameter file, so the rows of the QP are permuted: same optimum,
+            # different rounding
+            out["status_matches_device"] = bool(np.array_equal(st, status_ref))
+            out["max_abs_dnu_vs_device"] = float(np.abs(nu - nu_ref)[ok].max()) if ok.any() else None
+    return out
+
+
 # ------------------------------------------------------------------ our arm
 def workload_plan(args, world: int):
     """(config id, instances per GPU, scaling) of this run.  Default: C3, 65,536 instances PER GPU (weak), the line the driver
@@ -415,6 +451,12 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
                                                    "no polish), looser than the accuracy this run is held to"},
             "clocks": clocks,
         }
+        if cid == 3 and world == 1 and not args.no_host_leg:
+            # the same step through the reference-named C++ call (one process, one device here; `--via host --gpus N` for more)
+            try:
+                line["e2e_host_api"] = host_api_leg(w, inputs, [local_rank], min(steps, 20), 3, compact, nu_dev, status)
+            except Exception as e:   # the leg is an extra: never let it take the line down
+                line["e2e_host_api"] = {"error": repr(e)}
         print(json.dumps(line), flush=True)
     if e2e_prob is not prob:
         e2e_prob.close()
@@ -441,6 +483,8 @@ def main() -> None:
     ap.add_argument("--config", type=int, default=CONFIG_ID, choices=[2, 3, 4, 5], help="BASELINE.json configuration (default 3, the headline)")
     ap.add_argument("--scaling", default=None, choices=["weak", "strong"], help="weak: fixed instances per GPU; strong: fixed total (defaults per configuration)")
     ap.add_argument("--inputs", default="default", choices=["default", "survey"], help="synthetic input distribution (survey: SURVEY.md 8d as written)")
+    ap.add_argument("--no-host-leg", action="store_true", help="skip the extra leg through the C++ QPInverseKinematics::advance()")
+    ap.add_argument("--via", default="capi", choices=["capi", "host"], help="host: time ONLY the C++ host-layer call, one process driving --gpus devices (weak: 65,536 instances per GPU)")
     ap.add_argument("--no-shared", action="store_true", help="host-buffer (e2e) tick: send the batch-shared set-points with every record")
     ap.add_argument("--full-records", action="store_true", help="host-buffer (e2e) tick: send full records (with the zero feed-forward terms) instead of compact ones")
     ap.add_argument("--chunks", type=int, default=8,
@@ -451,6 +495,19 @@ def main() -> None:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.via == "host":
+        if rank == 0:
+            import blf_b200  # noqa: F401
+            from blf_b200 import workloads as W
+            w = W.config(3)
+            per = args.instances or PER_GPU_INSTANCES
+            inputs = W.synth_inputs(w, per * args.gpus, 3)
+            out = host_api_leg(w, inputs, list(range(args.gpus)), args.steps, max(3, args.warmup), not args.full_records)
+            out.update({"metric": METRIC, "unit": "ticks/s", "value": out.get("ticks_per_s"), "n_gpus": args.gpus, "scaling": "weak",
+                        "config": {"workload": "C3 through QPInverseKinematics::advance() (C++ host layer), one process, one host thread and one "
+                                               "blfik_problem per GPU, contiguous instance blocks", "instances_per_gpu": per}})
+            print(json.dumps(out), flush=True)
         return
     if world == 1 and args.gpus > 1:
         # convenience: relaunch under torchrun, one rank per GPU

@@ -854,9 +854,12 @@ class QPInverseKinematics:
         except capi.BlfikError as err:
             log().error("%s %s", prefix, err)
             return False
-        if np.any(self._status != 0):
-            log().error("%s osqp was not able to find a feasible solution for %d of %d robots.", prefix, int(np.sum(self._status != 0)), kd.N)   # :518-523
+        failed = int(np.sum(self._status == 2))   # Solved and SolvedInaccurate are accepted (:518-523)
+        if failed and kd.N == 1:
+            log().error("%s osqp was not able to find a feasible solution.", prefix)
             return False
+        if failed:   # a batch is not all-or-nothing: the call succeeded, each robot answers for itself (is_output_valid(i))
+            log().warning("%s osqp was not able to find a feasible solution for %d of %d robots.", prefix, failed, kd.N)
         self._state.base_velocity = manif.SE3Tangent(self._nu[0, :6])
         self._state.joint_velocity = self._nu[0, 6:].copy()
         self._output_valid = True
@@ -865,8 +868,11 @@ class QPInverseKinematics:
     def get_output(self):
         return self._state
 
-    def is_output_valid(self):
-        return self._output_valid
+    def is_output_valid(self, instance=None):
+        """without an argument: the reference's isOutputValid(); with a robot index: that robot's last solution is usable"""
+        if instance is None:
+            return self._output_valid
+        return bool(self._output_valid and self._status is not None and self._status[int(instance)] != 2)
 
     def get_raw_solution(self):
         return None if self._nu is None else self._nu[0]

@@ -40,7 +40,7 @@ EXPORTS = [
     "blfik_set_setpoint_trajectory", "blfik_set_time", "blfik_get_time", "blfik_set_limits",
     "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline", "blfik_set_setpoint_cubic_spline", "blfik_evaluate_setpoint",
     "blfik_packed_record_len_ex", "blfik_packed_offset_ex", "blfik_packed_part_len",
-    "blfik_set_setpoint_shared", "blfik_kernel_timing", "blfik_get_kernel_times",
+    "blfik_set_setpoint_shared", "blfik_kernel_timing", "blfik_get_kernel_times", "blfik_host_alloc", "blfik_host_free",
 ]
 
 

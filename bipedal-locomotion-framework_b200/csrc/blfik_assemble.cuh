@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
     double* bp = P.base_pos + 3 * robot;
     double* bq = P.base_quat + 4 * robot;
     double* s = P.s + (size_t)n * robot;
-    if (P.packed && active) {   // packed input records carry the state: it also goes to the state arrays (K4, blfik_get_state)
+    if (P.packed && active && !(P.flags & BLFIK_TICK_KEEP_STATE)) {   // packed input records carry the state: it also goes to the state arrays (K4, blfik_get_state)
         const double* pr = P.packed + (size_t)robot * P.packed_len;
         for (int i = 0; i < 3; i++) bp[i] = pr[i];
         for (int i = 0; i < 4; i++) bq[i] = pr[3 + i];

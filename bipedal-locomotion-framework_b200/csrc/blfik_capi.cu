@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
         double* bp = P.base_pos + 3 * robot;
         double* bq = P.base_quat + 4 * robot;
         double* s = P.s + (size_t)n * robot;
-        if (P.packed) unpack_state(P, robot, bp, bq, s, n, lane);
+        if (P.packed && !(P.flags & BLFIK_TICK_KEEP_STATE)) unpack_state(P, robot, bp, bq, s, n, lane);
         bool warm = (P.flags & BLFIK_TICK_WARM_START) != 0;
         if (warm) {
             for (int i = lane; i < nv; i += 32) {
@@ -398,6 +398,7 @@ struct blfik_problem {
     double time = 0.0;               // time of the next tick (advanced by integrating ticks; set-point trajectories)
     int packed_len = 0;              // doubles per packed input record: 7 + n + sum of set-point lengths
     int packed_len_c = 0;            // the same in the compact layout (BLFIK_TICK_NO_FEEDFORWARD)
+    int packed_len_max = 0;          // the longest a record can be (no batch-shared set-point): what d_packed is sized for
     double* d_packed = nullptr;      // device copy of the packed records (allocated on first use)
 };
 
@@ -816,6 +817,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
         p->tasks.push_back(std::move(h));
     }
     layout_packed(p);
+    p->packed_len_max = p->packed_len;
     if (me > 64) return bail(fail(BLFIK_ERR_UNSUPPORTED, "[blfik_problem_create] more than 64 dense equality rows (%d)", me));
     p->me = me;
     p->L = make_layout(n, me);
@@ -1682,6 +1684,7 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     int rc = check_tick_args(p, 1, dt, flags, "blfik_tick_packed", false);
     if (rc) return rc;
     if (!records || !nu) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_tick_packed] null input or output buffer");
+    if ((flags & BLFIK_TICK_KEEP_STATE) && !p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_tick_packed] BLFIK_TICK_KEEP_STATE: the device holds no state yet");
     if (nchunks <= 0) {
         // zero-copy: when every host buffer is page-locked and mapped into the device's address space (cudaHostAlloc /
         // cudaHostRegister / torch pin_memory), the kernel reads the records and writes nu / status over PCIe itself,
@@ -1714,7 +1717,7 @@ extern "C" int blfik_tick_packed(blfik_problem* p, const double* records, double
     if (nchunks > kMaxChunks) nchunks = kMaxChunks;
     if ((long long)nchunks > p->N) nchunks = (int)p->N;
     if ((rc = refresh_tasks(p))) return rc;
-    if (!p->d_packed && (rc = dev_alloc(p, (size_t)p->N * p->packed_len, &p->d_packed, false))) return rc;
+    if (!p->d_packed && (rc = dev_alloc(p, (size_t)p->N * p->packed_len_max, &p->d_packed, false))) return rc;
     if (!p->h2d_stream) {
         CU(cudaStreamCreateWithFlags(&p->h2d_stream, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&p->d2h_stream, cudaStreamNonBlocking));
@@ -2198,6 +2201,19 @@ extern "C" int32_t blfik_num_dofs(const blfik_problem* p) { return p ? p->n : -1
 extern "C" int32_t blfik_num_equality_rows(const blfik_problem* p) { return p ? p->me : -1; }
 extern "C" int64_t blfik_num_instances(const blfik_problem* p) { return p ? p->N : -1; }
 extern "C" int64_t blfik_launch_count(const blfik_problem* p) { return p ? p->launches : -1; }
+
+extern "C" int blfik_host_alloc(size_t bytes, void** out)
+{
+    if (!out || bytes == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_host_alloc] null argument or zero size");
+    const cudaError_t e = cudaHostAlloc(out, bytes, cudaHostAllocPortable | cudaHostAllocMapped);
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_host_alloc] cudaHostAlloc(%zu): %s", bytes, cudaGetErrorString(e));
+    return BLFIK_OK;
+}
+
+extern "C" void blfik_host_free(void* ptr)
+{
+    if (ptr) cudaFreeHost(ptr);
+}
 
 extern "C" int blfik_kernel_timing(blfik_problem* p, int32_t enabled)
 {

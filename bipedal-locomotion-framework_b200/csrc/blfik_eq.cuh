@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams 
         double* bp = P.base_pos + 3 * robot;
         double* bq = P.base_quat + 4 * robot;
         double* s = P.s + (size_t)n * robot;
-        if (P.packed) unpack_state(P, robot, bp, bq, s, n, lane);
+        if (P.packed && !(P.flags & BLFIK_TICK_KEEP_STATE)) unpack_state(P, robot, bp, bq, s, n, lane);
         bool warm = (P.flags & BLFIK_TICK_WARM_START) != 0;
         QpResult res = {2, 0};
         int iters = 0, worst = 0;

@@ -600,7 +600,7 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
         double* bp = P.base_pos + 3 * robot;
         double* bq = P.base_quat + 4 * robot;
         double* s = P.s + (size_t)n * robot;
-        if (P.packed && active) unpack_state(P, robot, bp, bq, s, n, lane);
+        if (P.packed && active && !(P.flags & BLFIK_TICK_KEEP_STATE)) unpack_state(P, robot, bp, bq, s, n, lane);
         const bool warm_flag = (P.flags & BLFIK_TICK_WARM_START) != 0;
         double x = 0.0, z = 0.0, y = 0.0;
         if (warm_flag && mine) {

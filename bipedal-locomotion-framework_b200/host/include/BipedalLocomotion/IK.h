@@ -68,9 +68,22 @@ public:
         if (!m_kinDyn || !data || setPointLength() == 0) return false;
         m_sp.assign(data, data + m_kinDyn->getBatchSize() * setPointLength());
         m_spVersion++;
+        m_spUniform = false;
         m_isSetPointSetAtLeastOnce = true;
+        mirrorSetPoint(-1);
         return true;
     }
+    /** The solver's page-locked packed records ([N][stride] doubles) as the place where this task's set-point lives: from now
+     *  on every setSetPoint / setFeedback also writes robot i's `spDoubles` leading doubles of the set-point at
+     *  base[i * stride + offset] and its feedback behind them, so that advance() has nothing to gather.  base = nullptr unbinds. */
+    void bindRecords(double* base, std::size_t stride, std::size_t offset, std::size_t spDoubles)
+    {
+        m_recBase = base, m_recStride = stride, m_recOffset = offset, m_recSp = spDoubles;
+        if (base) mirrorSetPoint(-1), mirrorFeedback(-1);
+    }
+    /** the last setSetPoint addressed every robot at once (instance = -1) and none individually since: the solver hands such a
+     *  set-point to the device once (blfik_set_setpoint_shared) instead of once per robot and period */
+    bool setPointIsUniform() const { return m_spUniform && !m_sp.empty(); }
     /** robot whose A and b are materialised by update() (getA / getB); -1 = none (default when N > 1) */
     void setInspectedInstance(int i) { m_inspect = i; }
     unsigned long gainsVersion() const { return m_gainsVersion; }
@@ -190,10 +203,26 @@ protected:
     {
         const std::size_t len = setPointLength(), N = m_kinDyn->getBatchSize();
         if (m_sp.size() != N * len) m_sp.assign(N * len, 0.0);
-        for (std::size_t i = 0; i < N; i++)
-            if (instance < 0 || static_cast<std::size_t>(instance) == i)
-                for (std::size_t c = 0; c < len; c++) m_sp[i * len + c] = rec[c];
+        const std::size_t a = instance < 0 ? 0 : static_cast<std::size_t>(instance), b = instance < 0 ? N : a + 1;
+        for (std::size_t i = a; i < b && i < N; i++) std::copy_n(rec, len, m_sp.data() + i * len);
         m_spVersion++;
+        m_spUniform = instance < 0;
+        mirrorSetPoint(instance);
+    }
+    void mirrorSetPoint(std::ptrdiff_t instance)
+    {
+        if (!m_recBase || m_sp.empty() || m_recSp == 0) return;
+        const std::size_t len = setPointLength(), N = m_kinDyn->getBatchSize();
+        const std::size_t a = instance < 0 ? 0 : static_cast<std::size_t>(instance), b = instance < 0 ? N : a + 1;
+        for (std::size_t i = a; i < b; i++) std::copy_n(m_sp.data() + i * len, m_recSp, m_recBase + i * m_recStride + m_recOffset);
+    }
+    void mirrorFeedback(std::ptrdiff_t instance)
+    {
+        const std::size_t len = feedbackLength();
+        if (!m_recBase || m_fb.empty() || len == 0 || m_recSp == 0) return;
+        const std::size_t N = m_kinDyn->getBatchSize();
+        const std::size_t a = instance < 0 ? 0 : static_cast<std::size_t>(instance), b = instance < 0 ? N : a + 1;
+        for (std::size_t i = a; i < b; i++) std::copy_n(m_fb.data() + i * len, len, m_recBase + i * m_recStride + m_recOffset + m_recSp);
     }
     /** writes `count` doubles at `first` of the feedback record of robot `instance` (-1: every robot); `init` is the
      *  record a fresh buffer starts from (the controllers' initial state) */
@@ -205,10 +234,10 @@ protected:
             for (std::size_t i = 0; i < N; i++)
                 for (std::size_t c = 0; c < len; c++) m_fb[i * len + c] = init[c];
         }
-        for (std::size_t i = 0; i < N; i++)
-            if (instance < 0 || static_cast<std::size_t>(instance) == i)
-                for (std::size_t c = 0; c < count; c++) m_fb[i * len + first + c] = values[c];
+        const std::size_t a = instance < 0 ? 0 : static_cast<std::size_t>(instance), b = instance < 0 ? N : a + 1;
+        for (std::size_t i = a; i < b && i < N; i++) std::copy_n(values, count, m_fb.data() + i * len + first);
         m_fbVersion++;
+        mirrorFeedback(instance);
     }
     int inspected() const { return m_inspect >= 0 ? m_inspect : ((m_kinDyn && m_kinDyn->getBatchSize() == 1) ? 0 : -1); }
     static bool readGain3(const ParametersHandler::IParametersHandler& h, const std::string& key, Vector3d& out)
@@ -248,6 +277,9 @@ protected:
     std::vector<double> m_minJerkTarget;
     double m_minJerkDuration{0.0};
     unsigned long m_minJerkVersion{0};
+    double* m_recBase{nullptr};
+    std::size_t m_recStride{0}, m_recOffset{0}, m_recSp{0};
+    bool m_spUniform{false};
 };
 
 using IKLinearTaskFactory = System::Factory<IKLinearTask>;
@@ -525,8 +557,28 @@ public:
     const std::vector<double>& getBatchOutput() const;
     /** per-robot blfik_status of the last advance() */
     const std::vector<int32_t>& getBatchStatus() const;
-    /** advance() and apply ForwardEuler on the device in the same launch; the new state is written back into kinDyn */
-    bool advanceAndIntegrate(std::chrono::nanoseconds dT);
+    /** the same two arrays where the device left them (page-locked host memory for batches of 64 robots and more): no copy */
+    const double* batchOutputData() const;
+    const int32_t* batchStatusData() const;
+    /** advance() and apply ForwardEuler on the device in the same launch.  syncHostState = true: the new state is read back
+     *  into kinDyn (the reference's caller does integrator->getSolution() + kinDyn->setRobotState every period).  false: the
+     *  state stays on the device, the next advance() / advanceAndIntegrate() starts from it (unless kinDyn->setRobotState is
+     *  called in between), and syncState() fetches it when the caller wants it. */
+    bool advanceAndIntegrate(std::chrono::nanoseconds dT, bool syncHostState = true);
+    bool syncState();
+    /** Spread the batch over several GPUs of this host: contiguous instance blocks, one blfik_problem and one host thread per
+     *  device, no data-path collective.  Call before finalize(); default: the device of the KinDynBatch. */
+    bool setDevices(const std::vector<int>& devices);
+    /** The caller promises that every set-point carries zero feed-forward velocities (the reference's setSetPoint(pose) with
+     *  its default zero velocity): the host records then hold the pose part only (BLFIK_TICK_NO_FEEDFORWARD).  Before finalize(). */
+    void setCompactRecords(bool on);
+    /** advance() starts every solve from the previous solution, as the reference warm-starts OSQP (QPInverseKinematics.cpp:494-509);
+     *  false: every tick solves from scratch (what bench.py times) */
+    void setWarmStart(bool on);
+    /** true if robot i's last solution is usable (status SOLVED or MAX_ITER, as the reference accepts Solved and
+     *  SolvedInaccurate, QPInverseKinematics.cpp:518-523) */
+    bool isOutputValid(std::size_t instance) const;
+    using IntegrationBasedIK::isOutputValid;
     /** time at which the on-device set-point generators (IKLinearTask::setSetPointSpline) are evaluated by the next advance();
      *  advanceAndIntegrate moves it on by dT */
     bool setTime(std::chrono::nanoseconds t);

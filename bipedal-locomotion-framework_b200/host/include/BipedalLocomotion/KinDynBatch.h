@@ -60,12 +60,18 @@ public:
     const std::vector<double>& baseQuaternions() const { return m_q; }
     const std::vector<double>& jointPositions() const { return m_s; }
     unsigned long stateVersion() const { return m_version; }
+    /** The solver's page-locked packed records as a second home of the state: setRobotState then also writes robot i's
+     *  p(3) q(4) s(n) at base[i * stride], so that advance() has nothing to gather.  base = nullptr unbinds. */
+    void bindRecords(double* base, std::size_t stride);
 
 private:
     bool ensureKinProblem();
     bool evalFrame(int frame);
     bool evalCom();
 
+    double* m_recBase{nullptr};
+    std::size_t m_recStride{0};
+    void mirrorState(std::size_t a, std::size_t b);
     blfik_model* m_model{nullptr};
     blfik_problem* m_kin{nullptr};  // kinematics-only problem (owns the device copy of the state for queries)
     std::size_t m_n{0}, m_N{1};

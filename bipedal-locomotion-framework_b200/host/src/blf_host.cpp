@@ -4,6 +4,7 @@
 #include <BipedalLocomotion/IK.h>
 
 #include <algorithm>
+#include <thread>
 #include <fstream>
 
 namespace BipedalLocomotion
@@ -142,7 +143,25 @@ bool KinDynBatch::setRobotState(const Vector3d& p, const SO3d& R, const VectorXd
     for (int c = 0; c < 4; c++) m_q[4 * instance + c] = q[c];
     std::copy(s.begin(), s.end(), m_s.begin() + m_n * instance);
     m_version++;
+    mirrorState(instance, instance + 1);
     return true;
+}
+
+void KinDynBatch::bindRecords(double* base, std::size_t stride)
+{
+    m_recBase = base, m_recStride = stride;
+    mirrorState(0, m_N);
+}
+
+void KinDynBatch::mirrorState(std::size_t a, std::size_t b)
+{
+    if (!m_recBase) return;
+    for (std::size_t i = a; i < b; i++) {
+        double* r = m_recBase + i * m_recStride;
+        std::copy_n(m_p.data() + 3 * i, 3, r);
+        std::copy_n(m_q.data() + 4 * i, 4, r + 3);
+        std::copy_n(m_s.data() + m_n * i, m_n, r + 7);
+    }
 }
 
 bool KinDynBatch::setRobotStateBatch(const double* p, const double* q, const double* s)
@@ -150,6 +169,7 @@ bool KinDynBatch::setRobotStateBatch(const double* p, const double* q, const dou
     if (!isValid() || !p || !q || !s) return false;
     m_p.assign(p, p + 3 * m_N), m_q.assign(q, q + 4 * m_N), m_s.assign(s, s + m_n * m_N);
     m_version++;
+    mirrorState(0, m_N);
     return true;
 }
 
@@ -1129,15 +1149,89 @@ struct QPInverseKinematics::Impl {
     System::VariablesHandler::VariableDescription robotVelocityVariable;
     std::size_t nVars{0};
     bool isInitialized{false}, isFinalized{false}, isValid{false}, isVerbose{false};
-    blfik_problem* problem{nullptr};
+    blfik_problem* problem{nullptr};   // the first shard's problem (the only one unless setDevices spread the batch)
     State solution;
     VectorXd rawSolution;
     std::vector<double> nu;
     std::vector<int32_t> status;
+    // ---- the batch path: contiguous instance blocks, one problem per device, page-locked packed records as the native storage
+    // of state and set-points (KinDynBatch and the tasks write straight into them), one blfik_tick_packed per device and tick
+    struct Shard {
+        int device{0};
+        std::size_t first{0}, count{0};
+        blfik_problem* prob{nullptr};
+    };
+    static constexpr std::size_t kPackedMin = 64;   // smaller batches keep the per-array calls (lower latency for a handful of robots)
+    std::vector<int> devices;
+    std::vector<Shard> shards;
+    bool compact{false}, packedPath{false}, warmStart{true};
+    double* hRec{nullptr};
+    double* hNu{nullptr};
+    int32_t* hStatus{nullptr};
+    std::size_t recLen{0}, recCap{0};
+    std::vector<char> sharedNow;
+    std::vector<unsigned long> sharedVersion;
+    bool nuStale{false}, statusStale{false};
+    bool deviceStateAhead{false};
+    unsigned long stateVersionAtTick{0};
+    int64_t unsolved{0};
+
+    uint32_t recordFlags() const { return compact ? BLFIK_TICK_NO_FEEDFORWARD : 0u; }
+    void destroyProblems()
+    {
+        for (auto& sh : shards)
+            if (sh.prob) blfik_problem_destroy(sh.prob);
+        shards.clear();
+        problem = nullptr;
+    }
+    void freeHost()
+    {
+        if (kinDyn) kinDyn->bindRecords(nullptr, 0);
+        for (auto& e : tasks) e.task->bindRecords(nullptr, 0, 0, 0);
+        if (hRec) blfik_host_free(hRec);
+        if (hNu) blfik_host_free(hNu);
+        if (hStatus) blfik_host_free(hStatus);
+        hRec = hNu = nullptr, hStatus = nullptr;
+    }
+    /** which set-points travel as one batch-shared record, where everything else sits in a packed record; binds KinDynBatch
+     *  and the tasks to the records */
+    bool layoutRecords()
+    {
+        const std::size_t N = kinDyn->getBatchSize();
+        for (std::size_t t = 0; t < tasks.size(); t++) {
+            auto& task = *tasks[t].task;
+            const bool want = task.setPointLength() > 0 && task.feedbackLength() == 0 && task.setPointIsUniform();
+            if (want == static_cast<bool>(sharedNow[t]) && (!want || sharedVersion[t] == task.setPointVersion())) continue;
+            for (auto& sh : shards) {
+                const int rc = want ? blfik_set_setpoint_shared(sh.prob, static_cast<int32_t>(t), task.setPointBuffer().data(), BLFIK_MEM_HOST)
+                                    : blfik_set_setpoint(sh.prob, static_cast<int32_t>(t), task.setPointBuffer().data() + sh.first * task.setPointLength(), BLFIK_MEM_HOST);
+                if (rc != BLFIK_OK) return false;
+            }
+            sharedNow[t] = want, sharedVersion[t] = task.setPointVersion();
+        }
+        const std::size_t len = static_cast<std::size_t>(blfik_packed_record_len_ex(shards[0].prob, recordFlags()));
+        if (len == recLen && hRec) return true;
+        recLen = len;
+        if (recLen > recCap) return false;
+        kinDyn->bindRecords(hRec, recLen);
+        for (std::size_t t = 0; t < tasks.size(); t++) {
+            auto& task = *tasks[t].task;
+            const int off = blfik_packed_offset_ex(shards[0].prob, static_cast<int32_t>(t), recordFlags());
+            if (off < 0) {
+                task.bindRecords(nullptr, 0, 0, 0);
+                continue;
+            }
+            const std::size_t part = static_cast<std::size_t>(blfik_packed_part_len(shards[0].prob, static_cast<int32_t>(t), recordFlags()));
+            task.bindRecords(hRec, recLen, static_cast<std::size_t>(off), part - task.feedbackLength());
+        }
+        (void)N;
+        return true;
+    }
 
     ~Impl()
     {
-        if (problem) blfik_problem_destroy(problem);
+        freeHost();
+        destroyProblems();
     }
 };
 
@@ -1156,6 +1250,11 @@ bool QPInverseKinematics::initialize(std::weak_ptr<const ParametersHandler::IPar
         log()->error("{} Unable to get the parameter 'robot_velocity_variable_name'.", logPrefix);
         return false;
     }
+    // batch extensions, both optional: the GPUs the batch is spread over and the compact host records (no reference counterpart)
+    std::vector<int> devs;
+    if (ptr->getParameter("cuda_devices", devs)) m_pimpl->devices = devs;
+    bool compactRecords = false;
+    if (ptr->getParameter("compact_records", compactRecords)) m_pimpl->compact = compactRecords;
     if (!ptr->getParameter("verbosity", m_pimpl->isVerbose))
         log()->info("{} 'verbosity' not found. The following parameter will be used '{}'.", logPrefix, m_pimpl->isVerbose);
     m_pimpl->isInitialized = true;
@@ -1296,15 +1395,43 @@ bool QPInverseKinematics::finalize(const System::VariablesHandler& handler)
         log()->error("{} No KinDyn object: build the solver with QPInverseKinematics::build or call setKinDyn through a task added by addTask.", logPrefix);
         return false;
     }
-    if (m_pimpl->problem) {
-        blfik_problem_destroy(m_pimpl->problem);
-        m_pimpl->problem = nullptr;
-    }
+    m_pimpl->freeHost();
+    m_pimpl->destroyProblems();
     const std::size_t N = m_pimpl->kinDyn->getBatchSize();
-    if (blfik_problem_create(m_pimpl->kinDyn->model(), descs.data(), static_cast<int32_t>(descs.size()), static_cast<int64_t>(N),
-                             m_pimpl->kinDyn->getDevice(), &m_pimpl->problem) != BLFIK_OK) {
-        log()->error("{} {}", logPrefix, blfik_last_error());
-        return false;
+    {
+        std::vector<int> devs = m_pimpl->devices;
+        if (devs.empty() || N < Impl::kPackedMin) devs = {m_pimpl->kinDyn->getDevice()};
+        if (devs.size() > N) devs.resize(N);
+        for (std::size_t d = 0; d < devs.size(); d++) {
+            Impl::Shard sh;
+            sh.device = devs[d], sh.first = N * d / devs.size(), sh.count = N * (d + 1) / devs.size() - sh.first;
+            if (blfik_problem_create(m_pimpl->kinDyn->model(), descs.data(), static_cast<int32_t>(descs.size()), static_cast<int64_t>(sh.count), sh.device,
+                                     &sh.prob) != BLFIK_OK) {
+                log()->error("{} {}", logPrefix, blfik_last_error());
+                m_pimpl->destroyProblems();
+                return false;
+            }
+            m_pimpl->shards.push_back(sh);
+        }
+        m_pimpl->problem = m_pimpl->shards[0].prob;
+    }
+    m_pimpl->packedPath = N >= Impl::kPackedMin;
+    m_pimpl->sharedNow.assign(m_pimpl->tasks.size(), 0), m_pimpl->sharedVersion.assign(m_pimpl->tasks.size(), 0);
+    m_pimpl->recLen = 0, m_pimpl->deviceStateAhead = false;
+    if (m_pimpl->packedPath) {
+        const std::size_t nvv = m_pimpl->kinDyn->getNrOfDegreesOfFreedom() + 6;
+        m_pimpl->recCap = static_cast<std::size_t>(blfik_packed_record_len_ex(m_pimpl->problem, 0u));   // the full layout is the longest
+        if (blfik_host_alloc(N * m_pimpl->recCap * sizeof(double), reinterpret_cast<void**>(&m_pimpl->hRec)) != BLFIK_OK ||
+            blfik_host_alloc(N * nvv * sizeof(double), reinterpret_cast<void**>(&m_pimpl->hNu)) != BLFIK_OK ||
+            blfik_host_alloc(N * sizeof(int32_t), reinterpret_cast<void**>(&m_pimpl->hStatus)) != BLFIK_OK) {
+            log()->error("{} {}", logPrefix, blfik_last_error());
+            return false;
+        }
+        std::fill(m_pimpl->hRec, m_pimpl->hRec + N * m_pimpl->recCap, 0.0);
+        if (!m_pimpl->layoutRecords()) {
+            log()->error("{} Unable to lay out the packed records: {}", logPrefix, blfik_last_error());
+            return false;
+        }
     }
     const std::size_t nv = m_pimpl->kinDyn->getNrOfDegreesOfFreedom() + 6;
     m_pimpl->nu.assign(N * nv, 0.0), m_pimpl->status.assign(N, 2);
@@ -1323,22 +1450,57 @@ std::vector<std::string> QPInverseKinematics::getTaskNames() const
 
 bool QPInverseKinematics::isOutputValid() const { return m_pimpl->isValid; }
 
-bool QPInverseKinematics::advance()
+bool QPInverseKinematics::isOutputValid(std::size_t instance) const
 {
-    return tick(0.0, BLFIK_TICK_WARM_START);
+    if (!m_pimpl->isValid && m_pimpl->status.size() == 1) return false;
+    const int32_t* st = m_pimpl->packedPath ? m_pimpl->hStatus : m_pimpl->status.data();
+    const std::size_t N = m_pimpl->kinDyn ? m_pimpl->kinDyn->getBatchSize() : 0;
+    return st && instance < N && st[instance] != BLFIK_STATUS_FAILED;
 }
 
-bool QPInverseKinematics::advanceAndIntegrate(std::chrono::nanoseconds dT)
+bool QPInverseKinematics::setDevices(const std::vector<int>& devices)
 {
-    const double dt = std::chrono::duration<double>(dT).count();
-    if (!tick(dt, BLFIK_TICK_WARM_START | BLFIK_TICK_INTEGRATE)) return false;
-    auto& kd = *m_pimpl->kinDyn;
-    std::vector<double> p(kd.basePositions().size()), q(kd.baseQuaternions().size()), s(kd.jointPositions().size());
-    if (blfik_get_state(m_pimpl->problem, p.data(), q.data(), s.data(), BLFIK_MEM_HOST) != BLFIK_OK) {
-        log()->error("[QPInverseKinematics::advanceAndIntegrate] {}", blfik_last_error());
+    if (m_pimpl->isFinalized) {
+        log()->error("[QPInverseKinematics::setDevices] Please call setDevices() before finalize().");
         return false;
     }
-    return kd.setRobotStateBatch(p.data(), q.data(), s.data());
+    m_pimpl->devices = devices;
+    return true;
+}
+
+void QPInverseKinematics::setCompactRecords(bool on) { m_pimpl->compact = on; }
+void QPInverseKinematics::setWarmStart(bool on) { m_pimpl->warmStart = on; }
+
+bool QPInverseKinematics::advance()
+{
+    return tick(0.0, m_pimpl->warmStart ? BLFIK_TICK_WARM_START : 0u);
+}
+
+bool QPInverseKinematics::syncState()
+{
+    Impl* pimpl = m_pimpl.get();
+    if (!pimpl->isFinalized) return false;
+    auto& kd = *pimpl->kinDyn;
+    std::vector<double> p(kd.basePositions().size()), q(kd.baseQuaternions().size()), s(kd.jointPositions().size());
+    const std::size_t n = kd.getNrOfDegreesOfFreedom();
+    for (auto& sh : pimpl->shards)
+        if (blfik_get_state(sh.prob, p.data() + 3 * sh.first, q.data() + 4 * sh.first, s.data() + n * sh.first, BLFIK_MEM_HOST) != BLFIK_OK) {
+            log()->error("[QPInverseKinematics::syncState] {}", blfik_last_error());
+            return false;
+        }
+    if (!kd.setRobotStateBatch(p.data(), q.data(), s.data())) return false;
+    pimpl->deviceStateAhead = false;
+    return true;
+}
+
+bool QPInverseKinematics::advanceAndIntegrate(std::chrono::nanoseconds dT, bool syncHostState)
+{
+    const double dt = std::chrono::duration<double>(dT).count();
+    if (!tick(dt, (m_pimpl->warmStart ? BLFIK_TICK_WARM_START : 0u) | BLFIK_TICK_INTEGRATE)) return false;
+    if (syncHostState) return syncState();
+    m_pimpl->deviceStateAhead = true;
+    m_pimpl->stateVersionAtTick = m_pimpl->kinDyn->stateVersion();
+    return true;
 }
 
 bool QPInverseKinematics::tick(double dt, uint32_t flags)
@@ -1364,77 +1526,137 @@ bool QPInverseKinematics::tick(double dt, uint32_t flags)
         log()->error("{} {}: {}", logPrefix, what, blfik_last_error());
         return false;
     };
-    blfik_problem* prob = pimpl->problem;
-    for (std::size_t t = 0; t < pimpl->tasks.size(); t++) {
-        auto& e = pimpl->tasks[t];
-        if (e.priority == 1) {   // the weight is read from its provider on every tick (:450-451)
-            const VectorXd& w = e.weightProvider->getOutput();
-            if (w.size() != e.task->size()) {
-                log()->error("{} The weight of the task named {} has the wrong size.", logPrefix, e.name);
-                return false;
+    auto& kd = *pimpl->kinDyn;
+    const std::size_t n = kd.getNrOfDegreesOfFreedom(), nv = n + 6, N = kd.getBatchSize();
+    // the state the device integrated itself stays in force until the caller sets a new one
+    const bool keepState = pimpl->deviceStateAhead && kd.stateVersion() == pimpl->stateVersionAtTick;
+    for (auto& sh : pimpl->shards) {
+        blfik_problem* prob = sh.prob;
+        for (std::size_t t = 0; t < pimpl->tasks.size(); t++) {
+            auto& e = pimpl->tasks[t];
+            const bool last = &sh == &pimpl->shards.back();
+            if (e.priority == 1) {   // the weight is read from its provider on every tick (:450-451)
+                const VectorXd& w = e.weightProvider->getOutput();
+                if (w.size() != e.task->size()) {
+                    log()->error("{} The weight of the task named {} has the wrong size.", logPrefix, e.name);
+                    return false;
+                }
+                if (w != e.uploadedWeight) {
+                    if (blfik_set_weight(prob, static_cast<int32_t>(t), w.data()) != BLFIK_OK) return fail("Unable to update the weight");
+                    if (last) e.uploadedWeight = w;
+                }
             }
-            if (w != e.uploadedWeight) {
-                if (blfik_set_weight(prob, static_cast<int32_t>(t), w.data()) != BLFIK_OK) return fail("Unable to update the weight");
-                e.uploadedWeight = w;
+            if (e.task->gainsVersion() != e.uploadedGains) {
+                blfik_task_desc d;
+                std::vector<std::vector<double>> keep;
+                e.task->fillDescriptor(d, keep);
+                if (blfik_set_controller_mode(prob, static_cast<int32_t>(t), d.controller_enabled) != BLFIK_OK) return fail("Unable to update the controller mode");
+                if (last) e.uploadedGains = e.task->gainsVersion();
             }
-        }
-        if (e.task->gainsVersion() != e.uploadedGains) {
-            blfik_task_desc d;
-            std::vector<std::vector<double>> keep;
-            e.task->fillDescriptor(d, keep);
-            if (blfik_set_controller_mode(prob, static_cast<int32_t>(t), d.controller_enabled) != BLFIK_OK) return fail("Unable to update the controller mode");
-            e.uploadedGains = e.task->gainsVersion();
-        }
-        if (e.task->setPointLength() > 0 && e.task->setPointVersion() != e.uploadedSetPoint) {
-            if (blfik_set_setpoint(prob, static_cast<int32_t>(t), e.task->setPointBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the set-point");
-            e.uploadedSetPoint = e.task->setPointVersion();
-        }
-        if (e.task->acceptsMinimumJerk() && e.task->minimumJerkVersion() != e.uploadedMinJerk) {   // setSetPointMinimumJerk(...) since the last tick
-            const double T = e.task->minimumJerkDuration();
-            if (blfik_set_setpoint_minimum_jerk(prob, static_cast<int32_t>(t), T > 0 ? e.task->minimumJerkTarget().data() : nullptr, T, BLFIK_MEM_HOST) != BLFIK_OK)
-                return fail("Unable to set the minimum-jerk generator");
-            e.uploadedMinJerk = e.task->minimumJerkVersion();
-        }
-        if (e.task->acceptsSetPointSpline() && e.task->splineVersion() != e.uploadedSpline) {   // setSetPointSpline(...) since the last tick
-            const auto& tm = e.task->splineTimes();
-            const auto set = e.task->splineIsCubic() ? blfik_set_setpoint_cubic_spline : blfik_set_setpoint_spline;
-            const int rc = tm.empty() ? set(prob, static_cast<int32_t>(t), 0, nullptr, nullptr, nullptr, BLFIK_MEM_HOST)
-                                      : set(prob, static_cast<int32_t>(t), static_cast<int32_t>(tm.size()), tm.data(), e.task->splinePositions().data(),
-                                            e.task->splineBoundary().data(), BLFIK_MEM_HOST);
-            if (rc != BLFIK_OK) return fail("Unable to set the set-point spline");
-            e.uploadedSpline = e.task->splineVersion();
-        }
-        if (e.task->feedbackLength() > 0 && e.task->feedbackVersion() != e.uploadedFeedback) {   // setFeedback(...) since the last tick
-            if (blfik_set_feedback(prob, static_cast<int32_t>(t), e.task->feedbackBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the feedback");
-            e.uploadedFeedback = e.task->feedbackVersion();
+            const std::size_t spl = e.task->setPointLength();
+            if (!pimpl->packedPath && spl > 0 && e.task->setPointVersion() != e.uploadedSetPoint) {
+                if (blfik_set_setpoint(prob, static_cast<int32_t>(t), e.task->setPointBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the set-point");
+                e.uploadedSetPoint = e.task->setPointVersion();
+            }
+            if (e.task->acceptsMinimumJerk() && e.task->minimumJerkVersion() != e.uploadedMinJerk) {   // setSetPointMinimumJerk(...) since the last tick
+                const double T = e.task->minimumJerkDuration();
+                if (blfik_set_setpoint_minimum_jerk(prob, static_cast<int32_t>(t), T > 0 ? e.task->minimumJerkTarget().data() + sh.first * spl : nullptr, T, BLFIK_MEM_HOST) != BLFIK_OK)
+                    return fail("Unable to set the minimum-jerk generator");
+                if (last) e.uploadedMinJerk = e.task->minimumJerkVersion();
+            }
+            if (e.task->acceptsSetPointSpline() && e.task->splineVersion() != e.uploadedSpline) {   // setSetPointSpline(...) since the last tick
+                const auto& tm = e.task->splineTimes();
+                const auto set = e.task->splineIsCubic() ? blfik_set_setpoint_cubic_spline : blfik_set_setpoint_spline;
+                const std::size_t nbc = e.task->splineIsCubic() ? 6 : 12;
+                const int rc = tm.empty() ? set(prob, static_cast<int32_t>(t), 0, nullptr, nullptr, nullptr, BLFIK_MEM_HOST)
+                                          : set(prob, static_cast<int32_t>(t), static_cast<int32_t>(tm.size()), tm.data(),
+                                                e.task->splinePositions().data() + sh.first * tm.size() * 3, e.task->splineBoundary().data() + sh.first * nbc, BLFIK_MEM_HOST);
+                if (rc != BLFIK_OK) return fail("Unable to set the set-point spline");
+                if (last) e.uploadedSpline = e.task->splineVersion();
+            }
+            if (!pimpl->packedPath && e.task->feedbackLength() > 0 && e.task->feedbackVersion() != e.uploadedFeedback) {   // setFeedback(...) since the last tick
+                if (blfik_set_feedback(prob, static_cast<int32_t>(t), e.task->feedbackBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the feedback");
+                e.uploadedFeedback = e.task->feedbackVersion();
+            }
         }
     }
-    auto& kd = *pimpl->kinDyn;
-    if (blfik_set_state(prob, kd.basePositions().data(), kd.baseQuaternions().data(), kd.jointPositions().data(), BLFIK_MEM_HOST) != BLFIK_OK)
+    if (pimpl->packedPath) {
+        // State and set-points already sit in the page-locked records (KinDynBatch::setRobotState and the tasks' setSetPoint
+        // wrote them there): one packed host tick per device, each from its own host thread.
+        if (!pimpl->layoutRecords()) return fail("Unable to lay out the packed records");
+        const uint32_t fl = flags | pimpl->recordFlags() | (keepState ? BLFIK_TICK_KEEP_STATE : 0u);
+        std::vector<int> rcs(pimpl->shards.size(), BLFIK_OK);
+        std::vector<std::string> errs(pimpl->shards.size());
+        auto run = [&](std::size_t k) {
+            const auto& sh = pimpl->shards[k];
+            rcs[k] = blfik_tick_packed(sh.prob, pimpl->hRec + sh.first * pimpl->recLen, pimpl->hNu + sh.first * nv, pimpl->hStatus + sh.first, dt, fl, 8);
+            if (rcs[k] != BLFIK_OK) errs[k] = blfik_last_error();   // the message is per thread
+        };
+        std::vector<std::thread> workers;
+        for (std::size_t k = 1; k < pimpl->shards.size(); k++) workers.emplace_back(run, k);
+        run(0);
+        for (auto& w : workers) w.join();
+        for (std::size_t k = 0; k < rcs.size(); k++)
+            if (rcs[k] != BLFIK_OK) {
+                log()->error("{} Unable to run the tick on device {}: {}", logPrefix, pimpl->shards[k].device, errs[k]);
+                return false;
+            }
+        pimpl->nuStale = pimpl->statusStale = true;
+        pimpl->unsolved = 0;
+        int64_t failed = 0;
+        for (std::size_t i = 0; i < N; i++) pimpl->unsolved += pimpl->hStatus[i] != BLFIK_STATUS_SOLVED, failed += pimpl->hStatus[i] == BLFIK_STATUS_FAILED;
+        for (int c = 0; c < 3; c++) pimpl->solution.baseVelocity.linear[c] = pimpl->hNu[c], pimpl->solution.baseVelocity.angular[c] = pimpl->hNu[3 + c];
+        pimpl->solution.jointVelocity.assign(pimpl->hNu + 6, pimpl->hNu + nv);
+        std::fill(pimpl->rawSolution.begin(), pimpl->rawSolution.end(), 0.0);
+        std::copy(pimpl->hNu, pimpl->hNu + nv, pimpl->rawSolution.begin() + pimpl->robotVelocityVariable.offset);
+        // A batch is not all-or-nothing: the call succeeded, each robot answers for itself (isOutputValid(i), getBatchStatus()).
+        if (failed != 0) log()->warn("{} osqp was not able to find a feasible solution for {} of {} robots.", logPrefix, failed, N);
+        pimpl->isValid = true;
+        return true;
+    }
+    blfik_problem* prob = pimpl->problem;
+    if (!keepState && blfik_set_state(prob, kd.basePositions().data(), kd.baseQuaternions().data(), kd.jointPositions().data(), BLFIK_MEM_HOST) != BLFIK_OK)
         return fail("Unable to set the robot state");
     if (blfik_tick(prob, 1, dt, flags) != BLFIK_OK) return fail("Unable to run the tick");
     if (blfik_get_output(prob, pimpl->nu.data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to get the solution");
     if (blfik_get_status(prob, pimpl->status.data(), nullptr, BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to get the status");
-    int64_t unsolved = 0;
-    for (int32_t s : pimpl->status) unsolved += s != BLFIK_STATUS_SOLVED;
+    int64_t failed = 0;
+    pimpl->unsolved = 0;
+    for (int32_t st : pimpl->status) pimpl->unsolved += st != BLFIK_STATUS_SOLVED, failed += st == BLFIK_STATUS_FAILED;
     // retrieve the solution of robot 0 (:531-541); the whole batch is in getBatchOutput()
-    const std::size_t nv = kd.getNrOfDegreesOfFreedom() + 6;
     for (int c = 0; c < 3; c++) pimpl->solution.baseVelocity.linear[c] = pimpl->nu[c], pimpl->solution.baseVelocity.angular[c] = pimpl->nu[3 + c];
     pimpl->solution.jointVelocity.assign(pimpl->nu.begin() + 6, pimpl->nu.begin() + nv);
     std::fill(pimpl->rawSolution.begin(), pimpl->rawSolution.end(), 0.0);
     std::copy(pimpl->nu.begin(), pimpl->nu.begin() + nv, pimpl->rawSolution.begin() + pimpl->robotVelocityVariable.offset);
-    if (unsolved != 0) {   // :518-523
-        log()->error("{} osqp was not able to find a feasible solution ({} of {} robots).", logPrefix, unsolved, pimpl->status.size());
+    if (N == 1 && failed != 0) {   // :518-523: Solved and SolvedInaccurate are accepted, anything else fails the call
+        log()->error("{} osqp was not able to find a feasible solution.", logPrefix);
         return false;
     }
+    if (failed != 0) log()->warn("{} osqp was not able to find a feasible solution for {} of {} robots.", logPrefix, failed, N);
     pimpl->isValid = true;
     return true;
 }
 
 const QPInverseKinematics::State& QPInverseKinematics::getOutput() const { return m_pimpl->solution; }
 const VectorXd& QPInverseKinematics::getRawSolution() const { return m_pimpl->rawSolution; }
-const std::vector<double>& QPInverseKinematics::getBatchOutput() const { return m_pimpl->nu; }
-const std::vector<int32_t>& QPInverseKinematics::getBatchStatus() const { return m_pimpl->status; }
+const std::vector<double>& QPInverseKinematics::getBatchOutput() const
+{
+    if (m_pimpl->packedPath && m_pimpl->nuStale) {   // the results live in page-locked memory; the vector is filled when somebody asks
+        m_pimpl->nu.assign(m_pimpl->hNu, m_pimpl->hNu + m_pimpl->nu.size());
+        m_pimpl->nuStale = false;
+    }
+    return m_pimpl->nu;
+}
+const std::vector<int32_t>& QPInverseKinematics::getBatchStatus() const
+{
+    if (m_pimpl->packedPath && m_pimpl->statusStale) {
+        m_pimpl->status.assign(m_pimpl->hStatus, m_pimpl->hStatus + m_pimpl->status.size());
+        m_pimpl->statusStale = false;
+    }
+    return m_pimpl->status;
+}
+const double* QPInverseKinematics::batchOutputData() const { return m_pimpl->packedPath ? m_pimpl->hNu : m_pimpl->nu.data(); }
+const int32_t* QPInverseKinematics::batchStatusData() const { return m_pimpl->packedPath ? m_pimpl->hStatus : m_pimpl->status.data(); }
 blfik_problem* QPInverseKinematics::handle() { return m_pimpl->problem; }
 bool QPInverseKinematics::setTime(std::chrono::nanoseconds t)
 {

@@ -39,7 +39,7 @@ static std::shared_ptr<KinDynBatch> loadKinDyn(const char* path, std::size_t N =
 }
 
 // the ergoCub IK of utilities/balancing-position-control/config/robots/ergoCubGazeboV1/blf_balancing_position_control/ik.ini
-static std::shared_ptr<IParametersHandler> ergoCubHandler(std::size_t n, bool withLimits)
+static std::shared_ptr<IParametersHandler> ergoCubHandler(std::size_t n, bool withLimits, const std::vector<int>& devices = {}, bool compactRecords = false)
 {
     auto h = std::make_shared<StdImplementation>();
     std::vector<std::string> tasks{"COM_TASK", "RIGHT_FOOT_TASK", "LEFT_FOOT_TASK", "TORSO_TASK", "JOINT_REGULARIZATION_TASK"};
@@ -47,6 +47,8 @@ static std::shared_ptr<IParametersHandler> ergoCubHandler(std::size_t n, bool wi
     h->setParameter("tasks", tasks);
     auto ik = std::make_shared<StdImplementation>();
     ik->setParameter("robot_velocity_variable_name", robotVelocity);
+    if (!devices.empty()) ik->setParameter("cuda_devices", devices);
+    if (compactRecords) ik->setParameter("compact_records", true);
     h->setGroup("IK", ik);
     auto com = std::make_shared<StdImplementation>();
     com->setParameter("type", "CoMTask"), com->setParameter("kp_linear", 2.0), com->setParameter("priority", 0);
@@ -950,6 +952,92 @@ static void testIntegrator()
     log()->setLevel(Logger::Level::warn);
 }
 
+
+// The batch path (N >= 64): packed page-locked records as the native storage of state and set-points, one blfik_tick_packed per
+// shard.  Its results must not depend on how the batch is cut: one shard, three shards (all on device 0 here: the sharding
+// logic is the same whichever device a block lands on), compact records; and each robot must get what it gets when it is solved
+// in a small batch through the per-array calls.  Also: the regularisation set-point given to all robots at once travels as
+// one batch-shared record, a per-robot call afterwards brings the records back, and advanceAndIntegrate without the host
+// copy-back follows the same trajectory as with it.
+static void testBatchPath(const char* modelPath)
+{
+    constexpr std::size_t N = 150;
+    constexpr auto dT = 10ms;
+    std::mt19937 gen(7);
+    std::normal_distribution<double> noise(0.0, 0.04);
+    struct Case { std::vector<int> devices; bool compact; std::size_t n; };
+    const std::vector<Case> cases{{{}, false, N}, {{0, 0, 0}, false, N}, {{0, 0}, true, N}, {{}, false, 40}};
+    std::vector<std::vector<double>> results;
+    std::vector<VectorXd> sDes(N), s0(N);
+    std::vector<double> tilt(N);
+    {
+        auto kd = loadKinDyn(modelPath, 1);
+        for (std::size_t i = 0; i < N; i++) {
+            sDes[i] = nominalJoints(*kd, gen, 0.15);
+            s0[i] = sDes[i];
+            for (auto& v : s0[i]) v += noise(gen);
+            tilt[i] = 0.05 + noise(gen);
+        }
+    }
+    for (const Case& c : cases) {
+        auto kinDyn = loadKinDyn(modelPath, c.n);
+        auto desired = loadKinDyn(modelPath, c.n);
+        const std::size_t n = kinDyn->getNrOfDegreesOfFreedom();
+        for (std::size_t i = 0; i < c.n; i++) REQUIRE(desired->setRobotState({0.0, 0.0, 0.75}, SO3d::Exp({0.0, 0.05, 0.1}), sDes[i], i));
+        auto problem = QPInverseKinematics::build(ergoCubHandler(n, true, c.devices, c.compact), kinDyn);
+        REQUIRE(problem.isValid());
+        auto* ik = static_cast<QPInverseKinematics*>(problem.ik.get());
+        auto comTask = std::dynamic_pointer_cast<CoMTask>(ik->getTask("COM_TASK").lock());
+        auto rFoot = std::dynamic_pointer_cast<SE3Task>(ik->getTask("RIGHT_FOOT_TASK").lock());
+        auto lFoot = std::dynamic_pointer_cast<SE3Task>(ik->getTask("LEFT_FOOT_TASK").lock());
+        auto torso = std::dynamic_pointer_cast<SO3Task>(ik->getTask("TORSO_TASK").lock());
+        auto reg = std::dynamic_pointer_cast<JointTrackingTask>(ik->getTask("JOINT_REGULARIZATION_TASK").lock());
+        for (std::size_t i = 0; i < c.n; i++) {
+            std::array<double, 9> R;
+            Vector3d com;
+            SE3d r, l, chest;
+            REQUIRE(desired->getCenterOfMassPosition(com, i));
+            REQUIRE(desired->getWorldTransform(kinDyn->getFrameIndex("r_sole"), r, R, i));
+            REQUIRE(desired->getWorldTransform(kinDyn->getFrameIndex("l_sole"), l, R, i));
+            REQUIRE(desired->getWorldTransform(kinDyn->getFrameIndex("chest"), chest, R, i));
+            REQUIRE(comTask->setSetPoint(com, {0, 0, 0}, i));
+            REQUIRE(rFoot->setSetPoint(r, SE3d::Tangent::Zero(), i) && lFoot->setSetPoint(l, SE3d::Tangent::Zero(), i));
+            REQUIRE(torso->setSetPoint(chest.R, SO3Tangentd::Zero(), i));
+            REQUIRE(kinDyn->setRobotState({0.0, 0.0, 0.75}, SO3d::Exp({0.0, tilt[i], 0.1}), s0[i], i));
+        }
+        REQUIRE(reg->setSetPoint(sDes[0]));                      // every robot at once: one batch-shared record
+        REQUIRE(reg->setPointIsUniform());
+        REQUIRE(ik->advance() && ik->isOutputValid());
+        std::vector<double> first(ik->batchOutputData(), ik->batchOutputData() + c.n * (n + 6));
+        for (std::size_t i = 0; i < c.n; i++) REQUIRE(reg->setSetPoint(sDes[i], i));   // and now one per robot: back into the records
+        REQUIRE_FALSE(reg->setPointIsUniform());
+        REQUIRE(ik->advance());
+        for (std::size_t i = 0; i < c.n; i++) REQUIRE(ik->isOutputValid(i));
+        REQUIRE(ik->getBatchStatus().size() == c.n);
+        std::vector<double> out(ik->getBatchOutput());
+        double moved = 0;
+        for (std::size_t k = 0; k < out.size(); k++) moved = std::max(moved, std::abs(out[k] - first[k]));
+        REQUIRE(moved > 1e-4);                                   // the per-robot postural targets differ from robot 0's
+        // closed loop on the device, with and without reading the state back every period
+        for (int it = 0; it < 5; it++) REQUIRE(ik->advanceAndIntegrate(dT, it % 2 == 0 ? false : true));
+        REQUIRE(ik->advanceAndIntegrate(dT, false) && ik->syncState());
+        const auto& sEnd = kinDyn->jointPositions();
+        out.insert(out.end(), sEnd.begin(), sEnd.end());
+        results.push_back(std::move(out));
+    }
+    const std::size_t nv = 29, n = 23;
+    REQUIRE(results[0].size() == N * (nv + n));
+    for (std::size_t k = 0; k < results[0].size(); k++) REQUIRE(results[1][k] == results[0][k]);            // cut differently: bit-identical
+    double dCompact = 0, dSmall = 0;
+    for (std::size_t k = 0; k < results[0].size(); k++) dCompact = std::max(dCompact, std::abs(results[2][k] - results[0][k]));
+    REQUIRE(dCompact == 0.0);                                                                               // the feed-forward terms were zero
+    for (std::size_t i = 0; i < 40; i++) {
+        for (std::size_t c = 0; c < nv; c++) dSmall = std::max(dSmall, std::abs(results[3][i * nv + c] - results[0][i * nv + c]));
+        for (std::size_t c = 0; c < n; c++) dSmall = std::max(dSmall, std::abs(results[3][40 * nv + i * n + c] - results[0][N * nv + i * n + c]));
+    }
+    REQUIRE(dSmall < 1e-7);   // the small batch takes the per-array calls (and, at 40 robots, the same kernels): same optimum, same rollout
+}
+
 int main(int argc, char** argv)
 {
     if (argc < 3) {
@@ -967,6 +1055,8 @@ int main(int argc, char** argv)
         testClosedLoop(argv[2], 1, false);
         testClosedLoop(argv[2], 1, true);
         testClosedLoop(argv[2], 48, true);
+        testClosedLoop(argv[2], 200, true);   // the packed-record batch path
+        testBatchPath(argv[2]);
         testFixedBase(argv[2], 1);
         testFixedBase(argv[2], 5);
         testSetPointSpline(argv[2], 3);

@@ -32,6 +32,7 @@
 #ifndef BLFIK_H
 #define BLFIK_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -77,6 +78,9 @@ typedef enum {
 /* flags of blfik_tick */
 #define BLFIK_TICK_INTEGRATE 1u   /* apply ForwardEuler after each solve (closed loop)           */
 #define BLFIK_TICK_NO_FEEDFORWARD 4u /* blfik_tick_packed only: compact records, see there                 */
+#define BLFIK_TICK_KEEP_STATE 8u  /* blfik_tick_packed only: the state part of the records is ignored, the tick starts from
+                                     the state the device holds (a closed loop integrated on the device whose host copy
+                                     the caller does not refresh every period)                                     */
 #define BLFIK_TICK_WARM_START 2u  /* start ADMM from the previous tick's (x, z, y) (reference does,
                                      QPInverseKinematics.cpp:494-509)                             */
 
@@ -398,6 +402,11 @@ int32_t blfik_get_kernel_path(const blfik_problem* problem);
  * of the assemble kernel (K1 + K2) and of the solve kernel (K3 + K4) in milliseconds.  bench.py's roofline uses it.   */
 int blfik_kernel_timing(blfik_problem* problem, int32_t enabled);
 int blfik_get_kernel_times(blfik_problem* problem, double* ms_assemble, double* ms_solve);
+/* Page-locked host memory, visible to every device of the process (cudaHostAllocPortable | cudaHostAllocMapped), for the
+ * buffers of blfik_tick_packed / blfik_tick_host: the host classes keep their packed records, nu and status there so that the
+ * library above the C ABI needs no CUDA headers.  No reference counterpart (Eigen vectors in pageable memory).            */
+int blfik_host_alloc(size_t bytes, void** out);
+void blfik_host_free(void* ptr);
 /* number of kernel launches issued so far by this problem                                */
 int64_t blfik_launch_count(const blfik_problem* problem);
 const char* blfik_last_error(void);
