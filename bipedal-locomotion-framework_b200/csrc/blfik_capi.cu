@@ -382,7 +382,7 @@ struct blfik_problem {
     void (*solve_kernel)(const SolveParams) = nullptr;
     int rec_len = 0, rec_off_c = 0, rec_off_v = 0, rec_kp = 0;
     void (*asm_kernel)(const AsmParams) = nullptr;
-    int solve_wpb = 1;
+    int solve_wpb = 1, solve_blocks = 16;
     size_t solve_smem = 0, asm_smem = 0;
     int pack_len = 0, asm_threads = 128, asm_D = 0, asm_nevents = 0;
     int* d_asm_events = nullptr;
@@ -483,7 +483,7 @@ static void pick_fast(blfik_problem* p)
     p->rec_len = QpRec<NV, KP>::LEN, p->rec_off_c = QpRec<NV, KP>::cvec, p->rec_off_v = QpRec<NV, KP>::vec;
     p->rec_kp = KP;
     p->asm_kernel = blfik_assemble_kernel<KP>;
-    p->solve_wpb = SolveDims<NV, KP>::WPB;
+    p->solve_wpb = SolveDims<NV, KP>::WPB, p->solve_blocks = SolveDims<NV, KP>::BLOCKS;
     p->solve_smem = (size_t)SolveDims<NV, KP>::WPB * SolveLayout<NV, KP>::TOTAL * sizeof(double);
     p->F = make_fast_layout<NV, KP>(p->n + 1);
     // the control-law buffer ([ntasks][12]) lives in the U region during K2
@@ -1487,11 +1487,12 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
             if (rc) return rc;
         }
         AsmParams A;
+        SolveParams S;
         A.T = P, A.qp = p->d_qp, A.rec_len = p->rec_len, A.K = p->K, A.off_c = p->rec_off_c, A.off_v = p->rec_off_v;
         A.model_pack = p->d_model_pack, A.pack_len = p->pack_len;
         A.sh_jump = p->F.sh_jump, A.sh_lod = p->F.sh_lod, A.sh_anc = p->F.sh_anc, A.sh_msub = p->F.sh_msub;
         A.events = p->d_asm_events, A.nevents = p->asm_nevents;
-        SolveParams S;
+        A.work_counter = S.work_counter = p->work_counter + counter_slot;   // launches that may overlap use different slots
         S.T = P, S.qp = p->d_qp, S.prefetch_ahead = p->num_sms * 16, S.nv = p->nv, S.K = p->K;
         for (int r = 0; r < 32; r++) S.evec[r] = 1.0;
         for (const HostTask& h : p->tasks)
@@ -1501,7 +1502,8 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         { const char* e = getenv("BLFIK_PDAS_FIRST"); S.pdas_first = e ? atoi(e) : 1; }
         { const char* e = getenv("BLFIK_MAX_ITERS"); if (e) S.max_total_iters = atoi(e); }
         { const char* e = getenv("BLFIK_MAX_AS"); if (e) S.max_as_iters = atoi(e); }
-        const int agrid = (int)((count + p->asm_threads - 1) / p->asm_threads), sgrid = (int)((count + p->solve_wpb - 1) / p->solve_wpb);
+        const long long swant = (count + p->solve_wpb - 1) / p->solve_wpb, scap = (long long)p->num_sms * p->solve_blocks;
+        const int agrid = (int)((count + p->asm_threads - 1) / p->asm_threads), sgrid = (int)(swant < scap ? swant : scap);
         for (int tick = 0; tick < nticks; tick++) {
             A.tick = S.tick = tick;
             A.tnow = p->time + tick * dt;

@@ -44,6 +44,7 @@ struct AsmParams {
     int nevents;
     int tick;                   // index of this tick inside a multi-tick launch (0: first)
     double tnow;
+    int* work_counter;          // kernel B's hand-out counter: zeroed here, one launch ahead
 };
 
 constexpr int kAsmMaxDense = 10;   // dense tasks the assemble kernel keeps frame origins for
@@ -53,6 +54,7 @@ constexpr int kAsmMaxDepth = 12;   // levels of its link stack (tree depth + 1)
 struct SolveParams {
     TickParams T;
     const double* qp;           // [N][QpRec::LEN]
+    int* work_counter;          // next robot to hand out, relative to T.first
     int prefetch_ahead;         // a block asks the L2 for the record of the robot this many places further on (the blocks in flight)
     double evec[32];            // E_r of the dense rows: 0 (equality) or 1 / weight (cost); 1 on the padding rows
     int nv, K;
@@ -332,14 +334,19 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     if (threadIdx.x < 32) s_evec[threadIdx.x] = SP.evec[threadIdx.x];
     __syncthreads();
-    const long long robot = P.first + (long long)blockIdx.x * SolveDims<NV, KP>::WPB + wib;
-    if (robot >= P.N) return;
+    double* base = smem + (size_t)wib * SL::TOTAL;
+    // Persistent warps: each takes its next robot from a device counter (zeroed by the assemble kernel of the same tick), so
+    // a slot is never idle between two robots (with one block per robot 13.6 of 16 warps were resident on average).
+  for (;;) {
+    long long robot = 0;
+    if (lane == 0) robot = P.first + atomicAdd(SP.work_counter, 1);
+    robot = __shfl_sync(kFull, robot, 0);
+    if (robot >= P.N) break;
     int worst = 0, iters_prev = 0;
     if (SP.tick > 0) {
         worst = P.status[robot], iters_prev = P.iters[robot];
-        if (worst == 2) return;   // a failed tick ended this robot's rollout: nu stays zero, the state where the failure happened
+        if (worst == 2) continue;   // a failed tick ended this robot's rollout: nu stays zero, the state where the failure happened
     }
-    double* base = smem + (size_t)wib * SL::TOTAL;
     double* Ns = base + SL::R1;
     double* MA = base + SL::R2;
     double* dinv = base + SL::dinv;
@@ -351,8 +358,8 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
     const bool mine = lane < nv;
     const bool joint = mine && lane >= 6;
     const double* rec = SP.qp + (size_t)robot * Rec::LEN;
-    // Ask the L2 for the record of the robot that takes this slot a few robots from now: that block then starts on L2 hits
-    // instead of a cold DRAM read (the blocks are not persistent, so there is no "next robot" of this warp to fetch).
+    // Ask the L2 for the record of the robot that some warp takes about one robot-time from now: its loads then hit the L2
+    // instead of reading DRAM cold (which robot this very warp gets next is not known: the hand-out is dynamic).
     if (robot + SP.prefetch_ahead < P.N) {
         const char* nxt = reinterpret_cast<const char*>(rec + (size_t)SP.prefetch_ahead * Rec::LEN);
         for (int l = lane * 128; l < Rec::LEN * 8; l += 32 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + l));
@@ -577,6 +584,8 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
         if (P.status_host) P.status_host[robot] = worst;
         P.iters[robot] = iters_prev + iters;
     }
+    __syncwarp();
+  }
 }
 
 }  // namespace blfik
