@@ -41,6 +41,7 @@ EXPORTS = [
     "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline", "blfik_set_setpoint_cubic_spline", "blfik_evaluate_setpoint",
     "blfik_packed_record_len_ex", "blfik_packed_offset_ex", "blfik_packed_part_len",
     "blfik_set_setpoint_shared", "blfik_kernel_timing", "blfik_get_kernel_times", "blfik_host_alloc", "blfik_host_free",
+    "blfik_set_weight_schedule", "blfik_get_weight",
 ]
 
 
@@ -258,6 +259,19 @@ class Problem:
     def set_setpoint(self, task: int, data):
         ptr, dev = _ptr(data)
         _check(self.L.blfik_set_setpoint(self.handle, int(task), ptr, MEM_DEVICE if dev else MEM_HOST))
+
+    def set_weight_schedule(self, task: int, target, settling_time: float):
+        """first-order approach of the task's weight to ``target`` (a = 3 / settling_time), one ForwardEuler step per tick on the
+        device side of a multi-tick launch (MultiStateWeightProvider / FirstOrderSmoother); settling_time <= 0: off"""
+        tg = None if target is None else _f64(np.asarray(target, dtype=np.float64).reshape(-1))
+        self.L.blfik_set_weight_schedule.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_double]
+        _check(self.L.blfik_set_weight_schedule(self.handle, int(task), None if tg is None else tg.ctypes.data, float(settling_time)))
+
+    def get_weight(self, task: int, rows: int):
+        w = np.empty(rows)
+        self.L.blfik_get_weight.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+        _check(self.L.blfik_get_weight(self.handle, int(task), w.ctypes.data))
+        return w
 
     def set_setpoint_shared(self, task: int, record):
         """one set-point for every robot of the batch (a single record of setpoint_len doubles); the task then leaves the packed

@@ -329,8 +329,9 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
                         const double* sp = task_record(P, tk, robot);
                         const double bj = (task_compact(P, tk) ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - sj);
                         if (tk.priority == 1) {
-                            dh += tk.weight[j];
-                            gd += tk.weight[j] * bj;
+                            const double wj = t == A.jw_task ? A.jw[j] : tk.weight[j];
+                            dh += wj;
+                            gd += wj * bj;
                         } else {
                             lo = fmax(lo, bj), hi = fmin(hi, bj);
                         }

@@ -325,6 +325,8 @@ struct HostTask {
     int sp_nk = 0, sp_cap = 0;       // quintic-spline generator: knots in force (0: off), knots the buffers hold
     double *d_sp_times = nullptr, *d_sp_fac = nullptr, *d_sp_coef = nullptr;
     bool setpoint_set = false;
+    std::vector<double> sched_target;  // weight schedule (blfik_set_weight_schedule): first-order approach of `weight` to this vector ...
+    double sched_a = 0.0;              // ... at rate a = 3 / settling_time per second; 0: no schedule
     bool shared = false;             // batch-shared set-point: one record for all robots, not part of the packed records
     double* d_setpoint = nullptr;
     double *d_kp_joint = nullptr, *d_weight = nullptr, *d_klim = nullptr, *d_upper = nullptr, *d_lower = nullptr;
@@ -1380,6 +1382,43 @@ extern "C" int blfik_set_weight(blfik_problem* p, int32_t t, const double* weigh
     return BLFIK_OK;
 }
 
+extern "C" int blfik_set_weight_schedule(blfik_problem* p, int32_t t, const double* target, double settling_time)
+{
+    CHECK_P(p, "blfik_set_weight_schedule");
+    CHECK_TASK(p, t, "blfik_set_weight_schedule");
+    HostTask& h = p->tasks[t];
+    if (h.d.priority != 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_weight_schedule] task %d is a hard constraint; only priority-1 tasks have a weight", t);
+    if (!(settling_time > 0.0) || !target) {   // off: the weight stays where the schedule has brought it
+        h.sched_a = 0.0, h.sched_target.clear();
+        return BLFIK_OK;
+    }
+    h.sched_target.assign(target, target + h.rows);
+    h.sched_a = 3.0 / settling_time;   // FirstOrderSmoother.cpp:73-77
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_get_weight(blfik_problem* p, int32_t t, double* weight)
+{
+    CHECK_P(p, "blfik_get_weight");
+    CHECK_TASK(p, t, "blfik_get_weight");
+    const HostTask& h = p->tasks[t];
+    if (h.d.priority != 1 || !weight) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_get_weight] task %d has no weight, or null buffer", t);
+    std::copy(h.weight.begin(), h.weight.end(), weight);
+    return BLFIK_OK;
+}
+
+// One ForwardEuler step of every scheduled weight (FirstOrderSmoother::advance: x += dt (a u - a x)); true if any weight moved.
+static bool step_weight_schedules(blfik_problem* p, double dt)
+{
+    bool any = false;
+    for (HostTask& h : p->tasks) {
+        if (h.sched_a == 0.0) continue;
+        for (size_t r = 0; r < h.weight.size(); r++) h.weight[r] += dt * (h.sched_a * h.sched_target[r] - h.sched_a * h.weight[r]);
+        any = true;
+    }
+    return any;
+}
+
 extern "C" int blfik_set_gains(blfik_problem* p, int32_t t, const double* kl, const double* ka, const double* kj)
 {
     CHECK_P(p, "blfik_set_gains");
@@ -1494,10 +1533,22 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         A.events = p->d_asm_events, A.nevents = p->asm_nevents;
         A.work_counter = S.work_counter = p->work_counter + counter_slot;   // launches that may overlap use different slots
         S.T = P, S.qp = p->d_qp, S.prefetch_ahead = p->num_sms * 16, S.nv = p->nv, S.K = p->K;
-        for (int r = 0; r < 32; r++) S.evec[r] = 1.0;
-        for (const HostTask& h : p->tasks)
-            if (is_dense(h.d.type))
-                for (int r = 0; r < h.rows; r++) S.evec[h.brow + r] = h.d.priority == 0 ? 0.0 : 1.0 / h.weight[r];
+        auto fill_weights = [&]() {
+            for (int r = 0; r < 32; r++) S.evec[r] = 1.0;
+            A.jw_task = -1;
+            for (size_t t = 0; t < p->tasks.size(); t++) {
+                const HostTask& h = p->tasks[t];
+                if (is_dense(h.d.type))
+                    for (int r = 0; r < h.rows; r++) S.evec[h.brow + r] = h.d.priority == 0 ? 0.0 : 1.0 / h.weight[r];
+                else if (h.d.type == BLFIK_TASK_JOINT_TRACKING && h.d.priority == 1 && h.sched_a != 0.0) {
+                    // a scheduled joint-space weight travels with the launch (the device copy of the task keeps the old one
+                    // until the next refresh); one such task per problem
+                    A.jw_task = (int)t;
+                    for (int j = 0; j < 32; j++) A.jw[j] = j < (int)h.weight.size() ? h.weight[j] : 0.0;
+                }
+            }
+        };
+        fill_weights();
         S.max_as_iters = p->max_as_iters, S.max_polish_iters = p->max_polish_iters, S.max_total_iters = p->max_total_iters;
         { const char* e = getenv("BLFIK_PDAS_FIRST"); S.pdas_first = e ? atoi(e) : 1; }
         { const char* e = getenv("BLFIK_MAX_ITERS"); if (e) S.max_total_iters = atoi(e); }
@@ -1507,6 +1558,10 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         for (int tick = 0; tick < nticks; tick++) {
             A.tick = S.tick = tick;
             A.tnow = p->time + tick * dt;
+            if (step_weight_schedules(p, dt)) {   // MultiStateWeightProvider::advance() of every period, then the solver reads the weight
+                fill_weights();
+                p->tasks_dirty = true;            // the device copies of the weights follow at the next refresh
+            }
             const bool timed = p->timing && tick == nticks - 1 && count == p->N;
             if (timed) CU(cudaEventRecord(p->ev_t[0], stream));
             if (asm_stream && asm_done) {
@@ -1526,6 +1581,21 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         }
         CU(cudaGetLastError());
         return BLFIK_OK;
+    }
+    {
+        bool scheduled = false;
+        for (const HostTask& h : p->tasks) scheduled |= h.sched_a != 0.0;
+        if (scheduled) {
+            // A single kernel cannot change a weight between its ticks (only the two-launch path above, whose ticks are
+            // separate launches, can): one tick per call here, the stepped weight uploaded before it.
+            if (nticks > 1)
+                return fail(BLFIK_ERR_UNSUPPORTED, "[blfik_tick] a weight schedule inside a multi-tick launch needs the two-launch kernel path "
+                                                   "(nv <= 32, <= 32 dense rows, kernel path 0); tick once per call instead");
+            step_weight_schedules(p, dt);
+            p->tasks_dirty = true;
+            const int rc = refresh_tasks(p);
+            if (rc) return rc;
+        }
     }
     if (p->fast_kernel && (p->path == 0 || p->path == 2)) {
         FastParams FP;

@@ -45,6 +45,8 @@ struct AsmParams {
     int tick;                   // index of this tick inside a multi-tick launch (0: first)
     double tnow;
     int* work_counter;          // kernel B's hand-out counter: zeroed here, one launch ahead
+    int jw_task;                // a JointTrackingTask whose weight comes with the launch (weight schedule), -1: none
+    double jw[32];
 };
 
 constexpr int kAsmMaxDense = 10;   // dense tasks the assemble kernel keeps frame origins for

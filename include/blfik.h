@@ -251,6 +251,15 @@ int blfik_set_weight(blfik_problem* problem, int32_t task, const double* weight)
 int blfik_set_gains(blfik_problem* problem, int32_t task, const double* kp_linear,
                     const double* kp_angular, const double* kp_joint);
 int blfik_set_controller_mode(blfik_problem* problem, int32_t task, int32_t enabled);
+/* replaces a MultiStateWeightProvider / FirstOrderSmoother on the task's weight port (MultiStateWeightProvider.cpp:22-134,
+ * FirstOrderSmoother.cpp:60-115) for ticks that run without the host in between: from its current value the weight moves to
+ * `target` [rows] along dx = -a x + a u, a = 3 / settling_time, one ForwardEuler step of dt at the start of every tick --
+ * what provider->advance() followed by ik->advance() does in the reference's loop.  Inside a multi-tick launch the weight
+ * therefore changes from tick to tick (two-launch kernel path; the other kernels take one tick per call with a schedule
+ * in force).  settling_time <= 0 or target = NULL ends the schedule, the weight stays where it is; blfik_set_weight sets it
+ * outright.  blfik_get_weight reads the current value.                                                              */
+int blfik_set_weight_schedule(blfik_problem* problem, int32_t task, const double* target, double settling_time);
+int blfik_get_weight(blfik_problem* problem, int32_t task, double* weight);
 /* replaces the upper_limits / lower_limits / klim / sampling_time keys of JointLimitsTask (JointLimitsTask.cpp:136-198)
  * and JointVelocityLimitsTask (JointVelocityLimitsTask.cpp:111-124) after construction; NULL / 0 keeps a value        */
 int blfik_set_limits(blfik_problem* problem, int32_t task, const double* upper_limits,

@@ -1851,3 +1851,54 @@ def test_batch_shared_setpoint_equals_per_robot_setpoints():
         prob.tick(1, w.dt, integrate=True)
         assert np.array_equal(prob.get_output(), nu_ref)
         prob.close()
+
+
+def test_weight_schedule_inside_a_multi_tick_launch():
+    """blfik_set_weight_schedule (MultiStateWeightProvider / FirstOrderSmoother on the device side): a 40-tick closed-loop launch
+    in which the chest and the postural weights move towards new values is bit-identical to 40 single ticks between which the
+    host steps the same first-order system and calls set_weight -- the reference's loop, provider->advance() then ik->advance()
+    (MultiStateWeightProvider.cpp:131, QPInverseKinematics.cpp:450-451).  The other kernels refuse the multi-tick form."""
+    w = W.config(3)
+    N, NT, dt = 300, 40, 0.01
+    inp = W.synth_inputs(w, N, 3)
+    model = capi.Model(w.model)
+    n = w.model.n
+    w_chest0, w_reg0 = np.array([5.0, 5.0, 5.0]), np.asarray(w.tasks[6].weight, dtype=np.float64)
+    tg_chest, tg_reg, Ts = np.array([0.5, 20.0, 5.0]), w_reg0 * 3.0, 0.2
+    # the reference's loop on the host
+    ref = capi.Problem(model, w.tasks, N)
+    ref.set_inputs(inp)
+    wc, wr, a = w_chest0.copy(), w_reg0.copy(), 3.0 / Ts
+    for _ in range(NT):
+        wc = wc + dt * (a * tg_chest - a * wc)
+        wr = wr + dt * (a * tg_reg - a * wr)
+        ref.set_weight(5, wc)
+        ref.set_weight(6, wr)
+        ref.tick(1, dt, integrate=True, warm_start=True)
+    nu_ref, state_ref = ref.get_output(), ref.get_state()
+    ref.close()
+    prob = capi.Problem(model, w.tasks, N)
+    prob.set_inputs(inp)
+    prob.set_weight_schedule(5, tg_chest, Ts)
+    prob.set_weight_schedule(6, tg_reg, Ts)
+    prob.tick(NT, dt, integrate=True, warm_start=True)
+    assert np.array_equal(prob.get_weight(5, 3), wc) and np.array_equal(prob.get_weight(6, n), wr)
+    assert np.array_equal(prob.get_output(), nu_ref)
+    for x, y in zip(prob.get_state(), state_ref):
+        assert np.array_equal(x, y)
+    assert np.abs(wc - w_chest0).max() > 1.0                      # and the weights did move
+    prob.set_weight_schedule(5, None, 0.0)
+    prob.set_weight_schedule(6, None, 0.0)
+    prob.tick(1, dt)                                              # schedules off: the weights stay where they are
+    assert np.array_equal(prob.get_weight(5, 3), wc)
+    prob.close()
+    fused = capi.Problem(model, w.tasks, N)
+    fused.set_kernel_path(2)
+    fused.set_inputs(inp)
+    fused.set_weight_schedule(5, tg_chest, Ts)
+    with pytest.raises(capi.BlfikError) as e:
+        fused.tick(3, dt, integrate=True)
+    assert e.value.code == -3
+    fused.tick(1, dt, integrate=True)                             # one tick per call is fine on every kernel
+    assert np.array_equal(fused.get_weight(5, 3), w_chest0 + dt * (a * tg_chest - a * w_chest0))
+    fused.close()
