@@ -309,18 +309,27 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(step_fn, steps, st=stream):
-        total = 0.0
+    def timed(step_fn, steps, st=stream, queued=False):
+        """Sum of the K step durations, each between its own pair of CUDA events on the stream the step runs on; the L2 flush
+        between steps is outside the events.  queued=True (device-resident step): flush, events and steps are all enqueued on
+        that one stream without a host synchronisation in between, so the device time of a step is measured, not the host's
+        call latency in front of an idle GPU.  queued=False (host-buffer step): the call is synchronous by design, every step is
+        timed from a quiet device."""
+        evs = []
         for _ in range(steps):
-            flush.fill_(1)                            # evict L2 (126 MB) between steps, untimed
-            torch.cuda.synchronize()
+            with torch.cuda.stream(st):
+                flush.fill_(1)                        # evict L2 (126 MB) between steps, untimed
+            if not queued:
+                torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(st)
             step_fn()
             e1.record(st)
-            e1.synchronize()
-            total += e0.elapsed_time(e1)
-        return total
+            if not queued:
+                e1.synchronize()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in evs)
 
     steps = args.steps if not rollout else max(1, min(args.steps, 10))
     for _ in range(max(3, args.warmup) if not rollout else 1):
@@ -332,7 +341,7 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
         sampler.start()
     launches0 = prob.launch_count
     barrier()
-    ms_dev = timed(device_step, steps)
+    ms_dev = timed(device_step, steps, queued=True)
     barrier()
     launches = prob.launch_count - launches0
     status, iters = prob.get_status()
