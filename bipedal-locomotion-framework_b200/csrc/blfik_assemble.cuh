@@ -23,7 +23,7 @@ namespace blfik {
 // Tasks this kernel does not assemble: DistanceTask (its direction needs both frames before any column) and
 // AngularMomentumTask (needs the CoM before any column): problems holding one take the fused kernel.
 template <int KP>
-__global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
+__global__ void __launch_bounds__(128, 4) blfik_assemble_kernel(const AsmParams A)
 {
     extern __shared__ double smem[];
     const TickParams& P = A.T;
@@ -72,9 +72,13 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
     const int lane = tid & 31;
     double* tile = smem + A.pack_len + tlen + ev_doubles + 4 * P.ntasks + (tid >> 5) * 32 * TS;   // this warp's [32][TS] staging tile
     double* trow = tile + lane * TS;
-    double l_stk[kAsmMaxDepth * 12], l_acc[kAsmMaxDepth * 3], l_pf[kAsmMaxDense * 3], cv[KP];
-#define STK(d, c) l_stk[(d) * 12 + (c)]
+    // per level of the walk: world axis (3) and origin (3) of the open link, CoM sum of its subtree (3); the rotation of an open
+    // link is only kept where the walk comes back to (links with two children or more), the others hand theirs to their only
+    // child in registers
+    double l_stk[kAsmMaxDepth * 6], l_acc[kAsmMaxDepth * 3], l_rot[kAsmMaxDepth * 9], l_pf[kAsmMaxDense * 3];
+#define STK(d, c) l_stk[(d) * 6 + (c)]
 #define ACC(d, c) l_acc[(d) * 3 + (c)]
+#define ROT(d, c) l_rot[(d) * 9 + (c)]
 #define PF(o, c) l_pf[(o) * 3 + (c)]
 
     const long long wfirst = P.first + (long long)blockIdx.x * nthr + (tid & ~31);   // first robot of this warp
@@ -86,6 +90,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
     const unsigned valid = __ballot_sync(kFull, active);
     if (valid == 0u) return;
     double* wq = A.qp + (size_t)wfirst * A.rec_len;
+    double* const myrhs = A.qp + (size_t)robot * A.rec_len + A.off_c;   // right-hand sides go out one by one as they are known
     // The 32 x LEN doubles the lanes have put into their tile rows go to doubles [off, off + LEN) of the 32 records: sixteen
     // lanes per robot write sixteen consecutive doubles (two robots per store instruction), and what is left of a row beyond
     // a multiple of sixteen goes out lane by lane.
@@ -112,7 +117,9 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
     using LenCol = std::integral_constant<int, KP>;
     using LenVec = std::integral_constant<int, 16>;
 #pragma unroll
-    for (int r = 0; r < KP; r++) trow[r] = 0.0, cv[r] = 0.0;   // rows beyond K stay zero in every column
+    for (int r = 0; r < KP; r++) trow[r] = 0.0;   // rows beyond K stay zero in every column
+    if (active)
+        for (int r = A.K; r < KP; r++) myrhs[r] = 0.0;
 
     // ---- state
     double* bp = P.base_pos + 3 * robot;
@@ -154,7 +161,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
                 for (int c = 0; c < 3; c++) {
                     const double pc = exo ? sp0[tk.fb_off + c] : pf[c];
                     const double bl = lin_on ? sp[voff + c] + tk.kp_lin[c] * (sp[c] - pc) : sp[voff + c];
-                    if (mp[c] >= 0) cv[mp[c]] = bl;
+                    if (mp[c] >= 0 && active) myrhs[mp[c]] = bl;
                 }
             }
             if (tk.type == T_SE3 || tk.type == T_SO3) {
@@ -167,20 +174,22 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
                 }
                 so3_control(Rf, qd, wff, tk.kp_ang, tk.type == T_SO3 ? true : (tk.enabled != 0), ba);
 #pragma unroll
-                for (int c = 0; c < 3; c++) cv[mp[3 + c]] = ba[c];
+                for (int c = 0; c < 3; c++)
+                    if (active) myrhs[mp[3 + c]] = ba[c];
             } else if (tk.type == T_GRAVITY) {   // GravityTask.cpp:149-185
                 double zb[3] = {sp[0], sp[1], sp[2]}, fb[3] = {sp[3], sp[4], sp[5]}, z[3], ff[3];
                 const double zn = rsqrt(zb[0] * zb[0] + zb[1] * zb[1] + zb[2] * zb[2]);
                 zb[0] *= zn, zb[1] *= zn, zb[2] *= zn;
                 mat3_vec(Rf, zb, z);
                 mat3_vec(Rf, fb, ff);
-                cv[mp[3]] = ff[0] + tk.kp_lin[0] * z[1];
-                cv[mp[4]] = ff[1] - tk.kp_lin[0] * z[0];
+                if (active) myrhs[mp[3]] = ff[0] + tk.kp_lin[0] * z[1], myrhs[mp[4]] = ff[1] - tk.kp_lin[0] * z[0];
             }
         }
     };
 
     // ---- K1 + the joint columns of K2: the walk
+    double Rcur[9], pcur[3];   // pose of the link visited last
+    int dcur = 0;
     {
         const double qb[4] = {bq[0], bq[1], bq[2], bq[3]};
         double R0[9];
@@ -191,15 +200,15 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
         double cw[3];
         mat3_vec(R0, cl, cw);
 #pragma unroll
-        for (int c = 0; c < 9; c++) STK(0, c) = R0[c];
+        for (int c = 0; c < 9; c++) ROT(0, c) = R0[c], Rcur[c] = R0[c];
 #pragma unroll
-        for (int c = 0; c < 3; c++) STK(0, 9 + c) = p0[c], ACC(0, c) = lp[18] * (p0[c] + cw[c]);
+        for (int c = 0; c < 3; c++) STK(0, 3 + c) = p0[c], pcur[c] = p0[c], ACC(0, c) = lp[18] * (p0[c] + cw[c]);
         frames_on_link(0, R0, p0);
     }
     for (int ev = 0; ev < A.nevents; ev++) {
         const int code = s_ev[ev], k = code & 0xff, d = (code >> 8) & 0xff;
         const double* lp = s_link + 20 * k;
-        if ((code >> 16) == 0) {
+        if (((code >> 16) & 1) == 0) {
             // visit: pose of link k from its parent's (one level up)
             const double a0 = lp[12], a1 = lp[13], a2 = lp[14];
             double sn, cs;
@@ -209,33 +218,48 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
             Rj[0] = cs + a0 * a0 * v, Rj[1] = a0 * a1 * v - a2 * sn, Rj[2] = a0 * a2 * v + a1 * sn;
             Rj[3] = a1 * a0 * v + a2 * sn, Rj[4] = cs + a1 * a1 * v, Rj[5] = a1 * a2 * v - a0 * sn;
             Rj[6] = a2 * a0 * v - a1 * sn, Rj[7] = a2 * a1 * v + a0 * sn, Rj[8] = cs + a2 * a2 * v;
+            double pp[3];
+            if (d == dcur + 1) {   // the parent is the link visited last: its pose is still in registers
 #pragma unroll
-            for (int c = 0; c < 9; c++) X[c] = lp[c], Rp[c] = STK(d - 1, c);
+                for (int c = 0; c < 9; c++) Rp[c] = Rcur[c];
+#pragma unroll
+                for (int c = 0; c < 3; c++) pp[c] = pcur[c];
+            } else {               // the walk came back to a link with several children
+#pragma unroll
+                for (int c = 0; c < 9; c++) Rp[c] = ROT(d - 1, c);
+#pragma unroll
+                for (int c = 0; c < 3; c++) pp[c] = STK(d - 1, 3 + c);
+            }
+#pragma unroll
+            for (int c = 0; c < 9; c++) X[c] = lp[c];
             mat3_mul(X, Rj, Rl);
             mat3_mul(Rp, Rl, R);
-            const double xp[3] = {lp[9], lp[10], lp[11]}, cl[3] = {lp[15], lp[16], lp[17]};
-            double off[3], cw[3];
+            const double xp[3] = {lp[9], lp[10], lp[11]}, cl[3] = {lp[15], lp[16], lp[17]}, ax[3] = {a0, a1, a2};
+            double off[3], cw[3], aw[3];
             mat3_vec(Rp, xp, off);
             mat3_vec(R, cl, cw);
+            mat3_vec(R, ax, aw);
+            if (code & (1 << 17)) {   // two children or more: the rotation is needed again
 #pragma unroll
-            for (int c = 0; c < 9; c++) STK(d, c) = R[c];
+                for (int c = 0; c < 9; c++) ROT(d, c) = R[c];
+            }
+#pragma unroll
+            for (int c = 0; c < 9; c++) Rcur[c] = R[c];
 #pragma unroll
             for (int c = 0; c < 3; c++) {
-                p[c] = STK(d - 1, 9 + c) + off[c];
-                STK(d, 9 + c) = p[c];
+                p[c] = pp[c] + off[c];
+                pcur[c] = p[c];
+                STK(d, c) = aw[c], STK(d, 3 + c) = p[c];
                 ACC(d, c) = lp[18] * (p[c] + cw[c]);
             }
+            dcur = d;
             frames_on_link(k, R, p);
         } else {
             // close: column 6 + dof(k) of every dense task; the subtree's CoM sum goes up one level
             const int j = s_dol[k], col = 6 + j;
-            double R[9], p[3], ms[3], aw[3];
+            double p[3], ms[3], aw[3];
 #pragma unroll
-            for (int c = 0; c < 9; c++) R[c] = STK(d, c);
-#pragma unroll
-            for (int c = 0; c < 3; c++) p[c] = STK(d, 9 + c), ms[c] = ACC(d, c);
-            const double ax[3] = {lp[12], lp[13], lp[14]};
-            mat3_vec(R, ax, aw);
+            for (int c = 0; c < 3; c++) aw[c] = STK(d, c), p[c] = STK(d, 3 + c), ms[c] = ACC(d, c);
             for (int t = 0; t < P.ntasks; t++) {
                 const DevTask& tk = s_tasks[t];
                 const int* mp = s_map + 8 * t;
@@ -264,7 +288,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
     }
     // ---- the CoM task's right-hand side, then the base columns: MIXED base block [I, -S(p - p_B); 0, I]
     const double com[3] = {ACC(0, 0) * m.inv_total_mass, ACC(0, 1) * m.inv_total_mass, ACC(0, 2) * m.inv_total_mass};
-    const double pB[3] = {STK(0, 9), STK(0, 10), STK(0, 11)};
+    const double pB[3] = {STK(0, 3), STK(0, 4), STK(0, 5)};
     for (int t = 0; t < P.ntasks; t++) {
         const DevTask& tk = s_tasks[t];
         const int* mp = s_map + 8 * t;
@@ -281,7 +305,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
 #pragma unroll
         for (int c = 0; c < 3; c++) {   // CoMTask.cpp:192-203: b = v_ff + kp (p_d - p_com), measured CoM with exogenous feedback
             const double pc = tk.exo_pos ? sp0[tk.fb_off + c] : com[c];
-            if (mp[c] >= 0) cv[mp[c]] = sp[3 + c] + tk.kp_lin[c] * (sp[c] - pc);
+            if (mp[c] >= 0 && active) myrhs[mp[c]] = sp[3 + c] + tk.kp_lin[c] * (sp[c] - pc);
         }
         PF(mp[6], 0) = com[0], PF(mp[6], 1) = com[1], PF(mp[6], 2) = com[2];
     }
@@ -309,9 +333,6 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
         }
         flush(c * KP, LenCol{});
     }
-#pragma unroll
-    for (int r = 0; r < KP; r++) trow[r] = cv[r];
-    flush(A.off_c, LenCol{});
 
     // ---- K2: joint-space tasks -> diagonal cost, its gradient, the box; four variables per pass, [variable][dh gd lo hi]
     for (int g = 0; g < 8; g++) {
@@ -350,6 +371,7 @@ __global__ void __launch_bounds__(128) blfik_assemble_kernel(const AsmParams A)
     }
 #undef STK
 #undef ACC
+#undef ROT
 #undef PF
 }
 

@@ -914,7 +914,7 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
                         auto& top = stack.back();
                         if (top.second < kids[top.first].size()) {
                             const int c = kids[top.first][top.second++];
-                            ev.push_back((0 << 16) | (model->depth[c] << 8) | c);
+                            ev.push_back((0 << 16) | ((kids[c].size() >= 2 ? 1 : 0) << 17) | (model->depth[c] << 8) | c);   // bit 17: the walk comes back to this link
                             stack.push_back({c, 0});
                         } else {
                             if (top.first != 0) ev.push_back((1 << 16) | (model->depth[top.first] << 8) | top.first);
