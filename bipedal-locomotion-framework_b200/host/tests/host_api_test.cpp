@@ -719,6 +719,101 @@ template <class Planner> static void so3PlannerSection(bool body, bool initialVe
     REQUIRE(near(planner.getOutput().rotation, R1));
 }
 
+static void testSO3Planner();
+// Planners::SwingFootPlanner, replaying src/Planners/tests/SwingFootPlannerTest.cpp (the reference's test only requires that
+// advance() succeeds over the whole contact list, in its three scenarios) plus what that trajectory must satisfy: the contact
+// pose while in contact, continuity, the apex height, and -- the property the device hand-over rests on -- that re-planning on
+// every advance() gives the curve planned once at take-off (planOnDevice).
+static Contacts::ContactList swingContactList(bool modified)
+{
+    Contacts::ContactList list;
+    auto rz = [](double a) { return SO3d::Exp({0.0, 0.0, a}); };
+    REQUIRE(list.addContact(SE3d({0.9, 0, 0}, rz(1.5708)), 0s, 300ms));
+    REQUIRE(list.addContact(SE3d({0.8899, 0.1345, 0.0600}, rz(1.7208)), 600ms, 1s + 500ms));
+    if (modified) REQUIRE(list.addContact(SE3d({0.5104, 0.415, 0.400}, rz(2.4)), 1s + 800ms, 2s + 700ms));
+    else REQUIRE(list.addContact(SE3d({0.8104, 0.3915, 0.1800}, rz(2.0208)), 1s + 800ms, 2s + 700ms));
+    REQUIRE(list.addContact(SE3d({0.6585, 0.6135, 0.3000}, rz(2.3208)), 3s, 3s + 900ms));
+    REQUIRE(list.addContact(SE3d({0.3261, 0.8388, 0.4800}, rz(2.7708)), 4s, 6s));
+    return list;
+}
+
+static void testSwingFootPlanner()
+{
+    using namespace BipedalLocomotion::Planners;
+    constexpr std::chrono::nanoseconds dT = 10ms;
+    for (const char* method : {"min_acceleration", "min_jerk"}) {
+        auto handler = std::make_shared<StdImplementation>();
+        handler->setParameter("sampling_time", dT), handler->setParameter("step_height", 0.1), handler->setParameter("foot_apex_time", 0.5);
+        handler->setParameter("foot_landing_velocity", 0.0), handler->setParameter("foot_landing_acceleration", 0.0);
+        handler->setParameter("interpolation_method", std::string(method));
+        const auto list = swingContactList(false), modifiedList = swingContactList(true);
+        for (int scenario = 0; scenario < 3; scenario++) {   // constant list, modified during contact, modified during swing
+            SwingFootPlanner planner;
+            REQUIRE(planner.initialize(handler));
+            REQUIRE(planner.setContactList(list));
+            SwingFootPlannerState prev;
+            double apex = -1.0;
+            SwingFootPlanner::DeviceSwing swing;
+            REQUIRE(planner.planOnDevice(list[0], swing));
+            std::unique_ptr<Math::Spline<Vector3d>> once;
+            if (swing.minJerk) once = std::make_unique<Math::QuinticSpline<Vector3d>>();
+            else once = std::make_unique<Math::CubicSpline<Vector3d>>();
+            REQUIRE(once->setInitialConditions(swing.initialVelocity, swing.initialAcceleration) && once->setFinalConditions(swing.finalVelocity, swing.finalAcceleration));
+            REQUIRE(once->setKnots(swing.positions, swing.times));
+            SO3PlannerInertial onceR;
+            REQUIRE(onceR.setInitialConditions(SO3Tangentd::Zero(), SO3Tangentd::Zero()) && onceR.setFinalConditions(SO3Tangentd::Zero(), SO3Tangentd::Zero()));
+            REQUIRE(onceR.setRotations(list[0].pose.R, swing.landingRotation, swing.duration));
+            for (std::chrono::nanoseconds time = list.firstContact()->activationTime; time < list.lastContact()->deactivationTime; time += dT) {
+                if (scenario == 1 && time == 1s) REQUIRE(planner.setContactList(modifiedList));
+                if (scenario == 2 && time == 1s + 600ms) REQUIRE(planner.setContactList(modifiedList));
+                REQUIRE(planner.advance());
+                REQUIRE(planner.isOutputValid());
+                const auto& out = planner.getOutput();
+                REQUIRE(out.time == time);
+                const auto& use = (scenario > 0 && time >= (scenario == 1 ? 1s : 1s + 600ms)) ? modifiedList : list;
+                const auto active = use.getActiveContact(time);
+                REQUIRE(out.isInContact == (active != use.cend()));
+                if (out.isInContact) {
+                    for (int c = 0; c < 3; c++) REQUIRE(out.transform.p[c] == active->pose.p[c] && out.mixedVelocity.linear[c] == 0.0);
+                } else if (time > list.firstContact()->activationTime) {
+                    for (int c = 0; c < 3; c++) {   // one sample apart: the foot moves by what its speed allows (trapezoid + curvature)
+                        const double moved = std::abs(out.transform.p[c] - prev.transform.p[c]);
+                        const double speed = std::max(std::abs(out.mixedVelocity.linear[c]), std::abs(prev.mixedVelocity.linear[c]));
+                        REQUIRE(moved <= speed * 0.01 * 1.05 + 1e-4);
+                    }
+                }
+                if (time >= 300ms && time < 600ms) {   // the first swing: the curve re-planned every period is the one planned at take-off
+                    Vector3d p, v;
+                    REQUIRE(once->evaluatePoint(time, p, v));
+                    for (int c = 0; c < 3; c++) REQUIRE(std::abs(out.transform.p[c] - p[c]) < 1e-9 && std::abs(out.mixedVelocity.linear[c] - v[c]) < 1e-7);
+                    apex = std::max(apex, out.transform.p[2]);
+                    SO3d R;
+                    SO3Tangentd w, dw;
+                    REQUIRE(onceR.evaluatePoint(time - swing.times[0], R, w, dw));
+                    const Vector3d dr = (R.inverse() * out.transform.R).Log();
+                    for (int c = 0; c < 3; c++) REQUIRE(std::abs(dr[c]) < 1e-9 && std::abs(w.w[c] - out.mixedVelocity.angular[c]) < 1e-7);
+                }
+                prev = out;
+            }
+            REQUIRE(std::abs(apex - 0.16) < 1e-3);   // step_height above the higher contact (z = 0.06), reached at half swing
+            log()->setLevel(Logger::Level::off);
+            REQUIRE_FALSE(planner.advance());        // past the last contact (:503-509)
+            log()->setLevel(Logger::Level::warn);
+        }
+    }
+    log()->setLevel(Logger::Level::off);
+    SwingFootPlanner planner;
+    auto bad = std::make_shared<StdImplementation>();
+    bad->setParameter("sampling_time", dT), bad->setParameter("step_height", 0.1), bad->setParameter("foot_apex_time", 1.5);
+    REQUIRE_FALSE(planner.initialize(bad));
+    REQUIRE_FALSE(planner.advance());                                      // empty contact list
+    Contacts::ContactList list;
+    REQUIRE_FALSE(list.addContact(SE3d(), 2s, 1s));                         // activation after deactivation
+    REQUIRE(list.addContact(SE3d(), 0s, 1s));
+    REQUIRE_FALSE(list.addContact(SE3d(), 500ms, 2s));                      // overlap
+    log()->setLevel(Logger::Level::warn);
+}
+
 static void testSO3Planner()
 {
     using namespace BipedalLocomotion::Planners;
@@ -844,6 +939,73 @@ static void testSetPointSpline(const char* modelPath, std::size_t N)
             for (std::size_t k = 0; k < ikDev.getBatchOutput().size(); k++) worstMj = std::max(worstMj, std::abs(ikDev.getBatchOutput()[k] - ikHost.getBatchOutput()[k]));
         }
         REQUIRE(worstMj < 1e-8);
+        REQUIRE(handDev->setSetPointMinimumJerk({}, 0ns) && ikDev.advance());
+    }
+    // A swing phase handed to the device at take-off (SwingFootPlanner::planOnDevice: one 3D spline for the origin + the landing
+    // rotation for the minimum-jerk generator) against the reference's loop: planner.advance() every period on the host, its
+    // output given to setSetPoint.  One planner per robot, same contact timing, different landing spots.
+    {
+        using namespace BipedalLocomotion::Planners;
+        constexpr std::chrono::nanoseconds dT = 10ms;
+        auto ph = std::make_shared<StdImplementation>();
+        ph->setParameter("sampling_time", dT), ph->setParameter("step_height", 0.03), ph->setParameter("foot_apex_time", 0.4);
+        ph->setParameter("interpolation_method", std::string("min_jerk"));
+        std::vector<SwingFootPlanner> planners(N);
+        std::vector<QuinticSpline<Vector3d>> origin(N);
+        std::vector<double> landing(N * 13, 0.0);
+        std::chrono::nanoseconds duration{0};
+        for (std::size_t i = 0; i < N; i++) {
+            Contacts::ContactList list;
+            const SE3d land({pose[i].p[0] + 0.02 * (i + 1), pose[i].p[1] - 0.015, pose[i].p[2] + 0.01}, SO3d::Exp({0.03, 0.05, 0.1 * (i + 1)}) * pose[i].R);
+            // (every component of the rotation error non-zero: SO3Planner finds the scalar between a boundary velocity and the error
+            // from the first component whose ratio is finite, SO3Planner.tpp:81-89 -- with an error component that is rounding noise
+            // that ratio is noise too, in the reference as in the host class that mirrors it; the device generator plans once)
+            REQUIRE(list.addContact(pose[i], 0s, 300ms) && list.addContact(land, 600ms, 2s));
+            REQUIRE(planners[i].initialize(ph) && planners[i].setContactList(list));
+            SwingFootPlanner::DeviceSwing swing;
+            REQUIRE(planners[i].planOnDevice(list[0], swing) && swing.minJerk);
+            REQUIRE(origin[i].setInitialConditions(swing.initialVelocity, swing.initialAcceleration) && origin[i].setFinalConditions(swing.finalVelocity, swing.finalAcceleration));
+            REQUIRE(origin[i].setKnots(swing.positions, swing.times));
+            const auto q = swing.landingRotation.quat().coeffs();
+            for (int c = 0; c < 3; c++) landing[i * 13 + c] = land.p[c];
+            for (int c = 0; c < 4; c++) landing[i * 13 + 3 + c] = q[c];
+            duration = swing.duration;
+            REQUIRE(handDev->setSetPoint(pose[i], SE3d::Tangent::Zero(), i));
+        }
+        REQUIRE(duration == 310ms);                                            // one period before the contact ends (createSE3Traj's previousTime)
+        REQUIRE(handDev->setSetPointSpline(origin) && handDev->setSetPointMinimumJerk(landing, duration));
+        REQUIRE(ikDev.setTime(290ms) && ikDev.advance());                      // the generators start here: tau = 0
+        double worstSwing = 0.0;
+        std::chrono::nanoseconds hostTime = 0ns;
+        for (const std::chrono::nanoseconds t : {300ms, 350ms, 420ms, 520ms, 590ms, 600ms, 800ms}) {
+            for (; hostTime <= t; hostTime += dT)
+                for (std::size_t i = 0; i < N; i++) REQUIRE(planners[i].advance());   // the planner is sampled every period, as in the reference's loop
+            for (std::size_t i = 0; i < N; i++) {
+                const auto& out = planners[i].getOutput();
+                REQUIRE(out.time == t);
+                REQUIRE(handHost->setSetPoint(out.transform, out.mixedVelocity, i));
+            }
+            REQUIRE(ikHost.advance());
+            REQUIRE(ikDev.setTime(t) && ikDev.advance());
+            double wt = 0.0;
+            for (std::size_t k = 0; k < ikDev.getBatchOutput().size(); k++) wt = std::max(wt, std::abs(ikDev.getBatchOutput()[k] - ikHost.getBatchOutput()[k]));
+            if (std::getenv("BLF_TEST_VERBOSE")) {
+                std::printf("swing t=%lld ms: max |dnu| %.3e\n", static_cast<long long>(t.count() / 1000000), wt);
+                for (int task = 0; task < 3; task++) {
+                    if (blfik_setpoint_len(ikDev.handle(), task) != 13) continue;
+                    std::vector<double> sp(N * 13);
+                    if (blfik_evaluate_setpoint(ikDev.handle(), task, std::chrono::duration<double>(t).count(), sp.data(), BLFIK_MEM_HOST) != BLFIK_OK) continue;
+                    const auto& out = planners[0].getOutput();
+                    const auto q = out.transform.R.quat().coeffs();
+                    std::printf("  task %d device sp: p %.6f %.6f %.6f q %.6f %.6f %.6f %.6f v %.4f %.4f %.4f w %.4f %.4f %.4f\n", task, sp[0], sp[1], sp[2], sp[3], sp[4], sp[5], sp[6], sp[7], sp[8], sp[9], sp[10], sp[11], sp[12]);
+                    std::printf("         host planner: p %.6f %.6f %.6f q %.6f %.6f %.6f %.6f v %.4f %.4f %.4f w %.4f %.4f %.4f\n", out.transform.p[0], out.transform.p[1], out.transform.p[2], q[0], q[1], q[2], q[3],
+                                out.mixedVelocity.linear[0], out.mixedVelocity.linear[1], out.mixedVelocity.linear[2], out.mixedVelocity.angular[0], out.mixedVelocity.angular[1], out.mixedVelocity.angular[2]);
+                }
+            }
+            worstSwing = std::max(worstSwing, wt);
+        }
+        REQUIRE(worstSwing < 1e-7);
+        handDev->clearSetPointSpline();
         REQUIRE(handDev->setSetPointMinimumJerk({}, 0ns) && ikDev.advance());
     }
 }
@@ -1050,6 +1212,7 @@ int main(int argc, char** argv)
     testWeightProviders();
     testSplines();
     testSO3Planner();
+    testSwingFootPlanner();
     if (gpu) {
         testTaskMatrices(argv[2]);
         testClosedLoop(argv[2], 1, false);
