@@ -41,7 +41,7 @@ EXPORTS = [
     "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline", "blfik_set_setpoint_cubic_spline", "blfik_evaluate_setpoint",
     "blfik_packed_record_len_ex", "blfik_packed_offset_ex", "blfik_packed_part_len",
     "blfik_set_setpoint_shared", "blfik_kernel_timing", "blfik_get_kernel_times", "blfik_host_alloc", "blfik_host_free",
-    "blfik_set_weight_schedule", "blfik_get_weight",
+    "blfik_set_weight_schedule", "blfik_get_weight", "blfik_integrate_acceleration_state", "blfik_dynamics",
 ]
 
 
@@ -120,6 +120,17 @@ def load():
         _lib.blfik_set_kernel_path.argtypes = [C.c_void_p, C.c_int32]
         _lib.blfik_get_kernel_path.argtypes = [C.c_void_p]
     return _lib
+
+
+def integrate_acceleration_state(p, q, s, dp, omega, ds, acc, dt: float, nsteps: int = 1, device: int = 0):
+    """FloatingBaseSystemAccelerationKinematics + ForwardEuler for a batch; returns the new (p, q, s, dp, omega, ds), the
+    arguments are left alone"""
+    lib = load()
+    N, n = s.shape
+    arrs = [np.array(a, dtype=np.float64, order="C", copy=True) for a in (p, q, s, dp, omega, ds, acc)]
+    lib.blfik_integrate_acceleration_state.argtypes = [C.c_int32, C.c_int64] + [C.c_void_p] * 7 + [C.c_double, C.c_int32, C.c_int32]
+    _check(lib.blfik_integrate_acceleration_state(int(n), int(N), *[a.ctypes.data for a in arrs], float(dt), int(nsteps), int(device)))
+    return arrs[:6]
 
 
 def measure_fp64_peak(device: int = 0, millis: float = 200.0) -> float:
@@ -454,6 +465,13 @@ class Problem:
         st, it = np.empty(self.N, dtype=np.int32), np.empty(self.N, dtype=np.int32)
         _check(self.L.blfik_get_status(self.handle, st.ctypes.data, it.ctypes.data, MEM_HOST))
         return st, it
+
+    def dynamics(self, gravity: float = 9.80665):
+        """free-floating mass matrix [N, nv, nv] and generalised gravity forces [N, nv] of the current state (MIXED)"""
+        M, G = np.empty((self.N, self.nv, self.nv)), np.empty((self.N, self.nv))
+        self.L.blfik_dynamics.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int32]
+        _check(self.L.blfik_dynamics(self.handle, M.ctypes.data, G.ctypes.data, float(gravity), MEM_HOST))
+        return M, G
 
     def count_unsolved(self) -> int:
         c = C.c_int64(0)

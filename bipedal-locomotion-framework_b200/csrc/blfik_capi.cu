@@ -139,6 +139,112 @@ __global__ void __launch_bounds__(256) blfik_integrate_kernel(int n, long long N
                          nu + (size_t)(n + 6) * robot, dt, lane);
 }
 
+// K4 at the acceleration level: FloatingBaseSystemAccelerationKinematics (state p, R, s, dp, omega, ds; input [dtwist; dds],
+// FloatingBaseSystemAccelerationKinematics.cpp:20-75) under ForwardEuler (ForwardEuler.h:72-124): every component moves by its
+// OLD derivative times dt, the rotation by the left-plus Exp(omega dt) R.  One warp per robot, nsteps steps with the input held.
+__global__ void __launch_bounds__(256) blfik_integrate_acceleration_kernel(int n, long long N, double* bp, double* bq, double* s, double* dp,
+                                                                           double* omega, double* ds, const double* acc, double dt, int nsteps)
+{
+    const int lane = threadIdx.x & 31;
+    const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long robot = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; robot < N; robot += warps) {
+        const double* a = acc + (size_t)(n + 6) * robot;
+        for (int k = 0; k < nsteps; k++) {
+            const double w[3] = {omega[3 * robot] * dt, omega[3 * robot + 1] * dt, omega[3 * robot + 2] * dt};
+            double dq[4], q[4] = {bq[4 * robot], bq[4 * robot + 1], bq[4 * robot + 2], bq[4 * robot + 3]}, qn[4];
+            so3_exp(w, dq);
+            quat_mul(dq, q, qn);
+            const double inv = 1.0 / sqrt(qn[0] * qn[0] + qn[1] * qn[1] + qn[2] * qn[2] + qn[3] * qn[3]);
+            __syncwarp();
+            if (lane < 3) {
+                bp[3 * robot + lane] += dp[3 * robot + lane] * dt;      // position by the old velocity ...
+                dp[3 * robot + lane] += a[lane] * dt;                   // ... velocity by the acceleration
+                omega[3 * robot + lane] += a[3 + lane] * dt;
+            }
+            if (lane < 4) bq[4 * robot + lane] = qn[lane] * inv;
+            for (int j = lane; j < n; j += 32) {
+                s[(size_t)n * robot + j] += ds[(size_t)n * robot + j] * dt;
+                ds[(size_t)n * robot + j] += a[6 + j] * dt;
+            }
+            __syncwarp();
+        }
+    }
+}
+
+// Free-floating mass matrix and generalised gravity forces in the MIXED representation (what iDynTree's
+// getFreeFloatingMassMatrix / generalizedGravityForces return to the TSID tasks: src/TSID/src/BaseDynamicsTask.cpp,
+// JointDynamicsTask.cpp).  One warp per robot, lane i owns row i (and i + 32):
+//   M = sum_k  m_k Jv_k' Jv_k + Jw_k' I_k^W Jw_k      (Jv_k: linear Jacobian of link k's CoM, Jw_k: its angular Jacobian)
+//   G = M_total J_com' (0, 0, g)
+__global__ void __launch_bounds__(256) blfik_dynamics_kernel(const KinParams P, double* mass_matrix, double* gravity, double g_acc)
+{
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const WM w = carve(smem + (size_t)wib * P.L.total, P.L);
+    const DevModel& m = P.m;
+    const int n = m.n, nv = n + 6, LD = P.L.LD;
+    for (long long robot = (long long)blockIdx.x * wpb + wib; robot < P.N; robot += (long long)gridDim.x * wpb) {
+        k1_fk(m, w, P.base_pos + 3 * robot, P.base_quat + 4 * robot, P.s + (size_t)n * robot, lane);
+        for (int i = lane; i < nv; i += 32)
+            for (int j = 0; j < nv; j++) w.Hs[i * LD + j] = 0.0;
+        __syncwarp();
+        for (int k = 0; k < m.nl; k++) {
+            const double mk = m.mass[k];
+            if (!(mk > 0.0) && !m.inertia) continue;
+            // world CoM of link k and its world inertia
+            const double* R = w.linkR + 9 * k;
+            double ck[3] = {w.linkP[3 * k], w.linkP[3 * k + 1], w.linkP[3 * k + 2]};
+            if (mk > 0.0) ck[0] = w.mcw[3 * k] / mk, ck[1] = w.mcw[3 * k + 1] / mk, ck[2] = w.mcw[3 * k + 2] / mk;
+            // columns of the CoM Jacobian of link k, one per lane, into Jt rows 0-2 (linear), 3-5 (angular), 6-8 (I^W angular)
+            for (int c = lane; c < nv; c += 32) {
+                double lin[3] = {0, 0, 0}, ang[3] = {0, 0, 0};
+                if (c < 3) {
+                    lin[c] = 1.0;
+                } else if (c < 6) {
+                    const double r[3] = {ck[0] - w.linkP[0], ck[1] - w.linkP[1], ck[2] - w.linkP[2]};
+                    ang[c - 3] = 1.0;
+                    cross3(ang, r, lin);
+                } else if ((m.anc[k] >> (c - 6)) & 1ull) {
+                    const int kj = m.link_of_dof[c - 6];
+                    const double d[3] = {ck[0] - w.linkP[3 * kj], ck[1] - w.linkP[3 * kj + 1], ck[2] - w.linkP[3 * kj + 2]};
+                    ang[0] = w.axisW[3 * kj], ang[1] = w.axisW[3 * kj + 1], ang[2] = w.axisW[3 * kj + 2];
+                    cross3(ang, d, lin);
+                }
+                double iw[3] = {0, 0, 0};
+                if (m.inertia) {
+                    const double* I6 = m.inertia + 6 * k;
+                    double al[3], il[3];
+                    mat3T_vec(R, ang, al);
+                    il[0] = I6[0] * al[0] + I6[1] * al[1] + I6[2] * al[2];
+                    il[1] = I6[1] * al[0] + I6[3] * al[1] + I6[4] * al[2];
+                    il[2] = I6[2] * al[0] + I6[4] * al[1] + I6[5] * al[2];
+                    mat3_vec(R, il, iw);
+                }
+                for (int r3 = 0; r3 < 3; r3++) w.Jt[r3 * LD + c] = lin[r3], w.A[r3 * LD + c] = ang[r3], w.B[r3 * LD + c] = iw[r3];
+            }
+            __syncwarp();
+            for (int i = lane; i < nv; i += 32) {
+                const double li[3] = {mk * w.Jt[i], mk * w.Jt[LD + i], mk * w.Jt[2 * LD + i]};
+                const double wi[3] = {w.B[i], w.B[LD + i], w.B[2 * LD + i]};
+                for (int j = 0; j < nv; j++)
+                    w.Hs[i * LD + j] += li[0] * w.Jt[j] + li[1] * w.Jt[LD + j] + li[2] * w.Jt[2 * LD + j] + wi[0] * w.A[j] + wi[1] * w.A[LD + j] + wi[2] * w.A[2 * LD + j];
+            }
+            __syncwarp();
+        }
+        if (mass_matrix)
+            for (int i = 0; i < nv; i++)
+                for (int j = lane; j < nv; j += 32) mass_matrix[((size_t)robot * nv + i) * nv + j] = w.Hs[i * LD + j];
+        if (gravity) {
+            double com[3];
+            k1_com(m, w, com, w.Jt, LD, lane);
+            __syncwarp();
+            const double M = 1.0 / m.inv_total_mass;
+            for (int c = lane; c < nv; c += 32) gravity[(size_t)robot * nv + c] = M * g_acc * w.Jt[2 * LD + c];
+        }
+        __syncwarp();
+    }
+}
+
 // Coefficients of the quintic splines of one task (Math::QuinticSpline, QuinticSpline.h:266-415), one thread per robot and
 // coordinate.  The interior-knot system is block tridiagonal with 2 x 2 blocks that depend on the knot times only, so the
 // host eliminates the blocks once (fac[i] = L_i, M_i = L_i D'_{i-1}^-1, D'_i^-1, U_i) and a thread runs the two sweeps on
@@ -2266,6 +2372,73 @@ extern "C" int blfik_integrate_state(int32_t n, int64_t N, double* bp, double* b
     }
     if (stage) cudaFree(stage);
     if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_integrate_state] %s", cudaGetErrorString(e));
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_integrate_acceleration_state(int32_t n, int64_t N, double* bp, double* bq, double* s, double* dp, double* omega, double* ds,
+                                                  const double* acc, double dt, int32_t nsteps, int32_t device)
+{
+    if (n < 1 || N < 1 || !bp || !bq || !s || !dp || !omega || !ds || !acc)
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate_acceleration_state] bad sizes or null buffer");
+    if (!(dt > 0)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate_acceleration_state] the integration step must be positive");
+    if (nsteps < 1) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate_acceleration_state] nsteps must be >= 1");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(BLFIK_ERR_CUDA, "[blfik_integrate_acceleration_state] no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_integrate_acceleration_state] device %d out of range", device);
+    CU(cudaSetDevice(device));
+    // host arrays in, host arrays out: staged through one temporary device buffer
+    const size_t Ns = (size_t)N, nv = (size_t)n + 6;
+    const size_t cnt[7] = {Ns * 3, Ns * 4, Ns * n, Ns * 3, Ns * 3, Ns * n, Ns * nv};
+    double* host[7] = {bp, bq, s, dp, omega, ds, const_cast<double*>(acc)};
+    size_t total = 0;
+    for (size_t c : cnt) total += c;
+    double* stage = nullptr;
+    CU(cudaMalloc((void**)&stage, total * sizeof(double)));
+    double* dev[7];
+    size_t off = 0;
+    for (int k = 0; k < 7; k++) {
+        dev[k] = stage + off, off += cnt[k];
+        cudaMemcpy(dev[k], host[k], cnt[k] * sizeof(double), cudaMemcpyHostToDevice);
+    }
+    const long long blocks = ((long long)N * 32 + 255) / 256;
+    blfik_integrate_acceleration_kernel<<<(int)(blocks < 148 * 8 ? blocks : 148 * 8), 256>>>(n, N, dev[0], dev[1], dev[2], dev[3], dev[4], dev[5], dev[6], dt, nsteps);
+    e = cudaGetLastError();
+    for (int k = 0; k < 6 && e == cudaSuccess; k++) e = cudaMemcpy(host[k], dev[k], cnt[k] * sizeof(double), cudaMemcpyDeviceToHost);
+    cudaFree(stage);
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_integrate_acceleration_state] %s", cudaGetErrorString(e));
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_dynamics(blfik_problem* p, double* mass_matrix, double* gravity_forces, double gravity_acceleration, int32_t mem)
+{
+    CHECK_P(p, "blfik_dynamics");
+    if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_dynamics] the robot state has never been set");
+    if (!mass_matrix && !gravity_forces) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_dynamics] nothing asked for");
+    const size_t N = (size_t)p->N, nv = p->nv;
+    double *dM = mass_matrix, *dG = gravity_forces;
+    std::vector<void*> tmp;
+    if (mem != BLFIK_MEM_DEVICE) {
+        if (mass_matrix) { if (cudaMalloc((void**)&dM, N * nv * nv * sizeof(double)) != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_dynamics] cudaMalloc failed"); tmp.push_back(dM); }
+        if (gravity_forces) { if (cudaMalloc((void**)&dG, N * nv * sizeof(double)) != cudaSuccess) { for (void* t : tmp) cudaFree(t); return fail(BLFIK_ERR_CUDA, "[blfik_dynamics] cudaMalloc failed"); } tmp.push_back(dG); }
+    }
+    KinParams K;
+    K.m = p->dm, K.N = p->N, K.base_pos = p->base_pos, K.base_quat = p->base_quat, K.s = p->s, K.frames = nullptr, K.nframes = 0;
+    K.frame_pos = K.frame_rot = K.frame_jac = K.com = K.com_jac = nullptr;
+    K.L = p->L;
+    cudaError_t e = cudaFuncSetAttribute(blfik_dynamics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes);
+    if (e == cudaSuccess) {
+        blfik_dynamics_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(K, dM, dG, gravity_acceleration);
+        e = cudaGetLastError();
+        p->launches++;
+    }
+    if (e == cudaSuccess && mem != BLFIK_MEM_DEVICE) {
+        if (mass_matrix) e = cudaMemcpyAsync(mass_matrix, dM, N * nv * nv * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+        if (gravity_forces && e == cudaSuccess) e = cudaMemcpyAsync(gravity_forces, dG, N * nv * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+    for (void* t : tmp) cudaFree(t);
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_dynamics] %s", cudaGetErrorString(e));
     return BLFIK_OK;
 }
 

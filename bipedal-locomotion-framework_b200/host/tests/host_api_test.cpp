@@ -1115,6 +1115,115 @@ static void testIntegrator()
 }
 
 
+// src/ContinuousDynamicalSystem/tests/IntegratorLinearSystem.cpp replayed: a mass-spring-damper driven by a step, against its
+// closed-form response, ForwardEuler at the reference's 1e-3 and RK4 at 1e-8 (the reference accepts 1e-3 for both).
+static void testLinearSystemIntegrators()
+{
+    constexpr auto dT = 100us;
+    constexpr double tolEuler = 1e-3, tolRK4 = 1e-8, simulationTime = 2.0;
+    const std::vector<double> A{0, 1, -2, -2}, B{0, 2};
+    auto closedForm = [](double t) {
+        return std::array<double, 2>{1 - std::exp(-t) * (std::cos(t) + std::sin(t)), 2 * std::exp(-t) * std::sin(t)};
+    };
+    auto run = [&](auto& integrator, auto system, double tol) {
+        REQUIRE(system->setSystemMatrices(A, 2, 2, B, 2, 1));
+        REQUIRE(system->setState({VectorXd{0.0, 0.0}}));
+        REQUIRE(system->setControlInput({VectorXd{1.0}}));
+        REQUIRE(integrator.setIntegrationStep(dT));
+        REQUIRE(integrator.setDynamicalSystem(system));
+        const int steps = static_cast<int>(simulationTime / 1e-4);
+        double worst = 0;
+        for (int i = 0; i < steps; i++) {
+            const auto& [x] = integrator.getSolution();
+            const auto e = closedForm(1e-4 * i);
+            worst = std::max({worst, std::abs(x[0] - e[0]), std::abs(x[1] - e[1])});
+            REQUIRE(integrator.integrate(0s, dT));
+        }
+        REQUIRE(worst < tol);
+    };
+    ForwardEuler<LinearTimeInvariantSystem> euler;
+    run(euler, std::make_shared<LinearTimeInvariantSystem>(), tolEuler);
+    RK4<LinearTimeInvariantSystem> rk4;
+    run(rk4, std::make_shared<LinearTimeInvariantSystem>(), tolRK4);
+    // the reference's error rules
+    log()->setLevel(Logger::Level::off);
+    LinearTimeInvariantSystem bad;
+    REQUIRE_FALSE(bad.setSystemMatrices(A, 2, 2, B, 1, 2));                           // A and B: different rows
+    REQUIRE_FALSE(bad.setSystemMatrices({0, 1, 2, 3, 4, 5}, 2, 3, {0, 2}, 2, 1));     // A not square
+    LinearTimeInvariantSystem::StateDerivative dx;
+    REQUIRE_FALSE(bad.dynamics(0s, dx));                                              // matrices never set
+    REQUIRE(bad.setSystemMatrices(A, 2, 2, B, 2, 1));
+    REQUIRE(bad.setState({VectorXd{0.0, 0.0, 0.0}}));
+    REQUIRE(bad.setControlInput({VectorXd{1.0}}));
+    REQUIRE_FALSE(bad.dynamics(0s, dx));                                              // state of the wrong size
+    REQUIRE(bad.setState({VectorXd{0.0, 0.0}}));
+    REQUIRE(bad.setControlInput({VectorXd{1.0, 2.0}}));
+    REQUIRE_FALSE(bad.dynamics(0s, dx));                                              // input of the wrong size
+    RK4<LinearTimeInvariantSystem> twice;
+    REQUIRE(twice.setDynamicalSystem(std::make_shared<LinearTimeInvariantSystem>()));
+    REQUIRE_FALSE(twice.setDynamicalSystem(std::make_shared<LinearTimeInvariantSystem>()));
+    REQUIRE_FALSE(twice.setIntegrationStep(0ns));
+    log()->setLevel(Logger::Level::warn);
+}
+
+// FloatingBaseSystemAccelerationKinematics under ForwardEuler, on the device: constant acceleration has the closed forms
+// v = v0 + a T and (explicit Euler, derivative at the old state) p_K = p0 + K dt v0 + dt^2 a K (K - 1) / 2; the rotation is checked
+// at zero angular acceleration, where R = Exp(w T) R0.  Batch of 3 robots with different inputs.
+static void testAccelerationIntegrator()
+{
+    constexpr auto dT = 1ms;
+    const std::size_t n = 7, N = 3;
+    const int K = 250;
+    std::mt19937 gen(11);
+    std::uniform_real_distribution<double> u(-1, 1);
+    auto system = std::make_shared<FloatingBaseSystemAccelerationKinematics>();
+    system->setBatchSize(N);
+    std::vector<FloatingBaseSystemAccelerationKinematics::State> x0(N);
+    std::vector<FloatingBaseSystemAccelerationKinematics::Input> in(N);
+    for (std::size_t i = 0; i < N; i++) {
+        auto& [p, R, s, dp, w, ds] = x0[i];
+        for (int c = 0; c < 3; c++) p[c] = u(gen), dp[c] = u(gen), w.w[c] = u(gen);
+        R = SO3d::Exp({u(gen), u(gen), u(gen)});
+        s.resize(n), ds.resize(n);
+        for (std::size_t j = 0; j < n; j++) s[j] = u(gen), ds[j] = u(gen);
+        auto& [dtw, dds] = in[i];
+        for (int c = 0; c < 6; c++) dtw[c] = c < 3 ? u(gen) : 0.0;
+        dds.resize(n);
+        for (auto& v : dds) v = u(gen);
+        REQUIRE(system->setState(x0[i], static_cast<std::ptrdiff_t>(i)));
+        REQUIRE(system->setControlInput(in[i], static_cast<std::ptrdiff_t>(i)));
+    }
+    FloatingBaseSystemAccelerationKinematics::StateDerivative d;
+    REQUIRE(system->dynamics(0s, d, 1));
+    for (int c = 0; c < 3; c++) REQUIRE(std::get<0>(d)[c] == std::get<3>(x0[1])[c] && std::get<3>(d)[c] == std::get<0>(in[1])[c]);
+    ForwardEuler<FloatingBaseSystemAccelerationKinematics> integrator;
+    REQUIRE(integrator.setIntegrationStep(dT) && integrator.setDynamicalSystem(system));
+    REQUIRE(integrator.integrate(0s, 250ms));
+    const double dt = 1e-3, T = K * dt, quad = dt * dt * K * (K - 1) / 2.0;
+    for (std::size_t i = 0; i < N; i++) {
+        const auto& [p, R, s, dp, w, ds] = integrator.getSolution(i);
+        const auto& [p0, R0, s0, dp0, w0, ds0] = x0[i];
+        const auto& [dtw, dds] = in[i];
+        for (int c = 0; c < 3; c++) {
+            REQUIRE(std::abs(dp[c] - (dp0[c] + T * dtw[c])) < 1e-12);
+            REQUIRE(std::abs(p[c] - (p0[c] + T * dp0[c] + quad * dtw[c])) < 1e-12);
+            REQUIRE(std::abs(w.w[c] - w0.w[c]) < 1e-15);
+        }
+        for (std::size_t j = 0; j < n; j++) {
+            REQUIRE(std::abs(ds[j] - (ds0[j] + T * dds[j])) < 1e-12);
+            REQUIRE(std::abs(s[j] - (s0[j] + T * ds0[j] + quad * dds[j])) < 1e-12);
+        }
+        const SO3d Rexp = SO3d::Exp({w0.w[0] * T, w0.w[1] * T, w0.w[2] * T});
+        const auto a = Rexp.rotation(), b = R0.rotation(), got = R.rotation();
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) {
+                double e = 0;
+                for (int k = 0; k < 3; k++) e += a[3 * r + k] * b[3 * k + c];
+                REQUIRE(std::abs(got[3 * r + c] - e) < 1e-10);
+            }
+    }
+}
+
 // The batch path (N >= 64): packed page-locked records as the native storage of state and set-points, one blfik_tick_packed per
 // shard.  Its results must not depend on how the batch is cut: one shard, three shards (all on device 0 here: the sharding
 // logic is the same whichever device a block lands on), compact records; and each robot must get what it gets when it is solved
@@ -1213,6 +1322,7 @@ int main(int argc, char** argv)
     testSplines();
     testSO3Planner();
     testSwingFootPlanner();
+    testLinearSystemIntegrators();
     if (gpu) {
         testTaskMatrices(argv[2]);
         testClosedLoop(argv[2], 1, false);
@@ -1224,6 +1334,7 @@ int main(int argc, char** argv)
         testFixedBase(argv[2], 5);
         testSetPointSpline(argv[2], 3);
         testIntegrator();
+        testAccelerationIntegrator();
     }
     std::printf("%s: %d checks, %d failures\n", gpu ? "gpu" : "cpu", g_checks, g_failures);
     return g_failures == 0 ? 0 : 1;

@@ -411,6 +411,20 @@ int32_t blfik_get_kernel_path(const blfik_problem* problem);
  * of the assemble kernel (K1 + K2) and of the solve kernel (K3 + K4) in milliseconds.  bench.py's roofline uses it.   */
 int blfik_kernel_timing(blfik_problem* problem, int32_t enabled);
 int blfik_get_kernel_times(blfik_problem* problem, double* ms_assemble, double* ms_solve);
+/* ---- first pieces of the TSID path ---------------------------------------------------------------------
+ * replaces FloatingBaseSystemAccelerationKinematics + ForwardEuler::integrate (FloatingBaseSystemAccelerationKinematics.cpp:20-75,
+ * ForwardEuler.h:72-124) for N robots: state base_pos [N][3], base_quat [N][4], s [N][n], base linear velocity dp [N][3], base
+ * angular velocity omega [N][3] (inertial frame), joint velocity ds [N][n]; input acc [N][6+n] = [base linear; base angular;
+ * joint accelerations] (MIXED), held for nsteps Euler steps of dt.  Every component moves by its OLD derivative; the rotation
+ * by the left-plus Exp(omega dt) R.  Host arrays in and out.                                                          */
+int blfik_integrate_acceleration_state(int32_t n_dofs, int64_t n_instances, double* base_pos, double* base_quat, double* s,
+                                       double* base_lin_vel, double* base_ang_vel, double* joint_vel, const double* acc,
+                                       double dt, int32_t nsteps, int32_t device);
+/* replaces kinDyn->getFreeFloatingMassMatrix / generalizedGravityForces (what the TSID dynamics tasks read,
+ * src/TSID/src/BaseDynamicsTask.cpp, JointDynamicsTask.cpp) for the state of the problem: mass_matrix [N][6+n][6+n] in the MIXED
+ * representation, gravity_forces [N][6+n] = M_total J_com' (0, 0, gravity_acceleration); either may be NULL.  Needs the link
+ * inertias in the model (blfik_model_desc.inertia; NULL = point masses).  Coriolis / centrifugal forces are not computed.  */
+int blfik_dynamics(blfik_problem* problem, double* mass_matrix, double* gravity_forces, double gravity_acceleration, int32_t mem);
 /* Page-locked host memory, visible to every device of the process (cudaHostAllocPortable | cudaHostAllocMapped), for the
  * buffers of blfik_tick_packed / blfik_tick_host: the host classes keep their packed records, nu and status there so that the
  * library above the C ABI needs no CUDA headers.  No reference counterpart (Eigen vectors in pageable memory).            */
