@@ -471,6 +471,7 @@ struct blfik_problem {
     size_t smem_bytes = 0;
     // equality-only kernel (blfik_eq.cuh): problems without inequality rows that the register-resident kernel cannot hold
     bool eq_kernel = false;
+    void (*eq_func)(const TickParams) = nullptr;   // blfik_tick_eq_kernel<KP> for this problem's row count
     Layout Leq;
     int eq_wpb = 8, eq_grid = 148;
     size_t eq_smem = 0;
@@ -751,6 +752,9 @@ static int dev_alloc(blfik_problem* p, size_t count, T** out, bool zero = true)
 // DistanceTask with a reference frame builds that frame's Jacobian) shares its words with what only K3 touches (G and its
 // Cholesky factor in Ss, the inverse factor in Ym, the iteration vectors): the two phases never overlap, and the smaller
 // footprint is what decides how many robots an SM holds.
+// lanes the dense rows of the factored-form kernel are padded to (blfik_tick_eq_kernel<KP>); 0: the generic instantiation
+static int eq_rider_rows(int K) { return K <= 16 ? 16 : (K <= 24 ? 24 : 0); }
+
 static Layout make_layout_eq(int n, int me, int K, bool needs_A, bool box)
 {
     Layout L;
@@ -772,12 +776,19 @@ static Layout make_layout_eq(int n, int me, int K, bool needs_A, bool box)
     const int end12 = o;
     // K3 only, over the same words
     o = shared0;
+    // eq_solve_rider<KP> (K <= 24): the factor region holds KP x ld2odd(KP) + the rotating elimination's overshoot, the riders'
+    // outputs and their products go where the generic kernel has no use for Wm
+    const int KP = eq_rider_rows(K);
+    const int fac = KP ? KP * ld2odd(KP) + KP : 0;
     L.Ss = take(K * L.LDE), L.Ym = take(K * L.LDE);
-    L.x = take(nv), L.r = take(nv), L.gp = take(nv), L.wb = take(K), L.lam = take(K), L.bp = take(K), L.t = take(K);
+    if (o - L.Ss < fac) o = L.Ss + ((fac + 1) & ~1);
+    L.Wm = KP ? take(9 * (KP + 1) + 81) : 0;
+    const int KV = K > KP ? K : KP;
+    L.x = take(nv), L.r = take(nv), L.gp = take(nv), L.wb = take(KV), L.lam = take(KV), L.bp = take(KV), L.t = take(KV);
     L.act = take((nv + 1) / 2 + 1);
     L.z = take(nv), L.y = take(nv), L.xb = take(nv);   // rho, the active-set codes, the codes proposed by the pivoting rule
     const int end3 = o;
-    L.B = L.Wm = 0;
+    L.B = 0;
     L.total = end12 > end3 ? end12 : end3;
     return L;
 }
@@ -1068,8 +1079,10 @@ extern "C" int blfik_problem_create(const blfik_model* model, const blfik_task_d
             int ewpb = 1;                              // block size (<= 8 warps) that leaves the fewest warps of the SM unused
             for (int c = 1; c <= 8; c++)
                 if ((ew / c) * c >= (ew / ewpb) * ewpb) ewpb = c;
+            const int ekp = eq_rider_rows(p->K);
+            p->eq_func = ekp == 16 ? blfik_tick_eq_kernel<16> : (ekp == 24 ? blfik_tick_eq_kernel<24> : blfik_tick_eq_kernel<0>);
             if (ew >= 1 && (size_t)ewpb * eper <= (size_t)smem_optin &&
-                cudaFuncSetAttribute(blfik_tick_eq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) == cudaSuccess) {
+                cudaFuncSetAttribute((const void*)p->eq_func, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin) == cudaSuccess) {
                 p->eq_kernel = true;
                 p->eq_wpb = ewpb, p->eq_smem = (size_t)ewpb * eper;
                 const long long ewant = (N + ewpb - 1) / ewpb;
@@ -1730,7 +1743,7 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
     } else if (p->eq_kernel && p->path != 1 && !P.dbg.H) {   // the debug read-back wants H: the generic kernel forms it
         P.L = p->Leq;
         const long long want = (count + p->eq_wpb - 1) / p->eq_wpb;
-        blfik_tick_eq_kernel<<<(int)(want < p->eq_grid ? want : p->eq_grid), p->eq_wpb * 32, p->eq_smem, stream>>>(P);
+        p->eq_func<<<(int)(want < p->eq_grid ? want : p->eq_grid), p->eq_wpb * 32, p->eq_smem, stream>>>(P);
     } else {
         const long long want = (count + p->warps_per_block - 1) / p->warps_per_block;
         blfik_tick_kernel<<<(int)(want < p->grid ? want : p->grid), p->warps_per_block * 32, p->smem_bytes, stream>>>(P);

@@ -23,10 +23,10 @@ namespace blfik {
 // One solve with the variables marked in w.y (0 free; +1 / -1 / 2: fixed at the upper / lower bound / at lo = hi) held at
 // their bounds: they leave D^-1 (w.gp = 0), keep their value through w.r, and enter the right-hand side of the rows like any
 // other known term.  Leaves x in w.x and z in w.lam; false if a pivot was not finite.
-__device__ __forceinline__ bool eq_solve_fixed(const TickParams& P, const WM& w, int lane, int& steps, bool& converged)
+__device__ __forceinline__ int eq_prepare(const TickParams& P, const WM& w, int lane)
 {
     const Layout& L = P.L;
-    const int nv = L.nv, K = L.K, LD = L.LD, LDE = L.LDE;
+    const int nv = L.nv;
     const double sigma = P.st.sigma;
     // Proximal weight per free variable, R_i = max(D0_i, sigma) - D0_i: only where the diagonal cost is missing (the base columns)
     // or below sigma.  D^-1 q = rho x_k + pc with rho = R / D (w.z) and the constant pc = -D^-1 g0 (w.r), so a step moves nothing
@@ -54,6 +54,13 @@ __device__ __forceinline__ bool eq_solve_fixed(const TickParams& P, const WM& w,
         nF += __popc(m);
     }
     __syncwarp();
+    return nF;
+}
+
+__device__ __forceinline__ bool eq_solve_generic(const TickParams& P, const WM& w, int lane, int nF, int& steps, bool& converged)
+{
+    const Layout& L = P.L;
+    const int nv = L.nv, K = L.K, LD = L.LD, LDE = L.LDE;
     // G = E + (B D^-1) B' as 8 x 8 tiles on the FP64 tensor path (DMMA m8n8k4, as in the register-resident kernel), tiles on
     // and below the diagonal only: one instruction per 256 multiply-adds where the lane-per-entry loop spent 1,500 per robot
     double gmax = 0.0;
@@ -178,6 +185,192 @@ __device__ __forceinline__ bool eq_solve_fixed(const TickParams& P, const WM& w,
     return ok;
 }
 
+// The same solve for K <= KP <= 24 dense rows and at most min(8, 31 - KP) proximal variables (C1 / C2: 15 rows, the six base
+// columns), on the pattern of solve_setup (blfik_split.cuh):
+//  * the Cholesky of G runs on rotating register rows, lane r = row r, and everything that needs L^-1 applied rides along in
+//    the lanes that hold no row: a lane whose row is used up carries the forward substitution of its unit vector (so the
+//    inverse factor costs no second pass), lane KP carries the constant right-hand side wb, lanes KP + 1 ... carry the columns
+//    of B that belong to the proximal variables F;
+//  * with t0 = L^-1 wb and V = L^-1 B_F the step x_F <- rho x_F + pc_F - D^-1_F B_F' G^-1 (wb + B_F rho x_F) is the affine map
+//    x_F <- y + pc_F - D^-1_F (h + S y), y = rho x_F, S = V'V (|F| x |F|), h = V't0: a step costs |F| multiply-adds per lane
+//    instead of two triangular products with L^-1; z and the other variables are evaluated once, after the last step.
+// A pivot below the floor drops its row exactly as the generic path does (a zero reciprocal pivot zeroes the column of L,
+// the row and the column of L^-1 and the rider entries).
+template <int KP>
+__device__ __forceinline__ bool eq_solve_rider(const TickParams& P, const WM& w, int lane, int nF, int& steps, bool& converged)
+{
+    static_assert(KP % 8 == 0 && KP <= 24, "rows by lanes, with spare lanes for the riders");
+    const Layout& L = P.L;
+    const int nv = L.nv, K = L.K, LD = L.LD;
+    constexpr int LDG = ld2odd(KP), LDV = KP + 1, RT = KP / 8;
+    double* Gs = w.Ss;            // G by columns, then row c: (L^-1)_{c, 0..c} followed by L_{c+1.., c}
+    double* Vs = w.Wm;            // [1 + nF][LDV]: t0, V
+    double* Sm = w.Wm + 9 * LDV;  // [9][9]: products of the columns of Vs
+    for (int k = lane; k < K; k += 32) {   // constant part of the right-hand side: B pc - [be; bc]
+        const double* bk = w.Cs + k * LD;
+        double v0 = -w.b[k], v1 = 0.0;
+        int c = 0;
+        for (; c + 1 < nv; c += 2) v0 = fma(bk[c], w.r[c], v0), v1 = fma(bk[c + 1], w.r[c + 1], v1);
+        if (c < nv) v0 = fma(bk[c], w.r[c], v0);
+        w.wb[k] = v0 + v1;
+    }
+    double gmax = 0.0;
+    {
+        const int gr = lane >> 2, tc = lane & 3;
+        const int KS = (nv + 3) >> 2;
+#pragma unroll
+        for (int ti = 0; ti < RT; ti++) {
+            const int row = 8 * ti + gr;
+            const double* ba = w.Cs + (row < K ? row : 0) * LD;
+#pragma unroll
+            for (int tj = 0; tj <= ti; tj++) {
+                const int rowb = 8 * tj + gr;
+                const double* bb = w.Cs + (rowb < K ? rowb : 0) * LD;
+                double c0 = 0.0, c1 = 0.0;
+                for (int s = 0; s < KS; s++) {
+                    const int col = 4 * s + tc;
+                    const bool in = col < nv;
+                    const double a = (in && row < K) ? ba[col] * w.gp[col] : 0.0;
+                    const double b = (in && rowb < K) ? bb[col] : 0.0;
+                    dmma884(c0, c1, a, b);
+                }
+                const int col = 8 * tj + 2 * tc;
+                const double er = row < K ? w.bd[row] : 1.0;   // padding rows: identity
+                if (row == col) c0 += er, gmax = fmax(gmax, c0);
+                if (row == col + 1) c1 += er, gmax = fmax(gmax, c1);
+                Gs[col * LDG + row] = c0, Gs[(col + 1) * LDG + row] = c1;
+                if (tj < ti) Gs[row * LDG + col] = c0, Gs[row * LDG + col + 1] = c1;
+            }
+        }
+    }
+    gmax = warp_max(gmax);
+    __syncwarp();
+    bool ok = true;
+    {
+        const double floor_ = 1e-11 * gmax + 1e-300;
+        double gA[KP], gB[KP];
+        const int myr = lane < KP ? lane : 0;
+        const int rider = lane - KP;   // 0: wb, 1 + f: column act[f] of B
+        const int rc = (rider >= 1 && rider <= nF) ? w.act[rider - 1] : 0;
+#pragma unroll
+        for (int j = 0; j < KP; j++) {
+            double v = Gs[j * LDG + myr];
+            if (rider >= 0) v = (j < K && rider <= nF) ? (rider == 0 ? w.wb[j] : w.Cs[j * LD + rc]) : 0.0;
+            gA[j] = v;
+        }
+        __syncwarp();
+        double* vout = Vs + (rider >= 0 && rider <= nF ? rider : 0) * LDV;
+        const bool rides = rider >= 0 && rider <= nF;
+#pragma unroll 1
+        for (int k = 0; k < KP; k += 2) {
+            {
+                const double piv = __shfl_sync(kFull, gA[0], k);
+                const bool dropped = !(piv > floor_);
+                if (dropped && !(piv == piv)) ok = false;
+                const double rinv = dropped ? 0.0 : rsqrt(piv);
+                const double f = gA[0] * rinv;
+                if (lane < KP) Gs[k * LDG + lane] = (lane == k) ? rinv : f;
+                if (rides) vout[k] = f;
+                __syncwarp();
+                rot_update<KP, 0>(gA, gB, lane == k ? f + rinv : f, Gs + k * LDG + k);
+            }
+            {
+                const int k1 = k + 1;
+                const double piv = __shfl_sync(kFull, gB[0], k1);
+                const bool dropped = !(piv > floor_);
+                if (dropped && !(piv == piv)) ok = false;
+                const double rinv = dropped ? 0.0 : rsqrt(piv);
+                const double f = gB[0] * rinv;
+                if (lane < KP) Gs[k1 * LDG + lane] = (lane == k1) ? rinv : f;
+                if (rides) vout[k1] = f;
+                __syncwarp();
+                rot_update<KP, 1>(gB, gA, lane == k1 ? f + rinv : f, Gs + k1 * LDG + k1);
+            }
+        }
+    }
+    __syncwarp();
+    // products of the columns (t0, V_1 ... V_nF): entry (a, b) by lane over the 9 x 8 slots
+    for (int e = lane; e < 72; e += 32) {
+        const int a = e >> 3, b = (e & 7) + 1;
+        if (a <= nF && b <= nF) {
+            const double *va = Vs + a * LDV, *vb = Vs + b * LDV;
+            double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+            for (int k = 0; k < KP; k += 2) s0 = fma(va[k], vb[k], s0), s1 = fma(va[k + 1], vb[k + 1], s1);
+            Sm[a * 9 + b] = s0 + s1;
+        }
+    }
+    __syncwarp();
+    const bool inF = lane < nF;
+    const int cF = inF ? w.act[lane] : 0;
+    double srow[8];
+#pragma unroll
+    for (int g = 0; g < 8; g++) srow[g] = (inF && g < nF) ? Sm[(lane + 1) * 9 + g + 1] : 0.0;
+    const double hf = inF ? Sm[lane + 1] : 0.0;
+    const double zf = inF ? w.z[cF] : 0.0, rf = inF ? w.r[cF] : 0.0, gpf = inF ? w.gp[cF] : 0.0;
+    double xf = inF ? w.x[cF] : 0.0;
+    const int max_steps = 60;
+    converged = false;
+    int it = 0;
+    for (; it < max_steps && !converged; it++) {
+        const double y = zf * xf;
+        double acc = hf;
+#pragma unroll
+        for (int g = 0; g < 8; g++) acc = fma(srow[g], __shfl_sync(kFull, y, g), acc);
+        const double v = y + rf - gpf * acc;
+        const bool settled = !inF || fabs(v - xf) <= 1e-10 * (1.0 + fabs(v));
+        const bool finite = v == v;
+        xf = v;
+        converged = __all_sync(kFull, settled);
+        if (!__all_sync(kFull, finite)) break;
+    }
+    // z = L^-T (t0 + V y) from the last iterate, then every variable (one more step for those of F)
+    {
+        const double y = zf * xf;
+        double t = lane < KP ? Vs[lane] : 0.0;
+#pragma unroll
+        for (int g = 0; g < 8; g++) {
+            const double yg = __shfl_sync(kFull, y, g);
+            if (g < nF && lane < KP) t = fma(Vs[(g + 1) * LDV + lane], yg, t);
+        }
+        if (lane < KP) w.t[lane] = t;
+        if (inF) w.x[cF] = xf;
+        __syncwarp();
+        if (lane < K) {
+            double v0 = 0.0, v1 = 0.0;
+#pragma unroll
+            for (int j = 0; j < KP; j += 2) {
+                v0 = fma(j >= lane ? Gs[j * LDG + lane] : 0.0, w.t[j], v0);
+                v1 = fma(j + 1 >= lane ? Gs[(j + 1) * LDG + lane] : 0.0, w.t[j + 1], v1);
+            }
+            w.lam[lane] = v0 + v1;
+        }
+        __syncwarp();
+    }
+    for (int c = lane; c < nv; c += 32) {
+        const double* bc = w.Cs + c;
+        double b0 = 0.0, b1 = 0.0;
+        int k = 0;
+        for (; k + 1 < K; k += 2) b0 = fma(bc[k * LD], w.lam[k], b0), b1 = fma(bc[(k + 1) * LD], w.lam[k + 1], b1);
+        if (k < K) b0 = fma(bc[k * LD], w.lam[k], b0);
+        w.x[c] = w.z[c] * w.x[c] + w.r[c] - w.gp[c] * (b0 + b1);
+    }
+    __syncwarp();
+    steps += it;
+    return ok;
+}
+
+template <int KP>
+__device__ __forceinline__ bool eq_solve_fixed(const TickParams& P, const WM& w, int lane, int& steps, bool& converged)
+{
+    const int nF = eq_prepare(P, w, lane);
+    if constexpr (KP > 0) {
+        constexpr int cap = 31 - KP < 8 ? 31 - KP : 8;
+        if (nF <= cap) return eq_solve_rider<KP>(P, w, lane, nF, steps, converged);
+    }
+    return eq_solve_generic(P, w, lane, nF, steps, converged);
+}
+
 // The QP of one tick.  Without a box (L.box == 0) it is the single solve above.  With one (JointLimitsTask,
 // JointVelocityLimitsTask, a priority-0 JointTrackingTask) the active set is found by block principal pivoting: every solve is
 // followed by the test of the complementarity conditions -- a free joint outside its bounds is fixed there, a fixed joint whose
@@ -185,6 +378,7 @@ __device__ __forceinline__ bool eq_solve_fixed(const TickParams& P, const WM& w,
 // active-set step of the register-resident kernel), one joint at a time, lowest index first, when it stalls (Murty's least-index
 // rule, the safeguard of Judice and Pires that makes the pivoting finite on a strictly convex problem).  No violation left is
 // the KKT certificate: primal feasible, dual feasible, stationary to the tolerance of the steps.
+template <int KP>
 __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w, bool warm, long long robot, int lane)
 {
     const Layout& L = P.L;
@@ -218,7 +412,7 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
     const int max_pivots = L.box ? 32 : 1;   // a feasible problem needs a handful; the bound is what an infeasible one costs
     int best = 1 << 30, stall = 0;
     for (int piv = 0; piv < max_pivots; piv++) {
-        ok = eq_solve_fixed(P, w, lane, res.iters, converged) && ok;
+        ok = eq_solve_fixed<KP>(P, w, lane, res.iters, converged) && ok;
         if (!L.box) {
             // the equality rows hold at every step by construction; what the step cap can leave unfinished is the cost
             // (a cost weight far below sigma contracts slowly), and then the tick must not claim SOLVED
@@ -282,7 +476,8 @@ __device__ __forceinline__ QpResult k3_solve_eq(const TickParams& P, const WM& w
 }
 
 // Same contract as blfik_tick_kernel (K1 -> K2 -> K3 -> K4, `nticks` times per launch); P.L is the row layout built by
-// make_layout_eq on the host.
+// make_layout_eq on the host.  KP: 16 / 24 = the dense rows fit that many lanes (eq_solve_rider), 0 = any K <= 64.
+template <int KP>
 __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams P)
 {
     extern __shared__ double smem[];
@@ -300,7 +495,7 @@ __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams 
         for (int tick = 0; tick < P.nticks; tick++) {
             k1_fk(P.m, w, bp, bq, s, lane);
             k2_assemble<true>(P, w, robot, s, lane, P.t0 + tick * P.dt);
-            res = k3_solve_eq(P, w, warm, robot, lane);
+            res = k3_solve_eq<KP>(P, w, warm, robot, lane);
             iters += res.iters;
             worst = res.status > worst ? res.status : worst;
             if (res.status == 2) {   // no velocity to report (the reference's advance() fails): hold still
