@@ -103,6 +103,17 @@ def test_k2_assembly_vs_oracle(cid, path):
 @pytest.mark.parametrize("cid,N", [(1, 256), (2, 4096), (3, 2048), (4, 1024)])
 def test_k3_solution_vs_oracle(cid, N, path):
     """nu against the oracle's optimum (OSQP-equivalent ADMM eps 1e-7 + polish, KKT <= 1e-9)."""
+    _k3_vs_oracle(cid, N, path)
+
+
+@pytest.mark.parametrize("cid,N", [(3, 65536), (4, 32768)])
+def test_k3_solution_vs_oracle_at_baseline_sizes(cid, N):
+    """The same comparison at the per-GPU batch sizes BASELINE.json quotes for C3 and C4, default kernel path, on 512 robots
+    spread over the whole batch (the launch geometry, the work queue and the record offsets are those of the bench)."""
+    _k3_vs_oracle(cid, N, 0)
+
+
+def _k3_vs_oracle(cid, N, path):
     w = W.config(cid)
     inp = W.synth_inputs(w, N, cid)
     model, prob = make(w.model, w.tasks, N, path)
@@ -1035,6 +1046,62 @@ def test_full_size_c5_rollout_properties():
     e0 = np.abs((k0["com"] - com_tgt0)[good][:, mask]).max()
     assert np.abs((k1["com"] - com_tgt)[good][:, mask]).max() < 0.15 * e0 + 5e-4
     assert np.abs(k1["com"] - k0["com"]).max() > 1e-3          # and it did move
+    prob.close()
+
+
+def test_c5_baseline_shape_vs_oracle():
+    """BASELINE.json config 5 at its per-GPU shape -- 8,192 ergoCubs, 1,000 closed-loop ticks at 1 kHz, set-points generated on
+    the device, warm start -- compared with the oracle on a sample of ticks and robots: the rollout is cut at ticks 0, 333, 666
+    and 999; there the GPU's state is read back, the oracle solves that tick for 64 robots spread over the batch with the
+    set-points of that instant evaluated on the host, and the GPU's next tick must return the same velocities."""
+    w = W.config(5)
+    N, dt, period = 8192, w.dt, 2.0
+    inp = W.synth_inputs(w, N, 5)
+    rng = np.random.default_rng(3)
+    amps = {0: [0.02, 0.015, 0.01, 0, 0, 0], 5: [0, 0, 0, 0.08, 0.05, -0.06]}
+    phases = {t: rng.uniform(0, 2 * np.pi, N) for t in amps}
+    sub = np.unique(np.linspace(0, N - 1, 64).astype(int))
+
+    def setpoints_at(t):
+        sps = [None if sp is None else sp[sub].copy() for sp in inp.setpoints]
+        om = 2 * np.pi / period
+        for ti, a in amps.items():
+            a = np.asarray(a)
+            sn, cs = np.sin(om * t + phases[ti][sub])[:, None], np.cos(om * t + phases[ti][sub])[:, None]
+            ty = w.tasks[ti].type
+            if ty in (T.TASK_SE3, T.TASK_COM, T.TASK_R3):
+                vo = 7 if ty == T.TASK_SE3 else 3
+                sps[ti][:, 0:3] += a[:3] * sn
+                sps[ti][:, vo:vo + 3] += a[:3] * om * cs
+            if ty in (T.TASK_SE3, T.TASK_SO3):
+                qo, wo = (3, 10) if ty == T.TASK_SE3 else (0, 4)
+                sps[ti][:, qo:qo + 4] = W.quat_mul(W.so3_exp(a[3:] * sn), sps[ti][:, qo:qo + 4])
+                sps[ti][:, wo:wo + 3] += a[3:] * om * cs
+        return sps
+
+    model, prob = make(w.model, w.tasks, N)
+    assert prob.kernel_path == 4
+    prob.set_inputs(inp)
+    for ti, a in amps.items():
+        prob.set_setpoint_trajectory(ti, a, period, phases[ti])
+    o = Oracle(w.model, w.tasks)
+    done, compared = 0, 0
+    for k in (0, 333, 666, 999):
+        if k > done:
+            prob.tick(k - done, dt, integrate=True, warm_start=True)
+            done = k
+        assert abs(prob.time - k * dt) < 1e-9
+        p, q, s = prob.get_state()
+        nur, str_, _ = o.tick_batch(p[sub].copy(), q[sub].copy(), s[sub].copy(), setpoints_at(k * dt), nthreads=8)
+        prob.tick(1, dt, integrate=True, warm_start=True)
+        done += 1
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        ok = (st[sub] == 0) & (str_ == 0)
+        assert ok.mean() > 0.95, (k, np.bincount(st[sub]), np.bincount(str_))
+        assert np.abs(nu[sub][ok] - nur[ok]).max() <= TOL_NU, (k, np.abs(nu[sub][ok] - nur[ok]).max())
+        compared += int(ok.sum())
+    assert done == 1000 and compared > 240
     prob.close()
 
 
