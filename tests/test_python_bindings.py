@@ -11,6 +11,7 @@ import pytest
 import blf_b200  # noqa: F401
 import blf_b200.bindings as blf
 from blf_b200 import models as M
+from blf_b200 import workloads as W
 from blf_b200.bindings import manif
 
 logging.getLogger("blf").setLevel(logging.CRITICAL)   # the error paths below are expected
@@ -314,6 +315,84 @@ def test_floating_base_system_kinematics():
         assert base_rotation.rotation() == pytest.approx(exact.rotation(), abs=tolerance)
         assert joint_position == pytest.approx(joint_position0 + t * joint_velocity, abs=tolerance)
         assert integrator.integrate(timedelta(seconds=0), timedelta(seconds=25 * dt))
+
+
+def test_linear_system():
+    """bindings/python/ContinuousDynamicalSystem/tests/test_linear_system.py replayed (ForwardEuler, tolerance 1e-3), and the same
+    run with the RK4 integrator at 1e-8; then the reference's error rules."""
+    def close_form_solution(t):
+        return np.array([1 - np.exp(-t) * (np.cos(t) + np.sin(t)), 2 * np.exp(-t) * np.sin(t)])
+
+    A = np.array([[0, 1], [-2, -2]])
+    B = np.array([0, 2])
+    u = np.array([1])
+    x0 = np.array([0, 0])
+    dt = 0.0001
+    simulation_time = 1
+    cds = blf.continuous_dynamical_system
+    for cls, tolerance in ((cds.LinearTimeInvariantSystemForwardEulerIntegrator, 1e-3), (cds.LinearTimeInvariantSystemRK4Integrator, 1e-8)):
+        system = cds.LinearTimeInvariantSystem()
+        assert system.set_system_matrices(A, B)
+        assert system.set_state((x0,))
+        assert system.set_control_input((u,))
+        integrator = cls()
+        assert integrator.set_dynamical_system(system)
+        assert integrator.set_integration_step(timedelta(seconds=dt))
+        for i in range(0, int(simulation_time / dt)):
+            solution, = integrator.get_solution()
+            assert solution == pytest.approx(close_form_solution(i * dt), abs=tolerance)
+            assert integrator.integrate(timedelta(seconds=0), timedelta(seconds=dt))
+    bad = cds.LinearTimeInvariantSystem()
+    assert bad.dynamics() is None                                             # matrices never set
+    assert not bad.set_system_matrices(A, np.zeros((3, 1)))                    # A and B: different rows
+    assert not bad.set_system_matrices(np.zeros((2, 3)), np.zeros((2, 1)))     # A not square
+    assert bad.set_system_matrices(A, B) and bad.set_state((np.zeros(3),)) and bad.set_control_input((u,))
+    assert bad.dynamics() is None                                             # state of the wrong size
+    integrator = cds.LinearTimeInvariantSystemRK4Integrator()
+    assert not integrator.integrate(timedelta(0), timedelta(seconds=dt))       # no system
+    assert integrator.set_dynamical_system(bad) and not integrator.set_dynamical_system(bad)
+    assert not integrator.set_integration_step(timedelta(0))
+    assert integrator.set_integration_step(timedelta(seconds=dt))
+    assert not integrator.integrate(timedelta(0), timedelta(seconds=dt))       # the dynamics cannot be evaluated
+    assert not integrator.integrate(timedelta(0), timedelta(seconds=dt / 2))   # shorter than the step
+
+
+@pytest.mark.gpu
+def test_floating_base_system_acceleration_kinematics():
+    """FloatingBaseSystemAccelerationKinematics under ForwardEuler on the device: constant accelerations against the closed forms
+    v = v0 + a T and (explicit Euler, derivative at the old state) p_K = p0 + K dt v0 + dt^2 a K (K - 1) / 2; with no angular
+    acceleration the rotation is Exp(omega T) R0 (left-plus).  One state, then a batch."""
+    cds = blf.continuous_dynamical_system
+    rng = np.random.default_rng(5)
+    dt, K = 0.001, 200
+    for N in (1, 5):
+        shape = (N,) if N > 1 else ()
+        p0, s0 = rng.uniform(-1, 1, shape + (3,)), rng.uniform(-1, 1, shape + (23,))
+        dp0, w0, ds0 = rng.uniform(-1, 1, shape + (3,)), rng.uniform(-1, 1, shape + (3,)), rng.uniform(-1, 1, shape + (23,))
+        phi0 = rng.uniform(-1, 1, shape + (3,))
+        R0 = manif.SO3Tangent(phi0).exp() if N == 1 else W.so3_exp(phi0)
+        dtw = np.concatenate([rng.uniform(-1, 1, shape + (3,)), np.zeros(shape + (3,))], axis=-1)
+        dds = rng.uniform(-1, 1, shape + (23,))
+        system = cds.FloatingBaseSystemAccelerationKinematics()
+        system.state = p0, R0, s0, dp0, w0, ds0
+        assert system.set_control_input((dtw, dds))
+        assert not system.set_control_input((dtw, dds[..., :-1]))
+        integrator = cds.FloatingBaseSystemAccelerationKinematicsForwardEulerIntegrator()
+        assert integrator.set_dynamical_system(system)
+        integrator.integration_step = timedelta(seconds=dt)
+        assert integrator.integrate(timedelta(0), timedelta(seconds=K * dt))
+        p, R, s, dp, w, ds = integrator.get_solution()
+        T_, quad = K * dt, dt * dt * K * (K - 1) / 2
+        assert dp == pytest.approx(dp0 + T_ * dtw[..., :3], abs=1e-12) and ds == pytest.approx(ds0 + T_ * dds, abs=1e-12)
+        assert p == pytest.approx(p0 + T_ * dp0 + quad * dtw[..., :3], abs=1e-12)
+        assert s == pytest.approx(s0 + T_ * ds0 + quad * dds, abs=1e-12)
+        assert w == pytest.approx(w0, abs=1e-15)
+        if N == 1:
+            exact = manif.SO3Tangent(w0 * T_) + R0
+            assert R.rotation() == pytest.approx(exact.rotation(), abs=1e-10)
+        else:
+            exact = W.quat_mul(W.so3_exp(w0 * T_), R0)
+            assert np.abs(W.quat_to_rot(R) - W.quat_to_rot(exact)).max() < 1e-10
 
 
 @pytest.mark.gpu
