@@ -107,6 +107,11 @@ class IKLinearTask:
         return True
 
     _spline_ok = False         # SE3Task, CoMTask, R3Task: the origin of the set-point can follow a quintic spline on the device
+    _min_jerk_ok = None        # None: as _spline_ok
+
+    def _spline_dim(self):
+        """coordinates of that spline: 3, or the number of joints for a JointTrackingTask (QuinticSpline over R^n)"""
+        return 3
 
     def set_set_point_spline(self, spline, positions=None, boundary=None, cubic=False):
         """Batch extension (no counterpart in the reference, where a Math::QuinticSpline is evaluated on the host and its
@@ -122,15 +127,18 @@ class IKLinearTask:
         if spline is None:
             self._spline, self._spline_version = None, self._spline_version + 1
             return True
-        N = self._kin_dyn.N
+        if self._kin_dyn is None:
+            log().error("[%s::setSetPointSpline] Please call setKinDyn first.", name)
+            return False
+        N, dim = self._kin_dyn.N, self._spline_dim()
         if hasattr(spline, "knots") or (isinstance(spline, (list, tuple)) and len(spline) and hasattr(spline[0], "knots")):
             group = [spline] * N if hasattr(spline, "knots") else list(spline)
             if len(group) != N:
                 log().error("[%s::setSetPointSpline] One spline per robot is expected. Expected: %d. Given: %d.", name, N, len(group))
                 return False
             parts = [g.knots() for g in group]
-            if any(k[0] is None or k[1] is None or k[1].shape[1] != 3 for k in parts):
-                log().error("[%s::setSetPointSpline] Every spline needs its knots set, in R^3.", name)
+            if any(k[0] is None or k[1] is None or k[1].shape[1] != dim for k in parts):
+                log().error("[%s::setSetPointSpline] Every spline needs its knots set, in R^%d.", name, dim)
                 return False
             if any(len(k[0]) != len(parts[0][0]) or np.any(k[0] != parts[0][0]) for k in parts):
                 log().error("[%s::setSetPointSpline] The splines of the robots must share their knot times.", name)
@@ -141,14 +149,14 @@ class IKLinearTask:
             cubic = group[0]._cubic
             times = parts[0][0]
             positions = np.stack([k[1] for k in parts])
-            boundary = np.stack([np.zeros((4, 3)) if k[2] is None else k[2] for k in parts])
+            boundary = np.stack([np.zeros((4, dim)) if k[2] is None else k[2] for k in parts])
             if cubic:
                 boundary = np.ascontiguousarray(boundary[:, [0, 2]])     # velocities only
         else:
             times = np.asarray(spline, dtype=np.float64).reshape(-1)
             positions = np.asarray(positions, dtype=np.float64)
             boundary = None if boundary is None else np.asarray(boundary, dtype=np.float64)
-            if positions.shape != (N, len(times), 3) or (boundary is not None and boundary.shape != (N, 2 if cubic else 4, 3)):
+            if positions.shape != (N, len(times), dim) or (boundary is not None and boundary.shape != (N, 2 if cubic else 4, dim)):
                 log().error("[%s::setSetPointSpline] positions must be [N, n_knots, 3] and boundary [N, 4, 3] ([N, 2, 3] for a cubic spline).", name)
                 return False
         if len(times) < 2:
@@ -171,7 +179,7 @@ class IKLinearTask:
         ``planners.SO3PlannerInertial`` with zero boundary conditions for the rotation).  SE3 / SO3 / CoM / R3 tasks; a
         non-positive duration switches it off."""
         name = type(self).__name__
-        if not (self._spline_ok or isinstance(self, SO3Task)):
+        if not ((self._spline_ok if self._min_jerk_ok is None else self._min_jerk_ok) or isinstance(self, SO3Task)):
             log().error("[%s::setSetPointMinimumJerk] The task has no pose set-point such a generator could drive.", name)
             return False
         T_ = duration.total_seconds() if hasattr(duration, "total_seconds") else float(duration)
@@ -549,6 +557,12 @@ class AngularMomentumTask(IKLinearTask):
 
 class JointTrackingTask(IKLinearTask):
     """JointTrackingTask.cpp:90-112 (key kp, size-checked), :127-155, setSetPoint :157-210"""
+
+    _spline_ok = True          # the joint positions can follow a spline over R^n evaluated on the device
+    _min_jerk_ok = False
+
+    def _spline_dim(self):
+        return self._kin_dyn.getNrOfDegreesOfFreedom()
 
     def initialize(self, param_handler):
         if not self._common_initialize(param_handler):

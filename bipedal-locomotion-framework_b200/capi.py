@@ -329,7 +329,8 @@ class Problem:
 
     def set_setpoint_spline(self, task: int, times, positions, boundary=None, cubic=False):
         """quintic spline through ``positions`` [N, n_knots, 3] at ``times`` [n_knots] (the problem's clock) for the linear part
-        of an SE3 / CoM / R3 task, evaluated on the device at every tick (Math::QuinticSpline semantics); ``boundary``
+        of an SE3 / CoM / R3 task -- or [N, n_knots, n] for the joint positions of a JointTrackingTask --, evaluated on the device
+        at every tick (Math::QuinticSpline semantics); ``boundary``
         [N, 4, 3] = velocity, acceleration at the first knot, velocity, acceleration at the last (None: zero);
         ``times=None`` switches it off.  ``cubic=True``: Math::CubicSpline instead, ``boundary`` [N, 2, 3] = velocity at the
         first and at the last knot"""
@@ -339,11 +340,14 @@ class Problem:
             _check(fn(self.handle, int(task), 0, None, None, None, MEM_HOST))
             return
         tm, x = _f64(times).reshape(-1), _f64(positions)
-        if x.shape != (self.N, len(tm), 3):
-            raise ValueError(f"positions must be [N, n_knots, 3] = {(self.N, len(tm), 3)}, got {x.shape}")
+        # a JointTrackingTask takes a joint-space spline (Spline<VectorXd>): n coordinates instead of 3
+        joint = 0 <= int(task) < len(self.tasks) and int(self.tasks[int(task)].type) == 3   # BLFIK_TASK_JOINT_TRACKING
+        dim = self.model.km.n if joint else 3
+        if x.shape != (self.N, len(tm), dim):
+            raise ValueError(f"positions must be [N, n_knots, {dim}] = {(self.N, len(tm), dim)}, got {x.shape}")
         bc = None if boundary is None else _f64(boundary)
-        if bc is not None and bc.shape != (self.N, 2 if cubic else 4, 3):
-            raise ValueError(f"boundary must be [N, {2 if cubic else 4}, 3], got {bc.shape}")
+        if bc is not None and bc.shape != (self.N, 2 if cubic else 4, dim):
+            raise ValueError(f"boundary must be [N, {2 if cubic else 4}, {dim}], got {bc.shape}")
         _check(fn(self.handle, int(task), len(tm), tm.ctypes.data, x.ctypes.data, None if bc is None else bc.ctypes.data, MEM_HOST))
 
     def evaluate_setpoint(self, task: int, time: float) -> np.ndarray:

@@ -348,7 +348,9 @@ __global__ void __launch_bounds__(128, 4) blfik_assemble_kernel(const AsmParams 
                     if (s_map[8 * t + 7] >= 0) continue;
                     if (tk.type == T_JOINT_TRACKING) {
                         const double* sp = task_record(P, tk, robot);
-                        const double bj = (task_compact(P, tk) ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - sj);
+                        double pj, vj;
+                        joint_setpoint(tk, robot, A.tnow, sp, task_compact(P, tk), n, j, pj, vj);
+                        const double bj = vj + tk.kp_joint[j] * (pj - sj);
                         if (tk.priority == 1) {
                             const double wj = t == A.jw_task ? A.jw[j] : tk.weight[j];
                             dh += wj;

@@ -252,24 +252,24 @@ __global__ void __launch_bounds__(256) blfik_dynamics_kernel(const KinParams P, 
 // coef[robot][interval][k][coordinate], interval j starting at knot j.
 __global__ void __launch_bounds__(128) blfik_spline_coefficients_kernel(long long N, int nk, const double* __restrict__ times,
                                                                         const double* __restrict__ fac, const double* __restrict__ x,
-                                                                        const double* __restrict__ bc, double* __restrict__ coef)
+                                                                        const double* __restrict__ bc, double* __restrict__ coef, int dim)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= N * 3) return;
-    const long long robot = idx / 3;
-    const int c = (int)(idx - robot * 3);
-    const double* xr = x + (size_t)robot * nk * 3 + c;
-    double* cf = coef + (size_t)robot * (nk - 1) * 18 + c;
+    if (idx >= N * dim) return;
+    const long long robot = idx / dim;
+    const int c = (int)(idx - robot * dim), S = 6 * dim;
+    const double* xr = x + (size_t)robot * nk * dim + c;
+    double* cf = coef + (size_t)robot * (nk - 1) * S + c;
     double v0 = 0.0, a0 = 0.0, vf = 0.0, af = 0.0;
     if (bc) {
-        const double* b = bc + (size_t)robot * 12 + c;
-        v0 = b[0], a0 = b[3], vf = b[6], af = b[9];
+        const double* b = bc + (size_t)robot * 4 * dim + c;
+        v0 = b[0], a0 = b[dim], vf = b[2 * dim], af = b[3 * dim];
     }
     const int m = nk - 2;
     double p0 = 0.0, p1 = 0.0;
     for (int i = 0; i < m; i++) {   // forward sweep: r'_i = r_i - M_i r'_{i-1}
         const double Tp = times[i + 1] - times[i], Tn = times[i + 2] - times[i + 1];
-        const double dp = xr[3 * (i + 1)] - xr[3 * i], dn = xr[3 * (i + 2)] - xr[3 * (i + 1)];
+        const double dp = xr[dim * (i + 1)] - xr[dim * i], dn = xr[dim * (i + 2)] - xr[dim * (i + 1)];
         const double ip = 1.0 / Tp, in = 1.0 / Tn;
         double r0 = 60.0 * (dn * in * in * in - dp * ip * ip * ip);
         double r1 = -360.0 * (dp * ip * ip * ip * ip + dn * in * in * in * in);
@@ -280,28 +280,28 @@ __global__ void __launch_bounds__(128) blfik_spline_coefficients_kernel(long lon
             const double t0 = r0 - (f[4] * p0 + f[5] * p1), t1 = r1 - (f[6] * p0 + f[7] * p1);
             r0 = t0, r1 = t1;
         }
-        cf[18 * (i + 1) + 9] = r0, cf[18 * (i + 1) + 12] = r1;
+        cf[S * (i + 1) + 3 * dim] = r0, cf[S * (i + 1) + 4 * dim] = r1;
         p0 = r0, p1 = r1;
     }
     double vn = vf, an = af;
     for (int i = m - 1; i >= 0; i--) {   // back substitution: (v, a)_i = D'_i^-1 (r'_i - U_i (v, a)_{i+1})
         const double* f = fac + 16 * i;
-        double r0 = cf[18 * (i + 1) + 9], r1 = cf[18 * (i + 1) + 12];
+        double r0 = cf[S * (i + 1) + 3 * dim], r1 = cf[S * (i + 1) + 4 * dim];
         if (i < m - 1) r0 -= f[12] * vn + f[13] * an, r1 -= f[14] * vn + f[15] * an;
         vn = f[8] * r0 + f[9] * r1, an = f[10] * r0 + f[11] * r1;
-        cf[18 * (i + 1) + 3] = vn, cf[18 * (i + 1) + 6] = 0.5 * an;
+        cf[S * (i + 1) + dim] = vn, cf[S * (i + 1) + 2 * dim] = 0.5 * an;
     }
-    cf[3] = v0, cf[6] = 0.5 * a0;
+    cf[dim] = v0, cf[2 * dim] = 0.5 * a0;
     for (int j = 0; j < nk - 1; j++) {   // the interval polynomials from their two end states
         const double T = times[j + 1] - times[j], iT = 1.0 / T;
-        const double x0 = xr[3 * j], d = xr[3 * (j + 1)] - x0;
-        const double vs = cf[18 * j + 3], as = 2.0 * cf[18 * j + 6];
-        const double ve = j + 1 <= nk - 2 ? cf[18 * (j + 1) + 3] : vf, ae = j + 1 <= nk - 2 ? 2.0 * cf[18 * (j + 1) + 6] : af;
+        const double x0 = xr[dim * j], d = xr[dim * (j + 1)] - x0;
+        const double vs = cf[S * j + dim], as = 2.0 * cf[S * j + 2 * dim];
+        const double ve = j + 1 <= nk - 2 ? cf[S * (j + 1) + dim] : vf, ae = j + 1 <= nk - 2 ? 2.0 * cf[S * (j + 1) + 2 * dim] : af;
         const double iT3 = iT * iT * iT;
-        cf[18 * j] = x0;
-        cf[18 * j + 9] = 0.5 * iT3 * (20.0 * d - (8.0 * ve + 12.0 * vs) * T - (3.0 * as - ae) * T * T);
-        cf[18 * j + 12] = 0.5 * iT3 * iT * (-30.0 * d + (14.0 * ve + 16.0 * vs) * T + (3.0 * as - 2.0 * ae) * T * T);
-        cf[18 * j + 15] = 0.5 * iT3 * iT * iT * (12.0 * d - 6.0 * (ve + vs) * T - (as - ae) * T * T);
+        cf[S * j] = x0;
+        cf[S * j + 3 * dim] = 0.5 * iT3 * (20.0 * d - (8.0 * ve + 12.0 * vs) * T - (3.0 * as - ae) * T * T);
+        cf[S * j + 4 * dim] = 0.5 * iT3 * iT * (-30.0 * d + (14.0 * ve + 16.0 * vs) * T + (3.0 * as - 2.0 * ae) * T * T);
+        cf[S * j + 5 * dim] = 0.5 * iT3 * iT * iT * (12.0 * d - 6.0 * (ve + vs) * T - (as - ae) * T * T);
     }
 }
 
@@ -311,46 +311,46 @@ __global__ void __launch_bounds__(128) blfik_spline_coefficients_kernel(long lon
 // bc: [N][2][3], velocity at the first and at the last knot.
 __global__ void __launch_bounds__(128) blfik_cubic_spline_coefficients_kernel(long long N, int nk, const double* __restrict__ times,
                                                                               const double* __restrict__ fac, const double* __restrict__ x,
-                                                                              const double* __restrict__ bc, double* __restrict__ coef)
+                                                                              const double* __restrict__ bc, double* __restrict__ coef, int dim)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= N * 3) return;
-    const long long robot = idx / 3;
-    const int c = (int)(idx - robot * 3);
-    const double* xr = x + (size_t)robot * nk * 3 + c;
-    double* cf = coef + (size_t)robot * (nk - 1) * 18 + c;
+    if (idx >= N * dim) return;
+    const long long robot = idx / dim;
+    const int c = (int)(idx - robot * dim), S = 6 * dim;
+    const double* xr = x + (size_t)robot * nk * dim + c;
+    double* cf = coef + (size_t)robot * (nk - 1) * S + c;
     double v0 = 0.0, vf = 0.0;
-    if (bc) v0 = bc[(size_t)robot * 6 + c], vf = bc[(size_t)robot * 6 + 3 + c];
+    if (bc) v0 = bc[(size_t)robot * 2 * dim + c], vf = bc[(size_t)robot * 2 * dim + dim + c];
     const int m = nk - 2;
     double prev = 0.0;
     for (int i = 0; i < m; i++) {
         const double ip = 1.0 / (times[i + 1] - times[i]), in = 1.0 / (times[i + 2] - times[i + 1]);
-        const double dp = xr[3 * (i + 1)] - xr[3 * i], dn = xr[3 * (i + 2)] - xr[3 * (i + 1)];
+        const double dp = xr[dim * (i + 1)] - xr[dim * i], dn = xr[dim * (i + 2)] - xr[dim * (i + 1)];
         const double* f = fac + 16 * i;
         double r = 6.0 * (dp * ip * ip + dn * in * in);
         if (i == 0) r -= f[0] * v0;
         if (i == m - 1) r -= f[12] * vf;
         if (i > 0) r -= f[4] * prev;
-        cf[18 * (i + 1) + 9] = r;
+        cf[S * (i + 1) + 3 * dim] = r;
         prev = r;
     }
     double vn = vf;
     for (int i = m - 1; i >= 0; i--) {
         const double* f = fac + 16 * i;
-        double r = cf[18 * (i + 1) + 9];
+        double r = cf[S * (i + 1) + 3 * dim];
         if (i < m - 1) r -= f[12] * vn;
         vn = f[8] * r;
-        cf[18 * (i + 1) + 3] = vn;
+        cf[S * (i + 1) + dim] = vn;
     }
-    cf[3] = v0;
+    cf[dim] = v0;
     for (int j = 0; j < nk - 1; j++) {
         const double T = times[j + 1] - times[j], iT = 1.0 / T;
-        const double x0 = xr[3 * j], d = xr[3 * (j + 1)] - x0;
-        const double vs = cf[18 * j + 3], ve = j + 1 <= nk - 2 ? cf[18 * (j + 1) + 3] : vf;
-        cf[18 * j] = x0;
-        cf[18 * j + 6] = (3.0 * d - (2.0 * vs + ve) * T) * iT * iT;
-        cf[18 * j + 9] = (-2.0 * d + (vs + ve) * T) * iT * iT * iT;
-        cf[18 * j + 12] = 0.0, cf[18 * j + 15] = 0.0;
+        const double x0 = xr[dim * j], d = xr[dim * (j + 1)] - x0;
+        const double vs = cf[S * j + dim], ve = j + 1 <= nk - 2 ? cf[S * (j + 1) + dim] : vf;
+        cf[S * j] = x0;
+        cf[S * j + 2 * dim] = (3.0 * d - (2.0 * vs + ve) * T) * iT * iT;
+        cf[S * j + 3 * dim] = (-2.0 * d + (vs + ve) * T) * iT * iT * iT;
+        cf[S * j + 4 * dim] = 0.0, cf[S * j + 5 * dim] = 0.0;
     }
 }
 
@@ -361,6 +361,11 @@ __global__ void __launch_bounds__(128) blfik_evaluate_setpoint_kernel(const DevT
     if (robot >= N) return;
     const DevTask& tk = tasks[t];
     const double* sp = tk.setpoint + (size_t)robot * tk.sp_stride;
+    if (tk.type == T_JOINT_TRACKING) {   // [position (n); velocity (n)]
+        const int n = tk.fb_off / 2;
+        for (int j = 0; j < n; j++) joint_setpoint(tk, robot, time, sp, false, n, j, out[(size_t)robot * tk.fb_off + j], out[(size_t)robot * tk.fb_off + n + j]);
+        return;
+    }
     double spl[13];
     const double* use = traj_eval(tk, robot, time, sp, spl);
     for (int c = 0; c < tk.fb_off; c++) out[(size_t)robot * tk.fb_off + c] = use[c];
@@ -829,7 +834,7 @@ static int refresh_tasks(blfik_problem* p)
         d.traj_phase = h.d_traj_phase, d.traj_omega = h.d_traj_phase ? h.traj_omega : 0.0;
         for (int c = 0; c < 6; c++) d.traj_amp[c] = h.traj_amp[c];
         d.mj_target = h.mj_T > 0.0 ? h.d_mj_target : nullptr, d.mj_t0 = h.mj_t0, d.mj_T = h.mj_T;
-        d.sp_nk = h.sp_nk, d.sp_times = h.d_sp_times, d.sp_coef = h.d_sp_coef;
+        d.sp_nk = h.sp_nk, d.sp_times = h.d_sp_times, d.sp_coef = h.d_sp_coef, d.sp_dim = h.d.type == BLFIK_TASK_JOINT_TRACKING ? p->model->n : 3;
         d.gen = (d.traj_omega != 0.0 ? 1 : 0) | (d.mj_target ? 2 : 0) | (h.sp_nk >= 2 ? 4 : 0);
         for (int c = 0; c < 9; c++) d.Fr[c] = (c % 4 == 0) ? 1.0 : 0.0;
         for (int c = 0; c < 3; c++) d.Fp[c] = 0.0;
@@ -1322,8 +1327,9 @@ static int set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_knots, con
     CHECK_P(p, "blfik_set_setpoint_spline");
     CHECK_TASK(p, t, "blfik_set_setpoint_spline");
     HostTask& h = p->tasks[t];
-    if (h.d.type != BLFIK_TASK_SE3 && h.d.type != BLFIK_TASK_R3 && h.d.type != BLFIK_TASK_COM)
-        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] task %d is not an SE3 / R3 / CoM task", t);
+    if (h.d.type != BLFIK_TASK_SE3 && h.d.type != BLFIK_TASK_R3 && h.d.type != BLFIK_TASK_COM && h.d.type != BLFIK_TASK_JOINT_TRACKING)
+        return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_set_setpoint_spline] task %d is not an SE3 / R3 / CoM / JointTracking task", t);
+    const int dim = h.d.type == BLFIK_TASK_JOINT_TRACKING ? p->model->n : 3;   // Spline<VectorXd> in joint space, Spline<Vector3d> otherwise
     if (n_knots == 0) {   // switch the generator off
         h.sp_nk = 0;
         p->tasks_dirty = true;
@@ -1379,10 +1385,10 @@ static int set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_knots, con
         p->tasks_dirty = true;
         CU(cudaMalloc((void**)&h.d_sp_times, (size_t)n_knots * sizeof(double)));
         CU(cudaMalloc((void**)&h.d_sp_fac, (size_t)16 * n_knots * sizeof(double)));
-        CU(cudaMalloc((void**)&h.d_sp_coef, (size_t)p->N * (n_knots - 1) * 18 * sizeof(double)));
+        CU(cudaMalloc((void**)&h.d_sp_coef, (size_t)p->N * (n_knots - 1) * 6 * dim * sizeof(double)));
         h.sp_cap = n_knots;
     }
-    const size_t npos = (size_t)p->N * n_knots * 3, nbc = (size_t)p->N * (cubic ? 6 : 12);
+    const size_t npos = (size_t)p->N * n_knots * dim, nbc = (size_t)p->N * (cubic ? 2 : 4) * dim;
     const double *d_x = positions, *d_bc = boundary;
     double* stage = nullptr;
     if (mem != BLFIK_MEM_DEVICE) {
@@ -1393,13 +1399,13 @@ static int set_setpoint_spline(blfik_problem* p, int32_t t, int32_t n_knots, con
     }
     cudaMemcpyAsync(h.d_sp_times, times, (size_t)n_knots * sizeof(double), cudaMemcpyHostToDevice, p->stream);
     cudaMemcpyAsync(h.d_sp_fac, fac.data(), fac.size() * sizeof(double), cudaMemcpyHostToDevice, p->stream);
-    const long long threads = (long long)p->N * 3;
+    const long long threads = (long long)p->N * dim;
     if (cubic)
         blfik_cubic_spline_coefficients_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, p->stream>>>(p->N, n_knots, h.d_sp_times, h.d_sp_fac,
-                                                                                                       d_x, d_bc, h.d_sp_coef);
+                                                                                                       d_x, d_bc, h.d_sp_coef, dim);
     else
         blfik_spline_coefficients_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, p->stream>>>(p->N, n_knots, h.d_sp_times, h.d_sp_fac, d_x,
-                                                                                                 d_bc, h.d_sp_coef);
+                                                                                                 d_bc, h.d_sp_coef, dim);
     p->launches++;
     cudaError_t e = cudaGetLastError();
     if (stage) {   // the pageable sources (times, fac, positions) are consumed before this returns

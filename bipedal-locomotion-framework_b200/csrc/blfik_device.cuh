@@ -77,6 +77,7 @@ struct DevTask {
     int sp_nk;
     const double* sp_times;  // device [sp_nk]
     const double* sp_coef;   // device, written by blfik_spline_coefficients_kernel
+    int sp_dim;              // coordinates of the spline: 3 (SE3 / R3 / CoM), n for a JointTrackingTask (Spline<VectorXd>)
 };
 
 struct Settings {
@@ -517,11 +518,10 @@ __device__ __forceinline__ const double* traj_eval(const DevTask& tk, long long 
 }
 // Linear part of the set-point from the task's quintic spline: position = the spline, feed-forward = stored + its derivative.
 // Outside the knots the end states hold, derivative included (Spline.h:607-625).
-__device__ __forceinline__ void spline_eval(const DevTask& tk, long long robot, double t, const double* sp, double* spl, int vo)
+__device__ __forceinline__ void spline_segment(const DevTask& tk, double t, int& seg, double& tl)
 {
     const int nk = tk.sp_nk;
-    int seg = 0;
-    double tl = 0.0;
+    seg = 0, tl = 0.0;
     if (t >= tk.sp_times[nk - 1]) {
         seg = nk - 2, tl = tk.sp_times[nk - 1] - tk.sp_times[nk - 2];
     } else if (t >= tk.sp_times[0]) {
@@ -532,7 +532,31 @@ __device__ __forceinline__ void spline_eval(const DevTask& tk, long long robot, 
         }
         seg = lo, tl = t - tk.sp_times[lo];
     }
-    const double* c = tk.sp_coef + ((size_t)robot * (nk - 1) + seg) * 18;
+}
+// JointTrackingTask set-point of joint j at time t (JointTrackingTask.cpp:162-185: position and feed-forward velocity): the
+// stored record, or -- with a joint-space spline attached (Math::QuinticSpline<VectorXd> / CubicSpline, whose output the
+// reference's callers hand to setSetPoint every period) -- the position from the spline and the stored velocity plus the
+// spline's derivative.  Compact packed records carry no feed-forward velocity.
+__device__ __forceinline__ void joint_setpoint(const DevTask& tk, long long robot, double t, const double* sp, bool compact, int n, int j,
+                                               double& pos, double& vel)
+{
+    pos = sp[j], vel = compact ? 0.0 : sp[n + j];
+    if (tk.gen & 4) {
+        int seg;
+        double tl;
+        spline_segment(tk, t, seg, tl);
+        const double* c = tk.sp_coef + ((size_t)robot * (tk.sp_nk - 1) + seg) * 6 * n + j;
+        const double c1 = c[n], c2 = c[2 * n], c3 = c[3 * n], c4 = c[4 * n], c5 = c[5 * n];
+        pos = c[0] + tl * (c1 + tl * (c2 + tl * (c3 + tl * (c4 + tl * c5))));
+        vel += c1 + tl * (2.0 * c2 + tl * (3.0 * c3 + tl * (4.0 * c4 + tl * 5.0 * c5)));
+    }
+}
+__device__ __forceinline__ void spline_eval(const DevTask& tk, long long robot, double t, const double* sp, double* spl, int vo)
+{
+    int seg;
+    double tl;
+    spline_segment(tk, t, seg, tl);
+    const double* c = tk.sp_coef + ((size_t)robot * (tk.sp_nk - 1) + seg) * 18;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
         const double c1 = c[3 + k], c2 = c[6 + k], c3 = c[9 + k], c4 = c[12 + k], c5 = c[15 + k];
@@ -750,7 +774,9 @@ __device__ __forceinline__ void k2_assemble(const TickParams& P, const WM& w, lo
             for (int j = lane; j < n; j += 32) {
                 const int i = 6 + j;
                 if (tk.type == T_JOINT_TRACKING) {  // JointTrackingTask.cpp:151
-                    const double bj = (compact ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - s[j]);
+                    double pj, vj;
+                    joint_setpoint(tk, robot, tnow, sp, compact, n, j, pj, vj);
+                    const double bj = vj + tk.kp_joint[j] * (pj - s[j]);
                     if (tk.priority == 1) {
                         w.Hs[ROWS ? i : i * LD + i] += tk.weight[j];
                         w.g[i] -= tk.weight[j] * bj;

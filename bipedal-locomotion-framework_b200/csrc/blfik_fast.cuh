@@ -885,7 +885,9 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
                     const double* sp = task_record(P, tk, robot);
                     const int j = lane - 6;
                     if (tk.type == T_JOINT_TRACKING) {
-                        const double bj = (task_compact(P, tk) ? 0.0 : sp[n + j]) + tk.kp_joint[j] * (sp[j] - sj);
+                        double pj, vj;
+                        joint_setpoint(tk, robot, P.t0 + tick * P.dt, sp, task_compact(P, tk), n, j, pj, vj);
+                        const double bj = vj + tk.kp_joint[j] * (pj - sj);
                         if (tk.priority == 1) {
                             dh += tk.weight[j];
                             gd += tk.weight[j] * bj;

@@ -95,7 +95,9 @@ public:
      *  solver's time (QPInverseKinematics::setTime; blfik_set_setpoint_spline) instead of a Math::QuinticSpline evaluated
      *  on the host whose point goes to setSetPoint every period.  One spline per robot, all with the same knot times. */
     virtual bool acceptsSetPointSpline() const { return false; }
-    template <class SplineType> bool setSetPointSpline(const std::vector<SplineType>& splines)   // Math::QuinticSpline<Vector3d> or Math::CubicSpline<Vector3d>
+    /** coordinates of that spline: 3, or the number of joints for a JointTrackingTask (Math::QuinticSpline<VectorXd>) */
+    virtual std::size_t splineDimension() const { return 3; }
+    template <class SplineType> bool setSetPointSpline(const std::vector<SplineType>& splines)   // Math::QuinticSpline<T> or Math::CubicSpline<T>, T = Vector3d / VectorXd
     {
         const std::size_t N = m_kinDyn ? m_kinDyn->getBatchSize() : 0;
         if (!acceptsSetPointSpline()) {
@@ -111,8 +113,9 @@ public:
             log()->error("[Spline::setKnots] The number of knots has to be at least 2.");
             return false;
         }
-        constexpr std::size_t nbc = SplineType::isCubic ? 6 : 12;   // the cubic spline takes the two end velocities only
-        std::vector<double> times(first.size()), pos(N * first.size() * 3), bc(N * nbc, 0.0);
+        const std::size_t dim = splineDimension();
+        const std::size_t nbc = (SplineType::isCubic ? 2 : 4) * dim;   // the cubic spline takes the two end velocities only
+        std::vector<double> times(first.size()), pos(N * first.size() * dim), bc(N * nbc, 0.0);
         for (std::size_t k = 0; k < first.size(); k++) times[k] = std::chrono::duration<double>(first[k].time).count();
         for (std::size_t i = 0; i < N; i++) {
             const auto& kn = splines[i].knots();
@@ -125,15 +128,21 @@ public:
                     log()->error("[{}::setSetPointSpline] The splines of the robots must share their knot times.", className());
                     return false;
                 }
-                for (int c = 0; c < 3; c++) pos[(i * kn.size() + k) * 3 + c] = kn[k].position[c];
+                if (kn[k].position.size() != dim) {
+                    log()->error("[{}::setSetPointSpline] The size of the knot is different from the one expected. Expected: {} Retrieved {}.", className(), dim,
+                                 kn[k].position.size());
+                    return false;
+                }
+                for (std::size_t c = 0; c < dim; c++) pos[(i * kn.size() + k) * dim + c] = kn[k].position[c];
             }
             typename SplineType::DerivativeBoundaryConditions ic, fc;
             if (splines[i].boundaryConditions(ic, fc))
-                for (int c = 0; c < 3; c++) {
+                for (std::size_t c = 0; c < dim; c++) {
                     if (SplineType::isCubic)
-                        bc[i * 6 + c] = ic.velocity[c], bc[i * 6 + 3 + c] = fc.velocity[c];
+                        bc[i * nbc + c] = ic.velocity[c], bc[i * nbc + dim + c] = fc.velocity[c];
                     else
-                        bc[i * 12 + c] = ic.velocity[c], bc[i * 12 + 3 + c] = ic.acceleration[c], bc[i * 12 + 6 + c] = fc.velocity[c], bc[i * 12 + 9 + c] = fc.acceleration[c];
+                        bc[i * nbc + c] = ic.velocity[c], bc[i * nbc + dim + c] = ic.acceleration[c], bc[i * nbc + 2 * dim + c] = fc.velocity[c],
+                                     bc[i * nbc + 3 * dim + c] = fc.acceleration[c];
                 }
         }
         for (std::size_t k = 0; k + 1 < times.size(); k++)
@@ -465,6 +474,11 @@ public:
     Type type() const override { return Type::equality; }
     bool fillDescriptor(blfik_task_desc& d, std::vector<std::vector<double>>& keep) const override;
     std::size_t setPointLength() const override { return m_kinDyn ? 2 * m_kinDyn->getNrOfDegreesOfFreedom() : 0; }
+    /** the joint positions of the set-point can follow a Math::QuinticSpline<VectorXd> / CubicSpline<VectorXd> evaluated on the
+     *  device (position = the spline, velocity = the stored feed-forward + its derivative) */
+    bool acceptsSetPointSpline() const override { return true; }
+    std::size_t splineDimension() const override { return m_kinDyn ? m_kinDyn->getNrOfDegreesOfFreedom() : 0; }
+    bool acceptsMinimumJerk() const override { return false; }
 
 private:
     VectorXd m_kp;

@@ -1558,6 +1558,13 @@ bool QPInverseKinematics::tick(double dt, uint32_t flags)
                 if (blfik_set_setpoint(prob, static_cast<int32_t>(t), e.task->setPointBuffer().data(), BLFIK_MEM_HOST) != BLFIK_OK) return fail("Unable to set the set-point");
                 e.uploadedSetPoint = e.task->setPointVersion();
             }
+            // A generator is attached to a stored set-point.  On the packed path the set-points live in the records and the device
+            // copy was never written: it is seeded once, so that the attach calls below find it (the ticks keep reading the records).
+            if (pimpl->packedPath && spl > 0 && !(t < pimpl->sharedNow.size() && pimpl->sharedNow[t]) &&
+                ((e.task->acceptsMinimumJerk() && e.task->minimumJerkVersion() != e.uploadedMinJerk && e.task->minimumJerkDuration() > 0) ||
+                 (e.task->acceptsSetPointSpline() && e.task->splineVersion() != e.uploadedSpline && !e.task->splineTimes().empty())) &&
+                blfik_set_setpoint(prob, static_cast<int32_t>(t), e.task->setPointBuffer().data() + sh.first * spl, BLFIK_MEM_HOST) != BLFIK_OK)
+                return fail("Unable to set the set-point");
             if (e.task->acceptsMinimumJerk() && e.task->minimumJerkVersion() != e.uploadedMinJerk) {   // setSetPointMinimumJerk(...) since the last tick
                 const double T = e.task->minimumJerkDuration();
                 if (blfik_set_setpoint_minimum_jerk(prob, static_cast<int32_t>(t), T > 0 ? e.task->minimumJerkTarget().data() + sh.first * spl : nullptr, T, BLFIK_MEM_HOST) != BLFIK_OK)
@@ -1567,10 +1574,10 @@ bool QPInverseKinematics::tick(double dt, uint32_t flags)
             if (e.task->acceptsSetPointSpline() && e.task->splineVersion() != e.uploadedSpline) {   // setSetPointSpline(...) since the last tick
                 const auto& tm = e.task->splineTimes();
                 const auto set = e.task->splineIsCubic() ? blfik_set_setpoint_cubic_spline : blfik_set_setpoint_spline;
-                const std::size_t nbc = e.task->splineIsCubic() ? 6 : 12;
+                const std::size_t dim = e.task->splineDimension(), nbc = (e.task->splineIsCubic() ? 2 : 4) * dim;
                 const int rc = tm.empty() ? set(prob, static_cast<int32_t>(t), 0, nullptr, nullptr, nullptr, BLFIK_MEM_HOST)
                                           : set(prob, static_cast<int32_t>(t), static_cast<int32_t>(tm.size()), tm.data(),
-                                                e.task->splinePositions().data() + sh.first * tm.size() * 3, e.task->splineBoundary().data() + sh.first * nbc, BLFIK_MEM_HOST);
+                                                e.task->splinePositions().data() + sh.first * tm.size() * dim, e.task->splineBoundary().data() + sh.first * nbc, BLFIK_MEM_HOST);
                 if (rc != BLFIK_OK) return fail("Unable to set the set-point spline");
                 if (last) e.uploadedSpline = e.task->splineVersion();
             }

@@ -1010,6 +1010,79 @@ static void testSetPointSpline(const char* modelPath, std::size_t N)
     }
 }
 
+// A JointTrackingTask whose joint positions follow a Math::QuinticSpline<VectorXd> / CubicSpline<VectorXd>: evaluated on the device
+// inside the tick (setSetPointSpline) against the reference's way -- the spline evaluated on the host, its point handed to
+// setSetPoint(position, velocity) every period.
+template <class SplineT> static void testJointSetPointSpline(const char* modelPath, std::size_t N)
+{
+    struct Solver {
+        std::shared_ptr<KinDynBatch> kinDyn;
+        std::shared_ptr<JointTrackingTask> reg;
+        QPFixedBaseInverseKinematics ik;
+    };
+    std::vector<VectorXd> s0(N);
+    auto make = [&](Solver& S) {
+        S.kinDyn = loadKinDyn(modelPath, N);
+        const std::size_t n = S.kinDyn->getNrOfDegreesOfFreedom();
+        auto ikHandler = std::make_shared<StdImplementation>();
+        ikHandler->setParameter("robot_velocity_variable_name", robotVelocity);
+        REQUIRE(S.ik.setKinDyn(S.kinDyn) && S.ik.initialize(ikHandler));
+        S.reg = std::make_shared<JointTrackingTask>();
+        auto rh = std::make_shared<StdImplementation>();
+        rh->setParameter("robot_velocity_variable_name", robotVelocity), rh->setParameter("kp", std::vector<double>(n, 2.0));
+        REQUIRE(S.reg->setKinDyn(S.kinDyn) && S.reg->initialize(rh) && S.ik.addTask(S.reg, "reg", 1, VectorXd(n, 1.0)));
+        VariablesHandler vh;
+        vh.addVariable(robotVelocity, n + 6);
+        REQUIRE(S.ik.finalize(vh));
+        std::mt19937 gen(3);
+        for (std::size_t i = 0; i < N; i++) {
+            s0[i] = nominalJoints(*S.kinDyn, gen, 0.2);
+            REQUIRE(S.kinDyn->setRobotState({0.0, 0.0, 0.7}, SO3d::Identity(), s0[i], i) && S.reg->setSetPoint(s0[i], i));
+        }
+    };
+    Solver dev, host;
+    make(dev), make(host);
+    const std::size_t n = dev.kinDyn->getNrOfDegreesOfFreedom();
+    std::mt19937 gen(23);
+    std::uniform_real_distribution<double> uni(-0.05, 0.05);
+    std::vector<SplineT> splines(N);
+    const std::vector<std::chrono::nanoseconds> time{0ms, 250ms, 600ms, 1000ms};
+    for (std::size_t i = 0; i < N; i++) {
+        std::vector<VectorXd> knots(4, s0[i]);
+        for (std::size_t k = 1; k < 4; k++)
+            for (std::size_t j = 0; j < n; j++) knots[k][j] += uni(gen) * k;
+        VectorXd v0(n), zero(n, 0.0);
+        for (auto& v : v0) v = uni(gen);
+        REQUIRE(splines[i].setKnots(knots, time));
+        REQUIRE(splines[i].setInitialConditions(v0, zero) && splines[i].setFinalConditions(zero, zero));
+    }
+    log()->setLevel(Logger::Level::off);
+    REQUIRE_FALSE(dev.reg->setSetPointSpline(std::vector<SplineT>(N + 1)));                              // one per robot
+    REQUIRE_FALSE(dev.reg->setSetPointSpline(std::vector<BipedalLocomotion::Math::QuinticSpline<Vector3d>>(N)));   // no knots
+    {
+        std::vector<BipedalLocomotion::Math::QuinticSpline<Vector3d>> wrong(N);
+        for (auto& w : wrong) REQUIRE(w.setKnots({Vector3d{0, 0, 0}, Vector3d{1, 1, 1}}, {0ms, 100ms}));
+        REQUIRE_FALSE(dev.reg->setSetPointSpline(wrong));                                                // three coordinates, n joints
+    }
+    REQUIRE_FALSE(dev.reg->setSetPointMinimumJerk(std::vector<double>(N * 2 * n, 0.0), 100ms));          // no such generator in joint space
+    log()->setLevel(Logger::Level::warn);
+    REQUIRE(dev.reg->setSetPointSpline(splines));
+    double worst = 0.0;
+    for (const std::chrono::nanoseconds t : {-100ms, 0ms, 120ms, 250ms, 777ms, 1000ms, 1400ms}) {
+        REQUIRE(dev.ik.setTime(t) && dev.ik.advance());
+        for (std::size_t i = 0; i < N; i++) {
+            VectorXd p, v, a;
+            REQUIRE(splines[i].evaluatePoint(t, p, v, a));
+            REQUIRE(host.reg->setSetPoint(p, v, i));
+        }
+        REQUIRE(host.ik.advance());
+        for (std::size_t k = 0; k < dev.ik.getBatchOutput().size(); k++) worst = std::max(worst, std::abs(dev.ik.getBatchOutput()[k] - host.ik.getBatchOutput()[k]));
+    }
+    REQUIRE(worst < 1e-8);
+    dev.reg->clearSetPointSpline();
+    REQUIRE(dev.ik.advance());
+}
+
 static void testFixedBase(const char* modelPath, std::size_t N)
 {
     constexpr auto dT = 10ms;
@@ -1333,6 +1406,8 @@ int main(int argc, char** argv)
         testFixedBase(argv[2], 1);
         testFixedBase(argv[2], 5);
         testSetPointSpline(argv[2], 3);
+        testJointSetPointSpline<BipedalLocomotion::Math::QuinticSpline<VectorXd>>(argv[2], 3);
+        testJointSetPointSpline<BipedalLocomotion::Math::CubicSpline<VectorXd>>(argv[2], 70);   // the packed-record path
         testIntegrator();
         testAccelerationIntegrator();
     }

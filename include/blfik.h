@@ -219,6 +219,10 @@ int blfik_set_setpoint_minimum_jerk(blfik_problem* problem, int32_t task, const 
  *   positions  [N][n_knots][3], the knots of every robot;
  *   boundary   [N][4][3]: velocity and acceleration at the first knot, velocity and acceleration at the last one
  *              (NULL: all zero);
+ * On a JointTrackingTask the spline lives in joint space (Math::QuinticSpline<Eigen::VectorXd>, whose output the reference's
+ * callers hand to JointTrackingTask::setSetPoint(position, velocity), JointTrackingTask.cpp:162-185): positions
+ * [N][n_knots][n_dofs], boundary [N][4][n_dofs]; the joint positions of the set-point are the spline, the joint velocities the
+ * stored ones plus its derivative (coefficients: 48 n_dofs (n_knots - 1) bytes per robot of device memory);
  * `mem` tells where positions and boundary live.  The velocities and accelerations at the interior knots are those that
  * make the third and fourth derivative continuous (the reference's linear system, solved here on the device for all
  * robots at once).  At a tick with time t the position of the set-point is the spline, its feed-forward velocity the stored

@@ -1237,7 +1237,7 @@ def test_quintic_spline_setpoint_generator(path):
         pr.set_setpoint_minimum_jerk(1, foot_target, dur)
         pr.set_setpoint_spline(0, t_com, x_com, bc_com)
         pr.set_setpoint_spline(1, t_foot, x_foot)
-    for bad in (lambda: prob.set_setpoint_spline(6, t_foot, x_foot),                      # joint tasks have no such generator
+    for bad in (lambda: prob.set_setpoint_spline(3, t_foot, x_foot),                      # limit tasks take no set-point
                 lambda: prob.set_setpoint_spline(5, t_foot, x_foot),                      # nor has SO3
                 lambda: prob.set_setpoint_spline(0, t_foot[:1], x_foot[:, :1]),           # Spline.h:338-342
                 lambda: prob.set_setpoint_spline(0, [0.0, 0.01, 0.01], x_foot),           # Spline.h:444-448
@@ -1283,6 +1283,79 @@ def test_quintic_spline_setpoint_generator(path):
     prob.set_setpoint_spline(1, None, None)
     prob.set_setpoint_spline(0, None, None)
     prob.tick(1, dt, integrate=False)
+    prob.close(), whole.close()
+
+
+@pytest.mark.parametrize("cubic", [False, True])
+@pytest.mark.parametrize("path", PATHS)
+def test_joint_space_spline_setpoint_generator(path, cubic):
+    """A JointTrackingTask fed by a joint-space spline on the device (Math::QuinticSpline<VectorXd> / CubicSpline<VectorXd> whose
+    output the reference's callers hand to JointTrackingTask::setSetPoint(position, velocity) every period): four knots per
+    joint and robot, non-zero boundary velocities (and accelerations for the quintic).  (a) blfik_evaluate_setpoint against the
+    host spline at times before, on, between and after the knots; (b) a lock-step closed loop against the oracle fed with the
+    host-evaluated set-points; (c) one multi-tick launch against the tick-by-tick run; (d) with the regularisation set-point
+    shared by the batch; (e) switched off, the stored set-point is back."""
+    from oracle.spline import cubic_spline_coefficients, quintic_spline_coefficients, spline_evaluate
+    w = W.config(5)
+    N, NT = 12, 30
+    dt, n = w.dt, w.model.n
+    inp = W.synth_inputs(w, N, 5)
+    rng = np.random.default_rng(61)
+    ti = next(i for i, t in enumerate(w.tasks) if t.type == T.TASK_JOINT_TRACKING)
+    tk = np.array([0.003, 0.011, 0.019, 0.026])
+    xk = inp.setpoints[ti][:, None, :n] + np.cumsum(rng.uniform(-0.002, 0.002, (N, 4, n)), axis=1)
+    if cubic:
+        bc = rng.uniform(-0.05, 0.05, (N, 2, n))
+        co = [cubic_spline_coefficients(tk, xk[i], bc[i, 0], bc[i, 1])[0] for i in range(N)]
+    else:
+        bc = np.stack([rng.uniform(-0.05, 0.05, (N, n)), rng.uniform(-1.0, 1.0, (N, n)), rng.uniform(-0.05, 0.05, (N, n)), rng.uniform(-1.0, 1.0, (N, n))], axis=1)
+        co = [quintic_spline_coefficients(tk, xk[i], *bc[i])[0] for i in range(N)]
+
+    def joint_setpoint_at(t):
+        sp = inp.setpoints[ti].copy()
+        for i in range(N):
+            pos, vel, _ = spline_evaluate(tk, co[i], t)
+            sp[i, :n], sp[i, n:] = pos, inp.setpoints[ti][i, n:] + vel
+        return sp
+
+    model, prob = make(w.model, w.tasks, N, path)
+    _, whole = make(w.model, w.tasks, N, path)
+    for pr in (prob, whole):
+        pr.set_inputs(inp)
+        pr.set_setpoint_spline(ti, tk, xk, bc, cubic=cubic)
+    with pytest.raises(ValueError):
+        prob.set_setpoint_spline(ti, tk, xk[:, :, :3], cubic=cubic)          # three coordinates are for the Cartesian tasks
+    for t in (-0.001, 0.003, 0.0071, 0.011, 0.0222, 0.026, 0.04):
+        got = prob.evaluate_setpoint(ti, t)
+        assert np.abs(got - joint_setpoint_at(t)).max() <= 1e-12, t
+    o = Oracle(w.model, w.tasks)
+    p, q, s = inp.base_pos.copy(), inp.base_quat.copy(), inp.s.copy()
+    for k in range(NT):
+        sps = [None if sp is None else sp.copy() for sp in inp.setpoints]
+        sps[ti] = joint_setpoint_at(k * dt)
+        nur, str_, _ = o.tick_batch(p.copy(), q.copy(), s.copy(), sps, dt_integrate=dt)
+        prob.tick(1, dt, integrate=True, warm_start=True)
+        nu = prob.get_output()
+        st, _ = prob.get_status()
+        p, q, s = prob.get_state()
+        ok = (st == 0) & (str_ == 0)
+        assert ok.mean() > 0.9
+        assert np.abs(nu - nur)[ok].max() <= TOL_NU, k
+    assert NT * dt > tk[-1]
+    whole.tick(NT, dt, integrate=True, warm_start=True)
+    pw, qw, sw = whole.get_state()
+    assert np.abs(sw - s).max() < 1e-9 and np.abs(pw - p).max() < 1e-9
+    # (d) a batch-shared regularisation record (velocity feed-forward of robot 0 for everybody) under the same per-robot splines
+    shared = inp.setpoints[ti][0].copy()
+    prob.set_setpoint_shared(ti, shared)
+    prob.set_setpoint_spline(ti, tk, xk, bc, cubic=cubic)
+    got = prob.evaluate_setpoint(ti, 0.015)
+    ref = joint_setpoint_at(0.015)
+    assert np.abs(got[:, :n] - ref[:, :n]).max() <= 1e-12
+    assert np.abs(got[:, n:] - (ref[:, n:] - inp.setpoints[ti][:, n:] + shared[n:])).max() <= 1e-12
+    # (e) off: the stored record again
+    prob.set_setpoint_spline(ti, None, None)
+    assert np.array_equal(prob.evaluate_setpoint(ti, 0.015), np.broadcast_to(shared, (N, 2 * n)))
     prob.close(), whole.close()
 
 

@@ -611,11 +611,11 @@ def test_set_point_spline_through_the_bindings():
         assert ik.add_task(com, "com", 0) and ik.add_task(reg, "reg", 1, weight=[1.0] * n)
         var = blf.system.VariablesHandler()
         assert var.add_variable("robotVelocity", n + 6) and ik.finalize(var)
-        return ik, com, c
+        return ik, com, c, reg
 
     rng = np.random.default_rng(4)
-    ik_dev, com_dev, c = make()
-    ik_host, com_host, _ = make()
+    ik_dev, com_dev, c, reg_dev = make()
+    ik_host, com_host, _, reg_host = make()
     times = [0.0, 0.3, 0.5, 1.0]
     splines = []
     for i in range(N):
@@ -623,8 +623,10 @@ def test_set_point_spline_through_the_bindings():
         assert sp.set_knots([c + rng.uniform(-0.01, 0.01, 3) * k for k in range(4)], times)
         assert sp.set_initial_conditions(rng.uniform(-0.01, 0.01, 3), np.zeros(3)) and sp.set_final_conditions(np.zeros(3), np.zeros(3))
         splines.append(sp)
-    reg_only = blf.ik.JointTrackingTask()
-    assert not reg_only.set_set_point_spline(splines[0])
+    reg_only = blf.ik.SO3Task()
+    assert not reg_only.set_set_point_spline(splines[0])                # no position set-point
+    assert not blf.ik.JointTrackingTask().set_set_point_spline(splines[0])   # no kinDyn yet
+    assert not reg_dev.set_set_point_spline(splines)                    # R^3 knots, n joints
     assert not com_dev.set_set_point_spline(splines[:2])                # one per robot
     assert com_dev.set_set_point_spline(splines)
     pos, vel = np.zeros(3), np.zeros(3)
@@ -640,7 +642,7 @@ def test_set_point_spline_through_the_bindings():
     assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
     # the minimum-jerk generator through the task: from c to c + d over 0.5 s, starting at the solver's time of the next advance
     d = np.array([0.01, -0.02, 0.005])
-    assert not reg_only.set_set_point_minimum_jerk(np.zeros(6), 0.5)
+    assert not reg_dev.set_set_point_minimum_jerk(np.zeros(2 * n), 0.5)   # no such generator in joint space
     assert com_dev.set_set_point_minimum_jerk(np.concatenate([c + d, np.zeros(3)]), timedelta(seconds=0.5))
     assert ik_dev.set_time(2.0) and ik_dev.advance()                     # tau = 0: still at c
     assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
@@ -652,6 +654,27 @@ def test_set_point_spline_through_the_bindings():
         assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
     assert com_dev.set_set_point_minimum_jerk(None, 0.0) and ik_dev.advance()
     assert com_host.set_set_point(position=c) and ik_host.advance()
+    assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
+
+    # a joint-space spline (QuinticSpline / CubicSpline over R^n) on the JointTrackingTask, one object per robot
+    for cls in (blf.math.QuinticSpline, blf.math.CubicSpline):
+        jsplines = []
+        for i in range(N):
+            sp = cls()
+            assert sp.set_knots([model.q_nominal + rng.uniform(-0.02, 0.02, n) * k for k in range(4)], times)
+            assert sp.set_initial_conditions(rng.uniform(-0.02, 0.02, n), np.zeros(n)) and sp.set_final_conditions(np.zeros(n), np.zeros(n))
+            jsplines.append(sp)
+        assert reg_dev.set_set_point_spline(jsplines)
+        jp, jv = np.zeros(n), np.zeros(n)
+        for t in (-0.1, 0.0, 0.12, 0.3, 0.77, 1.0, 1.4):
+            assert ik_dev.set_time(t) and ik_dev.advance()
+            for i in range(N):
+                assert jsplines[i].evaluate_point(t, jp, jv)
+                assert reg_host.set_set_point(joint_position=jp, joint_velocity=jv, instance=i)
+            assert ik_host.advance()
+            assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
+        assert reg_dev.set_set_point_spline(None)
+    assert reg_host.set_set_point(joint_position=model.q_nominal) and ik_host.advance() and ik_dev.advance()
     assert np.abs(ik_dev.get_batch_output() - ik_host.get_batch_output()).max() < 1e-8
 
 
