@@ -41,7 +41,7 @@ EXPORTS = [
     "blfik_set_feedback", "blfik_feedback_len", "blfik_record_len", "blfik_set_setpoint_minimum_jerk", "blfik_set_setpoint_spline", "blfik_set_setpoint_cubic_spline", "blfik_evaluate_setpoint",
     "blfik_packed_record_len_ex", "blfik_packed_offset_ex", "blfik_packed_part_len",
     "blfik_set_setpoint_shared", "blfik_kernel_timing", "blfik_get_kernel_times", "blfik_host_alloc", "blfik_host_free",
-    "blfik_set_weight_schedule", "blfik_get_weight", "blfik_integrate_acceleration_state", "blfik_dynamics",
+    "blfik_set_weight_schedule", "blfik_get_weight", "blfik_integrate_acceleration_state", "blfik_dynamics", "blfik_bias_forces",
 ]
 
 
@@ -476,6 +476,19 @@ class Problem:
         self.L.blfik_dynamics.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int32]
         _check(self.L.blfik_dynamics(self.handle, M.ctypes.data, G.ctypes.data, float(gravity), MEM_HOST))
         return M, G
+
+    def bias_forces(self, nu, frames: Sequence[int] = (), gravity: float = 9.80665):
+        """generalised bias forces h = C(q, nu) nu + g(q) [N, nv], the bias accelerations Jdot nu of ``frames`` [N, nframes, 6] and
+        of the CoM [N, 3] for the current state and the generalised velocity ``nu`` [N, nv] (MIXED)"""
+        v = _f64(nu)
+        if v.shape != (self.N, self.nv):
+            raise ValueError(f"nu must be [N, nv] = {(self.N, self.nv)}, got {v.shape}")
+        fr = np.ascontiguousarray(frames, dtype=np.int32)
+        h, fb, cb = np.empty((self.N, self.nv)), np.empty((self.N, len(fr), 6)), np.empty((self.N, 3))
+        self.L.blfik_bias_forces.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32]
+        _check(self.L.blfik_bias_forces(self.handle, v.ctypes.data, float(gravity), h.ctypes.data, fr.ctypes.data if len(fr) else None, len(fr),
+                                        fb.ctypes.data if len(fr) else None, cb.ctypes.data, MEM_HOST))
+        return h, fb, cb
 
     def count_unsolved(self) -> int:
         c = C.c_int64(0)

@@ -245,6 +245,139 @@ __global__ void __launch_bounds__(256) blfik_dynamics_kernel(const KinParams P, 
     }
 }
 
+// Velocity-dependent terms the TSID tasks read: the generalised bias forces h = C(q, nu) nu + g(q) of
+// M nu' + h = S'tau + sum J'f (kinDyn->generalizedBiasForces, BaseDynamicsTask.cpp:178, JointDynamicsTask.cpp:233), the bias
+// acceleration Jdot nu of frames (kinDyn->getFrameBiasAcc, TSID SE3Task.cpp:254, SO3Task.cpp:189, R3Task.cpp:219) and of the CoM
+// (getCenterOfMassBiasAcc, TSID CoMTask.cpp:195), all in the MIXED representation, where nu' = 0 means that the base origin and
+// the base angular velocity (both in world coordinates) stay constant.  One warp per robot.  Forward sweep by tree level
+// (link by lane): w_k = w_p + a_k sd_k, w'_k = w'_p + (w_p x a_k) sd_k, origin velocity and acceleration carried by the
+// parent; per link the force m (a_c + g z) and the moment I w' + w x I w about its CoM that this motion needs; column c of h is
+// the projection of those on the motion of variable c (all links for the base, the distal ones for a joint).
+__global__ void __launch_bounds__(256) blfik_bias_kernel(const KinParams P, const double* __restrict__ nu, double g_acc, double* __restrict__ bias,
+                                                         double* __restrict__ frame_bias, double* __restrict__ com_bias)
+{
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const WM w = carve(smem + (size_t)wib * P.L.total, P.L);
+    const DevModel& m = P.m;
+    const int n = m.n, nv = n + 6, nl = m.nl;
+    double *omW = w.A, *vO = w.A + 3 * nl, *dOm = w.A + 6 * nl, *aO = w.A + 9 * nl, *Fk = w.A + 12 * nl, *Nk = w.A + 15 * nl;
+    for (long long robot = (long long)blockIdx.x * wpb + wib; robot < P.N; robot += (long long)gridDim.x * wpb) {
+        k1_fk(m, w, P.base_pos + 3 * robot, P.base_quat + 4 * robot, P.s + (size_t)n * robot, lane);
+        const double* v = nu + (size_t)nv * robot;
+        if (lane < 3) omW[lane] = v[3 + lane], vO[lane] = v[lane], dOm[lane] = 0.0, aO[lane] = 0.0;
+        __syncwarp();
+        for (int d = 1; d <= m.maxdepth; d++) {
+            for (int k = lane; k < nl; k += 32) {
+                if (m.depth[k] != d) continue;
+                const int par = m.parent[k];
+                const double sd = v[6 + m.dof[k]];
+                const double a[3] = {w.axisW[3 * k], w.axisW[3 * k + 1], w.axisW[3 * k + 2]};
+                const double wp[3] = {omW[3 * par], omW[3 * par + 1], omW[3 * par + 2]};
+                const double dwp[3] = {dOm[3 * par], dOm[3 * par + 1], dOm[3 * par + 2]};
+                const double r[3] = {w.linkP[3 * k] - w.linkP[3 * par], w.linkP[3 * k + 1] - w.linkP[3 * par + 1], w.linkP[3 * k + 2] - w.linkP[3 * par + 2]};
+                double wxa[3], wxr[3], dwxr[3], wwr[3];
+                cross3(wp, a, wxa), cross3(wp, r, wxr), cross3(dwp, r, dwxr), cross3(wp, wxr, wwr);
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    omW[3 * k + c] = wp[c] + a[c] * sd;
+                    dOm[3 * k + c] = dwp[c] + wxa[c] * sd;
+                    vO[3 * k + c] = vO[3 * par + c] + wxr[c];
+                    aO[3 * k + c] = aO[3 * par + c] + dwxr[c] + wwr[c];
+                }
+            }
+            __syncwarp();
+        }
+        double macc[3] = {0.0, 0.0, 0.0};
+        for (int k = lane; k < nl; k += 32) {
+            const double mk = m.mass[k];
+            const double wk[3] = {omW[3 * k], omW[3 * k + 1], omW[3 * k + 2]}, dwk[3] = {dOm[3 * k], dOm[3 * k + 1], dOm[3 * k + 2]};
+            double f[3] = {0.0, 0.0, 0.0}, mo[3] = {0.0, 0.0, 0.0};
+            if (mk > 0.0) {
+                const double rc[3] = {w.mcw[3 * k] / mk - w.linkP[3 * k], w.mcw[3 * k + 1] / mk - w.linkP[3 * k + 1], w.mcw[3 * k + 2] / mk - w.linkP[3 * k + 2]};
+                double dwxr[3], wxr[3], wwr[3];
+                cross3(dwk, rc, dwxr), cross3(wk, rc, wxr), cross3(wk, wxr, wwr);
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    const double ac = aO[3 * k + c] + dwxr[c] + wwr[c];
+                    macc[c] += mk * ac;
+                    f[c] = mk * (ac + (c == 2 ? g_acc : 0.0));
+                }
+            }
+            if (m.inertia) {
+                const double* R = w.linkR + 9 * k;
+                const double* I6 = m.inertia + 6 * k;
+                auto apply = [&](const double* x, double* y) {   // I^W x = R I R' x
+                    double xl[3], il[3];
+                    mat3T_vec(R, x, xl);
+                    il[0] = I6[0] * xl[0] + I6[1] * xl[1] + I6[2] * xl[2];
+                    il[1] = I6[1] * xl[0] + I6[3] * xl[1] + I6[4] * xl[2];
+                    il[2] = I6[2] * xl[0] + I6[4] * xl[1] + I6[5] * xl[2];
+                    mat3_vec(R, il, y);
+                };
+                double Idw[3], Iw[3], wxIw[3];
+                apply(dwk, Idw), apply(wk, Iw);
+                cross3(wk, Iw, wxIw);
+#pragma unroll
+                for (int c = 0; c < 3; c++) mo[c] = Idw[c] + wxIw[c];
+            }
+#pragma unroll
+            for (int c = 0; c < 3; c++) Fk[3 * k + c] = f[c], Nk[3 * k + c] = mo[c];
+        }
+        if (com_bias) {
+#pragma unroll
+            for (int c = 0; c < 3; c++) macc[c] = warp_sum(macc[c]) * m.inv_total_mass;
+            if (lane < 3) com_bias[3 * robot + lane] = lane == 0 ? macc[0] : (lane == 1 ? macc[1] : macc[2]);
+        }
+        __syncwarp();
+        if (bias) {
+            for (int c = lane; c < nv; c += 32) {
+                double h = 0.0;
+                if (c < 3) {
+                    for (int k = 0; k < nl; k++) h += Fk[3 * k + c];
+                } else {
+                    const int j = c - 6;
+                    const int kj = c < 6 ? 0 : m.link_of_dof[j];
+                    double a[3] = {0.0, 0.0, 0.0};
+                    if (c < 6) a[c - 3] = 1.0;
+                    else a[0] = w.axisW[3 * kj], a[1] = w.axisW[3 * kj + 1], a[2] = w.axisW[3 * kj + 2];
+                    const double o[3] = {w.linkP[3 * kj], w.linkP[3 * kj + 1], w.linkP[3 * kj + 2]};
+                    double t[3] = {0.0, 0.0, 0.0};
+                    for (int k = 0; k < nl; k++) {
+                        if (c >= 6 && !((m.anc[k] >> j) & 1ull)) continue;
+                        const double mk = m.mass[k];
+                        if (mk > 0.0) {
+                            const double r[3] = {w.mcw[3 * k] / mk - o[0], w.mcw[3 * k + 1] / mk - o[1], w.mcw[3 * k + 2] / mk - o[2]};
+                            const double f[3] = {Fk[3 * k], Fk[3 * k + 1], Fk[3 * k + 2]};
+                            double rxf[3];
+                            cross3(r, f, rxf);
+                            t[0] += rxf[0], t[1] += rxf[1], t[2] += rxf[2];
+                        }
+                        t[0] += Nk[3 * k], t[1] += Nk[3 * k + 1], t[2] += Nk[3 * k + 2];
+                    }
+                    h = a[0] * t[0] + a[1] * t[1] + a[2] * t[2];
+                }
+                bias[(size_t)robot * nv + c] = h;
+            }
+        }
+        if (frame_bias) {
+            for (int f = lane; f < P.nframes; f += 32) {
+                const int fr = P.frames[f], L = m.frame_link[fr];
+                double off[3];
+                const double fp[3] = {m.Fp[3 * fr], m.Fp[3 * fr + 1], m.Fp[3 * fr + 2]};
+                mat3_vec(w.linkR + 9 * L, fp, off);
+                const double wk[3] = {omW[3 * L], omW[3 * L + 1], omW[3 * L + 2]}, dwk[3] = {dOm[3 * L], dOm[3 * L + 1], dOm[3 * L + 2]};
+                double dwxr[3], wxr[3], wwr[3];
+                cross3(dwk, off, dwxr), cross3(wk, off, wxr), cross3(wk, wxr, wwr);
+                double* out = frame_bias + ((size_t)robot * P.nframes + f) * 6;
+#pragma unroll
+                for (int c = 0; c < 3; c++) out[c] = aO[3 * L + c] + dwxr[c] + wwr[c], out[3 + c] = dwk[c];
+            }
+        }
+        __syncwarp();
+    }
+}
+
 // Coefficients of the quintic splines of one task (Math::QuinticSpline, QuinticSpline.h:266-415), one thread per robot and
 // coordinate.  The interior-knot system is block tridiagonal with 2 x 2 blocks that depend on the knot times only, so the
 // host eliminates the blocks once (fac[i] = L_i, M_i = L_i D'_{i-1}^-1, D'_i^-1, U_i) and a thread runs the two sweeps on
@@ -2458,6 +2591,55 @@ extern "C" int blfik_dynamics(blfik_problem* p, double* mass_matrix, double* gra
     if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
     for (void* t : tmp) cudaFree(t);
     if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_dynamics] %s", cudaGetErrorString(e));
+    return BLFIK_OK;
+}
+
+extern "C" int blfik_bias_forces(blfik_problem* p, const double* nu, double gravity_acceleration, double* bias_forces, const int32_t* frames,
+                                 int32_t nframes, double* frame_bias_acc, double* com_bias_acc, int32_t mem)
+{
+    CHECK_P(p, "blfik_bias_forces");
+    if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_bias_forces] the robot state has never been set");
+    if (!nu) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_bias_forces] null generalised velocity");
+    if (nframes < 0 || (nframes > 0 && !frames)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_bias_forces] invalid frame list");
+    if (!frame_bias_acc) nframes = 0;
+    if (!bias_forces && !com_bias_acc && nframes == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_bias_forces] nothing asked for");
+    for (int f = 0; f < nframes; f++)
+        if (frames[f] < 0 || frames[f] >= p->model->nf) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_bias_forces] frame index %d out of range", frames[f]);
+    const size_t N = (size_t)p->N, nv = p->nv;
+    const bool host = mem != BLFIK_MEM_DEVICE;
+    const size_t n_nu = N * nv, n_h = bias_forces ? N * nv : 0, n_f = (size_t)nframes * 6 * N, n_c = com_bias_acc ? 3 * N : 0;
+    double* stage = nullptr;
+    int* d_frames = nullptr;
+    auto cleanup = [&] { cudaFree(stage), cudaFree(d_frames); };
+    const double* d_nu = nu;
+    double *d_h = bias_forces, *d_f = frame_bias_acc, *d_c = com_bias_acc;
+    if (host) {
+        if (cudaMalloc((void**)&stage, (n_nu + n_h + n_f + n_c) * sizeof(double)) != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_bias_forces] cudaMalloc failed");
+        cudaMemcpyAsync(stage, nu, n_nu * sizeof(double), cudaMemcpyHostToDevice, p->stream);
+        d_nu = stage, d_h = bias_forces ? stage + n_nu : nullptr, d_f = nframes ? stage + n_nu + n_h : nullptr, d_c = com_bias_acc ? stage + n_nu + n_h + n_f : nullptr;
+    }
+    if (nframes) {
+        if (cudaMalloc((void**)&d_frames, nframes * sizeof(int)) != cudaSuccess) { cleanup(); return fail(BLFIK_ERR_CUDA, "[blfik_bias_forces] cudaMalloc failed"); }
+        cudaMemcpyAsync(d_frames, frames, nframes * sizeof(int), cudaMemcpyHostToDevice, p->stream);
+    }
+    KinParams K;
+    K.m = p->dm, K.N = p->N, K.base_pos = p->base_pos, K.base_quat = p->base_quat, K.s = p->s, K.frames = d_frames, K.nframes = nframes;
+    K.frame_pos = K.frame_rot = K.frame_jac = K.com = K.com_jac = nullptr;
+    K.L = p->L;
+    cudaError_t e = cudaFuncSetAttribute(blfik_bias_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes);
+    if (e == cudaSuccess) {
+        blfik_bias_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(K, d_nu, gravity_acceleration, d_h, d_f, d_c);
+        e = cudaGetLastError();
+        p->launches++;
+    }
+    if (e == cudaSuccess && host) {
+        if (bias_forces) e = cudaMemcpyAsync(bias_forces, d_h, n_h * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+        if (nframes && e == cudaSuccess) e = cudaMemcpyAsync(frame_bias_acc, d_f, n_f * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+        if (com_bias_acc && e == cudaSuccess) e = cudaMemcpyAsync(com_bias_acc, d_c, n_c * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);   // the staging buffers and the frame list die with this call
+    cleanup();
+    if (e != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_bias_forces] %s", cudaGetErrorString(e));
     return BLFIK_OK;
 }
 

@@ -97,3 +97,64 @@ def gravity_forces_fd(model, p, q, s, g=9.80665, eps=1e-6):
         _, cm = _links(model, *_perturbed(p, q, s, i, -eps))
         G[i] = g * float(model.mass @ (cp[:, 2] - cm[:, 2])) / (2 * eps)
     return G
+
+
+# ---- velocity-dependent terms: generalised bias forces and bias accelerations (kinDyn->generalizedBiasForces, getFrameBiasAcc,
+# getCenterOfMassBiasAcc; read by src/TSID/src/BaseDynamicsTask.cpp:178, JointDynamicsTask.cpp:233, SE3Task.cpp:254, CoMTask.cpp:195).
+# Restated as the projected Newton-Euler equations with NO recursion over velocities: per link, linear momentum m Jv nu and
+# angular momentum I^W Jw nu from Jacobians written down directly from the forward kinematics; their time derivative along the
+# motion with nu held constant by central finite differences of the state (MIXED: p + d v_B, Exp(d w_B) R, s + d sd);
+#     h = sum_k Jv_k' (d/dt (m_k v_ck) + m_k g z) + Jw_k' d/dt (I_k^W w_k).
+
+def _ancestors(model):
+    nl = model.n + 1
+    anc = [[] for _ in range(nl)]          # links on the path base -> k with a joint (k itself included, the base excluded)
+    for k in range(1, nl):
+        anc[k] = anc[int(model.parent[k])] + [k]
+    return anc
+
+
+def link_jacobians(model, p, q, s):
+    """Jv[k] (3 x nv, CoM of link k), Jw[k] (3 x nv), c[k], R[k]: MIXED representation, straight from the link poses"""
+    R, P = W.fk_batch(model, p[None], q[None], s[None])
+    R, P = R[0], P[0]
+    nl, nv = model.n + 1, model.n + 6
+    c = P + np.einsum("kij,kj->ki", R, model.com)
+    Jv, Jw = np.zeros((nl, 3, nv)), np.zeros((nl, 3, nv))
+    anc = _ancestors(model)
+    for k in range(nl):
+        Jv[k, :, :3] = np.eye(3)
+        Jw[k, :, 3:6] = np.eye(3)
+        r = c[k] - P[0]
+        Jv[k, :, 3:6] = -np.array([[0, -r[2], r[1]], [r[2], 0, -r[0]], [-r[1], r[0], 0]])
+        for a in anc[k]:
+            j = int(model.dof[a])
+            ax = R[a] @ model.axis[a]
+            Jw[k, :, 6 + j] = ax
+            Jv[k, :, 6 + j] = np.cross(ax, c[k] - P[a])
+    return Jv, Jw, c, R
+
+
+def moved(p, q, s, nu, d):
+    """the state after moving for a time d with the generalised velocity nu held constant (MIXED)"""
+    return p + d * nu[:3], _quat_mul(_exp_quat(d * nu[3:6]), q), s + d * nu[6:]
+
+
+def bias_forces_fd(model, p, q, s, nu, g=9.80665, d=1e-5):
+    def momenta(state):
+        Jv, Jw, _, R = link_jacobians(model, *state)
+        IW = np.einsum("kij,kjl,kml->kim", R, model.inertia, R)
+        return model.mass[:, None] * np.einsum("kci,i->kc", Jv, nu), np.einsum("kcd,kd->kc", IW, np.einsum("kci,i->kc", Jw, nu))
+    Pp, Lp = momenta(moved(p, q, s, nu, d))
+    Pm, Lm = momenta(moved(p, q, s, nu, -d))
+    dP, dL = (Pp - Pm) / (2 * d), (Lp - Lm) / (2 * d)
+    Jv, Jw, _, _ = link_jacobians(model, p, q, s)
+    dP[:, 2] += model.mass * g
+    return np.einsum("kci,kc->i", Jv, dP) + np.einsum("kci,kc->i", Jw, dL)
+
+
+def com_bias_acc_fd(model, p, q, s, nu, d=1e-5):
+    def vcom(state):
+        Jv, _, _, _ = link_jacobians(model, *state)
+        return np.einsum("k,kci,i->c", model.mass, Jv, nu) / model.mass.sum()
+    return (vcom(moved(p, q, s, nu, d)) - vcom(moved(p, q, s, nu, -d))) / (2 * d)
