@@ -622,7 +622,7 @@ struct blfik_problem {
     FastLayout F;
     size_t fast_smem = 0;
     int fast_grid = 0, fast_wpb = 12;
-    int max_as_iters = 6, max_polish_iters = 40, max_total_iters = 200;
+    int max_as_iters = 12, max_polish_iters = 40, max_total_iters = 200;
     double* d_model_pack = nullptr;
     int njump = 0, has_com = 0;
     // two-launch path (blfik_split.cuh): assemble (one thread per robot) -> QP records -> solve (one warp per robot)
@@ -1811,6 +1811,7 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         { const char* e = getenv("BLFIK_PDAS_FIRST"); S.pdas_first = e ? atoi(e) : 1; }
         { const char* e = getenv("BLFIK_MAX_ITERS"); if (e) S.max_total_iters = atoi(e); }
         { const char* e = getenv("BLFIK_MAX_AS"); if (e) S.max_as_iters = atoi(e); }
+        { const char* e = getenv("BLFIK_ADMM_STATUS"); S.admm_status = e ? atoi(e) : 0; }
         const long long swant = (count + p->solve_wpb - 1) / p->solve_wpb, scap = (long long)p->num_sms * p->solve_blocks;
         const int agrid = (int)((count + p->asm_threads - 1) / p->asm_threads), sgrid = (int)(swant < scap ? swant : scap);
         for (int tick = 0; tick < nticks; tick++) {

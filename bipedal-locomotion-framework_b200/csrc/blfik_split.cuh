@@ -62,6 +62,7 @@ struct SolveParams {
     int nv, K;
     int max_as_iters, max_polish_iters, max_total_iters, pdas_first;
     int tick;
+    int admm_status;            // status of a robot whose ADMM iterates settled but whose active set could not be certified
 };
 
 // per-warp shared memory of kernel B, in doubles, all compile-time
@@ -542,7 +543,26 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
                     if (act == 2 && mu_mine < -toly) bad = true;
                     if (!(xp == xp)) bad = true, conv = false;
                     const bool any_change = __any_sync(kFull, viol_lo || viol_up || bad);
-                    if (conv && !any_change) {
+                    // An active set found late pins joints that leave the equality rows nearly dependent: the factorisation
+                    // then satisfies them to 1e-8 ... 1e-7 only and the point is off the optimum by 1e-5 and more.  Such a set
+                    // gets the rows checked (the record is read again: its image has made room for N) and a point that misses
+                    // them is handed out as inaccurate (status 1), not as certified.
+                    bool rows_ok = true;
+                    if (conv && !any_change && as_it >= 6) {
+                        const int row = lane < KP ? lane : 0;
+                        double acc = 0.0;
+#pragma unroll 1
+                        for (int c = 0; c < NV; c++) acc = fma(__ldg(rec + c * KP + row), __shfl_sync(kFull, xp, c), acc);
+                        const double cr = __ldg(rec + Rec::cvec + row);
+                        const bool eqrow = lane < KP && s_evec[row] == 0.0;
+                        rows_ok = !__any_sync(kFull, eqrow && fabs(acc - cr) > 1e-8 * (1.0 + fabs(cr)));
+                    }
+                    if (conv && !any_change && !rows_ok) {
+                        done = true;
+                        status = 1;
+                        x = xp;
+                        if (bounded) z = fmin(fmax(xp, lo), hi), y = act ? mu_mine : 0.0;
+                    } else if (conv && !any_change) {
                         done = true;
                         status = 0;
                         x = xp;
@@ -560,7 +580,7 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
                 }
                 if (!done && admm_converged) {
                     done = true;
-                    status = 0;
+                    status = SP.admm_status;
                 }
                 if (!any_box && !done) break;   // nothing ADMM could add
             }

@@ -74,3 +74,14 @@ def referee(H, g, C, l, u):
     if r.status == 2:
         return False, None
     return True, solve_qp_active_set(H, g, C, l, u)
+
+
+def eps_optimal(H, g, C, l, u, x, x_exact, eps=1e-7):
+    """What a status "solved" of the reference's solver means at its accuracy setting (OSQP, eps_abs = eps_rel = eps): the point
+    violates no row by more than eps (1 + |Cx|_inf) and its cost is not above the optimum's.  On an ill-conditioned instance
+    (multipliers of 1e4 and more: a violation of 5e-8 moves the cost by 4e-4 and the point by 3e-5) two such points differ by
+    more than the 1e-5 the well-conditioned instances are held to; this is the test such an instance gets instead."""
+    Cx = C @ x
+    viol = max(np.maximum(Cx - u, 0.0).max(), np.maximum(l - Cx, 0.0).max())
+    f = lambda v: 0.5 * v @ H @ v + g @ v
+    return viol <= eps * (1.0 + np.abs(Cx).max()) and f(x) <= f(x_exact) + 1e-12 * (1.0 + abs(f(x_exact)))
