@@ -29,7 +29,10 @@ __global__ void __launch_bounds__(128, 4) blfik_assemble_kernel(const AsmParams 
     const TickParams& P = A.T;
     const DevModel& m = P.m;
     const int n = m.n, nv = n + 6, tid = threadIdx.x, nthr = blockDim.x;
-    if (blockIdx.x == 0 && tid == 0) *A.work_counter = 0;   // the solve kernel of this tick hands its robots out from zero
+    if (blockIdx.x == 0 && tid == 0) {
+        *A.work_counter = 0;   // the solve kernel of this tick hands its robots out from zero
+        if (A.slow_out_n) *A.slow_out_n = 0;
+    }
     // block-shared constants: the packed model, the task descriptors, the walk, the row maps
     for (int e = tid; e < A.pack_len; e += nthr) smem[e] = A.model_pack[e];
     const int tlen = P.ntasks * (int)(sizeof(DevTask) / sizeof(double));

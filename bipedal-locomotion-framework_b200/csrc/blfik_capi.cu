@@ -595,6 +595,11 @@ struct blfik_problem {
     double *base_pos = nullptr, *base_quat = nullptr, *s = nullptr, *nu = nullptr, *wx = nullptr, *wz = nullptr, *wy = nullptr;
     int *status = nullptr, *iters = nullptr;
     int* work_counter = nullptr;   // dynamic hand-out of robots in the register-resident kernel
+    // two-launch path, longest first (SolveParams::slow_*): two lists and two stamp arrays used alternately, their lengths, the
+    // stamp of the next solve launch and the stamp for which the list written last is valid (-1: none)
+    int* d_slow = nullptr;         // [2][N] lists, [2][N] stamps, [2] lengths, [N] consecutive unsolved ticks
+    int solve_stamp = 0;
+    int slow_list_for = -1;
     bool streaming_launch = false; // set around the one launch of the streaming-input mode
     bool streaming_off = false;    // the mode timed out once (serialised execution): chunk launches from then on
     int* d_arrived = nullptr;      // streaming-input mode of blfik_tick_packed: robots whose record is on the device; [1] = abort word
@@ -1324,6 +1329,9 @@ extern "C" int blfik_set_state(blfik_problem* p, const double* bp, const double*
     CU(cudaMemcpyAsync(p->base_quat, bq, N * 4 * sizeof(double), kind_in(mem), p->stream));
     CU(cudaMemcpyAsync(p->s, s, N * p->n * sizeof(double), kind_in(mem), p->stream));
     p->state_set = true;
+    // a state given from outside starts a new history: what the last ticks learnt about slow and unsolved robots is dropped
+    p->slow_list_for = -1;
+    if (p->d_slow) CU(cudaMemsetAsync(p->d_slow + 4 * N + 2, 0, N * sizeof(int), p->stream));
     return BLFIK_OK;
 }
 
@@ -1814,9 +1822,30 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
         { const char* e = getenv("BLFIK_ADMM_STATUS"); S.admm_status = e ? atoi(e) : 0; }
         const long long swant = (count + p->solve_wpb - 1) / p->solve_wpb, scap = (long long)p->num_sms * p->solve_blocks;
         const int agrid = (int)((count + p->asm_threads - 1) / p->asm_threads), sgrid = (int)(swant < scap ? swant : scap);
+        static const int lpt_env = [] { const char* e = getenv("BLFIK_LPT"); return e ? atoi(e) : 1; }();
+        const bool lpt = lpt_env && first == 0 && count == p->N && !asm_stream && p->N < 0x7fffff00LL;   // whole-batch launches only
+        if (lpt && !p->d_slow) {
+            const int rc = dev_alloc(p, (size_t)5 * p->N + 2, &p->d_slow);   // zero-filled: no stamp matches
+            if (rc) return rc;
+        }
+        S.slow_threshold = 16;
+        static const int short_env = [] { const char* e = getenv("BLFIK_SHORT_BUDGET"); return e ? atoi(e) : 48; }();
+        S.unsolved_run = lpt ? p->d_slow + 4 * p->N + 2 : nullptr, S.short_budget = short_env;
         for (int tick = 0; tick < nticks; tick++) {
             A.tick = S.tick = tick;
             A.tnow = p->time + tick * dt;
+            {
+                const int T = ++p->solve_stamp, par = T & 1;
+                int *lists = p->d_slow, *stamps = p->d_slow + 2 * p->N, *lens = p->d_slow + 4 * p->N;
+                const bool in_valid = lpt && p->slow_list_for == T;
+                S.stamp = T;
+                S.slow_in = in_valid ? lists + (size_t)par * p->N : nullptr, S.slow_in_n = in_valid ? lens + par : nullptr;
+                S.slow_stamp_in = in_valid ? stamps + (size_t)par * p->N : nullptr;
+                S.slow_out = lpt ? lists + (size_t)(par ^ 1) * p->N : nullptr, S.slow_out_n = lpt ? lens + (par ^ 1) : nullptr;
+                S.slow_stamp_out = lpt ? stamps + (size_t)(par ^ 1) * p->N : nullptr;
+                A.slow_out_n = S.slow_out_n;
+                p->slow_list_for = lpt ? T + 1 : -1;
+            }
             if (step_weight_schedules(p, dt)) {   // MultiStateWeightProvider::advance() of every period, then the solver reads the weight
                 fill_weights();
                 p->tasks_dirty = true;            // the device copies of the weights follow at the next refresh

@@ -45,6 +45,7 @@ struct AsmParams {
     int tick;                   // index of this tick inside a multi-tick launch (0: first)
     double tnow;
     int* work_counter;          // kernel B's hand-out counter: zeroed here, one launch ahead
+    int* slow_out_n;            // length of the slow-robot list the solve kernel of this tick writes (SolveParams): zeroed here; may be null
     int jw_task;                // a JointTrackingTask whose weight comes with the launch (weight schedule), -1: none
     double jw[32];
 };
@@ -63,6 +64,23 @@ struct SolveParams {
     int max_as_iters, max_polish_iters, max_total_iters, pdas_first;
     int tick;
     int admm_status;            // status of a robot whose ADMM iterates settled but whose active set could not be certified
+    // Longest first: the robots that needed many iterations in the previous tick of the same batch (a closed loop: they are
+    // mostly the same ones, e.g. those whose targets are out of reach) are handed out before the others, so that they run
+    // beside the bulk instead of after it.  slow_in / slow_in_n: the list written by the previous tick; slow_out / slow_out_n:
+    // the list this tick writes; slow_stamp_in[r] == stamp marks a robot of slow_in (the linear hand-out skips it);
+    // slow_stamp_out[r] = stamp + 1 marks one of slow_out.  All null / zero when the launch does not cover the whole batch.
+    const int* slow_in;
+    const int* slow_in_n;
+    int* slow_out;
+    int* slow_out_n;
+    const int* slow_stamp_in;
+    int* slow_stamp_out;
+    int stamp, slow_threshold;
+    // Consecutive ticks a robot has ended without a solution inside the iteration budget (closed loops: mostly robots whose
+    // constraints have no feasible point, tick after tick).  Such a robot gets a short budget, and the full one again every
+    // sixteenth tick; a tick that solves it clears the count.  Null: every robot gets the full budget.
+    int* unsolved_run;
+    int short_budget;
 };
 
 // per-warp shared memory of kernel B, in doubles, all compile-time
@@ -340,12 +358,29 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
     double* base = smem + (size_t)wib * SL::TOTAL;
     // Persistent warps: each takes its next robot from a device counter (zeroed by the assemble kernel of the same tick), so
     // a slot is never idle between two robots (with one block per robot 13.6 of 16 warps were resident on average).
+  const int n_slow = SP.slow_in_n ? *SP.slow_in_n : 0;
   for (;;) {
     long long robot = 0;
-    if (lane == 0) robot = P.first + atomicAdd(SP.work_counter, 1);
+    if (lane == 0) {
+        const int wi = atomicAdd(SP.work_counter, 1);
+        if (wi < n_slow) {
+            robot = SP.slow_in[wi];
+            if (SP.slow_stamp_in[robot] != SP.stamp) robot = -1;   // a stale entry: the linear hand-out takes this robot
+        } else {
+            robot = P.first + (wi - n_slow);
+            if (robot < P.N && n_slow > 0 && SP.slow_stamp_in[robot] == SP.stamp) robot = -1;   // handed out from the list
+        }
+    }
     robot = __shfl_sync(kFull, robot, 0);
+    if (robot < 0) continue;
     if (robot >= P.N) break;
     int worst = 0, iters_prev = 0;
+    int budget = SP.max_total_iters;
+    int run = 0;
+    if (SP.unsolved_run) {
+        run = SP.unsolved_run[robot];
+        if (run > 0 && (run & 15) != 0 && SP.short_budget < budget) budget = SP.short_budget;
+    }
     if (SP.tick > 0) {
         worst = P.status[robot], iters_prev = P.iters[robot];
         if (worst == 2) continue;   // a failed tick ended this robot's rollout: nu stays zero, the state where the failure happened
@@ -439,7 +474,7 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
             double mu_mine = 0.0;
             int act = 0;   // 0 free, 1 lower, 2 upper, 3 pinned
             const int max_rounds = with_rho ? st.max_rounds : 1;
-            for (int round = 0; round < max_rounds && !done && iters < SP.max_total_iters; round++) {
+            for (int round = 0; round < max_rounds && !done && iters < budget; round++) {
                 // ---- ADMM (skipped when there is no box row: the problem is a pure equality QP)
                 double rp = 0.0, rd = 0.0;
                 if (any_box && with_rho) {
@@ -477,7 +512,7 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
                     else if (hi - z < y) act = 2;
                 }
                 xp = x;
-                for (int as_it = 0; as_it < SP.max_as_iters && !done && iters < SP.max_total_iters; as_it++) {
+                for (int as_it = 0; as_it < SP.max_as_iters && !done && iters < budget; as_it++) {
                     const unsigned amask = __ballot_sync(kFull, act != 0);
                     const int a = __popc(amask);
                     const int rank = __popc(amask & ((1u << lane) - 1u));
@@ -605,6 +640,11 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
         P.status[robot] = worst;
         if (P.status_host) P.status_host[robot] = worst;
         P.iters[robot] = iters_prev + iters;
+        if (SP.unsolved_run) SP.unsolved_run[robot] = status == 1 ? (run < (1 << 30) ? run + 1 : run) : 0;
+        if (SP.slow_out && iters > SP.slow_threshold) {
+            SP.slow_out[atomicAdd(SP.slow_out_n, 1)] = (int)robot;
+            SP.slow_stamp_out[robot] = SP.stamp + 1;
+        }
     }
     __syncwarp();
   }

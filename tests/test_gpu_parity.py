@@ -1109,6 +1109,56 @@ def test_c5_baseline_shape_vs_oracle():
     prob.close()
 
 
+def test_slow_first_handout_and_short_budget_leave_solved_robots_alone():
+    """Closed loops on the two-launch path hand out first the robots that were slow at the previous tick, and give a robot
+    that has been ending without a solution a short iteration budget (the full one every sixteenth tick).  Neither may touch a
+    robot that solves every tick: its trajectory must be bit-identical with both switched off (BLFIK_LPT=0, read once per
+    process, hence the subprocesses).  The batch holds robots whose foot targets are out of reach, so both mechanisms have
+    work.  Then: a state set from outside drops the history (the run equals that of a fresh problem)."""
+    import subprocess
+    import sys
+    code = r'''
+import sys; sys.path.insert(0, %r)
+import numpy as np
+import blf_b200
+from blf_b200 import capi, workloads as W
+w = W.config(5); N = 4096
+inp = W.synth_inputs(w, N, 5)
+rng = np.random.default_rng(77)
+far = rng.choice(N, 40, replace=False)
+inp.setpoints[1][far, :3] += rng.uniform(0.4, 0.8, (40, 3))          # left foot target out of reach
+prob = capi.Problem(capi.Model(w.model), w.tasks, N)
+prob.set_inputs(inp)
+prob.tick(40, w.dt, integrate=True, warm_start=True)
+st, it = prob.get_status()
+p, q, s = prob.get_state()
+np.savez(sys.argv[1], st=st, it=it, nu=prob.get_output(), p=p, q=q, s=s)
+# history dropped by set_state: the second run equals the first
+prob.set_inputs(inp)
+prob.tick(40, w.dt, integrate=True, warm_start=False)
+a = (prob.get_status()[0].copy(), prob.get_output().copy())
+fresh = capi.Problem(capi.Model(w.model), w.tasks, N)
+fresh.set_inputs(inp)
+fresh.tick(40, w.dt, integrate=True, warm_start=False)
+b = (fresh.get_status()[0], fresh.get_output())
+print("HISTORY", bool(np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])))
+''' % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    import tempfile
+    out = {}
+    with tempfile.TemporaryDirectory() as d:
+        for lpt in ("1", "0"):
+            f = os.path.join(d, f"r{lpt}.npz")
+            r = subprocess.run([sys.executable, "-c", code, f], capture_output=True, text=True, timeout=600, env=dict(os.environ, BLFIK_LPT=lpt))
+            assert r.returncode == 0 and "HISTORY True" in r.stdout, r.stdout + r.stderr
+            out[lpt] = dict(np.load(f))
+    on, off = out["1"], out["0"]
+    always = (on["st"] == 0) & (off["st"] == 0)          # sticky status of the launch: solved at every one of the 40 ticks
+    assert always.mean() > 0.95 and (on["st"] != 0).sum() >= 20
+    for k in ("nu", "p", "q", "s"):
+        assert np.array_equal(on[k][always], off[k][always]), k
+    assert on["it"][on["st"] != 0].mean() < 0.75 * off["it"][off["st"] != 0].mean()     # the short budget is at work
+
+
 def _min_jerk_setpoint(ty, sp0, tg, tau, T_):
     """host restatement of the on-device generator (SO3Planner.tpp:96-105, 205-252 with zero boundary conditions)"""
     tau = np.clip(tau, 0.0, 1.0)
