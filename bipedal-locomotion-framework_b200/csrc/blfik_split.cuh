@@ -325,6 +325,18 @@ __device__ __forceinline__ bool solve_setup(double* base, const double* evec, in
     return __all_sync(kFull, ok);
 }
 
+// Do the equality rows of the record hold at x (one variable per lane)?  Rare (active sets certified late), hence out of line:
+// the solve kernel's instruction footprint is what its warps, each at a different place, share the instruction cache for.
+static __device__ __noinline__ bool solve_rows_hold(const double* rec, int cvec_off, int nv, int kp, const double* evec, double x, int lane)
+{
+    const int row = lane < kp ? lane : 0;
+    double acc = 0.0;
+    for (int c = 0; c < nv; c++) acc = fma(__ldg(rec + c * kp + row), __shfl_sync(kFull, x, c), acc);
+    const double cr = __ldg(rec + cvec_off + row);
+    const bool eqrow = lane < kp && evec[row] == 0.0;
+    return !__any_sync(kFull, eqrow && fabs(acc - cr) > 1e-8 * (1.0 + fabs(cr)));
+}
+
 template <int NV, int KP>
 struct SolveDims {
     // Warps (robots) per block and resident blocks per SM.  The small instantiations: 16 warps at 128 registers, 12.5 KB of
@@ -583,15 +595,7 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
                     // gets the rows checked (the record is read again: its image has made room for N) and a point that misses
                     // them is handed out as inaccurate (status 1), not as certified.
                     bool rows_ok = true;
-                    if (conv && !any_change && as_it >= 6) {
-                        const int row = lane < KP ? lane : 0;
-                        double acc = 0.0;
-#pragma unroll 1
-                        for (int c = 0; c < NV; c++) acc = fma(__ldg(rec + c * KP + row), __shfl_sync(kFull, xp, c), acc);
-                        const double cr = __ldg(rec + Rec::cvec + row);
-                        const bool eqrow = lane < KP && s_evec[row] == 0.0;
-                        rows_ok = !__any_sync(kFull, eqrow && fabs(acc - cr) > 1e-8 * (1.0 + fabs(cr)));
-                    }
+                    if (conv && !any_change && as_it >= 6) rows_ok = solve_rows_hold(rec, Rec::cvec, NV, KP, s_evec, xp, lane);
                     if (conv && !any_change && !rows_ok) {
                         done = true;
                         status = 1;
