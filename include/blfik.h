@@ -276,7 +276,12 @@ int blfik_set_limits(blfik_problem* problem, int32_t task, const double* upper_l
  * (the reference's advance() returns false there, QPInverseKinematics.cpp:511-523, and its caller stops
  * integrating) ends that robot's rollout: its nu is zero, its state stays where the failure happened and the
  * remaining ticks of the launch leave it alone.  MAX_ITER ("solved inaccurate") is accepted like the reference
- * accepts it: the tick's velocity is reported and integrated.                                              */
+ * accepts it: the tick's velocity is reported and integrated.
+ * Closed loops (two-launch kernel path, launches over the whole batch): like the warm start, two pieces of history
+ * travel from tick to tick, inside a launch and across launches -- the robots that needed many iterations at the
+ * previous tick are handed out first, and a robot that has been ending with MAX_ITER gets a quarter of the iteration
+ * budget (the full one every sixteenth such tick; the first solved tick clears it).  Neither changes a robot that
+ * solves every tick; blfik_set_state starts a new history.                                                  */
 int blfik_tick(blfik_problem* problem, int32_t nticks, double dt, uint32_t flags);
 
 /* The whole reference-facing tick for callers whose data live in HOST memory (what the reference's caller does
