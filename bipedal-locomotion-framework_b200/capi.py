@@ -485,9 +485,11 @@ class Problem:
             raise ValueError(f"nu must be [N, nv] = {(self.N, self.nv)}, got {v.shape}")
         fr = np.ascontiguousarray(frames, dtype=np.int32)
         h, fb, cb = np.empty((self.N, self.nv)), np.empty((self.N, len(fr), 6)), np.empty((self.N, 3))
-        self.L.blfik_bias_forces.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32]
+        fv = np.empty((self.N, len(fr), 6))
+        self.L.blfik_bias_forces.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
         _check(self.L.blfik_bias_forces(self.handle, v.ctypes.data, float(gravity), h.ctypes.data, fr.ctypes.data if len(fr) else None, len(fr),
-                                        fb.ctypes.data if len(fr) else None, cb.ctypes.data, MEM_HOST))
+                                        fb.ctypes.data if len(fr) else None, fv.ctypes.data if len(fr) else None, cb.ctypes.data, MEM_HOST))
+        self.last_frame_velocities = fv   # J nu of ``frames``, [N, nframes, 6]
         return h, fb, cb
 
     def count_unsolved(self) -> int:

@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(256) blfik_dynamics_kernel(const KinParams P, 
 // parent; per link the force m (a_c + g z) and the moment I w' + w x I w about its CoM that this motion needs; column c of h is
 // the projection of those on the motion of variable c (all links for the base, the distal ones for a joint).
 __global__ void __launch_bounds__(256) blfik_bias_kernel(const KinParams P, const double* __restrict__ nu, double g_acc, double* __restrict__ bias,
-                                                         double* __restrict__ frame_bias, double* __restrict__ com_bias)
+                                                         double* __restrict__ frame_bias, double* __restrict__ frame_vel, double* __restrict__ com_bias)
 {
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(256) blfik_bias_kernel(const KinParams P, cons
                 bias[(size_t)robot * nv + c] = h;
             }
         }
-        if (frame_bias) {
+        if (frame_bias || frame_vel) {
             for (int f = lane; f < P.nframes; f += 32) {
                 const int fr = P.frames[f], L = m.frame_link[fr];
                 double off[3];
@@ -369,9 +369,16 @@ __global__ void __launch_bounds__(256) blfik_bias_kernel(const KinParams P, cons
                 const double wk[3] = {omW[3 * L], omW[3 * L + 1], omW[3 * L + 2]}, dwk[3] = {dOm[3 * L], dOm[3 * L + 1], dOm[3 * L + 2]};
                 double dwxr[3], wxr[3], wwr[3];
                 cross3(dwk, off, dwxr), cross3(wk, off, wxr), cross3(wk, wxr, wwr);
-                double* out = frame_bias + ((size_t)robot * P.nframes + f) * 6;
+                if (frame_bias) {
+                    double* out = frame_bias + ((size_t)robot * P.nframes + f) * 6;
 #pragma unroll
-                for (int c = 0; c < 3; c++) out[c] = aO[3 * L + c] + dwxr[c] + wwr[c], out[3 + c] = dwk[c];
+                    for (int c = 0; c < 3; c++) out[c] = aO[3 * L + c] + dwxr[c] + wwr[c], out[3 + c] = dwk[c];
+                }
+                if (frame_vel) {   // J nu: velocity of the frame origin and angular velocity of its link
+                    double* out = frame_vel + ((size_t)robot * P.nframes + f) * 6;
+#pragma unroll
+                    for (int c = 0; c < 3; c++) out[c] = vO[3 * L + c] + wxr[c], out[3 + c] = wk[c];
+                }
             }
         }
         __syncwarp();
@@ -2625,28 +2632,30 @@ extern "C" int blfik_dynamics(blfik_problem* p, double* mass_matrix, double* gra
 }
 
 extern "C" int blfik_bias_forces(blfik_problem* p, const double* nu, double gravity_acceleration, double* bias_forces, const int32_t* frames,
-                                 int32_t nframes, double* frame_bias_acc, double* com_bias_acc, int32_t mem)
+                                 int32_t nframes, double* frame_bias_acc, double* frame_vel, double* com_bias_acc, int32_t mem)
 {
     CHECK_P(p, "blfik_bias_forces");
     if (!p->state_set) return fail(BLFIK_ERR_NOT_READY, "[blfik_bias_forces] the robot state has never been set");
     if (!nu) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_bias_forces] null generalised velocity");
     if (nframes < 0 || (nframes > 0 && !frames)) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_bias_forces] invalid frame list");
-    if (!frame_bias_acc) nframes = 0;
+    if (!frame_bias_acc && !frame_vel) nframes = 0;
     if (!bias_forces && !com_bias_acc && nframes == 0) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_bias_forces] nothing asked for");
     for (int f = 0; f < nframes; f++)
         if (frames[f] < 0 || frames[f] >= p->model->nf) return fail(BLFIK_ERR_INVALID_ARGUMENT, "[blfik_bias_forces] frame index %d out of range", frames[f]);
     const size_t N = (size_t)p->N, nv = p->nv;
     const bool host = mem != BLFIK_MEM_DEVICE;
-    const size_t n_nu = N * nv, n_h = bias_forces ? N * nv : 0, n_f = (size_t)nframes * 6 * N, n_c = com_bias_acc ? 3 * N : 0;
+    const size_t n_nu = N * nv, n_h = bias_forces ? N * nv : 0, n_f = frame_bias_acc ? (size_t)nframes * 6 * N : 0, n_v = frame_vel ? (size_t)nframes * 6 * N : 0,
+                 n_c = com_bias_acc ? 3 * N : 0;
     double* stage = nullptr;
     int* d_frames = nullptr;
     auto cleanup = [&] { cudaFree(stage), cudaFree(d_frames); };
     const double* d_nu = nu;
-    double *d_h = bias_forces, *d_f = frame_bias_acc, *d_c = com_bias_acc;
+    double *d_h = bias_forces, *d_f = frame_bias_acc, *d_v = frame_vel, *d_c = com_bias_acc;
     if (host) {
-        if (cudaMalloc((void**)&stage, (n_nu + n_h + n_f + n_c) * sizeof(double)) != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_bias_forces] cudaMalloc failed");
+        if (cudaMalloc((void**)&stage, (n_nu + n_h + n_f + n_v + n_c) * sizeof(double)) != cudaSuccess) return fail(BLFIK_ERR_CUDA, "[blfik_bias_forces] cudaMalloc failed");
         cudaMemcpyAsync(stage, nu, n_nu * sizeof(double), cudaMemcpyHostToDevice, p->stream);
-        d_nu = stage, d_h = bias_forces ? stage + n_nu : nullptr, d_f = nframes ? stage + n_nu + n_h : nullptr, d_c = com_bias_acc ? stage + n_nu + n_h + n_f : nullptr;
+        d_nu = stage, d_h = n_h ? stage + n_nu : nullptr, d_f = n_f ? stage + n_nu + n_h : nullptr, d_v = n_v ? stage + n_nu + n_h + n_f : nullptr;
+        d_c = n_c ? stage + n_nu + n_h + n_f + n_v : nullptr;
     }
     if (nframes) {
         if (cudaMalloc((void**)&d_frames, nframes * sizeof(int)) != cudaSuccess) { cleanup(); return fail(BLFIK_ERR_CUDA, "[blfik_bias_forces] cudaMalloc failed"); }
@@ -2658,13 +2667,14 @@ extern "C" int blfik_bias_forces(blfik_problem* p, const double* nu, double grav
     K.L = p->L;
     cudaError_t e = cudaFuncSetAttribute(blfik_bias_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes);
     if (e == cudaSuccess) {
-        blfik_bias_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(K, d_nu, gravity_acceleration, d_h, d_f, d_c);
+        blfik_bias_kernel<<<p->grid, p->warps_per_block * 32, p->smem_bytes, p->stream>>>(K, d_nu, gravity_acceleration, d_h, d_f, d_v, d_c);
         e = cudaGetLastError();
         p->launches++;
     }
     if (e == cudaSuccess && host) {
         if (bias_forces) e = cudaMemcpyAsync(bias_forces, d_h, n_h * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
-        if (nframes && e == cudaSuccess) e = cudaMemcpyAsync(frame_bias_acc, d_f, n_f * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+        if (n_f && e == cudaSuccess) e = cudaMemcpyAsync(frame_bias_acc, d_f, n_f * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+        if (n_v && e == cudaSuccess) e = cudaMemcpyAsync(frame_vel, d_v, n_v * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
         if (com_bias_acc && e == cudaSuccess) e = cudaMemcpyAsync(com_bias_acc, d_c, n_c * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);   // the staging buffers and the frame list die with this call

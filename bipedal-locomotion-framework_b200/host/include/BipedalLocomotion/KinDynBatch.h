@@ -54,6 +54,25 @@ public:
     bool getCenterOfMassPosition(Vector3d& com, std::size_t instance = 0);
     bool getCenterOfMassJacobian(System::MatrixXd& jacobian, std::size_t instance = 0);
 
+    // ---- dynamic quantities the TSID tasks read (iDynTree::KinDynComputations names), MIXED representation,
+    // evaluated for the whole batch on the GPU (blfik_dynamics, blfik_bias_forces) and cached per state / velocity
+    /** kinDyn->setRobotState(world_H_base, s, base_velocity, s_dot, world_gravity): the velocity part; baseVelocity = linear and
+     *  angular velocity of the base in world coordinates.  The gravity vector is (0, 0, -gravityAcceleration). */
+    bool setRobotVelocity(const std::array<double, 6>& baseVelocity, const VectorXd& jointVelocities, std::size_t instance = 0);
+    /** [N][6 + n] robot-major */
+    bool setRobotVelocityBatch(const double* nu);
+    void setGravityAcceleration(double g) { m_gravity = g, m_dynVersion = 0, m_biasVersion = 0; }
+    bool getFreeFloatingMassMatrix(System::MatrixXd& massMatrix, std::size_t instance = 0);
+    bool generalizedGravityForces(VectorXd& forces, std::size_t instance = 0);
+    /** C(q, nu) nu + g(q): the h of M nu' + h = S'tau + sum J'f (BaseDynamicsTask.cpp:178, JointDynamicsTask.cpp:233) */
+    bool generalizedBiasForces(VectorXd& forces, std::size_t instance = 0);
+    /** Jdot nu of a frame, linear then angular (TSID SE3Task.cpp:254, SO3Task.cpp:189, R3Task.cpp:219) */
+    bool getFrameBiasAcc(int frame, std::array<double, 6>& biasAcc, std::size_t instance = 0);
+    /** J nu of a frame, linear then angular (TSID SE3Task.cpp:256-263) */
+    bool getFrameVel(int frame, std::array<double, 6>& velocity, std::size_t instance = 0);
+    /** Jdot_com nu (TSID CoMTask.cpp:195) */
+    bool getCenterOfMassBiasAcc(Vector3d& biasAcc, std::size_t instance = 0);
+
     // ---- used by the solver
     const blfik_model* model() const { return m_model; }
     const std::vector<double>& basePositions() const { return m_p; }
@@ -68,6 +87,8 @@ private:
     bool ensureKinProblem();
     bool evalFrame(int frame);
     bool evalCom();
+    bool evalDynamics();
+    bool evalBias(int frame);
 
     double* m_recBase{nullptr};
     std::size_t m_recStride{0};
@@ -85,6 +106,11 @@ private:
     int m_cachedFrame{-1};
     unsigned long m_frameVersion{0}, m_comVersion{0};
     std::vector<double> m_framePos, m_frameRot, m_frameJac, m_com, m_comJac;
+    // dynamics
+    std::vector<double> m_nu, m_mass, m_gravityForces, m_bias, m_frameBias, m_frameVel, m_comBias;
+    double m_gravity{9.80665};
+    unsigned long m_velVersion{1}, m_dynVersion{0}, m_biasVersion{0}, m_biasVelVersion{0};
+    int m_biasFrame{-1};
 };
 
 }  // namespace BipedalLocomotion

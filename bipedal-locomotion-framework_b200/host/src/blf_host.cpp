@@ -297,6 +297,110 @@ bool KinDynBatch::getCenterOfMassJacobian(System::MatrixXd& J, std::size_t insta
     return true;
 }
 
+bool KinDynBatch::setRobotVelocity(const std::array<double, 6>& baseVelocity, const VectorXd& jointVelocities, std::size_t instance)
+{
+    if (!isValid() || jointVelocities.size() != m_n || instance >= m_N) {
+        log()->error("[KinDynBatch::setRobotVelocity] Invalid model, joint vector size or instance index.");
+        return false;
+    }
+    const std::size_t nv = m_n + 6;
+    if (m_nu.size() != nv * m_N) m_nu.assign(nv * m_N, 0.0);
+    std::copy(baseVelocity.begin(), baseVelocity.end(), m_nu.begin() + nv * instance);
+    std::copy(jointVelocities.begin(), jointVelocities.end(), m_nu.begin() + nv * instance + 6);
+    m_velVersion++;
+    return true;
+}
+
+bool KinDynBatch::setRobotVelocityBatch(const double* nu)
+{
+    if (!isValid() || !nu) return false;
+    m_nu.assign(nu, nu + (m_n + 6) * m_N);
+    m_velVersion++;
+    return true;
+}
+
+bool KinDynBatch::evalDynamics()
+{
+    if (!ensureKinProblem()) return false;
+    if (m_dynVersion == m_version) return true;
+    const std::size_t nv = m_n + 6;
+    m_mass.resize(nv * nv * m_N), m_gravityForces.resize(nv * m_N);
+    if (blfik_dynamics(m_kin, m_mass.data(), m_gravityForces.data(), m_gravity, BLFIK_MEM_HOST) != BLFIK_OK) {
+        log()->error("[KinDynBatch] {}", blfik_last_error());
+        return false;
+    }
+    m_dynVersion = m_version;
+    return true;
+}
+
+bool KinDynBatch::evalBias(int frame)
+{
+    if (frame >= static_cast<int>(m_frameNames.size())) {
+        log()->error("[KinDynBatch] Frame index {} out of range.", frame);
+        return false;
+    }
+    if (!ensureKinProblem()) return false;
+    const std::size_t nv = m_n + 6;
+    if (m_nu.size() != nv * m_N) m_nu.assign(nv * m_N, 0.0);   // a velocity never set is zero, as in iDynTree
+    if (m_biasVersion == m_version && m_biasVelVersion == m_velVersion && (frame < 0 || frame == m_biasFrame)) return true;
+    if (frame < 0) frame = m_biasFrame;                       // keep the frame of the last query in the cache
+    m_bias.resize(nv * m_N), m_comBias.resize(3 * m_N), m_frameBias.resize(6 * m_N), m_frameVel.resize(6 * m_N);
+    const int32_t f = frame;
+    if (blfik_bias_forces(m_kin, m_nu.data(), m_gravity, m_bias.data(), frame >= 0 ? &f : nullptr, frame >= 0 ? 1 : 0,
+                          frame >= 0 ? m_frameBias.data() : nullptr, frame >= 0 ? m_frameVel.data() : nullptr, m_comBias.data(), BLFIK_MEM_HOST) != BLFIK_OK) {
+        log()->error("[KinDynBatch] {}", blfik_last_error());
+        return false;
+    }
+    m_biasVersion = m_version, m_biasVelVersion = m_velVersion, m_biasFrame = frame;
+    return true;
+}
+
+bool KinDynBatch::getFreeFloatingMassMatrix(System::MatrixXd& M, std::size_t instance)
+{
+    if (instance >= m_N || !evalDynamics()) return false;
+    const std::size_t nv = m_n + 6;
+    M.resize(nv, nv);
+    std::copy(m_mass.begin() + nv * nv * instance, m_mass.begin() + nv * nv * (instance + 1), M.data.begin());
+    return true;
+}
+
+bool KinDynBatch::generalizedGravityForces(VectorXd& g, std::size_t instance)
+{
+    if (instance >= m_N || !evalDynamics()) return false;
+    const std::size_t nv = m_n + 6;
+    g.assign(m_gravityForces.begin() + nv * instance, m_gravityForces.begin() + nv * (instance + 1));
+    return true;
+}
+
+bool KinDynBatch::generalizedBiasForces(VectorXd& h, std::size_t instance)
+{
+    if (instance >= m_N || !evalBias(-1)) return false;
+    const std::size_t nv = m_n + 6;
+    h.assign(m_bias.begin() + nv * instance, m_bias.begin() + nv * (instance + 1));
+    return true;
+}
+
+bool KinDynBatch::getFrameBiasAcc(int frame, std::array<double, 6>& a, std::size_t instance)
+{
+    if (instance >= m_N || frame < 0 || !evalBias(frame)) return false;
+    std::copy_n(m_frameBias.begin() + 6 * instance, 6, a.begin());
+    return true;
+}
+
+bool KinDynBatch::getFrameVel(int frame, std::array<double, 6>& v, std::size_t instance)
+{
+    if (instance >= m_N || frame < 0 || !evalBias(frame)) return false;
+    std::copy_n(m_frameVel.begin() + 6 * instance, 6, v.begin());
+    return true;
+}
+
+bool KinDynBatch::getCenterOfMassBiasAcc(Vector3d& a, std::size_t instance)
+{
+    if (instance >= m_N || !evalBias(-1)) return false;
+    a = {m_comBias[3 * instance], m_comBias[3 * instance + 1], m_comBias[3 * instance + 2]};
+    return true;
+}
+
 namespace IK
 {
 

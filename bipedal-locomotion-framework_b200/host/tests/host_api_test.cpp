@@ -1151,6 +1151,104 @@ static void testFixedBase(const char* modelPath, std::size_t N)
     }
 }
 
+// KinDynBatch's dynamic quantities (what the TSID tasks read from kinDyn): mass matrix, gravity and bias forces, bias accelerations.
+// Checked by the physics that ties them together, on a batch of 3: M symmetric positive definite with the total mass on the base
+// translation block; bias forces at zero velocity = gravity forces; the Coriolis part is quadratic in the velocity; frame velocity
+// = J nu; and along a motion with constant nu (MIXED) the frame velocity changes by Jdot nu dt (finite difference through
+// ForwardEuler on the device).
+static void testKinDynDynamics(const char* modelPath)
+{
+    const std::size_t N = 3;
+    auto kinDyn = loadKinDyn(modelPath, N);
+    const std::size_t n = kinDyn->getNrOfDegreesOfFreedom(), nv = n + 6;
+    std::mt19937 gen(31);
+    std::uniform_real_distribution<double> uni(-1.0, 1.0);
+    std::vector<VectorXd> s(N), ds(N);
+    std::vector<std::array<double, 6>> vb(N);
+    std::vector<SO3d> R(N);
+    std::vector<Vector3d> p(N);
+    for (std::size_t i = 0; i < N; i++) {
+        s[i] = nominalJoints(*kinDyn, gen, 0.3);
+        ds[i].resize(n);
+        for (auto& v : ds[i]) v = uni(gen);
+        for (auto& v : vb[i]) v = uni(gen);
+        R[i] = SO3d::Exp({uni(gen), uni(gen), uni(gen)}), p[i] = {uni(gen), uni(gen), 0.7};
+        REQUIRE(kinDyn->setRobotState(p[i], R[i], s[i], i) && kinDyn->setRobotVelocity(vb[i], ds[i], i));
+    }
+    kinDyn->setGravityAcceleration(9.81);
+    const int hand = kinDyn->getFrameIndex("l_hand_palm");
+    REQUIRE(hand >= 0);
+    double totalMass = 0.0;
+    for (std::size_t i = 0; i < N; i++) {
+        System::MatrixXd M, J;
+        VectorXd g, h;
+        REQUIRE(kinDyn->getFreeFloatingMassMatrix(M, i) && kinDyn->generalizedGravityForces(g, i) && kinDyn->generalizedBiasForces(h, i));
+        REQUIRE(M.rows == nv && M.cols == nv && g.size() == nv && h.size() == nv);
+        if (i == 0) totalMass = M(0, 0);
+        REQUIRE(totalMass > 1.0 && std::abs(M(1, 1) - totalMass) < 1e-9 && std::abs(M(0, 1)) < 1e-9 && std::abs(M(0, 0) - totalMass) < 1e-9);
+        REQUIRE(std::abs(g[2] - 9.81 * totalMass) < 1e-8 && std::abs(g[0]) < 1e-10);
+        double asym = 0.0, mind = 1e300;
+        for (std::size_t a = 0; a < nv; a++) {
+            mind = std::min(mind, M(a, a));
+            for (std::size_t b = 0; b < nv; b++) asym = std::max(asym, std::abs(M(a, b) - M(b, a)));
+        }
+        REQUIRE(asym < 1e-10 && mind > 0.0);
+        std::array<double, 6> v, a;
+        REQUIRE(kinDyn->getFrameVel(hand, v, i) && kinDyn->getFrameBiasAcc(hand, a, i) && kinDyn->getFrameFreeFloatingJacobian(hand, J, i));
+        for (int r = 0; r < 6; r++) {
+            double acc = 0.0;
+            for (std::size_t c = 0; c < nv; c++) acc += J(r, c) * (c < 6 ? vb[i][c] : ds[i][c - 6]);
+            REQUIRE(std::abs(acc - v[r]) < 1e-11);
+        }
+    }
+    // zero velocity: bias = gravity; twice the velocity: four times the Coriolis part
+    std::vector<VectorXd> h1(N), g1(N);
+    for (std::size_t i = 0; i < N; i++) REQUIRE(kinDyn->generalizedBiasForces(h1[i], i) && kinDyn->generalizedGravityForces(g1[i], i));
+    for (std::size_t i = 0; i < N; i++) {
+        std::array<double, 6> v2 = vb[i];
+        VectorXd d2 = ds[i];
+        for (auto& v : v2) v *= 2.0;
+        for (auto& v : d2) v *= 2.0;
+        REQUIRE(kinDyn->setRobotVelocity(v2, d2, i));
+    }
+    for (std::size_t i = 0; i < N; i++) {
+        VectorXd h2;
+        REQUIRE(kinDyn->generalizedBiasForces(h2, i));
+        for (std::size_t c = 0; c < nv; c++) REQUIRE(std::abs((h2[c] - g1[i][c]) - 4.0 * (h1[i][c] - g1[i][c])) < 1e-8 * (1.0 + std::abs(h1[i][c])));
+        REQUIRE(kinDyn->setRobotVelocity({0, 0, 0, 0, 0, 0}, VectorXd(n, 0.0), i));
+    }
+    for (std::size_t i = 0; i < N; i++) {
+        VectorXd h0;
+        Vector3d cb;
+        REQUIRE(kinDyn->generalizedBiasForces(h0, i) && kinDyn->getCenterOfMassBiasAcc(cb, i));
+        for (std::size_t c = 0; c < nv; c++) REQUIRE(std::abs(h0[c] - g1[i][c]) < 1e-9 * (1.0 + std::abs(g1[i][c])));
+        REQUIRE(std::abs(cb[0]) + std::abs(cb[1]) + std::abs(cb[2]) == 0.0);
+    }
+    // Jdot nu against the change of J nu along a motion with nu held (central difference, ForwardEuler on the device)
+    const double d = 1e-5;
+    for (std::size_t i = 0; i < N; i++) REQUIRE(kinDyn->setRobotVelocity(vb[i], ds[i], i));
+    std::vector<std::array<double, 6>> bias(N), vp(N), vm(N);
+    for (std::size_t i = 0; i < N; i++) REQUIRE(kinDyn->getFrameBiasAcc(hand, bias[i], i));
+    for (int sign : {1, -1}) {
+        auto system = std::make_shared<FloatingBaseSystemVelocityKinematics>();
+        system->setBatchSize(N);
+        for (std::size_t i = 0; i < N; i++) {
+            std::array<double, 6> tw = vb[i];
+            VectorXd sd = ds[i];
+            for (auto& v : tw) v *= sign;
+            for (auto& v : sd) v *= sign;
+            REQUIRE(system->setState({p[i], R[i], s[i]}, static_cast<std::ptrdiff_t>(i)));
+            REQUIRE(system->setControlInput({tw, sd}, static_cast<std::ptrdiff_t>(i)));
+        }
+        ForwardEuler<FloatingBaseSystemVelocityKinematics> integrator;
+        REQUIRE(integrator.setIntegrationStep(10us) && integrator.setDynamicalSystem(system) && integrator.integrate(0s, 10us));
+        REQUIRE(kinDyn->setRobotStateBatch(system->basePositions().data(), system->baseQuaternions().data(), system->jointPositions().data()));
+        for (std::size_t i = 0; i < N; i++) REQUIRE(kinDyn->getFrameVel(hand, sign > 0 ? vp[i] : vm[i], i));
+    }
+    for (std::size_t i = 0; i < N; i++)
+        for (int r = 0; r < 6; r++) REQUIRE(std::abs((vp[i][r] - vm[i][r]) / (2 * d) - bias[i][r]) < 2e-5 * (1.0 + std::abs(bias[i][r])));
+}
+
 static void testIntegrator()
 {
     constexpr auto dT = 100us;
@@ -1410,6 +1508,7 @@ int main(int argc, char** argv)
         testJointSetPointSpline<BipedalLocomotion::Math::CubicSpline<VectorXd>>(argv[2], 70);   // the packed-record path
         testIntegrator();
         testAccelerationIntegrator();
+        testKinDynDynamics(argv[2]);
     }
     std::printf("%s: %d checks, %d failures\n", gpu ? "gpu" : "cpu", g_checks, g_failures);
     return g_failures == 0 ? 0 : 1;

@@ -438,10 +438,11 @@ int blfik_dynamics(blfik_problem* problem, double* mass_matrix, double* gravity_
  * (src/TSID/src/SE3Task.cpp:254, SO3Task.cpp:189, R3Task.cpp:219) and getCenterOfMassBiasAcc (src/TSID/src/CoMTask.cpp:195) for the
  * state of the problem and the generalised velocity nu [N][6+n] (MIXED: base linear and angular velocity in world coordinates,
  * joint velocities): bias_forces [N][6+n] = C(q, nu) nu + g(q), the h of M nu' + h = S'tau + sum J'f; frame_bias_acc
- * [N][nframes][6] = Jdot nu of the listed frames (linear, angular); com_bias_acc [N][3] = Jdot_com nu.  Any output may be NULL.
- * With nu = 0 the bias forces equal blfik_dynamics' gravity forces.                                                   */
+ * [N][nframes][6] = Jdot nu of the listed frames (linear, angular); frame_vel [N][nframes][6] = J nu of the same frames
+ * (kinDyn->getFrameVel, the controller state of the TSID SE3Task, SE3Task.cpp:256-263); com_bias_acc [N][3] = Jdot_com nu.
+ * Any output may be NULL.  With nu = 0 the bias forces equal blfik_dynamics' gravity forces.                          */
 int blfik_bias_forces(blfik_problem* problem, const double* nu, double gravity_acceleration, double* bias_forces, const int32_t* frames,
-                      int32_t nframes, double* frame_bias_acc, double* com_bias_acc, int32_t mem);
+                      int32_t nframes, double* frame_bias_acc, double* frame_vel, double* com_bias_acc, int32_t mem);
 /* Page-locked host memory, visible to every device of the process (cudaHostAllocPortable | cudaHostAllocMapped), for the
  * buffers of blfik_tick_packed / blfik_tick_host: the host classes keep their packed records, nu and status there so that the
  * library above the C ABI needs no CUDA headers.  No reference counterpart (Eigen vectors in pageable memory).            */

@@ -84,6 +84,8 @@ def test_bias_forces_and_bias_accelerations(mk):
     prob.set_state(p, q, s)
     h, fb, cb = prob.bias_forces(nu, frames, g)
     Mg, Gg = prob.dynamics(g)
+    kin = prob.kinematics(frames)
+    assert np.abs(prob.last_frame_velocities - np.einsum("nfrc,nc->nfr", kin["frame_jac"], nu)).max() <= 1e-12     # J nu of the frames
     o = Oracle(m, tasks)
     d = 1e-5
     for i in range(N):
