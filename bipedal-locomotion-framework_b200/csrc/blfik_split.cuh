@@ -347,8 +347,11 @@ struct SolveDims {
 #ifndef BLFIK_SOLVE_WPB
 #define BLFIK_SOLVE_WPB 1
 #endif
+#ifndef BLFIK_SOLVE_BIG_BLOCKS
+#define BLFIK_SOLVE_BIG_BLOCKS 11
+#endif
     static constexpr int WPB = SMALL ? BLFIK_SOLVE_WPB : 1;
-    static constexpr int BLOCKS = SMALL ? 16 / WPB : 10;
+    static constexpr int BLOCKS = SMALL ? 16 / WPB : BLFIK_SOLVE_BIG_BLOCKS;
     static constexpr bool NROW_SMEM = FastDims<NV, KP>::NROW_SMEM;
 };
 
