@@ -10,8 +10,10 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "bipedal-locomotion-framework_b200", "libblfik_cuda.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEEP = sys.argv[1:] or ["fast_kernelILi29ELi18", "blfik_tick_kernel", "blfik_tick_eq_kernel", "blfik_kinematics_kernel", "blfik_integrate_kernel",
-                       "blfik_spline_coefficients_kernel", "blfik_cubic_spline_coefficients_kernel"]
+KEEP = sys.argv[1:] or ["assemble_kernelILi18", "assemble_kernelILi32", "solve_kernelILi29ELi18", "solve_kernelILi29ELi32", "fast_kernelILi29ELi18",
+                       "blfik_tick_kernel", "blfik_tick_eq_kernel", "blfik_kinematics_kernel", "blfik_integrate_kernel",
+                       "blfik_integrate_acceleration_kernel", "blfik_dynamics_kernel", "blfik_bias_kernel",
+                       "blfik_spline_coefficients_kernel", "blfik_cubic_spline_coefficients_kernel", "blfik_evaluate_setpoint_kernel"]
 
 
 def main():
