@@ -605,6 +605,7 @@ struct blfik_problem {
     // two-launch path, longest first (SolveParams::slow_*): two lists and two stamp arrays used alternately, their lengths, the
     // stamp of the next solve launch and the stamp for which the list written last is valid (-1: none)
     int* d_slow = nullptr;         // [2][N] lists, [2][N] stamps, [2] lengths, [N] consecutive unsolved ticks
+    int* d_bins = nullptr;         // [64] robots per hardness bin, [64][N] their indices (hand-out order of the solve kernel)
     int solve_stamp = 0;
     int slow_list_for = -1;
     bool streaming_launch = false; // set around the one launch of the streaming-input mode
@@ -1835,6 +1836,13 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
             const int rc = dev_alloc(p, (size_t)5 * p->N + 2, &p->d_slow);   // zero-filled: no stamp matches
             if (rc) return rc;
         }
+        static const int bins_env = [] { const char* e = getenv("BLFIK_BINS"); return e ? atoi(e) : 1; }();
+        const bool bins = lpt && bins_env;
+        if (bins && !p->d_bins) {
+            const int rc = dev_alloc(p, (size_t)64 * p->N + 64, &p->d_bins, false);
+            if (rc) return rc;
+        }
+        A.bin_cap = S.bin_cap = p->N;
         S.slow_threshold = 16;
         static const int short_env = [] { const char* e = getenv("BLFIK_SHORT_BUDGET"); return e ? atoi(e) : 48; }();
         S.unsolved_run = lpt ? p->d_slow + 4 * p->N + 2 : nullptr, S.short_budget = short_env;
@@ -1852,6 +1860,12 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
                 S.slow_stamp_out = lpt ? stamps + (size_t)(par ^ 1) * p->N : nullptr;
                 A.slow_out_n = S.slow_out_n;
                 p->slow_list_for = lpt ? T + 1 : -1;
+                // the hardness bins order a tick that has no history to go by (a cold tick, the first tick of a rollout); once
+                // the previous tick's slow robots are known they lead, and the rest goes by index
+                const bool use_bins = bins && !in_valid;
+                A.bin_cnt = use_bins ? p->d_bins : nullptr, A.bin_list = use_bins ? p->d_bins + 64 : nullptr;
+                S.bin_cnt = A.bin_cnt, S.bin_list = A.bin_list;
+                if (use_bins) CU(cudaMemsetAsync(p->d_bins, 0, 64 * sizeof(int), stream));
             }
             if (step_weight_schedules(p, dt)) {   // MultiStateWeightProvider::advance() of every period, then the solver reads the weight
                 fill_weights();

@@ -46,6 +46,9 @@ struct AsmParams {
     double tnow;
     int* work_counter;          // kernel B's hand-out counter: zeroed here, one launch ahead
     int* slow_out_n;            // length of the slow-robot list the solve kernel of this tick writes (SolveParams): zeroed here; may be null
+    int* bin_cnt;               // [64] robots per hardness bin (zeroed by the host before the launch), null: no binning
+    int* bin_list;              // [64][bin_cap] robot indices per bin
+    long long bin_cap;
     int jw_task;                // a JointTrackingTask whose weight comes with the launch (weight schedule), -1: none
     double jw[32];
 };
@@ -76,6 +79,11 @@ struct SolveParams {
     const int* slow_stamp_in;
     int* slow_stamp_out;
     int stamp, slow_threshold;
+    // hand-out order of the robots that are not in slow_in: the hardness bins the assemble kernel of this tick filled, from the
+    // top bin down (null: by index)
+    const int* bin_cnt;
+    const int* bin_list;
+    long long bin_cap;
     // Consecutive ticks a robot has ended without a solution inside the iteration budget (closed loops: mostly robots whose
     // constraints have no feasible point, tick after tick).  Such a robot gets a short budget, and the full one again every
     // sixteenth tick; a tick that solves it clears the count.  Null: every robot gets the full budget.
@@ -374,13 +382,44 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
     // Persistent warps: each takes its next robot from a device counter (zeroed by the assemble kernel of the same tick), so
     // a slot is never idle between two robots (with one block per robot 13.6 of 16 warps were resident on average).
   const int n_slow = SP.slow_in_n ? *SP.slow_in_n : 0;
+  // s_bins[k]: how many robots the bins 63 ... 63 - k hold together (the top bin first), per warp of the block
+  __shared__ int s_bins_all[SolveDims<NV, KP>::WPB][66];
+  int* s_bins = s_bins_all[wib];
+  if (lane == 0) s_bins[64] = 0;   // [64]: the bins say something (more than one of them is occupied)
+  if (SP.bin_cnt) {
+      int p_hi = SP.bin_cnt[63 - lane], p_lo = SP.bin_cnt[31 - lane];
+      int cmax = p_hi > p_lo ? p_hi : p_lo;
+      for (int o = 16; o > 0; o >>= 1) {
+          const int other = __shfl_xor_sync(kFull, cmax, o);
+          cmax = other > cmax ? other : cmax;
+      }
+      for (int o = 1; o < 32; o <<= 1) {
+          const int a = __shfl_up_sync(kFull, p_hi, o), b = __shfl_up_sync(kFull, p_lo, o);
+          if (lane >= o) p_hi += a, p_lo += b;
+      }
+      const int t_hi = __shfl_sync(kFull, p_hi, 31);
+      s_bins[lane] = p_hi, s_bins[32 + lane] = p_lo + t_hi;
+      if (lane == 31) s_bins[64] = cmax < p_lo + t_hi;   // all robots in one bin: the order by index is as good, and cheaper
+  }
+  __syncwarp();
   for (;;) {
     long long robot = 0;
     if (lane == 0) {
         const int wi = atomicAdd(SP.work_counter, 1);
         if (wi < n_slow) {
             robot = SP.slow_in[wi];
-            if (SP.slow_stamp_in[robot] != SP.stamp) robot = -1;   // a stale entry: the linear hand-out takes this robot
+            if (SP.slow_stamp_in[robot] != SP.stamp) robot = -1;   // a stale entry: the ordinary hand-out takes this robot
+        } else if (s_bins[64]) {
+            const int v = wi - n_slow;
+            if (v >= s_bins[63]) {
+                robot = P.N;
+            } else {
+                int k = 0;   // the bin that holds item v: binary search over the running counts
+                for (int step = 32; step > 0; step >>= 1)
+                    if (v >= s_bins[k + step - 1]) k += step;
+                robot = SP.bin_list[(size_t)(63 - k) * SP.bin_cap + (v - (k ? s_bins[k - 1] : 0))];
+                if (n_slow > 0 && SP.slow_stamp_in[robot] == SP.stamp) robot = -1;   // handed out from the list
+            }
         } else {
             robot = P.first + (wi - n_slow);
             if (robot < P.N && n_slow > 0 && SP.slow_stamp_in[robot] == SP.stamp) robot = -1;   // handed out from the list
