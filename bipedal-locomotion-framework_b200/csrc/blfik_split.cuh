@@ -404,6 +404,7 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
   __syncwarp();
   for (;;) {
     long long robot = 0;
+    long long ahead = -1;   // the robot whose record the L2 is asked for: the one handed out prefetch_ahead items from now
     if (lane == 0) {
         const int wi = atomicAdd(SP.work_counter, 1);
         if (wi < n_slow) {
@@ -419,13 +420,21 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
                     if (v >= s_bins[k + step - 1]) k += step;
                 robot = SP.bin_list[(size_t)(63 - k) * SP.bin_cap + (v - (k ? s_bins[k - 1] : 0))];
                 if (n_slow > 0 && SP.slow_stamp_in[robot] == SP.stamp) robot = -1;   // handed out from the list
+                const int va = v + SP.prefetch_ahead;
+                if (va < s_bins[63]) {
+                    int ka = k;   // not below the bin of v
+                    while (va >= s_bins[ka]) ka++;
+                    ahead = SP.bin_list[(size_t)(63 - ka) * SP.bin_cap + (va - (ka ? s_bins[ka - 1] : 0))];
+                }
             }
         } else {
             robot = P.first + (wi - n_slow);
+            if (robot + SP.prefetch_ahead < P.N) ahead = robot + SP.prefetch_ahead;
             if (robot < P.N && n_slow > 0 && SP.slow_stamp_in[robot] == SP.stamp) robot = -1;   // handed out from the list
         }
     }
     robot = __shfl_sync(kFull, robot, 0);
+    ahead = __shfl_sync(kFull, ahead, 0);
     if (robot < 0) continue;
     if (robot >= P.N) break;
     int worst = 0, iters_prev = 0;
@@ -452,8 +461,8 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
     const double* rec = SP.qp + (size_t)robot * Rec::LEN;
     // Ask the L2 for the record of the robot that some warp takes about one robot-time from now: its loads then hit the L2
     // instead of reading DRAM cold (which robot this very warp gets next is not known: the hand-out is dynamic).
-    if (robot + SP.prefetch_ahead < P.N) {
-        const char* nxt = reinterpret_cast<const char*>(rec + (size_t)SP.prefetch_ahead * Rec::LEN);
+    if (ahead >= 0) {
+        const char* nxt = reinterpret_cast<const char*>(SP.qp + (size_t)ahead * Rec::LEN);
         for (int l = lane * 128; l < Rec::LEN * 8; l += 32 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + l));
     }
 
