@@ -479,12 +479,12 @@ def run_ours(args, rank: int, local_rank: int, world: int) -> None:
 
 
 # ncu captures of the shipped build (profiles/): DRAM bytes of one launch and warp-instructions of one step, keyed by workload
-NCU_TRAFFIC = {   # profiles/r2b_split_kernels_ncu_summary.txt, profiles/r2_eq_kernel_v3_ncu_summary.txt
-    ("blfik_solve_kernel", 3, 65536): 367.13e6 + 59.99e6,
-    ("blfik_assemble_kernel", 3, 65536): 183.88e6 + 471.59e6,
+NCU_TRAFFIC = {   # profiles/r2c_split_kernels_ncu_summary.txt, profiles/r2_eq_kernel_v3_ncu_summary.txt
+    ("blfik_solve_kernel", 3, 65536): 387.19e6 + 66.61e6,
+    ("blfik_assemble_kernel", 3, 65536): 185.93e6 + 474.26e6,
     ("blfik_tick_eq_kernel", 2, 4096): 5.10e6 + 0.03e6,
 }
-NCU_INSTR = {(3, 65536): 68165373 + 295098676}   # smsp__inst_executed.sum: assemble + solve
+NCU_INSTR = {(3, 65536): 70455143 + 302609305}   # smsp__inst_executed.sum: assemble + solve
 
 prob_settings = {"rho": 1.0, "sigma": 1e-2, "alpha": 1.6, "eps": 1e-7, "admm_iters": 10, "max_rounds": 8,
                  "polish_iters": 4, "eq_iters": 5}
