@@ -281,7 +281,8 @@ int blfik_set_limits(blfik_problem* problem, int32_t task, const double* upper_l
  * travel from tick to tick, inside a launch and across launches -- the robots that needed many iterations at the
  * previous tick are handed out first, and a robot that has been ending with MAX_ITER gets a quarter of the iteration
  * budget (the full one every sixteenth such tick; the first solved tick clears it).  Neither changes a robot that
- * solves every tick; blfik_set_state starts a new history.                                                  */
+ * solves every tick; blfik_set_state starts a new history.  A tick without history hands the robots out by how
+ * narrow their joint boxes are, the narrowest first; the order changes no result.                             */
 int blfik_tick(blfik_problem* problem, int32_t nticks, double dt, uint32_t flags);
 
 /* The whole reference-facing tick for callers whose data live in HOST memory (what the reference's caller does
