@@ -606,6 +606,7 @@ struct blfik_problem {
     // stamp of the next solve launch and the stamp for which the list written last is valid (-1: none)
     int* d_slow = nullptr;         // [2][N] lists, [2][N] stamps, [2] lengths, [N] consecutive unsolved ticks
     int* d_bins = nullptr;         // [64] robots per hardness bin, [64][N] their indices (hand-out order of the solve kernel)
+    int* d_bins_chunk = nullptr;   // the same for the chunk launches of the host tick: [kCounterSlots][64] counts, then [64 N] indices (a chunk's lists at 64 x first)
     int solve_stamp = 0;
     int slow_list_for = -1;
     bool streaming_launch = false; // set around the one launch of the streaming-input mode
@@ -1864,8 +1865,18 @@ static int launch_tick_range(blfik_problem* p, long long first, long long count,
                 // the previous tick's slow robots are known they lead, and the rest goes by index
                 const bool use_bins = bins && !in_valid;
                 A.bin_cnt = use_bins ? p->d_bins : nullptr, A.bin_list = use_bins ? p->d_bins + 64 : nullptr;
-                S.bin_cnt = A.bin_cnt, S.bin_list = A.bin_list;
                 if (use_bins) CU(cudaMemsetAsync(p->d_bins, 0, 64 * sizeof(int), stream));
+                // a chunk of the pipelined host tick: its own counters (by counter slot) and its own stretch of the lists
+                if (bins_env && !lpt && asm_stream && asm_done && nticks == 1 && p->N < 0x7fffff00LL / 64) {
+                    if (!p->d_bins_chunk) {
+                        const int rc = dev_alloc(p, (size_t)64 * kCounterSlots + (size_t)64 * p->N, &p->d_bins_chunk, false);
+                        if (rc) return rc;
+                    }
+                    A.bin_cnt = p->d_bins_chunk + 64 * counter_slot, A.bin_list = p->d_bins_chunk + 64 * kCounterSlots + 64 * first, A.bin_cap = count;
+                    S.bin_cap = count;
+                    CU(cudaMemsetAsync(A.bin_cnt, 0, 64 * sizeof(int), asm_stream));
+                }
+                S.bin_cnt = A.bin_cnt, S.bin_list = A.bin_list;
             }
             if (step_weight_schedules(p, dt)) {   // MultiStateWeightProvider::advance() of every period, then the solver reads the weight
                 fill_weights();
