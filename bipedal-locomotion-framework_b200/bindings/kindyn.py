@@ -24,6 +24,8 @@ class KinDynComputations:
         self._q = np.tile(np.array([0.0, 0.0, 0.0, 1.0]), (self.N, 1))
         self._s = np.zeros((self.N, self.n))
         self._version, self._kin_version, self._kin, self._model = 1, 0, None, None
+        self._nu = np.zeros((self.N, self.n + 6))     # generalised velocity, MIXED (set by setRobotState's velocity arguments)
+        self._gravity = 9.80665
 
     # ---- iDynTree-style model queries
     def model(self):
@@ -52,8 +54,9 @@ class KinDynComputations:
 
     # ---- state
     def setRobotState(self, world_T_base, s, base_velocity=None, s_dot=None, world_gravity=None, instance=None):
-        """``world_T_base`` 4x4 (or [N,4,4]), ``s`` [n] (or [N,n]); velocities and gravity are accepted and unused, as in
-        the IK path.  ``instance``: one robot of the batch (default: all of them)."""
+        """``world_T_base`` 4x4 (or [N,4,4]), ``s`` [n] (or [N,n]); ``base_velocity`` [6] (MIXED: linear and angular velocity of the
+        base in world coordinates), ``s_dot`` [n] and ``world_gravity`` [3] (its norm is used, along -z) are what the dynamic
+        queries below read; the IK path does not need them.  ``instance``: one robot of the batch (default: all of them)."""
         H = np.asarray(world_T_base, dtype=np.float64)
         s = np.asarray(s, dtype=np.float64)
         if H.shape[-2:] != (4, 4) or s.shape[-1] != self.n:
@@ -63,6 +66,12 @@ class KinDynComputations:
         self._p[sel] = H[..., :3, 3]
         self._q[sel] = _rot_to_quat(H[..., :3, :3]) if H.ndim == 3 else _rot_to_quat(H[:3, :3])[0]
         self._s[sel] = s
+        if base_velocity is not None:
+            self._nu[sel, :6] = np.asarray(base_velocity, dtype=np.float64)
+        if s_dot is not None:
+            self._nu[sel, 6:] = np.asarray(s_dot, dtype=np.float64)
+        if world_gravity is not None:
+            self._gravity = float(np.linalg.norm(np.asarray(world_gravity, dtype=np.float64)))
         self._version += 1
         return True
 
@@ -114,6 +123,30 @@ class KinDynComputations:
 
     def getCenterOfMassJacobian(self, instance=0):
         return self._problem().kinematics([], jac=True, com=True)["com_jac"][instance]
+
+    # ---- dynamic quantities the TSID tasks read (iDynTree names; MIXED representation; blfik_dynamics / blfik_bias_forces)
+    def getFreeFloatingMassMatrix(self, instance=0):
+        return self._problem().dynamics(self._gravity)[0][instance]
+
+    def generalizedGravityForces(self, instance=0):
+        return self._problem().dynamics(self._gravity)[1][instance]
+
+    def generalizedBiasForces(self, instance=0):
+        """C(q, nu) nu + g(q) (src/TSID/src/BaseDynamicsTask.cpp:178, JointDynamicsTask.cpp:233)"""
+        return self._problem().bias_forces(self._nu, (), self._gravity)[0][instance]
+
+    def getFrameBiasAcc(self, frame, instance=0):
+        """Jdot nu of the frame, linear then angular (src/TSID/src/SE3Task.cpp:254)"""
+        return self._problem().bias_forces(self._nu, [self._frame(frame)], self._gravity)[1][instance, 0]
+
+    def getFrameVel(self, frame, instance=0):
+        """J nu of the frame, linear then angular"""
+        prob = self._problem()
+        prob.bias_forces(self._nu, [self._frame(frame)], self._gravity)
+        return prob.last_frame_velocities[instance, 0]
+
+    def getCenterOfMassBiasAcc(self, instance=0):
+        return self._problem().bias_forces(self._nu, (), self._gravity)[2][instance]
 
     def batch_kinematics(self, frames, jac=True, com=True):
         """all robots at once: dict of ``frame_pos [N,F,3]``, ``frame_rot``, ``frame_jac [N,F,6,nv]``, ``com``, ``com_jac``"""

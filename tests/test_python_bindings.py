@@ -396,6 +396,33 @@ def test_floating_base_system_acceleration_kinematics():
 
 
 @pytest.mark.gpu
+def test_kindyn_dynamic_quantities():
+    """KinDynComputations' dynamic queries under iDynTree's names (what the TSID tasks read): the mass matrix is symmetric with the
+    total mass on the base translation block, bias forces at zero velocity are the gravity forces, the frame velocity is J nu, and
+    the Coriolis part is quadratic in the velocity."""
+    model = M.ergocub23()
+    n, nv = model.n, model.n + 6
+    _, kindyn = get_kindyn(model, 2)
+    rng = np.random.default_rng(8)
+    H = np.eye(4)
+    H[:3, 3] = [0.1, -0.2, 0.7]
+    s, v, sd = model.q_nominal + rng.uniform(-0.3, 0.3, n), rng.uniform(-1, 1, 6), rng.uniform(-1, 1, n)
+    g = np.array([0.0, 0.0, -9.81])
+    assert kindyn.setRobotState(H, s, v, sd, g)
+    Mm, G, h = kindyn.getFreeFloatingMassMatrix(), kindyn.generalizedGravityForces(), kindyn.generalizedBiasForces()
+    assert Mm.shape == (nv, nv) and np.abs(Mm - Mm.T).max() < 1e-10 and np.abs(Mm[:3, :3] - model.mass.sum() * np.eye(3)).max() < 1e-9
+    assert abs(G[2] - 9.81 * model.mass.sum()) < 1e-8
+    J = kindyn.getFrameFreeFloatingJacobian("l_sole")
+    assert kindyn.getFrameVel("l_sole") == pytest.approx(J @ np.concatenate([v, sd]), abs=1e-11)
+    a1 = kindyn.getFrameBiasAcc("l_sole")
+    assert kindyn.setRobotState(H, s, 2 * v, 2 * sd, g)
+    assert kindyn.generalizedBiasForces() - G == pytest.approx(4 * (h - G), abs=1e-8)
+    assert kindyn.getFrameBiasAcc("l_sole") == pytest.approx(4 * a1, abs=1e-9)
+    assert kindyn.setRobotState(H, s, 0 * v, 0 * sd, g)
+    assert kindyn.generalizedBiasForces() == pytest.approx(G, abs=1e-9) and np.abs(kindyn.getCenterOfMassBiasAcc()).max() == 0.0
+
+
+@pytest.mark.gpu
 def test_build_closed_loop_batch_and_fixed_base():
     """QPInverseKinematics.build from a parameter handler (QPInverseKinematicsTest.cpp:642-798) on a batch of 16 ergoCubs,
     closed with the Python integrator; then QPFixedBaseInverseKinematics: zero base twist on every tick."""
