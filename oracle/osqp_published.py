@@ -54,9 +54,11 @@ def ruiz_scale(P, q, A, l, u, iters=10):
 
 
 def solve(P, q, A, l, u, rho=0.1, sigma=1e-6, alpha=1.6, eps_abs=1e-3, eps_rel=1e-3, max_iter=4000, check_every=25,
-          adaptive_rho=True, scaling=10):
+          adaptive_rho=True, scaling=10, eps_prim_inf=1e-4, eps_dual_inf=1e-4):
     """OSQP Algorithm 1 on min 1/2 x'Px + q'x s.t. l <= Ax <= u.  Returns (x, y, status, iterations); status 0 solved,
-    1 maximum iterations reached."""
+    1 maximum iterations reached, 2 primal infeasible, 3 dual infeasible (paper section 3.4: the certificates on the increments
+    of y and x between two iterations, checked with the termination criteria; QPInverseKinematics::advance() fails on anything
+    but solved / solved inaccurate, QPInverseKinematics.cpp:518-523)."""
     n, m = P.shape[0], A.shape[0]
     Ps, qs, As, ls, us, D, E, c = ruiz_scale(P, q, A, l, u, scaling) if scaling else (P, q, A, l, u, np.ones(n), np.ones(m), 1.0)
     Dinv, Einv = 1.0 / D, 1.0 / E
@@ -78,6 +80,7 @@ def solve(P, q, A, l, u, rho=0.1, sigma=1e-6, alpha=1.6, eps_abs=1e-3, eps_rel=1
     x, z, y = np.zeros(n), np.zeros(m), np.zeros(m)
     status, it = 1, 0
     for it in range(1, max_iter + 1):
+        x_prev, y_prev = x, y
         rhs = np.concatenate([sigma * x - qs, z - y / rv])
         sol = Kinv @ rhs
         xt, nu = sol[:n], sol[n:]
@@ -98,6 +101,25 @@ def solve(P, q, A, l, u, rho=0.1, sigma=1e-6, alpha=1.6, eps_abs=1e-3, eps_rel=1
         if r_prim <= e_prim and r_dual <= e_dual:
             status = 0
             break
+        # certificates, in the unscaled problem (util.c is_primal_infeasible / is_dual_infeasible)
+        dy = E * (y - y_prev)
+        ndy = np.abs(dy).max() if m else 0.0
+        if ndy > 1e-30:
+            finite_u, finite_l = u < OSQP_INFTY * MIN_SCALING, l > -OSQP_INFTY * MIN_SCALING
+            support = float(np.sum(np.where(finite_u, u, 0.0) * np.maximum(dy, 0.0)) + np.sum(np.where(finite_l, l, 0.0) * np.minimum(dy, 0.0)))
+            unbounded_dir = np.any((dy > eps_prim_inf * ndy) & ~finite_u) or np.any((dy < -eps_prim_inf * ndy) & ~finite_l)
+            if not unbounded_dir and support <= -eps_prim_inf * ndy and np.abs(Dinv * (As.T @ (y - y_prev))).max() <= eps_prim_inf * ndy:
+                status = 2
+                break
+        dx = D * (x - x_prev)
+        ndx = np.abs(dx).max()
+        if ndx > 1e-30 and q @ dx <= -eps_dual_inf * ndx and np.abs(Dinv * (Ps @ (x - x_prev))).max() / c <= eps_dual_inf * ndx:
+            Adx = Einv * (As @ (x - x_prev))
+            ok_u = np.all((Adx <= eps_dual_inf * ndx) | (u >= OSQP_INFTY * MIN_SCALING))
+            ok_l = np.all((Adx >= -eps_dual_inf * ndx) | (l <= -OSQP_INFTY * MIN_SCALING))
+            if ok_u and ok_l:
+                status = 3
+                break
         if adaptive_rho:   # section 5.2: rho <- rho sqrt(normalised primal residual / normalised dual residual)
             pn = np.abs(Ax - z).max() / max(np.abs(Ax).max(), np.abs(z).max(), 1e-10) if m else 0.0
             dnm = np.abs(Px + qs + Aty).max() / max(np.abs(Px).max(), np.abs(Aty).max(), np.abs(qs).max(), 1e-10)
