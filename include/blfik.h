@@ -71,7 +71,10 @@ typedef enum { BLFIK_MEM_HOST = 0, BLFIK_MEM_DEVICE = 1 } blfik_mem;
 /* per-instance solver status after a tick */
 typedef enum {
     BLFIK_STATUS_SOLVED = 0,     /* KKT point certified (polish) or ADMM residuals below eps */
-    BLFIK_STATUS_MAX_ITER = 1,   /* OSQP "solved inaccurate": iteration budget exhausted      */
+    BLFIK_STATUS_MAX_ITER = 1,   /* OSQP "solved inaccurate": iteration budget exhausted.  There is no certificate of
+                                  * infeasibility on the device: an instance OSQP would prove primal infeasible (the reference's
+                                  * advance() fails there) also ends here, not in FAILED -- a caller that wants the reference's
+                                  * strictness treats this status as a failure                         */
     BLFIK_STATUS_FAILED = 2      /* infeasible bounds, factorisation breakdown or NaN         */
 } blfik_status;
 
