@@ -21,6 +21,7 @@ _lib = None
 
 MEM_HOST, MEM_DEVICE = 0, 1
 TICK_INTEGRATE, TICK_WARM_START, TICK_NO_FEEDFORWARD = 1, 2, 4
+TICK_STRICT = 16
 DEBUG_H, DEBUG_G, DEBUG_CEQ, DEBUG_BEQ, DEBUG_LO, DEBUG_HI = range(6)
 
 c_double_p = C.POINTER(C.c_double)
@@ -386,8 +387,9 @@ class Problem:
         _check(self.L.blfik_set_controller_mode(self.handle, int(task), int(enabled)))
 
     # ---- tick
-    def tick(self, nticks: int = 1, dt: float = 0.0, integrate: bool = False, warm_start: bool = False):
-        flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0)
+    def tick(self, nticks: int = 1, dt: float = 0.0, integrate: bool = False, warm_start: bool = False, strict: bool = False):
+        """``strict``: a tick that ends without a solution inside the iteration budget counts as FAILED (BLFIK_TICK_STRICT)"""
+        flags = (TICK_INTEGRATE if integrate else 0) | (TICK_WARM_START if warm_start else 0) | (TICK_STRICT if strict else 0)
         _check(self.L.blfik_tick(self.handle, int(nticks), float(dt), flags))
 
     def tick_host(self, base_pos, base_quat, s, setpoints, nu, status=None, dt: float = 0.0, integrate: bool = False,

@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(256) blfik_tick_kernel(const TickParams P)
                 for (int r = lane; r < me; r += 32) P.dbg.beq[(size_t)robot * me + r] = w.b[r];
             }
             res = k3_solve(P, w, warm, lane);
+            if (res.status == 1 && (P.flags & BLFIK_TICK_STRICT)) res.status = 2;
             iters += res.iters;
             worst = res.status > worst ? res.status : worst;
             if (res.status == 2) {   // no velocity to report (the reference's advance() fails): hold still

@@ -496,6 +496,7 @@ __global__ void __launch_bounds__(256, 2) blfik_tick_eq_kernel(const TickParams 
             k1_fk(P.m, w, bp, bq, s, lane);
             k2_assemble<true>(P, w, robot, s, lane, P.t0 + tick * P.dt);
             res = k3_solve_eq<KP>(P, w, warm, robot, lane);
+            if (res.status == 1 && (P.flags & BLFIK_TICK_STRICT)) res.status = 2;
             iters += res.iters;
             worst = res.status > worst ? res.status : worst;
             if (res.status == 2) {   // no velocity to report (the reference's advance() fails): hold still

@@ -1105,7 +1105,7 @@ __global__ void __launch_bounds__(FastDims<NV, KP>::WARPS * 32, 1) blfik_tick_fa
             // A failed tick ends this robot's rollout: no velocity to report (the reference's advance() fails), the state stays
             // where the failure happened.  The warp still walks through the remaining ticks -- its team meets at the phase
             // barriers of every tick -- but reports nothing from them.
-            if (dead) status = 2;
+            if (dead || (status == 1 && (P.flags & BLFIK_TICK_STRICT))) status = 2;
             worst = status > worst ? status : worst;
             if (status == 2) x = 0.0, dead = true;
             if (mine && active) {

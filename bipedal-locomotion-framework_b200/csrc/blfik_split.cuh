@@ -678,6 +678,7 @@ __global__ void __launch_bounds__(SolveDims<NV, KP>::WPB * 32, SolveDims<NV, KP>
         }
         if (!any_box) break;   // a pure equality QP has no second attempt
     }
+    if (status == 1 && (P.flags & BLFIK_TICK_STRICT)) status = 2;
     worst = status > worst ? status : worst;
     if (status == 2) x = 0.0;   // no velocity to report (the reference's advance() fails): hold still
     if (mine) {

@@ -86,6 +86,10 @@ typedef enum {
                                      the caller does not refresh every period)                                     */
 #define BLFIK_TICK_WARM_START 2u  /* start ADMM from the previous tick's (x, z, y) (reference does,
                                      QPInverseKinematics.cpp:494-509)                             */
+#define BLFIK_TICK_STRICT 16u     /* a tick that ends with MAX_ITER counts as FAILED: no velocity, the rollout of that robot ends
+                                     (what the reference does with an instance OSQP proves infeasible or cannot solve inside its
+                                     iteration limit, QPInverseKinematics.cpp:518-523; without the flag such a tick's best iterate
+                                     is reported and integrated like OSQP's "solved inaccurate")                          */
 
 /* Kinematic tree in the layout iDynTree's reduced models boil down to (stands in for
  * std::shared_ptr<iDynTree::KinDynComputations>, IKLinearTask.h:40).  Link 0 is the

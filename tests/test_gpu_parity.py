@@ -1109,6 +1109,40 @@ def test_c5_baseline_shape_vs_oracle():
     prob.close()
 
 
+@pytest.mark.parametrize("path", PATHS)
+def test_strict_flag_turns_unsolved_ticks_into_failures(path):
+    """BLFIK_TICK_STRICT: a tick that ends with MAX_ITER counts as FAILED, as the reference's advance() fails on an instance OSQP
+    proves infeasible or cannot solve (QPInverseKinematics.cpp:518-523): no velocity is reported, the robot's rollout ends where it
+    stands.  Robots with a foot target out of reach have no feasible point; without the flag they come back with status 1 and keep
+    moving, with it they are FAILED and frozen; the robots that solve are bit-identical either way."""
+    w = W.config(3)
+    N, NT = 192, 6
+    inp = W.synth_inputs(w, N, 3)
+    rng = np.random.default_rng(5)
+    far = rng.choice(N, 12, replace=False)
+    inp.setpoints[1][far, :3] += rng.uniform(0.5, 0.9, (12, 3))
+    out = {}
+    for strict in (False, True):
+        model, prob = make(w.model, w.tasks, N, path)
+        prob.set_inputs(inp)
+        prob.tick(NT, w.dt, integrate=True, warm_start=True, strict=strict)
+        st, _ = prob.get_status()
+        out[strict] = (st, prob.get_output(), prob.get_state())
+        prob.close()
+    st0, nu0, state0 = out[False]
+    st1, nu1, state1 = out[True]
+    assert np.all(st0[far] != 0) and (st0 == 1).sum() >= 8          # the unreachable targets end unsolved ...
+    assert np.array_equal(st1 == 2, st0 != 0)                        # ... and under the flag that is a failure
+    assert np.all(nu1[st1 == 2] == 0.0)
+    ok = st0 == 0
+    assert np.array_equal(nu0[ok], nu1[ok])
+    for a, b in zip(state0, state1):
+        assert np.array_equal(a[ok], b[ok])
+    moved = np.abs(state0[2][st0 == 1] - inp.s[st0 == 1]).max()
+    frozen = np.abs(state1[2][st0 == 1] - inp.s[st0 == 1]).max()
+    assert frozen < moved                                            # stopped at the first unsolved tick instead of drifting on
+
+
 def test_slow_first_handout_and_short_budget_leave_solved_robots_alone():
     """Closed loops on the two-launch path hand out first the robots that were slow at the previous tick, and give a robot
     that has been ending without a solution a short iteration budget (the full one every sixteenth tick).  Neither may touch a
