@@ -589,6 +589,10 @@ public:
     /** advance() starts every solve from the previous solution, as the reference warm-starts OSQP (QPInverseKinematics.cpp:494-509);
      *  false: every tick solves from scratch (what bench.py times) */
     void setWarmStart(bool on);
+    /** true: a robot whose QP is not solved inside the iteration budget counts as failed (BLFIK_TICK_STRICT) -- what the reference
+     *  does when OSQP proves the problem infeasible or hits its iteration limit (QPInverseKinematics.cpp:518-523); default false:
+     *  the best iterate is reported like OSQP's "solved inaccurate". */
+    void setStrictFailure(bool on);
     /** true if robot i's last solution is usable (status SOLVED or MAX_ITER, as the reference accepts Solved and
      *  SolvedInaccurate, QPInverseKinematics.cpp:518-523) */
     bool isOutputValid(std::size_t instance) const;

@@ -1268,7 +1268,7 @@ struct QPInverseKinematics::Impl {
     static constexpr std::size_t kPackedMin = 64;   // smaller batches keep the per-array calls (lower latency for a handful of robots)
     std::vector<int> devices;
     std::vector<Shard> shards;
-    bool compact{false}, packedPath{false}, warmStart{true};
+    bool compact{false}, packedPath{false}, warmStart{true}, strict{false};
     double* hRec{nullptr};
     double* hNu{nullptr};
     int32_t* hStatus{nullptr};
@@ -1574,10 +1574,11 @@ bool QPInverseKinematics::setDevices(const std::vector<int>& devices)
 
 void QPInverseKinematics::setCompactRecords(bool on) { m_pimpl->compact = on; }
 void QPInverseKinematics::setWarmStart(bool on) { m_pimpl->warmStart = on; }
+void QPInverseKinematics::setStrictFailure(bool on) { m_pimpl->strict = on; }
 
 bool QPInverseKinematics::advance()
 {
-    return tick(0.0, m_pimpl->warmStart ? BLFIK_TICK_WARM_START : 0u);
+    return tick(0.0, (m_pimpl->warmStart ? BLFIK_TICK_WARM_START : 0u) | (m_pimpl->strict ? BLFIK_TICK_STRICT : 0u));
 }
 
 bool QPInverseKinematics::syncState()
@@ -1600,7 +1601,7 @@ bool QPInverseKinematics::syncState()
 bool QPInverseKinematics::advanceAndIntegrate(std::chrono::nanoseconds dT, bool syncHostState)
 {
     const double dt = std::chrono::duration<double>(dT).count();
-    if (!tick(dt, (m_pimpl->warmStart ? BLFIK_TICK_WARM_START : 0u) | BLFIK_TICK_INTEGRATE)) return false;
+    if (!tick(dt, (m_pimpl->warmStart ? BLFIK_TICK_WARM_START : 0u) | (m_pimpl->strict ? BLFIK_TICK_STRICT : 0u) | BLFIK_TICK_INTEGRATE)) return false;
     if (syncHostState) return syncState();
     m_pimpl->deviceStateAhead = true;
     m_pimpl->stateVersionAtTick = m_pimpl->kinDyn->stateVersion();
